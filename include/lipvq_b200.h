@@ -1,0 +1,180 @@
+/*
+ * lipvq_b200.h -- C ABI of the B200-native LipVQ-VAE action-tokenizer hot path.
+ *
+ * The reference has no FFI: its seam is the Python class `LLFQVAE_V4`
+ * (robomimic/models/vq_vae/backbone_lfqvae_v5.py:51-84) resolved at
+ * robomimic/models/obs_nets.py:1225-1227.  Every entry point below replaces one torch-op
+ * sequence of that class (file:line cited per function); the Python mirror of the class
+ * (lipvq_vae_b200/tokenizer.py) is the only caller.
+ *
+ * Conventions
+ *   - all data pointers are DEVICE pointers into caller-owned, 16-byte aligned, contiguous
+ *     row-major fp32 buffers (indices: int64); nothing is allocated or kept across calls;
+ *   - `stream` is a cudaStream_t passed as void*; every call only enqueues work on it;
+ *   - scratch memory comes from the caller: `ws` of at least lipvq_workspace_bytes(...) bytes;
+ *   - return 0 on success, a negative LIPVQ_E* code otherwise; never throws;
+ *   - re-entrant across streams as long as the workspaces differ.
+ */
+#ifndef LIPVQ_B200_H
+#define LIPVQ_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define LIPVQ_ABI_VERSION 1
+
+enum {
+    LIPVQ_OK = 0,
+    LIPVQ_ESHAPE = -1,     /* a dimension is out of the supported range                    */
+    LIPVQ_EALIGN = -2,     /* a pointer is null or not 16-byte aligned                      */
+    LIPVQ_EARCH = -3,      /* the current device is not sm_100                              */
+    LIPVQ_EWORKSPACE = -4, /* ws_bytes is smaller than lipvq_workspace_bytes(...)           */
+    LIPVQ_ECUDA = -5       /* a CUDA runtime/driver call failed (see lipvq_last_cuda_error) */
+};
+
+/* search modes for lipvq_vq_argmin */
+enum {
+    LIPVQ_SEARCH_EXACT = 0,  /* fp32 direct-form scan sum_i (z_i-e_ki)^2 on CUDA cores        */
+    LIPVQ_SEARCH_TENSOR = 1  /* bf16 tcgen05 GEMM filter + fp32 direct-form rescore (default) */
+};
+
+/* dims of the 14 parameter tensors built at v5:52-68 */
+typedef struct {
+    int32_t F;  /* feature_dim (12 at obs_nets.py:2411)                */
+    int32_t H1; /* first hidden width, fixed 64 in the reference       */
+    int32_t H;  /* hidden_dim (128)                                    */
+    int32_t D;  /* latent_dim                                          */
+    int32_t K;  /* num_codes                                           */
+} lipvq_dims_t;
+
+/* the 14 tensors, state_dict order (v5:52-68) */
+typedef struct {
+    const float *enc0_w, *enc0_b; /* encoder.0.{weight[H1,F],bias[H1]}   */
+    const float *enc2_w, *enc2_b; /* encoder.2.{weight[H,H1],bias[H]}    */
+    const float *lat_W, *lat_b, *lat_ci; /* to_latent.{W[D,H],b[D],ci[D]}   */
+    const float *codebook;        /* quantizer.codebook[K,D]             */
+    const float *dec0_w, *dec0_b; /* decoder.0.{weight[H1,D],bias[H1]}   */
+    const float *dec2_w, *dec2_b; /* decoder.2.{weight[H,H1],bias[H]}    */
+    const float *out_w, *out_b;   /* to_output.{weight[F,H],bias[F]}     */
+} lipvq_params_t;
+
+/* gradient outputs, same layout; every tensor is OVERWRITTEN (not accumulated) */
+typedef struct {
+    float *enc0_w, *enc0_b, *enc2_w, *enc2_b;
+    float *lat_W, *lat_b, *lat_ci;
+    float *codebook;
+    float *dec0_w, *dec0_b, *dec2_w, *dec2_b;
+    float *out_w, *out_b;
+} lipvq_grads_t;
+
+/* activations kept between forward and backward (all [n_rows, width] fp32) */
+typedef struct {
+    float *a1, *h1; /* encoder.0 pre-activation / GELU output   [N,H1]            */
+    float *a2, *h2; /* encoder.2 pre-activation / GELU output   [N,H]             */
+    float *scale;   /* Lipschitz row scale min(1, softplus(ci)/sum|W|) [D]  v5:6-12 */
+    float *Wn;      /* normalised weight W*scale [D,H]                            */
+    float *z_e;     /* sigmoid(h2 Wn^T + b)  [N,D]   v5:22-24                      */
+    int64_t *idx;   /* nearest code per row [N]      v5:46                        */
+    float *z_q;     /* codebook[idx] [N,D]           v5:47                        */
+    float *c1, *d1; /* decoder.0 pre-activation / GELU output   [N,H1]            */
+    float *c2, *d2; /* decoder.2 pre-activation / GELU output   [N,H]             */
+    float *x_recon; /* to_output(...) [N,F]          v5:76                        */
+} lipvq_acts_t;
+
+int lipvq_abi_version(void);
+const char *lipvq_strerror(int code);
+/* last cudaError_t seen by this library on the calling thread (0 = none), and its string */
+int lipvq_last_cuda_error(void);
+const char *lipvq_last_cuda_error_string(void);
+/* 0 if the current device is compute capability 10.x, LIPVQ_EARCH otherwise */
+int lipvq_check_device(void);
+
+/* scratch bytes needed by any call below for n_rows rows with these dims */
+int lipvq_workspace_bytes(const lipvq_dims_t *dims, int64_t n_rows, size_t *out_bytes);
+
+/* Encoder: h=GELU(GELU(x W0^T+b0) W1^T+b1); z_e=sigmoid(h (W*scale)^T + b).
+ * Replaces v5:54-60 + normalization v5:6-12 + LipschitzMLP.forward v5:22-24 (called v5:71-72).
+ * acts: a1,h1,a2,h2,scale,Wn,z_e are written. */
+int lipvq_encoder_fwd(const lipvq_dims_t *dims, const lipvq_params_t *p, const float *x,
+                      int64_t n_rows, const lipvq_acts_t *acts, void *ws, size_t ws_bytes,
+                      void *stream);
+
+/* Nearest codeword: idx[n] = argmin_k ||z[n]-E[k]||_2, first minimal index on ties
+ * (LFQQuantizer.forward v5:37-46; the sign mask v5:39-40 is +-1 and vanishes under the norm).
+ * best_d2 (nullable) receives the fp32 direct-form squared distance of the winner.
+ * stats (nullable, int32[4]): [0] rows sent to the exact rescan, [1] candidate codes rescored. */
+int lipvq_vq_argmin(const float *z, const float *E, int64_t n_rows, int32_t D, int32_t K,
+                    int32_t mode, int64_t *idx, float *best_d2, int32_t *stats, void *ws,
+                    size_t ws_bytes, void *stream);
+
+/* z_q[n] = E[idx[n]] (v5:47); sse_q = sum (z_q - z_e)^2 (the value shared by the commitment and
+ * codebook losses, v5:80-81).  sse_q: device double[1], overwritten. */
+int lipvq_gather_loss(const float *z_e, const float *E, const int64_t *idx, int64_t n_rows,
+                      int32_t D, int32_t K, float *z_q, double *sse_q, void *ws, size_t ws_bytes,
+                      void *stream);
+
+/* Decoder: x_recon = GELU(GELU(z_q Wd0^T+bd0) Wd1^T+bd1) Wo^T + bo (v5:62-68, 75-76);
+ * sse_r = sum (x_recon - x)^2 (v5:79).  x may be null (then sse_r is not written).
+ * acts: c1,d1,c2,d2,x_recon are written. */
+int lipvq_decoder_fwd(const lipvq_dims_t *dims, const lipvq_params_t *p, const float *z_q,
+                      const float *x, int64_t n_rows, const lipvq_acts_t *acts, double *sse_r,
+                      void *ws, size_t ws_bytes, void *stream);
+
+/* loss = sse_r/(n_total*F) + 0.25*sse_q/(n_total*D) + 0.25*sse_q/(n_total*D)  (v5:79-83).
+ * out: device float[4] = {loss, recon, commit, codebook}. */
+int lipvq_loss_finalize(const double *sse_r, const double *sse_q, int64_t n_total, int32_t F,
+                        int32_t D, float *out, void *stream);
+
+/* Backward of the decoder + losses w.r.t. decoder/to_output parameters and z_q
+ * (autograd of v5:75-83 triggered at robomimic/algo/icl.py:969):
+ *   g_zq[n] = dRecon/dz_q[n] + 0.5*(z_q[n]-z_e[n])/(n_total*D).
+ * grad_scale: DEVICE scalar dL/dloss (nullable = 1), read by the kernels so the host never
+ * synchronises.  n_total = global row count (data parallel). */
+int lipvq_decoder_bwd(const lipvq_dims_t *dims, const lipvq_params_t *p, const float *x,
+                      int64_t n_rows, int64_t n_total, const float *grad_scale,
+                      const lipvq_acts_t *acts, const lipvq_grads_t *g, float *g_zq, void *ws,
+                      size_t ws_bytes, void *stream);
+
+/* sums[idx[n],:] += src[n,:]; counts[idx[n]] += 1 (counts nullable).  Serves the codebook
+ * gradient (index_put_ accumulate of autograd, v5:47) and the EMA cluster statistics.
+ * sums/counts are accumulated into: the caller zeroes them. */
+int lipvq_scatter_add(const float *src, const int64_t *idx, int64_t n_rows, int32_t D, int32_t K,
+                      float *sums, float *counts, void *stream);
+
+/* Backward of the encoder from the commitment term only (v5:80; there is no straight-through
+ * path): g_ze = 0.5*(z_e - z_q)/(n_total*D) -> sigmoid' -> Lipschitz-norm backward
+ * (through scale, sum|W|, softplus) -> MLP backward. */
+int lipvq_encoder_bwd(const lipvq_dims_t *dims, const lipvq_params_t *p, const float *x,
+                      int64_t n_rows, int64_t n_total, const float *grad_scale,
+                      const lipvq_acts_t *acts, const lipvq_grads_t *g, void *ws,
+                      size_t ws_bytes, void *stream);
+
+/* Whole forward in one call (inference / no-grad; LLFQVAE_V4.forward v5:70-84):
+ * x -> z_latent[N,D], idx[N], x_recon[N,F] (nullable), loss_out float[4] (nullable).
+ * Intermediates live in ws. */
+int lipvq_forward_fused(const lipvq_dims_t *dims, const lipvq_params_t *p, const float *x,
+                        int64_t n_rows, int64_t n_total, int32_t search_mode, float *z_latent,
+                        int64_t *idx, float *x_recon, float *loss_out, int32_t *stats, void *ws,
+                        size_t ws_bytes, void *stream);
+
+/* AdamW step over one flat fp32 tensor (torch.optim.AdamW semantics as configured at
+ * robomimic/algo/icl.py:886-889): decoupled weight decay, bias-corrected moments.
+ * step is the 1-based step count AFTER increment. */
+int lipvq_adamw_step(float *param, const float *grad, float *exp_avg, float *exp_avg_sq,
+                     int64_t n, int64_t step, float lr, float beta1, float beta2, float eps,
+                     float weight_decay, void *stream);
+
+/* EMA codebook update -- NOT in the reference (parity unpinned):
+ * n <- g n + (1-g) counts; m <- g m + (1-g) sums; E <- m / laplace(n). */
+int lipvq_ema_update(float *E, float *n_ema, float *m_ema, const float *counts,
+                     const float *sums, int32_t K, int32_t D, float gamma, float eps, void *ws,
+                     size_t ws_bytes, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* LIPVQ_B200_H */

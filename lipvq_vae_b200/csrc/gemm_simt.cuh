@@ -1,0 +1,209 @@
+// gemm_simt.cuh -- fp32 CUDA-core tile GEMM with fused epilogues, used for the small MLP layers
+// of the tokenizer (v5:54-68) and their backward.  Exact fp32 FMA arithmetic (the 1e-5 parity
+// tier); strides are generic so one kernel serves X*W^T, dY*W and dY^T*X (split over rows).
+#pragma once
+#include "common.cuh"
+
+namespace lipvq {
+
+struct GemmArgs {
+    const float *A; int64_t sam, sak;   // A(m,k) = A[m*sam + k*sak]
+    const float *B; int64_t sbk, sbn;   // B(k,n) = B[k*sbk + n*sbn]
+    float *C; int64_t ldc;              // C[m*ldc + n]
+    int64_t M; int N; int64_t K;
+    float alpha;                        // scale on the accumulator
+    const float *bias;                  // [N] or null
+    float *pre; int64_t ldpre;          // pre-activation output (nullable)
+    const float *dpre; int64_t lddpre;  // multiply by DACT'(dpre[m,n]) (nullable)
+    const float *aux1, *aux2; int64_t ldaux; float aux_alpha;  // += aux_alpha*(aux1-aux2)
+    const float *aux_scale_dev;         // device scalar multiplying aux_alpha (nullable)
+    int b_ones_col;                     // >=0: B(k, b_ones_col) == 1 (bias-gradient column)
+    int64_t k_chunk;                    // split-K: rows per blockIdx.z (0 = no split)
+};
+
+constexpr int GBM = 64, GBN = 64, GBK = 16, GLD = 68, GNT = 256;
+
+// A_KC: A is contiguous along k (sak==1); else contiguous along m (sam==1).
+// B_KC: B is contiguous along k (sbk==1); else contiguous along n (sbn==1).
+template <int ACT, int DACT, bool A_KC, bool B_KC>
+__global__ void __launch_bounds__(GNT) gemm_simt_kernel(const GemmArgs g) {
+    __shared__ __align__(16) float As[GBK][GLD];
+    __shared__ __align__(16) float Bs[GBK][GLD];
+    const int tid = threadIdx.x;
+    const int ty = tid >> 4, tx = tid & 15;
+    const int64_t m0 = (int64_t)blockIdx.x * GBM;
+    const int n0 = blockIdx.y * GBN;
+    int64_t kbeg = 0, kend = g.K;
+    if (g.k_chunk > 0) {
+        kbeg = (int64_t)blockIdx.z * g.k_chunk;
+        kend = kbeg + g.k_chunk < g.K ? kbeg + g.k_chunk : g.K;
+    }
+    float acc[4][4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+
+    float ra[4], rb[4];
+    auto fetch = [&](int64_t k0) {
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const int e = tid + q * GNT;
+            int m, k;
+            if (A_KC) { k = e & (GBK - 1); m = e >> 4; } else { m = e & (GBM - 1); k = e >> 6; }
+            const int64_t gm = m0 + m, gk = k0 + k;
+            ra[q] = (gm < g.M && gk < kend) ? __ldg(g.A + gm * g.sam + gk * g.sak) : 0.f;
+            int n, kb;
+            if (B_KC) { kb = e & (GBK - 1); n = e >> 4; } else { n = e & (GBN - 1); kb = e >> 6; }
+            const int gn = n0 + n;
+            const int64_t gkb = k0 + kb;
+            float v = 0.f;
+            if (gn < g.N && gkb < kend)
+                v = (gn == g.b_ones_col) ? 1.f : __ldg(g.B + gkb * g.sbk + (int64_t)gn * g.sbn);
+            rb[q] = v;
+        }
+    };
+    auto stash = [&]() {
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const int e = tid + q * GNT;
+            int m, k;
+            if (A_KC) { k = e & (GBK - 1); m = e >> 4; } else { m = e & (GBM - 1); k = e >> 6; }
+            As[k][m] = ra[q];
+            int n, kb;
+            if (B_KC) { kb = e & (GBK - 1); n = e >> 4; } else { n = e & (GBN - 1); kb = e >> 6; }
+            Bs[kb][n] = rb[q];
+        }
+    };
+
+    if (kbeg < kend) fetch(kbeg);
+    for (int64_t k0 = kbeg; k0 < kend; k0 += GBK) {
+        stash();
+        __syncthreads();
+        if (k0 + GBK < kend) fetch(k0 + GBK);
+#pragma unroll
+        for (int k = 0; k < GBK; ++k) {
+            const float4 a = *reinterpret_cast<const float4 *>(&As[k][ty * 4]);
+            const float4 b = *reinterpret_cast<const float4 *>(&Bs[k][tx * 4]);
+            const float av[4] = {a.x, a.y, a.z, a.w};
+            const float bv[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(av[i], bv[j], acc[i][j]);
+        }
+        __syncthreads();
+    }
+
+    float *C = g.C;
+    const float aux_alpha = g.aux_alpha * ((g.aux1 && g.aux_scale_dev) ? __ldg(g.aux_scale_dev) : 1.f);
+    if (g.k_chunk > 0) C += (int64_t)blockIdx.z * g.M * g.ldc;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const int64_t m = m0 + ty * 4 + i;
+        if (m >= g.M) continue;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int n = n0 + tx * 4 + j;
+            if (n >= g.N) continue;
+            float v = g.alpha * acc[i][j];
+            if (g.bias) v += __ldg(g.bias + n);
+            if (g.pre) g.pre[m * g.ldpre + n] = v;
+            v = apply_act<ACT>(v);
+            if (DACT == ACT_GELU) v *= gelu_grad_f(__ldg(g.dpre + m * g.lddpre + n));
+            if (g.aux1) v += aux_alpha * (__ldg(g.aux1 + m * g.ldaux + n) - __ldg(g.aux2 + m * g.ldaux + n));
+            C[m * g.ldc + n] = v;
+        }
+    }
+}
+
+inline GemmArgs gemm_args_zero() {
+    GemmArgs g;
+    g.A = nullptr; g.sam = g.sak = 0; g.B = nullptr; g.sbk = g.sbn = 0; g.C = nullptr; g.ldc = 0;
+    g.M = 0; g.N = 0; g.K = 0; g.alpha = 1.f; g.bias = nullptr; g.pre = nullptr; g.ldpre = 0;
+    g.dpre = nullptr; g.lddpre = 0; g.aux1 = g.aux2 = nullptr; g.ldaux = 0; g.aux_alpha = 0.f;
+    g.b_ones_col = -1; g.k_chunk = 0; g.aux_scale_dev = nullptr;
+    return g;
+}
+
+template <int ACT, int DACT, bool A_KC, bool B_KC>
+inline int gemm_launch(const GemmArgs &g, int splits, cudaStream_t st) {
+    if (g.M <= 0 || g.N <= 0) return LIPVQ_OK;
+    dim3 grid((unsigned)((g.M + GBM - 1) / GBM), (unsigned)((g.N + GBN - 1) / GBN), (unsigned)splits);
+    gemm_simt_kernel<ACT, DACT, A_KC, B_KC><<<grid, GNT, 0, st>>>(g);
+    LIPVQ_LAUNCH_OK();
+    return LIPVQ_OK;
+}
+
+// Y[M,N] = act(X[M,K] W[N,K]^T + b);  optional pre-activation output
+template <int ACT>
+inline int linear_fwd(const float *X, const float *W, const float *b, float *pre, float *Y,
+                      int64_t M, int N, int K, cudaStream_t st) {
+    GemmArgs g = gemm_args_zero();
+    g.A = X; g.sam = K; g.sak = 1;
+    g.B = W; g.sbk = 1; g.sbn = K;
+    g.C = Y; g.ldc = N; g.M = M; g.N = N; g.K = K;
+    g.bias = b; g.pre = pre; g.ldpre = N;
+    return gemm_launch<ACT, ACT_NONE, true, true>(g, 1, st);
+}
+
+// dX[M,K] = (dY[M,N] W[N,K]) (.) DACT'(dpre[M,K])  (+ aux_alpha*(aux1-aux2))
+template <int DACT>
+inline int linear_bwd_input(const float *dY, const float *W, const float *dpre, float *dX,
+                            int64_t M, int N, int K, const float *aux1, const float *aux2,
+                            float aux_alpha, const float *aux_scale_dev, cudaStream_t st) {
+    GemmArgs g = gemm_args_zero();
+    g.A = dY; g.sam = N; g.sak = 1;
+    g.B = W; g.sbk = K; g.sbn = 1;
+    g.C = dX; g.ldc = K; g.M = M; g.N = K; g.K = N;
+    g.dpre = dpre; g.lddpre = K;
+    g.aux1 = aux1; g.aux2 = aux2; g.ldaux = K; g.aux_alpha = aux_alpha; g.aux_scale_dev = aux_scale_dev;
+    return gemm_launch<ACT_NONE, DACT, true, false>(g, 1, st);
+}
+
+// Sum the split-K partials in split order (deterministic) and separate weight / bias gradients.
+// part: [splits][Nout][Kin+1]; dW[Nout,Kin]; db[Nout] (nullable)
+__global__ void splitk_reduce_kernel(const float *__restrict__ part, int splits, int Nout, int Kin,
+                                     float *__restrict__ dW, float *__restrict__ db) {
+    const int ld = Kin + 1;
+    const int total = Nout * ld;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+        float s = 0.f;
+        for (int z = 0; z < splits; ++z) s += part[(size_t)z * total + i];
+        const int m = i / ld, n = i - m * ld;
+        if (n < Kin) dW[(size_t)m * Kin + n] = s;
+        else if (db) db[m] = s;
+    }
+}
+
+inline int splits_for_rows(int64_t rows, int Nout, int Kin) {
+    const int tiles = ((Nout + GBM - 1) / GBM) * ((Kin + 1 + GBN - 1) / GBN);
+    int64_t s = (4 * kNumSMs + tiles - 1) / tiles;
+    const int64_t max_s = (rows + 255) / 256;   // at least 256 rows per split
+    if (s > max_s) s = max_s;
+    if (s < 1) s = 1;
+    return (int)s;
+}
+inline size_t splitk_ws_floats(int64_t rows, int Nout, int Kin) {
+    return (size_t)splits_for_rows(rows, Nout, Kin) * Nout * (Kin + 1);
+}
+
+// dW[Nout,Kin] = dY[rows,Nout]^T X[rows,Kin];  db[Nout] = column sums of dY.  part = scratch.
+inline int linear_bwd_weight(const float *dY, const float *X, float *dW, float *db, int64_t rows,
+                             int Nout, int Kin, float *part, cudaStream_t st) {
+    const int splits = splits_for_rows(rows, Nout, Kin);
+    GemmArgs g = gemm_args_zero();
+    g.A = dY; g.sam = 1; g.sak = Nout;
+    g.B = X; g.sbk = Kin; g.sbn = 1;
+    g.C = part; g.ldc = Kin + 1; g.M = Nout; g.N = Kin + 1; g.K = rows;
+    g.b_ones_col = Kin;
+    g.k_chunk = (rows + splits - 1) / splits;
+    g.k_chunk = (g.k_chunk + GBK - 1) / GBK * GBK;
+    LIPVQ_TRY((gemm_launch<ACT_NONE, ACT_NONE, false, false>(g, splits, st)));
+    const int total = Nout * (Kin + 1);
+    splitk_reduce_kernel<<<(total + 255) / 256, 256, 0, st>>>(part, splits, Nout, Kin, dW, db);
+    LIPVQ_LAUNCH_OK();
+    return LIPVQ_OK;
+}
+
+}  // namespace lipvq

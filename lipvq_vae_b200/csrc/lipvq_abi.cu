@@ -1,0 +1,311 @@
+// lipvq_abi.cu -- extern "C" entry points declared in include/lipvq_b200.h.
+// Host-side orchestration only: argument checks, workspace carving, kernel launches.
+#include <cstdio>
+#include <cstring>
+
+#include "common.cuh"
+#include "gemm_simt.cuh"
+#include "misc_kernels.cuh"
+#include "vq_exact.cuh"
+#include "vq_tensor.cuh"
+
+namespace lipvq {
+thread_local cudaError_t g_last_cuda_error = cudaSuccess;
+
+struct Bump {
+    char *base; size_t off, cap;
+    Bump(void *p, size_t c) : base((char *)p), off(0), cap(c) {}
+    template <typename T> T *take(size_t n) {
+        off = align_up(off, 256);
+        T *r = (T *)(base + off);
+        off += n * sizeof(T);
+        return r;
+    }
+    bool ok() const { return off <= cap; }
+};
+
+static bool dims_ok(const lipvq_dims_t *d) {
+    return d && d->F >= 1 && d->F <= 4096 && d->H1 >= 1 && d->H1 <= 4096 && d->H >= 1 && d->H <= 4096 &&
+           d->D >= 1 && d->D <= 8192 && d->K >= 1 && d->K <= (1 << 20);
+}
+
+static size_t max_splitk_floats(const lipvq_dims_t *d, int64_t n) {
+    size_t m = 0;
+    auto up = [&](int Nout, int Kin) { size_t v = splitk_ws_floats(n, Nout, Kin); if (v > m) m = v; };
+    up(d->F, d->H); up(d->H, d->H1); up(d->H1, d->D); up(d->D, d->H); up(d->H1, d->F);
+    return m;
+}
+
+static size_t workspace_bytes_impl(const lipvq_dims_t *d, int64_t n) {
+    const size_t N = (size_t)(n > 0 ? n : 1);
+    size_t fl = 0;
+    // forward intermediates (fused forward keeps all of them in ws)
+    fl += N * (size_t)(2 * d->H1 + 2 * d->H) * 2;   // a1,h1,a2,h2,c1,d1,c2,d2
+    fl += N * (size_t)d->D * 2;                      // z_e, z_q
+    fl += N * (size_t)d->F;                          // x_recon
+    fl += (size_t)d->D * d->H * 2 + d->D;            // Wn, gWn, scale
+    // backward scratch
+    fl += N * (size_t)(d->F + d->H + d->H1 + d->D);  // g_xr / g_pre / g_a2 / g_a1 style buffers
+    fl += max_splitk_floats(d, n);
+    fl += 4 * kRedBlocks + 64;
+    size_t bytes = fl * sizeof(float) + 64 * 256;    // alignment slack for the bump allocator
+    bytes += vq_tensor_ws_bytes(n, d->D, d->K);
+    bytes += N * sizeof(int64_t) + 4096;
+    return align_up(bytes, 256);
+}
+}  // namespace lipvq
+
+using namespace lipvq;
+
+extern "C" {
+
+int lipvq_abi_version(void) { return LIPVQ_ABI_VERSION; }
+
+const char *lipvq_strerror(int code) {
+    switch (code) {
+        case LIPVQ_OK: return "ok";
+        case LIPVQ_ESHAPE: return "unsupported shape";
+        case LIPVQ_EALIGN: return "null or misaligned pointer";
+        case LIPVQ_EARCH: return "device is not sm_100 (B200)";
+        case LIPVQ_EWORKSPACE: return "workspace too small";
+        case LIPVQ_ECUDA: return "CUDA error";
+        default: return "unknown error";
+    }
+}
+
+int lipvq_last_cuda_error(void) { return (int)g_last_cuda_error; }
+const char *lipvq_last_cuda_error_string(void) { return cudaGetErrorString(g_last_cuda_error); }
+
+int lipvq_check_device(void) {
+    int dev = 0, major = 0;
+    LIPVQ_CUDA_OK(cudaGetDevice(&dev));
+    LIPVQ_CUDA_OK(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev));
+    return major == 10 ? LIPVQ_OK : LIPVQ_EARCH;
+}
+
+int lipvq_workspace_bytes(const lipvq_dims_t *dims, int64_t n_rows, size_t *out_bytes) {
+    if (!dims_ok(dims) || n_rows < 0 || !out_bytes) return LIPVQ_ESHAPE;
+    *out_bytes = workspace_bytes_impl(dims, n_rows);
+    return LIPVQ_OK;
+}
+
+int lipvq_encoder_fwd(const lipvq_dims_t *d, const lipvq_params_t *p, const float *x, int64_t n,
+                      const lipvq_acts_t *a, void *ws, size_t ws_bytes, void *stream) {
+    (void)ws; (void)ws_bytes;
+    if (!dims_ok(d) || n < 0) return LIPVQ_ESHAPE;
+    if (!p || !a) return LIPVQ_EALIGN;
+    if (n == 0) return LIPVQ_OK;
+    if (!aligned16(x) || !aligned16(a->a1) || !aligned16(a->h1) || !aligned16(a->a2) || !aligned16(a->h2) ||
+        !aligned16(a->scale) || !aligned16(a->Wn) || !aligned16(a->z_e))
+        return LIPVQ_EALIGN;
+    cudaStream_t st = (cudaStream_t)stream;
+    lipschitz_prep_kernel<<<(d->D + 7) / 8, 256, 0, st>>>(p->lat_W, p->lat_ci, d->D, d->H, a->scale, a->Wn);
+    LIPVQ_LAUNCH_OK();
+    LIPVQ_TRY(linear_fwd<ACT_GELU>(x, p->enc0_w, p->enc0_b, a->a1, a->h1, n, d->H1, d->F, st));
+    LIPVQ_TRY(linear_fwd<ACT_GELU>(a->h1, p->enc2_w, p->enc2_b, a->a2, a->h2, n, d->H, d->H1, st));
+    LIPVQ_TRY(linear_fwd<ACT_SIGMOID>(a->h2, a->Wn, p->lat_b, nullptr, a->z_e, n, d->D, d->H, st));
+    return LIPVQ_OK;
+}
+
+int lipvq_vq_argmin(const float *z, const float *E, int64_t n, int32_t D, int32_t K, int32_t mode,
+                    int64_t *idx, float *best_d2, int32_t *stats, void *ws, size_t ws_bytes,
+                    void *stream) {
+    if (n < 0 || D < 1 || D > 8192 || K < 1 || K > (1 << 20)) return LIPVQ_ESHAPE;
+    if (n == 0) return LIPVQ_OK;
+    if (!aligned16(z) || !aligned16(E) || !idx) return LIPVQ_EALIGN;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (mode == LIPVQ_SEARCH_TENSOR && vq_tensor_supported(D, K)) {
+        if (ws_bytes < vq_tensor_ws_bytes(n, D, K) || !aligned16(ws)) return LIPVQ_EWORKSPACE;
+        return vq_tensor_launch(z, E, n, D, K, idx, best_d2, stats, ws, st);
+    }
+    if (stats) LIPVQ_CUDA_OK(cudaMemsetAsync(stats, 0, 4 * sizeof(int32_t), st));
+    return vq_exact_launch(z, E, n, D, K, nullptr, nullptr, idx, best_d2, st);
+}
+
+int lipvq_gather_loss(const float *z_e, const float *E, const int64_t *idx, int64_t n, int32_t D,
+                      int32_t K, float *z_q, double *sse_q, void *ws, size_t ws_bytes, void *stream) {
+    (void)K;
+    if (n < 0 || D < 1) return LIPVQ_ESHAPE;
+    if (!aligned16(z_e) || !aligned16(E) || !idx || !aligned16(z_q) || !sse_q) return LIPVQ_EALIGN;
+    if (ws_bytes < kRedBlocks * sizeof(float) || !aligned16(ws)) return LIPVQ_EWORKSPACE;
+    cudaStream_t st = (cudaStream_t)stream;
+    float *part = (float *)ws;
+    if ((D & 3) == 0)
+        gather_loss_kernel<true><<<kRedBlocks, 256, 0, st>>>(z_e, E, idx, n, D, z_q, part);
+    else
+        gather_loss_kernel<false><<<kRedBlocks, 256, 0, st>>>(z_e, E, idx, n, D, z_q, part);
+    LIPVQ_LAUNCH_OK();
+    partials_to_double_kernel<<<1, 256, 0, st>>>(part, kRedBlocks, sse_q);
+    LIPVQ_LAUNCH_OK();
+    return LIPVQ_OK;
+}
+
+int lipvq_decoder_fwd(const lipvq_dims_t *d, const lipvq_params_t *p, const float *z_q, const float *x,
+                      int64_t n, const lipvq_acts_t *a, double *sse_r, void *ws, size_t ws_bytes,
+                      void *stream) {
+    if (!dims_ok(d) || n < 0) return LIPVQ_ESHAPE;
+    if (!p || !a) return LIPVQ_EALIGN;
+    if (n == 0) return LIPVQ_OK;
+    if (!aligned16(z_q) || !aligned16(a->c1) || !aligned16(a->d1) || !aligned16(a->c2) || !aligned16(a->d2) ||
+        !aligned16(a->x_recon))
+        return LIPVQ_EALIGN;
+    cudaStream_t st = (cudaStream_t)stream;
+    LIPVQ_TRY(linear_fwd<ACT_GELU>(z_q, p->dec0_w, p->dec0_b, a->c1, a->d1, n, d->H1, d->D, st));
+    LIPVQ_TRY(linear_fwd<ACT_GELU>(a->d1, p->dec2_w, p->dec2_b, a->c2, a->d2, n, d->H, d->H1, st));
+    LIPVQ_TRY(linear_fwd<ACT_NONE>(a->d2, p->out_w, p->out_b, nullptr, a->x_recon, n, d->F, d->H, st));
+    if (x && sse_r) {
+        if (ws_bytes < kRedBlocks * sizeof(float) || !aligned16(ws)) return LIPVQ_EWORKSPACE;
+        float *part = (float *)ws;
+        sse_kernel<<<kRedBlocks, 256, 0, st>>>(a->x_recon, x, n * d->F, part);
+        LIPVQ_LAUNCH_OK();
+        partials_to_double_kernel<<<1, 256, 0, st>>>(part, kRedBlocks, sse_r);
+        LIPVQ_LAUNCH_OK();
+    }
+    return LIPVQ_OK;
+}
+
+int lipvq_loss_finalize(const double *sse_r, const double *sse_q, int64_t n_total, int32_t F, int32_t D,
+                        float *out, void *stream) {
+    if (n_total <= 0 || F < 1 || D < 1) return LIPVQ_ESHAPE;
+    if (!sse_q || !out) return LIPVQ_EALIGN;
+    loss_finalize_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(sse_r, sse_q, 1.0 / ((double)n_total * F),
+                                                            1.0 / ((double)n_total * D), out);
+    LIPVQ_LAUNCH_OK();
+    return LIPVQ_OK;
+}
+
+int lipvq_decoder_bwd(const lipvq_dims_t *d, const lipvq_params_t *p, const float *x, int64_t n,
+                      int64_t n_total, const float *grad_scale, const lipvq_acts_t *a, const lipvq_grads_t *g,
+                      float *g_zq, void *ws, size_t ws_bytes, void *stream) {
+    if (!dims_ok(d) || n <= 0 || n_total < n) return LIPVQ_ESHAPE;
+    if (!p || !a || !g || !aligned16(x) || !aligned16(g_zq)) return LIPVQ_EALIGN;
+    if (ws_bytes < workspace_bytes_impl(d, n) || !aligned16(ws)) return LIPVQ_EWORKSPACE;
+    cudaStream_t st = (cudaStream_t)stream;
+    Bump b(ws, ws_bytes);
+    float *g_xr = b.take<float>((size_t)n * d->F);
+    float *g_c2 = b.take<float>((size_t)n * d->H);
+    float *g_c1 = b.take<float>((size_t)n * d->H1);
+    float *part = b.take<float>(max_splitk_floats(d, n));
+    if (!b.ok()) return LIPVQ_EWORKSPACE;
+    const float a_r = (float)(2.0 / ((double)n_total * d->F));
+    const float a_q = (float)(0.5 / ((double)n_total * d->D));
+    scaled_diff_kernel<<<kRedBlocks, 256, 0, st>>>(a->x_recon, x, a_r, grad_scale, n * d->F, g_xr);
+    LIPVQ_LAUNCH_OK();
+    LIPVQ_TRY(linear_bwd_weight(g_xr, a->d2, g->out_w, g->out_b, n, d->F, d->H, part, st));
+    LIPVQ_TRY(linear_bwd_input<ACT_GELU>(g_xr, p->out_w, a->c2, g_c2, n, d->F, d->H, nullptr, nullptr, 0.f, nullptr, st));
+    LIPVQ_TRY(linear_bwd_weight(g_c2, a->d1, g->dec2_w, g->dec2_b, n, d->H, d->H1, part, st));
+    LIPVQ_TRY(linear_bwd_input<ACT_GELU>(g_c2, p->dec2_w, a->c1, g_c1, n, d->H, d->H1, nullptr, nullptr, 0.f, nullptr, st));
+    LIPVQ_TRY(linear_bwd_weight(g_c1, a->z_q, g->dec0_w, g->dec0_b, n, d->H1, d->D, part, st));
+    LIPVQ_TRY(linear_bwd_input<ACT_NONE>(g_c1, p->dec0_w, nullptr, g_zq, n, d->H1, d->D, a->z_q, a->z_e, a_q, grad_scale, st));
+    return LIPVQ_OK;
+}
+
+int lipvq_scatter_add(const float *src, const int64_t *idx, int64_t n, int32_t D, int32_t K, float *sums,
+                      float *counts, void *stream) {
+    if (n < 0 || D < 1 || K < 1) return LIPVQ_ESHAPE;
+    if (n == 0) return LIPVQ_OK;
+    if (!aligned16(src) || !idx || !aligned16(sums)) return LIPVQ_EALIGN;
+    const int64_t blocks = (n + SC_ROWS - 1) / SC_ROWS;
+    scatter_add_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(src, idx, n, D, K, sums, counts);
+    LIPVQ_LAUNCH_OK();
+    return LIPVQ_OK;
+}
+
+int lipvq_encoder_bwd(const lipvq_dims_t *d, const lipvq_params_t *p, const float *x, int64_t n,
+                      int64_t n_total, const float *grad_scale, const lipvq_acts_t *a, const lipvq_grads_t *g,
+                      void *ws, size_t ws_bytes, void *stream) {
+    if (!dims_ok(d) || n <= 0 || n_total < n) return LIPVQ_ESHAPE;
+    if (!p || !a || !g || !aligned16(x)) return LIPVQ_EALIGN;
+    if (ws_bytes < workspace_bytes_impl(d, n) || !aligned16(ws)) return LIPVQ_EWORKSPACE;
+    cudaStream_t st = (cudaStream_t)stream;
+    Bump b(ws, ws_bytes);
+    float *g_pre = b.take<float>((size_t)n * d->D);
+    float *g_a2 = b.take<float>((size_t)n * d->H);
+    float *g_a1 = b.take<float>((size_t)n * d->H1);
+    float *gWn = b.take<float>((size_t)d->D * d->H);
+    float *part = b.take<float>(max_splitk_floats(d, n));
+    if (!b.ok()) return LIPVQ_EWORKSPACE;
+    const float a_q = (float)(0.5 / ((double)n_total * d->D));
+    commit_sigmoid_bwd_kernel<<<kRedBlocks, 256, 0, st>>>(a->z_e, a->z_q, a_q, grad_scale, n * d->D, g_pre);
+    LIPVQ_LAUNCH_OK();
+    LIPVQ_TRY(linear_bwd_weight(g_pre, a->h2, gWn, g->lat_b, n, d->D, d->H, part, st));
+    lipschitz_bwd_kernel<<<(d->D + 7) / 8, 256, 0, st>>>(gWn, p->lat_W, p->lat_ci, a->scale, d->D, d->H,
+                                                        g->lat_W, g->lat_ci);
+    LIPVQ_LAUNCH_OK();
+    LIPVQ_TRY(linear_bwd_input<ACT_GELU>(g_pre, a->Wn, a->a2, g_a2, n, d->D, d->H, nullptr, nullptr, 0.f, nullptr, st));
+    LIPVQ_TRY(linear_bwd_weight(g_a2, a->h1, g->enc2_w, g->enc2_b, n, d->H, d->H1, part, st));
+    LIPVQ_TRY(linear_bwd_input<ACT_GELU>(g_a2, p->enc2_w, a->a1, g_a1, n, d->H, d->H1, nullptr, nullptr, 0.f, nullptr, st));
+    LIPVQ_TRY(linear_bwd_weight(g_a1, x, g->enc0_w, g->enc0_b, n, d->H1, d->F, part, st));
+    return LIPVQ_OK;
+}
+
+int lipvq_forward_fused(const lipvq_dims_t *d, const lipvq_params_t *p, const float *x, int64_t n,
+                        int64_t n_total, int32_t search_mode, float *z_latent, int64_t *idx,
+                        float *x_recon, float *loss_out, int32_t *stats, void *ws, size_t ws_bytes,
+                        void *stream) {
+    if (!dims_ok(d) || n < 0 || n_total < n) return LIPVQ_ESHAPE;
+    if (n == 0) return LIPVQ_OK;
+    if (!p || !aligned16(x) || !aligned16(z_latent)) return LIPVQ_EALIGN;
+    if (ws_bytes < workspace_bytes_impl(d, n) || !aligned16(ws)) return LIPVQ_EWORKSPACE;
+    cudaStream_t st = (cudaStream_t)stream;
+    Bump b(ws, ws_bytes);
+    lipvq_acts_t a;
+    a.a1 = b.take<float>((size_t)n * d->H1); a.h1 = b.take<float>((size_t)n * d->H1);
+    a.a2 = b.take<float>((size_t)n * d->H);  a.h2 = b.take<float>((size_t)n * d->H);
+    a.scale = b.take<float>(d->D); a.Wn = b.take<float>((size_t)d->D * d->H);
+    a.z_e = b.take<float>((size_t)n * d->D);
+    a.idx = idx ? idx : b.take<int64_t>(n);
+    a.z_q = z_latent;
+    a.c1 = a.a1; a.d1 = a.h1; a.c2 = a.a2; a.d2 = a.h2;   // encoder activations are dead by then
+    a.x_recon = x_recon ? x_recon : b.take<float>((size_t)n * d->F);
+    double *sse = b.take<double>(2);
+    float *part = b.take<float>(kRedBlocks);
+    const size_t vq_bytes = vq_tensor_ws_bytes(n, d->D, d->K);
+    void *vq_ws = b.take<char>(vq_bytes);
+    if (!b.ok()) return LIPVQ_EWORKSPACE;
+    LIPVQ_TRY(lipvq_encoder_fwd(d, p, x, n, &a, nullptr, 0, stream));
+    LIPVQ_TRY(lipvq_vq_argmin(a.z_e, p->codebook, n, d->D, d->K, search_mode, a.idx, nullptr, stats, vq_ws,
+                              vq_bytes, stream));
+    LIPVQ_TRY(lipvq_gather_loss(a.z_e, p->codebook, a.idx, n, d->D, d->K, a.z_q, sse + 1, part,
+                                kRedBlocks * sizeof(float), stream));
+    LIPVQ_TRY(lipvq_decoder_fwd(d, p, a.z_q, x, n, &a, sse, part, kRedBlocks * sizeof(float), stream));
+    if (loss_out) LIPVQ_TRY(lipvq_loss_finalize(sse, sse + 1, n_total, d->F, d->D, loss_out, stream));
+    (void)st;
+    return LIPVQ_OK;
+}
+
+int lipvq_adamw_step(float *param, const float *grad, float *exp_avg, float *exp_avg_sq, int64_t n,
+                     int64_t step, float lr, float beta1, float beta2, float eps, float weight_decay,
+                     void *stream) {
+    if (n < 0 || step < 1) return LIPVQ_ESHAPE;
+    if (n == 0) return LIPVQ_OK;
+    if (!param || !grad || !exp_avg || !exp_avg_sq) return LIPVQ_EALIGN;
+    const double bc1 = 1.0 - pow((double)beta1, (double)step);
+    const double bc2 = 1.0 - pow((double)beta2, (double)step);
+    int64_t blocks = (n + 255) / 256;
+    if (blocks > 8 * kNumSMs) blocks = 8 * kNumSMs;
+    adamw_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(param, grad, exp_avg, exp_avg_sq, n, lr,
+                                                                   beta1, beta2, eps, weight_decay,
+                                                                   (float)bc1, (float)sqrt(bc2));
+    LIPVQ_LAUNCH_OK();
+    return LIPVQ_OK;
+}
+
+int lipvq_ema_update(float *E, float *n_ema, float *m_ema, const float *counts, const float *sums,
+                     int32_t K, int32_t D, float gamma, float eps, void *ws, size_t ws_bytes, void *stream) {
+    if (K < 1 || D < 1) return LIPVQ_ESHAPE;
+    if (!E || !n_ema || !m_ema || !counts || !sums) return LIPVQ_EALIGN;
+    if (ws_bytes < 64 * sizeof(float) + 256 + sizeof(double) || !aligned16(ws)) return LIPVQ_EWORKSPACE;
+    cudaStream_t st = (cudaStream_t)stream;
+    float *part = (float *)ws;
+    double *tot = (double *)((char *)ws + 256);
+    ema_counts_kernel<<<64, 256, 0, st>>>(n_ema, counts, K, gamma, part);
+    LIPVQ_LAUNCH_OK();
+    partials_to_double_kernel<<<1, 256, 0, st>>>(part, 64, tot);
+    LIPVQ_LAUNCH_OK();
+    ema_apply_kernel<<<kRedBlocks, 256, 0, st>>>(E, n_ema, m_ema, sums, tot, K, D, gamma, eps);
+    LIPVQ_LAUNCH_OK();
+    return LIPVQ_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,265 @@
+// misc_kernels.cuh -- HBM-bound passes of the tokenizer: Lipschitz weight normalisation,
+// codeword gather + commitment SSE, reconstruction SSE, scatter-add, elementwise backward
+// pieces, loss finalisation, AdamW and the EMA extension.
+#pragma once
+#include "common.cuh"
+
+namespace lipvq {
+
+// ---------------------------------------------------------------- Lipschitz normalisation
+// scale_i = min(1, softplus(ci_i) / sum_j |W_ij|);  Wn = W * scale   (v5:6-12)
+// one warp per row of W[D,H]
+__global__ void lipschitz_prep_kernel(const float *__restrict__ W, const float *__restrict__ ci,
+                                      int D, int H, float *__restrict__ scale,
+                                      float *__restrict__ Wn) {
+    const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
+    if (row >= D) return;
+    float s = 0.f;
+    for (int j = lane; j < H; j += 32) s += fabsf(W[(size_t)row * H + j]);
+    s = warp_sum(s);
+    const float sc = fminf(1.0f, softplus_f(ci[row]) / s);
+    if (lane == 0) scale[row] = sc;
+    for (int j = lane; j < H; j += 32) Wn[(size_t)row * H + j] = W[(size_t)row * H + j] * sc;
+}
+
+// Backward through Wn = W * min(1, softplus(ci)/sum|W|)  (autograd of v5:6-12):
+//   dot_i = sum_j gWn_ij W_ij;  on the ratio branch (ratio<1; half weight on equality):
+//   gW_ij = gWn_ij*scale_i - dot_i*softplus(ci_i)/r_i^2 * sign(W_ij);  gci_i = dot_i/r_i*sigmoid(ci_i)
+__global__ void lipschitz_bwd_kernel(const float *__restrict__ gWn, const float *__restrict__ W,
+                                     const float *__restrict__ ci, const float *__restrict__ scale,
+                                     int D, int H, float *__restrict__ gW, float *__restrict__ gci) {
+    const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
+    if (row >= D) return;
+    float r = 0.f, dot = 0.f;
+    for (int j = lane; j < H; j += 32) {
+        const float w = W[(size_t)row * H + j];
+        r += fabsf(w);
+        dot = fmaf(gWn[(size_t)row * H + j], w, dot);
+    }
+    r = warp_sum(r);
+    dot = warp_sum(dot);
+    const float sp = softplus_f(ci[row]);
+    const float ratio = sp / r;
+    const float wr = ratio < 1.0f ? 1.0f : (ratio == 1.0f ? 0.5f : 0.0f);
+    const float g_ratio = dot * wr;
+    const float coef = g_ratio * (-sp / (r * r));
+    const float sc = scale[row];
+    for (int j = lane; j < H; j += 32) {
+        const float w = W[(size_t)row * H + j];
+        const float sg = (w > 0.f) ? 1.f : ((w < 0.f) ? -1.f : 0.f);
+        gW[(size_t)row * H + j] = gWn[(size_t)row * H + j] * sc + coef * sg;
+    }
+    if (lane == 0) gci[row] = g_ratio / r * sigmoid_f(ci[row]);
+}
+
+// ---------------------------------------------------------------- deterministic SSE reduction
+// stage 2: sum per-block partials in index order, in double.
+__global__ void partials_to_double_kernel(const float *__restrict__ part, int n, double *__restrict__ out) {
+    __shared__ double sm[32];
+    double s = 0.0;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) s += (double)part[i];
+    s = warp_sum_d(s);
+    if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = s;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        double r = threadIdx.x < (blockDim.x >> 5) ? sm[threadIdx.x] : 0.0;
+        r = warp_sum_d(r);
+        if (threadIdx.x == 0) *out = r;
+    }
+}
+
+constexpr int kRedBlocks = 4 * kNumSMs;  // grid of the streaming passes (4 CTAs per SM)
+
+// z_q[n,:] = E[idx[n],:]; partial[b] = sum over the block's elements of (z_q - z_e)^2  (v5:47,80-81)
+template <bool VEC4>
+__global__ void __launch_bounds__(256) gather_loss_kernel(
+    const float *__restrict__ z_e, const float *__restrict__ E, const int64_t *__restrict__ idx,
+    int64_t n_rows, int D, float *__restrict__ z_q, float *__restrict__ partial) {
+    __shared__ float red[8];
+    float s = 0.f;
+    if (VEC4) {
+        const int dq = D >> 2;
+        const int64_t total = n_rows * dq;
+        for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+             i += (int64_t)gridDim.x * blockDim.x) {
+            const int64_t n = i / dq;
+            const int c = (int)(i - n * dq);
+            const int64_t k = idx[n];
+            const float4 e = __ldg(reinterpret_cast<const float4 *>(E + k * D) + c);
+            const float4 z = __ldg(reinterpret_cast<const float4 *>(z_e + n * D) + c);
+            reinterpret_cast<float4 *>(z_q + n * D)[c] = e;
+            const float dx = e.x - z.x, dy = e.y - z.y, dz = e.z - z.z, dw = e.w - z.w;
+            s += dx * dx + dy * dy + dz * dz + dw * dw;
+        }
+    } else {
+        const int64_t total = n_rows * D;
+        for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+             i += (int64_t)gridDim.x * blockDim.x) {
+            const int64_t n = i / D;
+            const int c = (int)(i - n * D);
+            const float e = __ldg(E + idx[n] * D + c);
+            const float d = e - __ldg(z_e + i);
+            z_q[i] = e;
+            s += d * d;
+        }
+    }
+    s = block_sum<256>(s, red);
+    if (threadIdx.x == 0) partial[blockIdx.x] = s;
+}
+
+// partial[b] = sum (a - b)^2 over a flat range
+__global__ void __launch_bounds__(256) sse_kernel(const float *__restrict__ a, const float *__restrict__ b,
+                                                  int64_t n, float *__restrict__ partial) {
+    __shared__ float red[8];
+    float s = 0.f;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+         i += (int64_t)gridDim.x * blockDim.x) {
+        const float d = a[i] - b[i];
+        s += d * d;
+    }
+    s = block_sum<256>(s, red);
+    if (threadIdx.x == 0) partial[blockIdx.x] = s;
+}
+
+// out = alpha * (a - b)
+__global__ void scaled_diff_kernel(const float *__restrict__ a, const float *__restrict__ b,
+                                   float alpha, const float *__restrict__ gs, int64_t n,
+                                   float *__restrict__ out) {
+    if (gs) alpha *= *gs;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+         i += (int64_t)gridDim.x * blockDim.x)
+        out[i] = alpha * (a[i] - b[i]);
+}
+
+// g_pre = alpha * (z_e - z_q) * z_e * (1 - z_e)   (commitment gradient through the sigmoid)
+__global__ void commit_sigmoid_bwd_kernel(const float *__restrict__ z_e, const float *__restrict__ z_q,
+                                          float alpha, const float *__restrict__ gs, int64_t n,
+                                   float *__restrict__ out) {
+    if (gs) alpha *= *gs;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+         i += (int64_t)gridDim.x * blockDim.x) {
+        const float ze = z_e[i];
+        out[i] = alpha * (ze - z_q[i]) * ze * (1.0f - ze);
+    }
+}
+
+__global__ void loss_finalize_kernel(const double *sse_r, const double *sse_q, double inv_nf,
+                                     double inv_nd, float *out) {
+    if (threadIdx.x == 0 && blockIdx.x == 0) {
+        const double recon = sse_r ? (*sse_r) * inv_nf : 0.0;
+        const double commit = (*sse_q) * inv_nd;
+        out[0] = (float)(recon + 0.25 * commit + 0.25 * commit);
+        out[1] = (float)recon;
+        out[2] = (float)commit;
+        out[3] = (float)commit;
+    }
+}
+
+// ---------------------------------------------------------------- scatter-add (k8)
+// One CTA takes 256 consecutive rows, sorts their (code,row) keys in shared memory (bitonic),
+// and each warp then walks 32 sorted entries: runs of equal code are summed in registers and
+// flushed with ONE atomicAdd per (run, column) -- so a collapsed codebook (every row on one code,
+// SURVEY 0.9) costs gridDim atomics per address instead of n_rows.
+constexpr int SC_ROWS = 256;
+__global__ void __launch_bounds__(256) scatter_add_kernel(
+    const float *__restrict__ src, const int64_t *__restrict__ idx, int64_t n_rows, int D, int K,
+    float *__restrict__ sums, float *__restrict__ counts) {
+    __shared__ unsigned long long keys[SC_ROWS];
+    const int tid = threadIdx.x;
+    const int64_t r0 = (int64_t)blockIdx.x * SC_ROWS;
+    {
+        const int64_t r = r0 + tid;
+        unsigned long long key = ~0ull;   // padding sorts last
+        if (r < n_rows) key = ((unsigned long long)(unsigned)idx[r] << 32) | (unsigned)tid;
+        keys[tid] = key;
+    }
+    __syncthreads();
+    for (int k = 2; k <= SC_ROWS; k <<= 1)
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            const int p = tid ^ j;
+            if (p > tid) {
+                const unsigned long long a = keys[tid], b = keys[p];
+                const bool up = (tid & k) == 0;
+                if ((a > b) == up) { keys[tid] = b; keys[p] = a; }
+            }
+            __syncthreads();
+        }
+    const int warp = tid >> 5, lane = tid & 31;
+    const int e0 = warp * 32;
+    // counts: lane l owns entry e0+l; a run head adds the run length inside this warp's span
+    if (counts) {
+        const unsigned long long key = keys[e0 + lane];
+        const unsigned code = (unsigned)(key >> 32);
+        const bool valid = key != ~0ull;
+        const unsigned prev = __shfl_up_sync(0xffffffffu, code, 1);
+        const bool head = valid && (lane == 0 || prev != code);
+        const unsigned m = __match_any_sync(0xffffffffu, valid ? code : 0xffffffffu);
+        if (head) atomicAdd(counts + code, (float)__popc(m));
+    }
+    for (int c = lane; c < D; c += 32) {
+        float acc = 0.f;
+        unsigned cur = 0xffffffffu;
+        for (int e = 0; e < 32; ++e) {
+            const unsigned long long key = keys[e0 + e];
+            if (key == ~0ull) break;
+            const unsigned code = (unsigned)(key >> 32);
+            const int64_t row = r0 + (unsigned)(key & 0xffffffffu);
+            if (code != cur) {
+                if (cur != 0xffffffffu) atomicAdd(sums + (size_t)cur * D + c, acc);
+                cur = code;
+                acc = 0.f;
+            }
+            acc += __ldg(src + row * D + c);
+        }
+        if (cur != 0xffffffffu) atomicAdd(sums + (size_t)cur * D + c, acc);
+    }
+}
+
+// ---------------------------------------------------------------- AdamW (icl.py:886-889)
+__global__ void adamw_kernel(float *__restrict__ p, const float *__restrict__ g, float *__restrict__ m,
+                             float *__restrict__ v, int64_t n, float lr, float b1, float b2, float eps,
+                             float wd, float bc1, float bc2_sqrt) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+         i += (int64_t)gridDim.x * blockDim.x) {
+        const float gi = g[i];
+        float w = p[i] * (1.0f - lr * wd);
+        const float mi = b1 * m[i] + (1.0f - b1) * gi;
+        const float vi = b2 * v[i] + (1.0f - b2) * gi * gi;
+        m[i] = mi;
+        v[i] = vi;
+        const float denom = sqrtf(vi) / bc2_sqrt + eps;
+        p[i] = w - (lr / bc1) * (mi / denom);
+    }
+}
+
+// ---------------------------------------------------------------- EMA extension (unpinned)
+__global__ void ema_counts_kernel(float *__restrict__ n_ema, const float *__restrict__ counts, int K,
+                                  float gamma, float *__restrict__ partial) {
+    __shared__ float red[8];
+    float s = 0.f;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < K; i += gridDim.x * blockDim.x) {
+        const float v = gamma * n_ema[i] + (1.0f - gamma) * counts[i];
+        n_ema[i] = v;
+        s += v;
+    }
+    s = block_sum<256>(s, red);
+    if (threadIdx.x == 0) partial[blockIdx.x] = s;
+}
+__global__ void ema_apply_kernel(float *__restrict__ E, const float *__restrict__ n_ema,
+                                 float *__restrict__ m_ema, const float *__restrict__ sums,
+                                 const double *__restrict__ tot, int K, int D, float gamma, float eps) {
+    const float t = (float)(*tot);
+    const int64_t total = (int64_t)K * D;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+         i += (int64_t)gridDim.x * blockDim.x) {
+        const int k = (int)(i / D);
+        const float mv = gamma * m_ema[i] + (1.0f - gamma) * sums[i];
+        m_ema[i] = mv;
+        const float ns = (n_ema[k] + eps) / (t + K * eps) * t;
+        E[i] = mv / ns;
+    }
+}
+
+}  // namespace lipvq
