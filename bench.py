@@ -1,0 +1,337 @@
+#!/usr/bin/env python
+"""bench.py -- LipVQ-VAE tokenizer hot path on B200: action chunks tokenized / s.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+    python -m torch.distributed.run --nproc-per-node N ... bench.py --gpus N ...
+
+A "step" = one encode+quantize+decode pass (LLFQVAE_V4.forward, v5:70-84) over one batch of
+synthetic action chunks (BASELINE.json config 3's batch: 65 536 chunks = 655 360 rows x 12-D,
+D=208, K=1024, fp32, reference-distribution random-init weights) PER GPU (weak scaling; rows are
+independent so the forward has no data-path collective).  Rank 0 prints ONE JSON line.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+F_DIM, D_LAT, K_CODES, H_DIM = 12, 208, 1024, 128
+CHUNKS, CHUNK_LEN = 65536, 10
+FLOP_PER_ROW_SEARCH = 2 * K_CODES * D_LAT
+WORKLOAD = ("tokenizer encode+quantize+decode, %d chunks x %d rows x %d-D per GPU, D=%d, K=%d, fp32"
+            % (CHUNKS, CHUNK_LEN, F_DIM, D_LAT, K_CODES))
+
+
+def _peaks():
+    try:
+        return json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))), "measured"
+    except Exception:
+        return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0}, "fallback"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index=0):
+        self.rows, self.proc, self.idx = [], None, gpu_index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.idx), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
+                 "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm = sorted(float(r[1]) for r in self.rows if len(r) >= 9 and r[1].replace(".", "").isdigit())
+        mx = [float(r[2]) for r in self.rows if len(r) >= 9 and r[2].replace(".", "").isdigit()]
+        reasons = set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            if len(r) >= 9:
+                for n, v in zip(names, r[5:9]):
+                    if v.lower().startswith("active"):
+                        reasons.add(n)
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def _make_params(seed=0):
+    from oracle import lipvq_oracle as orc     # input generator only (numpy RNG, same as the tests)
+    return orc.init_params(F_DIM, D_LAT, K_CODES, H_DIM, seed=seed)
+
+
+# ------------------------------------------------------------------------------------------ CPU
+def cpu_reference_sample(rows, threads, search="reference"):
+    """Time the oracle port of the reference forward on `rows` rows with `threads` host threads.
+    Row blocks run in a thread pool (numpy releases the GIL inside ufuncs/BLAS)."""
+    import numpy as np
+    from concurrent.futures import ThreadPoolExecutor
+    from oracle import lipvq_oracle as orc
+    p = _make_params()
+    x = np.random.default_rng(1).standard_normal((rows, F_DIM)).astype(np.float32)
+    blk = max(64, (rows + threads - 1) // threads)
+    parts = [x[s:s + blk] for s in range(0, rows, blk)]
+
+    def run(xb):
+        return orc.forward(p, xb, search=search)["loss"]
+
+    t0 = time.perf_counter()
+    if threads > 1:
+        with ThreadPoolExecutor(threads) as ex:
+            list(ex.map(run, parts))
+    else:
+        [run(xb) for xb in parts]
+    return time.perf_counter() - t0
+
+
+def run_reference_arm(args, rank, world):
+    if rank != 0:
+        return
+    cores = os.cpu_count() or 1
+    sample_chunks = 256                                       # BASELINE config 1's batch
+    rows = sample_chunks * CHUNK_LEN
+    for _ in range(min(args.warmup, 1)):
+        cpu_reference_sample(rows, cores)
+    ts = [cpu_reference_sample(rows, cores) for _ in range(args.steps)]
+    ms = 1e3 * sum(ts) / len(ts)
+    val = sample_chunks / (ms / 1e3)
+    sample = ("%d chunks (%d rows) per step, numpy port of the reference's broadcast-form forward "
+              "(v5:37-48 literally), %d threads over row blocks" % (sample_chunks, rows, cores))
+    print(json.dumps({
+        "impl": "reference", "metric": "action chunks tokenized/sec (encode+quantize+decode)", "value": val,
+        "unit": "chunks/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "sample": sample},
+        "cpu_baseline": {"value": val, "unit": "chunks/s", "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": val, "unit": "chunks/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }))
+
+
+# ------------------------------------------------------------------------------------------ GPU
+def _time_events(fn, iters, torch, stream=None):
+    """average ms per call, CUDA events on the launching (current) stream."""
+    s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    s.record()
+    for i in range(iters):
+        fn(i)
+    e.record()
+    torch.cuda.synchronize()
+    return s.elapsed_time(e) / iters
+
+
+def run_ours(args, rank, world, local_rank):
+    import ctypes as C
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from lipvq_vae_b200 import LLFQVAE_V4, SEARCH_EXACT, SEARCH_TENSOR, _native as N
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py --impl ours needs a CUDA device (there is no CPU fallback)")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    lib = N.lib()
+    N.check(lib.lipvq_check_device(), "lipvq_check_device")
+    peaks, peak_src = _peaks()
+
+    rows = CHUNKS * CHUNK_LEN
+    p = _make_params()
+    m = LLFQVAE_V4(F_DIM, D_LAT, num_codes=K_CODES, hidden_dim=H_DIM).to(dev)
+    m.load_state_dict({k: torch.from_numpy(v) for k, v in p.items()})
+    m.search_mode = SEARCH_EXACT if args.search == "exact" else SEARCH_TENSOR
+    m.eval()
+
+    # rotating inputs: NBUF x 31.5 MB > the 126 MB L2, so no step re-reads a cached input
+    NBUF = 6
+    g = torch.Generator(device="cpu").manual_seed(1234 + rank)
+    host = [torch.randn(rows, F_DIM, generator=g).pin_memory() for _ in range(NBUF)]
+    xs = [h.to(dev) for h in host]
+    loss_host = torch.zeros(4).pin_memory()
+    idx_host = torch.zeros(rows, dtype=torch.int64).pin_memory()
+
+    def step(i):
+        with torch.no_grad():
+            return m(xs[i % NBUF])
+
+    def step_e2e(i):
+        xd = xs[i % NBUF]
+        xd.copy_(host[i % NBUF], non_blocking=True)            # H2D of this step's inputs
+        with torch.no_grad():
+            z, loss = m(xd)
+        loss_host.copy_(m.last_loss_terms, non_blocking=True)  # D2H of the step's result
+        idx_host.copy_(m.last_indices, non_blocking=True)      # ... and its tokens
+        torch.cuda.current_stream().synchronize()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+
+    for i in range(args.warmup):
+        step(i)
+    torch.cuda.synchronize()
+    barrier()
+    clocks = ClockSampler(local_rank)
+    if rank == 0:
+        clocks.start()
+    l0 = lib.lipvq_launch_count()
+    ms = _time_events(step, args.steps, torch)
+    launches = lib.lipvq_launch_count() - l0
+    barrier()
+    clk = clocks.stop() if rank == 0 else None
+
+    for i in range(min(args.warmup, 3)):
+        step_e2e(i)
+    barrier()
+    ms_e2e = _time_events(step_e2e, args.steps, torch)
+    barrier()
+
+    if world > 1:
+        t = torch.tensor([ms, ms_e2e], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms, ms_e2e = t.tolist()
+    value = world * CHUNKS / (ms / 1e3)
+    e2e = world * CHUNKS / (ms_e2e / 1e3)
+
+    if rank != 0:
+        return
+    # ---- dominant kernel (nearest-codeword search) timed alone on the workload's own z_e
+    with torch.no_grad():
+        z_e = m.encode(xs[0])
+    E = m.quantizer.codebook.detach()
+    idx = torch.empty(rows, dtype=torch.int64, device=dev)
+    ws = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    mode = int(m.search_mode)
+    stats = torch.zeros(4, dtype=torch.int32, device=dev)
+
+    def vq(i, z=z_e, Ecb=E, n=rows, D=D_LAT, K=K_CODES):
+        N.check(lib.lipvq_vq_argmin(z.data_ptr(), Ecb.data_ptr(), n, D, K, mode, idx.data_ptr(), None,
+                                    stats.data_ptr(), ws.data_ptr(), ws.numel(), st))
+    for i in range(3):
+        vq(i)
+    ms_vq = _time_events(vq, max(5, args.steps // 2), torch)
+    tf = rows * FLOP_PER_ROW_SEARCH / (ms_vq / 1e3) / 1e12
+    roofline = {"bound": "tensor", "kernel": "vq_argmin (mode=%s)" % ("exact" if mode == 0 else "tensor"),
+                "achieved": tf, "peak": peaks["bf16_tflops"], "unit": "TFLOP/s", "frac": tf / peaks["bf16_tflops"],
+                "traffic": None, "peak_source": peak_src + " bf16 burst (kernel timed alone)",
+                "ms_per_launch": ms_vq, "share_of_step": ms_vq / ms,
+                "fallback_rows": int(stats[0].item()), "rescored_codes": int(stats[1].item())}
+    # ---- BASELINE config 2: the search kernel alone, N=2^20, D=64, K=1024, fp32
+    n2, d2, k2 = 1 << 20, 64, 1024
+    z2 = torch.rand(n2, d2, device=dev)
+    E2 = torch.rand(k2, d2, device=dev)
+    idx2 = torch.empty(n2, dtype=torch.int64, device=dev)
+
+    def vq2(i):
+        N.check(lib.lipvq_vq_argmin(z2.data_ptr(), E2.data_ptr(), n2, d2, k2, mode, idx2.data_ptr(), None,
+                                    stats.data_ptr(), ws.data_ptr(), ws.numel(), st))
+    for i in range(3):
+        vq2(i)
+    ms2 = _time_events(vq2, max(5, args.steps // 2), torch)
+    tf2 = n2 * 2.0 * k2 * d2 / (ms2 / 1e3) / 1e12
+    c2 = {"workload": "VQ nearest-codeword kernel alone: N=2^20, D=64, K=1024, fp32", "ms": ms2,
+          "tflops": tf2, "frac_of_bf16_peak": tf2 / peaks["bf16_tflops"],
+          "algorithmic_gbs": (n2 * (4 * d2 + 8) + k2 * d2 * 4) / (ms2 / 1e3) / 1e9,
+          "fallback_rows": int(stats[0].item()), "rescored_codes": int(stats[1].item())}
+    # ---- HBM-bound gather+loss pass (k4/k5): 3 x N x D x 4 bytes
+    zq = torch.empty_like(z_e)
+    sse = torch.zeros(1, dtype=torch.float64, device=dev)
+
+    def gl(i):
+        N.check(lib.lipvq_gather_loss(z_e.data_ptr(), E.data_ptr(), idx.data_ptr(), rows, D_LAT, K_CODES,
+                                      zq.data_ptr(), sse.data_ptr(), ws.data_ptr(), ws.numel(), st))
+    vq(0)
+    for i in range(3):
+        gl(i)
+    ms_gl = _time_events(gl, max(5, args.steps // 2), torch)
+    gbs = (rows * D_LAT * 4 * 2 + rows * 8) / (ms_gl / 1e3) / 1e9
+    hbm = {"kernel": "gather_loss", "ms": ms_gl, "achieved_gbs": gbs, "peak_gbs": peaks["hbm_gbs"],
+           "frac": gbs / peaks["hbm_gbs"], "bytes": "read z_e + write z_q + idx (codebook rows hit L2)"}
+
+    cpu_baseline = None
+    if world == 1 and not args.no_cpu:
+        cores = os.cpu_count() or 1
+        sample_chunks = 256
+        t = min(cpu_reference_sample(sample_chunks * CHUNK_LEN, cores) for _ in range(2))
+        t_gemm = min(cpu_reference_sample(sample_chunks * CHUNK_LEN * 4, cores, search="gemm") for _ in range(2))
+        cpu_baseline = {"value": sample_chunks / t, "unit": "chunks/s", "cores": cores, "kind": "port",
+                        "sample": "%d chunks (%d rows): numpy port of the reference's broadcast-form forward "
+                                  "(v5:37-48), %d threads over row blocks, best of 2" % (sample_chunks,
+                                                                                       sample_chunks * 10, cores),
+                        "gemm_form_value": 4 * sample_chunks / t_gemm,
+                        "gemm_form_note": "same math with the search as ||e||^2-2zE^T in fp32 BLAS (SURVEY 6)"}
+    out = {
+        "metric": "action chunks tokenized/sec (encode+quantize+decode)", "value": value, "unit": "chunks/s",
+        "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "search": "exact" if mode == 0 else "tensor",
+                   "weights": "reference init distributions, numpy seed 0",
+                   "l2": "%d rotating input buffers (%.0f MB) + %.1f GB of per-step intermediates exceed the 126 MB L2"
+                         % (NBUF, NBUF * rows * F_DIM * 4 / 1e6, rows * (2 * D_LAT + 384) * 4 / 1e9)},
+        "e2e": {"value": e2e, "unit": "chunks/s", "ms_per_step": ms_e2e,
+                "h2d_bytes_per_step": rows * F_DIM * 4, "d2h_bytes_per_step": rows * 8 + 16,
+                "api": "LLFQVAE_V4.forward on a pinned-host batch; loss terms + token indices read back"},
+        "gpu_launches": int(launches), "clocks": clk, "roofline": roofline, "cpu_baseline": cpu_baseline,
+        "config2_vq_alone": c2, "hbm_kernel": hbm,
+    }
+    print(json.dumps(out))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--search", default="tensor", choices=["tensor", "exact"])
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference_arm(args, rank, world)
+        return
+    if world > 1:
+        import torch
+        import torch.distributed as dist
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        torch.cuda.set_device(local_rank)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    try:
+        run_ours(args, rank, world, local_rank)
+    finally:
+        if world > 1:
+            import torch.distributed as dist
+            dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -92,6 +92,8 @@ int lipvq_last_cuda_error(void);
 const char *lipvq_last_cuda_error_string(void);
 /* 0 if the current device is compute capability 10.x, LIPVQ_EARCH otherwise */
 int lipvq_check_device(void);
+/* number of kernels this library has launched in this process (bench.py's gpu_launches) */
+int64_t lipvq_launch_count(void);
 
 /* scratch bytes needed by any call below for n_rows rows with these dims */
 int lipvq_workspace_bytes(const lipvq_dims_t *dims, int64_t n_rows, size_t *out_bytes);
@@ -102,6 +104,15 @@ int lipvq_workspace_bytes(const lipvq_dims_t *dims, int64_t n_rows, size_t *out_
 int lipvq_encoder_fwd(const lipvq_dims_t *dims, const lipvq_params_t *p, const float *x,
                       int64_t n_rows, const lipvq_acts_t *acts, void *ws, size_t ws_bytes,
                       void *stream);
+
+/* One fused linear layer Y[M,N] = act(X[M,K] W[N,K]^T + b[N]) (nn.Linear + nn.GELU of v5:54-68 when a
+ * sub-module is called on its own); act: 0 none, 1 exact-erf GELU, 2 sigmoid.  b nullable. */
+int lipvq_linear_fwd(const float *X, const float *W, const float *b, float *Y, int64_t M, int32_t N,
+                     int32_t K, int32_t act, void *stream);
+
+/* LipschitzMLP.forward alone (v5:6-12, 22-24): scale[D], Wn[D,H] and z_e[N,D] are written. */
+int lipvq_lipschitz_fwd(const float *h, const float *W, const float *b, const float *ci, float *scale,
+                        float *Wn, float *z_e, int64_t n_rows, int32_t D, int32_t H, void *stream);
 
 /* Nearest codeword: idx[n] = argmin_k ||z[n]-E[k]||_2, first minimal index on ties
  * (LFQQuantizer.forward v5:37-46; the sign mask v5:39-40 is +-1 and vanishes under the norm).

@@ -103,8 +103,11 @@ SIGNATURES = {
     "lipvq_last_cuda_error": (C.c_int, []),
     "lipvq_last_cuda_error_string": (C.c_char_p, []),
     "lipvq_check_device": (C.c_int, []),
+    "lipvq_launch_count": (C.c_int64, []),
     "lipvq_workspace_bytes": (C.c_int, [_DP, _I64, C.POINTER(_SZ)]),
     "lipvq_encoder_fwd": (C.c_int, [_DP, _PP, _VP, _I64, _AP, _VP, _SZ, _VP]),
+    "lipvq_linear_fwd": (C.c_int, [_VP, _VP, _VP, _VP, _I64, _I32, _I32, _I32, _VP]),
+    "lipvq_lipschitz_fwd": (C.c_int, [_VP, _VP, _VP, _VP, _VP, _VP, _VP, _I64, _I32, _I32, _VP]),
     "lipvq_vq_argmin": (C.c_int, [_VP, _VP, _I64, _I32, _I32, _I32, _VP, _VP, _VP, _VP, _SZ, _VP]),
     "lipvq_gather_loss": (C.c_int, [_VP, _VP, _VP, _I64, _I32, _I32, _VP, _VP, _VP, _SZ, _VP]),
     "lipvq_decoder_fwd": (C.c_int, [_DP, _PP, _VP, _VP, _I64, _AP, _VP, _VP, _SZ, _VP]),

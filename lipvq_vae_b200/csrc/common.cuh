@@ -8,6 +8,7 @@
 namespace lipvq {
 
 extern thread_local cudaError_t g_last_cuda_error;
+extern long long g_launch_count;   // kernels launched by this library (bench.py's gpu_launches)
 
 #define LIPVQ_CUDA_OK(expr)                                   \
     do {                                                      \
@@ -20,6 +21,7 @@ extern thread_local cudaError_t g_last_cuda_error;
 
 #define LIPVQ_LAUNCH_OK()                                     \
     do {                                                      \
+        __atomic_fetch_add(&::lipvq::g_launch_count, 1LL, __ATOMIC_RELAXED); \
         cudaError_t _e = cudaGetLastError();                  \
         if (_e != cudaSuccess) {                              \
             ::lipvq::g_last_cuda_error = _e;                  \

@@ -11,6 +11,7 @@
 
 namespace lipvq {
 thread_local cudaError_t g_last_cuda_error = cudaSuccess;
+long long g_launch_count = 0;
 
 struct Bump {
     char *base; size_t off, cap;
@@ -76,6 +77,8 @@ const char *lipvq_strerror(int code) {
 int lipvq_last_cuda_error(void) { return (int)g_last_cuda_error; }
 const char *lipvq_last_cuda_error_string(void) { return cudaGetErrorString(g_last_cuda_error); }
 
+int64_t lipvq_launch_count(void) { return (int64_t)__atomic_load_n(&g_launch_count, __ATOMIC_RELAXED); }
+
 int lipvq_check_device(void) {
     int dev = 0, major = 0;
     LIPVQ_CUDA_OK(cudaGetDevice(&dev));
@@ -105,6 +108,30 @@ int lipvq_encoder_fwd(const lipvq_dims_t *d, const lipvq_params_t *p, const floa
     LIPVQ_TRY(linear_fwd<ACT_GELU>(a->h1, p->enc2_w, p->enc2_b, a->a2, a->h2, n, d->H, d->H1, st));
     LIPVQ_TRY(linear_fwd<ACT_SIGMOID>(a->h2, a->Wn, p->lat_b, nullptr, a->z_e, n, d->D, d->H, st));
     return LIPVQ_OK;
+}
+
+int lipvq_linear_fwd(const float *X, const float *W, const float *b, float *Y, int64_t M, int32_t Nn,
+                     int32_t K, int32_t act, void *stream) {
+    if (M < 0 || Nn < 1 || K < 1) return LIPVQ_ESHAPE;
+    if (M == 0) return LIPVQ_OK;
+    if (!aligned16(X) || !aligned16(W) || !aligned16(Y)) return LIPVQ_EALIGN;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (act == ACT_GELU) return linear_fwd<ACT_GELU>(X, W, b, nullptr, Y, M, Nn, K, st);
+    if (act == ACT_SIGMOID) return linear_fwd<ACT_SIGMOID>(X, W, b, nullptr, Y, M, Nn, K, st);
+    if (act == ACT_NONE) return linear_fwd<ACT_NONE>(X, W, b, nullptr, Y, M, Nn, K, st);
+    return LIPVQ_ESHAPE;
+}
+
+int lipvq_lipschitz_fwd(const float *h, const float *W, const float *b, const float *ci, float *scale,
+                        float *Wn, float *z_e, int64_t n, int32_t D, int32_t H, void *stream) {
+    if (n < 0 || D < 1 || H < 1) return LIPVQ_ESHAPE;
+    if (!aligned16(W) || !ci || !aligned16(scale) || !aligned16(Wn)) return LIPVQ_EALIGN;
+    cudaStream_t st = (cudaStream_t)stream;
+    lipschitz_prep_kernel<<<(D + 7) / 8, 256, 0, st>>>(W, ci, D, H, scale, Wn);
+    LIPVQ_LAUNCH_OK();
+    if (n == 0) return LIPVQ_OK;
+    if (!aligned16(h) || !aligned16(z_e)) return LIPVQ_EALIGN;
+    return linear_fwd<ACT_SIGMOID>(h, Wn, b, nullptr, z_e, n, D, H, st);
 }
 
 int lipvq_vq_argmin(const float *z, const float *E, int64_t n, int32_t D, int32_t K, int32_t mode,

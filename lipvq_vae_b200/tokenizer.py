@@ -1,0 +1,365 @@
+"""B200-native drop-in for the reference tokenizer ``LLFQVAE_V4``
+(robomimic/models/vq_vae/backbone_lfqvae_v5.py:51-84; instantiated at
+robomimic/models/obs_nets.py:1225-1227 behind ``algo.transformer.vq_vae_enabled``).
+
+Same constructor, same 14 parameter names/shapes/initialisers (so ``state_dict``s interchange
+and ``optim.AdamW(model.parameters())`` at robomimic/algo/icl.py:886-889 sees the same
+tensors), same ``forward(x) -> (z_latent, loss)`` contract.  All arithmetic runs in the
+hand-written sm_100a kernels behind the C ABI (include/lipvq_b200.h); there is no torch or CPU
+fallback -- CPU tensors raise ``LipVQNativeError``.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import math
+
+import torch
+import torch.nn as nn
+
+from . import _native as N
+from ._native import LipVQNativeError
+
+_WS = {}  # (device index, stream) -> uint8 workspace tensor
+
+
+def _stream_ptr(dev):
+    return C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+
+
+def _workspace(dev, dims, n_rows):
+    need = C.c_size_t(0)
+    N.check(N.lib().lipvq_workspace_bytes(C.byref(dims), n_rows, C.byref(need)), "lipvq_workspace_bytes")
+    key = (dev.index, torch.cuda.current_stream(dev).cuda_stream)
+    ws = _WS.get(key)
+    if ws is None or ws.numel() < need.value:
+        ws = torch.empty(int(need.value * 1.25) + 4096, dtype=torch.uint8, device=dev)
+        _WS[key] = ws
+    return ws
+
+
+def _check_cuda(t, name):
+    if not isinstance(t, torch.Tensor) or not t.is_cuda:
+        raise LipVQNativeError("%s must be a CUDA tensor: lipvq_vae_b200 has no CPU path" % name)
+    if t.dtype != torch.float32:
+        raise TypeError("%s must be float32 (the reference runs .float(), icl.py:883), got %s" % (name, t.dtype))
+
+
+def _p(t):
+    return C.c_void_p(t.data_ptr()) if t is not None else C.c_void_p(0)
+
+
+def _param_struct(cls, tensors):
+    s = cls()
+    for f, t in zip(N._PARAM_FIELDS, tensors):
+        setattr(s, f, t.data_ptr() if t is not None else 0)
+    return s
+
+
+def _acts_struct(**kw):
+    a = N.Acts()
+    for f in N._ACT_FIELDS:
+        t = kw.get(f)
+        setattr(a, f, t.data_ptr() if t is not None else 0)
+    return a
+
+
+def _contig(ts):
+    return [t if t.is_contiguous() else t.contiguous() for t in ts]
+
+
+class _TokenizerFn(torch.autograd.Function):
+    """forward + backward of LLFQVAE_V4.forward (v5:70-84) through the C ABI.
+
+    inputs : x, n_total, search_mode, the 14 parameters (reference state_dict order)
+    outputs: z_latent [N,D] (non-differentiable, v5:74), stats float[4] = loss/recon/commit/codebook,
+             idx int64 [N] (non-differentiable)
+    """
+
+    @staticmethod
+    def forward(ctx, x, n_total, search_mode, dims, *params):
+        lib = N.lib()
+        dev = x.device
+        n = x.shape[0]
+        params = _contig(params)
+        f32 = dict(dtype=torch.float32, device=dev)
+        F_, H1, H, D, K = dims.F, dims.H1, dims.H, dims.D, dims.K
+        st = _stream_ptr(dev)
+        ws = _workspace(dev, dims, n)
+        P = _param_struct(N.Params, params)
+        need_grad = any(ctx.needs_input_grad[4:])
+        stats = torch.zeros(4, **f32)
+        idx = torch.empty(n, dtype=torch.int64, device=dev)
+        z_q = torch.empty(n, D, **f32)
+        vq_stats = torch.zeros(4, dtype=torch.int32, device=dev)
+        if n == 0:
+            ctx.mark_non_differentiable(z_q, idx)
+            ctx.empty = True
+            return z_q, stats, idx, vq_stats
+        ctx.empty = False
+        if not need_grad:
+            N.check(lib.lipvq_forward_fused(C.byref(dims), C.byref(P), _p(x), n, n_total, search_mode, _p(z_q),
+                                            _p(idx), None, _p(stats), _p(vq_stats), _p(ws), ws.numel(), st),
+                    "lipvq_forward_fused")
+            ctx.mark_non_differentiable(z_q, idx, vq_stats)
+            return z_q, stats, idx, vq_stats
+        a1 = torch.empty(n, H1, **f32); h1 = torch.empty(n, H1, **f32)
+        a2 = torch.empty(n, H, **f32); h2 = torch.empty(n, H, **f32)
+        scale = torch.empty(D, **f32); Wn = torch.empty(D, H, **f32)
+        z_e = torch.empty(n, D, **f32)
+        c1 = torch.empty(n, H1, **f32); d1 = torch.empty(n, H1, **f32)
+        c2 = torch.empty(n, H, **f32); d2 = torch.empty(n, H, **f32)
+        x_recon = torch.empty(n, F_, **f32)
+        sse = torch.zeros(2, dtype=torch.float64, device=dev)
+        A = _acts_struct(a1=a1, h1=h1, a2=a2, h2=h2, scale=scale, Wn=Wn, z_e=z_e, idx=idx, z_q=z_q,
+                         c1=c1, d1=d1, c2=c2, d2=d2, x_recon=x_recon)
+        wsz = ws.numel()
+        N.check(lib.lipvq_encoder_fwd(C.byref(dims), C.byref(P), _p(x), n, C.byref(A), _p(ws), wsz, st),
+                "lipvq_encoder_fwd")
+        N.check(lib.lipvq_vq_argmin(_p(z_e), _p(params[7]), n, D, K, search_mode, _p(idx), None, _p(vq_stats),
+                                    _p(ws), wsz, st), "lipvq_vq_argmin")
+        N.check(lib.lipvq_gather_loss(_p(z_e), _p(params[7]), _p(idx), n, D, K, _p(z_q),
+                                      C.c_void_p(sse.data_ptr() + 8), _p(ws), wsz, st), "lipvq_gather_loss")
+        N.check(lib.lipvq_decoder_fwd(C.byref(dims), C.byref(P), _p(z_q), _p(x), n, C.byref(A), _p(sse), _p(ws),
+                                      wsz, st), "lipvq_decoder_fwd")
+        N.check(lib.lipvq_loss_finalize(_p(sse), C.c_void_p(sse.data_ptr() + 8), n_total, F_, D, _p(stats), st),
+                "lipvq_loss_finalize")
+        ctx.save_for_backward(x, *params, a1, h1, a2, h2, scale, Wn, z_e, idx, z_q, c1, d1, c2, d2, x_recon)
+        ctx.dims = dims
+        ctx.n_total = n_total
+        ctx.mark_non_differentiable(z_q, idx, vq_stats)
+        return z_q, stats, idx, vq_stats
+
+    @staticmethod
+    def backward(ctx, g_zlat, g_stats, g_idx, g_vq):
+        none4 = (None, None, None, None)
+        if ctx.empty or g_stats is None:
+            return none4 + (None,) * 14
+        lib = N.lib()
+        saved = ctx.saved_tensors
+        x, params = saved[0], saved[1:15]
+        a1, h1, a2, h2, scale, Wn, z_e, idx, z_q, c1, d1, c2, d2, x_recon = saved[15:]
+        dims = ctx.dims
+        dev = x.device
+        n = x.shape[0]
+        D, K = dims.D, dims.K
+        st = _stream_ptr(dev)
+        ws = _workspace(dev, dims, n)
+        wsz = ws.numel()
+        # dL/dloss lives on the device; the kernels read it there (no host sync)
+        gs = g_stats[0:1].contiguous().float()
+        grads = [torch.empty_like(p) for p in params]
+        grads[7] = torch.zeros_like(params[7])
+        P = _param_struct(N.Params, params)
+        G = _param_struct(N.Grads, grads)
+        A = _acts_struct(a1=a1, h1=h1, a2=a2, h2=h2, scale=scale, Wn=Wn, z_e=z_e, idx=idx, z_q=z_q,
+                         c1=c1, d1=d1, c2=c2, d2=d2, x_recon=x_recon)
+        g_zq = torch.empty_like(z_q)
+        N.check(lib.lipvq_decoder_bwd(C.byref(dims), C.byref(P), _p(x), n, ctx.n_total, _p(gs), C.byref(A),
+                                      C.byref(G), _p(g_zq), _p(ws), wsz, st), "lipvq_decoder_bwd")
+        N.check(lib.lipvq_scatter_add(_p(g_zq), _p(idx), n, D, K, _p(grads[7]), None, st), "lipvq_scatter_add")
+        N.check(lib.lipvq_encoder_bwd(C.byref(dims), C.byref(P), _p(x), n, ctx.n_total, _p(gs), C.byref(A),
+                                      C.byref(G), _p(ws), wsz, st), "lipvq_encoder_bwd")
+        out = [g if ctx.needs_input_grad[4 + i] else None for i, g in enumerate(grads)]
+        return none4 + tuple(out)
+
+
+def _linear_native(x, weight, bias, act):
+    """act(x W^T + b) through lipvq_linear_fwd; no autograd."""
+    _check_cuda(x, "x")
+    x = x.contiguous()
+    w = weight.detach().contiguous()
+    b = bias.detach().contiguous() if bias is not None else None
+    lead = x.shape[:-1]
+    x2 = x.reshape(-1, x.shape[-1])
+    y = torch.empty(x2.shape[0], w.shape[0], dtype=torch.float32, device=x.device)
+    N.check(N.lib().lipvq_linear_fwd(_p(x2), _p(w), _p(b), _p(y), x2.shape[0], w.shape[0], w.shape[1], act,
+                                     _stream_ptr(x.device)), "lipvq_linear_fwd")
+    return y.reshape(*lead, w.shape[0])
+
+
+class NativeLinear(nn.Linear):
+    """``nn.Linear`` parameters/initialiser; calling it alone runs the native kernel without
+    autograd (training goes through ``LLFQVAE_V4.forward``)."""
+    _act = 0
+
+    @torch.no_grad()
+    def forward(self, x):
+        return _linear_native(x, self.weight, self.bias, self._act)
+
+
+class _NativeMLP(nn.Sequential):
+    """``nn.Sequential(Linear, GELU, Linear, GELU)`` key layout (v5:54-59, 62-67).  Calling it on
+    its own fuses each Linear with the GELU that follows and runs the native kernels, no autograd."""
+
+    @torch.no_grad()
+    def forward(self, x):
+        mods = list(self)
+        i = 0
+        while i < len(mods):
+            m = mods[i]
+            if isinstance(m, nn.Linear):
+                gelu = i + 1 < len(mods) and isinstance(mods[i + 1], nn.GELU)
+                x = _linear_native(x, m.weight, m.bias, 1 if gelu else 0)
+                i += 2 if gelu else 1
+            else:
+                raise LipVQNativeError("unsupported layer %r in tokenizer MLP" % (m,))
+        return x
+
+
+class LipschitzMLP(nn.Module):
+    """Lipschitz-normalised sigmoid layer (v5:15-24): parameters W[out,in]~N(0,1), b=0, ci=1."""
+
+    def __init__(self, in_dim, out_dim):
+        super().__init__()
+        self.W = nn.Parameter(torch.randn(out_dim, in_dim))
+        self.b = nn.Parameter(torch.zeros(out_dim))
+        self.ci = nn.Parameter(torch.ones(out_dim))
+
+    @torch.no_grad()
+    def forward(self, h):
+        _check_cuda(h, "h")
+        h = h.contiguous()
+        D, H = self.W.shape
+        n = h.shape[0]
+        dev = h.device
+        scale = torch.empty(D, dtype=torch.float32, device=dev)
+        Wn = torch.empty(D, H, dtype=torch.float32, device=dev)
+        z_e = torch.empty(n, D, dtype=torch.float32, device=dev)
+        N.check(N.lib().lipvq_lipschitz_fwd(_p(h), _p(self.W.detach().contiguous()), _p(self.b.detach().contiguous()),
+                                            _p(self.ci.detach().contiguous()), _p(scale), _p(Wn), _p(z_e), n, D, H,
+                                            _stream_ptr(dev)), "lipvq_lipschitz_fwd")
+        return z_e
+
+
+class LFQQuantizer(nn.Module):
+    """Codebook holder + nearest-codeword search (v5:27-48): returns ``(z_q, indices)``."""
+
+    def __init__(self, num_codes, code_dim):
+        super().__init__()
+        self.num_codes = num_codes
+        self.code_dim = code_dim
+        self.codebook = nn.Parameter(torch.randn(num_codes, code_dim))
+        nn.init.kaiming_uniform_(self.codebook)          # v5:35
+        self.search_mode = N.SEARCH_TENSOR
+
+    @torch.no_grad()
+    def forward(self, z_e):
+        _check_cuda(z_e, "z_e")
+        z_e = z_e.contiguous()
+        E = self.codebook.detach().contiguous()
+        n, D = z_e.shape
+        K = E.shape[0]
+        dev = z_e.device
+        dims = N.Dims(1, 1, 1, D, K)
+        ws = _workspace(dev, dims, n)
+        idx = torch.empty(n, dtype=torch.int64, device=dev)
+        z_q = torch.empty(n, D, dtype=torch.float32, device=dev)
+        sse = torch.zeros(1, dtype=torch.float64, device=dev)
+        self.last_search_stats = torch.zeros(4, dtype=torch.int32, device=dev)
+        st = _stream_ptr(dev)
+        lib = N.lib()
+        N.check(lib.lipvq_vq_argmin(_p(z_e), _p(E), n, D, K, self.search_mode, _p(idx), None,
+                                    _p(self.last_search_stats), _p(ws), ws.numel(), st), "lipvq_vq_argmin")
+        N.check(lib.lipvq_gather_loss(_p(z_e), _p(E), _p(idx), n, D, K, _p(z_q), _p(sse), _p(ws), ws.numel(), st),
+                "lipvq_gather_loss")
+        return z_q, idx
+
+
+class LLFQVAE_V4(nn.Module):
+    """Drop-in for the reference ``LLFQVAE_V4`` (v5:51-84).
+
+    ``forward(x[N, feature_dim]) -> (z_latent[N, latent_dim] detached, loss 0-dim)`` exactly as
+    consumed at robomimic/models/obs_nets.py:1335-1337.  Extra, reference-compatible surface:
+    ``encode / quantize / decode`` (the submodule calls v5:71-76 spelled as methods),
+    ``last_indices``, ``last_loss_terms`` and ``last_search_stats`` (device tensors, no sync).
+
+    Knobs are attributes, not config keys (robomimic's config is locked, train.py:494-497):
+      ``search_mode``  N.SEARCH_TENSOR (default) or N.SEARCH_EXACT
+      ``n_total_rows`` global row count when ``x`` is one data-parallel shard (set by dist.py)
+    """
+
+    def __init__(self, feature_dim, latent_dim, num_codes=1024, hidden_dim=128):
+        super().__init__()
+        self.encoder = _NativeMLP(
+            NativeLinear(feature_dim, 64), nn.GELU(), NativeLinear(64, hidden_dim), nn.GELU())
+        self.to_latent = LipschitzMLP(hidden_dim, latent_dim)
+        self.quantizer = LFQQuantizer(num_codes, latent_dim)
+        self.decoder = _NativeMLP(
+            NativeLinear(latent_dim, 64), nn.GELU(), NativeLinear(64, hidden_dim), nn.GELU())
+        self.to_output = NativeLinear(hidden_dim, feature_dim)
+        self.feature_dim, self.latent_dim = feature_dim, latent_dim
+        self.num_codes, self.hidden_dim = num_codes, hidden_dim
+        self.search_mode = N.SEARCH_TENSOR
+        self.n_total_rows = None
+        self.last_indices = None
+        self.last_loss_terms = None
+        self.last_search_stats = None
+
+    # ------------------------------------------------------------------ helpers
+    def _dims(self):
+        return N.Dims(self.feature_dim, 64, self.hidden_dim, self.latent_dim, self.num_codes)
+
+    def _param_list(self):
+        e, d = self.encoder, self.decoder
+        return [e[0].weight, e[0].bias, e[2].weight, e[2].bias,
+                self.to_latent.W, self.to_latent.b, self.to_latent.ci,
+                self.quantizer.codebook,
+                d[0].weight, d[0].bias, d[2].weight, d[2].bias,
+                self.to_output.weight, self.to_output.bias]
+
+    # ------------------------------------------------------------------ reference interface
+    def forward(self, x):
+        _check_cuda(x, "x")
+        if x.dim() != 2 or x.shape[1] != self.feature_dim:
+            raise RuntimeError("expected x of shape [N, %d], got %s" % (self.feature_dim, tuple(x.shape)))
+        x = x.contiguous()
+        n_total = int(self.n_total_rows) if self.n_total_rows is not None else x.shape[0]
+        params = self._param_list()
+        if not torch.is_grad_enabled():
+            params = [p.detach() for p in params]
+        z_latent, stats, idx, vq_stats = _TokenizerFn.apply(
+            x.detach(), max(n_total, 1), int(self.search_mode), self._dims(), *params)
+        self.last_indices = idx
+        self.last_loss_terms = stats.detach()
+        self.last_search_stats = vq_stats
+        return z_latent, stats[0]
+
+    @torch.no_grad()
+    def encode(self, x):
+        """z_e = to_latent(encoder(x))  (v5:71-72)"""
+        return self.to_latent(self.encoder(x))
+
+    @torch.no_grad()
+    def quantize(self, z_e):
+        """(z_q, indices) = quantizer(z_e)  (v5:73, 37-48)"""
+        self.quantizer.search_mode = self.search_mode
+        return self.quantizer(z_e)
+
+    @torch.no_grad()
+    def decode(self, z_q):
+        """x_recon = to_output(decoder(z_q))  (v5:75-76)"""
+        return self.to_output(self.decoder(z_q))
+
+    @torch.no_grad()
+    def tokenize(self, x):
+        """indices only: the tokens of each action row."""
+        return self.quantize(self.encode(x))[1]
+
+    @torch.no_grad()
+    def codes_to_latent(self, indices):
+        E = self.quantizer.codebook.detach()
+        z = torch.zeros(indices.shape[0], self.latent_dim, dtype=torch.float32, device=E.device)
+        dummy = torch.zeros(1, dtype=torch.float64, device=E.device)
+        ws = _workspace(E.device, self._dims(), indices.shape[0])
+        N.check(N.lib().lipvq_gather_loss(_p(z), _p(E.contiguous()), _p(indices.contiguous()), indices.shape[0],
+                                          self.latent_dim, self.num_codes, _p(z), _p(dummy), _p(ws), ws.numel(),
+                                          _stream_ptr(E.device)), "lipvq_gather_loss")
+        return z
+
+
+def install_into_robomimic():
+    """Rebind ``LLFQVAE_V4`` in robomimic's ``obs_nets`` namespace (imported there at
+    obs_nets.py:47, looked up at call time :1225) so ``vq_vae_enabled`` builds this module."""
+    import robomimic.models.obs_nets as obs_nets  # noqa: WPS433 (optional dependency)
+    obs_nets.LLFQVAE_V4 = LLFQVAE_V4
+    return obs_nets
