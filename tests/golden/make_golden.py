@@ -31,8 +31,16 @@ def _load(name, path):
     return m
 
 
-v5 = _load("ref_v5", os.path.join(REF, "backbone_lfqvae_v5.py"))
-vq = _load("ref_vq", os.path.join(REF, "backbone.py"))
+_REF_MODS = {}
+
+
+def _ref(name):
+    """Import the reference module lazily: only the generator (run in the authoring container)
+    touches /root/reference; the tests import this file for the input generators alone."""
+    if name not in _REF_MODS:
+        fn = {"v5": "backbone_lfqvae_v5.py", "vq": "backbone.py"}[name]
+        _REF_MODS[name] = _load("ref_" + name, os.path.join(REF, fn))
+    return _REF_MODS[name]
 
 
 # ------------------------------------------------------------------ shared input generators
@@ -114,7 +122,7 @@ def _ref_model(p):
     F = p["encoder.0.weight"].shape[1]
     K, D = p["quantizer.codebook"].shape
     H = p["encoder.2.weight"].shape[0]
-    m = v5.LLFQVAE_V4(F, D, num_codes=K, hidden_dim=H)
+    m = _ref("v5").LLFQVAE_V4(F, D, num_codes=K, hidden_dim=H)
     m.load_state_dict({k: torch.from_numpy(v.copy()) for k, v in p.items()}, strict=True)
     return m.float()
 
@@ -166,7 +174,7 @@ def run_model_case(name):
 
 def run_quant_case(name):
     z, E = quant_inputs(name)
-    q = v5.LFQQuantizer(E.shape[0], E.shape[1])
+    q = _ref("v5").LFQQuantizer(E.shape[0], E.shape[1])
     with torch.no_grad():
         q.codebook.copy_(torch.from_numpy(E))
         idx = np.empty(len(z), np.int32)
@@ -174,7 +182,7 @@ def run_quant_case(name):
             _, i = q(torch.from_numpy(z[s:s + 256]))
             idx[s:s + 256] = i.numpy()
         # classic VQVAE.quantize (vq:55-76) on the same data
-        m = vq.VQVAE(4, E.shape[1], num_embeddings=E.shape[0])
+        m = _ref("vq").VQVAE(4, E.shape[1], num_embeddings=E.shape[0])
         m.embedding.weight.copy_(torch.from_numpy(E))
         zq2, qloss = m.quantize(torch.from_numpy(z[:256]))
         d = (torch.from_numpy(z[:256]).unsqueeze(1) - m.embedding.weight).pow(2).sum(-1)
