@@ -225,7 +225,12 @@ def run_ours(args, rank, world, local_rank):
         z_e = m.encode(xs[0])
     E = m.quantizer.codebook.detach()
     idx = torch.empty(rows, dtype=torch.int64, device=dev)
-    ws = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    def _ws_bytes(n, D, K):
+        need = C.c_size_t(0)
+        N.check(lib.lipvq_workspace_bytes(C.byref(N.Dims(1, 1, 1, D, K)), n, C.byref(need)))
+        return need.value
+    ws = torch.empty(max(_ws_bytes(rows, D_LAT, K_CODES), _ws_bytes(1 << 20, 64, 1024)) + 4096,
+                     dtype=torch.uint8, device=dev)
     st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
     mode = int(m.search_mode)
     stats = torch.zeros(4, dtype=torch.int32, device=dev)

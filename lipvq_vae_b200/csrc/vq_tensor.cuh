@@ -15,6 +15,7 @@
 #pragma once
 #include <cuda.h>
 #include <cuda_bf16.h>
+#include <stdlib.h>
 
 #include "common.cuh"
 #include "ptx_sm100.cuh"
@@ -30,7 +31,8 @@ constexpr int UK = 16;           // UMMA K for 16-bit inputs
 constexpr int A_KB_BYTES = BM * 128;
 constexpr int B_ST_BYTES = BN * 128;
 constexpr int NT = 384;          // warp0 TMA, warp1 MMA, warp2 TMEM alloc, warps 4..11 epilogue
-constexpr int NCAND = 4;         // chunk minima kept per (row, column half)
+constexpr int NCAND = 4;         // chunk minima kept per (row, column half, code tile)
+constexpr int LCAP = 16;         // candidate entries kept per (row, column half)
 constexpr float BIG = 3.0e38f;
 constexpr float PAD_SCORE = 1.0e30f;   // en of the padding codes (never inside any window)
 
@@ -53,13 +55,23 @@ inline Geometry geometry(int64_t n, int D, int K) {
 }
 
 // ------------------------------------------------------------------ pass 0: codebook operand
-// mu[d] = mean_k E[k,d]   (one thread per column, fixed order)
-__global__ void vq_prep_mean_kernel(const float *__restrict__ E, int K, int D, float *__restrict__ mu) {
-    const int d = blockIdx.x * blockDim.x + threadIdx.x;
-    if (d >= D) return;
+// mu[d] = mean_k E[k,d]: block = 32 columns x 32 row-slices, combined in slice order (deterministic)
+__global__ void __launch_bounds__(1024) vq_prep_mean_kernel(const float *__restrict__ E, int K, int D,
+                                                            float *__restrict__ mu) {
+    __shared__ float part[32][33];
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    const int d = blockIdx.x * 32 + tx;
     float s = 0.f;
-    for (int k = 0; k < K; ++k) s += E[(size_t)k * D + d];
-    mu[d] = s / (float)K;
+    if (d < D)
+        for (int k = ty; k < K; k += 32) s += E[(size_t)k * D + d];
+    part[ty][tx] = s;
+    __syncthreads();
+    if (ty == 0 && d < D) {
+        float t = 0.f;
+#pragma unroll
+        for (int i = 0; i < 32; ++i) t += part[i][tx];
+        mu[d] = t / (float)K;
+    }
 }
 
 __device__ __forceinline__ void split3_bf16(float v, __nv_bfloat16 &a, __nv_bfloat16 &b, __nv_bfloat16 &c) {
@@ -151,6 +163,10 @@ struct SmemLayout {
     static constexpr int TOTAL = BAR_OFF + NBARS * 8 + 16 + 1024;   // + tmem ptr + alignment slack
 };
 
+constexpr float RESC_C1 = 0.015625f * 1.004f;   // 2*(2u+u^2), u = 2^-8
+constexpr float RESC_C2 = 4.0e-5f;
+constexpr int RESC_MAXD = 320;
+
 // sorted insert of x into m0<=m1<=m2<=m3 (payload rides in the low mantissa bits): 7 FMNMX
 __device__ __forceinline__ void insert4(float (&m)[NCAND], float x) {
     float t;
@@ -159,26 +175,20 @@ __device__ __forceinline__ void insert4(float (&m)[NCAND], float x) {
     t = fminf(m[2], x); x = fmaxf(m[2], x); m[2] = t;
     m[3] = fminf(m[3], x);
 }
-// sorted insert of (v,id) into the row-level list starting at level L0 (earlier levels are known smaller)
-template <int L0>
-__device__ __forceinline__ void insert4_payload(float (&G)[NCAND], int (&Gid)[NCAND], float v, int id) {
-#pragma unroll
-    for (int i = L0; i < NCAND; ++i) {
-        const bool lt = v < G[i];
-        const float gv = G[i];
-        const int gi = Gid[i];
-        G[i] = lt ? v : gv;
-        Gid[i] = lt ? id : gi;
-        v = lt ? gv : v;
-        id = lt ? gi : id;
-    }
-}
-
-template <int NKB, int A_BUFS, int STAGES, int CHUNK>
+// Candidate record written by the epilogue for each (row, column half):
+//   entries[LCAP] = {packed score bits, code}: every chunk minimum that was within tau(row) of the running
+//                   row minimum when its code tile was finished (a superset of the final window);
+//   meta = {count, m4min, smin}: m4min = smallest 4th-best chunk minimum of any code tile (if it is inside
+//          the final window a 5th chunk may have been dropped -> exact scan); smin = smallest SECOND-best
+//          element of any chunk (ELEM only: if it is outside the window every window element is listed).
+// ELEM (CHUNK==4): the packed payload is the column inside the tile half (7 bits) -> entries name single codes.
+// otherwise the payload is the chunk id and an entry names CHUNK consecutive codes.
+template <int NKB, int A_BUFS, int STAGES, int CHUNK, bool ELEM>
 __global__ void __launch_bounds__(NT, 1) vq_tc_kernel(const __grid_constant__ CUtensorMap tmapA,
                                                        const __grid_constant__ CUtensorMap tmapB,
                                                        int64_t n_rows, int n_tiles, int nct, int nk16,
-                                                       float *__restrict__ cand_val, int *__restrict__ cand_code) {
+                                                       const float *__restrict__ zn, const float *__restrict__ emax_p,
+                                                       uint2 *__restrict__ cand, float4 *__restrict__ cand_meta) {
     using L = SmemLayout<NKB, A_BUFS, STAGES>;
     extern __shared__ uint8_t smem_raw[];
     const uint32_t raw = ptx::smem_u32(smem_raw);
@@ -268,15 +278,21 @@ __global__ void __launch_bounds__(NT, 1) vq_tc_kernel(const __grid_constant__ CU
         }
     } else if (warp >= 4) {
         // ===== epilogue: 8 warps; warp%4 = TMEM lane quarter, (warp-4)/4 = column half =====
+        static_assert(!ELEM || CHUNK == 4, "element payload needs 4-wide chunks");
         const int quarter = warp & 3, half = (warp - 4) >> 2;
         const uint32_t lane_addr = ((uint32_t)(quarter * 32) << 16);
         int acc = 0, accph = 0;
         constexpr int CPB = 32 / CHUNK;               // chunks per 32-column batch
+        constexpr uint32_t PMASK = ELEM ? 127u : 31u; // payload bits in the low mantissa
+        const float emax = __ldg(emax_p);
         for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-            float G[NCAND];
-            int Gid[NCAND];
-#pragma unroll
-            for (int i = 0; i < NCAND; ++i) { G[i] = BIG; Gid[i] = 0; }
+            const int64_t row = (int64_t)tile * BM + quarter * 32 + lane;
+            const bool row_ok = row < n_rows;
+            const float znr = row_ok ? __ldg(zn + row) : 0.f;
+            const float tau = 2.f * (RESC_C1 * znr * emax + RESC_C2 * (2.f * znr * emax + emax * emax)) + 1e-30f;
+            uint2 *out = cand + (row * 2 + half) * LCAP;
+            float gb = BIG, T = BIG, m4min = BIG, smin = BIG;
+            int cnt = 0;
             for (int c = 0; c < nct; ++c) {
                 ptx::mbar_wait(t_full(acc), accph);
                 ptx::tc_fence_after();
@@ -295,35 +311,56 @@ __global__ void __launch_bounds__(NT, 1) vq_tc_kernel(const __grid_constant__ CU
 #pragma unroll
                     for (int j = 0; j < CPB; ++j) {
                         float v;
-                        if (CHUNK == 4) {
+                        if (ELEM) {
+                            // payload = column inside the tile half (b*32 + 4j + pos), constant per unrolled slot
+                            const float e0 = __uint_as_float((r[4 * j + 0] & ~PMASK) | (uint32_t)(b * 32 + 4 * j + 0));
+                            const float e1 = __uint_as_float((r[4 * j + 1] & ~PMASK) | (uint32_t)(b * 32 + 4 * j + 1));
+                            const float e2 = __uint_as_float((r[4 * j + 2] & ~PMASK) | (uint32_t)(b * 32 + 4 * j + 2));
+                            const float e3 = __uint_as_float((r[4 * j + 3] & ~PMASK) | (uint32_t)(b * 32 + 4 * j + 3));
+                            const float lo1 = fminf(e0, e1), hi1 = fmaxf(e0, e1);
+                            const float lo2 = fminf(e2, e3), hi2 = fmaxf(e2, e3);
+                            v = fminf(lo1, lo2);
+                            smin = ptx::fmin3(smin, fmaxf(lo1, lo2), fminf(hi1, hi2));   // chunk's 2nd smallest
+                        } else if (CHUNK == 4) {
                             v = ptx::fmin3(__uint_as_float(r[4 * j]), __uint_as_float(r[4 * j + 1]),
                                            fminf(__uint_as_float(r[4 * j + 2]), __uint_as_float(r[4 * j + 3])));
+                            v = __uint_as_float((__float_as_uint(v) & ~PMASK) | (uint32_t)(b * CPB + j));
                         } else {
                             const float v0 = ptx::fmin3(__uint_as_float(r[8 * j]), __uint_as_float(r[8 * j + 1]),
                                                         __uint_as_float(r[8 * j + 2]));
                             const float v1 = ptx::fmin3(__uint_as_float(r[8 * j + 3]), __uint_as_float(r[8 * j + 4]),
                                                         __uint_as_float(r[8 * j + 5]));
                             v = ptx::fmin3(v0, v1, fminf(__uint_as_float(r[8 * j + 6]), __uint_as_float(r[8 * j + 7])));
+                            v = __uint_as_float((__float_as_uint(v) & ~PMASK) | (uint32_t)(b * CPB + j));
                         }
-                        // chunk id (< 32) rides in the 5 low mantissa bits
-                        const float pk = __uint_as_float((__float_as_uint(v) & ~31u) | (uint32_t)(b * CPB + j));
-                        insert4(m, pk);
+                        insert4(m, v);
                     }
                 }
                 if (++acc == 2) { acc = 0; accph ^= 1; }
-                // merge this tile-half's 4 minima into the row-level list (code index of the chunk start)
+                // keep the chunk minima of this code tile that are inside the window of the running row minimum
+                m4min = fminf(m4min, m[NCAND - 1]);
+                gb = fminf(gb, m[0]);
+                T = gb + tau;
                 const int code0 = c * BN + half * (BN / 2);
-                insert4_payload<0>(G, Gid, m[0], code0 + (int)(__float_as_uint(m[0]) & 31u) * CHUNK);
-                insert4_payload<1>(G, Gid, m[1], code0 + (int)(__float_as_uint(m[1]) & 31u) * CHUNK);
-                insert4_payload<2>(G, Gid, m[2], code0 + (int)(__float_as_uint(m[2]) & 31u) * CHUNK);
-                insert4_payload<3>(G, Gid, m[3], code0 + (int)(__float_as_uint(m[3]) & 31u) * CHUNK);
+#pragma unroll
+                for (int i = 0; i < NCAND; ++i) {
+                    if (row_ok && m[i] <= T) {
+                        const uint32_t bits = __float_as_uint(m[i]);
+                        if (cnt == LCAP) {   // full: drop entries that fell out of the (shrinking) window
+                            int k = 0;
+                            for (int e = 0; e < LCAP; ++e) {
+                                const uint2 x = out[e];
+                                if (__uint_as_float(x.x) <= T) out[k++] = x;
+                            }
+                            cnt = k;
+                        }
+                        if (cnt < LCAP)
+                            out[cnt] = make_uint2(bits, (uint32_t)(code0 + (int)(bits & PMASK) * (ELEM ? 1 : CHUNK)));
+                        ++cnt;
+                    }
+                }
             }
-            const int64_t row = (int64_t)tile * BM + quarter * 32 + lane;
-            if (row < n_rows) {
-                const int64_t o = (row * 2 + half) * NCAND;
-                *reinterpret_cast<float4 *>(cand_val + o) = make_float4(G[0], G[1], G[2], G[3]);
-                *reinterpret_cast<int4 *>(cand_code + o) = make_int4(Gid[0], Gid[1], Gid[2], Gid[3]);
-            }
+            if (row_ok) cand_meta[row * 2 + half] = make_float4(__int_as_float(cnt), m4min, smin, 0.f);
         }
     }
     ptx::tc_fence_before();
@@ -337,74 +374,126 @@ __global__ void __launch_bounds__(NT, 1) vq_tc_kernel(const __grid_constant__ CU
 // Cauchy-Schwarz; fp32 accumulation, the 3-way split of en and the 5 payload bits are covered by C2):
 //   |S_nk - (||e'_k||^2 - 2 z'_n.e'_k)| <= eps_n = C1*zn*emax + C2*(2*zn*emax + emax^2)
 // so every code whose exact score is minimal has S <= min_k S + 2*eps_n.
-constexpr float RESC_C1 = 0.015625f * 1.004f;   // 2*(2u+u^2), u = 2^-8
-constexpr float RESC_C2 = 4.0e-5f;
-constexpr int RESC_MAXD = 320;
 
-template <int CHUNK>
+template <int CHUNK, bool ELEM, bool VEC>
 __global__ void __launch_bounds__(256) vq_rescore_kernel(
     const float *__restrict__ z, const float *__restrict__ E, int64_t n_rows, int D, int K,
-    const float *__restrict__ cand_val, const int *__restrict__ cand_code, const float *__restrict__ zn,
+    const uint2 *__restrict__ cand, const float4 *__restrict__ cand_meta, const float *__restrict__ zn,
     const float *__restrict__ emax_p, int64_t *__restrict__ idx_out, float *__restrict__ d2_out,
     int *__restrict__ list, int *__restrict__ counters) {
-    const int lane = threadIdx.x & 31;
-    const float emax = *emax_p;
-    int n_resc = 0;
+    constexpr int NG = CHUNK;          // codes evaluated side by side
+    constexpr int LPG = 32 / NG;       // lanes per code
+    const int lane = threadIdx.x & 31, g = lane / LPG, l = lane % LPG;
+    const float emax = __ldg(emax_p);
+    int n_resc = 0, n_fast = 0;
     for (int64_t row = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5); row < n_rows; row += (int64_t)gridDim.x * 8) {
+        const float4 m0 = __ldg(cand_meta + row * 2), m1 = __ldg(cand_meta + row * 2 + 1);
+        const int cnt0 = __float_as_int(m0.x), cnt1 = __float_as_int(m1.x);
+        const int n0 = min(cnt0, LCAP), n1 = min(cnt1, LCAP);
         float v = BIG;
-        int code = 0;
-        if (lane < 2 * NCAND) { v = cand_val[row * 2 * NCAND + lane]; code = cand_code[row * 2 * NCAND + lane]; }
+        int code = 0x7fffffff;
+        if (lane < n0 + n1) {
+            const uint2 e = __ldg(cand + (row * 2 + (lane < n0 ? 0 : 1)) * LCAP + (lane < n0 ? lane : lane - n0));
+            v = __uint_as_float(e.x);
+            code = (int)e.y;
+        }
         float gb = v;
 #pragma unroll
-        for (int o = 4; o > 0; o >>= 1) gb = fminf(gb, __shfl_xor_sync(0xffffffffu, gb, o));
-        gb = __shfl_sync(0xffffffffu, gb, 0);
-        const float znr = zn[row];
-        const float eps = RESC_C1 * znr * emax + RESC_C2 * (2.f * znr * emax + emax * emax);
-        const float T = gb + 2.f * eps + 1e-30f;
-        const bool in = (lane < 2 * NCAND) && (v <= T) && (v < 1.0e29f) && (code < K);
-        const unsigned over = __ballot_sync(0xffffffffu, in && ((lane & (NCAND - 1)) == NCAND - 1));
-        if (over) {   // a 4th chunk is inside the window: more may have been dropped -> exact scan
+        for (int o = 16; o > 0; o >>= 1) gb = fminf(gb, __shfl_xor_sync(0xffffffffu, gb, o));
+        const float znr = __ldg(zn + row);
+        const float T = gb + 2.f * (RESC_C1 * znr * emax + RESC_C2 * (2.f * znr * emax + emax * emax)) + 1e-30f;
+        if (cnt0 > LCAP || cnt1 > LCAP || m0.y <= T || m1.y <= T) {
+            // the candidate record may be incomplete -> exact fp32 scan of the whole codebook
             if (lane == 0) list[atomicAdd(counters + 0, 1)] = (int)row;
             continue;
         }
+        const bool in = (v <= T) && (code < K);
         unsigned mask = __ballot_sync(0xffffffffu, in);
-        float zr[RESC_MAXD / 32];
-#pragma unroll
-        for (int i = 0; i < RESC_MAXD / 32; ++i) {
-            const int d = lane + 32 * i;
-            zr[i] = d < D ? __ldg(z + row * D + d) : 0.f;
+        const int nc = __popc(mask);
+        const bool elem_ok = ELEM && !(m0.z <= T || m1.z <= T);   // no chunk holds two window elements
+        if (elem_ok && nc == 1 && d2_out == nullptr) {
+            // a single element inside the rounding window IS the nearest code: nothing to rescore
+            const int w = __shfl_sync(0xffffffffu, code, __ffs(mask) - 1);
+            if (lane == 0) idx_out[row] = (int64_t)w;
+            ++n_fast;
+            continue;
         }
         float best = INFINITY;
         int bidx = 0x7fffffff;
-        while (mask) {
-            const int l = __ffs(mask) - 1;
-            mask &= mask - 1;
-            const int c0 = __shfl_sync(0xffffffffu, code, l);
-#pragma unroll 1
-            for (int j = 0; j < CHUNK; ++j) {
-                const int cj = c0 + j;
-                if (cj >= K) break;
+        const float *zr = z + row * D;
+        const int passes = elem_ok ? (nc + NG - 1) / NG : nc;
+        for (int p = 0; p < passes; ++p) {
+            int cj;
+            bool has;
+            if (elem_ok) {
+                const int e = p * NG + g;
+                has = e < nc;
+                const int src = __fns(mask, 0, (has ? e : 0) + 1);
+                cj = __shfl_sync(0xffffffffu, code, src);
+            } else {
+                const int src = __fns(mask, 0, p + 1);
+                int c0 = __shfl_sync(0xffffffffu, code, src);
+                if (ELEM) c0 &= ~(CHUNK - 1);
+                cj = c0 + g;
+                has = cj < K;
+            }
+            float s = 0.f;
+            if (has) {
                 const float *e = E + (size_t)cj * D;
-                float s = 0.f;
+                if (VEC) {
+                    // issue 4 independent (z,e) load pairs before using them: the loop is latency-bound
+                    const float4 *z4 = reinterpret_cast<const float4 *>(zr), *e4 = reinterpret_cast<const float4 *>(e);
+                    const int d4 = D >> 2;
+                    for (int i0 = l; i0 < d4; i0 += 4 * LPG) {
+                        float4 a[4], b[4];
 #pragma unroll
-                for (int i = 0; i < RESC_MAXD / 32; ++i) {
-                    const int d = lane + 32 * i;
-                    if (d < D) {
-                        const float df = zr[i] - __ldg(e + d);
-                        s = fmaf(df, df, s);
+                        for (int u = 0; u < 4; ++u) {
+                            const int i = i0 + u * LPG;
+                            a[u] = b[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+                            if (i < d4) { a[u] = __ldg(z4 + i); b[u] = __ldg(e4 + i); }
+                        }
+#pragma unroll
+                        for (int u = 0; u < 4; ++u) {
+                            const float dx = a[u].x - b[u].x, dy = a[u].y - b[u].y, dz = a[u].z - b[u].z, dw = a[u].w - b[u].w;
+                            s = fmaf(dx, dx, s); s = fmaf(dy, dy, s); s = fmaf(dz, dz, s); s = fmaf(dw, dw, s);
+                        }
+                    }
+                } else {
+                    for (int i0 = l; i0 < D; i0 += 4 * LPG) {
+                        float a[4], b[4];
+#pragma unroll
+                        for (int u = 0; u < 4; ++u) {
+                            const int i = i0 + u * LPG;
+                            a[u] = b[u] = 0.f;
+                            if (i < D) { a[u] = __ldg(zr + i); b[u] = __ldg(e + i); }
+                        }
+#pragma unroll
+                        for (int u = 0; u < 4; ++u) { const float df = a[u] - b[u]; s = fmaf(df, df, s); }
                     }
                 }
-                s = warp_sum(s);
-                argmin_merge(best, bidx, s, cj);
-                ++n_resc;
             }
+#pragma unroll
+            for (int o = LPG / 2; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+            float cs = has ? s : INFINITY;
+            int ci = has ? cj : 0x7fffffff;
+#pragma unroll
+            for (int o = LPG; o < 32; o <<= 1) {
+                const float os = __shfl_xor_sync(0xffffffffu, cs, o);
+                const int oi = __shfl_xor_sync(0xffffffffu, ci, o);
+                argmin_merge(cs, ci, os, oi);
+            }
+            argmin_merge(best, bidx, cs, ci);
+            n_resc += elem_ok ? min(NG, nc - p * NG) : NG;
         }
         if (lane == 0) {
             idx_out[row] = (int64_t)bidx;
             if (d2_out) d2_out[row] = best;
         }
     }
-    if (lane == 0 && n_resc) atomicAdd(counters + 1, n_resc);
+    if (lane == 0) {
+        if (n_resc) atomicAdd(counters + 1, n_resc);
+        if (n_fast) atomicAdd(counters + 2, n_fast);
+    }
 }
 
 // ------------------------------------------------------------------ host side
@@ -437,8 +526,10 @@ inline int make_tmap(CUtensorMap *m, const void *ptr, uint64_t rows, uint64_t co
 }
 
 struct Workspace {
-    float *mu, *enorm, *emax, *zn, *cand_val;
-    int *cand_code, *list, *counters;
+    float *mu, *enorm, *emax, *zn;
+    uint2 *cand;
+    float4 *cand_meta;
+    int *list, *counters;
     __nv_bfloat16 *Eb, *Zb;
     size_t bytes;
 };
@@ -453,25 +544,25 @@ inline Workspace carve(void *ws, const Geometry &g) {
     w.Eb = (__nv_bfloat16 *)take((size_t)g.Kp * g.DKp * 2);
     w.Zb = (__nv_bfloat16 *)take((size_t)g.Np * g.DKp * 2);
     w.zn = (float *)take(sizeof(float) * g.Np);
-    w.cand_val = (float *)take(sizeof(float) * g.Np * 2 * NCAND);
-    w.cand_code = (int *)take(sizeof(int) * g.Np * 2 * NCAND);
+    w.cand = (uint2 *)take(sizeof(uint2) * g.Np * 2 * LCAP);
+    w.cand_meta = (float4 *)take(sizeof(float4) * g.Np * 2);
     w.list = (int *)take(sizeof(int) * g.Np);
     w.bytes = align_up(off, 1024);
     return w;
 }
 
-template <int NKB, int A_BUFS, int STAGES, int CHUNK>
+template <int NKB, int A_BUFS, int STAGES, int CHUNK, bool ELEM>
 inline int launch_tc(const CUtensorMap &ta, const CUtensorMap &tb, const Geometry &g, const Workspace &w,
                      cudaStream_t st) {
     using L = SmemLayout<NKB, A_BUFS, STAGES>;
-    auto kern = vq_tc_kernel<NKB, A_BUFS, STAGES, CHUNK>;
+    auto kern = vq_tc_kernel<NKB, A_BUFS, STAGES, CHUNK, ELEM>;
     static bool attr_done = false;
     if (!attr_done) {
         LIPVQ_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::TOTAL));
         attr_done = true;
     }
     const int grid = (int)(g.n_tiles < kNumSMs ? g.n_tiles : kNumSMs);
-    kern<<<grid, NT, L::TOTAL, st>>>(ta, tb, g.n, (int)g.n_tiles, g.nct, g.NK16, w.cand_val, w.cand_code);
+    kern<<<grid, NT, L::TOTAL, st>>>(ta, tb, g.n, (int)g.n_tiles, g.nct, g.NK16, w.zn, w.emax, w.cand, w.cand_meta);
     LIPVQ_LAUNCH_OK();
     return LIPVQ_OK;
 }
@@ -492,7 +583,7 @@ inline int vq_tensor_launch(const float *z, const float *E, int64_t n, int D, in
     void *ws_al = (void *)align_up((size_t)ws, 1024);
     const Workspace w = carve(ws_al, g);
     LIPVQ_CUDA_OK(cudaMemsetAsync(w.counters, 0, 4 * sizeof(int), st));
-    vq_prep_mean_kernel<<<(D + 127) / 128, 128, 0, st>>>(E, K, D, w.mu);
+    vq_prep_mean_kernel<<<(D + 31) / 32, 1024, 0, st>>>(E, K, D, w.mu);
     LIPVQ_LAUNCH_OK();
     vq_prep_rows_kernel<<<(g.Kp + 7) / 8, 256, 0, st>>>(E, w.mu, K, g.Kp, D, g.DKp, w.Eb, w.enorm);
     LIPVQ_LAUNCH_OK();
@@ -507,26 +598,37 @@ inline int vq_tensor_launch(const float *z, const float *E, int64_t n, int D, in
     CUtensorMap ta, tb;
     LIPVQ_TRY(make_tmap(&ta, w.Zb, (uint64_t)g.Np, (uint64_t)g.DKp, BM));
     LIPVQ_TRY(make_tmap(&tb, w.Eb, (uint64_t)g.Kp, (uint64_t)g.DKp, BN));
-    const bool c8 = D <= 96;
+    // variant: small D has little epilogue slack per MMA -> 8-wide chunks without element payload
+    // (LIPVQ_TC_SMALL_D_ELEM=1 forces the element payload there too, for measurements)
+    static const int elem_env = [] { const char *e = getenv("LIPVQ_TC_ELEM"); return e ? atoi(e) : -1; }();
+    const bool elem = elem_env >= 0 ? elem_env != 0 : D > 96;
+    const bool c8 = !elem && D <= 96;     // chunk-level records: 8-wide chunks for small D, 4-wide otherwise
     int rc = LIPVQ_ESHAPE;
+#define LIPVQ_TC(NKB_, AB_, ST_)                                                                          \
+    rc = elem ? launch_tc<NKB_, AB_, ST_, 4, true>(ta, tb, g, w, st)                                      \
+              : (c8 ? launch_tc<NKB_, AB_, ST_, 8, false>(ta, tb, g, w, st)                               \
+                    : launch_tc<NKB_, AB_, ST_, 4, false>(ta, tb, g, w, st))
     switch (g.NKB) {
-        case 1: rc = c8 ? launch_tc<1, 2, 6, 8>(ta, tb, g, w, st) : launch_tc<1, 2, 6, 4>(ta, tb, g, w, st); break;
-        case 2: rc = c8 ? launch_tc<2, 2, 5, 8>(ta, tb, g, w, st) : launch_tc<2, 2, 5, 4>(ta, tb, g, w, st); break;
-        case 3: rc = launch_tc<3, 2, 4, 4>(ta, tb, g, w, st); break;
-        case 4: rc = launch_tc<4, 2, 3, 4>(ta, tb, g, w, st); break;
-        case 5: rc = launch_tc<5, 1, 4, 4>(ta, tb, g, w, st); break;
+        case 1: LIPVQ_TC(1, 2, 6); break;
+        case 2: LIPVQ_TC(2, 2, 5); break;
+        case 3: LIPVQ_TC(3, 2, 4); break;
+        case 4: LIPVQ_TC(4, 2, 3); break;
+        case 5: LIPVQ_TC(5, 1, 4); break;
         default: break;
     }
+#undef LIPVQ_TC
     LIPVQ_TRY(rc);
     {
         int64_t blocks = (n + 7) / 8;
         if (blocks > 16 * kNumSMs) blocks = 16 * kNumSMs;
-        if (c8)
-            vq_rescore_kernel<8><<<(unsigned)blocks, 256, 0, st>>>(z, E, n, D, K, w.cand_val, w.cand_code, w.zn, w.emax,
-                                                                  idx, d2, w.list, w.counters);
-        else
-            vq_rescore_kernel<4><<<(unsigned)blocks, 256, 0, st>>>(z, E, n, D, K, w.cand_val, w.cand_code, w.zn, w.emax,
-                                                                  idx, d2, w.list, w.counters);
+        const bool vec = (D & 3) == 0;
+#define LIPVQ_RESC(CH, EL, VE)                                                                                   \
+    vq_rescore_kernel<CH, EL, VE><<<(unsigned)blocks, 256, 0, st>>>(z, E, n, D, K, w.cand, w.cand_meta, w.zn, w.emax, \
+                                                                    idx, d2, w.list, w.counters)
+        if (elem)    { if (vec) LIPVQ_RESC(4, true, true);   else LIPVQ_RESC(4, true, false); }
+        else if (c8) { if (vec) LIPVQ_RESC(8, false, true);  else LIPVQ_RESC(8, false, false); }
+        else         { if (vec) LIPVQ_RESC(4, false, true);  else LIPVQ_RESC(4, false, false); }
+#undef LIPVQ_RESC
         LIPVQ_LAUNCH_OK();
     }
     // tier 2: rows whose candidate list overflowed -> exact fp32 scan (count stays on the device)

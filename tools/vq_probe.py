@@ -43,11 +43,16 @@ def run(n, D, K, dist="uniform", iters=5):
         idx = torch.full((n,), -1, dtype=torch.int64, device=dev)
         d2 = torch.zeros(n, device=dev)
         stats = torch.zeros(4, dtype=torch.int32, device=dev)
-        def call():
-            N.check(lib.lipvq_vq_argmin(z.data_ptr(), E.data_ptr(), n, D, K, mode, idx.data_ptr(), d2.data_ptr(),
+        def call(with_d2=False):
+            N.check(lib.lipvq_vq_argmin(z.data_ptr(), E.data_ptr(), n, D, K, mode, idx.data_ptr(),
+                                        d2.data_ptr() if with_d2 else None,
                                         stats.data_ptr(), ws.data_ptr(), ws.numel(), st), "vq_argmin")
+        call(True)
+        torch.cuda.synchronize()
+        idx_d2 = idx.clone()
         call()
         torch.cuda.synchronize()
+        assert torch.equal(idx, idx_d2), "index differs between the d2 and the no-d2 path"
         s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         s.record()
         for _ in range(iters):
@@ -63,9 +68,9 @@ def run(n, D, K, dist="uniform", iters=5):
     bad = int((diff & (rel > 2.5e-5)).sum())
     tf = 2.0 * n * D * K / 1e12
     print("N=%d D=%d K=%d %-9s exact %.3f ms (%.1f TF/s) | tensor %.3f ms (%.1f TF/s) | idx diff %d (outside tie "
-          "window: %d) maxrel %.2e | fallback rows %d rescored codes %d (%.2f/row)"
+          "window: %d) maxrel %.2e | fallback rows %d rescored codes %d (%.2f/row) unambiguous rows %.1f%%"
           % (n, D, K, dist, t0, tf / t0 * 1e3, t1, tf / t1 * 1e3, nd, bad, float(rel.max()), s1[0], s1[1],
-             s1[1] / max(n, 1)), flush=True)
+             s1[1] / max(n, 1), 100.0 * s1[2] / max(n, 1)), flush=True)
     if bad:
         w = torch.nonzero(diff & (rel > 2.5e-5))[:8, 0]
         print("  first bad rows", w.tolist(), "exact", i0[w].tolist(), "tensor", i1[w].tolist(),
