@@ -1,0 +1,120 @@
+"""Data-parallel plumbing for the tokenizer: rows shard across ranks, the 14
+parameters are replicated, and the only collective is ONE all-reduce per training step over a
+flat fp32 bucket (gradients, or EMA counts/sums).  The reference has no distributed code
+(single process on cuda:0, robomimic/utils/torch_utils.py:48-50); this wrapper adds the one
+strategy the path supports.  Works on any ``torch.distributed`` backend (NCCL on the GPUs; the
+host-side logic is covered with gloo on CPU in tests/test_dist_cpu.py).
+"""
+from __future__ import annotations
+
+import torch
+import torch.distributed as dist
+
+CHUNK_LEN = 10  # rows per action chunk (obs_nets.py:1298)
+
+
+def shard_rows(n_total: int, rank: int, world: int, align: int = CHUNK_LEN):
+    """Contiguous, chunk-aligned [start, stop) row range of ``rank``; the ranges tile [0, n_total)."""
+    if world < 1 or not (0 <= rank < world):
+        raise ValueError("bad rank/world %r/%r" % (rank, world))
+    units = (n_total + align - 1) // align
+    base, rem = divmod(units, world)
+    u0 = rank * base + min(rank, rem)
+    u1 = u0 + base + (1 if rank < rem else 0)
+    return min(u0 * align, n_total), min(u1 * align, n_total)
+
+
+class FlatBucket:
+    """One contiguous fp32 buffer viewed as a list of tensors (a single collective per step)."""
+
+    def __init__(self, shapes, device, extra=0):
+        self.shapes = [tuple(s) for s in shapes]
+        self.sizes = [int(torch.Size(s).numel()) for s in self.shapes]
+        self.flat = torch.zeros(sum(self.sizes) + extra, dtype=torch.float32, device=device)
+        self.views, off = [], 0
+        for s, n in zip(self.shapes, self.sizes):
+            self.views.append(self.flat[off:off + n].view(s))
+            off += n
+        self.extra = self.flat[off:]
+
+    def pack(self, tensors):
+        for v, t in zip(self.views, tensors):
+            if t is None:
+                v.zero_()
+            else:
+                v.copy_(t)
+
+    def unpack_into(self, tensors):
+        for v, t in zip(self.views, tensors):
+            if t is not None:
+                t.copy_(v)
+
+
+class DataParallelTokenizer:
+    """Wraps an ``LLFQVAE_V4``: call it on the rank's row shard, then ``allreduce_grads()``.
+
+    The kernels take the GLOBAL row count (``n_total_rows``), so each rank's loss and gradients
+    already carry the 1/N_global factor and the collective is a plain SUM: the result equals the
+    single-process gradient on the concatenated batch up to fp32 summation order.
+    """
+
+    def __init__(self, model, process_group=None, broadcast_params=True):
+        self.model = model
+        self.pg = process_group
+        self.world = dist.get_world_size(process_group) if dist.is_initialized() else 1
+        self.rank = dist.get_rank(process_group) if dist.is_initialized() else 0
+        self._bucket = None
+        self._stat_bucket = None
+        if broadcast_params and self.world > 1:
+            for p in model.parameters():
+                dist.broadcast(p.data, src=0, group=process_group)
+
+    # ------------------------------------------------------------------ forward
+    def global_rows(self, n_local: int, device) -> int:
+        if self.world == 1:
+            return n_local
+        t = torch.tensor([n_local], dtype=torch.int64, device=device)
+        dist.all_reduce(t, group=self.pg)
+        return int(t.item())
+
+    def __call__(self, x_local, n_total=None):
+        """forward on this rank's rows; ``n_total`` (global rows) skips the count all-reduce."""
+        if n_total is None:
+            n_total = self.global_rows(x_local.shape[0], x_local.device)
+        self.model.n_total_rows = n_total
+        return self.model(x_local)
+
+    # ------------------------------------------------------------------ collectives
+    def _params(self):
+        return [p for p in self.model.parameters()]
+
+    def allreduce_grads(self, loss=None):
+        """SUM all gradients (and optionally the scalar loss, same bucket) across ranks."""
+        params = self._params()
+        if self._bucket is None:
+            self._bucket = FlatBucket([p.shape for p in params], params[0].device, extra=1)
+        b = self._bucket
+        b.pack([p.grad for p in params])
+        if loss is not None:
+            b.extra.copy_(loss.detach().reshape(1))
+        else:
+            b.extra.zero_()
+        if self.world > 1:
+            dist.all_reduce(b.flat, group=self.pg)
+        for p, v in zip(params, b.views):
+            if p.grad is None:
+                p.grad = v.clone()
+            else:
+                p.grad.copy_(v)
+        return b.extra[0] if loss is not None else None
+
+    def allreduce_codebook_stats(self, counts, sums):
+        """EMA mode: SUM counts[K] and sums[K,D] in one collective (in place)."""
+        if self._stat_bucket is None or self._stat_bucket.shapes != [tuple(counts.shape), tuple(sums.shape)]:
+            self._stat_bucket = FlatBucket([counts.shape, sums.shape], counts.device)
+        b = self._stat_bucket
+        b.pack([counts, sums])
+        if self.world > 1:
+            dist.all_reduce(b.flat, group=self.pg)
+        b.unpack_into([counts, sums])
+        return counts, sums
