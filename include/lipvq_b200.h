@@ -135,6 +135,14 @@ int lipvq_decoder_fwd(const lipvq_dims_t *dims, const lipvq_params_t *p, const f
                       const float *x, int64_t n_rows, const lipvq_acts_t *acts, double *sse_r,
                       void *ws, size_t ws_bytes, void *stream);
 
+/* Gather + decoder + both loss sums in one pass (v5:47, 74-81): z_q[n] = E[idx[n]] is written to
+ * acts->z_q (this IS z_latent, v5:74), x_recon to acts->x_recon, and sse[0] = sum (x_recon-x)^2,
+ * sse[1] = sum (z_q-z_e)^2 (device double[2], overwritten).  acts: idx, z_e are read; z_q, x_recon are
+ * written; c1,d1,c2,d2 are written when non-null (kept for backward).  x may be null (sse[0] = 0). */
+int lipvq_quantize_decode_fwd(const lipvq_dims_t *dims, const lipvq_params_t *p, const float *x,
+                              int64_t n_rows, const lipvq_acts_t *acts, double *sse, void *ws,
+                              size_t ws_bytes, void *stream);
+
 /* loss = sse_r/(n_total*F) + 0.25*sse_q/(n_total*D) + 0.25*sse_q/(n_total*D)  (v5:79-83).
  * out: device float[4] = {loss, recon, commit, codebook}. */
 int lipvq_loss_finalize(const double *sse_r, const double *sse_q, int64_t n_total, int32_t F,

@@ -1,11 +1,13 @@
 // lipvq_abi.cu -- extern "C" entry points declared in include/lipvq_b200.h.
 // Host-side orchestration only: argument checks, workspace carving, kernel launches.
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 
 #include "common.cuh"
 #include "gemm_simt.cuh"
 #include "misc_kernels.cuh"
+#include "mlp_tc.cuh"
 #include "vq_exact.cuh"
 #include "vq_tensor.cuh"
 
@@ -30,6 +32,12 @@ static bool dims_ok(const lipvq_dims_t *d) {
            d->D >= 1 && d->D <= 8192 && d->K >= 1 && d->K <= (1 << 20);
 }
 
+// LIPVQ_MLP=simt forces the fp32 CUDA-core layer kernels (A/B measurements); default = tensor cores
+static bool use_mlp_tc(const lipvq_dims_t *d) {
+    static const bool simt = [] { const char *e = getenv("LIPVQ_MLP"); return e && !strcmp(e, "simt"); }();
+    return !simt && mlp::supported(d);
+}
+
 static size_t max_splitk_floats(const lipvq_dims_t *d, int64_t n) {
     size_t m = 0;
     auto up = [&](int Nout, int Kin) { size_t v = splitk_ws_floats(n, Nout, Kin); if (v > m) m = v; };
@@ -52,6 +60,7 @@ static size_t workspace_bytes_impl(const lipvq_dims_t *d, int64_t n) {
     size_t bytes = fl * sizeof(float) + 64 * 256;    // alignment slack for the bump allocator
     bytes += vq_tensor_ws_bytes(n, d->D, d->K);
     bytes += N * sizeof(int64_t) + 4096;
+    bytes += mlp::kPartBytes + 256;
     return align_up(bytes, 256);
 }
 }  // namespace lipvq
@@ -98,12 +107,16 @@ int lipvq_encoder_fwd(const lipvq_dims_t *d, const lipvq_params_t *p, const floa
     if (!dims_ok(d) || n < 0) return LIPVQ_ESHAPE;
     if (!p || !a) return LIPVQ_EALIGN;
     if (n == 0) return LIPVQ_OK;
-    if (!aligned16(x) || !aligned16(a->a1) || !aligned16(a->h1) || !aligned16(a->a2) || !aligned16(a->h2) ||
-        !aligned16(a->scale) || !aligned16(a->Wn) || !aligned16(a->z_e))
+    const bool tc = use_mlp_tc(d);   // tensor path: a1/h1/a2 are optional outputs (kept only for backward)
+    auto opt16 = [](const void *q) { return q == nullptr || aligned16(q); };
+    if (!aligned16(x) || !aligned16(a->h2) || !aligned16(a->scale) || !aligned16(a->Wn) || !aligned16(a->z_e))
+        return LIPVQ_EALIGN;
+    if (tc ? !(opt16(a->a1) && opt16(a->h1) && opt16(a->a2)) : !(aligned16(a->a1) && aligned16(a->h1) && aligned16(a->a2)))
         return LIPVQ_EALIGN;
     cudaStream_t st = (cudaStream_t)stream;
     lipschitz_prep_kernel<<<(d->D + 7) / 8, 256, 0, st>>>(p->lat_W, p->lat_ci, d->D, d->H, a->scale, a->Wn);
     LIPVQ_LAUNCH_OK();
+    if (tc) return mlp::encoder_launch(d, p, x, n, a->a1, a->h1, a->a2, a->h2, a->Wn, a->z_e, st);
     LIPVQ_TRY(linear_fwd<ACT_GELU>(x, p->enc0_w, p->enc0_b, a->a1, a->h1, n, d->H1, d->F, st));
     LIPVQ_TRY(linear_fwd<ACT_GELU>(a->h1, p->enc2_w, p->enc2_b, a->a2, a->h2, n, d->H, d->H1, st));
     LIPVQ_TRY(linear_fwd<ACT_SIGMOID>(a->h2, a->Wn, p->lat_b, nullptr, a->z_e, n, d->D, d->H, st));
@@ -189,6 +202,25 @@ int lipvq_decoder_fwd(const lipvq_dims_t *d, const lipvq_params_t *p, const floa
         LIPVQ_LAUNCH_OK();
     }
     return LIPVQ_OK;
+}
+
+int lipvq_quantize_decode_fwd(const lipvq_dims_t *d, const lipvq_params_t *p, const float *x, int64_t n,
+                              const lipvq_acts_t *a, double *sse, void *ws, size_t ws_bytes, void *stream) {
+    if (!dims_ok(d) || n < 0) return LIPVQ_ESHAPE;
+    if (!p || !a || !sse) return LIPVQ_EALIGN;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (n == 0) { LIPVQ_CUDA_OK(cudaMemsetAsync(sse, 0, 2 * sizeof(double), st)); return LIPVQ_OK; }
+    if (!a->idx || !aligned16(a->z_e) || !aligned16(a->z_q) || !aligned16(a->x_recon) || (x && !aligned16(x)))
+        return LIPVQ_EALIGN;
+    if (ws_bytes < mlp::kPartBytes + 256 || !aligned16(ws)) return LIPVQ_EWORKSPACE;
+    if (use_mlp_tc(d))
+        return mlp::decoder_launch(d, p, a->idx, p->codebook, a->z_e, x, n, a->z_q, a->c1, a->d1, a->c2, a->d2,
+                                   a->x_recon, (double *)ws, sse, st);
+    // CUDA-core path: gather+loss pass, then the three layer kernels (needs c1..d2 buffers)
+    if (!a->c1 || !a->d1 || !a->c2 || !a->d2) return LIPVQ_EALIGN;
+    if (!x) LIPVQ_CUDA_OK(cudaMemsetAsync(sse, 0, sizeof(double), st));
+    LIPVQ_TRY(lipvq_gather_loss(a->z_e, p->codebook, a->idx, n, d->D, d->K, a->z_q, sse + 1, ws, ws_bytes, stream));
+    return lipvq_decoder_fwd(d, p, a->z_q, x, n, a, sse, ws, ws_bytes, stream);
 }
 
 int lipvq_loss_finalize(const double *sse_r, const double *sse_q, int64_t n_total, int32_t F, int32_t D,
@@ -277,25 +309,30 @@ int lipvq_forward_fused(const lipvq_dims_t *d, const lipvq_params_t *p, const fl
     cudaStream_t st = (cudaStream_t)stream;
     Bump b(ws, ws_bytes);
     lipvq_acts_t a;
-    a.a1 = b.take<float>((size_t)n * d->H1); a.h1 = b.take<float>((size_t)n * d->H1);
-    a.a2 = b.take<float>((size_t)n * d->H);  a.h2 = b.take<float>((size_t)n * d->H);
+    const bool tc = use_mlp_tc(d);   // tensor path keeps h1/a*/c*/d* on chip: only h2 and z_e touch HBM
+    a.a1 = a.h1 = a.a2 = nullptr;
+    if (!tc) {
+        a.a1 = b.take<float>((size_t)n * d->H1); a.h1 = b.take<float>((size_t)n * d->H1);
+        a.a2 = b.take<float>((size_t)n * d->H);
+    }
+    a.h2 = b.take<float>((size_t)n * d->H);
     a.scale = b.take<float>(d->D); a.Wn = b.take<float>((size_t)d->D * d->H);
     a.z_e = b.take<float>((size_t)n * d->D);
     a.idx = idx ? idx : b.take<int64_t>(n);
     a.z_q = z_latent;
-    a.c1 = a.a1; a.d1 = a.h1; a.c2 = a.a2; a.d2 = a.h2;   // encoder activations are dead by then
+    a.c1 = a.a1; a.d1 = a.h1; a.c2 = a.a2; a.d2 = tc ? nullptr : a.h2;   // encoder activations are dead by then
     a.x_recon = x_recon ? x_recon : b.take<float>((size_t)n * d->F);
     double *sse = b.take<double>(2);
-    float *part = b.take<float>(kRedBlocks);
+    const size_t part_bytes = mlp::kPartBytes + 256 > kRedBlocks * sizeof(float) ? mlp::kPartBytes + 256
+                                                                                  : kRedBlocks * sizeof(float);
+    float *part = (float *)b.take<char>(part_bytes);
     const size_t vq_bytes = vq_tensor_ws_bytes(n, d->D, d->K);
     void *vq_ws = b.take<char>(vq_bytes);
     if (!b.ok()) return LIPVQ_EWORKSPACE;
     LIPVQ_TRY(lipvq_encoder_fwd(d, p, x, n, &a, nullptr, 0, stream));
     LIPVQ_TRY(lipvq_vq_argmin(a.z_e, p->codebook, n, d->D, d->K, search_mode, a.idx, nullptr, stats, vq_ws,
                               vq_bytes, stream));
-    LIPVQ_TRY(lipvq_gather_loss(a.z_e, p->codebook, a.idx, n, d->D, d->K, a.z_q, sse + 1, part,
-                                kRedBlocks * sizeof(float), stream));
-    LIPVQ_TRY(lipvq_decoder_fwd(d, p, a.z_q, x, n, &a, sse, part, kRedBlocks * sizeof(float), stream));
+    LIPVQ_TRY(lipvq_quantize_decode_fwd(d, p, x, n, &a, sse, part, part_bytes, stream));
     if (loss_out) LIPVQ_TRY(lipvq_loss_finalize(sse, sse + 1, n_total, d->F, d->D, loss_out, stream));
     (void)st;
     return LIPVQ_OK;

@@ -117,10 +117,8 @@ class _TokenizerFn(torch.autograd.Function):
                 "lipvq_encoder_fwd")
         N.check(lib.lipvq_vq_argmin(_p(z_e), _p(params[7]), n, D, K, search_mode, _p(idx), None, _p(vq_stats),
                                     _p(ws), wsz, st), "lipvq_vq_argmin")
-        N.check(lib.lipvq_gather_loss(_p(z_e), _p(params[7]), _p(idx), n, D, K, _p(z_q),
-                                      C.c_void_p(sse.data_ptr() + 8), _p(ws), wsz, st), "lipvq_gather_loss")
-        N.check(lib.lipvq_decoder_fwd(C.byref(dims), C.byref(P), _p(z_q), _p(x), n, C.byref(A), _p(sse), _p(ws),
-                                      wsz, st), "lipvq_decoder_fwd")
+        N.check(lib.lipvq_quantize_decode_fwd(C.byref(dims), C.byref(P), _p(x), n, C.byref(A), _p(sse), _p(ws),
+                                              wsz, st), "lipvq_quantize_decode_fwd")
         N.check(lib.lipvq_loss_finalize(_p(sse), C.c_void_p(sse.data_ptr() + 8), n_total, F_, D, _p(stats), st),
                 "lipvq_loss_finalize")
         ctx.save_for_backward(x, *params, a1, h1, a2, h2, scale, Wn, z_e, idx, z_q, c1, d1, c2, d2, x_recon)
