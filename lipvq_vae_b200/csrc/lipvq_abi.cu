@@ -8,6 +8,7 @@
 #include "gemm_simt.cuh"
 #include "misc_kernels.cuh"
 #include "mlp_tc.cuh"
+#include "mlp_dec2.cuh"
 #include "vq_exact.cuh"
 #include "vq_tensor.cuh"
 
@@ -60,7 +61,7 @@ static size_t workspace_bytes_impl(const lipvq_dims_t *d, int64_t n) {
     size_t bytes = fl * sizeof(float) + 64 * 256;    // alignment slack for the bump allocator
     bytes += vq_tensor_ws_bytes(n, d->D, d->K);
     bytes += N * sizeof(int64_t) + 4096;
-    bytes += mlp::kPartBytes + 256;
+    bytes += mlp::dec2_ws_bytes(d->K) + kRedBlocks * sizeof(float) + 256;
     return align_up(bytes, 256);
 }
 }  // namespace lipvq
@@ -212,10 +213,16 @@ int lipvq_quantize_decode_fwd(const lipvq_dims_t *d, const lipvq_params_t *p, co
     if (n == 0) { LIPVQ_CUDA_OK(cudaMemsetAsync(sse, 0, 2 * sizeof(double), st)); return LIPVQ_OK; }
     if (!a->idx || !aligned16(a->z_e) || !aligned16(a->z_q) || !aligned16(a->x_recon) || (x && !aligned16(x)))
         return LIPVQ_EALIGN;
-    if (ws_bytes < mlp::kPartBytes + 256 || !aligned16(ws)) return LIPVQ_EWORKSPACE;
-    if (use_mlp_tc(d))
-        return mlp::decoder_launch(d, p, a->idx, p->codebook, a->z_e, x, n, a->z_q, a->c1, a->d1, a->c2, a->d2,
-                                   a->x_recon, (double *)ws, sse, st);
+    const size_t need = mlp::dec2_ws_bytes(d->K) + kRedBlocks * sizeof(float) + 256;
+    if (ws_bytes < need || !aligned16(ws)) return LIPVQ_EWORKSPACE;
+    if (use_mlp_tc(d)) {
+        // z_q / z_latent + sum (z_q-z_e)^2: one HBM-bound streaming pass; decoder from the codeword table
+        char *gws = (char *)ws + align_up(mlp::dec2_ws_bytes(d->K), 256);
+        if (!x) LIPVQ_CUDA_OK(cudaMemsetAsync(sse, 0, sizeof(double), st));
+        LIPVQ_TRY(lipvq_gather_loss(a->z_e, p->codebook, a->idx, n, d->D, d->K, a->z_q, sse + 1, gws,
+                                    kRedBlocks * sizeof(float), stream));
+        return mlp::decoder2_launch(d, p, a->idx, x, n, a->c1, a->d1, a->c2, a->d2, a->x_recon, ws, sse, st);
+    }
     // CUDA-core path: gather+loss pass, then the three layer kernels (needs c1..d2 buffers)
     if (!a->c1 || !a->d1 || !a->c2 || !a->d2) return LIPVQ_EALIGN;
     if (!x) LIPVQ_CUDA_OK(cudaMemsetAsync(sse, 0, sizeof(double), st));
@@ -323,8 +330,7 @@ int lipvq_forward_fused(const lipvq_dims_t *d, const lipvq_params_t *p, const fl
     a.c1 = a.a1; a.d1 = a.h1; a.c2 = a.a2; a.d2 = tc ? nullptr : a.h2;   // encoder activations are dead by then
     a.x_recon = x_recon ? x_recon : b.take<float>((size_t)n * d->F);
     double *sse = b.take<double>(2);
-    const size_t part_bytes = mlp::kPartBytes + 256 > kRedBlocks * sizeof(float) ? mlp::kPartBytes + 256
-                                                                                  : kRedBlocks * sizeof(float);
+    const size_t part_bytes = mlp::dec2_ws_bytes(d->K) + kRedBlocks * sizeof(float) + 512;
     float *part = (float *)b.take<char>(part_bytes);
     const size_t vq_bytes = vq_tensor_ws_bytes(n, d->D, d->K);
     void *vq_ws = b.take<char>(vq_bytes);

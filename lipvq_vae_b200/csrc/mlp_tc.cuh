@@ -93,10 +93,11 @@ __device__ __forceinline__ void store_split16(uint32_t t_hi, uint32_t t_lo, cons
 
 // 16 consecutive floats of one row -> global (vector stores when the row pitch allows)
 __device__ __forceinline__ void store_row16(float *__restrict__ dst, const float (&v)[16], int valid, bool vec) {
-    if (vec && valid == 16) {
+    if (vec && (valid & 3) == 0) {
 #pragma unroll
         for (int i = 0; i < 4; ++i)
-            reinterpret_cast<float4 *>(dst)[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+            if (4 * i < valid)
+                reinterpret_cast<float4 *>(dst)[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
     } else {
 #pragma unroll
         for (int i = 0; i < 16; ++i)
@@ -333,7 +334,8 @@ dec_kernel(const int64_t *__restrict__ idx, const float *__restrict__ E, const f
            const float *__restrict__ Wd1, const float *__restrict__ bd1, const float *__restrict__ Wo,
            const float *__restrict__ bo, int64_t n_rows, int D, int K, int F, float *__restrict__ z_q,
            float *__restrict__ c1, float *__restrict__ d1, float *__restrict__ c2, float *__restrict__ d2,
-           float *__restrict__ x_recon, double *__restrict__ part /* [gridDim.x][2] = sse_r, sse_q */) {
+           float *__restrict__ x_recon, double *__restrict__ part /* [gridDim.x][2] = sse_r, sse_q */,
+           float *__restrict__ table_out /* non-null: stop after layer 0 and write src*Wd0^T (no bias) [n,64] */) {
     extern __shared__ uint8_t smem_raw[];
     const uint32_t raw = ptx::smem_u32(smem_raw);
     uint8_t *sm = smem_raw + (((raw + 1023u) & ~1023u) - raw);
@@ -347,7 +349,7 @@ dec_kernel(const int64_t *__restrict__ idx, const float *__restrict__ E, const f
     stage_weight(sm + L.w0, sm + L.w0 + L.img0, Wd0, H1, D, H1, L.KB0);
     stage_weight(sm + L.w1, sm + L.w1 + L.img1, Wd1, HH, H1, HH, 2);
     stage_weight(sm + L.w2, sm + L.w2 + L.img2, Wo, F, HH, 16, 4);
-    for (int i = threadIdx.x; i < H1; i += NTHR) sb0[i] = bd0[i];
+    for (int i = threadIdx.x; i < H1; i += NTHR) sb0[i] = table_out ? 0.f : bd0[i];
     for (int i = threadIdx.x; i < HH; i += NTHR) sb1[i] = bd1[i];
     for (int i = threadIdx.x; i < 16; i += NTHR) sb2[i] = i < F ? bo[i] : 0.f;
     ptx::fence_proxy_async();
@@ -394,6 +396,11 @@ dec_kernel(const int64_t *__restrict__ idx, const float *__restrict__ E, const f
             __syncthreads();
         }
         run_layer(t_acc1, t_zhi, t_zlo, s0 + L.w0, s0 + L.w0 + L.img0, H1, D16 / 8, c.bar, c.phase);
+        if (table_out) {
+            epilogue<ACT_NONE>(t_acc1, H1, H1, sb0, false, 0u, 0u, row_ok ? table_out + row * H1 : nullptr, H1, true,
+                               c.half, NoFn());
+            continue;
+        }
         {
             float *d1r = (d1 && row_ok) ? d1 + row * H1 : nullptr;
             epilogue<ACT_GELU>(t_acc1, H1, H1, sb0, true, c.tmem + 0, c.tmem + 64,
@@ -486,7 +493,7 @@ inline int decoder_launch(const lipvq_dims_t *d, const lipvq_params_t *p, const 
     const int grid = grid_for(n);
     dec_kernel<<<grid, NTHR, L.total, st>>>(idx, src, z_e, x, p->dec0_w, p->dec0_b, p->dec2_w, p->dec2_b,
                                             p->out_w, p->out_b, n, d->D, d->K, d->F, z_q, c1, d1, c2, d2, x_recon,
-                                            part);
+                                            part, nullptr);
     LIPVQ_LAUNCH_OK();
     sum_partials2_kernel<<<1, 32, 0, st>>>(part, grid, sse);
     LIPVQ_LAUNCH_OK();
