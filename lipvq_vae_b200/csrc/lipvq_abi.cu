@@ -9,6 +9,7 @@
 #include "misc_kernels.cuh"
 #include "mlp_tc.cuh"
 #include "mlp_dec2.cuh"
+#include "mlp_enc.cuh"
 #include "vq_exact.cuh"
 #include "vq_tensor.cuh"
 
@@ -62,6 +63,7 @@ static size_t workspace_bytes_impl(const lipvq_dims_t *d, int64_t n) {
     bytes += vq_tensor_ws_bytes(n, d->D, d->K);
     bytes += N * sizeof(int64_t) + 4096;
     bytes += mlp::dec2_ws_bytes(d->K) + kRedBlocks * sizeof(float) + 256;
+    bytes += mlp::enc_img_bytes(d->D) + 2048;
     return align_up(bytes, 256);
 }
 }  // namespace lipvq
@@ -104,20 +106,25 @@ int lipvq_workspace_bytes(const lipvq_dims_t *dims, int64_t n_rows, size_t *out_
 
 int lipvq_encoder_fwd(const lipvq_dims_t *d, const lipvq_params_t *p, const float *x, int64_t n,
                       const lipvq_acts_t *a, void *ws, size_t ws_bytes, void *stream) {
-    (void)ws; (void)ws_bytes;
     if (!dims_ok(d) || n < 0) return LIPVQ_ESHAPE;
     if (!p || !a) return LIPVQ_EALIGN;
     if (n == 0) return LIPVQ_OK;
     const bool tc = use_mlp_tc(d);   // tensor path: a1/h1/a2 are optional outputs (kept only for backward)
     auto opt16 = [](const void *q) { return q == nullptr || aligned16(q); };
-    if (!aligned16(x) || !aligned16(a->h2) || !aligned16(a->scale) || !aligned16(a->Wn) || !aligned16(a->z_e))
+    if (!aligned16(x) || !aligned16(a->scale) || !aligned16(a->Wn) || !aligned16(a->z_e)) return LIPVQ_EALIGN;
+    if (tc ? !(opt16(a->a1) && opt16(a->h1) && opt16(a->a2) && opt16(a->h2))
+           : !(aligned16(a->a1) && aligned16(a->h1) && aligned16(a->a2) && aligned16(a->h2)))
         return LIPVQ_EALIGN;
-    if (tc ? !(opt16(a->a1) && opt16(a->h1) && opt16(a->a2)) : !(aligned16(a->a1) && aligned16(a->h1) && aligned16(a->a2)))
-        return LIPVQ_EALIGN;
+    if (tc && (ws == nullptr || ws_bytes < mlp::enc_img_bytes(d->D) + 1024)) return LIPVQ_EWORKSPACE;
     cudaStream_t st = (cudaStream_t)stream;
     lipschitz_prep_kernel<<<(d->D + 7) / 8, 256, 0, st>>>(p->lat_W, p->lat_ci, d->D, d->H, a->scale, a->Wn);
     LIPVQ_LAUNCH_OK();
-    if (tc) return mlp::encoder_launch(d, p, x, n, a->a1, a->h1, a->a2, a->h2, a->Wn, a->z_e, st);
+    if (tc) {
+        static const bool split = [] { const char *e = getenv("LIPVQ_ENC"); return e && !strcmp(e, "split"); }();
+        if (split && a->h2) return mlp::encoder_launch(d, p, x, n, a->a1, a->h1, a->a2, a->h2, a->Wn, a->z_e, st);
+        uint8_t *img = (uint8_t *)align_up((size_t)ws, 1024);
+        return mlp::encoder_fused_launch(d, p, x, n, a->a1, a->h1, a->a2, a->h2, a->Wn, a->z_e, img, st);
+    }
     LIPVQ_TRY(linear_fwd<ACT_GELU>(x, p->enc0_w, p->enc0_b, a->a1, a->h1, n, d->H1, d->F, st));
     LIPVQ_TRY(linear_fwd<ACT_GELU>(a->h1, p->enc2_w, p->enc2_b, a->a2, a->h2, n, d->H, d->H1, st));
     LIPVQ_TRY(linear_fwd<ACT_SIGMOID>(a->h2, a->Wn, p->lat_b, nullptr, a->z_e, n, d->D, d->H, st));
@@ -322,7 +329,7 @@ int lipvq_forward_fused(const lipvq_dims_t *d, const lipvq_params_t *p, const fl
         a.a1 = b.take<float>((size_t)n * d->H1); a.h1 = b.take<float>((size_t)n * d->H1);
         a.a2 = b.take<float>((size_t)n * d->H);
     }
-    a.h2 = b.take<float>((size_t)n * d->H);
+    a.h2 = tc ? nullptr : b.take<float>((size_t)n * d->H);
     a.scale = b.take<float>(d->D); a.Wn = b.take<float>((size_t)d->D * d->H);
     a.z_e = b.take<float>((size_t)n * d->D);
     a.idx = idx ? idx : b.take<int64_t>(n);
@@ -334,8 +341,10 @@ int lipvq_forward_fused(const lipvq_dims_t *d, const lipvq_params_t *p, const fl
     float *part = (float *)b.take<char>(part_bytes);
     const size_t vq_bytes = vq_tensor_ws_bytes(n, d->D, d->K);
     void *vq_ws = b.take<char>(vq_bytes);
+    const size_t enc_ws_bytes = mlp::enc_img_bytes(d->D) + 1024;
+    void *enc_ws = b.take<char>(enc_ws_bytes);
     if (!b.ok()) return LIPVQ_EWORKSPACE;
-    LIPVQ_TRY(lipvq_encoder_fwd(d, p, x, n, &a, nullptr, 0, stream));
+    LIPVQ_TRY(lipvq_encoder_fwd(d, p, x, n, &a, enc_ws, enc_ws_bytes, stream));
     LIPVQ_TRY(lipvq_vq_argmin(a.z_e, p->codebook, n, d->D, d->K, search_mode, a.idx, nullptr, stats, vq_ws,
                               vq_bytes, stream));
     LIPVQ_TRY(lipvq_quantize_decode_fwd(d, p, x, n, &a, sse, part, part_bytes, stream));

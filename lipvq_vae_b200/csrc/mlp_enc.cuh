@@ -1,0 +1,273 @@
+// mlp_enc.cuh -- the whole encoder in ONE persistent kernel (v5:54-60, 6-12, 22-24, called v5:71-72):
+//   x[N,F] -> h1 = GELU(x W0^T + b0) -> h2 = GELU(h1 W1^T + b1) -> z_e = sigmoid(h2 Wn^T + b)
+// h1 and h2 never leave the SM.  Every GEMM is 3xTF32 on tcgen05 with the A operand in TMEM (mlp_tc.cuh).
+//
+// Shared memory cannot hold the hi/lo images of all three weights (288 KB at D=208), so W0 and W1 stay
+// resident (80 KB) and the Lipschitz-normalised Wn is streamed from L2 per tile in chunks of ENC_CH output
+// columns through a 2-stage ring of 1-D bulk copies (cp.async.bulk + mbarrier); each chunk's MMA commits
+// its own barrier so the sigmoid epilogue of chunk c overlaps the MMA of chunk c+1.
+//
+// Warps 0..15 (512 threads): staging + epilogues (warp%4 = TMEM lane quarter, warp/4 = 16-column block
+// owner).  Warp 16: control -- one thread issues every tcgen05.mma and every bulk copy.
+// TMEM columns: acc2 -> h2_hi [0,128) | h2_lo [128,256) | acc3 [256,256+D16);
+//               while layers 0/1 run: x_hi 256 | x_lo 272 | acc1 288 | h1_hi 352 | h1_lo 416  (inside acc3's range)
+#pragma once
+#include "mlp_tc.cuh"
+
+namespace lipvq {
+namespace mlp {
+
+constexpr int ENC_EPI = 512;             // epilogue threads
+constexpr int ENC_THR = ENC_EPI + 32;    // + control warp
+constexpr int ENC_CH = 48;               // Wn output columns per streamed chunk
+constexpr int ENC_NCMAX = 8;
+constexpr int ENC_STAGE_BYTES = ENC_CH * 1024;   // hi (CH x 4 blocks x 128 B) + lo
+
+struct EncSmem {
+    static constexpr int W0 = 0, W0_IMG = H1 * 128;
+    static constexpr int W1 = W0 + 2 * W0_IMG, W1_IMG = HH * 128 * 2;
+    static constexpr int RING = W1 + 2 * W1_IMG;
+    static constexpr int XS = RING + 2 * ENC_STAGE_BYTES;          // x staging: 128 rows x 64 B
+    static constexpr int BIAS = XS + TM * 64;                      // b0[64] b1[128] b[256]
+    static constexpr int BAR = BIAS + (H1 + HH + 256) * 4;         // mbarriers (8 B each), then the TMEM slot
+    static constexpr int NBAR = 3 + 2 + ENC_NCMAX + 4;             // a_ready[3] acc_ready[2] acc3[NC] w_full[2] w_empty[2]
+    static constexpr int TOTAL = BAR + NBAR * 8 + 16 + 1024;
+};
+
+// Wn [D,128] -> per-chunk images in global memory: chunk c = rows [c*CH, c*CH+rows_c): [hi | lo], each
+// 4 K-blocks x rows_c x 128 B in the swizzled layout of stage_weight().  One thread per 16-byte piece.
+__global__ void enc_wn_image_kernel(const float *__restrict__ Wn, int D, int D16, uint8_t *__restrict__ img) {
+    const int total = D16 * 4 * 8;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+        const int j = i & 7, kb = (i >> 3) & 3, n = i >> 5;
+        const int c = n / ENC_CH, nl = n - c * ENC_CH, rows_c = min(ENC_CH, D16 - c * ENC_CH);
+        uint32_t h[4], l[4];
+#pragma unroll
+        for (int t = 0; t < 4; ++t) {
+            const float v = n < D ? Wn[(size_t)n * HH + kb * 32 + j * 4 + t] : 0.f;
+            split_tf32(v, h[t], l[t]);
+        }
+        uint8_t *base = img + (size_t)c * ENC_STAGE_BYTES;
+        const int off = kb * rows_c * 128 + nl * 128 + ((j ^ (nl & 7)) << 4);
+        *reinterpret_cast<uint4 *>(base + off) = make_uint4(h[0], h[1], h[2], h[3]);
+        *reinterpret_cast<uint4 *>(base + rows_c * 512 + off) = make_uint4(l[0], l[1], l[2], l[3]);
+    }
+}
+
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void *src, uint32_t bytes, uint32_t bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
+                 "l"(src), "r"(bytes), "r"(bar)
+                 : "memory");
+}
+__device__ __forceinline__ void epi_sync() { asm volatile("bar.sync 1, 512;" ::: "memory"); }
+// epilogue thread: my part of an A operand is in TMEM -> tell the control thread
+__device__ __forceinline__ void a_ready_arrive(uint32_t bar) {
+    ptx::tmem_st_wait();
+    ptx::tc_fence_before();
+    ptx::mbar_arrive(bar);
+}
+
+// epilogue over the 16-column blocks cb in [cb0, cb1) with cb % nsub == sub (see mlp_tc.cuh::epilogue)
+template <int ACT, class Fn>
+__device__ __forceinline__ void epilogue_blocks(uint32_t t_acc, int cb0, int cb1, int sub, int nsub, int n_real,
+                                                const float *sbias, bool write_next, uint32_t t_next_hi,
+                                                uint32_t t_next_lo, float *__restrict__ a_out, bool vec, Fn fn) {
+    int cb = cb0 + ((sub - cb0) % nsub + nsub) % nsub;
+    for (; cb < cb1; cb += nsub) {
+        const int c0 = cb << 4;
+        uint32_t r[16];
+        ptx::tmem_ld_32x32b_x16(t_acc + c0, r);
+        ptx::tmem_ld_wait();
+        float v[16];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]) + sbias[c0 + i];
+        const int valid = min(16, n_real - c0);
+        if (a_out) store_row16(a_out + c0, v, valid, vec);
+#pragma unroll
+        for (int i = 0; i < 16; ++i) v[i] = apply_act<ACT>(v[i]);
+        fn(c0, valid, v);
+        if (write_next) store_split16(t_next_hi + c0, t_next_lo + c0, v);
+    }
+}
+
+__global__ void __launch_bounds__(ENC_THR, 1)
+enc_fused_kernel(const float *__restrict__ x, const float *__restrict__ W0, const float *__restrict__ b0,
+                 const float *__restrict__ W1, const float *__restrict__ b1, const uint8_t *__restrict__ wn_img,
+                 const float *__restrict__ b2, int64_t n_rows, int F, int D, float *__restrict__ a1,
+                 float *__restrict__ h1, float *__restrict__ a2, float *__restrict__ h2, float *__restrict__ z_e) {
+    using L = EncSmem;
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t raw = ptx::smem_u32(smem_raw);
+    uint8_t *sm = smem_raw + (((raw + 1023u) & ~1023u) - raw);
+    const uint32_t s0 = ptx::smem_u32(sm);
+    float *sb0 = reinterpret_cast<float *>(sm + L::BIAS), *sb1 = sb0 + H1, *sb2 = sb1 + HH;
+    const uint32_t bars = s0 + L::BAR;
+    auto bar_a = [&](int l) { return bars + 8u * l; };               // A operand of layer l ready (512 arrivals)
+    auto bar_acc = [&](int l) { return bars + 8u * (3 + l); };       // accumulator of layer 0/1 ready
+    auto bar_acc3 = [&](int c) { return bars + 8u * (5 + c); };      // chunk c of layer 2 ready
+    auto bar_wfull = [&](int s) { return bars + 8u * (5 + ENC_NCMAX + s); };
+    auto bar_wempty = [&](int s) { return bars + 8u * (7 + ENC_NCMAX + s); };
+    volatile uint32_t *tmem_slot = reinterpret_cast<volatile uint32_t *>(sm + L::BAR + L::NBAR * 8);
+
+    const int D16 = pad16(D), NC = (D16 + ENC_CH - 1) / ENC_CH;
+    stage_weight(sm + L::W0, sm + L::W0 + L::W0_IMG, W0, H1, F, H1, 1);
+    stage_weight(sm + L::W1, sm + L::W1 + L::W1_IMG, W1, HH, H1, HH, 2);
+    for (int i = threadIdx.x; i < H1; i += ENC_THR) sb0[i] = b0[i];
+    for (int i = threadIdx.x; i < HH; i += ENC_THR) sb1[i] = b1[i];
+    for (int i = threadIdx.x; i < 256; i += ENC_THR) sb2[i] = i < D ? b2[i] : 0.f;
+    ptx::fence_proxy_async();
+    if (threadIdx.x == 0) {
+        for (int l = 0; l < 3; ++l) ptx::mbar_init(bar_a(l), ENC_EPI);
+        for (int l = 0; l < 2; ++l) ptx::mbar_init(bar_acc(l), 1);
+        for (int c = 0; c < ENC_NCMAX; ++c) ptx::mbar_init(bar_acc3(c), 1);
+        for (int s = 0; s < 2; ++s) { ptx::mbar_init(bar_wfull(s), 1); ptx::mbar_init(bar_wempty(s), 1); }
+        ptx::fence_barrier_init();
+    }
+    if ((threadIdx.x >> 5) == 0) ptx::tmem_alloc<512>(ptx::smem_u32((const void *)tmem_slot));
+    ptx::tc_fence_before();
+    __syncthreads();
+    ptx::tc_fence_after();
+    const uint32_t tmem0 = *tmem_slot;
+
+    const int64_t n_tiles = (n_rows + TM - 1) / TM;
+    const int my_tiles = (int)((n_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x);   // blockIdx.x < n_tiles
+    const int k0_steps = (F + 7) / 8;
+
+    if (threadIdx.x >= ENC_EPI) {
+        // ============================ control warp: one thread issues all MMAs and weight copies
+        if (threadIdx.x == ENC_EPI) {
+            const int total = my_tiles * NC;
+            int g_load = 0;
+            auto load_next = [&]() {   // chunk g_load -> ring stage g_load & 1 (waits until that stage is free)
+                const int s = g_load & 1, c = g_load % NC;
+                if (g_load >= 2) ptx::mbar_wait(bar_wempty(s), ((g_load >> 1) - 1) & 1);
+                const uint32_t bytes = (uint32_t)min(ENC_CH, D16 - c * ENC_CH) * 1024u;
+                ptx::mbar_arrive_expect_tx(bar_wfull(s), bytes);
+                bulk_g2s(s0 + L::RING + s * ENC_STAGE_BYTES, wn_img + (size_t)c * ENC_STAGE_BYTES, bytes, bar_wfull(s));
+                ++g_load;
+            };
+            for (int t = 0; t < my_tiles; ++t) {
+                const uint32_t par = t & 1;
+                while (g_load < total && g_load < t * NC + 2) load_next();
+                ptx::mbar_wait(bar_a(0), par);
+                ptx::tc_fence_after();
+                issue_layer(tmem0 + 288, tmem0 + 256, tmem0 + 272, s0 + L::W0, s0 + L::W0 + L::W0_IMG, H1, k0_steps,
+                            bar_acc(0));
+                ptx::mbar_wait(bar_a(1), par);
+                ptx::tc_fence_after();
+                issue_layer(tmem0 + 0, tmem0 + 352, tmem0 + 416, s0 + L::W1, s0 + L::W1 + L::W1_IMG, HH, H1 / 8,
+                            bar_acc(1));
+                ptx::mbar_wait(bar_a(2), par);
+                ptx::tc_fence_after();
+                for (int c = 0; c < NC; ++c) {
+                    const int g = t * NC + c, s = g & 1, rows_c = min(ENC_CH, D16 - c * ENC_CH);
+                    ptx::mbar_wait(bar_wfull(s), (g >> 1) & 1);
+                    ptx::tc_fence_after();
+                    const uint32_t st = s0 + L::RING + s * ENC_STAGE_BYTES;
+                    issue_layer(tmem0 + 256 + c * ENC_CH, tmem0 + 0, tmem0 + 128, st, st + rows_c * 512, rows_c,
+                                HH / 8, bar_acc3(c));
+                    ptx::umma_commit(bar_wempty(s));
+                    while (g_load < total && g_load <= g + 1) load_next();
+                }
+            }
+        }
+    } else {
+        // ============================ staging + epilogue warps
+        const int warp = threadIdx.x >> 5, sub = warp >> 2, r_in = threadIdx.x & 127;
+        const uint32_t tm = tmem0 + ((uint32_t)((warp & 3) * 32) << 16);
+        uint8_t *xs = sm + L::XS;
+        const bool vec_x = (F & 3) == 0, vec_d = (D & 3) == 0;
+        // x prefetch: thread t holds float4 #(t&3) of row (t>>2) of the tile
+        const int xr = threadIdx.x >> 2, xj = threadIdx.x & 3;
+        auto fetch_x = [&](int64_t tile) {
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            const int64_t row = tile * TM + xr;
+            const int k0 = xj * 4;
+            if (tile < n_tiles && row < n_rows && k0 < F) {
+                const float *p = x + row * F + k0;
+                if (vec_x && k0 + 3 < F) v = __ldg(reinterpret_cast<const float4 *>(p));
+                else {
+                    v.x = __ldg(p);
+                    if (k0 + 1 < F) v.y = __ldg(p + 1);
+                    if (k0 + 2 < F) v.z = __ldg(p + 2);
+                    if (k0 + 3 < F) v.w = __ldg(p + 3);
+                }
+            }
+            return v;
+        };
+        float4 xq = fetch_x(blockIdx.x);
+        int t = 0;
+        for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++t) {
+            const uint32_t par = t & 1;
+            const int64_t row = tile * TM + r_in;
+            const bool row_ok = row < n_rows;
+            // ---- x -> A operand (hi/lo).  The barrier also orders last tile's acc3 reads before these writes.
+            *reinterpret_cast<float4 *>(xs + xr * 64 + ((xj ^ ((xr >> 1) & 3)) << 4)) = xq;
+            ptx::tc_fence_before();
+            epi_sync();
+            ptx::tc_fence_after();
+            if (sub == 0) {
+                float v[16];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const float4 q = *reinterpret_cast<const float4 *>(xs + r_in * 64 + ((j ^ ((r_in >> 1) & 3)) << 4));
+                    v[4 * j] = q.x; v[4 * j + 1] = q.y; v[4 * j + 2] = q.z; v[4 * j + 3] = q.w;
+                }
+                store_split16(tm + 256, tm + 272, v);
+            }
+            a_ready_arrive(bar_a(0));
+            xq = fetch_x(tile + gridDim.x);          // next tile's x flies during this tile
+            // ---- layer 0 epilogue: h1
+            ptx::mbar_wait(bar_acc(0), par);
+            ptx::tc_fence_after();
+            {
+                float *h1r = (h1 && row_ok) ? h1 + row * H1 : nullptr;
+                epilogue_blocks<ACT_GELU>(tm + 288, 0, H1 / 16, sub, 4, H1, sb0, true, tm + 352, tm + 416,
+                                          (a1 && row_ok) ? a1 + row * H1 : nullptr, true,
+                                          [&](int c0, int valid, float(&v)[16]) { if (h1r) store_row16(h1r + c0, v, valid, true); });
+            }
+            a_ready_arrive(bar_a(1));
+            // ---- layer 1 epilogue: h2 (hi written in place over the accumulator columns just read)
+            ptx::mbar_wait(bar_acc(1), par);
+            ptx::tc_fence_after();
+            {
+                float *h2r = (h2 && row_ok) ? h2 + row * HH : nullptr;
+                epilogue_blocks<ACT_GELU>(tm + 0, 0, HH / 16, sub, 4, HH, sb1, true, tm + 0, tm + 128,
+                                          (a2 && row_ok) ? a2 + row * HH : nullptr, true,
+                                          [&](int c0, int valid, float(&v)[16]) { if (h2r) store_row16(h2r + c0, v, valid, true); });
+            }
+            a_ready_arrive(bar_a(2));
+            // ---- layer 2: per streamed chunk, sigmoid and store z_e
+            float *zr = row_ok ? z_e + row * D : nullptr;
+            for (int c = 0; c < NC; ++c) {
+                ptx::mbar_wait(bar_acc3(c), par);
+                ptx::tc_fence_after();
+                const int cb0 = c * (ENC_CH / 16), cb1 = min(cb0 + ENC_CH / 16, D16 / 16);
+                epilogue_blocks<ACT_SIGMOID>(tm + 256, cb0, cb1, sub, 4, D, sb2, false, 0u, 0u, nullptr, vec_d,
+                                             [&](int c0, int valid, float(&v)[16]) { if (zr) store_row16(zr + c0, v, valid, vec_d); });
+            }
+        }
+    }
+    ptx::tc_fence_before();
+    __syncthreads();
+    if ((threadIdx.x >> 5) == 0) ptx::tmem_dealloc<512>(tmem0);
+}
+
+inline size_t enc_img_bytes(int D) { return (size_t)((pad16(D) + ENC_CH - 1) / ENC_CH) * ENC_STAGE_BYTES; }
+
+// img: enc_img_bytes(D) of 1024-byte aligned scratch
+inline int encoder_fused_launch(const lipvq_dims_t *d, const lipvq_params_t *p, const float *x, int64_t n, float *a1,
+                                float *h1, float *a2, float *h2, const float *Wn, float *z_e, uint8_t *img,
+                                cudaStream_t st) {
+    const int D16 = pad16(d->D);
+    enc_wn_image_kernel<<<(D16 * 32 + 255) / 256, 256, 0, st>>>(Wn, d->D, D16, img);
+    LIPVQ_LAUNCH_OK();
+    LIPVQ_TRY(set_smem(enc_fused_kernel, EncSmem::TOTAL));
+    enc_fused_kernel<<<grid_for(n), ENC_THR, EncSmem::TOTAL, st>>>(x, p->enc0_w, p->enc0_b, p->enc2_w, p->enc2_b, img,
+                                                                   p->lat_b, n, d->F, d->D, a1, h1, a2, h2, z_e);
+    LIPVQ_LAUNCH_OK();
+    return LIPVQ_OK;
+}
+
+}  // namespace mlp
+}  // namespace lipvq
