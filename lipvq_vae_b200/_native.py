@@ -80,7 +80,9 @@ def build_native(force: bool = False, verbose: bool = False) -> str:
         raise LipVQNativeError("nvcc not found; cannot build " + LIB_PATH)
     os.makedirs(LIB_DIR, exist_ok=True)
     tmp = LIB_PATH + ".tmp.%d" % os.getpid()
-    cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", tmp, os.path.join(CSRC, "lipvq_abi.cu")]
+    extra = os.environ.get("LIPVQ_NVCC_EXTRA", "").split()          # experiment knobs, e.g. -DENC_CH_=64
+    cmd = ([nvcc] + NVCC_FLAGS + extra + (["-Xptxas", "-v"] if verbose else [])
+           + ["-o", tmp, os.path.join(CSRC, "lipvq_abi.cu")])
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:
         raise LipVQNativeError("nvcc failed:\n" + r.stdout + r.stderr)

@@ -3,14 +3,15 @@
 // h1 and h2 never leave the SM.  Every GEMM is 3xTF32 on tcgen05 with the A operand in TMEM (mlp_tc.cuh).
 //
 // Shared memory cannot hold the hi/lo images of all three weights (288 KB at D=208), so W0 and W1 stay
-// resident (80 KB) and the Lipschitz-normalised Wn is streamed from L2 per tile in chunks of ENC_CH output
-// columns through a 2-stage ring of 1-D bulk copies (cp.async.bulk + mbarrier); each chunk's MMA commits
-// its own barrier so the sigmoid epilogue of chunk c overlaps the MMA of chunk c+1.
+// resident (80 KB) and the Lipschitz-normalised Wn is streamed from L2 per tile in K blocks of 32 (all D16
+// rows, 52 KB) through a 2-stage ring of 1-D bulk copies (cp.async.bulk + mbarrier).  Chunking along K keeps
+// every MMA at N = D16: measured, a tcgen05.mma with A in TMEM costs ~80 cycles however small N is, so
+// N-chunks of 48 made layer 2 four times slower than K-chunks.
 //
 // Warps 0..15 (512 threads): staging + epilogues (warp%4 = TMEM lane quarter, warp/4 = 16-column block
 // owner).  Warp 16: control -- one thread issues every tcgen05.mma and every bulk copy.
 // TMEM columns: acc2 -> h2_hi [0,128) | h2_lo [128,256) | acc3 [256,256+D16);
-//               while layers 0/1 run: x_hi 256 | x_lo 272 | acc1 288 | h1_hi 352 | h1_lo 416  (inside acc3's range)
+//               while layers 0/1 run: x_hi 256 | x_lo 320 | acc1 128 | h1_hi 352 | h1_lo 416
 #pragma once
 #include "mlp_tc.cuh"
 
@@ -19,38 +20,38 @@ namespace mlp {
 
 constexpr int ENC_EPI = 512;             // epilogue threads
 constexpr int ENC_THR = ENC_EPI + 32;    // + control warp
-constexpr int ENC_CH = 48;               // Wn output columns per streamed chunk
-constexpr int ENC_NCMAX = 8;
-constexpr int ENC_STAGE_BYTES = ENC_CH * 1024;   // hi (CH x 4 blocks x 128 B) + lo
+constexpr int ENC_NC = HH / 32;            // Wn is streamed per K block of 32 (all D16 rows): 4 chunks per tile
+constexpr int ENC_DMAX = 208;
+constexpr int ENC_NCMAX = 1;
+constexpr int ENC_STAGE_BYTES = ENC_DMAX * 256;   // one K block: hi (D16 x 128 B) + lo
 
 struct EncSmem {
     static constexpr int W0 = 0, W0_IMG = H1 * 128;
     static constexpr int W1 = W0 + 2 * W0_IMG, W1_IMG = HH * 128 * 2;
     static constexpr int RING = W1 + 2 * W1_IMG;
-    static constexpr int XS = RING + 2 * ENC_STAGE_BYTES;          // x staging: 128 rows x 64 B
-    static constexpr int BIAS = XS + TM * 64;                      // b0[64] b1[128] b[256]
+    static constexpr int WBUF = RING + 2 * ENC_STAGE_BYTES;        // 16 warps x 2 KB store-transpose buffers
+    static constexpr int BIAS = WBUF + 16 * 2048;                  // b0[64] b1[128] b[256]
     static constexpr int BAR = BIAS + (H1 + HH + 256) * 4;         // mbarriers (8 B each), then the TMEM slot
     static constexpr int NBAR = 3 + 2 + ENC_NCMAX + 4;             // a_ready[3] acc_ready[2] acc3[NC] w_full[2] w_empty[2]
     static constexpr int TOTAL = BAR + NBAR * 8 + 16 + 1024;
 };
 
-// Wn [D,128] -> per-chunk images in global memory: chunk c = rows [c*CH, c*CH+rows_c): [hi | lo], each
-// 4 K-blocks x rows_c x 128 B in the swizzled layout of stage_weight().  One thread per 16-byte piece.
+// Wn [D,128] -> per-K-block images in global memory: block kb = [hi | lo], each D16 rows x 128 B in the
+// swizzled layout of stage_weight().  One thread per 16-byte piece.
 __global__ void enc_wn_image_kernel(const float *__restrict__ Wn, int D, int D16, uint8_t *__restrict__ img) {
     const int total = D16 * 4 * 8;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
         const int j = i & 7, kb = (i >> 3) & 3, n = i >> 5;
-        const int c = n / ENC_CH, nl = n - c * ENC_CH, rows_c = min(ENC_CH, D16 - c * ENC_CH);
         uint32_t h[4], l[4];
 #pragma unroll
         for (int t = 0; t < 4; ++t) {
             const float v = n < D ? Wn[(size_t)n * HH + kb * 32 + j * 4 + t] : 0.f;
             split_tf32(v, h[t], l[t]);
         }
-        uint8_t *base = img + (size_t)c * ENC_STAGE_BYTES;
-        const int off = kb * rows_c * 128 + nl * 128 + ((j ^ (nl & 7)) << 4);
+        uint8_t *base = img + (size_t)kb * D16 * 256;
+        const int off = n * 128 + ((j ^ (n & 7)) << 4);
         *reinterpret_cast<uint4 *>(base + off) = make_uint4(h[0], h[1], h[2], h[3]);
-        *reinterpret_cast<uint4 *>(base + rows_c * 512 + off) = make_uint4(l[0], l[1], l[2], l[3]);
+        *reinterpret_cast<uint4 *>(base + D16 * 128 + off) = make_uint4(l[0], l[1], l[2], l[3]);
     }
 }
 
@@ -59,7 +60,6 @@ __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void *src, uint32_t
                  "l"(src), "r"(bytes), "r"(bar)
                  : "memory");
 }
-__device__ __forceinline__ void epi_sync() { asm volatile("bar.sync 1, 512;" ::: "memory"); }
 // epilogue thread: my part of an A operand is in TMEM -> tell the control thread
 __device__ __forceinline__ void a_ready_arrive(uint32_t bar) {
     ptx::tmem_st_wait();
@@ -67,11 +67,14 @@ __device__ __forceinline__ void a_ready_arrive(uint32_t bar) {
     ptx::mbar_arrive(bar);
 }
 
-// epilogue over the 16-column blocks cb in [cb0, cb1) with cb % nsub == sub (see mlp_tc.cuh::epilogue)
-template <int ACT, class Fn>
+// Epilogue over the 16-column blocks cb in [cb0, cb1) with cb % nsub == sub, for this thread's row:
+//   v = acc + bias -> [pre-activation rows to global] -> act -> [activation rows to global] -> [next A operand]
+// pre/post: &dst[warp_row0 * ld] or nullptr; stores go through the warp's transpose buffer (warp_store16).
+template <int ACT>
 __device__ __forceinline__ void epilogue_blocks(uint32_t t_acc, int cb0, int cb1, int sub, int nsub, int n_real,
                                                 const float *sbias, bool write_next, uint32_t t_next_hi,
-                                                uint32_t t_next_lo, float *__restrict__ a_out, bool vec, Fn fn) {
+                                                uint32_t t_next_lo, uint8_t *wbuf, float *__restrict__ pre,
+                                                float *__restrict__ post, int ld, int rows_valid, bool vec) {
     int cb = cb0 + ((sub - cb0) % nsub + nsub) % nsub;
     for (; cb < cb1; cb += nsub) {
         const int c0 = cb << 4;
@@ -82,10 +85,10 @@ __device__ __forceinline__ void epilogue_blocks(uint32_t t_acc, int cb0, int cb1
 #pragma unroll
         for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]) + sbias[c0 + i];
         const int valid = min(16, n_real - c0);
-        if (a_out) store_row16(a_out + c0, v, valid, vec);
+        if (pre) warp_store16(wbuf, pre + c0, ld, v, rows_valid, valid, vec);
 #pragma unroll
         for (int i = 0; i < 16; ++i) v[i] = apply_act<ACT>(v[i]);
-        fn(c0, valid, v);
+        if (post) warp_store16(wbuf, post + c0, ld, v, rows_valid, valid, vec);
         if (write_next) store_split16(t_next_hi + c0, t_next_lo + c0, v);
     }
 }
@@ -109,7 +112,7 @@ enc_fused_kernel(const float *__restrict__ x, const float *__restrict__ W0, cons
     auto bar_wempty = [&](int s) { return bars + 8u * (7 + ENC_NCMAX + s); };
     volatile uint32_t *tmem_slot = reinterpret_cast<volatile uint32_t *>(sm + L::BAR + L::NBAR * 8);
 
-    const int D16 = pad16(D), NC = (D16 + ENC_CH - 1) / ENC_CH;
+    const int D16 = pad16(D), NC = ENC_NC;
     stage_weight(sm + L::W0, sm + L::W0 + L::W0_IMG, W0, H1, F, H1, 1);
     stage_weight(sm + L::W1, sm + L::W1 + L::W1_IMG, W1, HH, H1, HH, 2);
     for (int i = threadIdx.x; i < H1; i += ENC_THR) sb0[i] = b0[i];
@@ -141,9 +144,9 @@ enc_fused_kernel(const float *__restrict__ x, const float *__restrict__ W0, cons
             auto load_next = [&]() {   // chunk g_load -> ring stage g_load & 1 (waits until that stage is free)
                 const int s = g_load & 1, c = g_load % NC;
                 if (g_load >= 2) ptx::mbar_wait(bar_wempty(s), ((g_load >> 1) - 1) & 1);
-                const uint32_t bytes = (uint32_t)min(ENC_CH, D16 - c * ENC_CH) * 1024u;
+                const uint32_t bytes = (uint32_t)D16 * 256u;
                 ptx::mbar_arrive_expect_tx(bar_wfull(s), bytes);
-                bulk_g2s(s0 + L::RING + s * ENC_STAGE_BYTES, wn_img + (size_t)c * ENC_STAGE_BYTES, bytes, bar_wfull(s));
+                bulk_g2s(s0 + L::RING + s * ENC_STAGE_BYTES, wn_img + (size_t)c * bytes, bytes, bar_wfull(s));
                 ++g_load;
             };
             for (int t = 0; t < my_tiles; ++t) {
@@ -151,7 +154,7 @@ enc_fused_kernel(const float *__restrict__ x, const float *__restrict__ W0, cons
                 while (g_load < total && g_load < t * NC + 2) load_next();
                 ptx::mbar_wait(bar_a(0), par);
                 ptx::tc_fence_after();
-                issue_layer(tmem0 + 288, tmem0 + 256, tmem0 + 272, s0 + L::W0, s0 + L::W0 + L::W0_IMG, H1, k0_steps,
+                issue_layer(tmem0 + 128, tmem0 + 256, tmem0 + 320, s0 + L::W0, s0 + L::W0 + L::W0_IMG, H1, k0_steps,
                             bar_acc(0));
                 ptx::mbar_wait(bar_a(1), par);
                 ptx::tc_fence_after();
@@ -159,101 +162,110 @@ enc_fused_kernel(const float *__restrict__ x, const float *__restrict__ W0, cons
                             bar_acc(1));
                 ptx::mbar_wait(bar_a(2), par);
                 ptx::tc_fence_after();
-                for (int c = 0; c < NC; ++c) {
-                    const int g = t * NC + c, s = g & 1, rows_c = min(ENC_CH, D16 - c * ENC_CH);
+                const uint32_t idesc = ptx::umma_idesc_tf32(TM, D16);
+                for (int c = 0; c < NC; ++c) {      // K block c of Wn against h2 columns [32c, 32c+32)
+                    const int g = t * NC + c, s = g & 1;
                     ptx::mbar_wait(bar_wfull(s), (g >> 1) & 1);
                     ptx::tc_fence_after();
                     const uint32_t st = s0 + L::RING + s * ENC_STAGE_BYTES;
-                    issue_layer(tmem0 + 256 + c * ENC_CH, tmem0 + 0, tmem0 + 128, st, st + rows_c * 512, rows_c,
-                                HH / 8, bar_acc3(c));
+                    const uint64_t bh = ptx::umma_desc_sw128(st), bl = ptx::umma_desc_sw128(st + D16 * 128);
+#pragma unroll
+                    for (int ks = 0; ks < 4; ++ks) {
+                        const uint32_t a_hi = tmem0 + 32 * c + 8 * ks, a_lo = a_hi + 128;
+                        ptx::umma_tf32_ts(tmem0 + 256, a_hi, bh + 2 * ks, idesc, (c | ks) ? 1u : 0u);
+                        ptx::umma_tf32_ts(tmem0 + 256, a_lo, bh + 2 * ks, idesc, 1u);
+                        ptx::umma_tf32_ts(tmem0 + 256, a_hi, bl + 2 * ks, idesc, 1u);
+                    }
                     ptx::umma_commit(bar_wempty(s));
+                    if (c == NC - 1) ptx::umma_commit(bar_acc3(0));
                     while (g_load < total && g_load <= g + 1) load_next();
                 }
             }
         }
     } else {
-        // ============================ staging + epilogue warps
-        const int warp = threadIdx.x >> 5, sub = warp >> 2, r_in = threadIdx.x & 127;
+        // ============================ input + epilogue warps
+        const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, sub = warp >> 2, r_in = threadIdx.x & 127;
         const uint32_t tm = tmem0 + ((uint32_t)((warp & 3) * 32) << 16);
-        uint8_t *xs = sm + L::XS;
+        uint8_t *wbuf = sm + L::WBUF + warp * 2048;
         const bool vec_x = (F & 3) == 0, vec_d = (D & 3) == 0;
-        // x prefetch: thread t holds float4 #(t&3) of row (t>>2) of the tile
-        const int xr = threadIdx.x >> 2, xj = threadIdx.x & 3;
+        // x: the sub-0 warp of each lane quarter loads its rows directly (16 floats per row, prefetched one tile
+        // ahead).  x_hi / x_lo live in acc3 blocks 0 and 4, both owned by sub 0, so no other warp touches them.
+        float xv[16];
         auto fetch_x = [&](int64_t tile) {
-            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-            const int64_t row = tile * TM + xr;
-            const int k0 = xj * 4;
-            if (tile < n_tiles && row < n_rows && k0 < F) {
-                const float *p = x + row * F + k0;
-                if (vec_x && k0 + 3 < F) v = __ldg(reinterpret_cast<const float4 *>(p));
-                else {
-                    v.x = __ldg(p);
-                    if (k0 + 1 < F) v.y = __ldg(p + 1);
-                    if (k0 + 2 < F) v.z = __ldg(p + 2);
-                    if (k0 + 3 < F) v.w = __ldg(p + 3);
+            const int64_t row = tile * TM + r_in;
+            const bool ok = sub == 0 && tile < n_tiles && row < n_rows;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+                const int k0 = 4 * j;
+                if (ok && k0 < F) {
+                    const float *p = x + row * F + k0;
+                    if (vec_x && k0 + 3 < F) v = __ldg(reinterpret_cast<const float4 *>(p));
+                    else {
+                        v.x = __ldg(p);
+                        if (k0 + 1 < F) v.y = __ldg(p + 1);
+                        if (k0 + 2 < F) v.z = __ldg(p + 2);
+                        if (k0 + 3 < F) v.w = __ldg(p + 3);
+                    }
                 }
+                xv[k0] = v.x; xv[k0 + 1] = v.y; xv[k0 + 2] = v.z; xv[k0 + 3] = v.w;
             }
-            return v;
         };
-        float4 xq = fetch_x(blockIdx.x);
+        fetch_x(blockIdx.x);
         int t = 0;
+#ifdef ENC_PROFILE
+        long long pc[8] = {0, 0, 0, 0, 0, 0, 0, 0}, pt = clock64();
+#define ENC_TICK(i) do { const long long _n = clock64(); pc[i] += _n - pt; pt = _n; } while (0)
+#else
+#define ENC_TICK(i) do { } while (0)
+#endif
         for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++t) {
             const uint32_t par = t & 1;
-            const int64_t row = tile * TM + r_in;
-            const bool row_ok = row < n_rows;
-            // ---- x -> A operand (hi/lo).  The barrier also orders last tile's acc3 reads before these writes.
-            *reinterpret_cast<float4 *>(xs + xr * 64 + ((xj ^ ((xr >> 1) & 3)) << 4)) = xq;
-            ptx::tc_fence_before();
-            epi_sync();
-            ptx::tc_fence_after();
-            if (sub == 0) {
-                float v[16];
-#pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    const float4 q = *reinterpret_cast<const float4 *>(xs + r_in * 64 + ((j ^ ((r_in >> 1) & 3)) << 4));
-                    v[4 * j] = q.x; v[4 * j + 1] = q.y; v[4 * j + 2] = q.z; v[4 * j + 3] = q.w;
-                }
-                store_split16(tm + 256, tm + 272, v);
-            }
+            const int64_t wrow0 = tile * TM + (r_in - lane);               // first row of this warp
+            const int rows_valid = (int)max((int64_t)0, min((int64_t)32, n_rows - wrow0));
+            // ---- x -> A operand (hi/lo)
+            if (sub == 0) store_split16(tm + 256, tm + 320, xv);
             a_ready_arrive(bar_a(0));
-            xq = fetch_x(tile + gridDim.x);          // next tile's x flies during this tile
+            fetch_x(tile + gridDim.x);               // next tile's x flies during this tile
+            ENC_TICK(0);
             // ---- layer 0 epilogue: h1
             ptx::mbar_wait(bar_acc(0), par);
             ptx::tc_fence_after();
-            {
-                float *h1r = (h1 && row_ok) ? h1 + row * H1 : nullptr;
-                epilogue_blocks<ACT_GELU>(tm + 288, 0, H1 / 16, sub, 4, H1, sb0, true, tm + 352, tm + 416,
-                                          (a1 && row_ok) ? a1 + row * H1 : nullptr, true,
-                                          [&](int c0, int valid, float(&v)[16]) { if (h1r) store_row16(h1r + c0, v, valid, true); });
-            }
+            ENC_TICK(1);
+            epilogue_blocks<ACT_GELU>(tm + 128, 0, H1 / 16, sub, 4, H1, sb0, true, tm + 352, tm + 416, wbuf,
+                                      a1 ? a1 + wrow0 * H1 : nullptr, h1 ? h1 + wrow0 * H1 : nullptr, H1, rows_valid,
+                                      true);
             a_ready_arrive(bar_a(1));
+            ENC_TICK(2);
             // ---- layer 1 epilogue: h2 (hi written in place over the accumulator columns just read)
             ptx::mbar_wait(bar_acc(1), par);
             ptx::tc_fence_after();
-            {
-                float *h2r = (h2 && row_ok) ? h2 + row * HH : nullptr;
-                epilogue_blocks<ACT_GELU>(tm + 0, 0, HH / 16, sub, 4, HH, sb1, true, tm + 0, tm + 128,
-                                          (a2 && row_ok) ? a2 + row * HH : nullptr, true,
-                                          [&](int c0, int valid, float(&v)[16]) { if (h2r) store_row16(h2r + c0, v, valid, true); });
-            }
+            ENC_TICK(3);
+            epilogue_blocks<ACT_GELU>(tm + 0, 0, HH / 16, sub, 4, HH, sb1, true, tm + 0, tm + 128, wbuf,
+                                      a2 ? a2 + wrow0 * HH : nullptr, h2 ? h2 + wrow0 * HH : nullptr, HH, rows_valid,
+                                      true);
             a_ready_arrive(bar_a(2));
-            // ---- layer 2: per streamed chunk, sigmoid and store z_e
-            float *zr = row_ok ? z_e + row * D : nullptr;
-            for (int c = 0; c < NC; ++c) {
-                ptx::mbar_wait(bar_acc3(c), par);
-                ptx::tc_fence_after();
-                const int cb0 = c * (ENC_CH / 16), cb1 = min(cb0 + ENC_CH / 16, D16 / 16);
-                epilogue_blocks<ACT_SIGMOID>(tm + 256, cb0, cb1, sub, 4, D, sb2, false, 0u, 0u, nullptr, vec_d,
-                                             [&](int c0, int valid, float(&v)[16]) { if (zr) store_row16(zr + c0, v, valid, vec_d); });
-            }
+            ENC_TICK(4);
+            // ---- layer 2 epilogue: sigmoid and store z_e
+            ptx::mbar_wait(bar_acc3(0), par);
+            ptx::tc_fence_after();
+            ENC_TICK(5);
+            epilogue_blocks<ACT_SIGMOID>(tm + 256, 0, D16 / 16, sub, 4, D, sb2, false, 0u, 0u, wbuf, nullptr,
+                                         z_e + wrow0 * D, D, rows_valid, vec_d);
+            ENC_TICK(6);
         }
+#ifdef ENC_PROFILE
+        if (blockIdx.x == 3 && (threadIdx.x & 31) == 0 && (threadIdx.x >> 5) < 8)
+            printf("w%d tiles %d cyc/tile: xstage %lld | wait0 %lld epi0 %lld | wait1 %lld epi1 %lld | wait2 %lld epi2 %lld\n",
+                   threadIdx.x >> 5, t, pc[0] / t, pc[1] / t, pc[2] / t, pc[3] / t, pc[4] / t, pc[5] / t, pc[6] / t);
+#endif
     }
     ptx::tc_fence_before();
     __syncthreads();
     if ((threadIdx.x >> 5) == 0) ptx::tmem_dealloc<512>(tmem0);
 }
 
-inline size_t enc_img_bytes(int D) { return (size_t)((pad16(D) + ENC_CH - 1) / ENC_CH) * ENC_STAGE_BYTES; }
+inline size_t enc_img_bytes(int D) { return (size_t)ENC_NC * pad16(D) * 256; }
 
 // img: enc_img_bytes(D) of 1024-byte aligned scratch
 inline int encoder_fused_launch(const lipvq_dims_t *d, const lipvq_params_t *p, const float *x, int64_t n, float *a1,

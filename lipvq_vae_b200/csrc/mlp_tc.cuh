@@ -105,6 +105,33 @@ __device__ __forceinline__ void store_row16(float *__restrict__ dst, const float
     }
 }
 
+// All 32 lanes of a warp: lane l holds v[16] = columns [c0, c0+16) of row (warp_row0 + l).  The block is
+// transposed through a warp-private 2 KB shared buffer so each store instruction covers 8 rows x 64
+// contiguous bytes (8 memory wavefronts instead of 32 with one row per lane).
+// base = &dst[warp_row0 * ld + c0]; rows >= rows_valid are not written.
+__device__ __forceinline__ void warp_store16(uint8_t *wbuf, float *__restrict__ base, int ld, const float (&v)[16],
+                                             int rows_valid, int valid_cols, bool vec) {
+    const int lane = threadIdx.x & 31;
+    if (vec && valid_cols == 16) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+            *reinterpret_cast<float4 *>(wbuf + lane * 64 + ((j ^ ((lane >> 1) & 3)) << 4)) =
+                make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+        __syncwarp();
+#pragma unroll
+        for (int it = 0; it < 4; ++it) {
+            const int f = it * 32 + lane, row = f >> 2, j = f & 3;
+            const float4 q = *reinterpret_cast<const float4 *>(wbuf + row * 64 + ((j ^ ((row >> 1) & 3)) << 4));
+            if (row < rows_valid) *reinterpret_cast<float4 *>(base + (size_t)row * ld + j * 4) = q;
+        }
+        __syncwarp();
+    } else if (lane < rows_valid) {
+#pragma unroll
+        for (int i = 0; i < 16; ++i)
+            if (i < valid_cols) base[(size_t)lane * ld + i] = v[i];
+    }
+}
+
 // Epilogue of one layer for this thread's row (TMEM lane): for each 16-column block owned by this warp
 //   v = acc + bias -> [pre-activation to global] -> act -> fn(c0, v) -> [next A operand hi/lo in TMEM]
 // `half` (warp / 4) selects the 16-column blocks cb with cb % 2 == half.
