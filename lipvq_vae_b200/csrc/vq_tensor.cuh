@@ -15,6 +15,7 @@
 #pragma once
 #include <cuda.h>
 #include <cuda_bf16.h>
+#include <cuda_fp16.h>
 #include <stdlib.h>
 
 #include "common.cuh"
@@ -34,6 +35,30 @@ constexpr int NT = 384;          // warp0 TMA, warp1 MMA, warp2 TMEM alloc, warp
 constexpr int NCAND = 4;         // chunk minima kept per (row, column half, code tile)
 constexpr int LCAP = 16;         // candidate entries kept per (row, column half)
 constexpr float BIG = 3.0e38f;
+
+// GEMM operand type.  fp16 (default): 11-bit significand -> the rounding window tau is 8x narrower than with
+// bf16 at the same tensor-core rate, so far fewer codes need the fp32 rescore.  Its narrow exponent range is
+// guarded twice: an absolute (subnormal) term in tau, and a range flag (counters[3]) that sends every row to
+// the exact scan when a value would overflow.  -DLIPVQ_VQ_BF16 restores bf16 operands (A/B measurements).
+#ifdef LIPVQ_VQ_BF16
+using op_t = __nv_bfloat16;
+using op2_t = __nv_bfloat162;
+constexpr float OP_U4 = 0.015625f;          // 4u, u = 2^-8
+constexpr float OP_ABS = 0.f;               // no subnormal term (fp32 exponent range)
+constexpr float OP_MAX = 3.0e38f;
+__device__ __forceinline__ op_t f2op(float v) { return __float2bfloat16_rn(v); }
+__device__ __forceinline__ float op2f(op_t v) { return __bfloat162float(v); }
+__device__ __forceinline__ op2_t f2op2(float a, float b) { return __floats2bfloat162_rn(a, b); }
+#else
+using op_t = __half;
+using op2_t = __half2;
+constexpr float OP_U4 = 0.001953125f;       // 4u, u = 2^-11
+constexpr float OP_ABS = 5.9604645e-8f * 1.01f;   // 2^-24: twice the largest subnormal rounding error
+constexpr float OP_MAX = 60000.f;
+__device__ __forceinline__ op_t f2op(float v) { return __float2half_rn(v); }
+__device__ __forceinline__ float op2f(op_t v) { return __half2float(v); }
+__device__ __forceinline__ op2_t f2op2(float a, float b) { return __floats2half2_rn(a, b); }
+#endif
 constexpr float PAD_SCORE = 1.0e30f;   // en of the padding codes (never inside any window)
 
 struct Geometry {
@@ -74,35 +99,39 @@ __global__ void __launch_bounds__(1024) vq_prep_mean_kernel(const float *__restr
     }
 }
 
-__device__ __forceinline__ void split3_bf16(float v, __nv_bfloat16 &a, __nv_bfloat16 &b, __nv_bfloat16 &c) {
-    a = __float2bfloat16_rn(v);
-    const float r1 = v - __bfloat162float(a);
-    b = __float2bfloat16_rn(r1);
-    const float r2 = r1 - __bfloat162float(b);
-    c = __float2bfloat16_rn(r2);
+__device__ __forceinline__ void split3_op(float v, op_t &a, op_t &b, op_t &c) {
+    a = f2op(v);
+    const float r1 = v - op2f(a);
+    b = f2op(r1);
+    const float r2 = r1 - op2f(b);
+    c = f2op(r2);
 }
 
 // one warp per (padded) code row; writes Eb row and enorm[k] = ||e'_k||
 __global__ void vq_prep_rows_kernel(const float *__restrict__ E, const float *__restrict__ mu, int K, int Kp,
-                                    int D, int DKp, __nv_bfloat16 *__restrict__ Eb, float *__restrict__ enorm) {
+                                    int D, int DKp, op_t *__restrict__ Eb, float *__restrict__ enorm,
+                                    int *__restrict__ counters) {
     const int k = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     const int lane = threadIdx.x & 31;
     if (k >= Kp) return;
-    __nv_bfloat16 *row = Eb + (size_t)k * DKp;
-    float s = 0.f;
+    op_t *row = Eb + (size_t)k * DKp;
+    float s = 0.f, amax = 0.f;
     for (int d = lane; d < DKp; d += 32) {
         float v = 0.f;
         if (k < K && d < D) {
             v = E[(size_t)k * D + d] - mu[d];
             s = fmaf(v, v, s);
+            amax = fmaxf(amax, fabsf(v));
         }
-        row[d] = __float2bfloat16_rn(-2.0f * v);
+        row[d] = f2op(-2.0f * v);
     }
     s = warp_sum(s);
+    for (int o = 16; o > 0; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
     if (lane == 0) {
-        const float en = (k < K) ? s : PAD_SCORE;
-        __nv_bfloat16 a, b, c;
-        split3_bf16(en, a, b, c);
+        if (k < K && !(2.f * amax <= OP_MAX && s <= 0.25f * OP_MAX)) atomicOr(counters + 3, 1);   // out of range
+        const float en = (k < K) ? s : fminf(PAD_SCORE, OP_MAX);
+        op_t a, b, c;
+        split3_op(en, a, b, c);
         row[D] = a; row[D + 1] = b; row[D + 2] = c;
         if (k < K) enorm[k] = sqrtf(s);
     }
@@ -127,11 +156,12 @@ __global__ void vq_prep_emax_kernel(const float *__restrict__ enorm, int K, floa
 // one warp per (padded) row: Zb row = [bf16(z - mu) | 1 1 1 | 0...]; zn = ||z - mu||
 __global__ void __launch_bounds__(256) vq_convert_z_kernel(const float *__restrict__ z, const float *__restrict__ mu,
                                                            int64_t n, int64_t Np, int D, int DKp,
-                                                           __nv_bfloat16 *__restrict__ Zb, float *__restrict__ zn) {
+                                                           op_t *__restrict__ Zb, float *__restrict__ zn,
+                                                           int *__restrict__ counters) {
     const int lane = threadIdx.x & 31;
     for (int64_t r = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5); r < Np; r += (int64_t)gridDim.x * 8) {
-        __nv_bfloat16 *row = Zb + r * DKp;
-        float s = 0.f;
+        op_t *row = Zb + r * DKp;
+        float s = 0.f, amax = 0.f;
         // two bf16 per lane per step -> 4-byte stores, 128 B per warp
         for (int d = lane * 2; d < DKp; d += 64) {
             float v0 = 0.f, v1 = 0.f;
@@ -142,10 +172,12 @@ __global__ void __launch_bounds__(256) vq_convert_z_kernel(const float *__restri
                 else if (d + 1 < D + 3) v1 = 1.0f;
                 if (d < D) s = fmaf(v0, v0, s);
                 if (d + 1 < D) s = fmaf(v1, v1, s);
+                amax = fmaxf(amax, fmaxf(fabsf(v0), fabsf(v1)));
             }
-            *reinterpret_cast<__nv_bfloat162 *>(row + d) = __floats2bfloat162_rn(v0, v1);
+            *reinterpret_cast<op2_t *>(row + d) = f2op2(v0, v1);
         }
         s = warp_sum(s);
+        if (!(amax <= OP_MAX)) atomicOr(counters + 3, 1);   // operand out of range -> whole launch goes exact
         if (lane == 0 && r < n) zn[r] = sqrtf(s);
     }
 }
@@ -163,9 +195,15 @@ struct SmemLayout {
     static constexpr int TOTAL = BAR_OFF + NBARS * 8 + 16 + 1024;   // + tmem ptr + alignment slack
 };
 
-constexpr float RESC_C1 = 0.015625f * 1.004f;   // 2*(2u+u^2), u = 2^-8
+constexpr float RESC_C1 = OP_U4 * 1.004f;       // 2*(2u+u^2), u = unit roundoff of the operand type
 constexpr float RESC_C2 = 4.0e-5f;
 constexpr int RESC_MAXD = 320;
+// window half-width*2 for a row with ||z'|| = znr: relative rounding (C1), fp32 accumulation / split / payload
+// bits (C2) and the absolute error of fp16 subnormals: sum_i 2^-25 (2|e_i| + |z_i|) <= 2^-25 sqrt(D) (2 emax + znr)
+__device__ __forceinline__ float tau_of(float znr, float emax, float abs_c) {
+    return 2.f * (RESC_C1 * znr * emax + RESC_C2 * (2.f * znr * emax + emax * emax)) + abs_c * (2.f * emax + znr) +
+           1e-30f;
+}
 
 // sorted insert of x into m0<=m1<=m2<=m3 (payload rides in the low mantissa bits): 7 FMNMX
 __device__ __forceinline__ void insert4(float (&m)[NCAND], float x) {
@@ -188,7 +226,8 @@ __global__ void __launch_bounds__(NT, 1) vq_tc_kernel(const __grid_constant__ CU
                                                        const __grid_constant__ CUtensorMap tmapB,
                                                        int64_t n_rows, int n_tiles, int nct, int nk16,
                                                        const float *__restrict__ zn, const float *__restrict__ emax_p,
-                                                       uint2 *__restrict__ cand, float4 *__restrict__ cand_meta) {
+                                                       float abs_c, uint2 *__restrict__ cand,
+                                                       float4 *__restrict__ cand_meta) {
     using L = SmemLayout<NKB, A_BUFS, STAGES>;
     extern __shared__ uint8_t smem_raw[];
     const uint32_t raw = ptx::smem_u32(smem_raw);
@@ -249,7 +288,11 @@ __global__ void __launch_bounds__(NT, 1) vq_tc_kernel(const __grid_constant__ CU
     } else if (warp == 1) {
         // ===== MMA issuer (one thread) =====
         if (lane == 0) {
+            #ifdef LIPVQ_VQ_BF16
             constexpr uint32_t idesc = ptx::umma_idesc_bf16(BM, BN);
+#else
+            constexpr uint32_t idesc = ptx::umma_idesc_f16(BM, BN);
+#endif
             int st = 0, sph = 0, ab = 0, aph = 0, acc = 0, accph = 0;
             for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
                 ptx::mbar_wait(a_full(ab), aph);
@@ -289,7 +332,7 @@ __global__ void __launch_bounds__(NT, 1) vq_tc_kernel(const __grid_constant__ CU
             const int64_t row = (int64_t)tile * BM + quarter * 32 + lane;
             const bool row_ok = row < n_rows;
             const float znr = row_ok ? __ldg(zn + row) : 0.f;
-            const float tau = 2.f * (RESC_C1 * znr * emax + RESC_C2 * (2.f * znr * emax + emax * emax)) + 1e-30f;
+            const float tau = tau_of(znr, emax, abs_c);
             uint2 *out = cand + (row * 2 + half) * LCAP;
             float gb = BIG, T = BIG, m4min = BIG, smin = BIG;
             int cnt = 0;
@@ -380,11 +423,12 @@ __global__ void __launch_bounds__(256) vq_rescore_kernel(
     const float *__restrict__ z, const float *__restrict__ E, int64_t n_rows, int D, int K,
     const uint2 *__restrict__ cand, const float4 *__restrict__ cand_meta, const float *__restrict__ zn,
     const float *__restrict__ emax_p, int64_t *__restrict__ idx_out, float *__restrict__ d2_out,
-    int *__restrict__ list, int *__restrict__ counters) {
+    int *__restrict__ list, int *__restrict__ counters, float abs_c) {
     constexpr int NG = CHUNK;          // codes evaluated side by side
     constexpr int LPG = 32 / NG;       // lanes per code
     const int lane = threadIdx.x & 31, g = lane / LPG, l = lane % LPG;
     const float emax = __ldg(emax_p);
+    const bool range_bad = counters[3] != 0;   // set by the operand passes, which finished before this launch
     int n_resc = 0, n_fast = 0;
     for (int64_t row = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5); row < n_rows; row += (int64_t)gridDim.x * 8) {
         const float4 m0 = __ldg(cand_meta + row * 2), m1 = __ldg(cand_meta + row * 2 + 1);
@@ -401,8 +445,8 @@ __global__ void __launch_bounds__(256) vq_rescore_kernel(
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) gb = fminf(gb, __shfl_xor_sync(0xffffffffu, gb, o));
         const float znr = __ldg(zn + row);
-        const float T = gb + 2.f * (RESC_C1 * znr * emax + RESC_C2 * (2.f * znr * emax + emax * emax)) + 1e-30f;
-        if (cnt0 > LCAP || cnt1 > LCAP || m0.y <= T || m1.y <= T) {
+        const float T = gb + tau_of(znr, emax, abs_c);
+        if (range_bad || cnt0 > LCAP || cnt1 > LCAP || m0.y <= T || m1.y <= T) {
             // the candidate record may be incomplete -> exact fp32 scan of the whole codebook
             if (lane == 0) list[atomicAdd(counters + 0, 1)] = (int)row;
             continue;
@@ -519,7 +563,12 @@ inline int make_tmap(CUtensorMap *m, const void *ptr, uint64_t rows, uint64_t co
     cuuint64_t strides[1] = {cols * 2};
     cuuint32_t box[2] = {(cuuint32_t)KBLK, box_rows};
     cuuint32_t estr[2] = {1, 1};
-    CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void *>(ptr), dims, strides, box, estr,
+#ifdef LIPVQ_VQ_BF16
+    const CUtensorMapDataType dt = CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+#else
+    const CUtensorMapDataType dt = CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
+#endif
+    CUresult r = fn(m, dt, 2, const_cast<void *>(ptr), dims, strides, box, estr,
                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     return r == CUDA_SUCCESS ? LIPVQ_OK : LIPVQ_ECUDA;
@@ -530,7 +579,7 @@ struct Workspace {
     uint2 *cand;
     float4 *cand_meta;
     int *list, *counters;
-    __nv_bfloat16 *Eb, *Zb;
+    op_t *Eb, *Zb;
     size_t bytes;
 };
 inline Workspace carve(void *ws, const Geometry &g) {
@@ -541,8 +590,8 @@ inline Workspace carve(void *ws, const Geometry &g) {
     w.enorm = (float *)take(sizeof(float) * g.K);
     w.emax = (float *)take(sizeof(float) * 4);
     w.counters = (int *)take(sizeof(int) * 4);
-    w.Eb = (__nv_bfloat16 *)take((size_t)g.Kp * g.DKp * 2);
-    w.Zb = (__nv_bfloat16 *)take((size_t)g.Np * g.DKp * 2);
+    w.Eb = (op_t *)take((size_t)g.Kp * g.DKp * 2);
+    w.Zb = (op_t *)take((size_t)g.Np * g.DKp * 2);
     w.zn = (float *)take(sizeof(float) * g.Np);
     w.cand = (uint2 *)take(sizeof(uint2) * g.Np * 2 * LCAP);
     w.cand_meta = (float4 *)take(sizeof(float4) * g.Np * 2);
@@ -562,7 +611,8 @@ inline int launch_tc(const CUtensorMap &ta, const CUtensorMap &tb, const Geometr
         attr_done = true;
     }
     const int grid = (int)(g.n_tiles < kNumSMs ? g.n_tiles : kNumSMs);
-    kern<<<grid, NT, L::TOTAL, st>>>(ta, tb, g.n, (int)g.n_tiles, g.nct, g.NK16, w.zn, w.emax, w.cand, w.cand_meta);
+    kern<<<grid, NT, L::TOTAL, st>>>(ta, tb, g.n, (int)g.n_tiles, g.nct, g.NK16, w.zn, w.emax,
+                                     OP_ABS * sqrtf((float)g.D), w.cand, w.cand_meta);
     LIPVQ_LAUNCH_OK();
     return LIPVQ_OK;
 }
@@ -585,14 +635,14 @@ inline int vq_tensor_launch(const float *z, const float *E, int64_t n, int D, in
     LIPVQ_CUDA_OK(cudaMemsetAsync(w.counters, 0, 4 * sizeof(int), st));
     vq_prep_mean_kernel<<<(D + 31) / 32, 1024, 0, st>>>(E, K, D, w.mu);
     LIPVQ_LAUNCH_OK();
-    vq_prep_rows_kernel<<<(g.Kp + 7) / 8, 256, 0, st>>>(E, w.mu, K, g.Kp, D, g.DKp, w.Eb, w.enorm);
+    vq_prep_rows_kernel<<<(g.Kp + 7) / 8, 256, 0, st>>>(E, w.mu, K, g.Kp, D, g.DKp, w.Eb, w.enorm, w.counters);
     LIPVQ_LAUNCH_OK();
     vq_prep_emax_kernel<<<1, 256, 0, st>>>(w.enorm, K, w.emax);
     LIPVQ_LAUNCH_OK();
     {
         int64_t blocks = (g.Np + 7) / 8;
         if (blocks > 16 * kNumSMs) blocks = 16 * kNumSMs;
-        vq_convert_z_kernel<<<(unsigned)blocks, 256, 0, st>>>(z, w.mu, n, g.Np, D, g.DKp, w.Zb, w.zn);
+        vq_convert_z_kernel<<<(unsigned)blocks, 256, 0, st>>>(z, w.mu, n, g.Np, D, g.DKp, w.Zb, w.zn, w.counters);
         LIPVQ_LAUNCH_OK();
     }
     CUtensorMap ta, tb;
@@ -624,7 +674,7 @@ inline int vq_tensor_launch(const float *z, const float *E, int64_t n, int D, in
         const bool vec = (D & 3) == 0;
 #define LIPVQ_RESC(CH, EL, VE)                                                                                   \
     vq_rescore_kernel<CH, EL, VE><<<(unsigned)blocks, 256, 0, st>>>(z, E, n, D, K, w.cand, w.cand_meta, w.zn, w.emax, \
-                                                                    idx, d2, w.list, w.counters)
+                                                                    idx, d2, w.list, w.counters, OP_ABS * sqrtf((float)D))
         if (elem)    { if (vec) LIPVQ_RESC(4, true, true);   else LIPVQ_RESC(4, true, false); }
         else if (c8) { if (vec) LIPVQ_RESC(8, false, true);  else LIPVQ_RESC(8, false, false); }
         else         { if (vec) LIPVQ_RESC(4, false, true);  else LIPVQ_RESC(4, false, false); }
