@@ -31,7 +31,8 @@ constexpr int KBLK = 64;         // bf16 elements per 128-byte swizzle row
 constexpr int UK = 16;           // UMMA K for 16-bit inputs
 constexpr int A_KB_BYTES = BM * 128;
 constexpr int B_ST_BYTES = BN * 128;
-constexpr int NT = 384;          // warp0 TMA, warp1 MMA, warp2 TMEM alloc, warps 4..11 epilogue
+constexpr int NT = 640;          // warp0 TMA, warp1 MMA, warp2 TMEM alloc, warps 4..19 epilogue
+constexpr int NPART = 4;         // column parts of an accumulator (64 columns each), one epilogue warp per (quarter, part)
 constexpr int NCAND = 4;         // chunk minima kept per (row, column half, code tile)
 constexpr int LCAP = 16;         // candidate entries kept per (row, column half)
 constexpr float BIG = 3.0e38f;
@@ -205,29 +206,34 @@ __device__ __forceinline__ float tau_of(float znr, float emax, float abs_c) {
            1e-30f;
 }
 
-// sorted insert of x into m0<=m1<=m2<=m3 (payload rides in the low mantissa bits): 7 FMNMX
-__device__ __forceinline__ void insert4(float (&m)[NCAND], float x) {
-    float t;
-    t = fminf(m[0], x); x = fmaxf(m[0], x); m[0] = t;
-    t = fminf(m[1], x); x = fmaxf(m[1], x); m[1] = t;
-    t = fminf(m[2], x); x = fmaxf(m[2], x); m[2] = t;
-    m[3] = fminf(m[3], x);
+// Candidate record written by the epilogue for each (row, column part), laid out so that both the epilogue
+// (thread = row) and the resolve pass (thread = row) touch it coalesced:
+//   entry e of (tile, part, row r)  at cand[((tile*NPART + part)*LCAP + e)*BM + r] = {chunk-min bits, code0 | mask<<24}
+//   meta of (tile, part, row r)     at cand_meta[(tile*NPART + part)*BM + r]       = entry count (LCAP+1 = overflow)
+// One entry per 8-code CHUNK whose minimum was within tau(row) of the running row minimum when it was read
+// (a superset of the final window: the running minimum only decreases); code0 = first code of the chunk and
+// mask = which of its 8 elements were inside that window.  The common path costs the chunk minima only.
+__device__ __noinline__ void cand_compact(uint2 *out, int &cnt, float T) {
+    int k = 0;                  // full: drop entries that fell out of the (shrinking) window
+    for (int e = 0; e < LCAP; ++e) {
+        const uint2 x = out[e * BM];
+        if (__uint_as_float(x.x) <= T) out[(k++) * BM] = x;
+    }
+    cnt = k < LCAP ? k : LCAP + 1;
 }
-// Candidate record written by the epilogue for each (row, column half):
-//   entries[LCAP] = {packed score bits, code}: every chunk minimum that was within tau(row) of the running
-//                   row minimum when its code tile was finished (a superset of the final window);
-//   meta = {count, m4min, smin}: m4min = smallest 4th-best chunk minimum of any code tile (if it is inside
-//          the final window a 5th chunk may have been dropped -> exact scan); smin = smallest SECOND-best
-//          element of any chunk (ELEM only: if it is outside the window every window element is listed).
-// ELEM (CHUNK==4): the packed payload is the column inside the tile half (7 bits) -> entries name single codes.
-// otherwise the payload is the chunk id and an entry names CHUNK consecutive codes.
-template <int NKB, int A_BUFS, int STAGES, int CHUNK, bool ELEM>
+__device__ __forceinline__ float min8(const uint32_t *r) {
+    const float a = ptx::fmin3(__uint_as_float(r[0]), __uint_as_float(r[1]), __uint_as_float(r[2]));
+    const float b = ptx::fmin3(__uint_as_float(r[3]), __uint_as_float(r[4]), __uint_as_float(r[5]));
+    return ptx::fmin3(a, b, fminf(__uint_as_float(r[6]), __uint_as_float(r[7])));
+}
+
+template <int NKB, int A_BUFS, int STAGES>
 __global__ void __launch_bounds__(NT, 1) vq_tc_kernel(const __grid_constant__ CUtensorMap tmapA,
                                                        const __grid_constant__ CUtensorMap tmapB,
                                                        int64_t n_rows, int n_tiles, int nct, int nk16,
                                                        const float *__restrict__ zn, const float *__restrict__ emax_p,
                                                        float abs_c, uint2 *__restrict__ cand,
-                                                       float4 *__restrict__ cand_meta) {
+                                                       int *__restrict__ cand_meta) {
     using L = SmemLayout<NKB, A_BUFS, STAGES>;
     extern __shared__ uint8_t smem_raw[];
     const uint32_t raw = ptx::smem_u32(smem_raw);
@@ -250,7 +256,7 @@ __global__ void __launch_bounds__(NT, 1) vq_tc_kernel(const __grid_constant__ CU
         ptx::tma_prefetch_desc(&tmapB);
         for (int i = 0; i < A_BUFS; ++i) { ptx::mbar_init(a_full(i), 1); ptx::mbar_init(a_empty(i), 1); }
         for (int i = 0; i < STAGES; ++i) { ptx::mbar_init(b_full(i), 1); ptx::mbar_init(b_empty(i), 1); }
-        for (int i = 0; i < 2; ++i) { ptx::mbar_init(t_full(i), 1); ptx::mbar_init(t_empty(i), 8); }
+        for (int i = 0; i < 2; ++i) { ptx::mbar_init(t_full(i), 1); ptx::mbar_init(t_empty(i), 4 * NPART); }
         ptx::fence_barrier_init();
     }
     if (warp == 2) ptx::tmem_alloc<512>(ptx::smem_u32((const void *)tmem_ptr));
@@ -320,90 +326,60 @@ __global__ void __launch_bounds__(NT, 1) vq_tc_kernel(const __grid_constant__ CU
             }
         }
     } else if (warp >= 4) {
-        // ===== epilogue: 8 warps; warp%4 = TMEM lane quarter, (warp-4)/4 = column half =====
-        static_assert(!ELEM || CHUNK == 4, "element payload needs 4-wide chunks");
-        const int quarter = warp & 3, half = (warp - 4) >> 2;
+        // ===== epilogue: 16 warps; warp%4 = TMEM lane quarter, (warp-4)/4 = 64-column part =====
+        // (TMEM reads run at 64 B/clk/SM: 2048 cycles per 128x256 accumulator, the floor of this kernel for
+        //  D < 256; enough warps are needed so that one warp's tcgen05.ld overlaps another's min network)
+        const int quarter = warp & 3, part = (warp - 4) >> 2;
         const uint32_t lane_addr = ((uint32_t)(quarter * 32) << 16);
+        constexpr int PW = BN / NPART;            // columns per part
         int acc = 0, accph = 0;
-        constexpr int CPB = 32 / CHUNK;               // chunks per 32-column batch
-        constexpr uint32_t PMASK = ELEM ? 127u : 31u; // payload bits in the low mantissa
         const float emax = __ldg(emax_p);
         for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-            const int64_t row = (int64_t)tile * BM + quarter * 32 + lane;
+            const int r_in = quarter * 32 + lane;
+            const int64_t row = (int64_t)tile * BM + r_in;
             const bool row_ok = row < n_rows;
             const float znr = row_ok ? __ldg(zn + row) : 0.f;
             const float tau = tau_of(znr, emax, abs_c);
-            uint2 *out = cand + (row * 2 + half) * LCAP;
-            float gb = BIG, T = BIG, m4min = BIG, smin = BIG;
+            uint2 *out = cand + ((size_t)tile * NPART + part) * LCAP * BM + r_in;
+            float gb = BIG;
             int cnt = 0;
             for (int c = 0; c < nct; ++c) {
                 ptx::mbar_wait(t_full(acc), accph);
                 ptx::tc_fence_after();
-                float m[NCAND] = {BIG, BIG, BIG, BIG};
-                const uint32_t col0 = tmem_base + acc * BN + half * (BN / 2);
+                const uint32_t col0 = tmem_base + acc * BN + part * PW;
+                const int code0 = c * BN + part * PW;
 #pragma unroll
-                for (int b = 0; b < 4; ++b) {
+                for (int b = 0; b < PW / 32; ++b) {
                     uint32_t r[32];
                     ptx::tmem_ld_32x32b_x32(lane_addr + col0 + b * 32, r);
                     ptx::tmem_ld_wait();
-                    if (b == 3) {   // accumulator fully in registers: hand the TMEM stage back
+                    if (b == PW / 32 - 1) {   // accumulator part fully in registers: hand the TMEM stage back
                         ptx::tc_fence_before();
                         __syncwarp();
                         if (lane == 0) ptx::mbar_arrive(t_empty(acc));
                     }
+                    float cm[4];
 #pragma unroll
-                    for (int j = 0; j < CPB; ++j) {
-                        float v;
-                        if (ELEM) {
-                            // payload = column inside the tile half (b*32 + 4j + pos), constant per unrolled slot
-                            const float e0 = __uint_as_float((r[4 * j + 0] & ~PMASK) | (uint32_t)(b * 32 + 4 * j + 0));
-                            const float e1 = __uint_as_float((r[4 * j + 1] & ~PMASK) | (uint32_t)(b * 32 + 4 * j + 1));
-                            const float e2 = __uint_as_float((r[4 * j + 2] & ~PMASK) | (uint32_t)(b * 32 + 4 * j + 2));
-                            const float e3 = __uint_as_float((r[4 * j + 3] & ~PMASK) | (uint32_t)(b * 32 + 4 * j + 3));
-                            const float lo1 = fminf(e0, e1), hi1 = fmaxf(e0, e1);
-                            const float lo2 = fminf(e2, e3), hi2 = fmaxf(e2, e3);
-                            v = fminf(lo1, lo2);
-                            smin = ptx::fmin3(smin, fmaxf(lo1, lo2), fminf(hi1, hi2));   // chunk's 2nd smallest
-                        } else if (CHUNK == 4) {
-                            v = ptx::fmin3(__uint_as_float(r[4 * j]), __uint_as_float(r[4 * j + 1]),
-                                           fminf(__uint_as_float(r[4 * j + 2]), __uint_as_float(r[4 * j + 3])));
-                            v = __uint_as_float((__float_as_uint(v) & ~PMASK) | (uint32_t)(b * CPB + j));
-                        } else {
-                            const float v0 = ptx::fmin3(__uint_as_float(r[8 * j]), __uint_as_float(r[8 * j + 1]),
-                                                        __uint_as_float(r[8 * j + 2]));
-                            const float v1 = ptx::fmin3(__uint_as_float(r[8 * j + 3]), __uint_as_float(r[8 * j + 4]),
-                                                        __uint_as_float(r[8 * j + 5]));
-                            v = ptx::fmin3(v0, v1, fminf(__uint_as_float(r[8 * j + 6]), __uint_as_float(r[8 * j + 7])));
-                            v = __uint_as_float((__float_as_uint(v) & ~PMASK) | (uint32_t)(b * CPB + j));
+                    for (int j = 0; j < 4; ++j) cm[j] = min8(r + 8 * j);
+                    gb = fminf(gb, ptx::fmin3(cm[0], cm[1], fminf(cm[2], cm[3])));
+                    const float T = gb + tau;
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        if (cm[j] <= T && row_ok) {
+                            uint32_t m = 0;
+#pragma unroll
+                            for (int e = 0; e < 8; ++e)
+                                if (__uint_as_float(r[8 * j + e]) <= T) m |= 1u << e;
+                            if (cnt >= LCAP) cand_compact(out, cnt, T);
+                            if (cnt < LCAP)
+                                out[(cnt++) * BM] =
+                                    make_uint2(__float_as_uint(cm[j]), (uint32_t)(code0 + b * 32 + 8 * j) | (m << 24));
                         }
-                        insert4(m, v);
                     }
                 }
                 if (++acc == 2) { acc = 0; accph ^= 1; }
-                // keep the chunk minima of this code tile that are inside the window of the running row minimum
-                m4min = fminf(m4min, m[NCAND - 1]);
-                gb = fminf(gb, m[0]);
-                T = gb + tau;
-                const int code0 = c * BN + half * (BN / 2);
-#pragma unroll
-                for (int i = 0; i < NCAND; ++i) {
-                    if (row_ok && m[i] <= T) {
-                        const uint32_t bits = __float_as_uint(m[i]);
-                        if (cnt == LCAP) {   // full: drop entries that fell out of the (shrinking) window
-                            int k = 0;
-                            for (int e = 0; e < LCAP; ++e) {
-                                const uint2 x = out[e];
-                                if (__uint_as_float(x.x) <= T) out[k++] = x;
-                            }
-                            cnt = k;
-                        }
-                        if (cnt < LCAP)
-                            out[cnt] = make_uint2(bits, (uint32_t)(code0 + (int)(bits & PMASK) * (ELEM ? 1 : CHUNK)));
-                        ++cnt;
-                    }
-                }
             }
-            if (row_ok) cand_meta[row * 2 + half] = make_float4(__int_as_float(cnt), m4min, smin, 0.f);
+            if (row_ok) cand_meta[((size_t)tile * NPART + part) * BM + r_in] = cnt;
         }
     }
     ptx::tc_fence_before();
@@ -412,83 +388,142 @@ __global__ void __launch_bounds__(NT, 1) vq_tc_kernel(const __grid_constant__ CU
 }
 
 
-// ------------------------------------------------------------------ pass 3: fp32 direct-form rescore
-// Rounding bound of pass 2 for row n and ANY code k (u = 2^-8, bf16 round-to-nearest on both operands,
-// Cauchy-Schwarz; fp32 accumulation, the 3-way split of en and the 5 payload bits are covered by C2):
-//   |S_nk - (||e'_k||^2 - 2 z'_n.e'_k)| <= eps_n = C1*zn*emax + C2*(2*zn*emax + emax^2)
+// ------------------------------------------------------------------ pass 3: resolve + fp32 direct-form rescore
+// Rounding bound of pass 2 for row n and ANY code k (u = unit roundoff of the operand type, round-to-nearest on
+// both operands, Cauchy-Schwarz; fp32 accumulation and the 3-way split of en are covered by C2, fp16
+// subnormals by the absolute term):
+//   |S_nk - (||e'_k||^2 - 2 z'_n.e'_k)| <= eps_n = tau_of(zn, emax)/2
 // so every code whose exact score is minimal has S <= min_k S + 2*eps_n.
+//
+// counters: [0] rows sent to the exact scan, [1] codes rescored, [2] rows resolved without rescoring,
+//           [3] operand-range flag, [4] rows on the rescore list.
 
-template <int CHUNK, bool ELEM, bool VEC>
-__global__ void __launch_bounds__(256) vq_rescore_kernel(
-    const float *__restrict__ z, const float *__restrict__ E, int64_t n_rows, int D, int K,
-    const uint2 *__restrict__ cand, const float4 *__restrict__ cand_meta, const float *__restrict__ zn,
-    const float *__restrict__ emax_p, int64_t *__restrict__ idx_out, float *__restrict__ d2_out,
-    int *__restrict__ list, int *__restrict__ counters, float abs_c) {
-    constexpr int NG = CHUNK;          // codes evaluated side by side
-    constexpr int LPG = 32 / NG;       // lanes per code
-    const int lane = threadIdx.x & 31, g = lane / LPG, l = lane % LPG;
+// 3a. one THREAD per row (coalesced record reads): a row with exactly one listed element inside its final
+// window is decided -- that element IS the nearest code; everything else goes on a work list.
+__global__ void __launch_bounds__(256) vq_resolve_kernel(int64_t n_rows, int K, const uint2 *__restrict__ cand,
+                                                         const int *__restrict__ cand_meta,
+                                                         const float *__restrict__ zn,
+                                                         const float *__restrict__ emax_p, float abs_c,
+                                                         int64_t *__restrict__ idx_out, int want_d2,
+                                                         int *__restrict__ resc_list, int *__restrict__ exact_list,
+                                                         int *__restrict__ counters) {
     const float emax = __ldg(emax_p);
     const bool range_bad = counters[3] != 0;   // set by the operand passes, which finished before this launch
-    int n_resc = 0, n_fast = 0;
-    for (int64_t row = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5); row < n_rows; row += (int64_t)gridDim.x * 8) {
-        const float4 m0 = __ldg(cand_meta + row * 2), m1 = __ldg(cand_meta + row * 2 + 1);
-        const int cnt0 = __float_as_int(m0.x), cnt1 = __float_as_int(m1.x);
-        const int n0 = min(cnt0, LCAP), n1 = min(cnt1, LCAP);
-        float v = BIG;
-        int code = 0x7fffffff;
-        if (lane < n0 + n1) {
-            const uint2 e = __ldg(cand + (row * 2 + (lane < n0 ? 0 : 1)) * LCAP + (lane < n0 ? lane : lane - n0));
-            v = __uint_as_float(e.x);
-            code = (int)e.y;
+    int n_fast = 0;
+    for (int64_t row = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; row < n_rows;
+         row += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t tile = row >> 7;
+        const int r = (int)(row & 127);
+        int cn[NPART];
+        bool bad = range_bad;
+#pragma unroll
+        for (int p = 0; p < NPART; ++p) {
+            cn[p] = __ldg(cand_meta + (tile * NPART + p) * BM + r);
+            bad |= cn[p] > LCAP;
         }
-        float gb = v;
+        if (bad) {
+            exact_list[atomicAdd(counters + 0, 1)] = (int)row;
+            continue;
+        }
+        const uint2 *e0 = cand + tile * NPART * LCAP * BM + r;
+        float gb = BIG;
+#pragma unroll
+        for (int p = 0; p < NPART; ++p)
+            for (int e = 0; e < cn[p]; ++e) gb = fminf(gb, __uint_as_float(__ldg(e0 + (p * LCAP + e) * BM).x));
+        const float T = gb + tau_of(__ldg(zn + row), emax, abs_c);
+        int nin = 0, code = 0;
+#pragma unroll
+        for (int p = 0; p < NPART; ++p)
+            for (int e = 0; e < cn[p]; ++e) {
+                const uint2 x = __ldg(e0 + (p * LCAP + e) * BM);
+                if (__uint_as_float(x.x) <= T) {
+                    const int c0 = (int)(x.y & 0xffffffu);
+                    uint32_t m = x.y >> 24;
+                    if (c0 + 8 > K) m &= (1u << max(K - c0, 0)) - 1u;     // padding codes of the last chunk
+                    nin += __popc(m);
+                    if (m) code = c0 + __ffs(m) - 1;
+                }
+            }
+        if (nin == 1 && !want_d2) {
+            idx_out[row] = (int64_t)code;
+            ++n_fast;
+        } else if (nin == 0 || nin > 64) {      // 0 cannot happen for finite inputs; > 64 exceeds the warp list
+            exact_list[atomicAdd(counters + 0, 1)] = (int)row;
+        } else {
+            resc_list[atomicAdd(counters + 4, 1)] = (int)row;
+        }
+    }
+    n_fast = (int)warp_sum((float)n_fast);
+    if ((threadIdx.x & 31) == 0 && n_fast) atomicAdd(counters + 2, n_fast);
+}
+
+// 3b. one WARP per listed row: the listed elements inside the window (<= 64) are rescored NG at a time in fp32
+// direct form sum (z-e)^2 (the reference's arithmetic, v5:41-45); the first minimal index wins.
+template <int NG, bool VEC>
+__global__ void __launch_bounds__(256) vq_rescore_kernel(
+    const float *__restrict__ z, const float *__restrict__ E, int D, int K, const uint2 *__restrict__ cand,
+    const int *__restrict__ cand_meta, const float *__restrict__ zn, const float *__restrict__ emax_p, float abs_c,
+    int64_t *__restrict__ idx_out, float *__restrict__ d2_out, const int *__restrict__ resc_list,
+    int *__restrict__ counters) {
+    constexpr int LPG = 32 / NG;       // lanes per code
+    __shared__ int s_codes[8][64];
+    __shared__ int s_cnt[8];
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5, g = lane / LPG, l = lane % LPG;
+    const float emax = __ldg(emax_p);
+    const int n_list = counters[4];
+    int n_resc = 0;
+    for (int li = blockIdx.x * 8 + wib; li < n_list; li += gridDim.x * 8) {
+        const int64_t row = resc_list[li];
+        const int64_t tile = row >> 7;
+        const int r = (int)(row & 127);
+        // lanes 0..15 / 16..31 read the entries of parts (0,1) then (2,3)
+        uint2 ent[2];
+        bool has_e[2];
+        float gb = BIG;
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const int p = 2 * h + (lane >> 4), e = lane & 15;
+            has_e[h] = e < __ldg(cand_meta + (tile * NPART + p) * BM + r);
+            ent[h] = make_uint2(0u, 0u);
+            if (has_e[h]) {
+                ent[h] = __ldg(cand + ((tile * NPART + p) * LCAP + e) * BM + r);
+                gb = fminf(gb, __uint_as_float(ent[h].x));
+            }
+        }
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) gb = fminf(gb, __shfl_xor_sync(0xffffffffu, gb, o));
-        const float znr = __ldg(zn + row);
-        const float T = gb + tau_of(znr, emax, abs_c);
-        if (range_bad || cnt0 > LCAP || cnt1 > LCAP || m0.y <= T || m1.y <= T) {
-            // the candidate record may be incomplete -> exact fp32 scan of the whole codebook
-            if (lane == 0) list[atomicAdd(counters + 0, 1)] = (int)row;
-            continue;
-        }
-        const bool in = (v <= T) && (code < K);
-        unsigned mask = __ballot_sync(0xffffffffu, in);
-        const int nc = __popc(mask);
-        const bool elem_ok = ELEM && !(m0.z <= T || m1.z <= T);   // no chunk holds two window elements
-        if (elem_ok && nc == 1 && d2_out == nullptr) {
-            // a single element inside the rounding window IS the nearest code: nothing to rescore
-            const int w = __shfl_sync(0xffffffffu, code, __ffs(mask) - 1);
-            if (lane == 0) idx_out[row] = (int64_t)w;
-            ++n_fast;
-            continue;
-        }
+        const float T = gb + tau_of(__ldg(zn + row), emax, abs_c);
+        if (lane == 0) s_cnt[wib] = 0;
+        __syncwarp();
+#pragma unroll
+        for (int h = 0; h < 2; ++h)
+            if (has_e[h] && __uint_as_float(ent[h].x) <= T) {
+                const int c0 = (int)(ent[h].y & 0xffffffu);
+                uint32_t m = ent[h].y >> 24;
+                if (c0 + 8 > K) m &= (1u << max(K - c0, 0)) - 1u;
+                while (m) {
+                    const int b = __ffs(m) - 1;
+                    m &= m - 1;
+                    const int pos = atomicAdd(&s_cnt[wib], 1);
+                    if (pos < 64) s_codes[wib][pos] = c0 + b;
+                }
+            }
+        __syncwarp();
+        const int nc = min(s_cnt[wib], 64);      // resolve guarantees <= 64
         float best = INFINITY;
         int bidx = 0x7fffffff;
         const float *zr = z + row * D;
-        const int passes = elem_ok ? (nc + NG - 1) / NG : nc;
-        for (int p = 0; p < passes; ++p) {
-            int cj;
-            bool has;
-            if (elem_ok) {
-                const int e = p * NG + g;
-                has = e < nc;
-                const int src = __fns(mask, 0, (has ? e : 0) + 1);
-                cj = __shfl_sync(0xffffffffu, code, src);
-            } else {
-                const int src = __fns(mask, 0, p + 1);
-                int c0 = __shfl_sync(0xffffffffu, code, src);
-                if (ELEM) c0 &= ~(CHUNK - 1);
-                cj = c0 + g;
-                has = cj < K;
-            }
+        for (int p = 0; p * NG < nc; ++p) {
+            const int e = p * NG + g;
+            const bool has = e < nc;
+            const int cj = has ? s_codes[wib][e] : 0;
             float s = 0.f;
             if (has) {
-                const float *e = E + (size_t)cj * D;
+                const float *ek = E + (size_t)cj * D;
                 if (VEC) {
-                    // issue 4 independent (z,e) load pairs before using them: the loop is latency-bound
-                    const float4 *z4 = reinterpret_cast<const float4 *>(zr), *e4 = reinterpret_cast<const float4 *>(e);
+                    const float4 *z4 = reinterpret_cast<const float4 *>(zr), *e4 = reinterpret_cast<const float4 *>(ek);
                     const int d4 = D >> 2;
-                    for (int i0 = l; i0 < d4; i0 += 4 * LPG) {
+                    for (int i0 = l; i0 < d4; i0 += 4 * LPG) {   // 4 independent load pairs in flight
                         float4 a[4], b[4];
 #pragma unroll
                         for (int u = 0; u < 4; ++u) {
@@ -503,17 +538,7 @@ __global__ void __launch_bounds__(256) vq_rescore_kernel(
                         }
                     }
                 } else {
-                    for (int i0 = l; i0 < D; i0 += 4 * LPG) {
-                        float a[4], b[4];
-#pragma unroll
-                        for (int u = 0; u < 4; ++u) {
-                            const int i = i0 + u * LPG;
-                            a[u] = b[u] = 0.f;
-                            if (i < D) { a[u] = __ldg(zr + i); b[u] = __ldg(e + i); }
-                        }
-#pragma unroll
-                        for (int u = 0; u < 4; ++u) { const float df = a[u] - b[u]; s = fmaf(df, df, s); }
-                    }
+                    for (int i = l; i < D; i += LPG) { const float df = __ldg(zr + i) - __ldg(ek + i); s = fmaf(df, df, s); }
                 }
             }
 #pragma unroll
@@ -527,17 +552,15 @@ __global__ void __launch_bounds__(256) vq_rescore_kernel(
                 argmin_merge(cs, ci, os, oi);
             }
             argmin_merge(best, bidx, cs, ci);
-            n_resc += elem_ok ? min(NG, nc - p * NG) : NG;
+            n_resc += min(NG, nc - p * NG);
         }
         if (lane == 0) {
             idx_out[row] = (int64_t)bidx;
             if (d2_out) d2_out[row] = best;
         }
+        __syncwarp();
     }
-    if (lane == 0) {
-        if (n_resc) atomicAdd(counters + 1, n_resc);
-        if (n_fast) atomicAdd(counters + 2, n_fast);
-    }
+    if (lane == 0 && n_resc) atomicAdd(counters + 1, n_resc);
 }
 
 // ------------------------------------------------------------------ host side
@@ -577,8 +600,7 @@ inline int make_tmap(CUtensorMap *m, const void *ptr, uint64_t rows, uint64_t co
 struct Workspace {
     float *mu, *enorm, *emax, *zn;
     uint2 *cand;
-    float4 *cand_meta;
-    int *list, *counters;
+    int *cand_meta, *list, *resc_list, *counters;
     op_t *Eb, *Zb;
     size_t bytes;
 };
@@ -589,22 +611,23 @@ inline Workspace carve(void *ws, const Geometry &g) {
     w.mu = (float *)take(sizeof(float) * g.D);
     w.enorm = (float *)take(sizeof(float) * g.K);
     w.emax = (float *)take(sizeof(float) * 4);
-    w.counters = (int *)take(sizeof(int) * 4);
+    w.counters = (int *)take(sizeof(int) * 8);
     w.Eb = (op_t *)take((size_t)g.Kp * g.DKp * 2);
     w.Zb = (op_t *)take((size_t)g.Np * g.DKp * 2);
     w.zn = (float *)take(sizeof(float) * g.Np);
-    w.cand = (uint2 *)take(sizeof(uint2) * g.Np * 2 * LCAP);
-    w.cand_meta = (float4 *)take(sizeof(float4) * g.Np * 2);
+    w.cand = (uint2 *)take(sizeof(uint2) * g.Np * NPART * LCAP);
+    w.cand_meta = (int *)take(sizeof(int) * g.Np * NPART);
     w.list = (int *)take(sizeof(int) * g.Np);
+    w.resc_list = (int *)take(sizeof(int) * g.Np);
     w.bytes = align_up(off, 1024);
     return w;
 }
 
-template <int NKB, int A_BUFS, int STAGES, int CHUNK, bool ELEM>
+template <int NKB, int A_BUFS, int STAGES>
 inline int launch_tc(const CUtensorMap &ta, const CUtensorMap &tb, const Geometry &g, const Workspace &w,
                      cudaStream_t st) {
     using L = SmemLayout<NKB, A_BUFS, STAGES>;
-    auto kern = vq_tc_kernel<NKB, A_BUFS, STAGES, CHUNK, ELEM>;
+    auto kern = vq_tc_kernel<NKB, A_BUFS, STAGES>;
     static bool attr_done = false;
     if (!attr_done) {
         LIPVQ_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::TOTAL));
@@ -625,66 +648,77 @@ inline size_t vq_tensor_ws_bytes(int64_t n, int D, int K) {
     return tc::carve(nullptr, tc::geometry(n > 0 ? n : 1, D, K)).bytes + 1024;
 }
 
-inline int vq_tensor_launch(const float *z, const float *E, int64_t n, int D, int K, int64_t *idx, float *d2,
-                            int32_t *stats, void *ws, cudaStream_t st) {
+// pass 0: codebook operand (mu, Eb, enorm, emax) into the workspace; zeroes the counters
+inline int vq_tensor_prep(const float *E, const tc::Geometry &g, const tc::Workspace &w, cudaStream_t st) {
     using namespace tc;
-    if (n > (int64_t)0x7fffffff - BM) return LIPVQ_ESHAPE;
-    const Geometry g = geometry(n, D, K);
-    void *ws_al = (void *)align_up((size_t)ws, 1024);
-    const Workspace w = carve(ws_al, g);
-    LIPVQ_CUDA_OK(cudaMemsetAsync(w.counters, 0, 4 * sizeof(int), st));
-    vq_prep_mean_kernel<<<(D + 31) / 32, 1024, 0, st>>>(E, K, D, w.mu);
+    LIPVQ_CUDA_OK(cudaMemsetAsync(w.counters, 0, 8 * sizeof(int), st));
+    vq_prep_mean_kernel<<<(g.D + 31) / 32, 1024, 0, st>>>(E, g.K, g.D, w.mu);
     LIPVQ_LAUNCH_OK();
-    vq_prep_rows_kernel<<<(g.Kp + 7) / 8, 256, 0, st>>>(E, w.mu, K, g.Kp, D, g.DKp, w.Eb, w.enorm, w.counters);
+    vq_prep_rows_kernel<<<(g.Kp + 7) / 8, 256, 0, st>>>(E, w.mu, g.K, g.Kp, g.D, g.DKp, w.Eb, w.enorm, w.counters);
     LIPVQ_LAUNCH_OK();
-    vq_prep_emax_kernel<<<1, 256, 0, st>>>(w.enorm, K, w.emax);
+    vq_prep_emax_kernel<<<1, 256, 0, st>>>(w.enorm, g.K, w.emax);
     LIPVQ_LAUNCH_OK();
-    {
-        int64_t blocks = (g.Np + 7) / 8;
-        if (blocks > 16 * kNumSMs) blocks = 16 * kNumSMs;
-        vq_convert_z_kernel<<<(unsigned)blocks, 256, 0, st>>>(z, w.mu, n, g.Np, D, g.DKp, w.Zb, w.zn, w.counters);
-        LIPVQ_LAUNCH_OK();
-    }
+    return LIPVQ_OK;
+}
+
+// passes 2-3 (+ exact tier) on operands already in the workspace (Zb, zn written by pass 1 or by the encoder)
+inline int vq_tensor_search(const float *z, const float *E, const tc::Geometry &g, const tc::Workspace &w,
+                            int64_t *idx, float *d2, int32_t *stats, cudaStream_t st) {
+    using namespace tc;
+    const int64_t n = g.n;
+    const int D = g.D, K = g.K;
     CUtensorMap ta, tb;
     LIPVQ_TRY(make_tmap(&ta, w.Zb, (uint64_t)g.Np, (uint64_t)g.DKp, BM));
     LIPVQ_TRY(make_tmap(&tb, w.Eb, (uint64_t)g.Kp, (uint64_t)g.DKp, BN));
-    // variant: small D has little epilogue slack per MMA -> 8-wide chunks without element payload
-    // (LIPVQ_TC_SMALL_D_ELEM=1 forces the element payload there too, for measurements)
-    static const int elem_env = [] { const char *e = getenv("LIPVQ_TC_ELEM"); return e ? atoi(e) : -1; }();
-    const bool elem = elem_env >= 0 ? elem_env != 0 : D > 96;
-    const bool c8 = !elem && D <= 96;     // chunk-level records: 8-wide chunks for small D, 4-wide otherwise
     int rc = LIPVQ_ESHAPE;
-#define LIPVQ_TC(NKB_, AB_, ST_)                                                                          \
-    rc = elem ? launch_tc<NKB_, AB_, ST_, 4, true>(ta, tb, g, w, st)                                      \
-              : (c8 ? launch_tc<NKB_, AB_, ST_, 8, false>(ta, tb, g, w, st)                               \
-                    : launch_tc<NKB_, AB_, ST_, 4, false>(ta, tb, g, w, st))
     switch (g.NKB) {
-        case 1: LIPVQ_TC(1, 2, 6); break;
-        case 2: LIPVQ_TC(2, 2, 5); break;
-        case 3: LIPVQ_TC(3, 2, 4); break;
-        case 4: LIPVQ_TC(4, 2, 3); break;
-        case 5: LIPVQ_TC(5, 1, 4); break;
+        case 1: rc = launch_tc<1, 2, 6>(ta, tb, g, w, st); break;
+        case 2: rc = launch_tc<2, 2, 5>(ta, tb, g, w, st); break;
+        case 3: rc = launch_tc<3, 2, 4>(ta, tb, g, w, st); break;
+        case 4: rc = launch_tc<4, 2, 3>(ta, tb, g, w, st); break;
+        case 5: rc = launch_tc<5, 1, 4>(ta, tb, g, w, st); break;
         default: break;
     }
-#undef LIPVQ_TC
     LIPVQ_TRY(rc);
+    const float abs_c = OP_ABS * sqrtf((float)D);
+    {
+        int64_t blocks = (n + 255) / 256;
+        if (blocks > 8 * kNumSMs) blocks = 8 * kNumSMs;
+        vq_resolve_kernel<<<(unsigned)blocks, 256, 0, st>>>(n, K, w.cand, w.cand_meta, w.zn, w.emax, abs_c, idx,
+                                                            d2 != nullptr, w.resc_list, w.list, w.counters);
+        LIPVQ_LAUNCH_OK();
+    }
     {
         int64_t blocks = (n + 7) / 8;
-        if (blocks > 16 * kNumSMs) blocks = 16 * kNumSMs;
-        const bool vec = (D & 3) == 0;
-#define LIPVQ_RESC(CH, EL, VE)                                                                                   \
-    vq_rescore_kernel<CH, EL, VE><<<(unsigned)blocks, 256, 0, st>>>(z, E, n, D, K, w.cand, w.cand_meta, w.zn, w.emax, \
-                                                                    idx, d2, w.list, w.counters, OP_ABS * sqrtf((float)D))
-        if (elem)    { if (vec) LIPVQ_RESC(4, true, true);   else LIPVQ_RESC(4, true, false); }
-        else if (c8) { if (vec) LIPVQ_RESC(8, false, true);  else LIPVQ_RESC(8, false, false); }
-        else         { if (vec) LIPVQ_RESC(4, false, true);  else LIPVQ_RESC(4, false, false); }
-#undef LIPVQ_RESC
+        if (blocks > 8 * kNumSMs) blocks = 8 * kNumSMs;   // grid-stride over the device-side list length
+        if ((D & 3) == 0)
+            vq_rescore_kernel<4, true><<<(unsigned)blocks, 256, 0, st>>>(z, E, D, K, w.cand, w.cand_meta, w.zn, w.emax,
+                                                                        abs_c, idx, d2, w.resc_list, w.counters);
+        else
+            vq_rescore_kernel<4, false><<<(unsigned)blocks, 256, 0, st>>>(z, E, D, K, w.cand, w.cand_meta, w.zn, w.emax,
+                                                                         abs_c, idx, d2, w.resc_list, w.counters);
         LIPVQ_LAUNCH_OK();
     }
     // tier 2: rows whose candidate list overflowed -> exact fp32 scan (count stays on the device)
     LIPVQ_TRY(vq_exact_launch(z, E, n, D, K, w.list, w.counters, idx, d2, st));
     if (stats) LIPVQ_CUDA_OK(cudaMemcpyAsync(stats, w.counters, 4 * sizeof(int), cudaMemcpyDeviceToDevice, st));
     return LIPVQ_OK;
+}
+
+inline int vq_tensor_launch(const float *z, const float *E, int64_t n, int D, int K, int64_t *idx, float *d2,
+                            int32_t *stats, void *ws, cudaStream_t st) {
+    using namespace tc;
+    if (n > (int64_t)0x7fffffff - BM) return LIPVQ_ESHAPE;
+    const Geometry g = geometry(n, D, K);
+    const Workspace w = carve((void *)align_up((size_t)ws, 1024), g);
+    LIPVQ_TRY(vq_tensor_prep(E, g, w, st));
+    {
+        int64_t blocks = (g.Np + 7) / 8;
+        if (blocks > 16 * kNumSMs) blocks = 16 * kNumSMs;
+        vq_convert_z_kernel<<<(unsigned)blocks, 256, 0, st>>>(z, w.mu, n, g.Np, D, g.DKp, w.Zb, w.zn, w.counters);
+        LIPVQ_LAUNCH_OK();
+    }
+    return vq_tensor_search(z, E, g, w, idx, d2, stats, st);
 }
 
 }  // namespace lipvq
