@@ -154,33 +154,77 @@ __global__ void vq_prep_emax_kernel(const float *__restrict__ enorm, int K, floa
 }
 
 // ------------------------------------------------------------------ pass 1: row operand
-// one warp per (padded) row: Zb row = [bf16(z - mu) | 1 1 1 | 0...]; zn = ||z - mu||
+// Zb row = [op(z - mu) | 1 1 1 | 0...]; zn = ||z - mu||.  One thread per 8 consecutive columns (32 B in, 16 B
+// out, fully coalesced); the row norm is combined in shared memory in column order (deterministic).
 __global__ void __launch_bounds__(256) vq_convert_z_kernel(const float *__restrict__ z, const float *__restrict__ mu,
                                                            int64_t n, int64_t Np, int D, int DKp,
                                                            op_t *__restrict__ Zb, float *__restrict__ zn,
                                                            int *__restrict__ counters) {
-    const int lane = threadIdx.x & 31;
-    for (int64_t r = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5); r < Np; r += (int64_t)gridDim.x * 8) {
-        op_t *row = Zb + r * DKp;
-        float s = 0.f, amax = 0.f;
-        // two bf16 per lane per step -> 4-byte stores, 128 B per warp
-        for (int d = lane * 2; d < DKp; d += 64) {
-            float v0 = 0.f, v1 = 0.f;
-            if (r < n) {
-                if (d < D) v0 = z[r * D + d] - mu[d];
-                else if (d < D + 3) v0 = 1.0f;
-                if (d + 1 < D) v1 = z[r * D + d + 1] - mu[d + 1];
-                else if (d + 1 < D + 3) v1 = 1.0f;
-                if (d < D) s = fmaf(v0, v0, s);
-                if (d + 1 < D) s = fmaf(v1, v1, s);
-                amax = fmaxf(amax, fmaxf(fabsf(v0), fabsf(v1)));
+    __shared__ float s_mu[5 * KBLK];
+    __shared__ float s_ss[256];
+    __shared__ int s_bad;
+    const int cpr = DKp >> 3, rpb = 256 / cpr;            // 8-column chunks per row, rows per block iteration
+    for (int i = threadIdx.x; i < DKp; i += 256) s_mu[i] = i < D ? mu[i] : 0.f;
+    if (threadIdx.x == 0) s_bad = 0;
+    __syncthreads();
+    const int rl = threadIdx.x / cpr, ch = threadIdx.x - rl * cpr;
+    const bool vec = (D & 3) == 0, pow2 = (cpr & (cpr - 1)) == 0 && cpr <= 32;
+    bool bad = false;
+    for (int64_t r0 = (int64_t)blockIdx.x * rpb; r0 < Np; r0 += (int64_t)gridDim.x * rpb) {
+        const int64_t r = r0 + rl;
+        float ss = 0.f;
+        if (rl < rpb && r < Np) {
+            float v[8];
+            const int d0 = ch * 8;
+#pragma unroll
+            for (int q = 0; q < 2; ++q) {
+                const int d = d0 + 4 * q;
+                float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (r < n && d < D) {
+                    const float *p = z + r * D + d;
+                    if (vec) t = __ldg(reinterpret_cast<const float4 *>(p));
+                    else {
+                        t.x = __ldg(p);
+                        if (d + 1 < D) t.y = __ldg(p + 1);
+                        if (d + 2 < D) t.z = __ldg(p + 2);
+                        if (d + 3 < D) t.w = __ldg(p + 3);
+                    }
+                }
+                v[4 * q] = t.x; v[4 * q + 1] = t.y; v[4 * q + 2] = t.z; v[4 * q + 3] = t.w;
             }
-            *reinterpret_cast<op2_t *>(row + d) = f2op2(v0, v1);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const int d = d0 + i;
+                if (r < n && d < D) {
+                    v[i] -= s_mu[d];
+                    ss = fmaf(v[i], v[i], ss);
+                    bad |= !(fabsf(v[i]) <= OP_MAX);
+                } else {
+                    v[i] = (r < n && d < D + 3) ? 1.0f : 0.f;
+                }
+            }
+            __align__(16) op2_t o[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) o[i] = f2op2(v[2 * i], v[2 * i + 1]);
+            *reinterpret_cast<uint4 *>(Zb + r * DKp + d0) = *reinterpret_cast<const uint4 *>(o);
         }
-        s = warp_sum(s);
-        if (!(amax <= OP_MAX)) atomicOr(counters + 3, 1);   // operand out of range -> whole launch goes exact
-        if (lane == 0 && r < n) zn[r] = sqrtf(s);
+        if (pow2) {     // the row's chunks sit in one warp: fixed shuffle tree, no block barrier
+            for (int o = cpr >> 1; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
+            if (ch == 0 && r < n) zn[r] = sqrtf(ss);
+        } else {
+            s_ss[threadIdx.x] = ss;
+            __syncthreads();
+            if (threadIdx.x < rpb && r0 + threadIdx.x < n) {
+                float t = 0.f;
+                for (int c = 0; c < cpr; ++c) t += s_ss[threadIdx.x * cpr + c];
+                zn[r0 + threadIdx.x] = sqrtf(t);
+            }
+            __syncthreads();
+        }
     }
+    if (bad) s_bad = 1;
+    __syncthreads();
+    if (threadIdx.x == 0 && s_bad) atomicOr(counters + 3, 1);   // operand out of range -> whole launch goes exact
 }
 
 
@@ -713,8 +757,9 @@ inline int vq_tensor_launch(const float *z, const float *E, int64_t n, int D, in
     const Workspace w = carve((void *)align_up((size_t)ws, 1024), g);
     LIPVQ_TRY(vq_tensor_prep(E, g, w, st));
     {
-        int64_t blocks = (g.Np + 7) / 8;
-        if (blocks > 16 * kNumSMs) blocks = 16 * kNumSMs;
+        const int rpb = 256 / (g.DKp >> 3);
+        int64_t blocks = (g.Np + rpb - 1) / rpb;
+        if (blocks > 8 * kNumSMs) blocks = 8 * kNumSMs;
         vq_convert_z_kernel<<<(unsigned)blocks, 256, 0, st>>>(z, w.mu, n, g.Np, D, g.DKp, w.Zb, w.zn, w.counters);
         LIPVQ_LAUNCH_OK();
     }
