@@ -122,6 +122,14 @@ int lipvq_vq_argmin(const float *z, const float *E, int64_t n_rows, int32_t D, i
                     int32_t mode, int64_t *idx, float *best_d2, int32_t *stats, void *ws,
                     size_t ws_bytes, void *stream);
 
+/* Encoder + nearest-codeword search in one call (v5:71-73): like lipvq_encoder_fwd followed by
+ * lipvq_vq_argmin(acts->z_e -> acts->idx), but on the tensor path the encoder's last epilogue also emits
+ * the search's row operand, so z_e is written once and never re-read for conversion.
+ * acts: scale, Wn, z_e, idx are written; a1, h1, a2, h2 are written when non-null (kept for backward). */
+int lipvq_encode_search_fwd(const lipvq_dims_t *dims, const lipvq_params_t *p, const float *x,
+                            int64_t n_rows, const lipvq_acts_t *acts, int32_t search_mode,
+                            int32_t *stats, void *ws, size_t ws_bytes, void *stream);
+
 /* z_q[n] = E[idx[n]] (v5:47); sse_q = sum (z_q - z_e)^2 (the value shared by the commitment and
  * codebook losses, v5:80-81).  sse_q: device double[1], overwritten. */
 int lipvq_gather_loss(const float *z_e, const float *E, const int64_t *idx, int64_t n_rows,

@@ -111,6 +111,7 @@ SIGNATURES = {
     "lipvq_linear_fwd": (C.c_int, [_VP, _VP, _VP, _VP, _I64, _I32, _I32, _I32, _VP]),
     "lipvq_lipschitz_fwd": (C.c_int, [_VP, _VP, _VP, _VP, _VP, _VP, _VP, _I64, _I32, _I32, _VP]),
     "lipvq_vq_argmin": (C.c_int, [_VP, _VP, _I64, _I32, _I32, _I32, _VP, _VP, _VP, _VP, _SZ, _VP]),
+    "lipvq_encode_search_fwd": (C.c_int, [_DP, _PP, _VP, _I64, _AP, _I32, _VP, _VP, _SZ, _VP]),
     "lipvq_gather_loss": (C.c_int, [_VP, _VP, _VP, _I64, _I32, _I32, _VP, _VP, _VP, _SZ, _VP]),
     "lipvq_decoder_fwd": (C.c_int, [_DP, _PP, _VP, _VP, _I64, _AP, _VP, _VP, _SZ, _VP]),
     "lipvq_quantize_decode_fwd": (C.c_int, [_DP, _PP, _VP, _I64, _AP, _VP, _VP, _SZ, _VP]),

@@ -123,7 +123,8 @@ int lipvq_encoder_fwd(const lipvq_dims_t *d, const lipvq_params_t *p, const floa
         static const bool split = [] { const char *e = getenv("LIPVQ_ENC"); return e && !strcmp(e, "split"); }();
         if (split && a->h2) return mlp::encoder_launch(d, p, x, n, a->a1, a->h1, a->a2, a->h2, a->Wn, a->z_e, st);
         uint8_t *img = (uint8_t *)align_up((size_t)ws, 1024);
-        return mlp::encoder_fused_launch(d, p, x, n, a->a1, a->h1, a->a2, a->h2, a->Wn, a->z_e, img, st);
+        return mlp::encoder_fused_launch(d, p, x, n, a->a1, a->h1, a->a2, a->h2, a->Wn, a->z_e, img, nullptr, nullptr,
+                                         nullptr, 0, nullptr, st);
     }
     LIPVQ_TRY(linear_fwd<ACT_GELU>(x, p->enc0_w, p->enc0_b, a->a1, a->h1, n, d->H1, d->F, st));
     LIPVQ_TRY(linear_fwd<ACT_GELU>(a->h1, p->enc2_w, p->enc2_b, a->a2, a->h2, n, d->H, d->H1, st));
@@ -168,6 +169,40 @@ int lipvq_vq_argmin(const float *z, const float *E, int64_t n, int32_t D, int32_
     }
     if (stats) LIPVQ_CUDA_OK(cudaMemsetAsync(stats, 0, 4 * sizeof(int32_t), st));
     return vq_exact_launch(z, E, n, D, K, nullptr, nullptr, idx, best_d2, st);
+}
+
+int lipvq_encode_search_fwd(const lipvq_dims_t *d, const lipvq_params_t *p, const float *x, int64_t n,
+                            const lipvq_acts_t *a, int32_t search_mode, int32_t *stats, void *ws, size_t ws_bytes,
+                            void *stream) {
+    if (!dims_ok(d) || n < 0) return LIPVQ_ESHAPE;
+    if (!p || !a) return LIPVQ_EALIGN;
+    if (n == 0) return LIPVQ_OK;
+    if (ws_bytes < mlp::enc_img_bytes(d->D) + 2048 + vq_tensor_ws_bytes(n, d->D, d->K) || !aligned16(ws))
+        return LIPVQ_EWORKSPACE;
+    cudaStream_t st = (cudaStream_t)stream;
+    const bool fuse = use_mlp_tc(d) && search_mode == LIPVQ_SEARCH_TENSOR && vq_tensor_supported(d->D, d->K) &&
+                      n <= (int64_t)0x7fffffff - tc::BM;
+    if (!fuse) {
+        LIPVQ_TRY(lipvq_encoder_fwd(d, p, x, n, a, ws, ws_bytes, stream));
+        return lipvq_vq_argmin(a->z_e, p->codebook, n, d->D, d->K, search_mode, a->idx, nullptr, stats, ws, ws_bytes,
+                               stream);
+    }
+    auto opt16 = [](const void *q) { return q == nullptr || aligned16(q); };
+    if (!aligned16(x) || !aligned16(a->scale) || !aligned16(a->Wn) || !aligned16(a->z_e) || !a->idx ||
+        !(opt16(a->a1) && opt16(a->h1) && opt16(a->a2) && opt16(a->h2)))
+        return LIPVQ_EALIGN;
+    // the row operand of the search (Zb, zn) is produced by the encoder's last epilogue: z_e is written once
+    // and never re-read for conversion
+    uint8_t *img = (uint8_t *)align_up((size_t)ws, 1024);
+    void *vq_ws = (void *)align_up((size_t)(img + mlp::enc_img_bytes(d->D)), 1024);
+    const tc::Geometry g = tc::geometry(n, d->D, d->K);
+    const tc::Workspace w = tc::carve(vq_ws, g);
+    lipschitz_prep_kernel<<<(d->D + 7) / 8, 256, 0, st>>>(p->lat_W, p->lat_ci, d->D, d->H, a->scale, a->Wn);
+    LIPVQ_LAUNCH_OK();
+    LIPVQ_TRY(vq_tensor_prep(p->codebook, g, w, st));
+    LIPVQ_TRY(mlp::encoder_fused_launch(d, p, x, n, a->a1, a->h1, a->a2, a->h2, a->Wn, a->z_e, img, w.mu, w.Zb, w.zn,
+                                        g.DKp, w.counters, st));
+    return vq_tensor_search(a->z_e, p->codebook, g, w, a->idx, nullptr, stats, st);
 }
 
 int lipvq_gather_loss(const float *z_e, const float *E, const int64_t *idx, int64_t n, int32_t D,
@@ -339,14 +374,11 @@ int lipvq_forward_fused(const lipvq_dims_t *d, const lipvq_params_t *p, const fl
     double *sse = b.take<double>(2);
     const size_t part_bytes = mlp::dec2_ws_bytes(d->K) + kRedBlocks * sizeof(float) + 512;
     float *part = (float *)b.take<char>(part_bytes);
-    const size_t vq_bytes = vq_tensor_ws_bytes(n, d->D, d->K);
-    void *vq_ws = b.take<char>(vq_bytes);
-    const size_t enc_ws_bytes = mlp::enc_img_bytes(d->D) + 1024;
-    void *enc_ws = b.take<char>(enc_ws_bytes);
     if (!b.ok()) return LIPVQ_EWORKSPACE;
-    LIPVQ_TRY(lipvq_encoder_fwd(d, p, x, n, &a, enc_ws, enc_ws_bytes, stream));
-    LIPVQ_TRY(lipvq_vq_argmin(a.z_e, p->codebook, n, d->D, d->K, search_mode, a.idx, nullptr, stats, vq_ws,
-                              vq_bytes, stream));
+    // the rest of the workspace serves the encoder image + the search (checked against their own needs there)
+    void *es_ws = (void *)align_up((size_t)(b.base + b.off), 256);
+    const size_t es_bytes = ws_bytes - (size_t)((char *)es_ws - (char *)ws);
+    LIPVQ_TRY(lipvq_encode_search_fwd(d, p, x, n, &a, search_mode, stats, es_ws, es_bytes, stream));
     LIPVQ_TRY(lipvq_quantize_decode_fwd(d, p, x, n, &a, sse, part, part_bytes, stream));
     if (loss_out) LIPVQ_TRY(lipvq_loss_finalize(sse, sse + 1, n_total, d->F, d->D, loss_out, stream));
     (void)st;

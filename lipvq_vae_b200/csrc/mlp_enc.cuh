@@ -14,6 +14,7 @@
 //               while layers 0/1 run: x_hi 256 | x_lo 320 | acc1 128 | h1_hi 352 | h1_lo 416
 #pragma once
 #include "mlp_tc.cuh"
+#include "vq_tensor.cuh"
 
 namespace lipvq {
 namespace mlp {
@@ -31,7 +32,9 @@ struct EncSmem {
     static constexpr int RING = W1 + 2 * W1_IMG;
     static constexpr int WBUF = RING + 2 * ENC_STAGE_BYTES;        // 16 warps x 2 KB store-transpose buffers
     static constexpr int BIAS = WBUF + 16 * 2048;                  // b0[64] b1[128] b[256]
-    static constexpr int BAR = BIAS + (H1 + HH + 256) * 4;         // mbarriers (8 B each), then the TMEM slot
+    static constexpr int MU = BIAS + (H1 + HH + 256) * 4;          // codebook mean mu[<=256+16] (search operand fusion)
+    static constexpr int ZNP = MU + 272 * 4;                       // [4 subs][128 rows] partial row norms
+    static constexpr int BAR = ZNP + 4 * TM * 4;                   // mbarriers (8 B each), then the TMEM slot
     static constexpr int NBAR = 3 + 2 + ENC_NCMAX + 4;             // a_ready[3] acc_ready[2] acc3[NC] w_full[2] w_empty[2]
     static constexpr int TOTAL = BAR + NBAR * 8 + 16 + 1024;
 };
@@ -97,7 +100,10 @@ __global__ void __launch_bounds__(ENC_THR, 1)
 enc_fused_kernel(const float *__restrict__ x, const float *__restrict__ W0, const float *__restrict__ b0,
                  const float *__restrict__ W1, const float *__restrict__ b1, const uint8_t *__restrict__ wn_img,
                  const float *__restrict__ b2, int64_t n_rows, int F, int D, float *__restrict__ a1,
-                 float *__restrict__ h1, float *__restrict__ a2, float *__restrict__ h2, float *__restrict__ z_e) {
+                 float *__restrict__ h1, float *__restrict__ a2, float *__restrict__ h2, float *__restrict__ z_e,
+                 // optional fusion of the search's row-operand pass (vq_tensor.cuh pass 1): Zb/zn/flag outputs
+                 const float *__restrict__ mu, tc::op_t *__restrict__ Zb, float *__restrict__ zn, int DKp,
+                 int *__restrict__ counters) {
     using L = EncSmem;
     extern __shared__ uint8_t smem_raw[];
     const uint32_t raw = ptx::smem_u32(smem_raw);
@@ -118,6 +124,8 @@ enc_fused_kernel(const float *__restrict__ x, const float *__restrict__ W0, cons
     for (int i = threadIdx.x; i < H1; i += ENC_THR) sb0[i] = b0[i];
     for (int i = threadIdx.x; i < HH; i += ENC_THR) sb1[i] = b1[i];
     for (int i = threadIdx.x; i < 256; i += ENC_THR) sb2[i] = i < D ? b2[i] : 0.f;
+    float *smu = reinterpret_cast<float *>(sm + L::MU), *sznp = reinterpret_cast<float *>(sm + L::ZNP);
+    for (int i = threadIdx.x; i < 272; i += ENC_THR) smu[i] = (Zb && i < D) ? mu[i] : 0.f;
     ptx::fence_proxy_async();
     if (threadIdx.x == 0) {
         for (int l = 0; l < 3; ++l) ptx::mbar_init(bar_a(l), ENC_EPI);
@@ -213,6 +221,7 @@ enc_fused_kernel(const float *__restrict__ x, const float *__restrict__ W0, cons
         };
         fetch_x(blockIdx.x);
         int t = 0;
+        bool zbad = false;
 #ifdef ENC_PROFILE
         long long pc[8] = {0, 0, 0, 0, 0, 0, 0, 0}, pt = clock64();
 #define ENC_TICK(i) do { const long long _n = clock64(); pc[i] += _n - pt; pt = _n; } while (0)
@@ -250,10 +259,64 @@ enc_fused_kernel(const float *__restrict__ x, const float *__restrict__ W0, cons
             ptx::mbar_wait(bar_acc3(0), par);
             ptx::tc_fence_after();
             ENC_TICK(5);
-            epilogue_blocks<ACT_SIGMOID>(tm + 256, 0, D16 / 16, sub, 4, D, sb2, false, 0u, 0u, wbuf, nullptr,
-                                         z_e + wrow0 * D, D, rows_valid, vec_d);
+            if (Zb == nullptr) {
+                epilogue_blocks<ACT_SIGMOID>(tm + 256, 0, D16 / 16, sub, 4, D, sb2, false, 0u, 0u, wbuf, nullptr,
+                                             z_e + wrow0 * D, D, rows_valid, vec_d);
+            } else {
+                // z_e plus the search's row operand: Zb = [fp16(z - mu) | 1 1 1 | 0...], zn = ||z - mu||
+                float ss = 0.f;
+                for (int cb = sub; cb < DKp / 16; cb += 4) {
+                    const int c0 = cb << 4;
+                    float v[16];
+                    if (c0 < D16) {
+                        uint32_t r[16];
+                        ptx::tmem_ld_32x32b_x16(tm + 256 + c0, r);
+                        ptx::tmem_ld_wait();
+#pragma unroll
+                        for (int i = 0; i < 16; ++i) v[i] = sigmoid_f(__uint_as_float(r[i]) + sb2[c0 + i]);
+                        warp_store16(wbuf, z_e + wrow0 * D + c0, D, v, rows_valid, min(16, D - c0), vec_d);
+                    }
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) {
+                        const int d = c0 + i;
+                        if (d < D) {
+                            v[i] -= smu[d];
+                            ss = fmaf(v[i], v[i], ss);
+                            zbad |= !(fabsf(v[i]) <= tc::OP_MAX);
+                        } else {
+                            v[i] = d < D + 3 ? 1.0f : 0.f;
+                        }
+                    }
+                    // 32 bytes of fp16 per row, transposed through the warp buffer: 16 rows x 32 B per store
+                    uint4 h0, h1v;
+                    {
+                        __align__(16) tc::op2_t o[8];
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) o[i] = tc::f2op2(v[2 * i], v[2 * i + 1]);
+                        h0 = reinterpret_cast<const uint4 *>(o)[0];
+                        h1v = reinterpret_cast<const uint4 *>(o)[1];
+                    }
+                    *reinterpret_cast<uint4 *>(wbuf + lane * 32 + ((0 ^ ((lane >> 2) & 1)) << 4)) = h0;
+                    *reinterpret_cast<uint4 *>(wbuf + lane * 32 + ((1 ^ ((lane >> 2) & 1)) << 4)) = h1v;
+                    __syncwarp();
+#pragma unroll
+                    for (int it = 0; it < 2; ++it) {
+                        const int f = it * 32 + lane, rw = f >> 1, j = f & 1;
+                        const uint4 q = *reinterpret_cast<const uint4 *>(wbuf + rw * 32 + ((j ^ ((rw >> 2) & 1)) << 4));
+                        if (rw < rows_valid)
+                            *reinterpret_cast<uint4 *>(Zb + (size_t)(wrow0 + rw) * DKp + c0 + j * 8) = q;
+                    }
+                    __syncwarp();
+                }
+                // row norm: the four column owners of a row combine through shared memory in a fixed order
+                sznp[sub * TM + r_in] = ss;
+                asm volatile("bar.sync 1, 512;" ::: "memory");
+                if (sub == 0 && lane < rows_valid)
+                    zn[wrow0 + lane] = sqrtf(((sznp[r_in] + sznp[TM + r_in]) + sznp[2 * TM + r_in]) + sznp[3 * TM + r_in]);
+            }
             ENC_TICK(6);
         }
+        if (zbad) atomicOr(counters + 3, 1);   // operand out of fp16 range -> the search goes exact for this launch
 #ifdef ENC_PROFILE
         if (blockIdx.x == 3 && (threadIdx.x & 31) == 0 && (threadIdx.x >> 5) < 8)
             printf("w%d tiles %d cyc/tile: xstage %lld | wait0 %lld epi0 %lld | wait1 %lld epi1 %lld | wait2 %lld epi2 %lld\n",
@@ -267,16 +330,17 @@ enc_fused_kernel(const float *__restrict__ x, const float *__restrict__ W0, cons
 
 inline size_t enc_img_bytes(int D) { return (size_t)ENC_NC * pad16(D) * 256; }
 
-// img: enc_img_bytes(D) of 1024-byte aligned scratch
+// img: enc_img_bytes(D) of 1024-byte aligned scratch.  mu/Zb/zn/counters: optional search-operand fusion.
 inline int encoder_fused_launch(const lipvq_dims_t *d, const lipvq_params_t *p, const float *x, int64_t n, float *a1,
                                 float *h1, float *a2, float *h2, const float *Wn, float *z_e, uint8_t *img,
-                                cudaStream_t st) {
+                                const float *mu, tc::op_t *Zb, float *zn, int DKp, int *counters, cudaStream_t st) {
     const int D16 = pad16(d->D);
     enc_wn_image_kernel<<<(D16 * 32 + 255) / 256, 256, 0, st>>>(Wn, d->D, D16, img);
     LIPVQ_LAUNCH_OK();
     LIPVQ_TRY(set_smem(enc_fused_kernel, EncSmem::TOTAL));
     enc_fused_kernel<<<grid_for(n), ENC_THR, EncSmem::TOTAL, st>>>(x, p->enc0_w, p->enc0_b, p->enc2_w, p->enc2_b, img,
-                                                                   p->lat_b, n, d->F, d->D, a1, h1, a2, h2, z_e);
+                                                                   p->lat_b, n, d->F, d->D, a1, h1, a2, h2, z_e, mu, Zb,
+                                                                   zn, DKp, counters);
     LIPVQ_LAUNCH_OK();
     return LIPVQ_OK;
 }

@@ -113,10 +113,8 @@ class _TokenizerFn(torch.autograd.Function):
         A = _acts_struct(a1=a1, h1=h1, a2=a2, h2=h2, scale=scale, Wn=Wn, z_e=z_e, idx=idx, z_q=z_q,
                          c1=c1, d1=d1, c2=c2, d2=d2, x_recon=x_recon)
         wsz = ws.numel()
-        N.check(lib.lipvq_encoder_fwd(C.byref(dims), C.byref(P), _p(x), n, C.byref(A), _p(ws), wsz, st),
-                "lipvq_encoder_fwd")
-        N.check(lib.lipvq_vq_argmin(_p(z_e), _p(params[7]), n, D, K, search_mode, _p(idx), None, _p(vq_stats),
-                                    _p(ws), wsz, st), "lipvq_vq_argmin")
+        N.check(lib.lipvq_encode_search_fwd(C.byref(dims), C.byref(P), _p(x), n, C.byref(A), search_mode,
+                                            _p(vq_stats), _p(ws), wsz, st), "lipvq_encode_search_fwd")
         N.check(lib.lipvq_quantize_decode_fwd(C.byref(dims), C.byref(P), _p(x), n, C.byref(A), _p(sse), _p(ws),
                                               wsz, st), "lipvq_quantize_decode_fwd")
         N.check(lib.lipvq_loss_finalize(_p(sse), C.c_void_p(sse.data_ptr() + 8), n_total, F_, D, _p(stats), st),
