@@ -276,8 +276,20 @@ def run_ours(args, rank, world, local_rank):
         gl(i)
     ms_gl = _time_events(gl, max(5, args.steps // 2), torch)
     gbs = (rows * D_LAT * 4 * 2 + rows * 8) / (ms_gl / 1e3) / 1e9
-    hbm = {"kernel": "gather_loss", "ms": ms_gl, "achieved_gbs": gbs, "peak_gbs": peaks["hbm_gbs"],
+    hbm = {"kernel": "quantize_emit (gather + commitment-SSE mode, via lipvq_gather_loss)", "ms": ms_gl, "achieved_gbs": gbs, "peak_gbs": peaks["hbm_gbs"],
            "frac": gbs / peaks["hbm_gbs"], "bytes": "read z_e + write z_q + idx (codebook rows hit L2)"}
+
+    # ---- BASELINE config 3 flavour: forward + backward of the tokenizer loss on the same batch (no optimiser)
+    def train_step(i):
+        for q in m.parameters():
+            q.grad = None
+        _, loss = m(xs[i % NBUF])
+        loss.backward()
+    for i in range(2):
+        train_step(i)
+    ms_train = _time_events(train_step, max(3, args.steps // 4), torch)
+    train = {"workload": "forward + backward (14 gradients), %d chunks, 1 GPU" % CHUNKS, "ms_per_step": ms_train,
+             "chunks_per_s": CHUNKS / (ms_train / 1e3)}
 
     cpu_baseline = None
     if world == 1 and not args.no_cpu:
@@ -303,7 +315,7 @@ def run_ours(args, rank, world, local_rank):
                 "h2d_bytes_per_step": rows * F_DIM * 4, "d2h_bytes_per_step": rows * 8 + 16,
                 "api": "LLFQVAE_V4.forward on a pinned-host batch; loss terms + token indices read back"},
         "gpu_launches": int(launches), "clocks": clk, "roofline": roofline, "cpu_baseline": cpu_baseline,
-        "config2_vq_alone": c2, "hbm_kernel": hbm,
+        "config2_vq_alone": c2, "hbm_kernel": hbm, "train_step": train,
     }
     print(json.dumps(out))
 

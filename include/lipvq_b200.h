@@ -25,7 +25,7 @@
 extern "C" {
 #endif
 
-#define LIPVQ_ABI_VERSION 1
+#define LIPVQ_ABI_VERSION 2
 
 enum {
     LIPVQ_OK = 0,
@@ -71,7 +71,8 @@ typedef struct {
     float *out_w, *out_b;
 } lipvq_grads_t;
 
-/* activations kept between forward and backward (all [n_rows, width] fp32) */
+/* activations kept between forward and backward (fp32).  The decoder acts on z_q = E[idx] (v5:47, 75), which
+ * takes only K distinct values, so its activations are kept PER CODE ([K, width]), not per row. */
 typedef struct {
     float *a1, *h1; /* encoder.0 pre-activation / GELU output   [N,H1]            */
     float *a2, *h2; /* encoder.2 pre-activation / GELU output   [N,H]             */
@@ -80,9 +81,10 @@ typedef struct {
     float *z_e;     /* sigmoid(h2 Wn^T + b)  [N,D]   v5:22-24                      */
     int64_t *idx;   /* nearest code per row [N]      v5:46                        */
     float *z_q;     /* codebook[idx] [N,D]           v5:47                        */
-    float *c1, *d1; /* decoder.0 pre-activation / GELU output   [N,H1]            */
-    float *c2, *d2; /* decoder.2 pre-activation / GELU output   [N,H]             */
-    float *x_recon; /* to_output(...) [N,F]          v5:76                        */
+    float *c1, *d1; /* decoder.0 pre-activation / GELU output of E  [K,H1]        */
+    float *c2, *d2; /* decoder.2 pre-activation / GELU output of E  [K,H]         */
+    float *x_recon; /* to_output(...) [N,F]          v5:76  (= xr_code[idx])       */
+    float *xr_code; /* to_output(decoder(E)) [K,F]: reconstruction of every code  */
 } lipvq_acts_t;
 
 int lipvq_abi_version(void);
@@ -143,10 +145,12 @@ int lipvq_decoder_fwd(const lipvq_dims_t *dims, const lipvq_params_t *p, const f
                       const float *x, int64_t n_rows, const lipvq_acts_t *acts, double *sse_r,
                       void *ws, size_t ws_bytes, void *stream);
 
-/* Gather + decoder + both loss sums in one pass (v5:47, 74-81): z_q[n] = E[idx[n]] is written to
- * acts->z_q (this IS z_latent, v5:74), x_recon to acts->x_recon, and sse[0] = sum (x_recon-x)^2,
- * sse[1] = sum (z_q-z_e)^2 (device double[2], overwritten).  acts: idx, z_e are read; z_q, x_recon are
- * written; c1,d1,c2,d2 are written when non-null (kept for backward).  x may be null (sse[0] = 0). */
+/* Gather + decoder + both loss sums (v5:47, 74-81).  The decoder runs once per CODE (xr_code = decoder(E),
+ * [K,F]); one streaming pass over the rows then writes z_q[n] = E[idx[n]] to acts->z_q (this IS z_latent,
+ * v5:74), x_recon[n] = xr_code[idx[n]] to acts->x_recon (nullable), and sse[0] = sum (x_recon-x)^2,
+ * sse[1] = sum (z_q-z_e)^2 (device double[2], overwritten).  acts: idx, z_e are read; z_q is written;
+ * c1,d1,c2,d2,xr_code ([K,.], code level) are written when non-null (kept for backward).
+ * x may be null (sse[0] = 0). */
 int lipvq_quantize_decode_fwd(const lipvq_dims_t *dims, const lipvq_params_t *p, const float *x,
                               int64_t n_rows, const lipvq_acts_t *acts, double *sse, void *ws,
                               size_t ws_bytes, void *stream);
@@ -156,15 +160,17 @@ int lipvq_quantize_decode_fwd(const lipvq_dims_t *dims, const lipvq_params_t *p,
 int lipvq_loss_finalize(const double *sse_r, const double *sse_q, int64_t n_total, int32_t F,
                         int32_t D, float *out, void *stream);
 
-/* Backward of the decoder + losses w.r.t. decoder/to_output parameters and z_q
- * (autograd of v5:75-83 triggered at robomimic/algo/icl.py:969):
- *   g_zq[n] = dRecon/dz_q[n] + 0.5*(z_q[n]-z_e[n])/(n_total*D).
- * grad_scale: DEVICE scalar dL/dloss (nullable = 1), read by the kernels so the host never
- * synchronises.  n_total = global row count (data parallel). */
+/* Backward of the decoder + losses w.r.t. decoder/to_output parameters and the codebook
+ * (autograd of v5:75-83 triggered at robomimic/algo/icl.py:969), evaluated per code: the reconstruction
+ * gradient is first summed over the rows of each code, g_R[k] = sum_{idx[n]=k} 2 (x_recon[n]-x[n])/(n_total F),
+ * the decoder backward then runs on the K code-level rows (acts->c1,d1,c2,d2,xr_code), and
+ *   g->codebook[k] = dRecon/dE[k] + sum_{idx[n]=k} 0.5*(E[k]-z_e[n])/(n_total*D)        (complete gradient).
+ * Writes g->{dec0_*, dec2_*, out_*, codebook}.  grad_scale: DEVICE scalar dL/dloss (nullable = 1), read by
+ * the kernels so the host never synchronises.  n_total = global row count (data parallel). */
 int lipvq_decoder_bwd(const lipvq_dims_t *dims, const lipvq_params_t *p, const float *x,
                       int64_t n_rows, int64_t n_total, const float *grad_scale,
-                      const lipvq_acts_t *acts, const lipvq_grads_t *g, float *g_zq, void *ws,
-                      size_t ws_bytes, void *stream);
+                      const lipvq_acts_t *acts, const lipvq_grads_t *g, void *ws, size_t ws_bytes,
+                      void *stream);
 
 /* sums[idx[n],:] += src[n,:]; counts[idx[n]] += 1 (counts nullable).  Serves the codebook
  * gradient (index_put_ accumulate of autograd, v5:47) and the EMA cluster statistics.

@@ -53,7 +53,7 @@ class Grads(C.Structure):
     _fields_ = [(n, C.c_void_p) for n in _PARAM_FIELDS]
 
 
-_ACT_FIELDS = ["a1", "h1", "a2", "h2", "scale", "Wn", "z_e", "idx", "z_q", "c1", "d1", "c2", "d2", "x_recon"]
+_ACT_FIELDS = ["a1", "h1", "a2", "h2", "scale", "Wn", "z_e", "idx", "z_q", "c1", "d1", "c2", "d2", "x_recon", "xr_code"]
 
 
 class Acts(C.Structure):
@@ -116,7 +116,7 @@ SIGNATURES = {
     "lipvq_decoder_fwd": (C.c_int, [_DP, _PP, _VP, _VP, _I64, _AP, _VP, _VP, _SZ, _VP]),
     "lipvq_quantize_decode_fwd": (C.c_int, [_DP, _PP, _VP, _I64, _AP, _VP, _VP, _SZ, _VP]),
     "lipvq_loss_finalize": (C.c_int, [_VP, _VP, _I64, _I32, _I32, _VP, _VP]),
-    "lipvq_decoder_bwd": (C.c_int, [_DP, _PP, _VP, _I64, _I64, _VP, _AP, _GP, _VP, _VP, _SZ, _VP]),
+    "lipvq_decoder_bwd": (C.c_int, [_DP, _PP, _VP, _I64, _I64, _VP, _AP, _GP, _VP, _SZ, _VP]),
     "lipvq_scatter_add": (C.c_int, [_VP, _VP, _I64, _I32, _I32, _VP, _VP, _VP]),
     "lipvq_encoder_bwd": (C.c_int, [_DP, _PP, _VP, _I64, _I64, _VP, _AP, _GP, _VP, _SZ, _VP]),
     "lipvq_forward_fused": (C.c_int, [_DP, _PP, _VP, _I64, _I64, _I32, _VP, _VP, _VP, _VP, _VP, _VP, _SZ, _VP]),
@@ -140,7 +140,7 @@ def lib():
                     fn = getattr(h, name)
                     fn.restype = res
                     fn.argtypes = args
-                if h.lipvq_abi_version() != 1:
+                if h.lipvq_abi_version() != 2:
                     raise LipVQNativeError("ABI version mismatch")
                 _lib = h
     return _lib

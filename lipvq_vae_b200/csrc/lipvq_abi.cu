@@ -8,7 +8,6 @@
 #include "gemm_simt.cuh"
 #include "misc_kernels.cuh"
 #include "mlp_tc.cuh"
-#include "mlp_dec2.cuh"
 #include "mlp_enc.cuh"
 #include "vq_exact.cuh"
 #include "vq_tensor.cuh"
@@ -47,22 +46,28 @@ static size_t max_splitk_floats(const lipvq_dims_t *d, int64_t n) {
     return m;
 }
 
+// per-code decoder tensors: c1,d1 [K,H1], c2,d2 [K,H], xr_code [K,F]
+static size_t code_level_floats(const lipvq_dims_t *d) {
+    return (size_t)d->K * (size_t)(2 * d->H1 + 2 * d->H + d->F) + 5 * 64;
+}
+
 static size_t workspace_bytes_impl(const lipvq_dims_t *d, int64_t n) {
     const size_t N = (size_t)(n > 0 ? n : 1);
     size_t fl = 0;
     // forward intermediates (fused forward keeps all of them in ws)
-    fl += N * (size_t)(2 * d->H1 + 2 * d->H) * 2;   // a1,h1,a2,h2,c1,d1,c2,d2
+    fl += N * (size_t)(2 * d->H1 + 2 * d->H);        // a1,h1,a2,h2 (CUDA-core encoder only)
     fl += N * (size_t)d->D * 2;                      // z_e, z_q
     fl += N * (size_t)d->F;                          // x_recon
     fl += (size_t)d->D * d->H * 2 + d->D;            // Wn, gWn, scale
+    fl += code_level_floats(d) * 2;                  // per-code decoder activations + their gradients
     // backward scratch
-    fl += N * (size_t)(d->F + d->H + d->H1 + d->D);  // g_xr / g_pre / g_a2 / g_a1 style buffers
-    fl += max_splitk_floats(d, n);
+    fl += N * (size_t)(d->H + d->H1 + d->D);         // g_pre / g_a2 / g_a1
+    fl += max_splitk_floats(d, n > d->K ? n : d->K);
     fl += 4 * kRedBlocks + 64;
     size_t bytes = fl * sizeof(float) + 64 * 256;    // alignment slack for the bump allocator
     bytes += vq_tensor_ws_bytes(n, d->D, d->K);
     bytes += N * sizeof(int64_t) + 4096;
-    bytes += mlp::dec2_ws_bytes(d->K) + kRedBlocks * sizeof(float) + 256;
+    bytes += align_up(2 * kQeBlocks * sizeof(float), 256) + align_up(mlp::kPartBytes, 256) + 1024;
     bytes += mlp::enc_img_bytes(d->D) + 2048;
     return align_up(bytes, 256);
 }
@@ -207,18 +212,20 @@ int lipvq_encode_search_fwd(const lipvq_dims_t *d, const lipvq_params_t *p, cons
 
 int lipvq_gather_loss(const float *z_e, const float *E, const int64_t *idx, int64_t n, int32_t D,
                       int32_t K, float *z_q, double *sse_q, void *ws, size_t ws_bytes, void *stream) {
-    (void)K;
-    if (n < 0 || D < 1) return LIPVQ_ESHAPE;
+    if (n < 0 || D < 1 || K < 1) return LIPVQ_ESHAPE;
     if (!aligned16(z_e) || !aligned16(E) || !idx || !aligned16(z_q) || !sse_q) return LIPVQ_EALIGN;
-    if (ws_bytes < kRedBlocks * sizeof(float) || !aligned16(ws)) return LIPVQ_EWORKSPACE;
+    if (ws_bytes < 2 * kQeBlocks * sizeof(float) || !aligned16(ws)) return LIPVQ_EWORKSPACE;
     cudaStream_t st = (cudaStream_t)stream;
+    if (n == 0) { LIPVQ_CUDA_OK(cudaMemsetAsync(sse_q, 0, sizeof(double), st)); return LIPVQ_OK; }
     float *part = (float *)ws;
+    const int64_t tiles = (n + QE_ROWS - 1) / QE_ROWS;
+    const int grid = (int)(tiles < kQeBlocks ? tiles : kQeBlocks);
     if ((D & 3) == 0)
-        gather_loss_kernel<true><<<kRedBlocks, 256, 0, st>>>(z_e, E, idx, n, D, z_q, part);
+        quantize_emit_kernel<true><<<grid, QE_THR, 0, st>>>(z_e, E, nullptr, idx, nullptr, n, D, 1, K, z_q, nullptr, part);
     else
-        gather_loss_kernel<false><<<kRedBlocks, 256, 0, st>>>(z_e, E, idx, n, D, z_q, part);
+        quantize_emit_kernel<false><<<grid, QE_THR, 0, st>>>(z_e, E, nullptr, idx, nullptr, n, D, 1, K, z_q, nullptr, part);
     LIPVQ_LAUNCH_OK();
-    partials_to_double_kernel<<<1, 256, 0, st>>>(part, kRedBlocks, sse_q);
+    partials_to_double_kernel<<<1, 256, 0, st>>>(part, grid, sse_q);
     LIPVQ_LAUNCH_OK();
     return LIPVQ_OK;
 }
@@ -247,29 +254,68 @@ int lipvq_decoder_fwd(const lipvq_dims_t *d, const lipvq_params_t *p, const floa
     return LIPVQ_OK;
 }
 
+// scratch of lipvq_quantize_decode_fwd: [sse partials | dec_kernel partials | code-level tensors not supplied]
+static size_t qd_ws_bytes(const lipvq_dims_t *d) {
+    return align_up(2 * kQeBlocks * sizeof(float), 256) + align_up(mlp::kPartBytes, 256) +
+           code_level_floats(d) * sizeof(float) + 256;
+}
+
+// R = decoder(E) for every code (v5:62-68, 75-76 applied to the K distinct values z_q can take)
+static int decoder_code_table(const lipvq_dims_t *d, const lipvq_params_t *p, float *c1, float *d1, float *c2,
+                              float *d2, float *R, double *part, cudaStream_t st) {
+    if (use_mlp_tc(d)) {
+        const mlp::DecLayout L = mlp::dec_layout(d->D);
+        LIPVQ_TRY(mlp::set_smem(mlp::dec_kernel, L.total));
+        mlp::dec_kernel<<<mlp::grid_for(d->K), mlp::NTHR, L.total, st>>>(
+            nullptr, p->codebook, nullptr, nullptr, p->dec0_w, p->dec0_b, p->dec2_w, p->dec2_b, p->out_w, p->out_b,
+            d->K, d->D, d->K, d->F, nullptr, c1, d1, c2, d2, R, part, nullptr);
+        LIPVQ_LAUNCH_OK();
+        return LIPVQ_OK;
+    }
+    LIPVQ_TRY(linear_fwd<ACT_GELU>(p->codebook, p->dec0_w, p->dec0_b, c1, d1, d->K, d->H1, d->D, st));
+    LIPVQ_TRY(linear_fwd<ACT_GELU>(d1, p->dec2_w, p->dec2_b, c2, d2, d->K, d->H, d->H1, st));
+    return linear_fwd<ACT_NONE>(d2, p->out_w, p->out_b, nullptr, R, d->K, d->F, d->H, st);
+}
+
 int lipvq_quantize_decode_fwd(const lipvq_dims_t *d, const lipvq_params_t *p, const float *x, int64_t n,
                               const lipvq_acts_t *a, double *sse, void *ws, size_t ws_bytes, void *stream) {
     if (!dims_ok(d) || n < 0) return LIPVQ_ESHAPE;
     if (!p || !a || !sse) return LIPVQ_EALIGN;
     cudaStream_t st = (cudaStream_t)stream;
     if (n == 0) { LIPVQ_CUDA_OK(cudaMemsetAsync(sse, 0, 2 * sizeof(double), st)); return LIPVQ_OK; }
-    if (!a->idx || !aligned16(a->z_e) || !aligned16(a->z_q) || !aligned16(a->x_recon) || (x && !aligned16(x)))
+    auto opt16 = [](const void *q) { return q == nullptr || aligned16(q); };
+    if (!a->idx || !aligned16(a->z_e) || !aligned16(a->z_q) || !opt16(a->x_recon) || !opt16(x) || !opt16(a->c1) ||
+        !opt16(a->d1) || !opt16(a->c2) || !opt16(a->d2) || !opt16(a->xr_code))
         return LIPVQ_EALIGN;
-    const size_t need = mlp::dec2_ws_bytes(d->K) + kRedBlocks * sizeof(float) + 256;
-    if (ws_bytes < need || !aligned16(ws)) return LIPVQ_EWORKSPACE;
-    if (use_mlp_tc(d)) {
-        // z_q / z_latent + sum (z_q-z_e)^2: one HBM-bound streaming pass; decoder from the codeword table
-        char *gws = (char *)ws + align_up(mlp::dec2_ws_bytes(d->K), 256);
-        if (!x) LIPVQ_CUDA_OK(cudaMemsetAsync(sse, 0, sizeof(double), st));
-        LIPVQ_TRY(lipvq_gather_loss(a->z_e, p->codebook, a->idx, n, d->D, d->K, a->z_q, sse + 1, gws,
-                                    kRedBlocks * sizeof(float), stream));
-        return mlp::decoder2_launch(d, p, a->idx, x, n, a->c1, a->d1, a->c2, a->d2, a->x_recon, ws, sse, st);
+    if (ws_bytes < qd_ws_bytes(d) || !aligned16(ws)) return LIPVQ_EWORKSPACE;
+    Bump b(ws, ws_bytes);
+    float *part = b.take<float>(2 * kQeBlocks);
+    double *dpart = b.take<double>(mlp::kPartBytes / sizeof(double));
+    const bool tc = use_mlp_tc(d);   // the tensor kernel keeps the code-level activations on chip unless asked
+    float *c1 = a->c1, *d1 = a->d1, *c2 = a->c2, *d2 = a->d2, *R = a->xr_code;
+    if (!tc) {
+        if (!c1) c1 = b.take<float>((size_t)d->K * d->H1);
+        if (!d1) d1 = b.take<float>((size_t)d->K * d->H1);
+        if (!c2) c2 = b.take<float>((size_t)d->K * d->H);
+        if (!d2) d2 = b.take<float>((size_t)d->K * d->H);
     }
-    // CUDA-core path: gather+loss pass, then the three layer kernels (needs c1..d2 buffers)
-    if (!a->c1 || !a->d1 || !a->c2 || !a->d2) return LIPVQ_EALIGN;
-    if (!x) LIPVQ_CUDA_OK(cudaMemsetAsync(sse, 0, sizeof(double), st));
-    LIPVQ_TRY(lipvq_gather_loss(a->z_e, p->codebook, a->idx, n, d->D, d->K, a->z_q, sse + 1, ws, ws_bytes, stream));
-    return lipvq_decoder_fwd(d, p, a->z_q, x, n, a, sse, ws, ws_bytes, stream);
+    if (!R) R = b.take<float>((size_t)d->K * d->F);
+    if (!b.ok()) return LIPVQ_EWORKSPACE;
+    // the decoder acts on z_q = E[idx] (v5:47, 75): K distinct inputs, so it runs once per CODE; the per-row
+    // work is the streaming pass below (z_q / z_latent write, x_recon = R[idx], both loss sums)
+    LIPVQ_TRY(decoder_code_table(d, p, c1, d1, c2, d2, R, dpart, st));
+    const int64_t tiles = (n + QE_ROWS - 1) / QE_ROWS;
+    const int grid = (int)(tiles < kQeBlocks ? tiles : kQeBlocks);
+    if ((d->D & 3) == 0)
+        quantize_emit_kernel<true><<<grid, QE_THR, 0, st>>>(a->z_e, p->codebook, R, a->idx, x, n, d->D, d->F, d->K,
+                                                            a->z_q, a->x_recon, part);
+    else
+        quantize_emit_kernel<false><<<grid, QE_THR, 0, st>>>(a->z_e, p->codebook, R, a->idx, x, n, d->D, d->F, d->K,
+                                                             a->z_q, a->x_recon, part);
+    LIPVQ_LAUNCH_OK();
+    partials2_to_double_kernel<<<1, 256, 0, st>>>(part, grid, sse);
+    LIPVQ_LAUNCH_OK();
+    return LIPVQ_OK;
 }
 
 int lipvq_loss_finalize(const double *sse_r, const double *sse_q, int64_t n_total, int32_t F, int32_t D,
@@ -284,27 +330,40 @@ int lipvq_loss_finalize(const double *sse_r, const double *sse_q, int64_t n_tota
 
 int lipvq_decoder_bwd(const lipvq_dims_t *d, const lipvq_params_t *p, const float *x, int64_t n,
                       int64_t n_total, const float *grad_scale, const lipvq_acts_t *a, const lipvq_grads_t *g,
-                      float *g_zq, void *ws, size_t ws_bytes, void *stream) {
+                      void *ws, size_t ws_bytes, void *stream) {
     if (!dims_ok(d) || n <= 0 || n_total < n) return LIPVQ_ESHAPE;
-    if (!p || !a || !g || !aligned16(x) || !aligned16(g_zq)) return LIPVQ_EALIGN;
+    if (!p || !a || !g || !aligned16(x) || !a->idx || !aligned16(a->z_e) || !aligned16(a->c1) || !aligned16(a->d1) ||
+        !aligned16(a->c2) || !aligned16(a->d2) || !aligned16(a->xr_code) || !aligned16(g->codebook))
+        return LIPVQ_EALIGN;
     if (ws_bytes < workspace_bytes_impl(d, n) || !aligned16(ws)) return LIPVQ_EWORKSPACE;
     cudaStream_t st = (cudaStream_t)stream;
+    const int K = d->K;
     Bump b(ws, ws_bytes);
-    float *g_xr = b.take<float>((size_t)n * d->F);
-    float *g_c2 = b.take<float>((size_t)n * d->H);
-    float *g_c1 = b.take<float>((size_t)n * d->H1);
-    float *part = b.take<float>(max_splitk_floats(d, n));
+    float *g_R = b.take<float>((size_t)K * d->F);
+    float *g_c2 = b.take<float>((size_t)K * d->H);
+    float *g_c1 = b.take<float>((size_t)K * d->H1);
+    float *part = b.take<float>(max_splitk_floats(d, K));
     if (!b.ok()) return LIPVQ_EWORKSPACE;
     const float a_r = (float)(2.0 / ((double)n_total * d->F));
     const float a_q = (float)(0.5 / ((double)n_total * d->D));
-    scaled_diff_kernel<<<kRedBlocks, 256, 0, st>>>(a->x_recon, x, a_r, grad_scale, n * d->F, g_xr);
+    const unsigned blocks = (unsigned)((n + SC_ROWS - 1) / SC_ROWS);
+    // every row with code k sees the same decoder, so the reconstruction gradient is summed per code first:
+    // g_R[k] = sum_{idx[n]=k} 2 (x_recon[n] - x[n]) / (n_total F), and the decoder backward runs on K rows
+    LIPVQ_CUDA_OK(cudaMemsetAsync(g_R, 0, (size_t)K * d->F * sizeof(float), st));
+    scatter_add_kernel<true><<<blocks, 256, 0, st>>>(x, a->idx, n, d->F, K, g_R, nullptr, a->xr_code, a_r, grad_scale);
     LIPVQ_LAUNCH_OK();
-    LIPVQ_TRY(linear_bwd_weight(g_xr, a->d2, g->out_w, g->out_b, n, d->F, d->H, part, st));
-    LIPVQ_TRY(linear_bwd_input<ACT_GELU>(g_xr, p->out_w, a->c2, g_c2, n, d->F, d->H, nullptr, nullptr, 0.f, nullptr, st));
-    LIPVQ_TRY(linear_bwd_weight(g_c2, a->d1, g->dec2_w, g->dec2_b, n, d->H, d->H1, part, st));
-    LIPVQ_TRY(linear_bwd_input<ACT_GELU>(g_c2, p->dec2_w, a->c1, g_c1, n, d->H, d->H1, nullptr, nullptr, 0.f, nullptr, st));
-    LIPVQ_TRY(linear_bwd_weight(g_c1, a->z_q, g->dec0_w, g->dec0_b, n, d->H1, d->D, part, st));
-    LIPVQ_TRY(linear_bwd_input<ACT_NONE>(g_c1, p->dec0_w, nullptr, g_zq, n, d->H1, d->D, a->z_q, a->z_e, a_q, grad_scale, st));
+    LIPVQ_TRY(linear_bwd_weight(g_R, a->d2, g->out_w, g->out_b, K, d->F, d->H, part, st));
+    LIPVQ_TRY(linear_bwd_input<ACT_GELU>(g_R, p->out_w, a->c2, g_c2, K, d->F, d->H, nullptr, nullptr, 0.f, nullptr, st));
+    LIPVQ_TRY(linear_bwd_weight(g_c2, a->d1, g->dec2_w, g->dec2_b, K, d->H, d->H1, part, st));
+    LIPVQ_TRY(linear_bwd_input<ACT_GELU>(g_c2, p->dec2_w, a->c1, g_c1, K, d->H, d->H1, nullptr, nullptr, 0.f, nullptr, st));
+    LIPVQ_TRY(linear_bwd_weight(g_c1, p->codebook, g->dec0_w, g->dec0_b, K, d->H1, d->D, part, st));
+    // codebook gradient: decoder path (row k of the code-level batch IS code k) ...
+    LIPVQ_TRY(linear_bwd_input<ACT_NONE>(g_c1, p->dec0_w, nullptr, g->codebook, K, d->H1, d->D, nullptr, nullptr, 0.f,
+                                         nullptr, st));
+    // ... plus the codebook loss: sum_{idx[n]=k} 0.5 (E[k] - z_e[n]) / (n_total D)   (v5:81)
+    scatter_add_kernel<true><<<blocks, 256, 0, st>>>(a->z_e, a->idx, n, d->D, K, g->codebook, nullptr, p->codebook,
+                                                     a_q, grad_scale);
+    LIPVQ_LAUNCH_OK();
     return LIPVQ_OK;
 }
 
@@ -314,7 +373,8 @@ int lipvq_scatter_add(const float *src, const int64_t *idx, int64_t n, int32_t D
     if (n == 0) return LIPVQ_OK;
     if (!aligned16(src) || !idx || !aligned16(sums)) return LIPVQ_EALIGN;
     const int64_t blocks = (n + SC_ROWS - 1) / SC_ROWS;
-    scatter_add_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(src, idx, n, D, K, sums, counts);
+    scatter_add_kernel<false><<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(src, idx, n, D, K, sums, counts,
+                                                                                  nullptr, 1.f, nullptr);
     LIPVQ_LAUNCH_OK();
     return LIPVQ_OK;
 }
@@ -369,10 +429,10 @@ int lipvq_forward_fused(const lipvq_dims_t *d, const lipvq_params_t *p, const fl
     a.z_e = b.take<float>((size_t)n * d->D);
     a.idx = idx ? idx : b.take<int64_t>(n);
     a.z_q = z_latent;
-    a.c1 = a.a1; a.d1 = a.h1; a.c2 = a.a2; a.d2 = tc ? nullptr : a.h2;   // encoder activations are dead by then
-    a.x_recon = x_recon ? x_recon : b.take<float>((size_t)n * d->F);
+    a.c1 = a.d1 = a.c2 = a.d2 = a.xr_code = nullptr;   // code-level decoder tensors come from the scratch below
+    a.x_recon = x_recon;                               // optional output
     double *sse = b.take<double>(2);
-    const size_t part_bytes = mlp::dec2_ws_bytes(d->K) + kRedBlocks * sizeof(float) + 512;
+    const size_t part_bytes = qd_ws_bytes(d);
     float *part = (float *)b.take<char>(part_bytes);
     if (!b.ok()) return LIPVQ_EWORKSPACE;
     // the rest of the workspace serves the encoder image + the search (checked against their own needs there)

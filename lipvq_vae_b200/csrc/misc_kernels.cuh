@@ -72,43 +72,6 @@ __global__ void partials_to_double_kernel(const float *__restrict__ part, int n,
 
 constexpr int kRedBlocks = 4 * kNumSMs;  // grid of the streaming passes (4 CTAs per SM)
 
-// z_q[n,:] = E[idx[n],:]; partial[b] = sum over the block's elements of (z_q - z_e)^2  (v5:47,80-81)
-template <bool VEC4>
-__global__ void __launch_bounds__(256) gather_loss_kernel(
-    const float *__restrict__ z_e, const float *__restrict__ E, const int64_t *__restrict__ idx,
-    int64_t n_rows, int D, float *__restrict__ z_q, float *__restrict__ partial) {
-    __shared__ float red[8];
-    float s = 0.f;
-    if (VEC4) {
-        const int dq = D >> 2;
-        const int64_t total = n_rows * dq;
-        for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
-             i += (int64_t)gridDim.x * blockDim.x) {
-            const int64_t n = i / dq;
-            const int c = (int)(i - n * dq);
-            const int64_t k = idx[n];
-            const float4 e = __ldg(reinterpret_cast<const float4 *>(E + k * D) + c);
-            const float4 z = __ldg(reinterpret_cast<const float4 *>(z_e + n * D) + c);
-            reinterpret_cast<float4 *>(z_q + n * D)[c] = e;
-            const float dx = e.x - z.x, dy = e.y - z.y, dz = e.z - z.z, dw = e.w - z.w;
-            s += dx * dx + dy * dy + dz * dz + dw * dw;
-        }
-    } else {
-        const int64_t total = n_rows * D;
-        for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
-             i += (int64_t)gridDim.x * blockDim.x) {
-            const int64_t n = i / D;
-            const int c = (int)(i - n * D);
-            const float e = __ldg(E + idx[n] * D + c);
-            const float d = e - __ldg(z_e + i);
-            z_q[i] = e;
-            s += d * d;
-        }
-    }
-    s = block_sum<256>(s, red);
-    if (threadIdx.x == 0) partial[blockIdx.x] = s;
-}
-
 // partial[b] = sum (a - b)^2 over a flat range
 __global__ void __launch_bounds__(256) sse_kernel(const float *__restrict__ a, const float *__restrict__ b,
                                                   int64_t n, float *__restrict__ partial) {
@@ -121,6 +84,101 @@ __global__ void __launch_bounds__(256) sse_kernel(const float *__restrict__ a, c
     }
     s = block_sum<256>(s, red);
     if (threadIdx.x == 0) partial[blockIdx.x] = s;
+}
+
+// ---------------------------------------------------------------- fused quantise + emit pass (k4/k5/k7)
+// One streaming pass over the rows (v5:47, 74-81): z_q[n] = E[idx[n]] (this is z_latent), sum (z_q-z_e)^2,
+// x_recon[n] = R[idx[n]] with R = decoder(E) the per-code reconstruction table, sum (x_recon-x)^2.
+// A CTA walks tiles of QE_ROWS rows: the tile's codes go to shared memory first, so the E / z_e loads of a
+// thread are independent (4 float4 pairs in flight); z_e / z_q are streamed past L1 (ld.cs / st.cs) while the
+// codebook and R stay cached.  partial: [2][gridDim.x] floats = {sse_q, sse_r} per CTA (summed in order later).
+constexpr int QE_ROWS = 64, QE_THR = 256;
+constexpr int kQeBlocks = 8 * kNumSMs;   // 8 resident CTAs of 256 threads per SM
+template <bool VEC4>
+__global__ void __launch_bounds__(QE_THR) quantize_emit_kernel(
+    const float *__restrict__ z_e, const float *__restrict__ E, const float *__restrict__ R,
+    const int64_t *__restrict__ idx, const float *__restrict__ x, int64_t n_rows, int D, int F, int K,
+    float *__restrict__ z_q, float *__restrict__ x_recon, float *__restrict__ partial) {
+    __shared__ int sidx[QE_ROWS];
+    __shared__ float red[8];
+    const int tid = threadIdx.x;
+    const unsigned dq = VEC4 ? (unsigned)D >> 2 : (unsigned)D;
+    const unsigned magic = (unsigned)((0x100000000ull + dq - 1) / dq);   // i / dq == umulhi(i, magic), i < 2^32/dq
+    const unsigned fmagic = (unsigned)((0x100000000ull + (unsigned)F - 1) / (unsigned)F);
+    float sq = 0.f, sr = 0.f;
+    const int64_t n_tiles = (n_rows + QE_ROWS - 1) / QE_ROWS;
+    for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        const int64_t r0 = tile * QE_ROWS;
+        const int rows = (int)(n_rows - r0 < QE_ROWS ? n_rows - r0 : QE_ROWS);
+        __syncthreads();
+        if (tid < rows) {
+            const int64_t k = idx[r0 + tid];
+            sidx[tid] = (k >= 0 && k < K) ? (int)k : 0;
+        }
+        __syncthreads();
+        const unsigned total = (unsigned)rows * dq;
+        if (VEC4) {
+            const float4 *zt = reinterpret_cast<const float4 *>(z_e + r0 * D);
+            float4 *qt = reinterpret_cast<float4 *>(z_q + r0 * D);
+            for (unsigned i0 = tid; i0 < total; i0 += 4 * QE_THR) {
+                float4 e[4], z[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    const unsigned i = i0 + u * QE_THR;
+                    if (i < total) {
+                        const unsigned r = __umulhi(i, magic), c = i - r * dq;
+                        e[u] = __ldg(reinterpret_cast<const float4 *>(E + (size_t)sidx[r] * D) + c);
+                        z[u] = __ldcs(zt + i);
+                    }
+                }
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    const unsigned i = i0 + u * QE_THR;
+                    if (i < total) {
+                        __stcs(qt + i, e[u]);
+                        const float dx = e[u].x - z[u].x, dy = e[u].y - z[u].y, dz = e[u].z - z[u].z,
+                                    dw = e[u].w - z[u].w;
+                        sq += dx * dx + dy * dy + dz * dz + dw * dw;
+                    }
+                }
+            }
+        } else {
+            for (unsigned i = tid; i < total; i += QE_THR) {
+                const unsigned r = __umulhi(i, magic), c = i - r * dq;
+                const float e = __ldg(E + (size_t)sidx[r] * D + c);
+                const float dd = e - __ldcs(z_e + r0 * D + i);
+                __stcs(z_q + r0 * D + i, e);
+                sq += dd * dd;
+            }
+        }
+        if (R) {
+            const unsigned tf = (unsigned)rows * (unsigned)F;
+            for (unsigned i = tid; i < tf; i += QE_THR) {
+                const unsigned r = __umulhi(i, fmagic), f = i - r * (unsigned)F;
+                const float v = __ldg(R + (size_t)sidx[r] * F + f);
+                if (x_recon) x_recon[r0 * F + i] = v;
+                if (x) { const float dd = v - __ldg(x + r0 * F + i); sr = fmaf(dd, dd, sr); }
+            }
+        }
+    }
+    sq = block_sum<QE_THR>(sq, red);
+    sr = block_sum<QE_THR>(sr, red);
+    if (tid == 0) { partial[blockIdx.x] = sq; partial[gridDim.x + blockIdx.x] = sr; }
+}
+
+// sse[0] = sum_i part[n + i] (recon), sse[1] = sum_i part[i] (quantisation); fixed order, double
+__global__ void partials2_to_double_kernel(const float *__restrict__ part, int n, double *__restrict__ sse) {
+    __shared__ double sm[2][8];
+    double a = 0.0, b = 0.0;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) { a += (double)part[i]; b += (double)part[n + i]; }
+    a = warp_sum_d(a); b = warp_sum_d(b);
+    if ((threadIdx.x & 31) == 0) { sm[0][threadIdx.x >> 5] = a; sm[1][threadIdx.x >> 5] = b; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double q = 0.0, r = 0.0;
+        for (int w = 0; w < (int)(blockDim.x >> 5); ++w) { q += sm[0][w]; r += sm[1][w]; }
+        sse[0] = r; sse[1] = q;
+    }
 }
 
 // out = alpha * (a - b)
@@ -162,17 +220,27 @@ __global__ void loss_finalize_kernel(const double *sse_r, const double *sse_q, d
 // and each warp then walks 32 sorted entries: runs of equal code are summed in registers and
 // flushed with ONE atomicAdd per (run, column) -- so a collapsed codebook (every row on one code,
 // SURVEY 0.9) costs gridDim atomics per address instead of n_rows.
+// DIFF = true accumulates alpha * gs * (T[code,:] - src[row,:]) instead of src[row,:] (T = a per-code table):
+// the codebook-loss gradient sum 0.5 (z_q - z_e)/(N D) with T = E, and the per-code reconstruction gradient
+// sum 2 (x_recon - x)/(N F) with T = decoder(E) -- neither difference tensor is ever materialised.
 constexpr int SC_ROWS = 256;
+template <bool DIFF>
 __global__ void __launch_bounds__(256) scatter_add_kernel(
     const float *__restrict__ src, const int64_t *__restrict__ idx, int64_t n_rows, int D, int K,
-    float *__restrict__ sums, float *__restrict__ counts) {
+    float *__restrict__ sums, float *__restrict__ counts, const float *__restrict__ T, float alpha,
+    const float *__restrict__ gs) {
+    if (DIFF && gs) alpha *= __ldg(gs);
     __shared__ unsigned long long keys[SC_ROWS];
     const int tid = threadIdx.x;
     const int64_t r0 = (int64_t)blockIdx.x * SC_ROWS;
     {
         const int64_t r = r0 + tid;
         unsigned long long key = ~0ull;   // padding sorts last
-        if (r < n_rows) key = ((unsigned long long)(unsigned)idx[r] << 32) | (unsigned)tid;
+        if (r < n_rows) {
+            int64_t k = idx[r];
+            if (k < 0 || k >= K) k = 0;
+            key = ((unsigned long long)(unsigned)k << 32) | (unsigned)tid;
+        }
         keys[tid] = key;
     }
     __syncthreads();
@@ -199,7 +267,7 @@ __global__ void __launch_bounds__(256) scatter_add_kernel(
         if (head) atomicAdd(counts + code, (float)__popc(m));
     }
     for (int c = lane; c < D; c += 32) {
-        float acc = 0.f;
+        float acc = 0.f, t = 0.f;
         unsigned cur = 0xffffffffu;
         for (int e = 0; e < 32; ++e) {
             const unsigned long long key = keys[e0 + e];
@@ -207,13 +275,15 @@ __global__ void __launch_bounds__(256) scatter_add_kernel(
             const unsigned code = (unsigned)(key >> 32);
             const int64_t row = r0 + (unsigned)(key & 0xffffffffu);
             if (code != cur) {
-                if (cur != 0xffffffffu) atomicAdd(sums + (size_t)cur * D + c, acc);
+                if (cur != 0xffffffffu) atomicAdd(sums + (size_t)cur * D + c, DIFF ? alpha * acc : acc);
                 cur = code;
                 acc = 0.f;
+                if (DIFF) t = __ldg(T + (size_t)code * D + c);
             }
-            acc += __ldg(src + row * D + c);
+            const float v = __ldg(src + row * D + c);
+            acc += DIFF ? t - v : v;
         }
-        if (cur != 0xffffffffu) atomicAdd(sums + (size_t)cur * D + c, acc);
+        if (cur != 0xffffffffu) atomicAdd(sums + (size_t)cur * D + c, DIFF ? alpha * acc : acc);
     }
 }
 

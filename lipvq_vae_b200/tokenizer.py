@@ -92,26 +92,29 @@ class _TokenizerFn(torch.autograd.Function):
         z_q = torch.empty(n, D, **f32)
         vq_stats = torch.zeros(4, dtype=torch.int32, device=dev)
         if n == 0:
-            ctx.mark_non_differentiable(z_q, idx)
+            x_recon = torch.empty(0, F_, **f32)
+            ctx.mark_non_differentiable(z_q, idx, vq_stats, x_recon)
             ctx.empty = True
-            return z_q, stats, idx, vq_stats
+            return z_q, stats, idx, vq_stats, x_recon
         ctx.empty = False
+        x_recon = torch.empty(n, F_, **f32)
         if not need_grad:
             N.check(lib.lipvq_forward_fused(C.byref(dims), C.byref(P), _p(x), n, n_total, search_mode, _p(z_q),
-                                            _p(idx), None, _p(stats), _p(vq_stats), _p(ws), ws.numel(), st),
+                                            _p(idx), _p(x_recon), _p(stats), _p(vq_stats), _p(ws), ws.numel(), st),
                     "lipvq_forward_fused")
-            ctx.mark_non_differentiable(z_q, idx, vq_stats)
-            return z_q, stats, idx, vq_stats
+            ctx.mark_non_differentiable(z_q, idx, vq_stats, x_recon)
+            return z_q, stats, idx, vq_stats, x_recon
         a1 = torch.empty(n, H1, **f32); h1 = torch.empty(n, H1, **f32)
         a2 = torch.empty(n, H, **f32); h2 = torch.empty(n, H, **f32)
         scale = torch.empty(D, **f32); Wn = torch.empty(D, H, **f32)
         z_e = torch.empty(n, D, **f32)
-        c1 = torch.empty(n, H1, **f32); d1 = torch.empty(n, H1, **f32)
-        c2 = torch.empty(n, H, **f32); d2 = torch.empty(n, H, **f32)
-        x_recon = torch.empty(n, F_, **f32)
+        # decoder activations are kept per CODE (z_q takes K distinct values), not per row
+        c1 = torch.empty(K, H1, **f32); d1 = torch.empty(K, H1, **f32)
+        c2 = torch.empty(K, H, **f32); d2 = torch.empty(K, H, **f32)
+        xr_code = torch.empty(K, F_, **f32)
         sse = torch.zeros(2, dtype=torch.float64, device=dev)
         A = _acts_struct(a1=a1, h1=h1, a2=a2, h2=h2, scale=scale, Wn=Wn, z_e=z_e, idx=idx, z_q=z_q,
-                         c1=c1, d1=d1, c2=c2, d2=d2, x_recon=x_recon)
+                         c1=c1, d1=d1, c2=c2, d2=d2, xr_code=xr_code, x_recon=x_recon)
         wsz = ws.numel()
         N.check(lib.lipvq_encode_search_fwd(C.byref(dims), C.byref(P), _p(x), n, C.byref(A), search_mode,
                                             _p(vq_stats), _p(ws), wsz, st), "lipvq_encode_search_fwd")
@@ -119,21 +122,21 @@ class _TokenizerFn(torch.autograd.Function):
                                               wsz, st), "lipvq_quantize_decode_fwd")
         N.check(lib.lipvq_loss_finalize(_p(sse), C.c_void_p(sse.data_ptr() + 8), n_total, F_, D, _p(stats), st),
                 "lipvq_loss_finalize")
-        ctx.save_for_backward(x, *params, a1, h1, a2, h2, scale, Wn, z_e, idx, z_q, c1, d1, c2, d2, x_recon)
+        ctx.save_for_backward(x, *params, a1, h1, a2, h2, scale, Wn, z_e, idx, z_q, c1, d1, c2, d2, xr_code)
         ctx.dims = dims
         ctx.n_total = n_total
-        ctx.mark_non_differentiable(z_q, idx, vq_stats)
-        return z_q, stats, idx, vq_stats
+        ctx.mark_non_differentiable(z_q, idx, vq_stats, x_recon)
+        return z_q, stats, idx, vq_stats, x_recon
 
     @staticmethod
-    def backward(ctx, g_zlat, g_stats, g_idx, g_vq):
+    def backward(ctx, g_zlat, g_stats, g_idx, g_vq, g_xr):
         none4 = (None, None, None, None)
         if ctx.empty or g_stats is None:
             return none4 + (None,) * 14
         lib = N.lib()
         saved = ctx.saved_tensors
         x, params = saved[0], saved[1:15]
-        a1, h1, a2, h2, scale, Wn, z_e, idx, z_q, c1, d1, c2, d2, x_recon = saved[15:]
+        a1, h1, a2, h2, scale, Wn, z_e, idx, z_q, c1, d1, c2, d2, xr_code = saved[15:]
         dims = ctx.dims
         dev = x.device
         n = x.shape[0]
@@ -144,15 +147,12 @@ class _TokenizerFn(torch.autograd.Function):
         # dL/dloss lives on the device; the kernels read it there (no host sync)
         gs = g_stats[0:1].contiguous().float()
         grads = [torch.empty_like(p) for p in params]
-        grads[7] = torch.zeros_like(params[7])
         P = _param_struct(N.Params, params)
         G = _param_struct(N.Grads, grads)
         A = _acts_struct(a1=a1, h1=h1, a2=a2, h2=h2, scale=scale, Wn=Wn, z_e=z_e, idx=idx, z_q=z_q,
-                         c1=c1, d1=d1, c2=c2, d2=d2, x_recon=x_recon)
-        g_zq = torch.empty_like(z_q)
+                         c1=c1, d1=d1, c2=c2, d2=d2, xr_code=xr_code)
         N.check(lib.lipvq_decoder_bwd(C.byref(dims), C.byref(P), _p(x), n, ctx.n_total, _p(gs), C.byref(A),
-                                      C.byref(G), _p(g_zq), _p(ws), wsz, st), "lipvq_decoder_bwd")
-        N.check(lib.lipvq_scatter_add(_p(g_zq), _p(idx), n, D, K, _p(grads[7]), None, st), "lipvq_scatter_add")
+                                      C.byref(G), _p(ws), wsz, st), "lipvq_decoder_bwd")
         N.check(lib.lipvq_encoder_bwd(C.byref(dims), C.byref(P), _p(x), n, ctx.n_total, _p(gs), C.byref(A),
                                       C.byref(G), _p(ws), wsz, st), "lipvq_encoder_bwd")
         out = [g if ctx.needs_input_grad[4 + i] else None for i, g in enumerate(grads)]
@@ -267,7 +267,8 @@ class LLFQVAE_V4(nn.Module):
     ``forward(x[N, feature_dim]) -> (z_latent[N, latent_dim] detached, loss 0-dim)`` exactly as
     consumed at robomimic/models/obs_nets.py:1335-1337.  Extra, reference-compatible surface:
     ``encode / quantize / decode`` (the submodule calls v5:71-76 spelled as methods),
-    ``last_indices``, ``last_loss_terms`` and ``last_search_stats`` (device tensors, no sync).
+    ``last_indices``, ``last_reconstruction``, ``last_loss_terms`` and ``last_search_stats`` (device tensors,
+    no sync).
 
     Knobs are attributes, not config keys (robomimic's config is locked, train.py:494-497):
       ``search_mode``  N.SEARCH_TENSOR (default) or N.SEARCH_EXACT
@@ -288,6 +289,7 @@ class LLFQVAE_V4(nn.Module):
         self.search_mode = N.SEARCH_TENSOR
         self.n_total_rows = None
         self.last_indices = None
+        self.last_reconstruction = None
         self.last_loss_terms = None
         self.last_search_stats = None
 
@@ -313,9 +315,10 @@ class LLFQVAE_V4(nn.Module):
         params = self._param_list()
         if not torch.is_grad_enabled():
             params = [p.detach() for p in params]
-        z_latent, stats, idx, vq_stats = _TokenizerFn.apply(
+        z_latent, stats, idx, vq_stats, x_recon = _TokenizerFn.apply(
             x.detach(), max(n_total, 1), int(self.search_mode), self._dims(), *params)
         self.last_indices = idx
+        self.last_reconstruction = x_recon          # decode(z_q) of this batch (v5:75-76), no graph
         self.last_loss_terms = stats.detach()
         self.last_search_stats = vq_stats
         return z_latent, stats[0]

@@ -67,6 +67,14 @@ def test_forward_backward_vs_reference_golden(case, mode):
         xr = m.decode(z_latent).cpu().numpy()
         assert orc.rel_err(xr[:32], g["x_recon_head"]) < RTOL
         assert abs(xr.astype(np.float64).sum() - g["x_recon_sum"]) < RTOL * g["x_recon_abs"]
+        # the forward's own reconstruction comes from the per-code table xr_code[idx]
+        for grad_on in (True, False):
+            with torch.set_grad_enabled(grad_on):
+                _, loss2 = m(xt)
+            xr2 = m.last_reconstruction.cpu().numpy()
+            assert orc.rel_err(xr2[:32], g["x_recon_head"]) < RTOL
+            assert abs(xr2.astype(np.float64).sum() - g["x_recon_sum"]) < RTOL * g["x_recon_abs"]
+            assert abs(loss2.item() - g["loss"]) < RTOL * abs(g["loss"])
         for k, t in m.named_parameters():
             v = t.grad.cpu().numpy()
             if "grad/" + k in g:
