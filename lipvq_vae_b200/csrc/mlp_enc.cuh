@@ -103,7 +103,9 @@ enc_fused_kernel(const float *__restrict__ x, const float *__restrict__ W0, cons
                  float *__restrict__ h1, float *__restrict__ a2, float *__restrict__ h2, float *__restrict__ z_e,
                  // optional fusion of the search's row-operand pass (vq_tensor.cuh pass 1): Zb/zn/flag outputs
                  const float *__restrict__ mu, tc::op_t *__restrict__ Zb, float *__restrict__ zn, int DKp,
-                 int *__restrict__ counters) {
+                 int *__restrict__ counters,
+                 // bulk tensor stores of z_e (fp32, box 8 x 32, 32-byte swizzle) and Zb (16-bit, box 16 x 32)
+                 const __grid_constant__ CUtensorMap tm_ze, const __grid_constant__ CUtensorMap tm_zb, int use_tma) {
     using L = EncSmem;
     extern __shared__ uint8_t smem_raw[];
     const uint32_t raw = ptx::smem_u32(smem_raw);
@@ -220,8 +222,9 @@ enc_fused_kernel(const float *__restrict__ x, const float *__restrict__ W0, cons
             }
         };
         fetch_x(blockIdx.x);
-        int t = 0;
+        int t = 0, slot_i = 0;
         bool zbad = false;
+        const bool keeps_acts = a1 || h1 || a2 || h2;   // their stores reuse the staging slots synchronously
 #ifdef ENC_PROFILE
         long long pc[8] = {0, 0, 0, 0, 0, 0, 0, 0}, pt = clock64();
 #define ENC_TICK(i) do { const long long _n = clock64(); pc[i] += _n - pt; pt = _n; } while (0)
@@ -232,6 +235,10 @@ enc_fused_kernel(const float *__restrict__ x, const float *__restrict__ W0, cons
             const uint32_t par = t & 1;
             const int64_t wrow0 = tile * TM + (r_in - lane);               // first row of this warp
             const int rows_valid = (int)max((int64_t)0, min((int64_t)32, n_rows - wrow0));
+            if (use_tma && keeps_acts) {   // the previous tile's bulk stores must have read the slots
+                if (lane == 0) ptx::bulk_wait_read<0>();
+                __syncwarp();
+            }
             // ---- x -> A operand (hi/lo)
             if (sub == 0) store_split16(tm + 256, tm + 320, xv);
             a_ready_arrive(bar_a(0));
@@ -241,7 +248,7 @@ enc_fused_kernel(const float *__restrict__ x, const float *__restrict__ W0, cons
             ptx::mbar_wait(bar_acc(0), par);
             ptx::tc_fence_after();
             ENC_TICK(1);
-            epilogue_blocks<ACT_GELU>(tm + 128, 0, H1 / 16, sub, 4, H1, sb0, true, tm + 352, tm + 416, wbuf,
+            epilogue_blocks<ACT_GELU_FAST>(tm + 128, 0, H1 / 16, sub, 4, H1, sb0, true, tm + 352, tm + 416, wbuf,
                                       a1 ? a1 + wrow0 * H1 : nullptr, h1 ? h1 + wrow0 * H1 : nullptr, H1, rows_valid,
                                       true);
             a_ready_arrive(bar_a(1));
@@ -250,7 +257,7 @@ enc_fused_kernel(const float *__restrict__ x, const float *__restrict__ W0, cons
             ptx::mbar_wait(bar_acc(1), par);
             ptx::tc_fence_after();
             ENC_TICK(3);
-            epilogue_blocks<ACT_GELU>(tm + 0, 0, HH / 16, sub, 4, HH, sb1, true, tm + 0, tm + 128, wbuf,
+            epilogue_blocks<ACT_GELU_FAST>(tm + 0, 0, HH / 16, sub, 4, HH, sb1, true, tm + 0, tm + 128, wbuf,
                                       a2 ? a2 + wrow0 * HH : nullptr, h2 ? h2 + wrow0 * HH : nullptr, HH, rows_valid,
                                       true);
             a_ready_arrive(bar_a(2));
@@ -259,9 +266,80 @@ enc_fused_kernel(const float *__restrict__ x, const float *__restrict__ W0, cons
             ptx::mbar_wait(bar_acc3(0), par);
             ptx::tc_fence_after();
             ENC_TICK(5);
-            if (Zb == nullptr) {
-                epilogue_blocks<ACT_SIGMOID>(tm + 256, 0, D16 / 16, sub, 4, D, sb2, false, 0u, 0u, wbuf, nullptr,
-                                             z_e + wrow0 * D, D, rows_valid, vec_d);
+            if (use_tma) {
+                // z_e (+ the search's row operand Zb = [fp16(z - mu) | 1 1 1], zn = ||z - mu||) leave through bulk
+                // tensor stores: a thread only writes its 16 columns into the warp's staging slots (two 1 KB
+                // slots in the 32-byte-swizzle pattern the tensor map expects); lane 0 issues the store.  A slot
+                // is rewritten once the store issued two stores ago has read it (wait_group.read 1).
+                float ss = 0.f;
+                const int nblk = Zb ? (D + 3 + 15) / 16 : D16 / 16;
+                const int sw = (lane >> 2) & 1;
+                auto slot_take = [&]() -> uint8_t * {
+                    if (lane == 0) ptx::bulk_wait_read<1>();
+                    __syncwarp();
+                    uint8_t *sl = wbuf + (slot_i & 1) * 1024;
+                    ++slot_i;
+                    return sl;
+                };
+                auto slot_send = [&](const CUtensorMap *tmap, uint8_t *sl, int c, int64_t row) {
+                    ptx::fence_proxy_async();
+                    __syncwarp();
+                    if (lane == 0) {
+                        ptx::tma_store_2d(tmap, ptx::smem_u32(sl), c, (int)row);
+                        ptx::bulk_commit();
+                    }
+                };
+                for (int cb = sub; cb < nblk; cb += 4) {
+                    const int c0 = cb << 4;
+                    float v[16];
+                    if (c0 < D16) {
+                        uint32_t r[16];
+                        ptx::tmem_ld_32x32b_x16(tm + 256 + c0, r);
+                        ptx::tmem_ld_wait();
+#pragma unroll
+                        for (int i = 0; i < 16; ++i) v[i] = sigmoid_fast_f(__uint_as_float(r[i]) + sb2[c0 + i]);
+#pragma unroll
+                        for (int hf = 0; hf < 2; ++hf) {
+                            if (c0 + 8 * hf >= D) break;
+                            uint8_t *sl = slot_take();
+                            *reinterpret_cast<float4 *>(sl + lane * 32 + ((0 ^ sw) << 4)) =
+                                make_float4(v[8 * hf], v[8 * hf + 1], v[8 * hf + 2], v[8 * hf + 3]);
+                            *reinterpret_cast<float4 *>(sl + lane * 32 + ((1 ^ sw) << 4)) =
+                                make_float4(v[8 * hf + 4], v[8 * hf + 5], v[8 * hf + 6], v[8 * hf + 7]);
+                            slot_send(&tm_ze, sl, c0 + 8 * hf, wrow0);
+                        }
+                    }
+                    if (Zb) {
+#pragma unroll
+                        for (int i = 0; i < 16; ++i) {
+                            const int d = c0 + i;
+                            if (d < D) {
+                                v[i] -= smu[d];
+                                ss = fmaf(v[i], v[i], ss);
+                            } else {
+                                v[i] = d < D + 3 ? 1.0f : 0.f;
+                            }
+                        }
+                        __align__(16) tc::op2_t o[8];
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) o[i] = tc::f2op2(v[2 * i], v[2 * i + 1]);
+                        uint8_t *sl = slot_take();
+                        *reinterpret_cast<uint4 *>(sl + lane * 32 + ((0 ^ sw) << 4)) = reinterpret_cast<const uint4 *>(o)[0];
+                        *reinterpret_cast<uint4 *>(sl + lane * 32 + ((1 ^ sw) << 4)) = reinterpret_cast<const uint4 *>(o)[1];
+                        slot_send(&tm_zb, sl, c0, wrow0);
+                    }
+                }
+                if (Zb) {
+                    // any |z - mu| beyond the 16-bit operand range (or a NaN) makes the partial norm fail this test
+                    zbad |= !(ss <= tc::OP_MAX * tc::OP_MAX);
+                    sznp[sub * TM + r_in] = ss;
+                    asm volatile("bar.sync 1, 512;" ::: "memory");
+                    if (sub == 0 && lane < rows_valid)
+                        zn[wrow0 + lane] = sqrtf(((sznp[r_in] + sznp[TM + r_in]) + sznp[2 * TM + r_in]) + sznp[3 * TM + r_in]);
+                }
+            } else if (Zb == nullptr) {
+                epilogue_blocks<ACT_SIGMOID_FAST>(tm + 256, 0, D16 / 16, sub, 4, D, sb2, false, 0u, 0u, wbuf, nullptr,
+                                                  z_e + wrow0 * D, D, rows_valid, vec_d);
             } else {
                 // z_e plus the search's row operand: Zb = [fp16(z - mu) | 1 1 1 | 0...], zn = ||z - mu||
                 float ss = 0.f;
@@ -273,7 +351,7 @@ enc_fused_kernel(const float *__restrict__ x, const float *__restrict__ W0, cons
                         ptx::tmem_ld_32x32b_x16(tm + 256 + c0, r);
                         ptx::tmem_ld_wait();
 #pragma unroll
-                        for (int i = 0; i < 16; ++i) v[i] = sigmoid_f(__uint_as_float(r[i]) + sb2[c0 + i]);
+                        for (int i = 0; i < 16; ++i) v[i] = sigmoid_fast_f(__uint_as_float(r[i]) + sb2[c0 + i]);
                         warp_store16(wbuf, z_e + wrow0 * D + c0, D, v, rows_valid, min(16, D - c0), vec_d);
                     }
 #pragma unroll
@@ -317,6 +395,7 @@ enc_fused_kernel(const float *__restrict__ x, const float *__restrict__ W0, cons
             ENC_TICK(6);
         }
         if (zbad) atomicOr(counters + 3, 1);   // operand out of fp16 range -> the search goes exact for this launch
+        if (use_tma && lane == 0) ptx::bulk_wait<0>();   // every bulk store has landed before the CTA retires
 #ifdef ENC_PROFILE
         if (blockIdx.x == 3 && (threadIdx.x & 31) == 0 && (threadIdx.x >> 5) < 8)
             printf("w%d tiles %d cyc/tile: xstage %lld | wait0 %lld epi0 %lld | wait1 %lld epi1 %lld | wait2 %lld epi2 %lld\n",
@@ -331,6 +410,21 @@ enc_fused_kernel(const float *__restrict__ x, const float *__restrict__ W0, cons
 inline size_t enc_img_bytes(int D) { return (size_t)ENC_NC * pad16(D) * 256; }
 
 // img: enc_img_bytes(D) of 1024-byte aligned scratch.  mu/Zb/zn/counters: optional search-operand fusion.
+// row-major [rows, cols] tensor of `esize`-byte elements, box = {32 bytes of columns, 32 rows}, 32-byte swizzle
+inline int make_store_tmap(CUtensorMap *m, const void *ptr, CUtensorMapDataType dt, int esize, uint64_t rows,
+                           uint64_t cols, uint64_t pitch_elems) {
+    tc::EncodeTiledFn fn = tc::encode_fn();
+    if (!fn) return LIPVQ_ECUDA;
+    cuuint64_t dims[2] = {cols, rows};
+    cuuint64_t strides[1] = {pitch_elems * (uint64_t)esize};
+    cuuint32_t box[2] = {(cuuint32_t)(32 / esize), 32};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = fn(m, dt, 2, const_cast<void *>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                    CU_TENSOR_MAP_SWIZZLE_32B, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    return r == CUDA_SUCCESS ? LIPVQ_OK : LIPVQ_ECUDA;
+}
+
+// img: enc_img_bytes(D) of 1024-byte aligned scratch.  mu/Zb/zn/counters: optional search-operand fusion.
 inline int encoder_fused_launch(const lipvq_dims_t *d, const lipvq_params_t *p, const float *x, int64_t n, float *a1,
                                 float *h1, float *a2, float *h2, const float *Wn, float *z_e, uint8_t *img,
                                 const float *mu, tc::op_t *Zb, float *zn, int DKp, int *counters, cudaStream_t st) {
@@ -338,9 +432,28 @@ inline int encoder_fused_launch(const lipvq_dims_t *d, const lipvq_params_t *p, 
     enc_wn_image_kernel<<<(D16 * 32 + 255) / 256, 256, 0, st>>>(Wn, d->D, D16, img);
     LIPVQ_LAUNCH_OK();
     LIPVQ_TRY(set_smem(enc_fused_kernel, EncSmem::TOTAL));
+    // bulk tensor stores need 16-byte row pitches and 32-bit row coordinates; otherwise the per-thread path
+    static const bool no_tma = [] { const char *e = getenv("LIPVQ_ENC_TMA"); return e && !strcmp(e, "0"); }();
+    CUtensorMap tm_ze, tm_zb;
+    memset(&tm_ze, 0, sizeof(tm_ze));
+    memset(&tm_zb, 0, sizeof(tm_zb));
+    int use_tma = !no_tma && (d->D & 3) == 0 && n < (int64_t)0x7fffffff - TM && (!Zb || (DKp & 7) == 0);
+    if (use_tma) {
+        LIPVQ_TRY(make_store_tmap(&tm_ze, z_e, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, (uint64_t)n, (uint64_t)d->D,
+                                  (uint64_t)d->D));
+        if (Zb) {
+#ifdef LIPVQ_VQ_BF16
+            const CUtensorMapDataType dt = CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+#else
+            const CUtensorMapDataType dt = CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
+#endif
+            const uint64_t np = (uint64_t)((n + TM - 1) / TM * TM);
+            LIPVQ_TRY(make_store_tmap(&tm_zb, Zb, dt, 2, np, (uint64_t)DKp, (uint64_t)DKp));
+        }
+    }
     enc_fused_kernel<<<grid_for(n), ENC_THR, EncSmem::TOTAL, st>>>(x, p->enc0_w, p->enc0_b, p->enc2_w, p->enc2_b, img,
                                                                    p->lat_b, n, d->F, d->D, a1, h1, a2, h2, z_e, mu, Zb,
-                                                                   zn, DKp, counters);
+                                                                   zn, DKp, counters, tm_ze, tm_zb, use_tma);
     LIPVQ_LAUNCH_OK();
     return LIPVQ_OK;
 }

@@ -39,5 +39,11 @@ def timeit(fn, iters=10):
 
 enc = lambda: N.check(lib.lipvq_encoder_fwd(C.byref(dims), C.byref(P), _p(x), n, C.byref(A), _p(ws), ws.numel(), st))
 dec = lambda: N.check(lib.lipvq_quantize_decode_fwd(C.byref(dims), C.byref(P), _p(x), n, C.byref(A), _p(sse), _p(ws), ws.numel(), st))
+vqs = torch.zeros(4, dtype=torch.int32, device=dev)
+A2 = _acts_struct(scale=scale, Wn=Wn, z_e=z_e, idx=idx, z_q=z_q, x_recon=xr)
+es = lambda: N.check(lib.lipvq_encode_search_fwd(C.byref(dims), C.byref(P), _p(x), n, C.byref(A2), 1, _p(vqs), _p(ws), ws.numel(), st))
+if os.environ.get("ENC_PROBE_ONCE"):
+    es(); torch.cuda.synchronize(); sys.exit(0)
+print("encode_search_fwd %.1f us" % (1e3 * timeit(es)))
 print("encoder_fwd %.1f us   quantize_decode_fwd %.1f us   (n=%d D=%d K=%d, extra=%r)"
       % (1e3 * timeit(enc), 1e3 * timeit(dec), n, D, K, os.environ.get("LIPVQ_NVCC_EXTRA", "")))
