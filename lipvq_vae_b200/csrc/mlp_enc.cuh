@@ -35,7 +35,7 @@ struct EncSmem {
     static constexpr int MU = BIAS + (H1 + HH + 256) * 4;          // codebook mean mu[<=256+16] (search operand fusion)
     static constexpr int ZNP = MU + 272 * 4;                       // [4 subs][128 rows] partial row norms
     static constexpr int BAR = ZNP + 4 * TM * 4;                   // mbarriers (8 B each), then the TMEM slot
-    static constexpr int NBAR = 3 + 2 + ENC_NCMAX + 4;             // a_ready[3] acc_ready[2] acc3[NC] w_full[2] w_empty[2]
+    static constexpr int NBAR = 3 + 2 + ENC_NCMAX + 4 + ENC_NC;    // a_ready[3] acc_ready[2] acc3[NC] w_full[2] w_empty[2] a2_ready[4]
     static constexpr int TOTAL = BAR + NBAR * 8 + 16 + 1024;
 };
 
@@ -64,10 +64,12 @@ __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void *src, uint32_t
                  : "memory");
 }
 // epilogue thread: my part of an A operand is in TMEM -> tell the control thread
+// (one arrival per WARP: 512 threads arriving on one mbarrier serialise on its shared-memory word)
 __device__ __forceinline__ void a_ready_arrive(uint32_t bar) {
     ptx::tmem_st_wait();
     ptx::tc_fence_before();
-    ptx::mbar_arrive(bar);
+    __syncwarp();
+    if ((threadIdx.x & 31) == 0) ptx::mbar_arrive(bar);
 }
 
 // Epilogue over the 16-column blocks cb in [cb0, cb1) with cb % nsub == sub, for this thread's row:
@@ -86,7 +88,11 @@ __device__ __forceinline__ void epilogue_blocks(uint32_t t_acc, int cb0, int cb1
         ptx::tmem_ld_wait();
         float v[16];
 #pragma unroll
-        for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]) + sbias[c0 + i];
+        for (int i = 0; i < 4; ++i) {
+            const float4 bq = *reinterpret_cast<const float4 *>(sbias + c0 + 4 * i);
+            v[4 * i] = __uint_as_float(r[4 * i]) + bq.x; v[4 * i + 1] = __uint_as_float(r[4 * i + 1]) + bq.y;
+            v[4 * i + 2] = __uint_as_float(r[4 * i + 2]) + bq.z; v[4 * i + 3] = __uint_as_float(r[4 * i + 3]) + bq.w;
+        }
         const int valid = min(16, n_real - c0);
         if (pre) warp_store16(wbuf, pre + c0, ld, v, rows_valid, valid, vec);
 #pragma unroll
@@ -113,11 +119,14 @@ enc_fused_kernel(const float *__restrict__ x, const float *__restrict__ W0, cons
     const uint32_t s0 = ptx::smem_u32(sm);
     float *sb0 = reinterpret_cast<float *>(sm + L::BIAS), *sb1 = sb0 + H1, *sb2 = sb1 + HH;
     const uint32_t bars = s0 + L::BAR;
-    auto bar_a = [&](int l) { return bars + 8u * l; };               // A operand of layer l ready (512 arrivals)
+    auto bar_a = [&](int l) { return bars + 8u * l; };               // A operand of layer l ready (16 warp arrivals)
     auto bar_acc = [&](int l) { return bars + 8u * (3 + l); };       // accumulator of layer 0/1 ready
     auto bar_acc3 = [&](int c) { return bars + 8u * (5 + c); };      // chunk c of layer 2 ready
     auto bar_wfull = [&](int s) { return bars + 8u * (5 + ENC_NCMAX + s); };
     auto bar_wempty = [&](int s) { return bars + 8u * (7 + ENC_NCMAX + s); };
+    // h2 columns [32c, 32c+32) (K block c of layer 2) ready: 2 column owners x 4 lane quarters = 8 warp arrivals, so
+    // the layer-2 MMAs of the first K blocks run while the layer-1 epilogue is still producing the later ones
+    auto bar_a2 = [&](int c) { return bars + 8u * (9 + ENC_NCMAX + c); };
     volatile uint32_t *tmem_slot = reinterpret_cast<volatile uint32_t *>(sm + L::BAR + L::NBAR * 8);
 
     const int D16 = pad16(D), NC = ENC_NC;
@@ -130,10 +139,12 @@ enc_fused_kernel(const float *__restrict__ x, const float *__restrict__ W0, cons
     for (int i = threadIdx.x; i < 272; i += ENC_THR) smu[i] = (Zb && i < D) ? mu[i] : 0.f;
     ptx::fence_proxy_async();
     if (threadIdx.x == 0) {
-        for (int l = 0; l < 3; ++l) ptx::mbar_init(bar_a(l), ENC_EPI);
+        for (int l = 0; l < 2; ++l) ptx::mbar_init(bar_a(l), ENC_EPI / 32);
+        ptx::mbar_init(bar_a(2), 1);   // (unused: layer 2 is released per K block, bar_a2)
         for (int l = 0; l < 2; ++l) ptx::mbar_init(bar_acc(l), 1);
         for (int c = 0; c < ENC_NCMAX; ++c) ptx::mbar_init(bar_acc3(c), 1);
         for (int s = 0; s < 2; ++s) { ptx::mbar_init(bar_wfull(s), 1); ptx::mbar_init(bar_wempty(s), 1); }
+        for (int c = 0; c < ENC_NC; ++c) ptx::mbar_init(bar_a2(c), 8);
         ptx::fence_barrier_init();
     }
     if ((threadIdx.x >> 5) == 0) ptx::tmem_alloc<512>(ptx::smem_u32((const void *)tmem_slot));
@@ -170,11 +181,10 @@ enc_fused_kernel(const float *__restrict__ x, const float *__restrict__ W0, cons
                 ptx::tc_fence_after();
                 issue_layer(tmem0 + 0, tmem0 + 352, tmem0 + 416, s0 + L::W1, s0 + L::W1 + L::W1_IMG, HH, H1 / 8,
                             bar_acc(1));
-                ptx::mbar_wait(bar_a(2), par);
-                ptx::tc_fence_after();
                 const uint32_t idesc = ptx::umma_idesc_tf32(TM, D16);
                 for (int c = 0; c < NC; ++c) {      // K block c of Wn against h2 columns [32c, 32c+32)
                     const int g = t * NC + c, s = g & 1;
+                    ptx::mbar_wait(bar_a2(c), par);
                     ptx::mbar_wait(bar_wfull(s), (g >> 1) & 1);
                     ptx::tc_fence_after();
                     const uint32_t st = s0 + L::RING + s * ENC_STAGE_BYTES;
@@ -225,6 +235,8 @@ enc_fused_kernel(const float *__restrict__ x, const float *__restrict__ W0, cons
         int t = 0, slot_i = 0;
         bool zbad = false;
         const bool keeps_acts = a1 || h1 || a2 || h2;   // their stores reuse the staging slots synchronously
+        int64_t zn_row0 = 0;
+        int zn_rows = -1;                               // pending row-norm combine of the previous tile
 #ifdef ENC_PROFILE
         long long pc[8] = {0, 0, 0, 0, 0, 0, 0, 0}, pt = clock64();
 #define ENC_TICK(i) do { const long long _n = clock64(); pc[i] += _n - pt; pt = _n; } while (0)
@@ -247,6 +259,11 @@ enc_fused_kernel(const float *__restrict__ x, const float *__restrict__ W0, cons
             // ---- layer 0 epilogue: h1
             ptx::mbar_wait(bar_acc(0), par);
             ptx::tc_fence_after();
+            if (zn_rows >= 0) {
+                if (sub == 0 && lane < zn_rows)
+                    zn[zn_row0 + lane] = sqrtf(((sznp[r_in] + sznp[TM + r_in]) + sznp[2 * TM + r_in]) + sznp[3 * TM + r_in]);
+                zn_rows = -1;
+            }
             ENC_TICK(1);
             epilogue_blocks<ACT_GELU_FAST>(tm + 128, 0, H1 / 16, sub, 4, H1, sb0, true, tm + 352, tm + 416, wbuf,
                                       a1 ? a1 + wrow0 * H1 : nullptr, h1 ? h1 + wrow0 * H1 : nullptr, H1, rows_valid,
@@ -257,10 +274,12 @@ enc_fused_kernel(const float *__restrict__ x, const float *__restrict__ W0, cons
             ptx::mbar_wait(bar_acc(1), par);
             ptx::tc_fence_after();
             ENC_TICK(3);
-            epilogue_blocks<ACT_GELU_FAST>(tm + 0, 0, HH / 16, sub, 4, HH, sb1, true, tm + 0, tm + 128, wbuf,
-                                      a2 ? a2 + wrow0 * HH : nullptr, h2 ? h2 + wrow0 * HH : nullptr, HH, rows_valid,
-                                      true);
-            a_ready_arrive(bar_a(2));
+            for (int cb = sub; cb < HH / 16; cb += 4) {
+                epilogue_blocks<ACT_GELU_FAST>(tm + 0, cb, cb + 1, sub, 4, HH, sb1, true, tm + 0, tm + 128, wbuf,
+                                               a2 ? a2 + wrow0 * HH : nullptr, h2 ? h2 + wrow0 * HH : nullptr, HH,
+                                               rows_valid, true);
+                a_ready_arrive(bar_a2(cb >> 1));
+            }
             ENC_TICK(4);
             // ---- layer 2 epilogue: sigmoid and store z_e
             ptx::mbar_wait(bar_acc3(0), par);
@@ -281,11 +300,15 @@ enc_fused_kernel(const float *__restrict__ x, const float *__restrict__ W0, cons
                     ++slot_i;
                     return sl;
                 };
+                const uint32_t wbuf_s = ptx::smem_u32(wbuf);
                 auto slot_send = [&](const CUtensorMap *tmap, uint8_t *sl, int c, int64_t row) {
                     ptx::fence_proxy_async();
                     __syncwarp();
+#ifdef ENC_EXP_SKIP
+                    if (tmap == &tm_ze ? (ENC_EXP_SKIP & 1) : (ENC_EXP_SKIP & 2)) return;
+#endif
                     if (lane == 0) {
-                        ptx::tma_store_2d(tmap, ptx::smem_u32(sl), c, (int)row);
+                        ptx::tma_store_2d(tmap, wbuf_s + (uint32_t)(sl - wbuf), c, (int)row);
                         ptx::bulk_commit();
                     }
                 };
@@ -297,7 +320,13 @@ enc_fused_kernel(const float *__restrict__ x, const float *__restrict__ W0, cons
                         ptx::tmem_ld_32x32b_x16(tm + 256 + c0, r);
                         ptx::tmem_ld_wait();
 #pragma unroll
-                        for (int i = 0; i < 16; ++i) v[i] = sigmoid_fast_f(__uint_as_float(r[i]) + sb2[c0 + i]);
+                        for (int i = 0; i < 4; ++i) {
+                            const float4 bq = *reinterpret_cast<const float4 *>(sb2 + c0 + 4 * i);
+                            v[4 * i] = sigmoid_fast_f(__uint_as_float(r[4 * i]) + bq.x);
+                            v[4 * i + 1] = sigmoid_fast_f(__uint_as_float(r[4 * i + 1]) + bq.y);
+                            v[4 * i + 2] = sigmoid_fast_f(__uint_as_float(r[4 * i + 2]) + bq.z);
+                            v[4 * i + 3] = sigmoid_fast_f(__uint_as_float(r[4 * i + 3]) + bq.w);
+                        }
 #pragma unroll
                         for (int hf = 0; hf < 2; ++hf) {
                             if (c0 + 8 * hf >= D) break;
@@ -310,32 +339,47 @@ enc_fused_kernel(const float *__restrict__ x, const float *__restrict__ W0, cons
                         }
                     }
                     if (Zb) {
+                        if (c0 + 16 <= D) {           // full block: no per-element bounds
 #pragma unroll
-                        for (int i = 0; i < 16; ++i) {
-                            const int d = c0 + i;
-                            if (d < D) {
-                                v[i] -= smu[d];
-                                ss = fmaf(v[i], v[i], ss);
-                            } else {
-                                v[i] = d < D + 3 ? 1.0f : 0.f;
+                            for (int i = 0; i < 4; ++i) {
+                                const float4 mq = *reinterpret_cast<const float4 *>(smu + c0 + 4 * i);
+                                v[4 * i] -= mq.x; v[4 * i + 1] -= mq.y; v[4 * i + 2] -= mq.z; v[4 * i + 3] -= mq.w;
+                            }
+#pragma unroll
+                            for (int i = 0; i < 16; ++i) ss = fmaf(v[i], v[i], ss);
+                        } else {
+#pragma unroll
+                            for (int i = 0; i < 16; ++i) {
+                                const int d = c0 + i;
+                                if (d < D) {
+                                    v[i] -= smu[d];
+                                    ss = fmaf(v[i], v[i], ss);
+                                } else {
+                                    v[i] = d < D + 3 ? 1.0f : 0.f;
+                                }
                             }
                         }
-                        __align__(16) tc::op2_t o[8];
+                        uint32_t o[8];
 #pragma unroll
-                        for (int i = 0; i < 8; ++i) o[i] = tc::f2op2(v[2 * i], v[2 * i + 1]);
+                        for (int i = 0; i < 8; ++i) {
+                            const tc::op2_t pr = tc::f2op2(v[2 * i], v[2 * i + 1]);
+                            o[i] = *reinterpret_cast<const uint32_t *>(&pr);
+                        }
                         uint8_t *sl = slot_take();
-                        *reinterpret_cast<uint4 *>(sl + lane * 32 + ((0 ^ sw) << 4)) = reinterpret_cast<const uint4 *>(o)[0];
-                        *reinterpret_cast<uint4 *>(sl + lane * 32 + ((1 ^ sw) << 4)) = reinterpret_cast<const uint4 *>(o)[1];
+                        *reinterpret_cast<uint4 *>(sl + lane * 32 + ((0 ^ sw) << 4)) = make_uint4(o[0], o[1], o[2], o[3]);
+                        *reinterpret_cast<uint4 *>(sl + lane * 32 + ((1 ^ sw) << 4)) = make_uint4(o[4], o[5], o[6], o[7]);
                         slot_send(&tm_zb, sl, c0, wrow0);
                     }
                 }
                 if (Zb) {
                     // any |z - mu| beyond the 16-bit operand range (or a NaN) makes the partial norm fail this test
                     zbad |= !(ss <= tc::OP_MAX * tc::OP_MAX);
+                    // the four column owners of a row leave their partial norms in shared memory; they are combined
+                    // (fixed order) after the NEXT tile's first accumulator wait, which every thread of this tile
+                    // has passed its epilogue to reach -- no extra barrier
                     sznp[sub * TM + r_in] = ss;
-                    asm volatile("bar.sync 1, 512;" ::: "memory");
-                    if (sub == 0 && lane < rows_valid)
-                        zn[wrow0 + lane] = sqrtf(((sznp[r_in] + sznp[TM + r_in]) + sznp[2 * TM + r_in]) + sznp[3 * TM + r_in]);
+                    zn_row0 = wrow0;
+                    zn_rows = rows_valid;
                 }
             } else if (Zb == nullptr) {
                 epilogue_blocks<ACT_SIGMOID_FAST>(tm + 256, 0, D16 / 16, sub, 4, D, sb2, false, 0u, 0u, wbuf, nullptr,
@@ -393,6 +437,11 @@ enc_fused_kernel(const float *__restrict__ x, const float *__restrict__ W0, cons
                     zn[wrow0 + lane] = sqrtf(((sznp[r_in] + sznp[TM + r_in]) + sznp[2 * TM + r_in]) + sznp[3 * TM + r_in]);
             }
             ENC_TICK(6);
+        }
+        if (use_tma && Zb) {                   // row norms of the last tile
+            asm volatile("bar.sync 1, 512;" ::: "memory");
+            if (zn_rows >= 0 && sub == 0 && lane < zn_rows)
+                zn[zn_row0 + lane] = sqrtf(((sznp[r_in] + sznp[TM + r_in]) + sznp[2 * TM + r_in]) + sznp[3 * TM + r_in]);
         }
         if (zbad) atomicOr(counters + 3, 1);   // operand out of fp16 range -> the search goes exact for this launch
         if (use_tma && lane == 0) ptx::bulk_wait<0>();   // every bulk store has landed before the CTA retires
