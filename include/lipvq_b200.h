@@ -97,6 +97,13 @@ int lipvq_check_device(void);
 /* number of kernels this library has launched in this process (bench.py's gpu_launches) */
 int64_t lipvq_launch_count(void);
 
+/* Per-kernel timing for measurement (bench.py's roofline): between begin and end every kernel launch of this
+ * library is bracketed by CUDA events on its launching stream.  end() synchronises those events, writes one
+ * line per kernel name, "name count total_ms\n", into report (NUL-terminated, truncated to cap) and frees
+ * the events.  Not re-entrant; off by default. */
+int lipvq_profile_begin(int32_t max_records);
+int lipvq_profile_end(char *report, size_t cap);
+
 /* scratch bytes needed by any call below for n_rows rows with these dims */
 int lipvq_workspace_bytes(const lipvq_dims_t *dims, int64_t n_rows, size_t *out_bytes);
 

@@ -7,6 +7,7 @@ behind the C ABI in include/lipvq_b200.h.  No CPU path, no torch fallback.
 from ._native import (LipVQNativeError, SEARCH_EXACT, SEARCH_TENSOR, build_native, lib as native_lib,
                       LIB_PATH)
 from .tokenizer import LLFQVAE_V4, LFQQuantizer, LipschitzMLP, install_into_robomimic
+from .stream import HostTokenizer
 
-__all__ = ["LLFQVAE_V4", "LFQQuantizer", "LipschitzMLP", "install_into_robomimic", "LipVQNativeError",
+__all__ = ["LLFQVAE_V4", "LFQQuantizer", "LipschitzMLP", "install_into_robomimic", "HostTokenizer", "LipVQNativeError",
            "SEARCH_EXACT", "SEARCH_TENSOR", "build_native", "native_lib", "LIB_PATH"]

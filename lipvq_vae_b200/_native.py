@@ -106,6 +106,8 @@ SIGNATURES = {
     "lipvq_last_cuda_error_string": (C.c_char_p, []),
     "lipvq_check_device": (C.c_int, []),
     "lipvq_launch_count": (C.c_int64, []),
+    "lipvq_profile_begin": (C.c_int, [_I32]),
+    "lipvq_profile_end": (C.c_int, [C.c_char_p, _SZ]),
     "lipvq_workspace_bytes": (C.c_int, [_DP, _I64, C.POINTER(_SZ)]),
     "lipvq_encoder_fwd": (C.c_int, [_DP, _PP, _VP, _I64, _AP, _VP, _SZ, _VP]),
     "lipvq_linear_fwd": (C.c_int, [_VP, _VP, _VP, _VP, _I64, _I32, _I32, _I32, _VP]),
@@ -153,3 +155,21 @@ def check(code: int, what: str = "") -> None:
         if code == -5:
             msg += ": " + h.lipvq_last_cuda_error_string().decode()
         raise LipVQNativeError("%s failed (%d): %s" % (what or "lipvq call", code, msg))
+
+
+def profile_kernels(fn, iters):
+    """Run ``fn(i)`` ``iters`` times with the library's per-kernel CUDA-event timing on; returns
+    ``{kernel name: (launches, total_ms)}``."""
+    h = lib()
+    check(h.lipvq_profile_begin(64 * max(iters, 1) + 64), "lipvq_profile_begin")
+    try:
+        for i in range(iters):
+            fn(i)
+    finally:
+        buf = C.create_string_buffer(1 << 14)
+        check(h.lipvq_profile_end(buf, len(buf)), "lipvq_profile_end")
+    out = {}
+    for line in buf.value.decode().splitlines():
+        name, count, ms = line.rsplit(" ", 2)
+        out[name] = (int(count), float(ms))
+    return out

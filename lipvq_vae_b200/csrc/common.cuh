@@ -35,6 +35,18 @@ extern long long g_launch_count;   // kernels launched by this library (bench.py
         if (_r != LIPVQ_OK) return _r; \
     } while (0)
 
+// ---- optional per-kernel timing (lipvq_profile_begin / lipvq_profile_end): CUDA events recorded on the
+// launching stream right before and after a kernel launch, so bench.py reads every kernel's duration inside
+// the real step.  Off by default (one relaxed load per launch site).
+extern int g_prof_on;
+int prof_open(const char *name, cudaStream_t st);   // -> record index or -1
+void prof_close(int rec, cudaStream_t st);
+struct ProfScope {
+    int rec; cudaStream_t st;
+    ProfScope(const char *name, cudaStream_t s) : rec(g_prof_on ? prof_open(name, s) : -1), st(s) {}
+    ~ProfScope() { if (rec >= 0) prof_close(rec, st); }
+};
+
 constexpr int kNumSMs = 148;  // B200: 2 dies x 74 SMs
 
 // *_FAST: the per-row epilogues of the fused encoder (error at the fp32 rounding floor, see gelu_fast_f)

@@ -16,6 +16,22 @@ namespace lipvq {
 thread_local cudaError_t g_last_cuda_error = cudaSuccess;
 long long g_launch_count = 0;
 
+// ---- per-kernel event timing
+int g_prof_on = 0;
+namespace {
+struct ProfRec { const char *name; cudaEvent_t beg, end; };
+ProfRec *g_prof = nullptr;
+int g_prof_cap = 0, g_prof_n = 0;
+}  // namespace
+int prof_open(const char *name, cudaStream_t st) {
+    const int i = __atomic_fetch_add(&g_prof_n, 1, __ATOMIC_RELAXED);
+    if (i >= g_prof_cap) return -1;
+    g_prof[i].name = name;
+    cudaEventRecord(g_prof[i].beg, st);
+    return i;
+}
+void prof_close(int rec, cudaStream_t st) { cudaEventRecord(g_prof[rec].end, st); }
+
 struct Bump {
     char *base; size_t off, cap;
     Bump(void *p, size_t c) : base((char *)p), off(0), cap(c) {}
@@ -101,6 +117,51 @@ int lipvq_check_device(void) {
     LIPVQ_CUDA_OK(cudaGetDevice(&dev));
     LIPVQ_CUDA_OK(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev));
     return major == 10 ? LIPVQ_OK : LIPVQ_EARCH;
+}
+
+int lipvq_profile_begin(int32_t max_records) {
+    if (max_records < 1 || max_records > (1 << 20)) return LIPVQ_ESHAPE;
+    if (g_prof) return LIPVQ_ESHAPE;   // already profiling
+    g_prof = (ProfRec *)calloc((size_t)max_records, sizeof(ProfRec));
+    if (!g_prof) return LIPVQ_EWORKSPACE;
+    for (int i = 0; i < max_records; ++i) {
+        LIPVQ_CUDA_OK(cudaEventCreate(&g_prof[i].beg));
+        LIPVQ_CUDA_OK(cudaEventCreate(&g_prof[i].end));
+    }
+    g_prof_cap = max_records;
+    g_prof_n = 0;
+    __atomic_store_n(&g_prof_on, 1, __ATOMIC_RELEASE);
+    return LIPVQ_OK;
+}
+
+int lipvq_profile_end(char *report, size_t cap) {
+    if (!g_prof) return LIPVQ_ESHAPE;
+    __atomic_store_n(&g_prof_on, 0, __ATOMIC_RELEASE);
+    const int n = g_prof_n < g_prof_cap ? g_prof_n : g_prof_cap;
+    struct Agg { const char *name; double ms; int count; } agg[64];
+    int na = 0, rc = LIPVQ_OK;
+    for (int i = 0; i < n; ++i) {
+        float ms = 0.f;
+        if (cudaEventSynchronize(g_prof[i].end) != cudaSuccess ||
+            cudaEventElapsedTime(&ms, g_prof[i].beg, g_prof[i].end) != cudaSuccess) { rc = LIPVQ_ECUDA; break; }
+        int j = 0;
+        while (j < na && strcmp(agg[j].name, g_prof[i].name) != 0) ++j;
+        if (j == na) { if (na == 64) continue; agg[na].name = g_prof[i].name; agg[na].ms = 0.0; agg[na].count = 0; ++na; }
+        agg[j].ms += ms; agg[j].count += 1;
+    }
+    size_t off = 0;
+    if (report && cap) {
+        report[0] = 0;
+        for (int j = 0; j < na; ++j) {
+            const int w = snprintf(report + off, cap - off, "%s %d %.6f\n", agg[j].name, agg[j].count, agg[j].ms);
+            if (w < 0 || (size_t)w >= cap - off) break;
+            off += (size_t)w;
+        }
+    }
+    for (int i = 0; i < g_prof_cap; ++i) { cudaEventDestroy(g_prof[i].beg); cudaEventDestroy(g_prof[i].end); }
+    free(g_prof);
+    g_prof = nullptr; g_prof_cap = 0; g_prof_n = 0;
+    return rc;
 }
 
 int lipvq_workspace_bytes(const lipvq_dims_t *dims, int64_t n_rows, size_t *out_bytes) {
@@ -263,6 +324,7 @@ static size_t qd_ws_bytes(const lipvq_dims_t *d) {
 // R = decoder(E) for every code (v5:62-68, 75-76 applied to the K distinct values z_q can take)
 static int decoder_code_table(const lipvq_dims_t *d, const lipvq_params_t *p, float *c1, float *d1, float *c2,
                               float *d2, float *R, double *part, cudaStream_t st) {
+    ProfScope prof("decoder_code_table", st);
     if (use_mlp_tc(d)) {
         const mlp::DecLayout L = mlp::dec_layout(d->D);
         LIPVQ_TRY(mlp::set_smem(mlp::dec_kernel, L.total));
@@ -306,6 +368,7 @@ int lipvq_quantize_decode_fwd(const lipvq_dims_t *d, const lipvq_params_t *p, co
     LIPVQ_TRY(decoder_code_table(d, p, c1, d1, c2, d2, R, dpart, st));
     const int64_t tiles = (n + QE_ROWS - 1) / QE_ROWS;
     const int grid = (int)(tiles < kQeBlocks ? tiles : kQeBlocks);
+    ProfScope prof("quantize_emit_kernel", st);
     if ((d->D & 3) == 0)
         quantize_emit_kernel<true><<<grid, QE_THR, 0, st>>>(a->z_e, p->codebook, R, a->idx, x, n, d->D, d->F, d->K,
                                                             a->z_q, a->x_recon, part);

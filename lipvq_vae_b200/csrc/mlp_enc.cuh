@@ -500,6 +500,7 @@ inline int encoder_fused_launch(const lipvq_dims_t *d, const lipvq_params_t *p, 
             LIPVQ_TRY(make_store_tmap(&tm_zb, Zb, dt, 2, np, (uint64_t)DKp, (uint64_t)DKp));
         }
     }
+    ProfScope prof("enc_fused_kernel", st);
     enc_fused_kernel<<<grid_for(n), ENC_THR, EncSmem::TOTAL, st>>>(x, p->enc0_w, p->enc0_b, p->enc2_w, p->enc2_b, img,
                                                                    p->lat_b, n, d->F, d->D, a1, h1, a2, h2, z_e, mu, Zb,
                                                                    zn, DKp, counters, tm_ze, tm_zb, use_tma);

@@ -125,6 +125,7 @@ inline int vq_exact_launch(const float *z, const float *E, int64_t n_rows, int D
     // fallback-list mode: the count lives on the device, so size the grid for a modest share
     // of the rows and let the grid-stride loop cover the rest.
     int64_t grid = list ? (tiles < 4 * kNumSMs ? tiles : 4 * kNumSMs) : (tiles < 65535 * 16 ? tiles : 65535 * 16);
+    ProfScope prof("vq_exact_kernel", st);
     if ((D & 3) == 0)
         vq_exact_kernel<true><<<(unsigned)grid, XNT, 0, st>>>(z, E, n_rows, D, K, list, list_count, idx, d2);
     else

@@ -678,6 +678,7 @@ inline int launch_tc(const CUtensorMap &ta, const CUtensorMap &tb, const Geometr
         attr_done = true;
     }
     const int grid = (int)(g.n_tiles < kNumSMs ? g.n_tiles : kNumSMs);
+    ProfScope prof("vq_tc_kernel", st);
     kern<<<grid, NT, L::TOTAL, st>>>(ta, tb, g.n, (int)g.n_tiles, g.nct, g.NK16, w.zn, w.emax,
                                      OP_ABS * sqrtf((float)g.D), w.cand, w.cand_meta);
     LIPVQ_LAUNCH_OK();
@@ -695,6 +696,7 @@ inline size_t vq_tensor_ws_bytes(int64_t n, int D, int K) {
 // pass 0: codebook operand (mu, Eb, enorm, emax) into the workspace; zeroes the counters
 inline int vq_tensor_prep(const float *E, const tc::Geometry &g, const tc::Workspace &w, cudaStream_t st) {
     using namespace tc;
+    ProfScope prof("vq_prep (3 kernels)", st);
     LIPVQ_CUDA_OK(cudaMemsetAsync(w.counters, 0, 8 * sizeof(int), st));
     vq_prep_mean_kernel<<<(g.D + 31) / 32, 1024, 0, st>>>(E, g.K, g.D, w.mu);
     LIPVQ_LAUNCH_OK();
@@ -728,6 +730,7 @@ inline int vq_tensor_search(const float *z, const float *E, const tc::Geometry &
     {
         int64_t blocks = (n + 255) / 256;
         if (blocks > 8 * kNumSMs) blocks = 8 * kNumSMs;
+        ProfScope prof("vq_resolve_kernel", st);
         vq_resolve_kernel<<<(unsigned)blocks, 256, 0, st>>>(n, K, w.cand, w.cand_meta, w.zn, w.emax, abs_c, idx,
                                                             d2 != nullptr, w.resc_list, w.list, w.counters);
         LIPVQ_LAUNCH_OK();
@@ -735,6 +738,7 @@ inline int vq_tensor_search(const float *z, const float *E, const tc::Geometry &
     {
         int64_t blocks = (n + 7) / 8;
         if (blocks > 8 * kNumSMs) blocks = 8 * kNumSMs;   // grid-stride over the device-side list length
+        ProfScope prof("vq_rescore_kernel", st);
         if ((D & 3) == 0)
             vq_rescore_kernel<4, true><<<(unsigned)blocks, 256, 0, st>>>(z, E, D, K, w.cand, w.cand_meta, w.zn, w.emax,
                                                                         abs_c, idx, d2, w.resc_list, w.counters);
@@ -760,6 +764,7 @@ inline int vq_tensor_launch(const float *z, const float *E, int64_t n, int D, in
         const int rpb = 256 / (g.DKp >> 3);
         int64_t blocks = (g.Np + rpb - 1) / rpb;
         if (blocks > 8 * kNumSMs) blocks = 8 * kNumSMs;
+        ProfScope prof("vq_convert_z_kernel", st);
         vq_convert_z_kernel<<<(unsigned)blocks, 256, 0, st>>>(z, w.mu, n, g.Np, D, g.DKp, w.Zb, w.zn, w.counters);
         LIPVQ_LAUNCH_OK();
     }

@@ -247,3 +247,32 @@ def test_large_n_properties():
     q.search_mode = 1
     _, i2 = q(zq1)
     assert torch.equal(i2, i1) or (E[i2] == E[i1]).all()
+
+
+@pytest.mark.gpu
+def test_host_tokenizer_pipeline_matches_direct_calls():
+    """HostTokenizer (pinned-host batches, 2 slots in flight) returns exactly what the module returns."""
+    from lipvq_vae_b200 import HostTokenizer
+    p, x = case_inputs("small")
+    m = _model(p, MODES[-1])
+    rng = np.random.default_rng(7)
+    batches = [torch.from_numpy(rng.standard_normal((n, x.shape[1])).astype(np.float32)).pin_memory()
+               for n in (x.shape[0], 17, x.shape[0], 1, 33)]
+    want = []
+    with torch.no_grad():
+        for b in batches:
+            z, loss = m(b.cuda())
+            want.append((m.last_indices.cpu().clone(), m.last_loss_terms.cpu().clone(), z.cpu().clone()))
+    ht = HostTokenizer(m, max(b.shape[0] for b in batches), depth=2)
+    got = []
+    for i, b in enumerate(batches):
+        ht.submit(b)
+        if i >= 1:
+            idx, terms, z = ht.collect()
+            got.append((idx.clone(), terms.clone(), z.cpu().clone()))
+    idx, terms, z = ht.collect()
+    got.append((idx.clone(), terms.clone(), z.cpu().clone()))
+    for (wi, wt, wz), (gi, gt, gz) in zip(want, got):
+        assert torch.equal(wi, gi) and torch.equal(wt, gt) and torch.equal(wz, gz)
+    with pytest.raises(ValueError):
+        ht.submit(torch.zeros(10 ** 6, x.shape[1]))
