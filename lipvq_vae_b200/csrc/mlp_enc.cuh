@@ -75,11 +75,15 @@ __device__ __forceinline__ void a_ready_arrive(uint32_t bar) {
 // Epilogue over the 16-column blocks cb in [cb0, cb1) with cb % nsub == sub, for this thread's row:
 //   v = acc + bias -> [pre-activation rows to global] -> act -> [activation rows to global] -> [next A operand]
 // pre/post: &dst[warp_row0 * ld] or nullptr; stores go through the warp's transpose buffer (warp_store16).
-template <int ACT>
+// after(cb) runs once block cb is complete (its operand stored).  (Prefetching the next block's TMEM load was
+// measured slower: the extra live registers spill at the 96-register cap of a 17-warp CTA.)
+struct NoAfter { __device__ __forceinline__ void operator()(int) const {} };
+template <int ACT, class After>
 __device__ __forceinline__ void epilogue_blocks(uint32_t t_acc, int cb0, int cb1, int sub, int nsub, int n_real,
                                                 const float *sbias, bool write_next, uint32_t t_next_hi,
                                                 uint32_t t_next_lo, uint8_t *wbuf, float *__restrict__ pre,
-                                                float *__restrict__ post, int ld, int rows_valid, bool vec) {
+                                                float *__restrict__ post, int ld, int rows_valid, bool vec,
+                                                After after) {
     int cb = cb0 + ((sub - cb0) % nsub + nsub) % nsub;
     for (; cb < cb1; cb += nsub) {
         const int c0 = cb << 4;
@@ -99,9 +103,11 @@ __device__ __forceinline__ void epilogue_blocks(uint32_t t_acc, int cb0, int cb1
         for (int i = 0; i < 16; ++i) v[i] = apply_act<ACT>(v[i]);
         if (post) warp_store16(wbuf, post + c0, ld, v, rows_valid, valid, vec);
         if (write_next) store_split16(t_next_hi + c0, t_next_lo + c0, v);
+        after(cb);
     }
 }
 
+template <bool TMA>
 __global__ void __launch_bounds__(ENC_THR, 1)
 enc_fused_kernel(const float *__restrict__ x, const float *__restrict__ W0, const float *__restrict__ b0,
                  const float *__restrict__ W1, const float *__restrict__ b1, const uint8_t *__restrict__ wn_img,
@@ -111,7 +117,7 @@ enc_fused_kernel(const float *__restrict__ x, const float *__restrict__ W0, cons
                  const float *__restrict__ mu, tc::op_t *__restrict__ Zb, float *__restrict__ zn, int DKp,
                  int *__restrict__ counters,
                  // bulk tensor stores of z_e (fp32, box 8 x 32, 32-byte swizzle) and Zb (16-bit, box 16 x 32)
-                 const __grid_constant__ CUtensorMap tm_ze, const __grid_constant__ CUtensorMap tm_zb, int use_tma) {
+                 const __grid_constant__ CUtensorMap tm_ze, const __grid_constant__ CUtensorMap tm_zb) {
     using L = EncSmem;
     extern __shared__ uint8_t smem_raw[];
     const uint32_t raw = ptx::smem_u32(smem_raw);
@@ -247,7 +253,7 @@ enc_fused_kernel(const float *__restrict__ x, const float *__restrict__ W0, cons
             const uint32_t par = t & 1;
             const int64_t wrow0 = tile * TM + (r_in - lane);               // first row of this warp
             const int rows_valid = (int)max((int64_t)0, min((int64_t)32, n_rows - wrow0));
-            if (use_tma && keeps_acts) {   // the previous tile's bulk stores must have read the slots
+            if (TMA && keeps_acts) {   // the previous tile's bulk stores must have read the slots
                 if (lane == 0) ptx::bulk_wait_read<0>();
                 __syncwarp();
             }
@@ -266,26 +272,23 @@ enc_fused_kernel(const float *__restrict__ x, const float *__restrict__ W0, cons
             }
             ENC_TICK(1);
             epilogue_blocks<ACT_GELU_FAST>(tm + 128, 0, H1 / 16, sub, 4, H1, sb0, true, tm + 352, tm + 416, wbuf,
-                                      a1 ? a1 + wrow0 * H1 : nullptr, h1 ? h1 + wrow0 * H1 : nullptr, H1, rows_valid,
-                                      true);
+                                           a1 ? a1 + wrow0 * H1 : nullptr, h1 ? h1 + wrow0 * H1 : nullptr, H1,
+                                           rows_valid, true, NoAfter());
             a_ready_arrive(bar_a(1));
             ENC_TICK(2);
             // ---- layer 1 epilogue: h2 (hi written in place over the accumulator columns just read)
             ptx::mbar_wait(bar_acc(1), par);
             ptx::tc_fence_after();
             ENC_TICK(3);
-            for (int cb = sub; cb < HH / 16; cb += 4) {
-                epilogue_blocks<ACT_GELU_FAST>(tm + 0, cb, cb + 1, sub, 4, HH, sb1, true, tm + 0, tm + 128, wbuf,
-                                               a2 ? a2 + wrow0 * HH : nullptr, h2 ? h2 + wrow0 * HH : nullptr, HH,
-                                               rows_valid, true);
-                a_ready_arrive(bar_a2(cb >> 1));
-            }
+            epilogue_blocks<ACT_GELU_FAST>(tm + 0, 0, HH / 16, sub, 4, HH, sb1, true, tm + 0, tm + 128, wbuf,
+                                           a2 ? a2 + wrow0 * HH : nullptr, h2 ? h2 + wrow0 * HH : nullptr, HH,
+                                           rows_valid, true, [&](int cb) { a_ready_arrive(bar_a2(cb >> 1)); });
             ENC_TICK(4);
             // ---- layer 2 epilogue: sigmoid and store z_e
             ptx::mbar_wait(bar_acc3(0), par);
             ptx::tc_fence_after();
             ENC_TICK(5);
-            if (use_tma) {
+            if constexpr (TMA) {
                 // z_e (+ the search's row operand Zb = [fp16(z - mu) | 1 1 1], zn = ||z - mu||) leave through bulk
                 // tensor stores: a thread only writes its 16 columns into the warp's staging slots (two 1 KB
                 // slots in the 32-byte-swizzle pattern the tensor map expects); lane 0 issues the store.  A slot
@@ -322,11 +325,11 @@ enc_fused_kernel(const float *__restrict__ x, const float *__restrict__ W0, cons
 #pragma unroll
                         for (int i = 0; i < 4; ++i) {
                             const float4 bq = *reinterpret_cast<const float4 *>(sb2 + c0 + 4 * i);
-                            v[4 * i] = sigmoid_fast_f(__uint_as_float(r[4 * i]) + bq.x);
-                            v[4 * i + 1] = sigmoid_fast_f(__uint_as_float(r[4 * i + 1]) + bq.y);
-                            v[4 * i + 2] = sigmoid_fast_f(__uint_as_float(r[4 * i + 2]) + bq.z);
-                            v[4 * i + 3] = sigmoid_fast_f(__uint_as_float(r[4 * i + 3]) + bq.w);
+                            v[4 * i] = __uint_as_float(r[4 * i]) + bq.x; v[4 * i + 1] = __uint_as_float(r[4 * i + 1]) + bq.y;
+                            v[4 * i + 2] = __uint_as_float(r[4 * i + 2]) + bq.z; v[4 * i + 3] = __uint_as_float(r[4 * i + 3]) + bq.w;
                         }
+#pragma unroll
+                        for (int i = 0; i < 16; ++i) v[i] = sigmoid_fast_f(v[i]);
 #pragma unroll
                         for (int hf = 0; hf < 2; ++hf) {
                             if (c0 + 8 * hf >= D) break;
@@ -383,7 +386,7 @@ enc_fused_kernel(const float *__restrict__ x, const float *__restrict__ W0, cons
                 }
             } else if (Zb == nullptr) {
                 epilogue_blocks<ACT_SIGMOID_FAST>(tm + 256, 0, D16 / 16, sub, 4, D, sb2, false, 0u, 0u, wbuf, nullptr,
-                                                  z_e + wrow0 * D, D, rows_valid, vec_d);
+                                                  z_e + wrow0 * D, D, rows_valid, vec_d, NoAfter());
             } else {
                 // z_e plus the search's row operand: Zb = [fp16(z - mu) | 1 1 1 | 0...], zn = ||z - mu||
                 float ss = 0.f;
@@ -438,13 +441,13 @@ enc_fused_kernel(const float *__restrict__ x, const float *__restrict__ W0, cons
             }
             ENC_TICK(6);
         }
-        if (use_tma && Zb) {                   // row norms of the last tile
+        if (TMA && Zb) {                       // row norms of the last tile
             asm volatile("bar.sync 1, 512;" ::: "memory");
             if (zn_rows >= 0 && sub == 0 && lane < zn_rows)
                 zn[zn_row0 + lane] = sqrtf(((sznp[r_in] + sznp[TM + r_in]) + sznp[2 * TM + r_in]) + sznp[3 * TM + r_in]);
         }
         if (zbad) atomicOr(counters + 3, 1);   // operand out of fp16 range -> the search goes exact for this launch
-        if (use_tma && lane == 0) ptx::bulk_wait<0>();   // every bulk store has landed before the CTA retires
+        if (TMA && lane == 0) ptx::bulk_wait<0>();   // every bulk store has landed before the CTA retires
 #ifdef ENC_PROFILE
         if (blockIdx.x == 3 && (threadIdx.x & 31) == 0 && (threadIdx.x >> 5) < 8)
             printf("w%d tiles %d cyc/tile: xstage %lld | wait0 %lld epi0 %lld | wait1 %lld epi1 %lld | wait2 %lld epi2 %lld\n",
@@ -480,7 +483,8 @@ inline int encoder_fused_launch(const lipvq_dims_t *d, const lipvq_params_t *p, 
     const int D16 = pad16(d->D);
     enc_wn_image_kernel<<<(D16 * 32 + 255) / 256, 256, 0, st>>>(Wn, d->D, D16, img);
     LIPVQ_LAUNCH_OK();
-    LIPVQ_TRY(set_smem(enc_fused_kernel, EncSmem::TOTAL));
+    LIPVQ_TRY(set_smem(enc_fused_kernel<true>, EncSmem::TOTAL));
+    LIPVQ_TRY(set_smem(enc_fused_kernel<false>, EncSmem::TOTAL));
     // bulk tensor stores need 16-byte row pitches and 32-bit row coordinates; otherwise the per-thread path
     static const bool no_tma = [] { const char *e = getenv("LIPVQ_ENC_TMA"); return e && !strcmp(e, "0"); }();
     CUtensorMap tm_ze, tm_zb;
@@ -501,9 +505,14 @@ inline int encoder_fused_launch(const lipvq_dims_t *d, const lipvq_params_t *p, 
         }
     }
     ProfScope prof("enc_fused_kernel", st);
-    enc_fused_kernel<<<grid_for(n), ENC_THR, EncSmem::TOTAL, st>>>(x, p->enc0_w, p->enc0_b, p->enc2_w, p->enc2_b, img,
-                                                                   p->lat_b, n, d->F, d->D, a1, h1, a2, h2, z_e, mu, Zb,
-                                                                   zn, DKp, counters, tm_ze, tm_zb, use_tma);
+    if (use_tma)
+        enc_fused_kernel<true><<<grid_for(n), ENC_THR, EncSmem::TOTAL, st>>>(
+            x, p->enc0_w, p->enc0_b, p->enc2_w, p->enc2_b, img, p->lat_b, n, d->F, d->D, a1, h1, a2, h2, z_e, mu, Zb, zn,
+            DKp, counters, tm_ze, tm_zb);
+    else
+        enc_fused_kernel<false><<<grid_for(n), ENC_THR, EncSmem::TOTAL, st>>>(
+            x, p->enc0_w, p->enc0_b, p->enc2_w, p->enc2_b, img, p->lat_b, n, d->F, d->D, a1, h1, a2, h2, z_e, mu, Zb, zn,
+            DKp, counters, tm_ze, tm_zb);
     LIPVQ_LAUNCH_OK();
     return LIPVQ_OK;
 }

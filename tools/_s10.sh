@@ -1,0 +1,3 @@
+timeout 120 python tools/enc_probe.py 2>&1 | tail -2
+ENC_PROBE_ONCE=1 timeout 120 python tools/enc_probe.py > /dev/null 2>&1 && ncu --set full --clock-control none --import-source on -k regex:"enc_fused_kernel" -c 1 -o gpurun_out/s10_enc -f env ENC_PROBE_ONCE=1 python tools/enc_probe.py > gpurun_out/s10_ncu.log 2>&1
+tail -2 gpurun_out/s10_ncu.log
