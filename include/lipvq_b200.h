@@ -25,7 +25,7 @@
 extern "C" {
 #endif
 
-#define LIPVQ_ABI_VERSION 2
+#define LIPVQ_ABI_VERSION 3
 
 enum {
     LIPVQ_OK = 0,
@@ -157,10 +157,11 @@ int lipvq_decoder_fwd(const lipvq_dims_t *dims, const lipvq_params_t *p, const f
  * v5:74), x_recon[n] = xr_code[idx[n]] to acts->x_recon (nullable), and sse[0] = sum (x_recon-x)^2,
  * sse[1] = sum (z_q-z_e)^2 (device double[2], overwritten).  acts: idx, z_e are read; z_q is written;
  * c1,d1,c2,d2,xr_code ([K,.], code level) are written when non-null (kept for backward).
- * x may be null (sse[0] = 0). */
+ * x may be null (sse[0] = 0).  loss_out (nullable, needs x): device float[4] = {loss, recon, commit, codebook}
+ * as lipvq_loss_finalize would write them for n_total global rows (v5:79-83), from the same reduction. */
 int lipvq_quantize_decode_fwd(const lipvq_dims_t *dims, const lipvq_params_t *p, const float *x,
-                              int64_t n_rows, const lipvq_acts_t *acts, double *sse, void *ws,
-                              size_t ws_bytes, void *stream);
+                              int64_t n_rows, int64_t n_total, const lipvq_acts_t *acts, double *sse,
+                              float *loss_out, void *ws, size_t ws_bytes, void *stream);
 
 /* loss = sse_r/(n_total*F) + 0.25*sse_q/(n_total*D) + 0.25*sse_q/(n_total*D)  (v5:79-83).
  * out: device float[4] = {loss, recon, commit, codebook}. */

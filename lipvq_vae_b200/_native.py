@@ -116,7 +116,7 @@ SIGNATURES = {
     "lipvq_encode_search_fwd": (C.c_int, [_DP, _PP, _VP, _I64, _AP, _I32, _VP, _VP, _SZ, _VP]),
     "lipvq_gather_loss": (C.c_int, [_VP, _VP, _VP, _I64, _I32, _I32, _VP, _VP, _VP, _SZ, _VP]),
     "lipvq_decoder_fwd": (C.c_int, [_DP, _PP, _VP, _VP, _I64, _AP, _VP, _VP, _SZ, _VP]),
-    "lipvq_quantize_decode_fwd": (C.c_int, [_DP, _PP, _VP, _I64, _AP, _VP, _VP, _SZ, _VP]),
+    "lipvq_quantize_decode_fwd": (C.c_int, [_DP, _PP, _VP, _I64, _I64, _AP, _VP, _VP, _VP, _SZ, _VP]),
     "lipvq_loss_finalize": (C.c_int, [_VP, _VP, _I64, _I32, _I32, _VP, _VP]),
     "lipvq_decoder_bwd": (C.c_int, [_DP, _PP, _VP, _I64, _I64, _VP, _AP, _GP, _VP, _SZ, _VP]),
     "lipvq_scatter_add": (C.c_int, [_VP, _VP, _I64, _I32, _I32, _VP, _VP, _VP]),
@@ -142,7 +142,7 @@ def lib():
                     fn = getattr(h, name)
                     fn.restype = res
                     fn.argtypes = args
-                if h.lipvq_abi_version() != 2:
+                if h.lipvq_abi_version() != 3:
                     raise LipVQNativeError("ABI version mismatch")
                 _lib = h
     return _lib

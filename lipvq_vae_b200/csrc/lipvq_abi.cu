@@ -325,26 +325,30 @@ static size_t qd_ws_bytes(const lipvq_dims_t *d) {
 static int decoder_code_table(const lipvq_dims_t *d, const lipvq_params_t *p, float *c1, float *d1, float *c2,
                               float *d2, float *R, double *part, cudaStream_t st) {
     ProfScope prof("decoder_code_table", st);
-    if (use_mlp_tc(d)) {
-        const mlp::DecLayout L = mlp::dec_layout(d->D);
-        LIPVQ_TRY(mlp::set_smem(mlp::dec_kernel, L.total));
-        mlp::dec_kernel<<<mlp::grid_for(d->K), mlp::NTHR, L.total, st>>>(
-            nullptr, p->codebook, nullptr, nullptr, p->dec0_w, p->dec0_b, p->dec2_w, p->dec2_b, p->out_w, p->out_b,
-            d->K, d->D, d->K, d->F, nullptr, c1, d1, c2, d2, R, part, nullptr);
-        LIPVQ_LAUNCH_OK();
-        return LIPVQ_OK;
-    }
-    LIPVQ_TRY(linear_fwd<ACT_GELU>(p->codebook, p->dec0_w, p->dec0_b, c1, d1, d->K, d->H1, d->D, st));
-    LIPVQ_TRY(linear_fwd<ACT_GELU>(d1, p->dec2_w, p->dec2_b, c2, d2, d->K, d->H, d->H1, st));
-    return linear_fwd<ACT_NONE>(d2, p->out_w, p->out_b, nullptr, R, d->K, d->F, d->H, st);
+    (void)part;
+    const size_t smem = (size_t)CT_CODES * (d->D + d->H1 + d->H) * sizeof(float);
+    if (smem > 200 * 1024) return LIPVQ_ESHAPE;
+    if (smem > 48 * 1024)
+        LIPVQ_CUDA_OK(cudaFuncSetAttribute(decoder_code_table_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                           (int)smem));
+    decoder_code_table_kernel<<<(d->K + CT_CODES - 1) / CT_CODES, 256, smem, st>>>(
+        p->codebook, p->dec0_w, p->dec0_b, p->dec2_w, p->dec2_b, p->out_w, p->out_b, d->K, d->D, d->H1, d->H, d->F, c1,
+        d1, c2, d2, R);
+    LIPVQ_LAUNCH_OK();
+    return LIPVQ_OK;
 }
 
 int lipvq_quantize_decode_fwd(const lipvq_dims_t *d, const lipvq_params_t *p, const float *x, int64_t n,
-                              const lipvq_acts_t *a, double *sse, void *ws, size_t ws_bytes, void *stream) {
-    if (!dims_ok(d) || n < 0) return LIPVQ_ESHAPE;
+                              int64_t n_total, const lipvq_acts_t *a, double *sse, float *loss_out, void *ws,
+                              size_t ws_bytes, void *stream) {
+    if (!dims_ok(d) || n < 0 || n_total < n || (loss_out && n_total < 1)) return LIPVQ_ESHAPE;
     if (!p || !a || !sse) return LIPVQ_EALIGN;
     cudaStream_t st = (cudaStream_t)stream;
-    if (n == 0) { LIPVQ_CUDA_OK(cudaMemsetAsync(sse, 0, 2 * sizeof(double), st)); return LIPVQ_OK; }
+    if (n == 0) {
+        LIPVQ_CUDA_OK(cudaMemsetAsync(sse, 0, 2 * sizeof(double), st));
+        if (loss_out) LIPVQ_CUDA_OK(cudaMemsetAsync(loss_out, 0, 4 * sizeof(float), st));
+        return LIPVQ_OK;
+    }
     auto opt16 = [](const void *q) { return q == nullptr || aligned16(q); };
     if (!a->idx || !aligned16(a->z_e) || !aligned16(a->z_q) || !opt16(a->x_recon) || !opt16(x) || !opt16(a->c1) ||
         !opt16(a->d1) || !opt16(a->c2) || !opt16(a->d2) || !opt16(a->xr_code))
@@ -353,14 +357,7 @@ int lipvq_quantize_decode_fwd(const lipvq_dims_t *d, const lipvq_params_t *p, co
     Bump b(ws, ws_bytes);
     float *part = b.take<float>(2 * kQeBlocks);
     double *dpart = b.take<double>(mlp::kPartBytes / sizeof(double));
-    const bool tc = use_mlp_tc(d);   // the tensor kernel keeps the code-level activations on chip unless asked
-    float *c1 = a->c1, *d1 = a->d1, *c2 = a->c2, *d2 = a->d2, *R = a->xr_code;
-    if (!tc) {
-        if (!c1) c1 = b.take<float>((size_t)d->K * d->H1);
-        if (!d1) d1 = b.take<float>((size_t)d->K * d->H1);
-        if (!c2) c2 = b.take<float>((size_t)d->K * d->H);
-        if (!d2) d2 = b.take<float>((size_t)d->K * d->H);
-    }
+    float *c1 = a->c1, *d1 = a->d1, *c2 = a->c2, *d2 = a->d2, *R = a->xr_code;   // code-level, kept when non-null
     if (!R) R = b.take<float>((size_t)d->K * d->F);
     if (!b.ok()) return LIPVQ_EWORKSPACE;
     // the decoder acts on z_q = E[idx] (v5:47, 75): K distinct inputs, so it runs once per CODE; the per-row
@@ -376,7 +373,9 @@ int lipvq_quantize_decode_fwd(const lipvq_dims_t *d, const lipvq_params_t *p, co
         quantize_emit_kernel<false><<<grid, QE_THR, 0, st>>>(a->z_e, p->codebook, R, a->idx, x, n, d->D, d->F, d->K,
                                                              a->z_q, a->x_recon, part);
     LIPVQ_LAUNCH_OK();
-    partials2_to_double_kernel<<<1, 256, 0, st>>>(part, grid, sse);
+    partials2_to_double_kernel<<<1, 256, 0, st>>>(part, grid, sse, x ? loss_out : nullptr,
+                                                  1.0 / ((double)(n_total > 0 ? n_total : 1) * d->F),
+                                                  1.0 / ((double)(n_total > 0 ? n_total : 1) * d->D));
     LIPVQ_LAUNCH_OK();
     return LIPVQ_OK;
 }
@@ -502,8 +501,7 @@ int lipvq_forward_fused(const lipvq_dims_t *d, const lipvq_params_t *p, const fl
     void *es_ws = (void *)align_up((size_t)(b.base + b.off), 256);
     const size_t es_bytes = ws_bytes - (size_t)((char *)es_ws - (char *)ws);
     LIPVQ_TRY(lipvq_encode_search_fwd(d, p, x, n, &a, search_mode, stats, es_ws, es_bytes, stream));
-    LIPVQ_TRY(lipvq_quantize_decode_fwd(d, p, x, n, &a, sse, part, part_bytes, stream));
-    if (loss_out) LIPVQ_TRY(lipvq_loss_finalize(sse, sse + 1, n_total, d->F, d->D, loss_out, stream));
+    LIPVQ_TRY(lipvq_quantize_decode_fwd(d, p, x, n, n_total, &a, sse, loss_out, part, part_bytes, stream));
     (void)st;
     return LIPVQ_OK;
 }

@@ -14,7 +14,7 @@ __global__ void lipschitz_prep_kernel(const float *__restrict__ W, const float *
                                       float *__restrict__ Wn) {
     const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     const int lane = threadIdx.x & 31;
-    if (row >= D) return;
+    if (row >= D) return;   // (whole warps leave together)
     float s = 0.f;
     for (int j = lane; j < H; j += 32) s += fabsf(W[(size_t)row * H + j]);
     s = warp_sum(s);
@@ -166,8 +166,10 @@ __global__ void __launch_bounds__(QE_THR) quantize_emit_kernel(
     if (tid == 0) { partial[blockIdx.x] = sq; partial[gridDim.x + blockIdx.x] = sr; }
 }
 
-// sse[0] = sum_i part[n + i] (recon), sse[1] = sum_i part[i] (quantisation); fixed order, double
-__global__ void partials2_to_double_kernel(const float *__restrict__ part, int n, double *__restrict__ sse) {
+// sse[0] = sum_i part[n + i] (recon), sse[1] = sum_i part[i] (quantisation); fixed order, double.
+// loss_out (nullable): the four loss terms of loss_finalize_kernel, written by the same thread.
+__global__ void partials2_to_double_kernel(const float *__restrict__ part, int n, double *__restrict__ sse,
+                                           float *__restrict__ loss_out, double inv_nf, double inv_nd) {
     __shared__ double sm[2][8];
     double a = 0.0, b = 0.0;
     for (int i = threadIdx.x; i < n; i += blockDim.x) { a += (double)part[i]; b += (double)part[n + i]; }
@@ -178,7 +180,71 @@ __global__ void partials2_to_double_kernel(const float *__restrict__ part, int n
         double q = 0.0, r = 0.0;
         for (int w = 0; w < (int)(blockDim.x >> 5); ++w) { q += sm[0][w]; r += sm[1][w]; }
         sse[0] = r; sse[1] = q;
+        if (loss_out) {
+            const double recon = r * inv_nf, commit = q * inv_nd;
+            loss_out[0] = (float)(recon + 0.25 * commit + 0.25 * commit);
+            loss_out[1] = (float)recon;
+            loss_out[2] = (float)commit;
+            loss_out[3] = (float)commit;
+        }
     }
+}
+
+// ---------------------------------------------------------------- per-code decoder table (k7)
+// xr_code = to_output(decoder(E)) for all K codes (v5:62-68, 75-76 on the K distinct values of z_q).  K rows are
+// too few for the tensor cores to pay off (a 128-row UMMA tile would keep 8 SMs busy for 40 us), so this runs on
+// the CUDA cores in exact fp32: a CTA takes CT_CODES codes through the three layers; a warp owns an output
+// neuron at a time, its lanes stride the reduction axis (coalesced weight rows), one accumulator per code.
+constexpr int CT_CODES = 8;
+template <int ACT, int KIN_MAX_UNUSED = 0>
+__device__ __forceinline__ void ct_layer(const float *__restrict__ W, const float *__restrict__ bias, int n_out,
+                                         int k_in, const float *s_in /* [CT][k_in] */, float *s_out /* [CT][n_out] */,
+                                         float *__restrict__ g_pre, float *__restrict__ g_post, int ld, int code0,
+                                         int n_codes) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarp = blockDim.x >> 5;
+    for (int j = warp; j < n_out; j += nwarp) {
+        float acc[CT_CODES];
+#pragma unroll
+        for (int c = 0; c < CT_CODES; ++c) acc[c] = 0.f;
+        for (int k = lane; k < k_in; k += 32) {
+            const float w = __ldg(W + (size_t)j * k_in + k);
+#pragma unroll
+            for (int c = 0; c < CT_CODES; ++c) acc[c] = fmaf(w, s_in[c * k_in + k], acc[c]);
+        }
+#pragma unroll
+        for (int c = 0; c < CT_CODES; ++c) acc[c] = warp_sum(acc[c]);
+        if (lane < CT_CODES) {
+            float v = 0.f;
+#pragma unroll
+            for (int c = 0; c < CT_CODES; ++c) v = lane == c ? acc[c] : v;
+            v += __ldg(bias + j);
+            const bool ok = lane < n_codes;
+            if (g_pre && ok) g_pre[(size_t)(code0 + lane) * ld + j] = v;
+            v = apply_act<ACT>(v);
+            if (g_post && ok) g_post[(size_t)(code0 + lane) * ld + j] = v;
+            if (s_out) s_out[lane * n_out + j] = v;
+        }
+    }
+}
+__global__ void __launch_bounds__(256) decoder_code_table_kernel(
+    const float *__restrict__ E, const float *__restrict__ Wd0, const float *__restrict__ bd0,
+    const float *__restrict__ Wd1, const float *__restrict__ bd1, const float *__restrict__ Wo,
+    const float *__restrict__ bo, int K, int D, int H1, int H, int F, float *__restrict__ c1,
+    float *__restrict__ d1, float *__restrict__ c2, float *__restrict__ d2, float *__restrict__ R) {
+    extern __shared__ float ct_smem[];
+    float *s_e = ct_smem, *s_a = s_e + CT_CODES * D, *s_b = s_a + CT_CODES * H1;
+    const int code0 = blockIdx.x * CT_CODES;
+    const int n_codes = K - code0 < CT_CODES ? K - code0 : CT_CODES;
+    for (int i = threadIdx.x; i < CT_CODES * D; i += blockDim.x) {
+        const int c = i / D, k = i - c * D;
+        s_e[i] = c < n_codes ? __ldg(E + (size_t)(code0 + c) * D + k) : 0.f;
+    }
+    __syncthreads();
+    ct_layer<ACT_GELU>(Wd0, bd0, H1, D, s_e, s_a, c1, d1, H1, code0, n_codes);
+    __syncthreads();
+    ct_layer<ACT_GELU>(Wd1, bd1, H, H1, s_a, s_b, c2, d2, H, code0, n_codes);
+    __syncthreads();
+    ct_layer<ACT_NONE>(Wo, bo, F, H, s_b, nullptr, nullptr, R, F, code0, n_codes);
 }
 
 // out = alpha * (a - b)

@@ -111,7 +111,7 @@ __device__ __forceinline__ void split3_op(float v, op_t &a, op_t &b, op_t &c) {
 // one warp per (padded) code row; writes Eb row and enorm[k] = ||e'_k||
 __global__ void vq_prep_rows_kernel(const float *__restrict__ E, const float *__restrict__ mu, int K, int Kp,
                                     int D, int DKp, op_t *__restrict__ Eb, float *__restrict__ enorm,
-                                    int *__restrict__ counters) {
+                                    int *__restrict__ counters, float *__restrict__ emax) {
     const int k = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     const int lane = threadIdx.x & 31;
     if (k >= Kp) return;
@@ -134,22 +134,12 @@ __global__ void vq_prep_rows_kernel(const float *__restrict__ E, const float *__
         op_t a, b, c;
         split3_op(en, a, b, c);
         row[D] = a; row[D + 1] = b; row[D + 2] = c;
-        if (k < K) enorm[k] = sqrtf(s);
-    }
-}
-
-// emax = max_k enorm[k] (single block)
-__global__ void vq_prep_emax_kernel(const float *__restrict__ enorm, int K, float *__restrict__ emax) {
-    __shared__ float sm[32];
-    float m = 0.f;
-    for (int i = threadIdx.x; i < K; i += blockDim.x) m = fmaxf(m, enorm[i]);
-    for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
-    if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = m;
-    __syncthreads();
-    if (threadIdx.x < 32) {
-        m = threadIdx.x < (blockDim.x >> 5) ? sm[threadIdx.x] : 0.f;
-        for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
-        if (threadIdx.x == 0) *emax = m;
+        if (k < K) {
+            const float en_k = sqrtf(s);
+            enorm[k] = en_k;
+            // emax = max_k enorm[k]: non-negative floats order like their bit patterns (emax is zeroed with the counters)
+            atomicMax(reinterpret_cast<int *>(emax), __float_as_int(en_k));
+        }
     }
 }
 
@@ -654,8 +644,8 @@ inline Workspace carve(void *ws, const Geometry &g) {
     auto take = [&](size_t b) { off = align_up(off, 1024); size_t o = off; off += b; return (char *)ws + o; };
     w.mu = (float *)take(sizeof(float) * g.D);
     w.enorm = (float *)take(sizeof(float) * g.K);
-    w.emax = (float *)take(sizeof(float) * 4);
     w.counters = (int *)take(sizeof(int) * 8);
+    w.emax = (float *)(w.counters + 6);          // zeroed together with the counters, filled by atomicMax
     w.Eb = (op_t *)take((size_t)g.Kp * g.DKp * 2);
     w.Zb = (op_t *)take((size_t)g.Np * g.DKp * 2);
     w.zn = (float *)take(sizeof(float) * g.Np);
@@ -696,13 +686,12 @@ inline size_t vq_tensor_ws_bytes(int64_t n, int D, int K) {
 // pass 0: codebook operand (mu, Eb, enorm, emax) into the workspace; zeroes the counters
 inline int vq_tensor_prep(const float *E, const tc::Geometry &g, const tc::Workspace &w, cudaStream_t st) {
     using namespace tc;
-    ProfScope prof("vq_prep (3 kernels)", st);
+    ProfScope prof("vq_prep (2 kernels)", st);
     LIPVQ_CUDA_OK(cudaMemsetAsync(w.counters, 0, 8 * sizeof(int), st));
     vq_prep_mean_kernel<<<(g.D + 31) / 32, 1024, 0, st>>>(E, g.K, g.D, w.mu);
     LIPVQ_LAUNCH_OK();
-    vq_prep_rows_kernel<<<(g.Kp + 7) / 8, 256, 0, st>>>(E, w.mu, g.K, g.Kp, g.D, g.DKp, w.Eb, w.enorm, w.counters);
-    LIPVQ_LAUNCH_OK();
-    vq_prep_emax_kernel<<<1, 256, 0, st>>>(w.enorm, g.K, w.emax);
+    vq_prep_rows_kernel<<<(g.Kp + 7) / 8, 256, 0, st>>>(E, w.mu, g.K, g.Kp, g.D, g.DKp, w.Eb, w.enorm, w.counters,
+                                                        w.emax);
     LIPVQ_LAUNCH_OK();
     return LIPVQ_OK;
 }

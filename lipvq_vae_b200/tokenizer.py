@@ -87,11 +87,12 @@ class _TokenizerFn(torch.autograd.Function):
         ws = _workspace(dev, dims, n)
         P = _param_struct(N.Params, params)
         need_grad = any(ctx.needs_input_grad[4:])
-        stats = torch.zeros(4, **f32)
+        stats = torch.empty(4, **f32)
         idx = torch.empty(n, dtype=torch.int64, device=dev)
         z_q = torch.empty(n, D, **f32)
-        vq_stats = torch.zeros(4, dtype=torch.int32, device=dev)
+        vq_stats = torch.empty(4, dtype=torch.int32, device=dev)
         if n == 0:
+            stats.zero_(); vq_stats.zero_()
             x_recon = torch.empty(0, F_, **f32)
             ctx.mark_non_differentiable(z_q, idx, vq_stats, x_recon)
             ctx.empty = True
@@ -112,16 +113,14 @@ class _TokenizerFn(torch.autograd.Function):
         c1 = torch.empty(K, H1, **f32); d1 = torch.empty(K, H1, **f32)
         c2 = torch.empty(K, H, **f32); d2 = torch.empty(K, H, **f32)
         xr_code = torch.empty(K, F_, **f32)
-        sse = torch.zeros(2, dtype=torch.float64, device=dev)
+        sse = torch.empty(2, dtype=torch.float64, device=dev)
         A = _acts_struct(a1=a1, h1=h1, a2=a2, h2=h2, scale=scale, Wn=Wn, z_e=z_e, idx=idx, z_q=z_q,
                          c1=c1, d1=d1, c2=c2, d2=d2, xr_code=xr_code, x_recon=x_recon)
         wsz = ws.numel()
         N.check(lib.lipvq_encode_search_fwd(C.byref(dims), C.byref(P), _p(x), n, C.byref(A), search_mode,
                                             _p(vq_stats), _p(ws), wsz, st), "lipvq_encode_search_fwd")
-        N.check(lib.lipvq_quantize_decode_fwd(C.byref(dims), C.byref(P), _p(x), n, C.byref(A), _p(sse), _p(ws),
-                                              wsz, st), "lipvq_quantize_decode_fwd")
-        N.check(lib.lipvq_loss_finalize(_p(sse), C.c_void_p(sse.data_ptr() + 8), n_total, F_, D, _p(stats), st),
-                "lipvq_loss_finalize")
+        N.check(lib.lipvq_quantize_decode_fwd(C.byref(dims), C.byref(P), _p(x), n, n_total, C.byref(A), _p(sse),
+                                              _p(stats), _p(ws), wsz, st), "lipvq_quantize_decode_fwd")
         ctx.save_for_backward(x, *params, a1, h1, a2, h2, scale, Wn, z_e, idx, z_q, c1, d1, c2, d2, xr_code)
         ctx.dims = dims
         ctx.n_total = n_total

@@ -38,7 +38,7 @@ def timeit(fn, iters=10):
 
 
 enc = lambda: N.check(lib.lipvq_encoder_fwd(C.byref(dims), C.byref(P), _p(x), n, C.byref(A), _p(ws), ws.numel(), st))
-dec = lambda: N.check(lib.lipvq_quantize_decode_fwd(C.byref(dims), C.byref(P), _p(x), n, C.byref(A), _p(sse), _p(ws), ws.numel(), st))
+dec = lambda: N.check(lib.lipvq_quantize_decode_fwd(C.byref(dims), C.byref(P), _p(x), n, n, C.byref(A), _p(sse), None, _p(ws), ws.numel(), st))
 vqs = torch.zeros(4, dtype=torch.int32, device=dev)
 A2 = _acts_struct(scale=scale, Wn=Wn, z_e=z_e, idx=idx, z_q=z_q, x_recon=xr)
 es = lambda: N.check(lib.lipvq_encode_search_fwd(C.byref(dims), C.byref(P), _p(x), n, C.byref(A2), 1, _p(vqs), _p(ws), ws.numel(), st))
