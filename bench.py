@@ -28,6 +28,15 @@ WORKLOAD = ("tokenizer encode+quantize+decode, %d chunks x %d rows x %d-D per GP
             % (CHUNKS, CHUNK_LEN, F_DIM, D_LAT, K_CODES))
 
 
+_REAL_STDOUT = None
+
+
+def _emit(obj):
+    out = _REAL_STDOUT or sys.stdout
+    out.write(json.dumps(obj) + "\n")
+    out.flush()
+
+
 def _peaks():
     try:
         return json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))), "measured"
@@ -122,14 +131,14 @@ def run_reference_arm(args, rank, world):
     val = sample_chunks / (ms / 1e3)
     sample = ("%d chunks (%d rows) per step, numpy port of the reference's broadcast-form forward "
               "(v5:37-48 literally), %d threads over row blocks" % (sample_chunks, rows, cores))
-    print(json.dumps({
+    _emit({
         "impl": "reference", "metric": "action chunks tokenized/sec (encode+quantize+decode)", "value": val,
         "unit": "chunks/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": WORKLOAD, "sample": sample},
         "cpu_baseline": {"value": val, "unit": "chunks/s", "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": val, "unit": "chunks/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-    }))
+    })
 
 
 # ------------------------------------------------------------------------------------------ GPU
@@ -388,7 +397,7 @@ def run_ours(args, rank, world, local_rank):
         "kernels_us_per_step": kern_us, "cpu_baseline": cpu_baseline,
         "config2_vq_alone": c2, "hbm_kernel": hbm, "train_step": train,
     }
-    print(json.dumps(out))
+    _emit(out)
 
 
 def main():
@@ -401,6 +410,11 @@ def main():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    # libraries (NCCL's version banner, ...) write to fd 1: keep stdout for the ONE JSON line
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))

@@ -83,7 +83,7 @@ static size_t workspace_bytes_impl(const lipvq_dims_t *d, int64_t n) {
     size_t bytes = fl * sizeof(float) + 64 * 256;    // alignment slack for the bump allocator
     bytes += vq_tensor_ws_bytes(n, d->D, d->K);
     bytes += N * sizeof(int64_t) + 4096;
-    bytes += align_up(2 * kQeBlocks * sizeof(float), 256) + align_up(mlp::kPartBytes, 256) + 1024;
+    bytes += align_up(2 * kQeBlocks * sizeof(float), 256) + 1024;
     bytes += mlp::enc_img_bytes(d->D) + 2048;
     return align_up(bytes, 256);
 }
@@ -315,17 +315,16 @@ int lipvq_decoder_fwd(const lipvq_dims_t *d, const lipvq_params_t *p, const floa
     return LIPVQ_OK;
 }
 
-// scratch of lipvq_quantize_decode_fwd: [sse partials | dec_kernel partials | code-level tensors not supplied]
+// scratch of lipvq_quantize_decode_fwd: [sse partials | xr_code when not supplied]
 static size_t qd_ws_bytes(const lipvq_dims_t *d) {
-    return align_up(2 * kQeBlocks * sizeof(float), 256) + align_up(mlp::kPartBytes, 256) +
+    return align_up(2 * kQeBlocks * sizeof(float), 256) +
            code_level_floats(d) * sizeof(float) + 256;
 }
 
 // R = decoder(E) for every code (v5:62-68, 75-76 applied to the K distinct values z_q can take)
 static int decoder_code_table(const lipvq_dims_t *d, const lipvq_params_t *p, float *c1, float *d1, float *c2,
-                              float *d2, float *R, double *part, cudaStream_t st) {
+                              float *d2, float *R, cudaStream_t st) {
     ProfScope prof("decoder_code_table", st);
-    (void)part;
     const size_t smem = (size_t)CT_CODES * (d->D + d->H1 + d->H) * sizeof(float);
     if (smem > 200 * 1024) return LIPVQ_ESHAPE;
     if (smem > 48 * 1024)
@@ -356,13 +355,12 @@ int lipvq_quantize_decode_fwd(const lipvq_dims_t *d, const lipvq_params_t *p, co
     if (ws_bytes < qd_ws_bytes(d) || !aligned16(ws)) return LIPVQ_EWORKSPACE;
     Bump b(ws, ws_bytes);
     float *part = b.take<float>(2 * kQeBlocks);
-    double *dpart = b.take<double>(mlp::kPartBytes / sizeof(double));
     float *c1 = a->c1, *d1 = a->d1, *c2 = a->c2, *d2 = a->d2, *R = a->xr_code;   // code-level, kept when non-null
     if (!R) R = b.take<float>((size_t)d->K * d->F);
     if (!b.ok()) return LIPVQ_EWORKSPACE;
     // the decoder acts on z_q = E[idx] (v5:47, 75): K distinct inputs, so it runs once per CODE; the per-row
     // work is the streaming pass below (z_q / z_latent write, x_recon = R[idx], both loss sums)
-    LIPVQ_TRY(decoder_code_table(d, p, c1, d1, c2, d2, R, dpart, st));
+    LIPVQ_TRY(decoder_code_table(d, p, c1, d1, c2, d2, R, st));
     const int64_t tiles = (n + QE_ROWS - 1) / QE_ROWS;
     const int grid = (int)(tiles < kQeBlocks ? tiles : kQeBlocks);
     ProfScope prof("quantize_emit_kernel", st);

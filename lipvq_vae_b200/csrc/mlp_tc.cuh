@@ -2,8 +2,7 @@
 //
 //   enc12 : x[N,F] -> h1 = GELU(x W0^T + b0) -> h2 = GELU(h1 W1^T + b1)            (v5:54-59, 71)
 //   lat   : h2[N,128] -> z_e = sigmoid(h2 Wn^T + b),  Wn = W * lipschitz scale     (v5:6-12, 22-24)
-//   dec   : idx[N] -> z_q = E[idx] (v5:47) -> GELU -> GELU -> x_recon (v5:62-68, 75-76),
-//           fused with z_latent write (v5:74), sum (z_q-z_e)^2 (v5:80-81) and sum (x_recon-x)^2 (v5:79)
+//   (the decoder runs once per CODE on the CUDA cores: decoder_code_table_kernel, misc_kernels.cuh)
 //
 // fp32 parity (1e-5) rules out one tf32/bf16 pass, so every GEMM runs as 3xTF32:
 //   A*B ~= A_hi*B_hi + A_lo*B_hi + A_hi*B_lo   (hi = tf32-rounded value, lo = exact remainder)
@@ -335,155 +334,10 @@ lat_kernel(const float *__restrict__ h2, const float *__restrict__ Wn, const flo
     ctx_end(c);
 }
 
-// ------------------------------------------------------------------ dec: idx -> z_q -> d1 -> d2 -> x_recon
-// smem: Wd0 hi|lo (64 x KB0 blocks) | Wd1 hi|lo (128 x 2) | Wo hi|lo (16 x 4) | stage | biases | idx | red | barrier
-// TMEM: z_hi 0 | z_lo D16 | acc1 2*D16 (64)  ->  d1_hi 0 | d1_lo 64 | acc2 128 (128)  ->  d2_hi 256 | d2_lo 384 | acc3 0 (16)
-struct DecLayout {
-    int KB0, img0, img1, img2, w0, w1, w2, stg, bias, idx, red, bar, total;
-};
-__host__ __device__ inline DecLayout dec_layout(int D) {
-    DecLayout l;
-    l.KB0 = blocks32(D);
-    l.img0 = H1 * 128 * l.KB0; l.img1 = HH * 128 * 2; l.img2 = 16 * 128 * 4;
-    l.w0 = 0; l.w1 = l.w0 + 2 * l.img0; l.w2 = l.w1 + 2 * l.img1;
-    l.stg = l.w2 + 2 * l.img2;
-    l.bias = l.stg + STG_BYTES;
-    l.idx = l.bias + (H1 + HH + 16) * 4;
-    l.red = l.idx + TM * 4;
-    l.bar = l.red + 2 * 8 * 8;
-    l.total = l.bar + 16 + 1024;
-    return l;
-}
-
-__global__ void __launch_bounds__(NTHR, 1)
-dec_kernel(const int64_t *__restrict__ idx, const float *__restrict__ E, const float *__restrict__ z_e,
-           const float *__restrict__ x, const float *__restrict__ Wd0, const float *__restrict__ bd0,
-           const float *__restrict__ Wd1, const float *__restrict__ bd1, const float *__restrict__ Wo,
-           const float *__restrict__ bo, int64_t n_rows, int D, int K, int F, float *__restrict__ z_q,
-           float *__restrict__ c1, float *__restrict__ d1, float *__restrict__ c2, float *__restrict__ d2,
-           float *__restrict__ x_recon, double *__restrict__ part /* [gridDim.x][2] = sse_r, sse_q */,
-           float *__restrict__ table_out /* non-null: stop after layer 0 and write src*Wd0^T (no bias) [n,64] */) {
-    extern __shared__ uint8_t smem_raw[];
-    const uint32_t raw = ptx::smem_u32(smem_raw);
-    uint8_t *sm = smem_raw + (((raw + 1023u) & ~1023u) - raw);
-    const uint32_t s0 = ptx::smem_u32(sm);
-    const DecLayout L = dec_layout(D);
-    const int D16 = pad16(D);
-    float *sb0 = reinterpret_cast<float *>(sm + L.bias), *sb1 = sb0 + H1, *sb2 = sb1 + HH;
-    int *sidx = reinterpret_cast<int *>(sm + L.idx);
-    double *sred = reinterpret_cast<double *>(sm + L.red);
-
-    stage_weight(sm + L.w0, sm + L.w0 + L.img0, Wd0, H1, D, H1, L.KB0);
-    stage_weight(sm + L.w1, sm + L.w1 + L.img1, Wd1, HH, H1, HH, 2);
-    stage_weight(sm + L.w2, sm + L.w2 + L.img2, Wo, F, HH, 16, 4);
-    for (int i = threadIdx.x; i < H1; i += NTHR) sb0[i] = table_out ? 0.f : bd0[i];
-    for (int i = threadIdx.x; i < HH; i += NTHR) sb1[i] = bd1[i];
-    for (int i = threadIdx.x; i < 16; i += NTHR) sb2[i] = i < F ? bo[i] : 0.f;
-    ptx::fence_proxy_async();
-    Ctx c = ctx_begin(sm + L.bar, reinterpret_cast<volatile uint32_t *>(sm + L.bar + 8));
-
-    const int64_t n_tiles = (n_rows + TM - 1) / TM;
-    const bool vec_d = (D & 3) == 0, vec_f = (F & 3) == 0;
-    const int r_in = threadIdx.x & 127;
-    const uint32_t t_zhi = c.tmem, t_zlo = c.tmem + D16, t_acc1 = c.tmem + 2 * D16;
-    double sse_q = 0.0, sse_r = 0.0;
-    for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-        const int64_t row0 = tile * TM, row = row0 + r_in;
-        const bool row_ok = row < n_rows;
-        if (threadIdx.x < TM) {   // idx == nullptr: rows come densely from E (= an already gathered z_q)
-            const bool in = row0 + threadIdx.x < n_rows;
-            int64_t k = in ? (idx ? idx[row0 + threadIdx.x] : 0) : -1;
-            sidx[threadIdx.x] = (k >= 0 && (idx == nullptr || k < K)) ? (int)k : -1;
-        }
-        __syncthreads();
-        for (int kb = 0; kb < L.KB0; ++kb) {
-            stage_block_to_tmem(
-                sm + L.stg, kb, D, vec_d,
-                [&](int r) {
-                    const int k = sidx[r];
-                    return k >= 0 ? E + (idx ? (size_t)k : (size_t)(row0 + r)) * D : (const float *)nullptr;
-                },
-                [&](int r, int k0, const float4 &q) {
-                    const size_t o = (size_t)(row0 + r) * D + k0;
-                    const int nv = min(4, D - k0);
-                    if (z_q) {
-                        if (vec_d) *reinterpret_cast<float4 *>(z_q + o) = q;
-                        else { z_q[o] = q.x; if (nv > 1) z_q[o + 1] = q.y; if (nv > 2) z_q[o + 2] = q.z; if (nv > 3) z_q[o + 3] = q.w; }
-                    }
-                    if (z_e) {
-                        float4 e = make_float4(0.f, 0.f, 0.f, 0.f);
-                        if (vec_d) e = __ldg(reinterpret_cast<const float4 *>(z_e + o));
-                        else { e.x = z_e[o]; if (nv > 1) e.y = z_e[o + 1]; if (nv > 2) e.z = z_e[o + 2]; if (nv > 3) e.w = z_e[o + 3]; }
-                        const float dx = q.x - e.x, dy = nv > 1 ? q.y - e.y : 0.f, dz = nv > 2 ? q.z - e.z : 0.f,
-                                    dw = nv > 3 ? q.w - e.w : 0.f;
-                        sse_q += (double)(dx * dx + dy * dy + dz * dz + dw * dw);
-                    }
-                },
-                t_zhi, t_zlo, D16, c.half);
-            __syncthreads();
-        }
-        run_layer(t_acc1, t_zhi, t_zlo, s0 + L.w0, s0 + L.w0 + L.img0, H1, D16 / 8, c.bar, c.phase);
-        if (table_out) {
-            epilogue<ACT_NONE>(t_acc1, H1, H1, sb0, false, 0u, 0u, row_ok ? table_out + row * H1 : nullptr, H1, true,
-                               c.half, NoFn());
-            continue;
-        }
-        {
-            float *d1r = (d1 && row_ok) ? d1 + row * H1 : nullptr;
-            epilogue<ACT_GELU>(t_acc1, H1, H1, sb0, true, c.tmem + 0, c.tmem + 64,
-                               (c1 && row_ok) ? c1 + row * H1 : nullptr, H1, true, c.half,
-                               [&](int c0, int valid, float(&v)[16]) { if (d1r) store_row16(d1r + c0, v, valid, true); });
-        }
-        run_layer(c.tmem + 128, c.tmem + 0, c.tmem + 64, s0 + L.w1, s0 + L.w1 + L.img1, HH, H1 / 8, c.bar, c.phase);
-        {
-            float *d2r = (d2 && row_ok) ? d2 + row * HH : nullptr;
-            epilogue<ACT_GELU>(c.tmem + 128, HH, HH, sb1, true, c.tmem + 256, c.tmem + 384,
-                               (c2 && row_ok) ? c2 + row * HH : nullptr, HH, true, c.half,
-                               [&](int c0, int valid, float(&v)[16]) { if (d2r) store_row16(d2r + c0, v, valid, true); });
-        }
-        run_layer(c.tmem + 0, c.tmem + 256, c.tmem + 384, s0 + L.w2, s0 + L.w2 + L.img2, 16, HH / 8, c.bar, c.phase);
-        epilogue<ACT_NONE>(c.tmem + 0, 16, F, sb2, false, 0u, 0u, nullptr, F, vec_f, c.half,
-                           [&](int c0, int valid, float(&v)[16]) {
-                               if (!row_ok) return;
-                               if (x_recon) store_row16(x_recon + row * F + c0, v, valid, vec_f);
-                               if (x) {
-                                   float s = 0.f;
-#pragma unroll
-                                   for (int i = 0; i < 16; ++i)
-                                       if (i < valid) { const float df = v[i] - __ldg(x + row * F + c0 + i); s = fmaf(df, df, s); }
-                                   sse_r += (double)s;
-                               }
-                           });
-    }
-    // deterministic CTA reduction of the two loss partials (fixed shuffle tree, warps combined in order)
-    sse_r = warp_sum_d(sse_r);
-    sse_q = warp_sum_d(sse_q);
-    __syncthreads();
-    if ((threadIdx.x & 31) == 0) { sred[(threadIdx.x >> 5) * 2] = sse_r; sred[(threadIdx.x >> 5) * 2 + 1] = sse_q; }
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        double a = 0.0, b = 0.0;
-        for (int w = 0; w < NTHR / 32; ++w) { a += sred[2 * w]; b += sred[2 * w + 1]; }
-        part[blockIdx.x * 2] = a;
-        part[blockIdx.x * 2 + 1] = b;
-    }
-    ctx_end(c);
-}
-
-// sse[0] = sum_i part[2i] (recon), sse[1] = sum_i part[2i+1] (quantisation); fixed order
-__global__ void sum_partials2_kernel(const double *__restrict__ part, int n, double *__restrict__ sse) {
-    if (threadIdx.x < 2) {
-        double s = 0.0;
-        for (int i = 0; i < n; ++i) s += part[2 * i + threadIdx.x];
-        sse[threadIdx.x] = s;
-    }
-}
-
 // ------------------------------------------------------------------ host side
 inline bool supported(const lipvq_dims_t *d) {
     return d->H1 == H1 && d->H == HH && d->F >= 1 && d->F <= 16 && d->D >= 1 && d->D <= 208;
 }
-constexpr size_t kPartBytes = (size_t)kNumSMs * 2 * sizeof(double);
 
 template <class Kern>
 inline int set_smem(Kern kern, int bytes) {
@@ -505,24 +359,6 @@ inline int encoder_launch(const lipvq_dims_t *d, const lipvq_params_t *p, const 
     const int lb = lat_smem_bytes(pad16(d->D));
     LIPVQ_TRY(set_smem(lat_kernel, lb));
     lat_kernel<<<grid_for(n), NTHR, lb, st>>>(h2, Wn, p->lat_b, n, d->D, z_e);
-    LIPVQ_LAUNCH_OK();
-    return LIPVQ_OK;
-}
-
-// gather + decoder + both loss sums; sse = device double[2] {sse_r, sse_q}; part = kPartBytes of scratch
-// src = codebook (rows gathered through idx) or, with idx == nullptr, an already gathered z_q [n, D]
-inline int decoder_launch(const lipvq_dims_t *d, const lipvq_params_t *p, const int64_t *idx, const float *src,
-                          const float *z_e,
-                          const float *x, int64_t n, float *z_q, float *c1, float *d1, float *c2, float *d2,
-                          float *x_recon, double *part, double *sse, cudaStream_t st) {
-    const DecLayout L = dec_layout(d->D);
-    LIPVQ_TRY(set_smem(dec_kernel, L.total));
-    const int grid = grid_for(n);
-    dec_kernel<<<grid, NTHR, L.total, st>>>(idx, src, z_e, x, p->dec0_w, p->dec0_b, p->dec2_w, p->dec2_b,
-                                            p->out_w, p->out_b, n, d->D, d->K, d->F, z_q, c1, d1, c2, d2, x_recon,
-                                            part, nullptr);
-    LIPVQ_LAUNCH_OK();
-    sum_partials2_kernel<<<1, 32, 0, st>>>(part, grid, sse);
     LIPVQ_LAUNCH_OK();
     return LIPVQ_OK;
 }
