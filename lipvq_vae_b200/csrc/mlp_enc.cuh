@@ -10,8 +10,10 @@
 //
 // Warps 0..15 (512 threads): staging + epilogues (warp%4 = TMEM lane quarter, warp/4 = 16-column block
 // owner).  Warp 16: control -- one thread issues every tcgen05.mma and every bulk copy.
-// TMEM columns: acc2 -> h2_hi [0,128) | h2_lo [128,256) | acc3 [256,256+D16);
-//               while layers 0/1 run: x_hi 256 | x_lo 320 | acc1 128 | h1_hi 352 | h1_lo 416
+// TMEM columns: h1_hi [0,64) h1_lo [64,128) -> later h2_lo [0,128) | acc1 [128,192) -> acc2 -> h2_hi [128,256) |
+//               acc3 [256,256+D16) | x_hi [464,480) x_lo [480,496).
+// x of tile t+1 has its own columns, and acc1 / h1 reuse columns that are dead once tile t's layer-2 MMAs have
+// completed, so layer 0 of tile t+1 is issued while the epilogue warps are still in tile t's last epilogue.
 #pragma once
 #include "mlp_tc.cuh"
 #include "vq_tensor.cuh"
@@ -176,16 +178,19 @@ enc_fused_kernel(const float *__restrict__ x, const float *__restrict__ W0, cons
                 bulk_g2s(s0 + L::RING + s * ENC_STAGE_BYTES, wn_img + (size_t)c * bytes, bytes, bar_wfull(s));
                 ++g_load;
             };
+            auto issue_layer0 = [&](int t) {   // x of tile t is staged -> acc1
+                ptx::mbar_wait(bar_a(0), t & 1);
+                ptx::tc_fence_after();
+                issue_layer(tmem0 + 128, tmem0 + 464, tmem0 + 480, s0 + L::W0, s0 + L::W0 + L::W0_IMG, H1, k0_steps,
+                            bar_acc(0));
+            };
             for (int t = 0; t < my_tiles; ++t) {
                 const uint32_t par = t & 1;
                 while (g_load < total && g_load < t * NC + 2) load_next();
-                ptx::mbar_wait(bar_a(0), par);
-                ptx::tc_fence_after();
-                issue_layer(tmem0 + 128, tmem0 + 256, tmem0 + 320, s0 + L::W0, s0 + L::W0 + L::W0_IMG, H1, k0_steps,
-                            bar_acc(0));
+                if (t == 0) issue_layer0(0);
                 ptx::mbar_wait(bar_a(1), par);
                 ptx::tc_fence_after();
-                issue_layer(tmem0 + 0, tmem0 + 352, tmem0 + 416, s0 + L::W1, s0 + L::W1 + L::W1_IMG, HH, H1 / 8,
+                issue_layer(tmem0 + 128, tmem0 + 0, tmem0 + 64, s0 + L::W1, s0 + L::W1 + L::W1_IMG, HH, H1 / 8,
                             bar_acc(1));
                 const uint32_t idesc = ptx::umma_idesc_tf32(TM, D16);
                 for (int c = 0; c < NC; ++c) {      // K block c of Wn against h2 columns [32c, 32c+32)
@@ -197,7 +202,7 @@ enc_fused_kernel(const float *__restrict__ x, const float *__restrict__ W0, cons
                     const uint64_t bh = ptx::umma_desc_sw128(st), bl = ptx::umma_desc_sw128(st + D16 * 128);
 #pragma unroll
                     for (int ks = 0; ks < 4; ++ks) {
-                        const uint32_t a_hi = tmem0 + 32 * c + 8 * ks, a_lo = a_hi + 128;
+                        const uint32_t a_lo = tmem0 + 32 * c + 8 * ks, a_hi = a_lo + 128;
                         ptx::umma_tf32_ts(tmem0 + 256, a_hi, bh + 2 * ks, idesc, (c | ks) ? 1u : 0u);
                         ptx::umma_tf32_ts(tmem0 + 256, a_lo, bh + 2 * ks, idesc, 1u);
                         ptx::umma_tf32_ts(tmem0 + 256, a_hi, bl + 2 * ks, idesc, 1u);
@@ -205,6 +210,12 @@ enc_fused_kernel(const float *__restrict__ x, const float *__restrict__ W0, cons
                     ptx::umma_commit(bar_wempty(s));
                     if (c == NC - 1) ptx::umma_commit(bar_acc3(0));
                     while (g_load < total && g_load <= g + 1) load_next();
+                }
+                if (t + 1 < my_tiles) {
+                    // h2 is dead once this tile's layer-2 MMAs have completed: layer 0 of the next tile (its x was
+                    // staged before the epilogue warps started waiting for acc3) overlaps this tile's last epilogue
+                    ptx::mbar_wait(bar_acc3(0), par);
+                    issue_layer0(t + 1);
                 }
             }
         }
@@ -257,21 +268,19 @@ enc_fused_kernel(const float *__restrict__ x, const float *__restrict__ W0, cons
                 if (lane == 0) ptx::bulk_wait_read<0>();
                 __syncwarp();
             }
-            // ---- x -> A operand (hi/lo)
-            if (sub == 0) store_split16(tm + 256, tm + 320, xv);
-            a_ready_arrive(bar_a(0));
-            fetch_x(tile + gridDim.x);               // next tile's x flies during this tile
+            // ---- x -> A operand (hi/lo): only the first tile stages here, later tiles were staged during the
+            //      previous tile (below, before its acc3 wait)
+            if (t == 0) {
+                if (sub == 0) store_split16(tm + 464, tm + 480, xv);
+                a_ready_arrive(bar_a(0));
+                fetch_x(tile + gridDim.x);
+            }
             ENC_TICK(0);
             // ---- layer 0 epilogue: h1
             ptx::mbar_wait(bar_acc(0), par);
             ptx::tc_fence_after();
-            if (zn_rows >= 0) {
-                if (sub == 0 && lane < zn_rows)
-                    zn[zn_row0 + lane] = sqrtf(((sznp[r_in] + sznp[TM + r_in]) + sznp[2 * TM + r_in]) + sznp[3 * TM + r_in]);
-                zn_rows = -1;
-            }
             ENC_TICK(1);
-            epilogue_blocks<ACT_GELU_FAST>(tm + 128, 0, H1 / 16, sub, 4, H1, sb0, true, tm + 352, tm + 416, wbuf,
+            epilogue_blocks<ACT_GELU_FAST>(tm + 128, 0, H1 / 16, sub, 4, H1, sb0, true, tm + 0, tm + 64, wbuf,
                                            a1 ? a1 + wrow0 * H1 : nullptr, h1 ? h1 + wrow0 * H1 : nullptr, H1,
                                            rows_valid, true, NoAfter());
             a_ready_arrive(bar_a(1));
@@ -279,10 +288,21 @@ enc_fused_kernel(const float *__restrict__ x, const float *__restrict__ W0, cons
             // ---- layer 1 epilogue: h2 (hi written in place over the accumulator columns just read)
             ptx::mbar_wait(bar_acc(1), par);
             ptx::tc_fence_after();
+            if (zn_rows >= 0) {   // (every warp passed the previous tile's last epilogue before acc2 could complete)
+                if (sub == 0 && lane < zn_rows)
+                    zn[zn_row0 + lane] = sqrtf(((sznp[r_in] + sznp[TM + r_in]) + sznp[2 * TM + r_in]) + sznp[3 * TM + r_in]);
+                zn_rows = -1;
+            }
             ENC_TICK(3);
-            epilogue_blocks<ACT_GELU_FAST>(tm + 0, 0, HH / 16, sub, 4, HH, sb1, true, tm + 0, tm + 128, wbuf,
+            epilogue_blocks<ACT_GELU_FAST>(tm + 128, 0, HH / 16, sub, 4, HH, sb1, true, tm + 128, tm + 0, wbuf,
                                            a2 ? a2 + wrow0 * HH : nullptr, h2 ? h2 + wrow0 * HH : nullptr, HH,
                                            rows_valid, true, [&](int cb) { a_ready_arrive(bar_a2(cb >> 1)); });
+            // ---- next tile's x -> its own TMEM columns (layer 0 of tile t+1 runs during this tile's last epilogue)
+            if (tile + gridDim.x < n_tiles) {
+                if (sub == 0) store_split16(tm + 464, tm + 480, xv);
+                a_ready_arrive(bar_a(0));
+                fetch_x(tile + 2 * (int64_t)gridDim.x);
+            }
             ENC_TICK(4);
             // ---- layer 2 epilogue: sigmoid and store z_e
             ptx::mbar_wait(bar_acc3(0), par);
@@ -378,7 +398,7 @@ enc_fused_kernel(const float *__restrict__ x, const float *__restrict__ W0, cons
                     // any |z - mu| beyond the 16-bit operand range (or a NaN) makes the partial norm fail this test
                     zbad |= !(ss <= tc::OP_MAX * tc::OP_MAX);
                     // the four column owners of a row leave their partial norms in shared memory; they are combined
-                    // (fixed order) after the NEXT tile's first accumulator wait, which every thread of this tile
+                    // (fixed order) after the NEXT tile's layer-1 accumulator wait, which every thread of this tile
                     // has passed its epilogue to reach -- no extra barrier
                     sznp[sub * TM + r_in] = ss;
                     zn_row0 = wrow0;
