@@ -2,6 +2,9 @@
 // of the tokenizer (v5:54-68) and their backward.  Exact fp32 FMA arithmetic (the 1e-5 parity
 // tier); strides are generic so one kernel serves X*W^T, dY*W and dY^T*X (split over rows).
 #pragma once
+#include <cstdlib>
+#include <cstring>
+
 #include "common.cuh"
 
 namespace lipvq {
@@ -117,6 +120,146 @@ __global__ void __launch_bounds__(GNT) gemm_simt_kernel(const GemmArgs g) {
     }
 }
 
+// ---------------------------------------------------------------- 3xTF32 variant for the big backward GEMMs
+// Same tiling, operand staging and fused epilogue as gemm_simt_kernel, but the 64x64x16 tile product runs on the
+// tensor cores as three tf32 mma.sync passes (a_hi*b_hi + a_lo*b_hi + a_hi*b_lo, hi = cvt.rna.tf32, lo = exact
+// remainder): fp32-grade products.  The mma accumulators are folded into plain fp32 (round-to-nearest) sums after
+// every 16-deep slab, so a reduction over 10^5..10^6 rows (weight gradients) does not inherit the tensor core's
+// accumulation rounding.  8 warps = 2 (m) x 4 (n); a warp owns 32x16 = 2x2 m16n8 tiles.
+constexpr int TLD = 72;   // slab row pitch: lane (g, t) reads word t*72 + g -> 32 distinct banks
+__device__ __forceinline__ void split_tf32_rna(float v, uint32_t &hi, uint32_t &lo) {
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(hi) : "f"(v));
+    lo = __float_as_uint(v - __uint_as_float(hi));
+}
+__device__ __forceinline__ void mma_tf32_16x8x8(float (&c)[4], const uint32_t (&a)[4], const uint32_t (&b)[2]) {
+    asm volatile(
+        "mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+        : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+        : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b[0]), "r"(b[1]));
+}
+
+template <int ACT, int DACT, bool A_KC, bool B_KC>
+__global__ void __launch_bounds__(GNT) gemm_tc3_kernel(const GemmArgs g) {
+    __shared__ __align__(16) float As[GBK][TLD];
+    __shared__ __align__(16) float Bs[GBK][TLD];
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int wm = warp >> 2, wn = warp & 3, gq = lane >> 2, tq = lane & 3;
+    const int64_t m0 = (int64_t)blockIdx.x * GBM;
+    const int n0 = blockIdx.y * GBN;
+    int64_t kbeg = 0, kend = g.K;
+    if (g.k_chunk > 0) {
+        kbeg = (int64_t)blockIdx.z * g.k_chunk;
+        kend = kbeg + g.k_chunk < g.K ? kbeg + g.k_chunk : g.K;
+    }
+    float acc[2][2][4];
+#pragma unroll
+    for (int i = 0; i < 2; ++i)
+#pragma unroll
+        for (int j = 0; j < 2; ++j)
+#pragma unroll
+            for (int q = 0; q < 4; ++q) acc[i][j][q] = 0.f;
+
+    float ra[4], rb[4];
+    auto fetch = [&](int64_t k0) {
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const int e = tid + q * GNT;
+            int m, k;
+            if (A_KC) { k = e & (GBK - 1); m = e >> 4; } else { m = e & (GBM - 1); k = e >> 6; }
+            const int64_t gm = m0 + m, gk = k0 + k;
+            ra[q] = (gm < g.M && gk < kend) ? __ldg(g.A + gm * g.sam + gk * g.sak) : 0.f;
+            int n, kb;
+            if (B_KC) { kb = e & (GBK - 1); n = e >> 4; } else { n = e & (GBN - 1); kb = e >> 6; }
+            const int gn = n0 + n;
+            const int64_t gkb = k0 + kb;
+            float v = 0.f;
+            if (gn < g.N && gkb < kend)
+                v = (gn == g.b_ones_col) ? 1.f : __ldg(g.B + gkb * g.sbk + (int64_t)gn * g.sbn);
+            rb[q] = v;
+        }
+    };
+    auto stash = [&]() {
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const int e = tid + q * GNT;
+            int m, k;
+            if (A_KC) { k = e & (GBK - 1); m = e >> 4; } else { m = e & (GBM - 1); k = e >> 6; }
+            As[k][m] = ra[q];
+            int n, kb;
+            if (B_KC) { kb = e & (GBK - 1); n = e >> 4; } else { n = e & (GBN - 1); kb = e >> 6; }
+            Bs[kb][n] = rb[q];
+        }
+    };
+
+    if (kbeg < kend) fetch(kbeg);
+    for (int64_t k0 = kbeg; k0 < kend; k0 += GBK) {
+        stash();
+        __syncthreads();
+        if (k0 + GBK < kend) fetch(k0 + GBK);
+        float slab[2][2][4];
+#pragma unroll
+        for (int i = 0; i < 2; ++i)
+#pragma unroll
+            for (int j = 0; j < 2; ++j)
+#pragma unroll
+                for (int q = 0; q < 4; ++q) slab[i][j][q] = 0.f;
+#pragma unroll
+        for (int ks = 0; ks < GBK; ks += 8) {
+            uint32_t ah[2][4], al[2][4], bh[2][2], bl[2][2];
+#pragma unroll
+            for (int i = 0; i < 2; ++i) {
+                const int m = wm * 32 + i * 16 + gq;
+                split_tf32_rna(As[ks + tq][m], ah[i][0], al[i][0]);
+                split_tf32_rna(As[ks + tq][m + 8], ah[i][1], al[i][1]);
+                split_tf32_rna(As[ks + tq + 4][m], ah[i][2], al[i][2]);
+                split_tf32_rna(As[ks + tq + 4][m + 8], ah[i][3], al[i][3]);
+            }
+#pragma unroll
+            for (int j = 0; j < 2; ++j) {
+                const int n = wn * 16 + j * 8 + gq;
+                split_tf32_rna(Bs[ks + tq][n], bh[j][0], bl[j][0]);
+                split_tf32_rna(Bs[ks + tq + 4][n], bh[j][1], bl[j][1]);
+            }
+#pragma unroll
+            for (int i = 0; i < 2; ++i)
+#pragma unroll
+                for (int j = 0; j < 2; ++j) {
+                    mma_tf32_16x8x8(slab[i][j], al[i], bh[j]);
+                    mma_tf32_16x8x8(slab[i][j], ah[i], bl[j]);
+                    mma_tf32_16x8x8(slab[i][j], ah[i], bh[j]);
+                }
+        }
+#pragma unroll
+        for (int i = 0; i < 2; ++i)
+#pragma unroll
+            for (int j = 0; j < 2; ++j)
+#pragma unroll
+                for (int q = 0; q < 4; ++q) acc[i][j][q] += slab[i][j][q];
+        __syncthreads();
+    }
+
+    float *C = g.C;
+    const float aux_alpha = g.aux_alpha * ((g.aux1 && g.aux_scale_dev) ? __ldg(g.aux_scale_dev) : 1.f);
+    if (g.k_chunk > 0) C += (int64_t)blockIdx.z * g.M * g.ldc;
+#pragma unroll
+    for (int i = 0; i < 2; ++i)
+#pragma unroll
+        for (int j = 0; j < 2; ++j)
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const int64_t m = m0 + wm * 32 + i * 16 + gq + (q >> 1) * 8;
+                const int n = n0 + wn * 16 + j * 8 + 2 * tq + (q & 1);
+                if (m >= g.M || n >= g.N) continue;
+                float v = g.alpha * acc[i][j][q];
+                if (g.bias) v += __ldg(g.bias + n);
+                if (g.pre) g.pre[m * g.ldpre + n] = v;
+                v = apply_act<ACT>(v);
+                if (DACT == ACT_GELU) v *= gelu_grad_f(__ldg(g.dpre + m * g.lddpre + n));
+                if (g.aux1) v += aux_alpha * (__ldg(g.aux1 + m * g.ldaux + n) - __ldg(g.aux2 + m * g.ldaux + n));
+                C[m * g.ldc + n] = v;
+            }
+}
+
 inline GemmArgs gemm_args_zero() {
     GemmArgs g;
     g.A = nullptr; g.sam = g.sak = 0; g.B = nullptr; g.sbk = g.sbn = 0; g.C = nullptr; g.ldc = 0;
@@ -130,6 +273,15 @@ template <int ACT, int DACT, bool A_KC, bool B_KC>
 inline int gemm_launch(const GemmArgs &g, int splits, cudaStream_t st) {
     if (g.M <= 0 || g.N <= 0) return LIPVQ_OK;
     dim3 grid((unsigned)((g.M + GBM - 1) / GBM), (unsigned)((g.N + GBN - 1) / GBN), (unsigned)splits);
+    // big products (the N-row backward GEMMs) go to the 3xTF32 tensor-core variant; LIPVQ_GEMM=simt forces FFMA
+    static const bool simt = [] { const char *e = getenv("LIPVQ_GEMM"); return e && !strcmp(e, "simt"); }();
+    if (!simt && (double)g.M * g.N * (double)g.K >= 1.0e7) {
+        ProfScope prof("gemm_tc3_kernel", st);
+        gemm_tc3_kernel<ACT, DACT, A_KC, B_KC><<<grid, GNT, 0, st>>>(g);
+        LIPVQ_LAUNCH_OK();
+        return LIPVQ_OK;
+    }
+    ProfScope prof("gemm_simt_kernel", st);
     gemm_simt_kernel<ACT, DACT, A_KC, B_KC><<<grid, GNT, 0, st>>>(g);
     LIPVQ_LAUNCH_OK();
     return LIPVQ_OK;
@@ -188,10 +340,142 @@ inline size_t splitk_ws_floats(int64_t rows, int Nout, int Kin) {
     return (size_t)splits_for_rows(rows, Nout, Kin) * Nout * (Kin + 1);
 }
 
+// ---------------------------------------------------------------- weight gradient on the tensor cores
+// part[z][Nout][Kin+1] = dY[rows_z, Nout]^T [X[rows_z, Kin] | 1]  for the row range of split z (3xTF32 mma.sync).
+// The reduction axis is the ROW axis (10^5..10^6 long): both operands stream through a 4-stage cp.async pipeline
+// of 32-row slabs (16-byte copies, zero-filled past the edges), a CTA owns a 64 x 64 tile of dW for its row range;
+// the bias column (column sums of dY) is accumulated by 64 threads of the first column tile from the same slabs.
+// Needs Nout % 4 == 0, Kin % 4 == 0 and 16-byte aligned operands (row pitches are then 16-byte multiples).
+constexpr int WG_BK = 32, WG_ST = 4;
+__device__ __forceinline__ void cp_async16(void *dst, const void *src, bool valid) {
+    const uint32_t d = (uint32_t)__cvta_generic_to_shared(dst);
+    const int sz = valid ? 16 : 0;
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(d), "l"(src), "r"(sz) : "memory");
+}
+__global__ void __launch_bounds__(GNT) wgrad_tc3_kernel(const float *__restrict__ dY, const float *__restrict__ X,
+                                                        int64_t rows, int Nout, int Kin, int64_t k_chunk,
+                                                        float *__restrict__ part) {
+    extern __shared__ __align__(16) float wg_smem[];
+    float(*As)[WG_BK][TLD] = reinterpret_cast<float(*)[WG_BK][TLD]>(wg_smem);
+    float(*Bs)[WG_BK][TLD] = reinterpret_cast<float(*)[WG_BK][TLD]>(wg_smem + WG_ST * WG_BK * TLD);
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int wm = warp >> 2, wn = warp & 3, gq = lane >> 2, tq = lane & 3;
+    const int m0 = blockIdx.x * GBM, n0 = blockIdx.y * GBN;
+    const int64_t kbeg = (int64_t)blockIdx.z * k_chunk;
+    const int64_t kend = kbeg + k_chunk < rows ? kbeg + k_chunk : rows;
+    const int n_slabs = kbeg < kend ? (int)((kend - kbeg + WG_BK - 1) / WG_BK) : 0;
+    // copy assignment: 32 rows x 16 float4 per operand per slab = 512 copies each, 2 + 2 per thread
+    auto issue = [&](int slab, int stage) {
+        const int64_t r0 = kbeg + (int64_t)slab * WG_BK;
+#pragma unroll
+        for (int q = 0; q < 2; ++q) {
+            const int e = tid + q * GNT, r = e >> 4, c = (e & 15) << 2;
+            const int64_t row = r0 + r;
+            const bool rok = slab < n_slabs && row < kend;
+            const bool aok = rok && m0 + c < Nout, bok = rok && n0 + c < Kin;
+            cp_async16(&As[stage][r][c], aok ? dY + row * Nout + m0 + c : dY, aok);
+            cp_async16(&Bs[stage][r][c], bok ? X + row * Kin + n0 + c : X, bok);
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+    float acc[2][2][4];
+#pragma unroll
+    for (int i = 0; i < 2; ++i)
+#pragma unroll
+        for (int j = 0; j < 2; ++j)
+#pragma unroll
+            for (int q = 0; q < 4; ++q) acc[i][j][q] = 0.f;
+    float bsum = 0.f;
+    for (int s = 0; s < WG_ST - 1; ++s) issue(s, s);
+    for (int slab = 0; slab < n_slabs; ++slab) {
+        const int stage = slab % WG_ST;
+        asm volatile("cp.async.wait_group %0;" ::"n"(WG_ST - 2) : "memory");
+        __syncthreads();                                   // slab landed; everyone left the stage refilled below
+        issue(slab + WG_ST - 1, (slab + WG_ST - 1) % WG_ST);
+        float part_acc[2][2][4];
+#pragma unroll
+        for (int i = 0; i < 2; ++i)
+#pragma unroll
+            for (int j = 0; j < 2; ++j)
+#pragma unroll
+                for (int q = 0; q < 4; ++q) part_acc[i][j][q] = 0.f;
+#pragma unroll
+        for (int ks = 0; ks < WG_BK; ks += 8) {
+            uint32_t ah[2][4], al[2][4], bh[2][2], bl[2][2];
+#pragma unroll
+            for (int i = 0; i < 2; ++i) {
+                const int m = wm * 32 + i * 16 + gq;
+                split_tf32_rna(As[stage][ks + tq][m], ah[i][0], al[i][0]);
+                split_tf32_rna(As[stage][ks + tq][m + 8], ah[i][1], al[i][1]);
+                split_tf32_rna(As[stage][ks + tq + 4][m], ah[i][2], al[i][2]);
+                split_tf32_rna(As[stage][ks + tq + 4][m + 8], ah[i][3], al[i][3]);
+            }
+#pragma unroll
+            for (int j = 0; j < 2; ++j) {
+                const int n = wn * 16 + j * 8 + gq;
+                split_tf32_rna(Bs[stage][ks + tq][n], bh[j][0], bl[j][0]);
+                split_tf32_rna(Bs[stage][ks + tq + 4][n], bh[j][1], bl[j][1]);
+            }
+#pragma unroll
+            for (int i = 0; i < 2; ++i)
+#pragma unroll
+                for (int j = 0; j < 2; ++j) {
+                    mma_tf32_16x8x8(part_acc[i][j], al[i], bh[j]);
+                    mma_tf32_16x8x8(part_acc[i][j], ah[i], bl[j]);
+                    mma_tf32_16x8x8(part_acc[i][j], ah[i], bh[j]);
+                }
+        }
+#pragma unroll
+        for (int i = 0; i < 2; ++i)
+#pragma unroll
+            for (int j = 0; j < 2; ++j)
+#pragma unroll
+                for (int q = 0; q < 4; ++q) acc[i][j][q] += part_acc[i][j][q];
+        if (blockIdx.y == 0 && tid < GBM) {                // bias gradient: column sums of dY
+            float t = 0.f;
+#pragma unroll
+            for (int k = 0; k < WG_BK; ++k) t += As[stage][k][tid];
+            bsum += t;
+        }
+    }
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    const int ld = Kin + 1;
+    float *C = part + (size_t)blockIdx.z * Nout * ld;
+#pragma unroll
+    for (int i = 0; i < 2; ++i)
+#pragma unroll
+        for (int j = 0; j < 2; ++j)
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const int m = m0 + wm * 32 + i * 16 + gq + (q >> 1) * 8;
+                const int n = n0 + wn * 16 + j * 8 + 2 * tq + (q & 1);
+                if (m < Nout && n < Kin) C[(size_t)m * ld + n] = acc[i][j][q];
+            }
+    if (blockIdx.y == 0 && tid < GBM && m0 + tid < Nout) C[(size_t)(m0 + tid) * ld + Kin] = bsum;
+}
+
 // dW[Nout,Kin] = dY[rows,Nout]^T X[rows,Kin];  db[Nout] = column sums of dY.  part = scratch.
 inline int linear_bwd_weight(const float *dY, const float *X, float *dW, float *db, int64_t rows,
                              int Nout, int Kin, float *part, cudaStream_t st) {
     const int splits = splits_for_rows(rows, Nout, Kin);
+    static const bool simt = [] { const char *e = getenv("LIPVQ_GEMM"); return e && !strcmp(e, "simt"); }();
+    if (!simt && (Nout & 3) == 0 && (Kin & 3) == 0 && aligned16(dY) && aligned16(X) &&
+        (double)rows * Nout * Kin >= 1.0e7) {
+        int64_t k_chunk = (rows + splits - 1) / splits;
+        k_chunk = (k_chunk + WG_BK - 1) / WG_BK * WG_BK;
+        const int smem = 2 * WG_ST * WG_BK * TLD * (int)sizeof(float);
+        LIPVQ_CUDA_OK(cudaFuncSetAttribute(wgrad_tc3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        dim3 grid((unsigned)((Nout + GBM - 1) / GBM), (unsigned)((Kin + GBN - 1) / GBN), (unsigned)splits);
+        {
+            ProfScope prof("wgrad_tc3_kernel", st);
+            wgrad_tc3_kernel<<<grid, GNT, smem, st>>>(dY, X, rows, Nout, Kin, k_chunk, part);
+            LIPVQ_LAUNCH_OK();
+        }
+        const int total = Nout * (Kin + 1);
+        splitk_reduce_kernel<<<(total + 255) / 256, 256, 0, st>>>(part, splits, Nout, Kin, dW, db);
+        LIPVQ_LAUNCH_OK();
+        return LIPVQ_OK;
+    }
     GemmArgs g = gemm_args_zero();
     g.A = dY; g.sam = 1; g.sak = Nout;
     g.B = X; g.sbk = Kin; g.sbn = 1;

@@ -17,3 +17,15 @@ for it in range(3):
     loss.backward()
     e.record(); torch.cuda.synchronize()
     print("fwd+bwd %.3f ms" % s.elapsed_time(e))
+
+from lipvq_vae_b200 import _native as N
+def step(i):
+    for p in m.parameters():
+        p.grad = None
+    z, loss = m(x)
+    loss.backward()
+prof = N.profile_kernels(step, 3)
+tot = 0.0
+for k, (c, ms) in sorted(prof.items(), key=lambda kv: -kv[1][1]):
+    print("  %-28s %3d launches/step %9.1f us/step" % (k, c // 3, 1e3 * ms / 3)); tot += 1e3 * ms / 3
+print("  profiled kernels total %.1f us/step" % tot)
