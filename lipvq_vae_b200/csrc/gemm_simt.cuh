@@ -299,11 +299,149 @@ inline int linear_fwd(const float *X, const float *W, const float *b, float *pre
     return gemm_launch<ACT, ACT_NONE, true, true>(g, 1, st);
 }
 
+__device__ __forceinline__ void cp_async16(void *dst, const void *src, bool valid) {
+    const uint32_t d = (uint32_t)__cvta_generic_to_shared(dst);
+    const int sz = valid ? 16 : 0;
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(d), "l"(src), "r"(sz) : "memory");
+}
+
+// ---------------------------------------------------------------- input gradient on the tensor cores
+// dX[M, KK] = (dY[M, Nn] W[Nn, KK]) (.) gelu'(dpre[M, KK])   (KK = 64 or 128 output columns, 3xTF32 mma.sync).
+// Persistent CTAs: W stays in shared memory for the CTA's lifetime, dY streams through a 3-stage cp.async pipeline
+// of [128 rows x 32 k] slabs that runs across row-tile boundaries; 8 warps = (8/WN) x WN with WN = KK/32, a warp
+// owns (128*WN/8) rows x 32 columns.  Needs Nn % 4 == 0 and 16-byte aligned operands.
+constexpr int DG_BM = 128, DG_BK = 32, DG_ST = 3, DG_ALD = DG_BK + 4;
+template <int KK, int DACT>
+__global__ void __launch_bounds__(GNT, 1) dgrad_tc3_kernel(const float *__restrict__ dY, const float *__restrict__ W,
+                                                           const float *__restrict__ dpre, float *__restrict__ dX,
+                                                           int64_t M, int Nn) {
+    constexpr int WN = KK / 32, WM = 8 / WN, MF = DG_BM / WM / 16, BLD = KK + 8;
+    extern __shared__ __align__(16) float dg_smem[];
+    float *Bs = dg_smem;                                             // [Nn_pad][BLD]
+    const int n_slabs = (Nn + DG_BK - 1) / DG_BK;
+    float(*As)[DG_BM][DG_ALD] = reinterpret_cast<float(*)[DG_BM][DG_ALD]>(dg_smem + (size_t)n_slabs * DG_BK * BLD);
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int wm = warp / WN, wn = warp % WN, gq = lane >> 2, tq = lane & 3;
+    for (int i = tid; i < n_slabs * DG_BK * (KK / 4); i += GNT) {
+        const int k = i / (KK / 4), c = (i - k * (KK / 4)) << 2;
+        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (k < Nn) v = __ldg(reinterpret_cast<const float4 *>(W + (size_t)k * KK + c));
+        *reinterpret_cast<float4 *>(Bs + (size_t)k * BLD + c) = v;
+    }
+    const int64_t n_tiles = (M + DG_BM - 1) / DG_BM;
+    const int64_t my_tiles = blockIdx.x < n_tiles ? (n_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+    const int64_t total = my_tiles * n_slabs;
+    auto issue = [&](int64_t s) {
+        if (s < total) {
+            const int64_t tile = blockIdx.x + (s / n_slabs) * gridDim.x;
+            const int slab = (int)(s % n_slabs), stage = (int)(s % DG_ST);
+            const int64_t r0 = tile * DG_BM;
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {                           // 128 rows x 8 float4 = 1024 copies
+                const int e = tid + q * GNT, r = e >> 3, c = (e & 7) << 2;
+                const int k = slab * DG_BK + c;
+                const bool ok = r0 + r < M && k < Nn;
+                cp_async16(&As[stage][r][c], ok ? dY + (r0 + r) * Nn + k : dY, ok);
+            }
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+    for (int s = 0; s < DG_ST - 1; ++s) issue(s);
+    float acc[MF][4][4];
+    for (int64_t s = 0; s < total; ++s) {
+        const int slab = (int)(s % n_slabs), stage = (int)(s % DG_ST);
+        if (slab == 0) {
+#pragma unroll
+            for (int i = 0; i < MF; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) acc[i][j][q] = 0.f;
+        }
+        asm volatile("cp.async.wait_group %0;" ::"n"(DG_ST - 2) : "memory");
+        __syncthreads();
+        issue(s + DG_ST - 1);
+        const float *Bk = Bs + (size_t)slab * DG_BK * BLD;
+#pragma unroll
+        for (int ks = 0; ks < DG_BK; ks += 8) {
+            uint32_t bh[4][2], bl[4][2];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const int n = wn * 32 + j * 8 + gq;
+                split_tf32_rna(Bk[(ks + tq) * BLD + n], bh[j][0], bl[j][0]);
+                split_tf32_rna(Bk[(ks + tq + 4) * BLD + n], bh[j][1], bl[j][1]);
+            }
+#pragma unroll
+            for (int i = 0; i < MF; ++i) {
+                const int m = wm * (MF * 16) + i * 16 + gq;
+                uint32_t ah[4], al[4];
+                split_tf32_rna(As[stage][m][ks + tq], ah[0], al[0]);
+                split_tf32_rna(As[stage][m + 8][ks + tq], ah[1], al[1]);
+                split_tf32_rna(As[stage][m][ks + tq + 4], ah[2], al[2]);
+                split_tf32_rna(As[stage][m + 8][ks + tq + 4], ah[3], al[3]);
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    mma_tf32_16x8x8(acc[i][j], al, bh[j]);
+                    mma_tf32_16x8x8(acc[i][j], ah, bl[j]);
+                    mma_tf32_16x8x8(acc[i][j], ah, bh[j]);
+                }
+            }
+        }
+        if (slab == n_slabs - 1) {
+            const int64_t tile = blockIdx.x + (s / n_slabs) * gridDim.x;
+#pragma unroll
+            for (int i = 0; i < MF; ++i)
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    const int64_t m = tile * DG_BM + wm * (MF * 16) + i * 16 + gq + h * 8;
+                    if (m >= M) continue;
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        const int n = wn * 32 + j * 8 + 2 * tq;
+                        float2 v = make_float2(acc[i][j][2 * h], acc[i][j][2 * h + 1]);
+                        if (DACT == ACT_GELU) {
+                            const float2 a = __ldg(reinterpret_cast<const float2 *>(dpre + m * KK + n));
+                            v.x *= gelu_grad_f(a.x);
+                            v.y *= gelu_grad_f(a.y);
+                        }
+                        *reinterpret_cast<float2 *>(dX + m * KK + n) = v;
+                    }
+                }
+        }
+    }
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+}
+
+template <int KK, int DACT>
+inline int dgrad_tc3_launch(const float *dY, const float *W, const float *dpre, float *dX, int64_t M, int Nn,
+                            cudaStream_t st) {
+    const int n_slabs = (Nn + DG_BK - 1) / DG_BK;
+    const size_t smem = ((size_t)n_slabs * DG_BK * (KK + 8) + (size_t)DG_ST * DG_BM * DG_ALD) * sizeof(float);
+    if (smem > 220 * 1024) return LIPVQ_ESHAPE;
+    LIPVQ_CUDA_OK(cudaFuncSetAttribute(dgrad_tc3_kernel<KK, DACT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)smem));
+    const int64_t tiles = (M + DG_BM - 1) / DG_BM;
+    const int per_sm = smem <= 110 * 1024 ? 2 : 1;
+    const int grid = (int)(tiles < per_sm * kNumSMs ? tiles : per_sm * kNumSMs);
+    ProfScope prof("dgrad_tc3_kernel", st);
+    dgrad_tc3_kernel<KK, DACT><<<grid, GNT, smem, st>>>(dY, W, dpre, dX, M, Nn);
+    LIPVQ_LAUNCH_OK();
+    return LIPVQ_OK;
+}
+
 // dX[M,K] = (dY[M,N] W[N,K]) (.) DACT'(dpre[M,K])  (+ aux_alpha*(aux1-aux2))
 template <int DACT>
 inline int linear_bwd_input(const float *dY, const float *W, const float *dpre, float *dX,
                             int64_t M, int N, int K, const float *aux1, const float *aux2,
                             float aux_alpha, const float *aux_scale_dev, cudaStream_t st) {
+    static const bool simt = [] { const char *e = getenv("LIPVQ_GEMM"); return e && !strcmp(e, "simt"); }();
+    if (!simt && !aux1 && (K == 64 || K == 128) && (N & 3) == 0 && aligned16(dY) && aligned16(W) && aligned16(dX) &&
+        (DACT == ACT_NONE || aligned16(dpre)) && (double)M * N * K >= 1.0e7) {
+        const size_t smem = ((size_t)((N + DG_BK - 1) / DG_BK) * DG_BK * (K + 8) + (size_t)DG_ST * DG_BM * DG_ALD) * 4;
+        if (smem <= 220 * 1024)
+            return K == 64 ? dgrad_tc3_launch<64, DACT>(dY, W, dpre, dX, M, N, st)
+                           : dgrad_tc3_launch<128, DACT>(dY, W, dpre, dX, M, N, st);
+    }
     GemmArgs g = gemm_args_zero();
     g.A = dY; g.sam = N; g.sak = 1;
     g.B = W; g.sbk = K; g.sbn = 1;
@@ -347,11 +485,6 @@ inline size_t splitk_ws_floats(int64_t rows, int Nout, int Kin) {
 // the bias column (column sums of dY) is accumulated by 64 threads of the first column tile from the same slabs.
 // Needs Nout % 4 == 0, Kin % 4 == 0 and 16-byte aligned operands (row pitches are then 16-byte multiples).
 constexpr int WG_BK = 32, WG_ST = 4;
-__device__ __forceinline__ void cp_async16(void *dst, const void *src, bool valid) {
-    const uint32_t d = (uint32_t)__cvta_generic_to_shared(dst);
-    const int sz = valid ? 16 : 0;
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(d), "l"(src), "r"(sz) : "memory");
-}
 __global__ void __launch_bounds__(GNT) wgrad_tc3_kernel(const float *__restrict__ dY, const float *__restrict__ X,
                                                         int64_t rows, int Nout, int Kin, int64_t k_chunk,
                                                         float *__restrict__ part) {

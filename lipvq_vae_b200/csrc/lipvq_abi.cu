@@ -330,7 +330,7 @@ static int decoder_code_table(const lipvq_dims_t *d, const lipvq_params_t *p, fl
     if (smem > 48 * 1024)
         LIPVQ_CUDA_OK(cudaFuncSetAttribute(decoder_code_table_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                            (int)smem));
-    decoder_code_table_kernel<<<(d->K + CT_CODES - 1) / CT_CODES, 256, smem, st>>>(
+    decoder_code_table_kernel<<<(d->K + CT_CODES - 1) / CT_CODES, 512, smem, st>>>(
         p->codebook, p->dec0_w, p->dec0_b, p->dec2_w, p->dec2_b, p->out_w, p->out_b, d->K, d->D, d->H1, d->H, d->F, c1,
         d1, c2, d2, R);
     LIPVQ_LAUNCH_OK();

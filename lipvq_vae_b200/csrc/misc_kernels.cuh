@@ -202,31 +202,46 @@ __device__ __forceinline__ void ct_layer(const float *__restrict__ W, const floa
                                          float *__restrict__ g_pre, float *__restrict__ g_post, int ld, int code0,
                                          int n_codes) {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarp = blockDim.x >> 5;
-    for (int j = warp; j < n_out; j += nwarp) {
-        float acc[CT_CODES];
+    constexpr int NJ = 4;   // output neurons in flight per warp: NJ independent weight loads per step hide the L2 latency
+    for (int j0 = warp * NJ; j0 < n_out; j0 += nwarp * NJ) {
+        float acc[NJ][CT_CODES];
 #pragma unroll
-        for (int c = 0; c < CT_CODES; ++c) acc[c] = 0.f;
+        for (int q = 0; q < NJ; ++q)
+#pragma unroll
+            for (int c = 0; c < CT_CODES; ++c) acc[q][c] = 0.f;
+#pragma unroll 2
         for (int k = lane; k < k_in; k += 32) {
-            const float w = __ldg(W + (size_t)j * k_in + k);
+            float w[NJ];
 #pragma unroll
-            for (int c = 0; c < CT_CODES; ++c) acc[c] = fmaf(w, s_in[c * k_in + k], acc[c]);
+            for (int q = 0; q < NJ; ++q) w[q] = j0 + q < n_out ? __ldg(W + (size_t)(j0 + q) * k_in + k) : 0.f;
+#pragma unroll
+            for (int c = 0; c < CT_CODES; ++c) {
+                const float e = s_in[c * k_in + k];
+#pragma unroll
+                for (int q = 0; q < NJ; ++q) acc[q][c] = fmaf(w[q], e, acc[q][c]);
+            }
         }
 #pragma unroll
-        for (int c = 0; c < CT_CODES; ++c) acc[c] = warp_sum(acc[c]);
-        if (lane < CT_CODES) {
-            float v = 0.f;
+        for (int q = 0; q < NJ; ++q) {
+            const int j = j0 + q;
+            if (j >= n_out) break;          // warp-uniform
 #pragma unroll
-            for (int c = 0; c < CT_CODES; ++c) v = lane == c ? acc[c] : v;
-            v += __ldg(bias + j);
-            const bool ok = lane < n_codes;
-            if (g_pre && ok) g_pre[(size_t)(code0 + lane) * ld + j] = v;
-            v = apply_act<ACT>(v);
-            if (g_post && ok) g_post[(size_t)(code0 + lane) * ld + j] = v;
-            if (s_out) s_out[lane * n_out + j] = v;
+            for (int c = 0; c < CT_CODES; ++c) acc[q][c] = warp_sum(acc[q][c]);
+            if (lane < CT_CODES) {
+                float v = 0.f;
+#pragma unroll
+                for (int c = 0; c < CT_CODES; ++c) v = lane == c ? acc[q][c] : v;
+                v += __ldg(bias + j);
+                const bool ok = lane < n_codes;
+                if (g_pre && ok) g_pre[(size_t)(code0 + lane) * ld + j] = v;
+                v = apply_act<ACT>(v);
+                if (g_post && ok) g_post[(size_t)(code0 + lane) * ld + j] = v;
+                if (s_out) s_out[lane * n_out + j] = v;
+            }
         }
     }
 }
-__global__ void __launch_bounds__(256) decoder_code_table_kernel(
+__global__ void __launch_bounds__(512) decoder_code_table_kernel(
     const float *__restrict__ E, const float *__restrict__ Wd0, const float *__restrict__ bd0,
     const float *__restrict__ Wd1, const float *__restrict__ bd1, const float *__restrict__ Wo,
     const float *__restrict__ bo, int K, int D, int H1, int H, int F, float *__restrict__ c1,

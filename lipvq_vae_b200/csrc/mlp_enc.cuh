@@ -109,7 +109,7 @@ __device__ __forceinline__ void epilogue_blocks(uint32_t t_acc, int cb0, int cb1
     }
 }
 
-template <bool TMA>
+template <bool TMA, bool KEEP>   // KEEP: a1/h1/a2/h2 are written for backward (training forward)
 __global__ void __launch_bounds__(ENC_THR, 1)
 enc_fused_kernel(const float *__restrict__ x, const float *__restrict__ W0, const float *__restrict__ b0,
                  const float *__restrict__ W1, const float *__restrict__ b1, const uint8_t *__restrict__ wn_img,
@@ -251,7 +251,7 @@ enc_fused_kernel(const float *__restrict__ x, const float *__restrict__ W0, cons
         fetch_x(blockIdx.x);
         int t = 0, slot_i = 0;
         bool zbad = false;
-        const bool keeps_acts = a1 || h1 || a2 || h2;   // their stores reuse the staging slots synchronously
+        constexpr bool keeps_acts = KEEP;               // their stores reuse the staging slots synchronously
         int64_t zn_row0 = 0;
         int zn_rows = -1;                               // pending row-norm combine of the previous tile
 #ifdef ENC_PROFILE
@@ -281,7 +281,7 @@ enc_fused_kernel(const float *__restrict__ x, const float *__restrict__ W0, cons
             ptx::tc_fence_after();
             ENC_TICK(1);
             epilogue_blocks<ACT_GELU_FAST>(tm + 128, 0, H1 / 16, sub, 4, H1, sb0, true, tm + 0, tm + 64, wbuf,
-                                           a1 ? a1 + wrow0 * H1 : nullptr, h1 ? h1 + wrow0 * H1 : nullptr, H1,
+                                           (KEEP && a1) ? a1 + wrow0 * H1 : nullptr, (KEEP && h1) ? h1 + wrow0 * H1 : nullptr, H1,
                                            rows_valid, true, NoAfter());
             a_ready_arrive(bar_a(1));
             ENC_TICK(2);
@@ -295,7 +295,7 @@ enc_fused_kernel(const float *__restrict__ x, const float *__restrict__ W0, cons
             }
             ENC_TICK(3);
             epilogue_blocks<ACT_GELU_FAST>(tm + 128, 0, HH / 16, sub, 4, HH, sb1, true, tm + 128, tm + 0, wbuf,
-                                           a2 ? a2 + wrow0 * HH : nullptr, h2 ? h2 + wrow0 * HH : nullptr, HH,
+                                           (KEEP && a2) ? a2 + wrow0 * HH : nullptr, (KEEP && h2) ? h2 + wrow0 * HH : nullptr, HH,
                                            rows_valid, true, [&](int cb) { a_ready_arrive(bar_a2(cb >> 1)); });
             // ---- next tile's x -> its own TMEM columns (layer 0 of tile t+1 runs during this tile's last epilogue)
             if (tile + gridDim.x < n_tiles) {
@@ -503,8 +503,7 @@ inline int encoder_fused_launch(const lipvq_dims_t *d, const lipvq_params_t *p, 
     const int D16 = pad16(d->D);
     enc_wn_image_kernel<<<(D16 * 32 + 255) / 256, 256, 0, st>>>(Wn, d->D, D16, img);
     LIPVQ_LAUNCH_OK();
-    LIPVQ_TRY(set_smem(enc_fused_kernel<true>, EncSmem::TOTAL));
-    LIPVQ_TRY(set_smem(enc_fused_kernel<false>, EncSmem::TOTAL));
+    const bool keep = a1 || h1 || a2 || h2;
     // bulk tensor stores need 16-byte row pitches and 32-bit row coordinates; otherwise the per-thread path
     static const bool no_tma = [] { const char *e = getenv("LIPVQ_ENC_TMA"); return e && !strcmp(e, "0"); }();
     CUtensorMap tm_ze, tm_zb;
@@ -525,14 +524,15 @@ inline int encoder_fused_launch(const lipvq_dims_t *d, const lipvq_params_t *p, 
         }
     }
     ProfScope prof("enc_fused_kernel", st);
-    if (use_tma)
-        enc_fused_kernel<true><<<grid_for(n), ENC_THR, EncSmem::TOTAL, st>>>(
-            x, p->enc0_w, p->enc0_b, p->enc2_w, p->enc2_b, img, p->lat_b, n, d->F, d->D, a1, h1, a2, h2, z_e, mu, Zb, zn,
-            DKp, counters, tm_ze, tm_zb);
-    else
-        enc_fused_kernel<false><<<grid_for(n), ENC_THR, EncSmem::TOTAL, st>>>(
-            x, p->enc0_w, p->enc0_b, p->enc2_w, p->enc2_b, img, p->lat_b, n, d->F, d->D, a1, h1, a2, h2, z_e, mu, Zb, zn,
-            DKp, counters, tm_ze, tm_zb);
+    auto launch = [&](auto kern) -> int {
+        LIPVQ_TRY(set_smem(kern, EncSmem::TOTAL));
+        kern<<<grid_for(n), ENC_THR, EncSmem::TOTAL, st>>>(x, p->enc0_w, p->enc0_b, p->enc2_w, p->enc2_b, img, p->lat_b, n,
+                                                           d->F, d->D, a1, h1, a2, h2, z_e, mu, Zb, zn, DKp, counters,
+                                                           tm_ze, tm_zb);
+        return LIPVQ_OK;
+    };
+    if (use_tma) LIPVQ_TRY(keep ? launch(enc_fused_kernel<true, true>) : launch(enc_fused_kernel<true, false>));
+    else LIPVQ_TRY(keep ? launch(enc_fused_kernel<false, true>) : launch(enc_fused_kernel<false, false>));
     LIPVQ_LAUNCH_OK();
     return LIPVQ_OK;
 }
