@@ -9,6 +9,7 @@
 #include "misc_kernels.cuh"
 #include "mlp_tc.cuh"
 #include "mlp_enc.cuh"
+#include "mlp_enc16.cuh"
 #include "vq_exact.cuh"
 #include "vq_tensor.cuh"
 
@@ -84,7 +85,7 @@ static size_t workspace_bytes_impl(const lipvq_dims_t *d, int64_t n) {
     bytes += vq_tensor_ws_bytes(n, d->D, d->K);
     bytes += N * sizeof(int64_t) + 4096;
     bytes += align_up(2 * kQeBlocks * sizeof(float), 256) + 1024;
-    bytes += mlp::enc_img_bytes(d->D) + 2048;
+    bytes += mlp::enc_scratch_bytes(d->D) + 2048;
     return align_up(bytes, 256);
 }
 }  // namespace lipvq
@@ -181,17 +182,21 @@ int lipvq_encoder_fwd(const lipvq_dims_t *d, const lipvq_params_t *p, const floa
     if (tc ? !(opt16(a->a1) && opt16(a->h1) && opt16(a->a2) && opt16(a->h2))
            : !(aligned16(a->a1) && aligned16(a->h1) && aligned16(a->a2) && aligned16(a->h2)))
         return LIPVQ_EALIGN;
-    if (tc && (ws == nullptr || ws_bytes < mlp::enc_img_bytes(d->D) + 1024)) return LIPVQ_EWORKSPACE;
+    if (tc && (ws == nullptr || ws_bytes < mlp::enc_scratch_bytes(d->D) + 1024)) return LIPVQ_EWORKSPACE;
     cudaStream_t st = (cudaStream_t)stream;
-    lipschitz_prep_kernel<<<(d->D + 7) / 8, 256, 0, st>>>(p->lat_W, p->lat_ci, d->D, d->H, a->scale, a->Wn);
-    LIPVQ_LAUNCH_OK();
     if (tc) {
         static const bool split = [] { const char *e = getenv("LIPVQ_ENC"); return e && !strcmp(e, "split"); }();
-        if (split && a->h2) return mlp::encoder_launch(d, p, x, n, a->a1, a->h1, a->a2, a->h2, a->Wn, a->z_e, st);
+        if (split && a->h2) {
+            lipschitz_prep_kernel<<<(d->D + 7) / 8, 256, 0, st>>>(p->lat_W, p->lat_ci, d->D, d->H, a->scale, a->Wn);
+            LIPVQ_LAUNCH_OK();
+            return mlp::encoder_launch(d, p, x, n, a->a1, a->h1, a->a2, a->h2, a->Wn, a->z_e, st);
+        }
         uint8_t *img = (uint8_t *)align_up((size_t)ws, 1024);
-        return mlp::encoder_fused_launch(d, p, x, n, a->a1, a->h1, a->a2, a->h2, a->Wn, a->z_e, img, nullptr, nullptr,
-                                         nullptr, 0, nullptr, st);
+        return mlp::encoder_fused16_launch(d, p, x, n, a->a1, a->h1, a->a2, a->h2, a->scale, a->Wn, a->z_e, img, nullptr,
+                                           nullptr, nullptr, 0, nullptr, st);
     }
+    lipschitz_prep_kernel<<<(d->D + 7) / 8, 256, 0, st>>>(p->lat_W, p->lat_ci, d->D, d->H, a->scale, a->Wn);
+    LIPVQ_LAUNCH_OK();
     LIPVQ_TRY(linear_fwd<ACT_GELU>(x, p->enc0_w, p->enc0_b, a->a1, a->h1, n, d->H1, d->F, st));
     LIPVQ_TRY(linear_fwd<ACT_GELU>(a->h1, p->enc2_w, p->enc2_b, a->a2, a->h2, n, d->H, d->H1, st));
     LIPVQ_TRY(linear_fwd<ACT_SIGMOID>(a->h2, a->Wn, p->lat_b, nullptr, a->z_e, n, d->D, d->H, st));
@@ -243,7 +248,7 @@ int lipvq_encode_search_fwd(const lipvq_dims_t *d, const lipvq_params_t *p, cons
     if (!dims_ok(d) || n < 0) return LIPVQ_ESHAPE;
     if (!p || !a) return LIPVQ_EALIGN;
     if (n == 0) return LIPVQ_OK;
-    if (ws_bytes < mlp::enc_img_bytes(d->D) + 2048 + vq_tensor_ws_bytes(n, d->D, d->K) || !aligned16(ws))
+    if (ws_bytes < mlp::enc_scratch_bytes(d->D) + 2048 + vq_tensor_ws_bytes(n, d->D, d->K) || !aligned16(ws))
         return LIPVQ_EWORKSPACE;
     cudaStream_t st = (cudaStream_t)stream;
     const bool fuse = use_mlp_tc(d) && search_mode == LIPVQ_SEARCH_TENSOR && vq_tensor_supported(d->D, d->K) &&
@@ -260,14 +265,12 @@ int lipvq_encode_search_fwd(const lipvq_dims_t *d, const lipvq_params_t *p, cons
     // the row operand of the search (Zb, zn) is produced by the encoder's last epilogue: z_e is written once
     // and never re-read for conversion
     uint8_t *img = (uint8_t *)align_up((size_t)ws, 1024);
-    void *vq_ws = (void *)align_up((size_t)(img + mlp::enc_img_bytes(d->D)), 1024);
+    void *vq_ws = (void *)align_up((size_t)(img + mlp::enc_scratch_bytes(d->D)), 1024);
     const tc::Geometry g = tc::geometry(n, d->D, d->K);
     const tc::Workspace w = tc::carve(vq_ws, g);
-    lipschitz_prep_kernel<<<(d->D + 7) / 8, 256, 0, st>>>(p->lat_W, p->lat_ci, d->D, d->H, a->scale, a->Wn);
-    LIPVQ_LAUNCH_OK();
     LIPVQ_TRY(vq_tensor_prep(p->codebook, g, w, st));
-    LIPVQ_TRY(mlp::encoder_fused_launch(d, p, x, n, a->a1, a->h1, a->a2, a->h2, a->Wn, a->z_e, img, w.mu, w.Zb, w.zn,
-                                        g.DKp, w.counters, st));
+    LIPVQ_TRY(mlp::encoder_fused16_launch(d, p, x, n, a->a1, a->h1, a->a2, a->h2, a->scale, a->Wn, a->z_e, img, w.mu,
+                                          w.Zb, w.zn, g.DKp, w.counters, st));
     return vq_tensor_search(a->z_e, p->codebook, g, w, a->idx, nullptr, stats, st);
 }
 

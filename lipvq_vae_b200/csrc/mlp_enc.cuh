@@ -41,25 +41,6 @@ struct EncSmem {
     static constexpr int TOTAL = BAR + NBAR * 8 + 16 + 1024;
 };
 
-// Wn [D,128] -> per-K-block images in global memory: block kb = [hi | lo], each D16 rows x 128 B in the
-// swizzled layout of stage_weight().  One thread per 16-byte piece.
-__global__ void enc_wn_image_kernel(const float *__restrict__ Wn, int D, int D16, uint8_t *__restrict__ img) {
-    const int total = D16 * 4 * 8;
-    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
-        const int j = i & 7, kb = (i >> 3) & 3, n = i >> 5;
-        uint32_t h[4], l[4];
-#pragma unroll
-        for (int t = 0; t < 4; ++t) {
-            const float v = n < D ? Wn[(size_t)n * HH + kb * 32 + j * 4 + t] : 0.f;
-            split_tf32(v, h[t], l[t]);
-        }
-        uint8_t *base = img + (size_t)kb * D16 * 256;
-        const int off = n * 128 + ((j ^ (n & 7)) << 4);
-        *reinterpret_cast<uint4 *>(base + off) = make_uint4(h[0], h[1], h[2], h[3]);
-        *reinterpret_cast<uint4 *>(base + D16 * 128 + off) = make_uint4(l[0], l[1], l[2], l[3]);
-    }
-}
-
 __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void *src, uint32_t bytes, uint32_t bar) {
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
                  "l"(src), "r"(bytes), "r"(bar)
@@ -118,9 +99,12 @@ enc_fused_kernel(const float *__restrict__ x, const float *__restrict__ W0, cons
                  // optional fusion of the search's row-operand pass (vq_tensor.cuh pass 1): Zb/zn/flag outputs
                  const float *__restrict__ mu, tc::op_t *__restrict__ Zb, float *__restrict__ zn, int DKp,
                  int *__restrict__ counters,
+                 // gate != nullptr: run only if *gate != 0 (fallback of the fp16-split kernel, mlp_enc16.cuh)
+                 const int *__restrict__ gate,
                  // bulk tensor stores of z_e (fp32, box 8 x 32, 32-byte swizzle) and Zb (16-bit, box 16 x 32)
                  const __grid_constant__ CUtensorMap tm_ze, const __grid_constant__ CUtensorMap tm_zb) {
     using L = EncSmem;
+    if (gate != nullptr && *gate == 0) return;                       // (uniform over the grid)
     extern __shared__ uint8_t smem_raw[];
     const uint32_t raw = ptx::smem_u32(smem_raw);
     uint8_t *sm = smem_raw + (((raw + 1023u) & ~1023u) - raw);
@@ -466,7 +450,7 @@ enc_fused_kernel(const float *__restrict__ x, const float *__restrict__ W0, cons
             if (zn_rows >= 0 && sub == 0 && lane < zn_rows)
                 zn[zn_row0 + lane] = sqrtf(((sznp[r_in] + sznp[TM + r_in]) + sznp[2 * TM + r_in]) + sznp[3 * TM + r_in]);
         }
-        if (zbad) atomicOr(counters + 3, 1);   // operand out of fp16 range -> the search goes exact for this launch
+        if (zbad && counters) atomicOr(counters + 3, 1);   // operand out of fp16 range -> the search goes exact for this launch
         if (TMA && lane == 0) ptx::bulk_wait<0>();   // every bulk store has landed before the CTA retires
 #ifdef ENC_PROFILE
         if (blockIdx.x == 3 && (threadIdx.x & 31) == 0 && (threadIdx.x >> 5) < 8)
@@ -481,7 +465,6 @@ enc_fused_kernel(const float *__restrict__ x, const float *__restrict__ W0, cons
 
 inline size_t enc_img_bytes(int D) { return (size_t)ENC_NC * pad16(D) * 256; }
 
-// img: enc_img_bytes(D) of 1024-byte aligned scratch.  mu/Zb/zn/counters: optional search-operand fusion.
 // row-major [rows, cols] tensor of `esize`-byte elements, box = {32 bytes of columns, 32 rows}, 32-byte swizzle
 inline int make_store_tmap(CUtensorMap *m, const void *ptr, CUtensorMapDataType dt, int esize, uint64_t rows,
                            uint64_t cols, uint64_t pitch_elems) {
@@ -494,47 +477,6 @@ inline int make_store_tmap(CUtensorMap *m, const void *ptr, CUtensorMapDataType 
     CUresult r = fn(m, dt, 2, const_cast<void *>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                     CU_TENSOR_MAP_SWIZZLE_32B, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     return r == CUDA_SUCCESS ? LIPVQ_OK : LIPVQ_ECUDA;
-}
-
-// img: enc_img_bytes(D) of 1024-byte aligned scratch.  mu/Zb/zn/counters: optional search-operand fusion.
-inline int encoder_fused_launch(const lipvq_dims_t *d, const lipvq_params_t *p, const float *x, int64_t n, float *a1,
-                                float *h1, float *a2, float *h2, const float *Wn, float *z_e, uint8_t *img,
-                                const float *mu, tc::op_t *Zb, float *zn, int DKp, int *counters, cudaStream_t st) {
-    const int D16 = pad16(d->D);
-    enc_wn_image_kernel<<<(D16 * 32 + 255) / 256, 256, 0, st>>>(Wn, d->D, D16, img);
-    LIPVQ_LAUNCH_OK();
-    const bool keep = a1 || h1 || a2 || h2;
-    // bulk tensor stores need 16-byte row pitches and 32-bit row coordinates; otherwise the per-thread path
-    static const bool no_tma = [] { const char *e = getenv("LIPVQ_ENC_TMA"); return e && !strcmp(e, "0"); }();
-    CUtensorMap tm_ze, tm_zb;
-    memset(&tm_ze, 0, sizeof(tm_ze));
-    memset(&tm_zb, 0, sizeof(tm_zb));
-    int use_tma = !no_tma && (d->D & 3) == 0 && n < (int64_t)0x7fffffff - TM && (!Zb || (DKp & 7) == 0);
-    if (use_tma) {
-        LIPVQ_TRY(make_store_tmap(&tm_ze, z_e, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, (uint64_t)n, (uint64_t)d->D,
-                                  (uint64_t)d->D));
-        if (Zb) {
-#ifdef LIPVQ_VQ_BF16
-            const CUtensorMapDataType dt = CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
-#else
-            const CUtensorMapDataType dt = CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
-#endif
-            const uint64_t np = (uint64_t)((n + TM - 1) / TM * TM);
-            LIPVQ_TRY(make_store_tmap(&tm_zb, Zb, dt, 2, np, (uint64_t)DKp, (uint64_t)DKp));
-        }
-    }
-    ProfScope prof("enc_fused_kernel", st);
-    auto launch = [&](auto kern) -> int {
-        LIPVQ_TRY(set_smem(kern, EncSmem::TOTAL));
-        kern<<<grid_for(n), ENC_THR, EncSmem::TOTAL, st>>>(x, p->enc0_w, p->enc0_b, p->enc2_w, p->enc2_b, img, p->lat_b, n,
-                                                           d->F, d->D, a1, h1, a2, h2, z_e, mu, Zb, zn, DKp, counters,
-                                                           tm_ze, tm_zb);
-        return LIPVQ_OK;
-    };
-    if (use_tma) LIPVQ_TRY(keep ? launch(enc_fused_kernel<true, true>) : launch(enc_fused_kernel<true, false>));
-    else LIPVQ_TRY(keep ? launch(enc_fused_kernel<false, true>) : launch(enc_fused_kernel<false, false>));
-    LIPVQ_LAUNCH_OK();
-    return LIPVQ_OK;
 }
 
 }  // namespace mlp

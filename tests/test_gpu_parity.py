@@ -276,3 +276,41 @@ def test_host_tokenizer_pipeline_matches_direct_calls():
         assert torch.equal(wi, gi) and torch.equal(wt, gt) and torch.equal(wz, gz)
     with pytest.raises(ValueError):
         ht.submit(torch.zeros(10 ** 6, x.shape[1]))
+
+
+def _encoder_fwd_abi(p, x):
+    """z_e of lipvq_encoder_fwd (the fused tensor-core encoder for the reference widths) for numpy inputs."""
+    import ctypes as C
+    from lipvq_vae_b200 import _native as N
+    from lipvq_vae_b200.tokenizer import _workspace, _param_struct, _acts_struct, _p
+    m = _model(p, 1)
+    dev = torch.device("cuda:0")
+    dims = m._dims()
+    params = [q.detach() for q in m._param_list()]
+    P = _param_struct(N.Params, params)
+    xt = torch.from_numpy(x).to(dev)
+    n, D = x.shape[0], dims.D
+    ws = _workspace(dev, dims, n)
+    f32 = dict(dtype=torch.float32, device=dev)
+    scale, Wn, z_e = torch.empty(D, **f32), torch.empty(D, dims.H, **f32), torch.empty(n, D, **f32)
+    A = _acts_struct(scale=scale, Wn=Wn, z_e=z_e)
+    st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    N.check(N.lib().lipvq_encoder_fwd(C.byref(dims), C.byref(P), _p(xt), n, C.byref(A), _p(ws), ws.numel(), st))
+    torch.cuda.synchronize()
+    return z_e.cpu().numpy()
+
+
+@pytest.mark.parametrize("case", ["c1_spread", "small"])
+def test_fused_encoder_latents_and_range_fallback(case):
+    """The fused encoder computes its GEMMs as fp16 hi/lo split products (operands scaled by 2^8): z_e must sit
+    at the fp32 rounding floor of the reference, and inputs outside the fp16 operand range (|x| >= 255) must
+    take the gated tf32 kernel and still match."""
+    p, x = case_inputs(case)
+    for mult in (1.0, 400.0):
+        xs = (x * mult).astype(np.float32)
+        ref = orc.forward(p, xs)["z_e"]
+        got = _encoder_fwd_abi(p, xs)
+        assert np.isfinite(got).all()
+        # (at 400x the pre-activations are O(100): fp32 dot products of that size round at ~1e-5 themselves)
+        assert np.abs(got - ref).max() < (2e-6 if mult == 1.0 else 5e-5), (mult, np.abs(got - ref).max())
+        assert orc.rel_err(got, ref) < RTOL
