@@ -34,8 +34,8 @@ struct Enc16Smem {
     static constexpr int BIAS = WBUF + 16 * 2048;
     static constexpr int MU = BIAS + (H1 + HH + 256) * 4;
     static constexpr int ZNP = MU + 272 * 4;
-    static constexpr int BAR = ZNP + 4 * TM * 4;
-    static constexpr int NBAR = 2 + 2 + 1 + ENC_NC;                 // a_ready[2] acc_ready[2] acc3 a2_ready[4]
+    static constexpr int BAR = ZNP + 2 * 4 * TM * 4;                // (partial row norms: two tiles in flight)
+    static constexpr int NBAR = 2 + 2 + 1 + ENC_NC + 1;             // a_ready[2] acc_ready[2] acc3 a2_ready[4] r3_free
     static constexpr int TOTAL = BAR + NBAR * 8 + 16 + 1024;
 };
 
@@ -164,6 +164,7 @@ enc16_fused_kernel(const float *__restrict__ x, const float *__restrict__ W0, co
     const uint32_t bar_acc3 = bars + 8u * 4;                         // layer-2 accumulator ready
     // h2 blocks 2c, 2c+1 (K steps 2c, 2c+1 of layer 2) ready: 2 column owners x 4 lane quarters = 8 warp arrivals
     auto bar_a2 = [&](int c) { return bars + 8u * (5 + c); };
+    const uint32_t bar_r3 = bars + 8u * (5 + ENC_NC);                // every warp has read acc3 of the previous tile
     volatile uint32_t *tmem_slot = reinterpret_cast<volatile uint32_t *>(sm + L::BAR + L::NBAR * 8);
 
     const int D16 = pad16(D);
@@ -182,6 +183,7 @@ enc16_fused_kernel(const float *__restrict__ x, const float *__restrict__ W0, co
         for (int l = 0; l < 2; ++l) ptx::mbar_init(bar_acc(l), 1);
         ptx::mbar_init(bar_acc3, 1);
         for (int c = 0; c < ENC_NC; ++c) ptx::mbar_init(bar_a2(c), 8);
+        ptx::mbar_init(bar_r3, ENC_EPI / 32);
         ptx::fence_barrier_init();
     }
     if ((threadIdx.x >> 5) == 0) ptx::tmem_alloc<512>(ptx::smem_u32((const void *)tmem_slot));
@@ -204,22 +206,25 @@ enc16_fused_kernel(const float *__restrict__ x, const float *__restrict__ W0, co
                 issue_steps16(tmem0 + E16_R1, tmem0 + E16_X, w0h, w0l, H1, 0, 1, true);
                 ptx::umma_commit(bar_acc(0));
             };
+            // Order in the tensor pipe: L0(0) | L1(t) L0(t+1) L2(t) ...  The epilogue warps run
+            // epi0(t) -> epi2(t-1) -> epi1(t): layer 1 of tile t executes under the previous tile's long sigmoid
+            // epilogue, layer 0 of tile t+1 is done long before it is needed, and the tail of layer 2 (released per
+            // pair of h2 blocks during epi1) drains under epi0(t+1).
+            issue_layer0(0);
             for (int t = 0; t < my_tiles; ++t) {
                 const uint32_t par = t & 1;
-                if (t == 0) issue_layer0(0);
                 ptx::mbar_wait(bar_a(1), par);
                 ptx::tc_fence_after();
                 issue_steps16(tmem0 + E16_R2, tmem0 + E16_R1, w1h, w1l, HH, 0, H1 / 16, true);
                 ptx::umma_commit(bar_acc(1));
+                if (t + 1 < my_tiles) issue_layer0(t + 1);      // (queued behind L1(t), which reads h1(t) from acc1's columns)
+                if (t >= 1) ptx::mbar_wait(bar_r3, (t - 1) & 1);    // acc3 of tile t-1 has been read by every warp
                 for (int c = 0; c < ENC_NC; ++c) {      // K steps 2c, 2c+1 of Wn against h2 blocks 2c, 2c+1
                     ptx::mbar_wait(bar_a2(c), par);
                     ptx::tc_fence_after();
                     issue_steps16(tmem0 + E16_R3, tmem0 + E16_R2, wnh, wnl, D16, 2 * c, 2 * c + 2, c == 0);
                 }
                 ptx::umma_commit(bar_acc3);
-                // layer 0 of the next tile queues behind this tile's layer 2 (its x was staged before the epilogue
-                // warps started waiting for acc3) and completes during this tile's last epilogue
-                if (t + 1 < my_tiles) issue_layer0(t + 1);
             }
         }
     } else {
@@ -258,58 +263,52 @@ enc16_fused_kernel(const float *__restrict__ x, const float *__restrict__ W0, co
             a_ready_arrive(bar_a(0));
         };
         fetch_x(blockIdx.x);
-        int t = 0, slot_i = 0;
+        int slot_i = 0;
         bool zbad = false;
         int64_t zn_row0 = 0;
         int zn_rows = -1;                               // pending row-norm combine of the previous tile
 #ifdef ENC_PROFILE
         long long pc[8] = {0, 0, 0, 0, 0, 0, 0, 0}, pt = clock64();
 #endif
-        for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++t) {
-            const uint32_t par = t & 1;
-            const int64_t wrow0 = tile * TM + (r_in - lane);               // first row of this warp
-            const int rows_valid = (int)max((int64_t)0, min((int64_t)32, n_rows - wrow0));
-            if (TMA && KEEP) {   // the previous tile's bulk stores must have read the staging slots
-                if (lane == 0) ptx::bulk_wait_read<0>();
-                __syncwarp();
-            }
-            if (t == 0) {
-                stage_x();
-                fetch_x(tile + gridDim.x);
-            }
+        stage_x();
+        fetch_x(blockIdx.x + (int64_t)gridDim.x);
+        // iteration it: epi0(it) | epi2(it-1) | epi1(it)   (tile index of local tile i = blockIdx.x + i * gridDim.x)
+        for (int it = 0; it <= my_tiles; ++it) {
+            const int64_t tile = blockIdx.x + (int64_t)it * gridDim.x;
+            const uint32_t par = it & 1;
+            const int64_t wrow0_cur = tile * TM + (r_in - lane);           // first row of this warp
+            const int rows_valid_cur = (int)max((int64_t)0, min((int64_t)32, n_rows - wrow0_cur));
             ENC_TICK(0);
-            // ---- layer 0 epilogue: h1 (in place over acc1)
-            ptx::mbar_wait(bar_acc(0), par);
+            if (it < my_tiles) {
+                // ---- layer 0 epilogue: h1 (in place over acc1)
+                ptx::mbar_wait(bar_acc(0), par);
+                ptx::tc_fence_after();
+                ENC_TICK(1);
+                epilogue_blocks16<ACT_GELU_FAST>(tm + E16_R1, 0, H1 / 16, sub, 4, H1, sb0, wbuf,
+                                                 (KEEP && a1) ? a1 + wrow0_cur * H1 : nullptr,
+                                                 (KEEP && h1) ? h1 + wrow0_cur * H1 : nullptr, H1, rows_valid_cur, amax,
+                                                 NoAfter());
+                a_ready_arrive(bar_a(1));
+                // ---- next tile's x -> its TMEM columns (layer 0 of this tile has completed)
+                if (it + 1 < my_tiles) {
+                    stage_x();
+                    fetch_x(tile + 2 * (int64_t)gridDim.x);
+                }
+                ENC_TICK(2);
+            }
+            if (it >= 1) {
+            // ---- layer 2 epilogue of the PREVIOUS tile: sigmoid and store z_e
+            const int64_t wrow0 = wrow0_cur - (int64_t)gridDim.x * TM;
+            const int rows_valid = (int)max((int64_t)0, min((int64_t)32, n_rows - wrow0));
+            float *sznp_w = sznp + ((it - 1) & 1) * 4 * TM, *sznp_r = sznp + (it & 1) * 4 * TM;
+            ptx::mbar_wait(bar_acc3, par ^ 1u);
             ptx::tc_fence_after();
-            ENC_TICK(1);
-            epilogue_blocks16<ACT_GELU_FAST>(tm + E16_R1, 0, H1 / 16, sub, 4, H1, sb0, wbuf,
-                                             (KEEP && a1) ? a1 + wrow0 * H1 : nullptr,
-                                             (KEEP && h1) ? h1 + wrow0 * H1 : nullptr, H1, rows_valid, amax, NoAfter());
-            a_ready_arrive(bar_a(1));
-            ENC_TICK(2);
-            // ---- layer 1 epilogue: h2 (in place over acc2), released to layer 2 per pair of blocks
-            ptx::mbar_wait(bar_acc(1), par);
-            ptx::tc_fence_after();
-            if (zn_rows >= 0) {   // (every warp passed the previous tile's last epilogue before acc2 could complete)
+            if (zn_rows >= 0) {   // tile it-2: every warp wrote its partial norms before layer 2 of tile it-1 could start
                 if (sub == 0 && lane < zn_rows)
-                    zn[zn_row0 + lane] = sqrtf(((sznp[r_in] + sznp[TM + r_in]) + sznp[2 * TM + r_in]) + sznp[3 * TM + r_in]);
+                    zn[zn_row0 + lane] = sqrtf(((sznp_r[r_in] + sznp_r[TM + r_in]) + sznp_r[2 * TM + r_in]) + sznp_r[3 * TM + r_in]);
                 zn_rows = -1;
             }
             ENC_TICK(3);
-            epilogue_blocks16<ACT_GELU_FAST>(tm + E16_R2, 0, HH / 16, sub, 4, HH, sb1, wbuf,
-                                             (KEEP && a2) ? a2 + wrow0 * HH : nullptr,
-                                             (KEEP && h2) ? h2 + wrow0 * HH : nullptr, HH, rows_valid, amax,
-                                             [&](int cb) { a_ready_arrive(bar_a2(cb >> 1)); });
-            // ---- next tile's x -> its TMEM columns (layer 0 of tile t+1 runs during this tile's last epilogue)
-            if (tile + gridDim.x < n_tiles) {
-                stage_x();
-                fetch_x(tile + 2 * (int64_t)gridDim.x);
-            }
-            ENC_TICK(4);
-            // ---- layer 2 epilogue: sigmoid and store z_e
-            ptx::mbar_wait(bar_acc3, par);
-            ptx::tc_fence_after();
-            ENC_TICK(5);
             if constexpr (TMA) {
                 // z_e (+ the search's row operand Zb = [fp16(z - mu) | 1 1 1], zn = ||z - mu||) leave through bulk
                 // tensor stores from the warp's two 1 KB staging slots (see mlp_enc.cuh)
@@ -327,6 +326,9 @@ enc16_fused_kernel(const float *__restrict__ x, const float *__restrict__ W0, co
                 auto slot_send = [&](const CUtensorMap *tmap, uint8_t *sl, int c, int64_t row) {
                     ptx::fence_proxy_async();
                     __syncwarp();
+#ifdef ENC_EXP_SKIP
+                    if (tmap == &tm_ze ? (ENC_EXP_SKIP & 1) : (ENC_EXP_SKIP & 2)) return;
+#endif
                     if (lane == 0) {
                         ptx::tma_store_2d(tmap, wbuf_s + (uint32_t)(sl - wbuf), c, (int)row);
                         ptx::bulk_commit();
@@ -397,7 +399,7 @@ enc16_fused_kernel(const float *__restrict__ x, const float *__restrict__ W0, co
                     zbad |= !(ss <= tc::OP_MAX * tc::OP_MAX);
                     // partial norms of the four column owners are combined (fixed order) after the NEXT tile's
                     // layer-1 accumulator wait, which every thread of this tile has passed its epilogue to reach
-                    sznp[sub * TM + r_in] = ss;
+                    sznp_w[sub * TM + r_in] = ss;
                     zn_row0 = wrow0;
                     zn_rows = rows_valid;
                 }
@@ -452,26 +454,48 @@ enc16_fused_kernel(const float *__restrict__ x, const float *__restrict__ W0, co
                 }
                 if (Zb) {
                     // row norm: the four column owners of a row combine through shared memory in a fixed order
-                    sznp[sub * TM + r_in] = ss;
+                    sznp_w[sub * TM + r_in] = ss;
                     asm volatile("bar.sync 1, 512;" ::: "memory");
                     if (sub == 0 && lane < rows_valid)
-                        zn[wrow0 + lane] = sqrtf(((sznp[r_in] + sznp[TM + r_in]) + sznp[2 * TM + r_in]) + sznp[3 * TM + r_in]);
+                        zn[wrow0 + lane] = sqrtf(((sznp_w[r_in] + sznp_w[TM + r_in]) + sznp_w[2 * TM + r_in]) + sznp_w[3 * TM + r_in]);
                     asm volatile("bar.sync 1, 512;" ::: "memory");
                 }
             }
-            ENC_TICK(6);
+            // acc3 of that tile is free for layer 2 of this one
+            ptx::tc_fence_before();
+            __syncwarp();
+            if (lane == 0) ptx::mbar_arrive(bar_r3);
+            ENC_TICK(4);
+            }
+            if (it < my_tiles) {
+                if (TMA && KEEP && it >= 1) {   // the bulk stores just issued must have read the staging slots
+                    if (lane == 0) ptx::bulk_wait_read<0>();
+                    __syncwarp();
+                }
+                // ---- layer 1 epilogue: h2 (in place over acc2), released to layer 2 per pair of blocks
+                ptx::mbar_wait(bar_acc(1), par);
+                ptx::tc_fence_after();
+                ENC_TICK(5);
+                epilogue_blocks16<ACT_GELU_FAST>(tm + E16_R2, 0, HH / 16, sub, 4, HH, sb1, wbuf,
+                                                 (KEEP && a2) ? a2 + wrow0_cur * HH : nullptr,
+                                                 (KEEP && h2) ? h2 + wrow0_cur * HH : nullptr, HH, rows_valid_cur, amax,
+                                                 [&](int cb) { a_ready_arrive(bar_a2(cb >> 1)); });
+                ENC_TICK(6);
+            }
         }
         if (TMA && Zb) {                       // row norms of the last tile
             asm volatile("bar.sync 1, 512;" ::: "memory");
+            const float *sl = sznp + ((my_tiles - 1) & 1) * 4 * TM;
             if (zn_rows >= 0 && sub == 0 && lane < zn_rows)
-                zn[zn_row0 + lane] = sqrtf(((sznp[r_in] + sznp[TM + r_in]) + sznp[2 * TM + r_in]) + sznp[3 * TM + r_in]);
+                zn[zn_row0 + lane] = sqrtf(((sl[r_in] + sl[TM + r_in]) + sl[2 * TM + r_in]) + sl[3 * TM + r_in]);
         }
         if (zbad && counters) atomicOr(counters + 3, 1);   // search operand out of range -> exact search
         if (TMA && lane == 0) ptx::bulk_wait<0>();   // every bulk store has landed before the CTA retires
 #ifdef ENC_PROFILE
         if (blockIdx.x == 3 && (threadIdx.x & 31) == 0 && (threadIdx.x >> 5) < 8)
-            printf("w%d tiles %d cyc/tile: xstage %lld | wait0 %lld epi0 %lld | wait1 %lld epi1 %lld | wait2 %lld epi2 %lld\n",
-                   threadIdx.x >> 5, t, pc[0] / t, pc[1] / t, pc[2] / t, pc[3] / t, pc[4] / t, pc[5] / t, pc[6] / t);
+            printf("w%d tiles %d cyc/tile: loop %lld | wait0 %lld epi0 %lld | wait3 %lld epi2 %lld | wait1 %lld epi1 %lld\n",
+                   threadIdx.x >> 5, my_tiles, pc[0] / my_tiles, pc[1] / my_tiles, pc[2] / my_tiles, pc[3] / my_tiles,
+                   pc[4] / my_tiles, pc[5] / my_tiles, pc[6] / my_tiles);
 #endif
     }
     // an operand left the fp16 range (or was NaN): the tf32 kernel redoes this launch
