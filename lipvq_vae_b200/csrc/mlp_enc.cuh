@@ -467,15 +467,15 @@ inline size_t enc_img_bytes(int D) { return (size_t)ENC_NC * pad16(D) * 256; }
 
 // row-major [rows, cols] tensor of `esize`-byte elements, box = {32 bytes of columns, 32 rows}, 32-byte swizzle
 inline int make_store_tmap(CUtensorMap *m, const void *ptr, CUtensorMapDataType dt, int esize, uint64_t rows,
-                           uint64_t cols, uint64_t pitch_elems) {
+                           uint64_t cols, uint64_t pitch_elems, int box_bytes = 32) {
     tc::EncodeTiledFn fn = tc::encode_fn();
     if (!fn) return LIPVQ_ECUDA;
     cuuint64_t dims[2] = {cols, rows};
     cuuint64_t strides[1] = {pitch_elems * (uint64_t)esize};
-    cuuint32_t box[2] = {(cuuint32_t)(32 / esize), 32};
+    cuuint32_t box[2] = {(cuuint32_t)(box_bytes / esize), 32};   // swizzle span = box row bytes (32 or 64)
     cuuint32_t estr[2] = {1, 1};
     CUresult r = fn(m, dt, 2, const_cast<void *>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                    CU_TENSOR_MAP_SWIZZLE_32B, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                    box_bytes == 64 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_32B, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     return r == CUDA_SUCCESS ? LIPVQ_OK : LIPVQ_ECUDA;
 }
 

@@ -30,14 +30,25 @@ struct Enc16Smem {
     static constexpr int W0 = 0, W0_IMG = H1 * 128;                 // 64 rows x one 128-byte K block (16 of 64 used)
     static constexpr int W1 = W0 + 2 * W0_IMG, W1_IMG = HH * 128;   // 128 rows x one K block (64 fp16)
     static constexpr int WN = W1 + 2 * W1_IMG, WN_IMG = ENC_DMAX * 128 * 2;   // D16 rows x two K blocks
-    static constexpr int WBUF = WN + 2 * WN_IMG;                    // 16 warps x 2 KB store staging
-    static constexpr int BIAS = WBUF + 16 * 2048;
+    static constexpr int WBUF_W = 3072;                             // per warp: z_e slot (2 KB) + Zb slot (1 KB)
+    static constexpr int WBUF = WN + 2 * WN_IMG;                    // 16 warps x 3 KB store staging
+    static constexpr int BIAS = WBUF + 16 * WBUF_W;
     static constexpr int MU = BIAS + (H1 + HH + 256) * 4;
     static constexpr int ZNP = MU + 272 * 4;
     static constexpr int BAR = ZNP + 2 * 4 * TM * 4;                // (partial row norms: two tiles in flight)
     static constexpr int NBAR = 2 + 2 + 1 + ENC_NC + 1;             // a_ready[2] acc_ready[2] acc3 a2_ready[4] r3_free
     static constexpr int TOTAL = BAR + NBAR * 8 + 16 + 1024;
 };
+
+// two sigmoids with ONE reciprocal: 1/a = b * rcp(a b), 1/b = a * rcp(a b), a = 1 + 2^t.  t is clamped at 60 so
+// the product cannot overflow (sigmoid(x) for x < -41.6 returns 2^-60 instead of a smaller positive number).
+__device__ __forceinline__ void sigmoid_fast_pair(float &x0, float &x1) {
+    const float a0 = 1.0f + ex2_approx(fminf(-1.4426950408889634f * x0, 60.0f));
+    const float a1 = 1.0f + ex2_approx(fminf(-1.4426950408889634f * x1, 60.0f));
+    const float r = rcp_approx(a0 * a1);
+    x0 = r * a1;
+    x1 = r * a0;
+}
 
 // two scaled values -> packed hi / lo halves (low 16 bits = first value = even k)
 __device__ __forceinline__ void split_f16x2(float a, float b, uint32_t &hi, uint32_t &lo) {
@@ -231,7 +242,7 @@ enc16_fused_kernel(const float *__restrict__ x, const float *__restrict__ W0, co
         // ============================ input + epilogue warps
         const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, sub = warp >> 2, r_in = threadIdx.x & 127;
         const uint32_t tm = tmem0 + ((uint32_t)((warp & 3) * 32) << 16);
-        uint8_t *wbuf = sm + L::WBUF + warp * 2048;
+        uint8_t *wbuf = sm + L::WBUF + warp * L::WBUF_W;
         const bool vec_x = (F & 3) == 0, vec_d = (D & 3) == 0;
         float xv[16];
         auto fetch_x = [&](int64_t tile) {
@@ -311,32 +322,19 @@ enc16_fused_kernel(const float *__restrict__ x, const float *__restrict__ W0, co
             ENC_TICK(3);
             if constexpr (TMA) {
                 // z_e (+ the search's row operand Zb = [fp16(z - mu) | 1 1 1], zn = ||z - mu||) leave through bulk
-                // tensor stores from the warp's two 1 KB staging slots (see mlp_enc.cuh)
-                float ss = 0.f;
+                // tensor stores: per 16-column block a thread writes its 64 bytes of z_e (64-byte-swizzle slot, 2 KB
+                // per warp) and its 32 bytes of Zb (32-byte-swizzle slot, 1 KB); ONE proxy fence and ONE bulk group
+                // per block, lane 0 issues both stores.  The slots are rewritten once that group has read them
+                // (wait_group.read 0 after the next block's arithmetic).
+                float ss0 = 0.f, ss1 = 0.f;
                 const int nblk = Zb ? (D + 3 + 15) / 16 : D16 / 16;
-                const int sw = (lane >> 2) & 1;
-                auto slot_take = [&]() -> uint8_t * {
-                    if (lane == 0) ptx::bulk_wait_read<1>();
-                    __syncwarp();
-                    uint8_t *sl = wbuf + (slot_i & 1) * 1024;
-                    ++slot_i;
-                    return sl;
-                };
+                const int sw32 = (lane >> 2) & 1, sw64 = (lane >> 1) & 3;
+                uint8_t *sl_ze = wbuf, *sl_zb = wbuf + 2048;
                 const uint32_t wbuf_s = ptx::smem_u32(wbuf);
-                auto slot_send = [&](const CUtensorMap *tmap, uint8_t *sl, int c, int64_t row) {
-                    ptx::fence_proxy_async();
-                    __syncwarp();
-#ifdef ENC_EXP_SKIP
-                    if (tmap == &tm_ze ? (ENC_EXP_SKIP & 1) : (ENC_EXP_SKIP & 2)) return;
-#endif
-                    if (lane == 0) {
-                        ptx::tma_store_2d(tmap, wbuf_s + (uint32_t)(sl - wbuf), c, (int)row);
-                        ptx::bulk_commit();
-                    }
-                };
                 for (int cb = sub; cb < nblk; cb += 4) {
                     const int c0 = cb << 4;
                     float v[16];
+                    const bool has_ze = c0 < D;
                     if (c0 < D16) {
                         uint32_t r[16];
                         ptx::tmem_ld_32x32b_x16(tm + E16_R3 + c0, r);
@@ -350,17 +348,16 @@ enc16_fused_kernel(const float *__restrict__ x, const float *__restrict__ W0, co
                             v[4 * i + 3] = fmaf(__uint_as_float(r[4 * i + 3]), E16_DESCALE, bq.w);
                         }
 #pragma unroll
-                        for (int i = 0; i < 16; ++i) v[i] = sigmoid_fast_f(v[i]);
+                        for (int i = 0; i < 8; ++i) sigmoid_fast_pair(v[2 * i], v[2 * i + 1]);
+                    }
+                    (void)slot_i;
+                    if (lane == 0) ptx::bulk_wait_read<0>();
+                    __syncwarp();
+                    if (has_ze) {
 #pragma unroll
-                        for (int hf = 0; hf < 2; ++hf) {
-                            if (c0 + 8 * hf >= D) break;
-                            uint8_t *sl = slot_take();
-                            *reinterpret_cast<float4 *>(sl + lane * 32 + ((0 ^ sw) << 4)) =
-                                make_float4(v[8 * hf], v[8 * hf + 1], v[8 * hf + 2], v[8 * hf + 3]);
-                            *reinterpret_cast<float4 *>(sl + lane * 32 + ((1 ^ sw) << 4)) =
-                                make_float4(v[8 * hf + 4], v[8 * hf + 5], v[8 * hf + 6], v[8 * hf + 7]);
-                            slot_send(&tm_ze, sl, c0 + 8 * hf, wrow0);
-                        }
+                        for (int j = 0; j < 4; ++j)
+                            *reinterpret_cast<float4 *>(sl_ze + lane * 64 + ((j ^ sw64) << 4)) =
+                                make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
                     }
                     if (Zb) {
                         if (c0 + 16 <= D) {           // full block: no per-element bounds
@@ -370,14 +367,17 @@ enc16_fused_kernel(const float *__restrict__ x, const float *__restrict__ W0, co
                                 v[4 * i] -= mq.x; v[4 * i + 1] -= mq.y; v[4 * i + 2] -= mq.z; v[4 * i + 3] -= mq.w;
                             }
 #pragma unroll
-                            for (int i = 0; i < 16; ++i) ss = fmaf(v[i], v[i], ss);
+                            for (int i = 0; i < 8; ++i) {
+                                ss0 = fmaf(v[2 * i], v[2 * i], ss0);
+                                ss1 = fmaf(v[2 * i + 1], v[2 * i + 1], ss1);
+                            }
                         } else {
 #pragma unroll
                             for (int i = 0; i < 16; ++i) {
                                 const int d = c0 + i;
                                 if (d < D) {
                                     v[i] -= smu[d];
-                                    ss = fmaf(v[i], v[i], ss);
+                                    ss0 = fmaf(v[i], v[i], ss0);
                                 } else {
                                     v[i] = d < D + 3 ? 1.0f : 0.f;
                                 }
@@ -389,12 +389,24 @@ enc16_fused_kernel(const float *__restrict__ x, const float *__restrict__ W0, co
                             const tc::op2_t pr = tc::f2op2(v[2 * i], v[2 * i + 1]);
                             o[i] = *reinterpret_cast<const uint32_t *>(&pr);
                         }
-                        uint8_t *sl = slot_take();
-                        *reinterpret_cast<uint4 *>(sl + lane * 32 + ((0 ^ sw) << 4)) = make_uint4(o[0], o[1], o[2], o[3]);
-                        *reinterpret_cast<uint4 *>(sl + lane * 32 + ((1 ^ sw) << 4)) = make_uint4(o[4], o[5], o[6], o[7]);
-                        slot_send(&tm_zb, sl, c0, wrow0);
+                        *reinterpret_cast<uint4 *>(sl_zb + lane * 32 + ((0 ^ sw32) << 4)) = make_uint4(o[0], o[1], o[2], o[3]);
+                        *reinterpret_cast<uint4 *>(sl_zb + lane * 32 + ((1 ^ sw32) << 4)) = make_uint4(o[4], o[5], o[6], o[7]);
+                    }
+                    ptx::fence_proxy_async();
+                    __syncwarp();
+                    if (lane == 0) {
+#ifdef ENC_EXP_SKIP
+                        if (!(ENC_EXP_SKIP & 1))
+#endif
+                        if (has_ze) ptx::tma_store_2d(&tm_ze, wbuf_s, c0, (int)wrow0);
+#ifdef ENC_EXP_SKIP
+                        if (!(ENC_EXP_SKIP & 2))
+#endif
+                        if (Zb) ptx::tma_store_2d(&tm_zb, wbuf_s + 2048u, c0, (int)wrow0);
+                        ptx::bulk_commit();
                     }
                 }
+                const float ss = ss0 + ss1;
                 if (Zb) {
                     zbad |= !(ss <= tc::OP_MAX * tc::OP_MAX);
                     // partial norms of the four column owners are combined (fixed order) after the NEXT tile's
@@ -549,13 +561,16 @@ inline int encoder_fused16_launch(const lipvq_dims_t *d, const lipvq_params_t *p
     const bool keep = a1 || h1 || a2 || h2;
     static const bool no_tma = [] { const char *e = getenv("LIPVQ_ENC_TMA"); return e && !strcmp(e, "0"); }();
     static const bool force_tf32 = [] { const char *e = getenv("LIPVQ_ENC"); return e && !strcmp(e, "tf32"); }();
-    CUtensorMap tm_ze, tm_zb;
+    CUtensorMap tm_ze, tm_zb, tm_ze64;   // z_e boxes: 32 bytes x 32 rows (tf32 kernel), 64 bytes x 32 rows (this one)
+    memset(&tm_ze64, 0, sizeof(tm_ze64));
     memset(&tm_ze, 0, sizeof(tm_ze));
     memset(&tm_zb, 0, sizeof(tm_zb));
     const int use_tma = !no_tma && (d->D & 3) == 0 && n < (int64_t)0x7fffffff - TM && (!Zb || (DKp & 7) == 0);
     if (use_tma) {
         LIPVQ_TRY(make_store_tmap(&tm_ze, z_e, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, (uint64_t)n, (uint64_t)d->D,
                                   (uint64_t)d->D));
+        LIPVQ_TRY(make_store_tmap(&tm_ze64, z_e, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, (uint64_t)n, (uint64_t)d->D,
+                                  (uint64_t)d->D, 64));
         if (Zb) {
 #ifdef LIPVQ_VQ_BF16
             const CUtensorMapDataType dt = CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
@@ -572,7 +587,7 @@ inline int encoder_fused16_launch(const lipvq_dims_t *d, const lipvq_params_t *p
             LIPVQ_TRY(set_smem(kern, Enc16Smem::TOTAL));
             kern<<<grid_for(n), ENC_THR, Enc16Smem::TOTAL, st>>>(x, p->enc0_w, p->enc0_b, p->enc2_w, p->enc2_b, Wn,
                                                                  p->lat_b, n, d->F, d->D, a1, h1, a2, h2, z_e, mu, Zb, zn,
-                                                                 DKp, counters, flag, tm_ze, tm_zb);
+                                                                 DKp, counters, flag, tm_ze64, tm_zb);
             return LIPVQ_OK;
         };
         if (use_tma) LIPVQ_TRY(keep ? launch(enc16_fused_kernel<true, true>) : launch(enc16_fused_kernel<true, false>));
