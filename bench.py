@@ -251,6 +251,37 @@ def run_ours(args, rank, world, local_rank):
     value = world * CHUNKS / (ms / 1e3)
     e2e = world * CHUNKS / (ms_e2e / 1e3)
 
+    # ---- BASELINE config 3: the data-parallel training step on ALL ranks -- forward + backward of the tokenizer loss
+    #      on this rank's 65 536 chunks, ONE NCCL all-reduce of the flat gradient bucket (+ the loss scalar), ONE fused
+    #      AdamW launch over the 14 tensors (icl.py:886-889, 913-914, 968-970).  Weak scaling like the forward.
+    import copy
+    from lipvq_vae_b200 import TokenizerTrainer
+    m_tr = copy.deepcopy(m).train()
+    trainer = TokenizerTrainer(m_tr)
+    n_total = world * rows
+    tr_steps = max(3, args.steps // 4)
+
+    def train_step(i):
+        trainer.step(xs[i % NBUF], n_total)
+    for i in range(2):
+        train_step(i)
+    torch.cuda.synchronize()
+    barrier()
+    lt0 = lib.lipvq_launch_count()
+    ms_train = _time_events(train_step, tr_steps, torch)
+    train_launches = (lib.lipvq_launch_count() - lt0) / tr_steps
+    barrier()
+    if world > 1:
+        t = torch.tensor([ms_train], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms_train = float(t.item())
+    train = {"workload": "training step: forward + backward (14 gradients) + flat-bucket all-reduce + fused AdamW, "
+                         "%d chunks per GPU" % CHUNKS,
+             "n_gpus": world, "ms_per_step": ms_train, "chunks_per_s": world * CHUNKS / (ms_train / 1e3),
+             "steps": tr_steps, "own_kernel_launches_per_step": train_launches,
+             "allreduce_bytes": int(trainer.dp._bucket.flat.numel() * 4), "timing": "CUDA events, max over ranks"}
+    del trainer, m_tr
+
     if rank != 0:
         return
     # ---- per-kernel durations INSIDE the step: the library brackets each of its launches with CUDA events on
@@ -352,18 +383,6 @@ def run_ours(args, rank, world, local_rank):
     gbs = (rows * D_LAT * 4 * 2 + rows * 8) / (ms_gl / 1e3) / 1e9
     hbm = {"kernel": "quantize_emit (gather + commitment-SSE mode, via lipvq_gather_loss)", "ms": ms_gl, "achieved_gbs": gbs, "peak_gbs": peaks["hbm_gbs"],
            "frac": gbs / peaks["hbm_gbs"], "bytes": "read z_e + write z_q + idx (codebook rows hit L2)"}
-
-    # ---- BASELINE config 3 flavour: forward + backward of the tokenizer loss on the same batch (no optimiser)
-    def train_step(i):
-        for q in m.parameters():
-            q.grad = None
-        _, loss = m(xs[i % NBUF])
-        loss.backward()
-    for i in range(2):
-        train_step(i)
-    ms_train = _time_events(train_step, max(3, args.steps // 4), torch)
-    train = {"workload": "forward + backward (14 gradients), %d chunks, 1 GPU" % CHUNKS, "ms_per_step": ms_train,
-             "chunks_per_s": CHUNKS / (ms_train / 1e3)}
 
     cpu_baseline = None
     if world == 1 and not args.no_cpu:

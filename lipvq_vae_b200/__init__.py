@@ -8,6 +8,8 @@ from ._native import (LipVQNativeError, SEARCH_EXACT, SEARCH_TENSOR, build_nativ
                       LIB_PATH)
 from .tokenizer import LLFQVAE_V4, LFQQuantizer, LipschitzMLP, install_into_robomimic
 from .stream import HostTokenizer
+from .dist import DataParallelTokenizer, FlatAdamW, TokenizerTrainer, shard_rows
 
-__all__ = ["LLFQVAE_V4", "LFQQuantizer", "LipschitzMLP", "install_into_robomimic", "HostTokenizer", "LipVQNativeError",
+__all__ = ["LLFQVAE_V4", "LFQQuantizer", "LipschitzMLP", "install_into_robomimic", "HostTokenizer", "DataParallelTokenizer", "FlatAdamW", "TokenizerTrainer",
+           "shard_rows", "LipVQNativeError",
            "SEARCH_EXACT", "SEARCH_TENSOR", "build_native", "native_lib", "LIB_PATH"]

@@ -118,3 +118,57 @@ class DataParallelTokenizer:
             dist.all_reduce(b.flat, group=self.pg)
         b.unpack_into([counts, sums])
         return counts, sums
+
+
+class FlatAdamW:
+    """``torch.optim.AdamW(model.parameters(), lr, weight_decay)`` (robomimic/algo/icl.py:886-889) as ONE kernel
+    launch per step: the 14 parameters are re-pointed at views of one flat fp32 buffer, the moments are flat too,
+    and ``lipvq_adamw_step`` updates everything at once from a flat gradient (the all-reduce bucket)."""
+
+    def __init__(self, model, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=1e-4):
+        self.params = [p for p in model.parameters()]
+        dev = self.params[0].device
+        self.numel = sum(p.numel() for p in self.params)
+        self.flat = torch.empty(self.numel, dtype=torch.float32, device=dev)
+        off = 0
+        for p in self.params:
+            n = p.numel()
+            self.flat[off:off + n].copy_(p.data.reshape(-1))
+            p.data = self.flat[off:off + n].view(p.shape)      # same values, storage now inside the flat buffer
+            off += n
+        self.exp_avg = torch.zeros_like(self.flat)
+        self.exp_avg_sq = torch.zeros_like(self.flat)
+        self.lr, self.betas, self.eps, self.weight_decay = lr, betas, eps, weight_decay
+        self.steps = 0
+
+    def step(self, flat_grad):
+        """flat_grad: fp32 [numel] in ``model.parameters()`` order (FlatBucket.flat[:numel])."""
+        import ctypes as C
+        from . import _native as N
+        if flat_grad.numel() < self.numel or not flat_grad.is_cuda:
+            raise ValueError("flat_grad must be a CUDA tensor with at least %d elements" % self.numel)
+        self.steps += 1
+        st = C.c_void_p(torch.cuda.current_stream(self.flat.device).cuda_stream)
+        N.check(N.lib().lipvq_adamw_step(self.flat.data_ptr(), flat_grad.data_ptr(), self.exp_avg.data_ptr(),
+                                         self.exp_avg_sq.data_ptr(), self.numel, self.steps, self.lr, self.betas[0],
+                                         self.betas[1], self.eps, self.weight_decay, st), "lipvq_adamw_step")
+
+
+class TokenizerTrainer:
+    """One data-parallel training step of the tokenizer (BASELINE config 3): forward + backward on this rank's
+    rows, ONE all-reduce of the flat gradient bucket, ONE fused AdamW launch.  Mirrors what
+    ``ICLTransformer_GMM`` does with ``self.vq_vae_model`` each iteration (icl.py:913-914, 968-970)."""
+
+    def __init__(self, model, process_group=None, lr=1e-3, weight_decay=1e-4):
+        self.dp = DataParallelTokenizer(model, process_group)
+        self.opt = FlatAdamW(model, lr=lr, weight_decay=weight_decay)
+        self.model = model
+
+    def step(self, x_local, n_total=None):
+        for p in self.opt.params:
+            p.grad = None                       # optimizer.zero_grad(set_to_none=True), icl.py:913
+        z_latent, loss = self.dp(x_local, n_total)
+        loss.backward()
+        loss_global = self.dp.allreduce_grads(loss)
+        self.opt.step(self.dp._bucket.flat)
+        return z_latent, loss_global

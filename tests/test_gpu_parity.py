@@ -314,3 +314,32 @@ def test_fused_encoder_latents_and_range_fallback(case):
         # (at 400x the pre-activations are O(100): fp32 dot products of that size round at ~1e-5 themselves)
         assert np.abs(got - ref).max() < (2e-6 if mult == 1.0 else 5e-5), (mult, np.abs(got - ref).max())
         assert orc.rel_err(got, ref) < (RTOL if mult == 1.0 else 5e-5)
+
+
+def test_trainer_step_matches_torch_adamw():
+    """TokenizerTrainer (forward + backward + flat bucket + one fused AdamW launch) against the oracle's gradients fed
+    to torch.optim.AdamW with the reference's settings (icl.py:886-889), two steps."""
+    from lipvq_vae_b200 import TokenizerTrainer
+    p, x = case_inputs("small")
+    m = _model(p, 1)
+    tr = TokenizerTrainer(m)
+    ref = {k: torch.nn.Parameter(torch.from_numpy(v.copy()).double()) for k, v in p.items()}
+    opt = torch.optim.AdamW(list(ref.values()), lr=1e-3, weight_decay=1e-4)
+    xt = torch.from_numpy(x).cuda()
+    for _ in range(2):
+        cur = {k: v.detach().numpy().astype(np.float32) for k, v in ref.items()}
+        fw = orc.forward(cur, x)
+        gr = orc.backward(cur, x, fw)
+        opt.zero_grad()
+        for k, v in ref.items():
+            v.grad = torch.from_numpy(gr[k]).double()
+        opt.step()
+        _, loss = tr.step(xt)
+        assert abs(loss.item() - fw["loss"]) < 1e-5 * abs(fw["loss"])
+    # Adam's update lr * m / (sqrt(v) + eps) is ill-conditioned where |g| is at the gradient's own rounding noise
+    # (its sign decides a +-lr move), so: all elements within the total possible movement (2 steps x lr), and
+    # 99% of them at fp32 rounding level
+    for k, t in m.named_parameters():
+        d = np.abs(t.detach().cpu().numpy().astype(np.float64) - ref[k].detach().numpy()).reshape(-1)
+        assert d.max() <= 2 * 1e-3 * 1.01, k
+        assert np.quantile(d, 0.99) < 2e-6, (k, np.quantile(d, 0.99))
