@@ -270,7 +270,7 @@ int lipvq_encode_search_fwd(const lipvq_dims_t *d, const lipvq_params_t *p, cons
     const tc::Workspace w = tc::carve(vq_ws, g);
     LIPVQ_TRY(vq_tensor_prep(p->codebook, g, w, st));
     LIPVQ_TRY(mlp::encoder_fused16_launch(d, p, x, n, a->a1, a->h1, a->a2, a->h2, a->scale, a->Wn, a->z_e, img, w.mu,
-                                          w.Zb, w.zn, g.DKp, w.counters, st));
+                                          w.Zb, w.zn, g.DKz, w.counters, st));
     return vq_tensor_search(a->z_e, p->codebook, g, w, a->idx, nullptr, stats, st);
 }
 

@@ -63,7 +63,7 @@ __device__ __forceinline__ op2_t f2op2(float a, float b) { return __floats2half2
 constexpr float PAD_SCORE = 1.0e30f;   // en of the padding codes (never inside any window)
 
 struct Geometry {
-    int D, K, DK, DKp, NKB, NK16, Kp, nct;
+    int D, K, DK, DKp, DKz, NKB, NK16, Kp, nct;   // DKp: Eb row pitch (whole K blocks); DKz: Zb row pitch (whole MMA K steps)
     int64_t n, Np, n_tiles;
 };
 inline Geometry geometry(int64_t n, int D, int K) {
@@ -73,6 +73,7 @@ inline Geometry geometry(int64_t n, int D, int K) {
     g.DKp = (g.DK + KBLK - 1) / KBLK * KBLK;
     g.NKB = g.DKp / KBLK;
     g.NK16 = (g.DK + UK - 1) / UK;
+    g.DKz = g.NK16 * UK;   // the part of the last K block past DKz is out of bounds for the TMA loads (zero fill)
     g.Kp = (K + BN - 1) / BN * BN;
     g.nct = g.Kp / BN;
     g.Np = (n + BM - 1) / BM * BM;
@@ -146,6 +147,68 @@ __global__ void vq_prep_rows_kernel(const float *__restrict__ E, const float *__
 // ------------------------------------------------------------------ pass 1: row operand
 // Zb row = [op(z - mu) | 1 1 1 | 0...]; zn = ||z - mu||.  One thread per 8 consecutive columns (32 B in, 16 B
 // out, fully coalesced); the row norm is combined in shared memory in column order (deterministic).
+// Rows never straddle a warp: a warp holds floor(32 / cpr) rows (cpr = 8-column chunks per row <= 32), the row norm
+// is a fixed-order shuffle sum inside the row's lanes -- no block barrier in the streaming loop.
+__global__ void __launch_bounds__(256) vq_convert_z_warp_kernel(const float *__restrict__ z, const float *__restrict__ mu,
+                                                                int64_t n, int64_t Np, int D, int DKz,
+                                                                op_t *__restrict__ Zb, float *__restrict__ zn,
+                                                                int *__restrict__ counters) {
+    __shared__ float s_mu[5 * KBLK];
+    for (int i = threadIdx.x; i < DKz; i += 256) s_mu[i] = i < D ? mu[i] : 0.f;
+    __syncthreads();
+    const int cpr = DKz >> 3, rpw = 32 / cpr, rpb = 8 * rpw;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int rl = lane / cpr, ch = lane - rl * cpr;
+    const bool active = rl < rpw, vec = (D & 3) == 0;
+    const int d0 = ch * 8;
+    bool bad = false;
+    for (int64_t r0 = (int64_t)blockIdx.x * rpb; r0 < Np; r0 += (int64_t)gridDim.x * rpb) {
+        const int64_t r = r0 + warp * rpw + rl;
+        float ss = 0.f;
+        if (active && r < Np) {
+            float v[8];
+#pragma unroll
+            for (int q = 0; q < 2; ++q) {
+                const int d = d0 + 4 * q;
+                float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (r < n && d < D) {
+                    const float *p = z + r * D + d;
+                    if (vec) t = __ldg(reinterpret_cast<const float4 *>(p));
+                    else {
+                        t.x = __ldg(p);
+                        if (d + 1 < D) t.y = __ldg(p + 1);
+                        if (d + 2 < D) t.z = __ldg(p + 2);
+                        if (d + 3 < D) t.w = __ldg(p + 3);
+                    }
+                }
+                v[4 * q] = t.x; v[4 * q + 1] = t.y; v[4 * q + 2] = t.z; v[4 * q + 3] = t.w;
+            }
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const int d = d0 + i;
+                if (r < n && d < D) {
+                    v[i] -= s_mu[d];
+                    ss = fmaf(v[i], v[i], ss);
+                    bad |= !(fabsf(v[i]) <= OP_MAX);
+                } else {
+                    v[i] = (r < n && d < D + 3) ? 1.0f : 0.f;
+                }
+            }
+            __align__(16) op2_t o[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) o[i] = f2op2(v[2 * i], v[2 * i + 1]);
+            *reinterpret_cast<uint4 *>(Zb + r * DKz + d0) = *reinterpret_cast<const uint4 *>(o);
+        }
+        float t = ss;                                    // chunk 0 + chunk 1 + ... (fixed order)
+        for (int i = 1; i < cpr; ++i) {
+            const float o = __shfl_down_sync(0xffffffffu, ss, i);
+            if (ch + i < cpr) t += o;
+        }
+        if (active && ch == 0 && r < n) zn[r] = sqrtf(t);
+    }
+    if (__any_sync(0xffffffffu, bad) && lane == 0) atomicOr(counters + 3, 1);   // operand out of range -> exact search
+}
+
 __global__ void __launch_bounds__(256) vq_convert_z_kernel(const float *__restrict__ z, const float *__restrict__ mu,
                                                            int64_t n, int64_t Np, int D, int DKp,
                                                            op_t *__restrict__ Zb, float *__restrict__ zn,
@@ -647,7 +710,7 @@ inline Workspace carve(void *ws, const Geometry &g) {
     w.counters = (int *)take(sizeof(int) * 8);
     w.emax = (float *)(w.counters + 6);          // zeroed together with the counters, filled by atomicMax
     w.Eb = (op_t *)take((size_t)g.Kp * g.DKp * 2);
-    w.Zb = (op_t *)take((size_t)g.Np * g.DKp * 2);
+    w.Zb = (op_t *)take((size_t)g.Np * g.DKz * 2);
     w.zn = (float *)take(sizeof(float) * g.Np);
     w.cand = (uint2 *)take(sizeof(uint2) * g.Np * NPART * LCAP);
     w.cand_meta = (int *)take(sizeof(int) * g.Np * NPART);
@@ -703,7 +766,7 @@ inline int vq_tensor_search(const float *z, const float *E, const tc::Geometry &
     const int64_t n = g.n;
     const int D = g.D, K = g.K;
     CUtensorMap ta, tb;
-    LIPVQ_TRY(make_tmap(&ta, w.Zb, (uint64_t)g.Np, (uint64_t)g.DKp, BM));
+    LIPVQ_TRY(make_tmap(&ta, w.Zb, (uint64_t)g.Np, (uint64_t)g.DKz, BM));
     LIPVQ_TRY(make_tmap(&tb, w.Eb, (uint64_t)g.Kp, (uint64_t)g.DKp, BN));
     int rc = LIPVQ_ESHAPE;
     switch (g.NKB) {
@@ -750,11 +813,15 @@ inline int vq_tensor_launch(const float *z, const float *E, int64_t n, int D, in
     const Workspace w = carve((void *)align_up((size_t)ws, 1024), g);
     LIPVQ_TRY(vq_tensor_prep(E, g, w, st));
     {
-        const int rpb = 256 / (g.DKp >> 3);
+        const int cpr = g.DKz >> 3;
+        const int rpb = cpr <= 32 ? 8 * (32 / cpr) : 256 / cpr;
         int64_t blocks = (g.Np + rpb - 1) / rpb;
         if (blocks > 8 * kNumSMs) blocks = 8 * kNumSMs;
         ProfScope prof("vq_convert_z_kernel", st);
-        vq_convert_z_kernel<<<(unsigned)blocks, 256, 0, st>>>(z, w.mu, n, g.Np, D, g.DKp, w.Zb, w.zn, w.counters);
+        if (cpr <= 32)
+            vq_convert_z_warp_kernel<<<(unsigned)blocks, 256, 0, st>>>(z, w.mu, n, g.Np, D, g.DKz, w.Zb, w.zn, w.counters);
+        else
+            vq_convert_z_kernel<<<(unsigned)blocks, 256, 0, st>>>(z, w.mu, n, g.Np, D, g.DKz, w.Zb, w.zn, w.counters);
         LIPVQ_LAUNCH_OK();
     }
     return vq_tensor_search(z, E, g, w, idx, d2, stats, st);
