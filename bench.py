@@ -281,6 +281,24 @@ def run_ours(args, rank, world, local_rank):
              "steps": tr_steps, "own_kernel_launches_per_step": train_launches,
              "allreduce_bytes": int(trainer.dp._bucket.flat.numel() * 4), "timing": "CUDA events, max over ranks"}
     del trainer, m_tr
+    # EMA variant of the same step (north_star item 3; extension, not in the reference): the codebook follows the EMA
+    # of its clusters -- per-code counts/sums by the scatter-add kernel, all-reduced in one more collective
+    m_tr = copy.deepcopy(m).train()
+    trainer = TokenizerTrainer(m_tr, ema_codebook=True)
+    for i in range(2):
+        train_step(i)
+    torch.cuda.synchronize()
+    barrier()
+    ms_ema = _time_events(train_step, tr_steps, torch)
+    barrier()
+    if world > 1:
+        t = torch.tensor([ms_ema], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms_ema = float(t.item())
+    train["ema_codebook_variant"] = {"ms_per_step": ms_ema, "chunks_per_s": world * CHUNKS / (ms_ema / 1e3),
+                                     "extra": "scatter-add of z_e per code + all-reduce of counts[K], sums[K,D] + "
+                                              "lipvq_ema_update (parity unpinned: no reference counterpart)"}
+    del trainer, m_tr
 
     if rank != 0:
         return

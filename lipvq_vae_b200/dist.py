@@ -159,16 +159,31 @@ class TokenizerTrainer:
     rows, ONE all-reduce of the flat gradient bucket, ONE fused AdamW launch.  Mirrors what
     ``ICLTransformer_GMM`` does with ``self.vq_vae_model`` each iteration (icl.py:913-914, 968-970)."""
 
-    def __init__(self, model, process_group=None, lr=1e-3, weight_decay=1e-4):
+    def __init__(self, model, process_group=None, lr=1e-3, weight_decay=1e-4, ema_codebook=False, ema_gamma=0.99):
         self.dp = DataParallelTokenizer(model, process_group)
         self.opt = FlatAdamW(model, lr=lr, weight_decay=weight_decay)
         self.model = model
+        # EMA mode (extension, SURVEY 8a row 11): the codebook follows the EMA of its clusters instead of AdamW --
+        # its gradient is zeroed in the bucket and counts[K] + sums[K,D] are all-reduced in one more collective
+        self.ema_codebook, self.ema_gamma = ema_codebook, ema_gamma
+        self._cb_index = [i for i, p in enumerate(self.opt.params) if p is model.quantizer.codebook][0]
 
     def step(self, x_local, n_total=None):
         for p in self.opt.params:
             p.grad = None                       # optimizer.zero_grad(set_to_none=True), icl.py:913
         z_latent, loss = self.dp(x_local, n_total)
         loss.backward()
+        if self.ema_codebook:
+            counts, sums = self.model.codebook_statistics()
+            self.dp.allreduce_codebook_stats(counts, sums)
         loss_global = self.dp.allreduce_grads(loss)
-        self.opt.step(self.dp._bucket.flat)
+        if self.ema_codebook:
+            cb = self.model.quantizer.codebook
+            keep = cb.data.clone()                              # AdamW must not move (or decay) the codebook
+            self.dp._bucket.views[self._cb_index].zero_()
+            self.opt.step(self.dp._bucket.flat)
+            cb.data.copy_(keep)
+            self.model.ema_update(counts, sums, gamma=self.ema_gamma)
+        else:
+            self.opt.step(self.dp._bucket.flat)
         return z_latent, loss_global

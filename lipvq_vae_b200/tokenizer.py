@@ -96,7 +96,7 @@ class _TokenizerFn(torch.autograd.Function):
             x_recon = torch.empty(0, F_, **f32)
             ctx.mark_non_differentiable(z_q, idx, vq_stats, x_recon)
             ctx.empty = True
-            return z_q, stats, idx, vq_stats, x_recon
+            return z_q, stats, idx, vq_stats, x_recon, None
         ctx.empty = False
         x_recon = torch.empty(n, F_, **f32)
         if not need_grad:
@@ -104,7 +104,7 @@ class _TokenizerFn(torch.autograd.Function):
                                             _p(idx), _p(x_recon), _p(stats), _p(vq_stats), _p(ws), ws.numel(), st),
                     "lipvq_forward_fused")
             ctx.mark_non_differentiable(z_q, idx, vq_stats, x_recon)
-            return z_q, stats, idx, vq_stats, x_recon
+            return z_q, stats, idx, vq_stats, x_recon, None
         a1 = torch.empty(n, H1, **f32); h1 = torch.empty(n, H1, **f32)
         a2 = torch.empty(n, H, **f32); h2 = torch.empty(n, H, **f32)
         scale = torch.empty(D, **f32); Wn = torch.empty(D, H, **f32)
@@ -124,11 +124,11 @@ class _TokenizerFn(torch.autograd.Function):
         ctx.save_for_backward(x, *params, a1, h1, a2, h2, scale, Wn, z_e, idx, z_q, c1, d1, c2, d2, xr_code)
         ctx.dims = dims
         ctx.n_total = n_total
-        ctx.mark_non_differentiable(z_q, idx, vq_stats, x_recon)
-        return z_q, stats, idx, vq_stats, x_recon
+        ctx.mark_non_differentiable(z_q, idx, vq_stats, x_recon, z_e)
+        return z_q, stats, idx, vq_stats, x_recon, z_e
 
     @staticmethod
-    def backward(ctx, g_zlat, g_stats, g_idx, g_vq, g_xr):
+    def backward(ctx, g_zlat, g_stats, g_idx, g_vq, g_xr, g_ze=None):
         none4 = (None, None, None, None)
         if ctx.empty or g_stats is None:
             return none4 + (None,) * 14
@@ -291,6 +291,44 @@ class LLFQVAE_V4(nn.Module):
         self.last_reconstruction = None
         self.last_loss_terms = None
         self.last_search_stats = None
+        self.last_z_e = None
+        # EMA codebook state (extension, NOT in the reference): plain attributes created on first use -- the module
+        # keeps the reference's "14 parameters, no buffers" surface (algo.py:323-337 serialises state_dict only)
+        self.ema_cluster_size = None
+        self.ema_cluster_sum = None
+
+    # ------------------------------------------------------------------ EMA codebook update (extension)
+    @torch.no_grad()
+    def codebook_statistics(self, z_e=None, indices=None):
+        """Per-code ``counts[K]`` and ``sums[K, D] = sum_{idx[n]=k} z_e[n]`` of a batch (the EMA statistics; the
+        same scatter-add access pattern as the codebook gradient).  Defaults to the last training forward."""
+        z_e = self.last_z_e if z_e is None else z_e
+        indices = self.last_indices if indices is None else indices
+        if z_e is None or indices is None:
+            raise LipVQNativeError("codebook_statistics needs a training-mode forward first (or explicit z_e, indices)")
+        _check_cuda(z_e, "z_e")
+        z_e = z_e.contiguous()
+        indices = indices.contiguous()
+        K, D = self.num_codes, self.latent_dim
+        counts = torch.zeros(K, dtype=torch.float32, device=z_e.device)
+        sums = torch.zeros(K, D, dtype=torch.float32, device=z_e.device)
+        N.check(N.lib().lipvq_scatter_add(_p(z_e), _p(indices), z_e.shape[0], D, K, _p(sums), _p(counts),
+                                          _stream_ptr(z_e.device)), "lipvq_scatter_add")
+        return counts, sums
+
+    @torch.no_grad()
+    def ema_update(self, counts, sums, gamma=0.99, eps=1e-5):
+        """``n <- g n + (1-g) counts; m <- g m + (1-g) sums; codebook <- m / laplace(n)`` in place.  ``counts`` /
+        ``sums`` must already be summed over the data-parallel ranks (``DataParallelTokenizer.allreduce_codebook_stats``)
+        so every replica applies the identical update.  Parity unpinned: the reference trains the codebook with AdamW."""
+        E = self.quantizer.codebook.data
+        if self.ema_cluster_size is None or self.ema_cluster_size.device != E.device:
+            self.ema_cluster_sum = E.detach().clone()     # m_0 = E, n_0 = 1: the first update starts from the codebook
+            self.ema_cluster_size = torch.ones(self.num_codes, dtype=torch.float32, device=E.device)
+        ws = _workspace(E.device, self._dims(), 1)
+        N.check(N.lib().lipvq_ema_update(_p(E), _p(self.ema_cluster_size), _p(self.ema_cluster_sum), _p(counts.contiguous()),
+                                         _p(sums.contiguous()), self.num_codes, self.latent_dim, float(gamma), float(eps),
+                                         _p(ws), ws.numel(), _stream_ptr(E.device)), "lipvq_ema_update")
 
     # ------------------------------------------------------------------ helpers
     def _dims(self):
@@ -314,8 +352,9 @@ class LLFQVAE_V4(nn.Module):
         params = self._param_list()
         if not torch.is_grad_enabled():
             params = [p.detach() for p in params]
-        z_latent, stats, idx, vq_stats, x_recon = _TokenizerFn.apply(
+        z_latent, stats, idx, vq_stats, x_recon, z_e = _TokenizerFn.apply(
             x.detach(), max(n_total, 1), int(self.search_mode), self._dims(), *params)
+        self.last_z_e = z_e                         # encoder output of this batch (training forward only), no graph
         self.last_indices = idx
         self.last_reconstruction = x_recon          # decode(z_q) of this batch (v5:75-76), no graph
         self.last_loss_terms = stats.detach()

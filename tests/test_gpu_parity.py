@@ -343,3 +343,25 @@ def test_trainer_step_matches_torch_adamw():
         d = np.abs(t.detach().cpu().numpy().astype(np.float64) - ref[k].detach().numpy()).reshape(-1)
         assert d.max() <= 2 * 1e-3 * 1.01, k
         assert np.quantile(d, 0.99) < 2e-6, (k, np.quantile(d, 0.99))
+
+
+def test_ema_codebook_mode_vs_oracle():
+    """EMA codebook mode of the module (extension; parity unpinned -> checked against the oracle's own restatement):
+    statistics of a training forward + two EMA updates."""
+    p, x = case_inputs("small")
+    m = _model(p, 1).train()
+    E = p["quantizer.codebook"].copy()
+    n_ema, m_ema = np.ones(E.shape[0], np.float32), E.copy()
+    xt = torch.from_numpy(x).cuda()
+    for _ in range(2):
+        cur = dict(p)
+        cur["quantizer.codebook"] = E
+        fw = orc.forward(cur, x)
+        E, n_ema, m_ema, counts_ref, sums_ref = orc.ema_update(E, n_ema, m_ema, fw["z_e"], fw["idx"], gamma=0.9)
+        m(xt)
+        counts, sums = m.codebook_statistics()
+        assert np.array_equal(counts.cpu().numpy(), counts_ref)
+        assert orc.rel_err(sums.cpu().numpy(), sums_ref) < RTOL
+        m.ema_update(counts, sums, gamma=0.9)
+        assert orc.rel_err(m.quantizer.codebook.detach().cpu().numpy(), E) < RTOL
+    assert "ema_cluster_size" not in m.state_dict() and len(list(m.buffers())) == 0   # reference surface intact
