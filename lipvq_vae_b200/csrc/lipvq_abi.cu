@@ -413,8 +413,11 @@ int lipvq_decoder_bwd(const lipvq_dims_t *d, const lipvq_params_t *p, const floa
     // every row with code k sees the same decoder, so the reconstruction gradient is summed per code first:
     // g_R[k] = sum_{idx[n]=k} 2 (x_recon[n] - x[n]) / (n_total F), and the decoder backward runs on K rows
     LIPVQ_CUDA_OK(cudaMemsetAsync(g_R, 0, (size_t)K * d->F * sizeof(float), st));
-    scatter_add_kernel<true><<<blocks, 256, 0, st>>>(x, a->idx, n, d->F, K, g_R, nullptr, a->xr_code, a_r, grad_scale);
-    LIPVQ_LAUNCH_OK();
+    {
+        ProfScope prof("scatter_add_kernel", st);
+        scatter_add_kernel<true><<<blocks, 256, 0, st>>>(x, a->idx, n, d->F, K, g_R, nullptr, a->xr_code, a_r, grad_scale);
+        LIPVQ_LAUNCH_OK();
+    }
     LIPVQ_TRY(linear_bwd_weight(g_R, a->d2, g->out_w, g->out_b, K, d->F, d->H, part, st));
     LIPVQ_TRY(linear_bwd_input<ACT_GELU>(g_R, p->out_w, a->c2, g_c2, K, d->F, d->H, nullptr, nullptr, 0.f, nullptr, st));
     LIPVQ_TRY(linear_bwd_weight(g_c2, a->d1, g->dec2_w, g->dec2_b, K, d->H, d->H1, part, st));
@@ -424,9 +427,12 @@ int lipvq_decoder_bwd(const lipvq_dims_t *d, const lipvq_params_t *p, const floa
     LIPVQ_TRY(linear_bwd_input<ACT_NONE>(g_c1, p->dec0_w, nullptr, g->codebook, K, d->H1, d->D, nullptr, nullptr, 0.f,
                                          nullptr, st));
     // ... plus the codebook loss: sum_{idx[n]=k} 0.5 (E[k] - z_e[n]) / (n_total D)   (v5:81)
-    scatter_add_kernel<true><<<blocks, 256, 0, st>>>(a->z_e, a->idx, n, d->D, K, g->codebook, nullptr, p->codebook,
-                                                     a_q, grad_scale);
-    LIPVQ_LAUNCH_OK();
+    {
+        ProfScope prof("scatter_add_kernel", st);
+        scatter_add_kernel<true><<<blocks, 256, 0, st>>>(a->z_e, a->idx, n, d->D, K, g->codebook, nullptr, p->codebook,
+                                                         a_q, grad_scale);
+        LIPVQ_LAUNCH_OK();
+    }
     return LIPVQ_OK;
 }
 
@@ -457,8 +463,11 @@ int lipvq_encoder_bwd(const lipvq_dims_t *d, const lipvq_params_t *p, const floa
     float *part = b.take<float>(max_splitk_floats(d, n));
     if (!b.ok()) return LIPVQ_EWORKSPACE;
     const float a_q = (float)(0.5 / ((double)n_total * d->D));
-    commit_sigmoid_bwd_kernel<<<kRedBlocks, 256, 0, st>>>(a->z_e, a->z_q, a_q, grad_scale, n * d->D, g_pre);
-    LIPVQ_LAUNCH_OK();
+    {
+        ProfScope prof("commit_sigmoid_bwd_kernel", st);
+        commit_sigmoid_bwd_kernel<<<kRedBlocks, 256, 0, st>>>(a->z_e, a->z_q, a_q, grad_scale, n * d->D, g_pre);
+        LIPVQ_LAUNCH_OK();
+    }
     LIPVQ_TRY(linear_bwd_weight(g_pre, a->h2, gWn, g->lat_b, n, d->D, d->H, part, st));
     lipschitz_bwd_kernel<<<(d->D + 7) / 8, 256, 0, st>>>(gWn, p->lat_W, p->lat_ci, a->scale, d->D, d->H,
                                                         g->lat_W, g->lat_ci);

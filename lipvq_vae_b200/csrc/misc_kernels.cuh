@@ -347,6 +347,47 @@ __global__ void __launch_bounds__(256) scatter_add_kernel(
         const unsigned m = __match_any_sync(0xffffffffu, valid ? code : 0xffffffffu);
         if (head) atomicAdd(counts + code, (float)__popc(m));
     }
+    if ((D & 3) == 0 && ((reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(sums) |
+                          (DIFF ? reinterpret_cast<uintptr_t>(T) : 0)) & 15) == 0) {
+        // vector path: a lane owns 4 consecutive columns; 4 rows' loads are in flight before the run logic touches
+        // them; a run is flushed with one 16-byte vector atomic per lane
+        const int D4 = D >> 2;
+        for (int c = lane; c < D4; c += 32) {
+            float4 acc = make_float4(0.f, 0.f, 0.f, 0.f), t = acc;
+            unsigned cur = 0xffffffffu;
+            auto flush = [&]() {
+                const float s = DIFF ? alpha : 1.0f;
+                atomicAdd(reinterpret_cast<float4 *>(sums + (size_t)cur * D) + c,
+                          make_float4(s * acc.x, s * acc.y, s * acc.z, s * acc.w));
+            };
+            for (int e = 0; e < 32; e += 4) {
+                unsigned long long k4[4];
+                float4 v[4];
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    k4[q] = keys[e0 + e + q];
+                    v[q] = make_float4(0.f, 0.f, 0.f, 0.f);
+                    if (k4[q] != ~0ull)
+                        v[q] = __ldg(reinterpret_cast<const float4 *>(src + (r0 + (unsigned)(k4[q] & 0xffffffffu)) * D) + c);
+                }
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    if (k4[q] == ~0ull) continue;          // (padding sorts last)
+                    const unsigned code = (unsigned)(k4[q] >> 32);
+                    if (code != cur) {
+                        if (cur != 0xffffffffu) flush();
+                        cur = code;
+                        acc = make_float4(0.f, 0.f, 0.f, 0.f);
+                        if (DIFF) t = __ldg(reinterpret_cast<const float4 *>(T + (size_t)code * D) + c);
+                    }
+                    if (DIFF) { acc.x += t.x - v[q].x; acc.y += t.y - v[q].y; acc.z += t.z - v[q].z; acc.w += t.w - v[q].w; }
+                    else { acc.x += v[q].x; acc.y += v[q].y; acc.z += v[q].z; acc.w += v[q].w; }
+                }
+            }
+            if (cur != 0xffffffffu) flush();
+        }
+        return;
+    }
     for (int c = lane; c < D; c += 32) {
         float acc = 0.f, t = 0.f;
         unsigned cur = 0xffffffffu;
