@@ -25,7 +25,7 @@
 extern "C" {
 #endif
 
-#define LIPVQ_ABI_VERSION 3
+#define LIPVQ_ABI_VERSION 4
 
 enum {
     LIPVQ_OK = 0,
@@ -85,6 +85,9 @@ typedef struct {
     float *c2, *d2; /* decoder.2 pre-activation / GELU output of E  [K,H]         */
     float *x_recon; /* to_output(...) [N,F]          v5:76  (= xr_code[idx])       */
     float *xr_code; /* to_output(decoder(E)) [K,F]: reconstruction of every code  */
+    float *g_pre;   /* nullable [N,D]: 0.5 (z_e - z_q) z_e (1 - z_e) / (n_total D), the commitment gradient through
+                     * the sigmoid up to dL/dloss (v5:80).  Written by lipvq_quantize_decode_fwd while the row is in
+                     * registers; lipvq_encoder_bwd then skips its own pass over z_e and z_q.               */
 } lipvq_acts_t;
 
 int lipvq_abi_version(void);
@@ -156,7 +159,7 @@ int lipvq_decoder_fwd(const lipvq_dims_t *dims, const lipvq_params_t *p, const f
  * [K,F]); one streaming pass over the rows then writes z_q[n] = E[idx[n]] to acts->z_q (this IS z_latent,
  * v5:74), x_recon[n] = xr_code[idx[n]] to acts->x_recon (nullable), and sse[0] = sum (x_recon-x)^2,
  * sse[1] = sum (z_q-z_e)^2 (device double[2], overwritten).  acts: idx, z_e are read; z_q is written;
- * c1,d1,c2,d2,xr_code ([K,.], code level) are written when non-null (kept for backward).
+ * c1,d1,c2,d2,xr_code ([K,.], code level) and g_pre ([N,D]) are written when non-null (kept for backward).
  * x may be null (sse[0] = 0).  loss_out (nullable, needs x): device float[4] = {loss, recon, commit, codebook}
  * as lipvq_loss_finalize would write them for n_total global rows (v5:79-83), from the same reduction. */
 int lipvq_quantize_decode_fwd(const lipvq_dims_t *dims, const lipvq_params_t *p, const float *x,
@@ -188,7 +191,8 @@ int lipvq_scatter_add(const float *src, const int64_t *idx, int64_t n_rows, int3
 
 /* Backward of the encoder from the commitment term only (v5:80; there is no straight-through
  * path): g_ze = 0.5*(z_e - z_q)/(n_total*D) -> sigmoid' -> Lipschitz-norm backward
- * (through scale, sum|W|, softplus) -> MLP backward. */
+ * (through scale, sum|W|, softplus) -> MLP backward.  With acts->g_pre (written by the forward for the same
+ * n_total) the first two steps are already done; grad_scale is then applied in the GEMM epilogues. */
 int lipvq_encoder_bwd(const lipvq_dims_t *dims, const lipvq_params_t *p, const float *x,
                       int64_t n_rows, int64_t n_total, const float *grad_scale,
                       const lipvq_acts_t *acts, const lipvq_grads_t *g, void *ws,

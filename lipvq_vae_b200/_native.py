@@ -53,7 +53,7 @@ class Grads(C.Structure):
     _fields_ = [(n, C.c_void_p) for n in _PARAM_FIELDS]
 
 
-_ACT_FIELDS = ["a1", "h1", "a2", "h2", "scale", "Wn", "z_e", "idx", "z_q", "c1", "d1", "c2", "d2", "x_recon", "xr_code"]
+_ACT_FIELDS = ["a1", "h1", "a2", "h2", "scale", "Wn", "z_e", "idx", "z_q", "c1", "d1", "c2", "d2", "x_recon", "xr_code", "g_pre"]
 
 
 class Acts(C.Structure):
@@ -142,7 +142,7 @@ def lib():
                     fn = getattr(h, name)
                     fn.restype = res
                     fn.argtypes = args
-                if h.lipvq_abi_version() != 3:
+                if h.lipvq_abi_version() != 4:
                     raise LipVQNativeError("ABI version mismatch")
                 _lib = h
     return _lib

@@ -15,6 +15,7 @@ struct GemmArgs {
     float *C; int64_t ldc;              // C[m*ldc + n]
     int64_t M; int N; int64_t K;
     float alpha;                        // scale on the accumulator
+    const float *alpha_dev;             // device scalar multiplying alpha (nullable)
     const float *bias;                  // [N] or null
     float *pre; int64_t ldpre;          // pre-activation output (nullable)
     const float *dpre; int64_t lddpre;  // multiply by DACT'(dpre[m,n]) (nullable)
@@ -100,6 +101,7 @@ __global__ void __launch_bounds__(GNT) gemm_simt_kernel(const GemmArgs g) {
 
     float *C = g.C;
     const float aux_alpha = g.aux_alpha * ((g.aux1 && g.aux_scale_dev) ? __ldg(g.aux_scale_dev) : 1.f);
+    const float alpha = g.alpha * (g.alpha_dev ? __ldg(g.alpha_dev) : 1.f);
     if (g.k_chunk > 0) C += (int64_t)blockIdx.z * g.M * g.ldc;
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
@@ -109,7 +111,7 @@ __global__ void __launch_bounds__(GNT) gemm_simt_kernel(const GemmArgs g) {
         for (int j = 0; j < 4; ++j) {
             const int n = n0 + tx * 4 + j;
             if (n >= g.N) continue;
-            float v = g.alpha * acc[i][j];
+            float v = alpha * acc[i][j];
             if (g.bias) v += __ldg(g.bias + n);
             if (g.pre) g.pre[m * g.ldpre + n] = v;
             v = apply_act<ACT>(v);
@@ -240,6 +242,7 @@ __global__ void __launch_bounds__(GNT) gemm_tc3_kernel(const GemmArgs g) {
 
     float *C = g.C;
     const float aux_alpha = g.aux_alpha * ((g.aux1 && g.aux_scale_dev) ? __ldg(g.aux_scale_dev) : 1.f);
+    const float alpha = g.alpha * (g.alpha_dev ? __ldg(g.alpha_dev) : 1.f);
     if (g.k_chunk > 0) C += (int64_t)blockIdx.z * g.M * g.ldc;
 #pragma unroll
     for (int i = 0; i < 2; ++i)
@@ -250,7 +253,7 @@ __global__ void __launch_bounds__(GNT) gemm_tc3_kernel(const GemmArgs g) {
                 const int64_t m = m0 + wm * 32 + i * 16 + gq + (q >> 1) * 8;
                 const int n = n0 + wn * 16 + j * 8 + 2 * tq + (q & 1);
                 if (m >= g.M || n >= g.N) continue;
-                float v = g.alpha * acc[i][j][q];
+                float v = alpha * acc[i][j][q];
                 if (g.bias) v += __ldg(g.bias + n);
                 if (g.pre) g.pre[m * g.ldpre + n] = v;
                 v = apply_act<ACT>(v);
@@ -265,7 +268,7 @@ inline GemmArgs gemm_args_zero() {
     g.A = nullptr; g.sam = g.sak = 0; g.B = nullptr; g.sbk = g.sbn = 0; g.C = nullptr; g.ldc = 0;
     g.M = 0; g.N = 0; g.K = 0; g.alpha = 1.f; g.bias = nullptr; g.pre = nullptr; g.ldpre = 0;
     g.dpre = nullptr; g.lddpre = 0; g.aux1 = g.aux2 = nullptr; g.ldaux = 0; g.aux_alpha = 0.f;
-    g.b_ones_col = -1; g.k_chunk = 0; g.aux_scale_dev = nullptr;
+    g.b_ones_col = -1; g.k_chunk = 0; g.aux_scale_dev = nullptr; g.alpha_dev = nullptr;
     return g;
 }
 
@@ -314,11 +317,12 @@ constexpr int DG_BM = 128, DG_BK = 32, DG_ST = 3, DG_ALD = DG_BK + 4;
 template <int KK, int DACT>
 __global__ void __launch_bounds__(GNT, 1) dgrad_tc3_kernel(const float *__restrict__ dY, const float *__restrict__ W,
                                                            const float *__restrict__ dpre, float *__restrict__ dX,
-                                                           int64_t M, int Nn) {
+                                                           int64_t M, int Nn, const float *__restrict__ scale_dev) {
     constexpr int WN = KK / 32, WM = 8 / WN, MF = DG_BM / WM / 16, BLD = KK + 8;
     extern __shared__ __align__(16) float dg_smem[];
     float *Bs = dg_smem;                                             // [Nn_pad][BLD]
     const int n_slabs = (Nn + DG_BK - 1) / DG_BK;
+    const float out_scale = scale_dev ? __ldg(scale_dev) : 1.f;
     float(*As)[DG_BM][DG_ALD] = reinterpret_cast<float(*)[DG_BM][DG_ALD]>(dg_smem + (size_t)n_slabs * DG_BK * BLD);
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int wm = warp / WN, wn = warp % WN, gq = lane >> 2, tq = lane & 3;
@@ -398,7 +402,7 @@ __global__ void __launch_bounds__(GNT, 1) dgrad_tc3_kernel(const float *__restri
 #pragma unroll
                     for (int j = 0; j < 4; ++j) {
                         const int n = wn * 32 + j * 8 + 2 * tq;
-                        float2 v = make_float2(acc[i][j][2 * h], acc[i][j][2 * h + 1]);
+                        float2 v = make_float2(out_scale * acc[i][j][2 * h], out_scale * acc[i][j][2 * h + 1]);
                         if (DACT == ACT_GELU) {
                             const float2 a = __ldg(reinterpret_cast<const float2 *>(dpre + m * KK + n));
                             v.x *= gelu_grad_f(a.x);
@@ -414,7 +418,7 @@ __global__ void __launch_bounds__(GNT, 1) dgrad_tc3_kernel(const float *__restri
 
 template <int KK, int DACT>
 inline int dgrad_tc3_launch(const float *dY, const float *W, const float *dpre, float *dX, int64_t M, int Nn,
-                            cudaStream_t st) {
+                            const float *scale_dev, cudaStream_t st) {
     const int n_slabs = (Nn + DG_BK - 1) / DG_BK;
     const size_t smem = ((size_t)n_slabs * DG_BK * (KK + 8) + (size_t)DG_ST * DG_BM * DG_ALD) * sizeof(float);
     if (smem > 220 * 1024) return LIPVQ_ESHAPE;
@@ -424,7 +428,7 @@ inline int dgrad_tc3_launch(const float *dY, const float *W, const float *dpre, 
     const int per_sm = smem <= 110 * 1024 ? 2 : 1;
     const int grid = (int)(tiles < per_sm * kNumSMs ? tiles : per_sm * kNumSMs);
     ProfScope prof("dgrad_tc3_kernel", st);
-    dgrad_tc3_kernel<KK, DACT><<<grid, GNT, smem, st>>>(dY, W, dpre, dX, M, Nn);
+    dgrad_tc3_kernel<KK, DACT><<<grid, GNT, smem, st>>>(dY, W, dpre, dX, M, Nn, scale_dev);
     LIPVQ_LAUNCH_OK();
     return LIPVQ_OK;
 }
@@ -433,14 +437,15 @@ inline int dgrad_tc3_launch(const float *dY, const float *W, const float *dpre, 
 template <int DACT>
 inline int linear_bwd_input(const float *dY, const float *W, const float *dpre, float *dX,
                             int64_t M, int N, int K, const float *aux1, const float *aux2,
-                            float aux_alpha, const float *aux_scale_dev, cudaStream_t st) {
+                            float aux_alpha, const float *aux_scale_dev, cudaStream_t st,
+                            const float *out_scale_dev = nullptr) {
     static const bool simt = [] { const char *e = getenv("LIPVQ_GEMM"); return e && !strcmp(e, "simt"); }();
     if (!simt && !aux1 && (K == 64 || K == 128) && (N & 3) == 0 && aligned16(dY) && aligned16(W) && aligned16(dX) &&
         (DACT == ACT_NONE || aligned16(dpre)) && (double)M * N * K >= 1.0e7) {
         const size_t smem = ((size_t)((N + DG_BK - 1) / DG_BK) * DG_BK * (K + 8) + (size_t)DG_ST * DG_BM * DG_ALD) * 4;
         if (smem <= 220 * 1024)
-            return K == 64 ? dgrad_tc3_launch<64, DACT>(dY, W, dpre, dX, M, N, st)
-                           : dgrad_tc3_launch<128, DACT>(dY, W, dpre, dX, M, N, st);
+            return K == 64 ? dgrad_tc3_launch<64, DACT>(dY, W, dpre, dX, M, N, out_scale_dev, st)
+                           : dgrad_tc3_launch<128, DACT>(dY, W, dpre, dX, M, N, out_scale_dev, st);
     }
     GemmArgs g = gemm_args_zero();
     g.A = dY; g.sam = N; g.sak = 1;
@@ -448,21 +453,24 @@ inline int linear_bwd_input(const float *dY, const float *W, const float *dpre, 
     g.C = dX; g.ldc = K; g.M = M; g.N = K; g.K = N;
     g.dpre = dpre; g.lddpre = K;
     g.aux1 = aux1; g.aux2 = aux2; g.ldaux = K; g.aux_alpha = aux_alpha; g.aux_scale_dev = aux_scale_dev;
+    g.alpha_dev = out_scale_dev;
     return gemm_launch<ACT_NONE, DACT, true, false>(g, 1, st);
 }
 
 // Sum the split-K partials in split order (deterministic) and separate weight / bias gradients.
 // part: [splits][Nout][Kin+1]; dW[Nout,Kin]; db[Nout] (nullable)
 __global__ void splitk_reduce_kernel(const float *__restrict__ part, int splits, int Nout, int Kin,
-                                     float *__restrict__ dW, float *__restrict__ db) {
+                                     float *__restrict__ dW, float *__restrict__ db,
+                                     const float *__restrict__ scale_dev = nullptr) {
+    const float out_scale = scale_dev ? __ldg(scale_dev) : 1.f;
     const int ld = Kin + 1;
     const int total = Nout * ld;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
         float s = 0.f;
         for (int z = 0; z < splits; ++z) s += part[(size_t)z * total + i];
         const int m = i / ld, n = i - m * ld;
-        if (n < Kin) dW[(size_t)m * Kin + n] = s;
-        else if (db) db[m] = s;
+        if (n < Kin) dW[(size_t)m * Kin + n] = out_scale * s;
+        else if (db) db[m] = out_scale * s;
     }
 }
 
@@ -589,7 +597,7 @@ __global__ void __launch_bounds__(GNT) wgrad_tc3_kernel(const float *__restrict_
 
 // dW[Nout,Kin] = dY[rows,Nout]^T X[rows,Kin];  db[Nout] = column sums of dY.  part = scratch.
 inline int linear_bwd_weight(const float *dY, const float *X, float *dW, float *db, int64_t rows,
-                             int Nout, int Kin, float *part, cudaStream_t st) {
+                             int Nout, int Kin, float *part, cudaStream_t st, const float *out_scale_dev = nullptr) {
     const int splits = splits_for_rows(rows, Nout, Kin);
     static const bool simt = [] { const char *e = getenv("LIPVQ_GEMM"); return e && !strcmp(e, "simt"); }();
     if (!simt && (Nout & 3) == 0 && (Kin & 3) == 0 && aligned16(dY) && aligned16(X) &&
@@ -605,7 +613,7 @@ inline int linear_bwd_weight(const float *dY, const float *X, float *dW, float *
             LIPVQ_LAUNCH_OK();
         }
         const int total = Nout * (Kin + 1);
-        splitk_reduce_kernel<<<(total + 255) / 256, 256, 0, st>>>(part, splits, Nout, Kin, dW, db);
+        splitk_reduce_kernel<<<(total + 255) / 256, 256, 0, st>>>(part, splits, Nout, Kin, dW, db, out_scale_dev);
         LIPVQ_LAUNCH_OK();
         return LIPVQ_OK;
     }
@@ -618,7 +626,7 @@ inline int linear_bwd_weight(const float *dY, const float *X, float *dW, float *
     g.k_chunk = (g.k_chunk + GBK - 1) / GBK * GBK;
     LIPVQ_TRY((gemm_launch<ACT_NONE, ACT_NONE, false, false>(g, splits, st)));
     const int total = Nout * (Kin + 1);
-    splitk_reduce_kernel<<<(total + 255) / 256, 256, 0, st>>>(part, splits, Nout, Kin, dW, db);
+    splitk_reduce_kernel<<<(total + 255) / 256, 256, 0, st>>>(part, splits, Nout, Kin, dW, db, out_scale_dev);
     LIPVQ_LAUNCH_OK();
     return LIPVQ_OK;
 }

@@ -367,7 +367,16 @@ int lipvq_quantize_decode_fwd(const lipvq_dims_t *d, const lipvq_params_t *p, co
     const int64_t tiles = (n + QE_ROWS - 1) / QE_ROWS;
     const int grid = (int)(tiles < kQeBlocks ? tiles : kQeBlocks);
     ProfScope prof("quantize_emit_kernel", st);
-    if ((d->D & 3) == 0)
+    const float a_q = (float)(0.5 / ((double)(n_total > 0 ? n_total : 1) * d->D));
+    const bool vec = (d->D & 3) == 0 && (a->g_pre == nullptr || aligned16(a->g_pre));
+    if (a->g_pre) {
+        if (vec)
+            quantize_emit_kernel<true, true><<<grid, QE_THR, 0, st>>>(a->z_e, p->codebook, R, a->idx, x, n, d->D, d->F, d->K,
+                                                                      a->z_q, a->x_recon, part, a->g_pre, a_q);
+        else
+            quantize_emit_kernel<false, true><<<grid, QE_THR, 0, st>>>(a->z_e, p->codebook, R, a->idx, x, n, d->D, d->F,
+                                                                       d->K, a->z_q, a->x_recon, part, a->g_pre, a_q);
+    } else if (vec)
         quantize_emit_kernel<true><<<grid, QE_THR, 0, st>>>(a->z_e, p->codebook, R, a->idx, x, n, d->D, d->F, d->K,
                                                             a->z_q, a->x_recon, part);
     else
@@ -456,23 +465,28 @@ int lipvq_encoder_bwd(const lipvq_dims_t *d, const lipvq_params_t *p, const floa
     if (ws_bytes < workspace_bytes_impl(d, n) || !aligned16(ws)) return LIPVQ_EWORKSPACE;
     cudaStream_t st = (cudaStream_t)stream;
     Bump b(ws, ws_bytes);
-    float *g_pre = b.take<float>((size_t)n * d->D);
+    // g_pre comes from the forward's streaming pass when the caller kept it (acts->g_pre, without dL/dloss: the
+    // factor is applied in the two GEMM epilogues that consume it); otherwise it is computed here
+    const bool saved = a->g_pre != nullptr;
+    float *g_pre = saved ? a->g_pre : b.take<float>((size_t)n * d->D);
     float *g_a2 = b.take<float>((size_t)n * d->H);
     float *g_a1 = b.take<float>((size_t)n * d->H1);
     float *gWn = b.take<float>((size_t)d->D * d->H);
     float *part = b.take<float>(max_splitk_floats(d, n));
     if (!b.ok()) return LIPVQ_EWORKSPACE;
     const float a_q = (float)(0.5 / ((double)n_total * d->D));
-    {
+    const float *late_scale = saved ? grad_scale : nullptr;
+    if (!saved) {
         ProfScope prof("commit_sigmoid_bwd_kernel", st);
         commit_sigmoid_bwd_kernel<<<kRedBlocks, 256, 0, st>>>(a->z_e, a->z_q, a_q, grad_scale, n * d->D, g_pre);
         LIPVQ_LAUNCH_OK();
     }
-    LIPVQ_TRY(linear_bwd_weight(g_pre, a->h2, gWn, g->lat_b, n, d->D, d->H, part, st));
+    LIPVQ_TRY(linear_bwd_weight(g_pre, a->h2, gWn, g->lat_b, n, d->D, d->H, part, st, late_scale));
     lipschitz_bwd_kernel<<<(d->D + 7) / 8, 256, 0, st>>>(gWn, p->lat_W, p->lat_ci, a->scale, d->D, d->H,
                                                         g->lat_W, g->lat_ci);
     LIPVQ_LAUNCH_OK();
-    LIPVQ_TRY(linear_bwd_input<ACT_GELU>(g_pre, a->Wn, a->a2, g_a2, n, d->D, d->H, nullptr, nullptr, 0.f, nullptr, st));
+    LIPVQ_TRY(linear_bwd_input<ACT_GELU>(g_pre, a->Wn, a->a2, g_a2, n, d->D, d->H, nullptr, nullptr, 0.f, nullptr, st,
+                                         late_scale));
     LIPVQ_TRY(linear_bwd_weight(g_a2, a->h1, g->enc2_w, g->enc2_b, n, d->H, d->H1, part, st));
     LIPVQ_TRY(linear_bwd_input<ACT_GELU>(g_a2, p->enc2_w, a->a1, g_a1, n, d->H, d->H1, nullptr, nullptr, 0.f, nullptr, st));
     LIPVQ_TRY(linear_bwd_weight(g_a1, x, g->enc0_w, g->enc0_b, n, d->H1, d->F, part, st));
@@ -501,6 +515,7 @@ int lipvq_forward_fused(const lipvq_dims_t *d, const lipvq_params_t *p, const fl
     a.z_e = b.take<float>((size_t)n * d->D);
     a.idx = idx ? idx : b.take<int64_t>(n);
     a.z_q = z_latent;
+    a.g_pre = nullptr;
     a.c1 = a.d1 = a.c2 = a.d2 = a.xr_code = nullptr;   // code-level decoder tensors come from the scratch below
     a.x_recon = x_recon;                               // optional output
     double *sse = b.take<double>(2);

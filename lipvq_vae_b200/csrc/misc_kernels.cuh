@@ -94,11 +94,15 @@ __global__ void __launch_bounds__(256) sse_kernel(const float *__restrict__ a, c
 // codebook and R stay cached.  partial: [2][gridDim.x] floats = {sse_q, sse_r} per CTA (summed in order later).
 constexpr int QE_ROWS = 64, QE_THR = 256;
 constexpr int kQeBlocks = 8 * kNumSMs;   // 8 resident CTAs of 256 threads per SM
-template <bool VEC4>
+// GPRE (training forward): also writes gpre = a_q (z_e - z_q) z_e (1 - z_e), the commitment gradient through the
+// sigmoid up to the upstream dL/dloss factor (v5:80; applied by the backward GEMMs' epilogues) -- the row is in
+// registers here, so the backward needs no separate pass over z_e and z_q.
+template <bool VEC4, bool GPRE = false>
 __global__ void __launch_bounds__(QE_THR) quantize_emit_kernel(
     const float *__restrict__ z_e, const float *__restrict__ E, const float *__restrict__ R,
     const int64_t *__restrict__ idx, const float *__restrict__ x, int64_t n_rows, int D, int F, int K,
-    float *__restrict__ z_q, float *__restrict__ x_recon, float *__restrict__ partial) {
+    float *__restrict__ z_q, float *__restrict__ x_recon, float *__restrict__ partial,
+    float *__restrict__ gpre = nullptr, float a_q = 0.f) {
     __shared__ int sidx[QE_ROWS];
     __shared__ float red[8];
     const int tid = threadIdx.x;
@@ -139,6 +143,12 @@ __global__ void __launch_bounds__(QE_THR) quantize_emit_kernel(
                         const float dx = e[u].x - z[u].x, dy = e[u].y - z[u].y, dz = e[u].z - z[u].z,
                                     dw = e[u].w - z[u].w;
                         sq += dx * dx + dy * dy + dz * dz + dw * dw;
+                        if (GPRE) {
+                            const float4 zz = z[u];
+                            __stcs(reinterpret_cast<float4 *>(gpre + r0 * D) + i,
+                                   make_float4(-a_q * dx * zz.x * (1.0f - zz.x), -a_q * dy * zz.y * (1.0f - zz.y),
+                                               -a_q * dz * zz.z * (1.0f - zz.z), -a_q * dw * zz.w * (1.0f - zz.w)));
+                        }
                     }
                 }
             }
@@ -146,9 +156,11 @@ __global__ void __launch_bounds__(QE_THR) quantize_emit_kernel(
             for (unsigned i = tid; i < total; i += QE_THR) {
                 const unsigned r = __umulhi(i, magic), c = i - r * dq;
                 const float e = __ldg(E + (size_t)sidx[r] * D + c);
-                const float dd = e - __ldcs(z_e + r0 * D + i);
+                const float zz = __ldcs(z_e + r0 * D + i);
+                const float dd = e - zz;
                 __stcs(z_q + r0 * D + i, e);
                 sq += dd * dd;
+                if (GPRE) __stcs(gpre + r0 * D + i, -a_q * dd * zz * (1.0f - zz));
             }
         }
         if (R) {

@@ -114,14 +114,15 @@ class _TokenizerFn(torch.autograd.Function):
         c2 = torch.empty(K, H, **f32); d2 = torch.empty(K, H, **f32)
         xr_code = torch.empty(K, F_, **f32)
         sse = torch.empty(2, dtype=torch.float64, device=dev)
+        g_pre = torch.empty(n, D, **f32)     # commitment gradient through the sigmoid, written by the emit pass
         A = _acts_struct(a1=a1, h1=h1, a2=a2, h2=h2, scale=scale, Wn=Wn, z_e=z_e, idx=idx, z_q=z_q,
-                         c1=c1, d1=d1, c2=c2, d2=d2, xr_code=xr_code, x_recon=x_recon)
+                         c1=c1, d1=d1, c2=c2, d2=d2, xr_code=xr_code, x_recon=x_recon, g_pre=g_pre)
         wsz = ws.numel()
         N.check(lib.lipvq_encode_search_fwd(C.byref(dims), C.byref(P), _p(x), n, C.byref(A), search_mode,
                                             _p(vq_stats), _p(ws), wsz, st), "lipvq_encode_search_fwd")
         N.check(lib.lipvq_quantize_decode_fwd(C.byref(dims), C.byref(P), _p(x), n, n_total, C.byref(A), _p(sse),
                                               _p(stats), _p(ws), wsz, st), "lipvq_quantize_decode_fwd")
-        ctx.save_for_backward(x, *params, a1, h1, a2, h2, scale, Wn, z_e, idx, z_q, c1, d1, c2, d2, xr_code)
+        ctx.save_for_backward(x, *params, a1, h1, a2, h2, scale, Wn, z_e, idx, z_q, c1, d1, c2, d2, xr_code, g_pre)
         ctx.dims = dims
         ctx.n_total = n_total
         ctx.mark_non_differentiable(z_q, idx, vq_stats, x_recon, z_e)
@@ -135,7 +136,7 @@ class _TokenizerFn(torch.autograd.Function):
         lib = N.lib()
         saved = ctx.saved_tensors
         x, params = saved[0], saved[1:15]
-        a1, h1, a2, h2, scale, Wn, z_e, idx, z_q, c1, d1, c2, d2, xr_code = saved[15:]
+        a1, h1, a2, h2, scale, Wn, z_e, idx, z_q, c1, d1, c2, d2, xr_code, g_pre = saved[15:]
         dims = ctx.dims
         dev = x.device
         n = x.shape[0]
@@ -149,7 +150,7 @@ class _TokenizerFn(torch.autograd.Function):
         P = _param_struct(N.Params, params)
         G = _param_struct(N.Grads, grads)
         A = _acts_struct(a1=a1, h1=h1, a2=a2, h2=h2, scale=scale, Wn=Wn, z_e=z_e, idx=idx, z_q=z_q,
-                         c1=c1, d1=d1, c2=c2, d2=d2, xr_code=xr_code)
+                         c1=c1, d1=d1, c2=c2, d2=d2, xr_code=xr_code, g_pre=g_pre)
         N.check(lib.lipvq_decoder_bwd(C.byref(dims), C.byref(P), _p(x), n, ctx.n_total, _p(gs), C.byref(A),
                                       C.byref(G), _p(ws), wsz, st), "lipvq_decoder_bwd")
         N.check(lib.lipvq_encoder_bwd(C.byref(dims), C.byref(P), _p(x), n, ctx.n_total, _p(gs), C.byref(A),
