@@ -3,6 +3,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <pthread.h>
 
 #include "common.cuh"
 #include "gemm_simt.cuh"
@@ -54,6 +55,34 @@ static bool dims_ok(const lipvq_dims_t *d) {
 static bool use_mlp_tc(const lipvq_dims_t *d) {
     static const bool simt = [] { const char *e = getenv("LIPVQ_MLP"); return e && !strcmp(e, "simt"); }();
     return !simt && mlp::supported(d);
+}
+
+// One low-priority helper stream per device for parameter-only work that is off the critical path (the per-code
+// decoder table of the fused forward): forked from / joined to the caller's stream with events, so the caller's
+// stream order is preserved and the work fills the SMs the persistent kernels leave idle at their tails.
+// LIPVQ_SIDE_STREAM=0 keeps everything on the caller's stream.
+static cudaStream_t side_stream() {
+    static const bool off = [] { const char *e = getenv("LIPVQ_SIDE_STREAM"); return e && !strcmp(e, "0"); }();
+    if (off) return nullptr;
+    static cudaStream_t streams[64] = {};
+    static bool tried[64] = {};
+    int dev = -1;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
+    if (!__atomic_load_n(&tried[dev], __ATOMIC_ACQUIRE)) {
+        static pthread_mutex_t mu = PTHREAD_MUTEX_INITIALIZER;
+        pthread_mutex_lock(&mu);
+        if (!tried[dev]) {
+            int lo = 0, hi = 0;
+            cudaStream_t s = nullptr;
+            if (cudaDeviceGetStreamPriorityRange(&lo, &hi) != cudaSuccess ||
+                cudaStreamCreateWithPriority(&s, cudaStreamNonBlocking, lo) != cudaSuccess)
+                s = nullptr;
+            streams[dev] = s;
+            __atomic_store_n(&tried[dev], true, __ATOMIC_RELEASE);
+        }
+        pthread_mutex_unlock(&mu);
+    }
+    return streams[dev];
 }
 
 static size_t max_splitk_floats(const lipvq_dims_t *d, int64_t n) {
@@ -340,9 +369,20 @@ static int decoder_code_table(const lipvq_dims_t *d, const lipvq_params_t *p, fl
     return LIPVQ_OK;
 }
 
+static int quantize_decode_impl(const lipvq_dims_t *d, const lipvq_params_t *p, const float *x, int64_t n,
+                                int64_t n_total, const lipvq_acts_t *a, double *sse, float *loss_out, void *ws,
+                                size_t ws_bytes, void *stream, bool table_ready);
+
 int lipvq_quantize_decode_fwd(const lipvq_dims_t *d, const lipvq_params_t *p, const float *x, int64_t n,
                               int64_t n_total, const lipvq_acts_t *a, double *sse, float *loss_out, void *ws,
                               size_t ws_bytes, void *stream) {
+    return quantize_decode_impl(d, p, x, n, n_total, a, sse, loss_out, ws, ws_bytes, stream, false);
+}
+
+// table_ready: acts->xr_code already holds decoder(E) (computed on the helper stream by lipvq_forward_fused)
+static int quantize_decode_impl(const lipvq_dims_t *d, const lipvq_params_t *p, const float *x, int64_t n,
+                                int64_t n_total, const lipvq_acts_t *a, double *sse, float *loss_out, void *ws,
+                                size_t ws_bytes, void *stream, bool table_ready) {
     if (!dims_ok(d) || n < 0 || n_total < n || (loss_out && n_total < 1)) return LIPVQ_ESHAPE;
     if (!p || !a || !sse) return LIPVQ_EALIGN;
     cudaStream_t st = (cudaStream_t)stream;
@@ -363,7 +403,7 @@ int lipvq_quantize_decode_fwd(const lipvq_dims_t *d, const lipvq_params_t *p, co
     if (!b.ok()) return LIPVQ_EWORKSPACE;
     // the decoder acts on z_q = E[idx] (v5:47, 75): K distinct inputs, so it runs once per CODE; the per-row
     // work is the streaming pass below (z_q / z_latent write, x_recon = R[idx], both loss sums)
-    LIPVQ_TRY(decoder_code_table(d, p, c1, d1, c2, d2, R, st));
+    if (!table_ready) LIPVQ_TRY(decoder_code_table(d, p, c1, d1, c2, d2, R, st));
     const int64_t tiles = (n + QE_ROWS - 1) / QE_ROWS;
     const int grid = (int)(tiles < kQeBlocks ? tiles : kQeBlocks);
     ProfScope prof("quantize_emit_kernel", st);
@@ -525,10 +565,29 @@ int lipvq_forward_fused(const lipvq_dims_t *d, const lipvq_params_t *p, const fl
     // the rest of the workspace serves the encoder image + the search (checked against their own needs there)
     void *es_ws = (void *)align_up((size_t)(b.base + b.off), 256);
     const size_t es_bytes = ws_bytes - (size_t)((char *)es_ws - (char *)ws);
-    LIPVQ_TRY(lipvq_encode_search_fwd(d, p, x, n, &a, search_mode, stats, es_ws, es_bytes, stream));
-    LIPVQ_TRY(lipvq_quantize_decode_fwd(d, p, x, n, n_total, &a, sse, loss_out, part, part_bytes, stream));
-    (void)st;
-    return LIPVQ_OK;
+    // the per-code decoder table depends on the parameters only: it runs on the helper stream (forked here, joined
+    // before the emit pass) beside the encoder / search kernels instead of between them
+    cudaStream_t side = side_stream();
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+    bool forked = false;
+    if (side && cudaEventCreateWithFlags(&ev_fork, cudaEventDisableTiming) == cudaSuccess &&
+        cudaEventCreateWithFlags(&ev_join, cudaEventDisableTiming) == cudaSuccess) {
+        float *R = (float *)align_up((size_t)part + align_up(2 * kQeBlocks * sizeof(float), 256), 256);   // qd scratch tail
+        int rc = LIPVQ_OK;
+        if (cudaEventRecord(ev_fork, st) == cudaSuccess && cudaStreamWaitEvent(side, ev_fork, 0) == cudaSuccess) {
+            rc = decoder_code_table(d, p, nullptr, nullptr, nullptr, nullptr, R, side);
+            if (rc == LIPVQ_OK && cudaEventRecord(ev_join, side) == cudaSuccess) {
+                forked = true;
+                a.xr_code = R;
+            }
+        }
+    }
+    int rc = lipvq_encode_search_fwd(d, p, x, n, &a, search_mode, stats, es_ws, es_bytes, stream);
+    if (forked && cudaStreamWaitEvent(st, ev_join, 0) != cudaSuccess && rc == LIPVQ_OK) rc = LIPVQ_ECUDA;
+    if (ev_fork) cudaEventDestroy(ev_fork);
+    if (ev_join) cudaEventDestroy(ev_join);
+    LIPVQ_TRY(rc);
+    return quantize_decode_impl(d, p, x, n, n_total, &a, sse, loss_out, part, part_bytes, stream, forked);
 }
 
 int lipvq_adamw_step(float *param, const float *grad, float *exp_avg, float *exp_avg_sq, int64_t n,
