@@ -29,7 +29,7 @@ MULT = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
 lines, traffic, seen = [header], {}, set()
 for r in rows[2:]:
     name = r[ix["Kernel Name"]]
-    short = name.split("(")[0].split("::")[-1].split("<")[0].strip()
+    short = name.split("(")[0].split("<")[0].split("::")[-1].replace("void ", "").strip()
     if short in seen:
         continue
     seen.add(short)
