@@ -165,6 +165,9 @@ def run_ours(args, rank, world, local_rank):
         raise SystemExit("bench.py --impl ours needs a CUDA device (there is no CPU fallback)")
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
+    # one process per GPU: stage the pinned host batches on the GPU's own NUMA node (matters for `e2e` at N > 1)
+    from lipvq_vae_b200 import bind_host_thread_to_gpu_node
+    numa_cpus = bind_host_thread_to_gpu_node(local_rank) if world > 1 else None
     lib = N.lib()
     N.check(lib.lipvq_check_device(), "lipvq_check_device")
     peaks, peak_src = _peaks()
@@ -431,6 +434,7 @@ def run_ours(args, rank, world, local_rank):
                 "api": "HostTokenizer.submit(pinned host batch) / collect(): per step one H2D of the batch, "
                        "LLFQVAE_V4.forward, one D2H of token indices + loss terms; uploads/downloads of neighbouring "
                        "steps overlap the kernels (2 slots)",
+                "host_numa_binding": ("rank bound to %d CPUs local to its GPU" % len(numa_cpus)) if numa_cpus else "none",
                 "serial_ms_per_step": ms_e2e_serial,
                 "serial_value": world * CHUNKS / (ms_e2e_serial / 1e3)},
         "gpu_launches": int(launches), "clocks": clk, "roofline": roofline, "rooflines": rooflines,

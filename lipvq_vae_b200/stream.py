@@ -19,6 +19,34 @@ import torch
 from .tokenizer import LLFQVAE_V4, LipVQNativeError
 
 
+def bind_host_thread_to_gpu_node(device_index: int):
+    """Pin the calling process to the CPUs local to ``cuda:device_index`` (sysfs ``local_cpulist`` of the GPU's PCI
+    function) so that pinned host buffers allocated afterwards sit on the GPU's own NUMA node: with one process per
+    GPU, batches staged on the wrong socket cross the inter-socket link on every upload.  Returns the CPU list, or
+    ``None`` when the topology is not exposed (single node, containers without sysfs) -- nothing is changed then."""
+    import os
+    try:
+        pr = torch.cuda.get_device_properties(device_index)
+        bdf = "%04x:%02x:%02x.0" % (pr.pci_domain_id, pr.pci_bus_id, pr.pci_device_id)
+        with open("/sys/bus/pci/devices/%s/local_cpulist" % bdf) as f:
+            spec = f.read().strip()
+        cpus = set()
+        for part in spec.split(","):
+            if "-" in part:
+                a, b = part.split("-")
+                cpus.update(range(int(a), int(b) + 1))
+            elif part:
+                cpus.add(int(part))
+        allowed = os.sched_getaffinity(0)
+        cpus &= allowed
+        if not cpus or cpus == allowed:
+            return None
+        os.sched_setaffinity(0, cpus)
+        return sorted(cpus)
+    except Exception:
+        return None
+
+
 class HostTokenizer:
     def __init__(self, model: LLFQVAE_V4, max_rows: int, depth: int = 2, fetch_latent: bool = False):
         dev = next(model.parameters()).device
