@@ -365,3 +365,40 @@ def test_ema_codebook_mode_vs_oracle():
         m.ema_update(counts, sums, gamma=0.9)
         assert orc.rel_err(m.quantizer.codebook.detach().cpu().numpy(), E) < RTOL
     assert "ema_cluster_size" not in m.state_dict() and len(list(m.buffers())) == 0   # reference surface intact
+
+
+@pytest.mark.parametrize("n,D,K", [(1, 208, 1024), (129, 50, 100), (1000, 36, 64), (257, 100, 1000), (4099, 207, 300)])
+def test_fused_paths_ragged_and_unaligned_shapes(n, D, K):
+    """Edge shapes of the fused tensor-core path against the oracle on the same seeded inputs: a single row, row counts
+    that straddle the 128-row tile, latent widths that are not multiples of 16 / 4 (per-thread store path instead of
+    bulk tensor stores, padded operand blocks), codebooks that are not multiples of the 256-code tile.  Forward with
+    and without autograd, and all 14 gradients."""
+    rng = np.random.default_rng(7000 + n + D + K)
+    p = orc.init_params(12, D, K, 128, seed=n + D)
+    p["to_latent.W"] = (0.08 * p["to_latent.W"]).astype(np.float32)
+    p["to_latent.ci"][::3] = 5.0
+    z = orc.encode(p, (2.0 * rng.random((K, 12)) - 1.0).astype(np.float32))
+    p["quantizer.codebook"] = (z + 1e-3 * rng.standard_normal(z.shape)).astype(np.float32)
+    x = (2.0 * rng.random((n, 12)) - 1.0).astype(np.float32)
+    fw = orc.forward(p, x)
+    _, d1, d2 = orc.exact_top2(fw["z_e"], p["quantizer.codebook"])
+    must = orc.index_parity_mask(d1, d2)
+    m = _model(p, 1)
+    xt = torch.from_numpy(x).cuda()
+    with torch.no_grad():
+        z_lat0, loss0 = m(xt)
+    idx0 = m.last_indices.cpu().numpy()
+    z_lat, loss = m(xt)
+    loss.backward()
+    torch.cuda.synchronize()
+    idx = m.last_indices.cpu().numpy()
+    assert np.array_equal(idx, idx0) and torch.equal(z_lat, z_lat0)
+    assert np.array_equal(idx[must], fw["idx"][must])
+    if np.array_equal(idx, fw["idx"]):
+        assert abs(loss.item() - fw["loss"]) < RTOL * abs(fw["loss"])
+        assert abs(loss0.item() - fw["loss"]) < RTOL * abs(fw["loss"])
+        assert orc.rel_err(z_lat.cpu().numpy(), fw["z_latent"]) < 1e-6
+        assert orc.rel_err(m.last_reconstruction.cpu().numpy(), fw["x_recon"]) < RTOL
+        gr = orc.backward(p, x, fw)
+        for k, t in m.named_parameters():
+            assert orc.rel_err(t.grad.cpu().numpy(), gr[k]) < GTOL, k
