@@ -227,23 +227,28 @@ def run_ours(args, rank, world, local_rank):
     # batch and brings its tokens + loss terms back, but batch i+1's upload and batch i-1's download run on the
     # copy engines while batch i's kernels run.  All K uploads / K forwards / K downloads are inside the region.
     from lipvq_vae_b200 import HostTokenizer
-    ht = HostTokenizer(m, rows, depth=2)
+    DEPTH = int(os.environ.get("LIPVQ_E2E_DEPTH", "2"))
+    ht = HostTokenizer(m, rows, depth=DEPTH)
 
     def e2e_loop(k):
         sink = 0.0
         for i in range(k):
             ht.submit(host[i % NBUF])
-            if i >= 1:
-                sink += float(ht.collect()[1][0])          # host reads the previous step's loss
+            if i >= DEPTH - 1:
+                sink += float(ht.collect()[1][0])          # host reads the loss of the oldest batch in flight
         ht.drain_to()
         return sink
-    e2e_loop(min(args.warmup, 3)); ht.collect(); torch.cuda.synchronize()
+
+    def e2e_flush():
+        while ht.pending:
+            ht.collect()
+    e2e_loop(min(args.warmup, 3)); e2e_flush(); torch.cuda.synchronize()
     barrier()
     s_ev, e_ev = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     s_ev.record()
     e2e_loop(args.steps)
     e_ev.record()
-    ht.collect()
+    e2e_flush()
     torch.cuda.synchronize()
     ms_e2e = s_ev.elapsed_time(e_ev) / args.steps
     barrier()
@@ -441,7 +446,7 @@ def run_ours(args, rank, world, local_rank):
                 "h2d_bytes_per_step": rows * F_DIM * 4, "d2h_bytes_per_step": rows * 8 + 16,
                 "api": "HostTokenizer.submit(pinned host batch) / collect(): per step one H2D of the batch, "
                        "LLFQVAE_V4.forward, one D2H of token indices + loss terms; uploads/downloads of neighbouring "
-                       "steps overlap the kernels (2 slots)",
+                       "steps overlap the kernels (%d slots)" % DEPTH,
                 "host_numa_binding": ("rank bound to %d CPUs local to its GPU" % len(numa_cpus)) if numa_cpus else "none",
                 "serial_ms_per_step": ms_e2e_serial,
                 "serial_value": world * CHUNKS / (ms_e2e_serial / 1e3)},
