@@ -25,7 +25,7 @@
 extern "C" {
 #endif
 
-#define LIPVQ_ABI_VERSION 4
+#define LIPVQ_ABI_VERSION 5
 
 enum {
     LIPVQ_OK = 0,
@@ -118,7 +118,8 @@ int lipvq_encoder_fwd(const lipvq_dims_t *dims, const lipvq_params_t *p, const f
                       void *stream);
 
 /* One fused linear layer Y[M,N] = act(X[M,K] W[N,K]^T + b[N]) (nn.Linear + nn.GELU of v5:54-68 when a
- * sub-module is called on its own); act: 0 none, 1 exact-erf GELU, 2 sigmoid.  b nullable. */
+ * sub-module is called on its own); act: 0 none, 1 exact-erf GELU, 2 sigmoid, 5 ReLU (the classic VQVAE's layers,
+ * robomimic/models/vq_vae/backbone.py:17-32).  b nullable. */
 int lipvq_linear_fwd(const float *X, const float *W, const float *b, float *Y, int64_t M, int32_t N,
                      int32_t K, int32_t act, void *stream);
 
@@ -218,6 +219,41 @@ int lipvq_adamw_step(float *param, const float *grad, float *exp_avg, float *exp
 int lipvq_ema_update(float *E, float *n_ema, float *m_ema, const float *counts,
                      const float *sums, int32_t K, int32_t D, float gamma, float eps, void *ws,
                      size_t ws_bytes, void *stream);
+
+/* ---- secondary variant: the classic VQVAE of robomimic/models/vq_vae/backbone.py:6-76 (ReLU MLPs, nn.Embedding
+ * codebook, squared distances, loss = mse(x_recon, x) + mse(z_q, sg z_e) + cc * mse(sg z_q, z_e), straight-through
+ * estimator z_e + (z_q - z_e).detach()).  Its call site is commented out at robomimic/models/obs_nets.py:1220-1222;
+ * it reuses lipvq_vq_argmin / lipvq_gather_loss / the scatter-add kernel with a different gradient route. */
+
+/* Backward of Y = act(X W^T + b) given dY = dL/d(pre-activation) [M,N]:
+ *   dW[N,K] = dY^T X, db[N] = column sums of dY (nullable), dX[M,K] = (dY W) * [x_mask > 0] (dX nullable;
+ *   x_mask = the ReLU OUTPUT X itself when X came out of a ReLU, or null for no mask).  autograd of backbone.py:17-32. */
+size_t lipvq_linear_bwd_ws_bytes(int64_t M, int32_t N, int32_t K);
+int lipvq_linear_bwd(const float *dY, const float *X, const float *W, const float *x_mask, float *dX,
+                     float *dW, float *db, int64_t M, int32_t N, int32_t K, void *ws, size_t ws_bytes,
+                     void *stream);
+
+/* sums[idx[n],:] += alpha * gs * (table[idx[n],:] - src[n,:]) (gs = *grad_scale, nullable): the embedding-loss
+ * gradient 2 (z_q - z_e)/(N D) summed per code (backbone.py:70) without materialising the difference. */
+int lipvq_scatter_add_diff(const float *src, const int64_t *idx, const float *table, float alpha,
+                           const float *grad_scale, int64_t n_rows, int32_t D, int32_t K, float *sums,
+                           void *stream);
+
+/* out[0] = sum (a - b)^2 over n elements (device double), fixed-order reduction; ws >= 4 KB. */
+int lipvq_sse(const float *a, const float *b, int64_t n, double *out, void *ws, size_t ws_bytes, void *stream);
+
+/* out float[4] = {loss, recon, commitment_cost * mse_q, mse_q} (backbone.py:49-50, 69-71). */
+int lipvq_vqvae_loss(const double *sse_r, const double *sse_q, int64_t n_total, int32_t F, int32_t D,
+                     float commitment_cost, float *out, void *stream);
+
+/* out = gs * alpha * (x_recon - x) * [x_recon > 0]: mse gradient through the decoder's output ReLU (backbone.py:31). */
+int lipvq_vqvae_recon_grad(const float *x_recon, const float *x, int64_t n_elems, float alpha,
+                           const float *grad_scale, float *out, void *stream);
+
+/* g_zq <- (g_zq + gs * alpha * (z_e - z_q)) * [z_e > 0]: straight-through route of the decoder gradient to the
+ * encoder + commitment term + the encoder's output ReLU (backbone.py:23, 69, 74). */
+int lipvq_vqvae_ste_grad(float *g_zq, const float *z_e, const float *z_q, int64_t n_elems, float alpha,
+                         const float *grad_scale, void *stream);
 
 #ifdef __cplusplus
 }

@@ -7,9 +7,10 @@ behind the C ABI in include/lipvq_b200.h.  No CPU path, no torch fallback.
 from ._native import (LipVQNativeError, SEARCH_EXACT, SEARCH_TENSOR, build_native, lib as native_lib,
                       LIB_PATH)
 from .tokenizer import LLFQVAE_V4, LFQQuantizer, LipschitzMLP, install_into_robomimic
+from .vqvae_classic import VQVAE
 from .stream import HostTokenizer, bind_host_thread_to_gpu_node
 from .dist import DataParallelTokenizer, FlatAdamW, TokenizerTrainer, shard_rows
 
-__all__ = ["LLFQVAE_V4", "LFQQuantizer", "LipschitzMLP", "install_into_robomimic", "HostTokenizer", "bind_host_thread_to_gpu_node", "DataParallelTokenizer", "FlatAdamW", "TokenizerTrainer",
+__all__ = ["LLFQVAE_V4", "VQVAE", "LFQQuantizer", "LipschitzMLP", "install_into_robomimic", "HostTokenizer", "bind_host_thread_to_gpu_node", "DataParallelTokenizer", "FlatAdamW", "TokenizerTrainer",
            "shard_rows", "LipVQNativeError",
            "SEARCH_EXACT", "SEARCH_TENSOR", "build_native", "native_lib", "LIB_PATH"]

@@ -124,6 +124,13 @@ SIGNATURES = {
     "lipvq_forward_fused": (C.c_int, [_DP, _PP, _VP, _I64, _I64, _I32, _VP, _VP, _VP, _VP, _VP, _VP, _SZ, _VP]),
     "lipvq_adamw_step": (C.c_int, [_VP, _VP, _VP, _VP, _I64, _I64, _F32, _F32, _F32, _F32, _F32, _VP]),
     "lipvq_ema_update": (C.c_int, [_VP, _VP, _VP, _VP, _VP, _I32, _I32, _F32, _F32, _VP, _SZ, _VP]),
+    "lipvq_linear_bwd_ws_bytes": (_SZ, [_I64, _I32, _I32]),
+    "lipvq_linear_bwd": (C.c_int, [_VP, _VP, _VP, _VP, _VP, _VP, _VP, _I64, _I32, _I32, _VP, _SZ, _VP]),
+    "lipvq_scatter_add_diff": (C.c_int, [_VP, _VP, _VP, _F32, _VP, _I64, _I32, _I32, _VP, _VP]),
+    "lipvq_sse": (C.c_int, [_VP, _VP, _I64, _VP, _VP, _SZ, _VP]),
+    "lipvq_vqvae_loss": (C.c_int, [_VP, _VP, _I64, _I32, _I32, _F32, _VP, _VP]),
+    "lipvq_vqvae_recon_grad": (C.c_int, [_VP, _VP, _I64, _F32, _VP, _VP, _VP]),
+    "lipvq_vqvae_ste_grad": (C.c_int, [_VP, _VP, _VP, _I64, _F32, _VP, _VP]),
 }
 
 
@@ -142,7 +149,7 @@ def lib():
                     fn = getattr(h, name)
                     fn.restype = res
                     fn.argtypes = args
-                if h.lipvq_abi_version() != 4:
+                if h.lipvq_abi_version() != 5:
                     raise LipVQNativeError("ABI version mismatch")
                 _lib = h
     return _lib

@@ -50,7 +50,7 @@ struct ProfScope {
 constexpr int kNumSMs = 148;  // B200: 2 dies x 74 SMs
 
 // *_FAST: the per-row epilogues of the fused encoder (error at the fp32 rounding floor, see gelu_fast_f)
-enum Act : int { ACT_NONE = 0, ACT_GELU = 1, ACT_SIGMOID = 2, ACT_GELU_FAST = 3, ACT_SIGMOID_FAST = 4 };
+enum Act : int { ACT_NONE = 0, ACT_GELU = 1, ACT_SIGMOID = 2, ACT_GELU_FAST = 3, ACT_SIGMOID_FAST = 4, ACT_RELU = 5 };
 
 // exact-erf GELU, nn.GELU() default (v5:56,58,64,66)
 __device__ __forceinline__ float gelu_f(float a) {
@@ -105,6 +105,7 @@ __device__ __forceinline__ float apply_act(float v) {
     if (ACT == ACT_SIGMOID_FAST) return sigmoid_fast_f(v);
     if (ACT == ACT_GELU) return gelu_f(v);
     if (ACT == ACT_SIGMOID) return sigmoid_f(v);
+    if (ACT == ACT_RELU) return fmaxf(v, 0.f);
     return v;
 }
 

@@ -116,6 +116,7 @@ __global__ void __launch_bounds__(GNT) gemm_simt_kernel(const GemmArgs g) {
             if (g.pre) g.pre[m * g.ldpre + n] = v;
             v = apply_act<ACT>(v);
             if (DACT == ACT_GELU) v *= gelu_grad_f(__ldg(g.dpre + m * g.lddpre + n));
+            if (DACT == ACT_RELU) v = __ldg(g.dpre + m * g.lddpre + n) > 0.f ? v : 0.f;
             if (g.aux1) v += aux_alpha * (__ldg(g.aux1 + m * g.ldaux + n) - __ldg(g.aux2 + m * g.ldaux + n));
             C[m * g.ldc + n] = v;
         }
@@ -258,6 +259,8 @@ __global__ void __launch_bounds__(GNT) gemm_tc3_kernel(const GemmArgs g) {
                 if (g.pre) g.pre[m * g.ldpre + n] = v;
                 v = apply_act<ACT>(v);
                 if (DACT == ACT_GELU) v *= gelu_grad_f(__ldg(g.dpre + m * g.lddpre + n));
+                if (DACT == ACT_RELU) v = __ldg(g.dpre + m * g.lddpre + n) > 0.f ? v : 0.f;
+            if (DACT == ACT_RELU) v = __ldg(g.dpre + m * g.lddpre + n) > 0.f ? v : 0.f;
                 if (g.aux1) v += aux_alpha * (__ldg(g.aux1 + m * g.ldaux + n) - __ldg(g.aux2 + m * g.ldaux + n));
                 C[m * g.ldc + n] = v;
             }
@@ -407,6 +410,11 @@ __global__ void __launch_bounds__(GNT, 1) dgrad_tc3_kernel(const float *__restri
                             const float2 a = __ldg(reinterpret_cast<const float2 *>(dpre + m * KK + n));
                             v.x *= gelu_grad_f(a.x);
                             v.y *= gelu_grad_f(a.y);
+                        }
+                        if (DACT == ACT_RELU) {
+                            const float2 a = __ldg(reinterpret_cast<const float2 *>(dpre + m * KK + n));
+                            v.x = a.x > 0.f ? v.x : 0.f;
+                            v.y = a.y > 0.f ? v.y : 0.f;
                         }
                         *reinterpret_cast<float2 *>(dX + m * KK + n) = v;
                     }

@@ -241,7 +241,89 @@ int lipvq_linear_fwd(const float *X, const float *W, const float *b, float *Y, i
     if (act == ACT_GELU) return linear_fwd<ACT_GELU>(X, W, b, nullptr, Y, M, Nn, K, st);
     if (act == ACT_SIGMOID) return linear_fwd<ACT_SIGMOID>(X, W, b, nullptr, Y, M, Nn, K, st);
     if (act == ACT_NONE) return linear_fwd<ACT_NONE>(X, W, b, nullptr, Y, M, Nn, K, st);
+    if (act == ACT_RELU) return linear_fwd<ACT_RELU>(X, W, b, nullptr, Y, M, Nn, K, st);
     return LIPVQ_ESHAPE;
+}
+
+size_t lipvq_linear_bwd_ws_bytes(int64_t M, int32_t Nn, int32_t K) {
+    if (M < 0 || Nn < 1 || K < 1) return 0;
+    return splitk_ws_floats(M > 0 ? M : 1, Nn, K) * sizeof(float) + 1024;
+}
+
+int lipvq_linear_bwd(const float *dY, const float *X, const float *W, const float *x_mask, float *dX, float *dW,
+                     float *db, int64_t M, int32_t Nn, int32_t K, void *ws, size_t ws_bytes, void *stream) {
+    if (M < 0 || Nn < 1 || K < 1) return LIPVQ_ESHAPE;
+    if (!aligned16(dY) || !aligned16(X) || !aligned16(W) || !dW) return LIPVQ_EALIGN;
+    if (ws_bytes < lipvq_linear_bwd_ws_bytes(M, Nn, K) || !aligned16(ws)) return LIPVQ_EWORKSPACE;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (M == 0) {
+        LIPVQ_CUDA_OK(cudaMemsetAsync(dW, 0, (size_t)Nn * K * sizeof(float), st));
+        if (db) LIPVQ_CUDA_OK(cudaMemsetAsync(db, 0, (size_t)Nn * sizeof(float), st));
+        return LIPVQ_OK;
+    }
+    LIPVQ_TRY(linear_bwd_weight(dY, X, dW, db, M, Nn, K, (float *)ws, st));
+    if (dX) {
+        if (!aligned16(dX)) return LIPVQ_EALIGN;
+        if (x_mask) LIPVQ_TRY(linear_bwd_input<ACT_RELU>(dY, W, x_mask, dX, M, Nn, K, nullptr, nullptr, 0.f, nullptr, st));
+        else LIPVQ_TRY(linear_bwd_input<ACT_NONE>(dY, W, nullptr, dX, M, Nn, K, nullptr, nullptr, 0.f, nullptr, st));
+    }
+    return LIPVQ_OK;
+}
+
+int lipvq_scatter_add_diff(const float *src, const int64_t *idx, const float *table, float alpha,
+                           const float *grad_scale, int64_t n, int32_t D, int32_t K, float *sums, void *stream) {
+    if (n < 0 || D < 1 || K < 1) return LIPVQ_ESHAPE;
+    if (n == 0) return LIPVQ_OK;
+    if (!aligned16(src) || !idx || !aligned16(table) || !aligned16(sums)) return LIPVQ_EALIGN;
+    const int64_t blocks = (n + SC_ROWS - 1) / SC_ROWS;
+    scatter_add_kernel<true><<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(src, idx, n, D, K, sums, nullptr, table,
+                                                                                 alpha, grad_scale);
+    LIPVQ_LAUNCH_OK();
+    return LIPVQ_OK;
+}
+
+int lipvq_sse(const float *a, const float *b, int64_t n, double *out, void *ws, size_t ws_bytes, void *stream) {
+    if (n < 0) return LIPVQ_ESHAPE;
+    if (!out) return LIPVQ_EALIGN;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (n == 0) { LIPVQ_CUDA_OK(cudaMemsetAsync(out, 0, sizeof(double), st)); return LIPVQ_OK; }
+    if (!a || !b) return LIPVQ_EALIGN;
+    if (ws_bytes < kRedBlocks * sizeof(float) || !aligned16(ws)) return LIPVQ_EWORKSPACE;
+    sse_kernel<<<kRedBlocks, 256, 0, st>>>(a, b, n, (float *)ws);
+    LIPVQ_LAUNCH_OK();
+    partials_to_double_kernel<<<1, 256, 0, st>>>((float *)ws, kRedBlocks, out);
+    LIPVQ_LAUNCH_OK();
+    return LIPVQ_OK;
+}
+
+int lipvq_vqvae_loss(const double *sse_r, const double *sse_q, int64_t n_total, int32_t F, int32_t D,
+                     float commitment_cost, float *out, void *stream) {
+    if (n_total <= 0 || F < 1 || D < 1) return LIPVQ_ESHAPE;
+    if (!sse_r || !sse_q || !out) return LIPVQ_EALIGN;
+    vqvae_loss_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(sse_r, sse_q, 1.0 / ((double)n_total * F),
+                                                         1.0 / ((double)n_total * D), commitment_cost, out);
+    LIPVQ_LAUNCH_OK();
+    return LIPVQ_OK;
+}
+
+int lipvq_vqvae_recon_grad(const float *x_recon, const float *x, int64_t n_elems, float alpha,
+                           const float *grad_scale, float *out, void *stream) {
+    if (n_elems < 0) return LIPVQ_ESHAPE;
+    if (n_elems == 0) return LIPVQ_OK;
+    if (!x_recon || !x || !out) return LIPVQ_EALIGN;
+    recon_grad_relu_kernel<<<kRedBlocks, 256, 0, (cudaStream_t)stream>>>(x_recon, x, alpha, grad_scale, n_elems, out);
+    LIPVQ_LAUNCH_OK();
+    return LIPVQ_OK;
+}
+
+int lipvq_vqvae_ste_grad(float *g_zq, const float *z_e, const float *z_q, int64_t n_elems, float alpha,
+                         const float *grad_scale, void *stream) {
+    if (n_elems < 0) return LIPVQ_ESHAPE;
+    if (n_elems == 0) return LIPVQ_OK;
+    if (!g_zq || !z_e || !z_q) return LIPVQ_EALIGN;
+    ste_commit_relu_kernel<<<kRedBlocks, 256, 0, (cudaStream_t)stream>>>(g_zq, z_e, z_q, alpha, grad_scale, n_elems);
+    LIPVQ_LAUNCH_OK();
+    return LIPVQ_OK;
 }
 
 int lipvq_lipschitz_fwd(const float *h, const float *W, const float *b, const float *ci, float *scale,

@@ -296,6 +296,39 @@ __global__ void commit_sigmoid_bwd_kernel(const float *__restrict__ z_e, const f
     }
 }
 
+// classic VQVAE (vq_vae/backbone.py): gradient of mse(x_recon, x) through the ReLU on the decoder output
+//   out = gs * alpha * (x_recon - x) * [x_recon > 0]
+__global__ void recon_grad_relu_kernel(const float *__restrict__ xr, const float *__restrict__ x, float alpha,
+                                       const float *__restrict__ gs, int64_t n, float *__restrict__ out) {
+    if (gs) alpha *= *gs;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        const float v = xr[i];
+        out[i] = v > 0.f ? alpha * (v - x[i]) : 0.f;
+    }
+}
+// straight-through estimator + commitment term + the encoder's output ReLU (backbone.py:69, 74):
+//   g = (g_zq + gs * alpha * (z_e - z_q)) * [z_e > 0], in place over g_zq
+__global__ void ste_commit_relu_kernel(float *__restrict__ g, const float *__restrict__ z_e,
+                                       const float *__restrict__ z_q, float alpha, const float *__restrict__ gs,
+                                       int64_t n) {
+    if (gs) alpha *= *gs;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        const float ze = z_e[i];
+        g[i] = ze > 0.f ? g[i] + alpha * (ze - z_q[i]) : 0.f;
+    }
+}
+// loss = mse(x_recon, x) + (1 + cc) * mse(z_q, z_e)  (backbone.py:49-50, 69-71); out = {loss, recon, cc*mse_q, mse_q}
+__global__ void vqvae_loss_kernel(const double *sse_r, const double *sse_q, double inv_nf, double inv_nd, float cc,
+                                  float *out) {
+    if (threadIdx.x == 0 && blockIdx.x == 0) {
+        const double recon = (*sse_r) * inv_nf, q = (*sse_q) * inv_nd;
+        out[0] = (float)(recon + q + (double)cc * q);
+        out[1] = (float)recon;
+        out[2] = (float)((double)cc * q);
+        out[3] = (float)q;
+    }
+}
+
 __global__ void loss_finalize_kernel(const double *sse_r, const double *sse_q, double inv_nf,
                                      double inv_nd, float *out) {
     if (threadIdx.x == 0 && blockIdx.x == 0) {

@@ -399,5 +399,7 @@ def install_into_robomimic():
     """Rebind ``LLFQVAE_V4`` in robomimic's ``obs_nets`` namespace (imported there at
     obs_nets.py:47, looked up at call time :1225) so ``vq_vae_enabled`` builds this module."""
     import robomimic.models.obs_nets as obs_nets  # noqa: WPS433 (optional dependency)
+    from .vqvae_classic import VQVAE
     obs_nets.LLFQVAE_V4 = LLFQVAE_V4
+    obs_nets.VQVAE = VQVAE                        # the commented-out alternative at obs_nets.py:1220-1222
     return obs_nets

@@ -317,6 +317,88 @@ def vqvae_quantize(z_e, E, commitment_cost=0.25):
     return z_q, idx, mse + commitment_cost * mse
 
 
+VQ_PARAM_NAMES = ("encoder.0.weight", "encoder.0.bias", "encoder.2.weight", "encoder.2.bias",
+                  "encoder.4.weight", "encoder.4.bias", "decoder.0.weight", "decoder.0.bias",
+                  "decoder.2.weight", "decoder.2.bias", "decoder.4.weight", "decoder.4.bias", "embedding.weight")
+
+
+def vqvae_param_shapes(feature_dim, latent_dim, num_embeddings=128):
+    """state_dict of the classic VQVAE (vq:17-36): ReLU MLPs 12-64-128-D / D-128-64-12, nn.Embedding codebook."""
+    F, D, K = feature_dim, latent_dim, num_embeddings
+    return {"encoder.0.weight": (64, F), "encoder.0.bias": (64,), "encoder.2.weight": (128, 64),
+            "encoder.2.bias": (128,), "encoder.4.weight": (D, 128), "encoder.4.bias": (D,),
+            "decoder.0.weight": (128, D), "decoder.0.bias": (128,), "decoder.2.weight": (64, 128),
+            "decoder.2.bias": (64,), "decoder.4.weight": (F, 64), "decoder.4.bias": (F,),
+            "embedding.weight": (K, D)}
+
+
+def vqvae_init_params(feature_dim, latent_dim, num_embeddings=128, seed=0):
+    """nn.Linear default init; embedding U(+-1/K) (vq:35-36)."""
+    rng = np.random.default_rng(seed)
+    p = {}
+    for name, shp in vqvae_param_shapes(feature_dim, latent_dim, num_embeddings).items():
+        if name == "embedding.weight":
+            b = 1.0 / num_embeddings
+        else:
+            fan_in = shp[1] if len(shp) == 2 else vqvae_param_shapes(feature_dim, latent_dim, num_embeddings)[
+                name.replace("bias", "weight")][1]
+            b = 1.0 / math.sqrt(fan_in)
+        p[name] = rng.uniform(-b, b, shp).astype(np.float32)
+    return p
+
+
+def _lin(x, W, b):
+    return (x @ W.T + b).astype(np.float32)
+
+
+def vqvae_forward(p, x, commitment_cost=0.25):
+    """VQVAE.forward (vq:38-53) + quantize (vq:55-76), fp32 like the reference."""
+    relu = lambda a: np.maximum(a, np.float32(0))
+    h1 = relu(_lin(x, p["encoder.0.weight"], p["encoder.0.bias"]))
+    h2 = relu(_lin(h1, p["encoder.2.weight"], p["encoder.2.bias"]))
+    z_e = relu(_lin(h2, p["encoder.4.weight"], p["encoder.4.bias"]))
+    E = p["embedding.weight"]
+    idx = exact_top2(z_e, E)[0]
+    z_q = E[idx]
+    d1 = relu(_lin(z_q, p["decoder.0.weight"], p["decoder.0.bias"]))
+    d2 = relu(_lin(d1, p["decoder.2.weight"], p["decoder.2.bias"]))
+    xr = relu(_lin(d2, p["decoder.4.weight"], p["decoder.4.bias"]))
+    recon = float(np.mean((xr.astype(np.float64) - x) ** 2))
+    mse_q = float(np.mean((z_q.astype(np.float64) - z_e) ** 2))
+    return dict(h1=h1, h2=h2, z_e=z_e, idx=idx, z_q=z_q, z_latent=z_q.copy(), d1=d1, d2=d2, x_recon=xr,
+                recon=recon, mse_q=mse_q, loss=recon + mse_q + commitment_cost * mse_q)
+
+
+def vqvae_backward(p, x, fw, commitment_cost=0.25):
+    """autograd of vqvae_forward: recon -> decoder -> (straight-through, vq:74) -> encoder; commitment term
+    -> encoder; embedding loss -> codebook only (the decoder does NOT reach the codebook through the STE)."""
+    f64 = np.float64
+    N, F = x.shape
+    D = fw["z_e"].shape[1]
+    g = (2.0 / (N * F)) * (fw["x_recon"].astype(f64) - x) * (fw["x_recon"] > 0)
+    gr = {}
+
+    def back(g_out, inp, W, mask_src):
+        dW = g_out.T @ inp.astype(f64)
+        db = g_out.sum(0)
+        g_in = g_out @ W.astype(f64)
+        if mask_src is not None:
+            g_in = g_in * (mask_src > 0)
+        return dW, db, g_in
+    gr["decoder.4.weight"], gr["decoder.4.bias"], g = back(g, fw["d2"], p["decoder.4.weight"], fw["d2"])
+    gr["decoder.2.weight"], gr["decoder.2.bias"], g = back(g, fw["d1"], p["decoder.2.weight"], fw["d1"])
+    gr["decoder.0.weight"], gr["decoder.0.bias"], g = back(g, fw["z_q"], p["decoder.0.weight"], None)
+    diff = fw["z_e"].astype(f64) - fw["z_q"]
+    g = (g + commitment_cost * (2.0 / (N * D)) * diff) * (fw["z_e"] > 0)
+    gE = np.zeros(p["embedding.weight"].shape, f64)
+    np.add.at(gE, fw["idx"], -(2.0 / (N * D)) * diff)
+    gr["embedding.weight"] = gE
+    gr["encoder.4.weight"], gr["encoder.4.bias"], g = back(g, fw["h2"], p["encoder.4.weight"], fw["h2"])
+    gr["encoder.2.weight"], gr["encoder.2.bias"], g = back(g, fw["h1"], p["encoder.2.weight"], fw["h1"])
+    gr["encoder.0.weight"], gr["encoder.0.bias"], _ = back(g, x, p["encoder.0.weight"], None)
+    return {k: v.astype(np.float32) for k, v in gr.items()}
+
+
 # ----------------------------------------------------------------------------- EMA extension
 def ema_update(E, n_ema, m_ema, z_e, idx, gamma=0.99, eps=1e-5):
     """EMA codebook update -- NOT IN THE REFERENCE (parity unpinned).  Standard VQ-VAE EMA:

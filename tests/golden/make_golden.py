@@ -114,6 +114,50 @@ def quant_inputs(name):
     raise KeyError(name)
 
 
+VQVAE_CASES = ("vq_small", "vq_ref")
+
+
+def vqvae_case_inputs(name):
+    """Deterministic (params, x) for the classic-VQVAE cases (vq:6-76)."""
+    if name == "vq_small":
+        F, D, K, n, seed = 12, 24, 64, 80, 300
+    elif name == "vq_ref":         # the widths of the commented-out call site (obs_nets.py:1220-1222): K=128 default
+        F, D, K, n, seed = 12, 208, 128, 2560, 301
+    else:
+        raise KeyError(name)
+    p = orc.vqvae_init_params(F, D, K, seed=seed)
+    rng = np.random.default_rng(seed + 1000)
+    x = rng.random((n, F)).astype(np.float32)                # the output ReLU can only reconstruct x >= 0
+    for k in ("encoder.0.bias", "encoder.2.bias", "encoder.4.bias"):
+        p[k] = (p[k] + 0.05).astype(np.float32)              # keep a healthy share of ReLU units alive
+    z = orc.vqvae_forward(p, rng.random((K, F)).astype(np.float32))["z_e"]
+    p["embedding.weight"] = (z + 1e-3 * rng.standard_normal(z.shape)).astype(np.float32)   # spread codebook
+    return p, x
+
+
+def run_vqvae_case(name):
+    p, x = vqvae_case_inputs(name)
+    K, D = p["embedding.weight"].shape
+    m = _ref("vq").VQVAE(x.shape[1], D, num_embeddings=K)
+    m.load_state_dict({k: torch.from_numpy(v.copy()) for k, v in p.items()}, strict=True)
+    assert tuple(m.state_dict().keys()) == orc.VQ_PARAM_NAMES
+    xt = torch.from_numpy(x)
+    z_latent, loss = m(xt)                                                    # vq:38-53
+    loss.backward()
+    with torch.no_grad():
+        z_e = m.encoder(xt)
+        d = (z_e.unsqueeze(1) - m.embedding.weight).pow(2).sum(-1)
+        idx = torch.argmin(d, dim=1)
+        x_rec = m.decoder(m.embedding(idx))
+    out = dict(loss=np.float64(loss.item()), idx=idx.numpy().astype(np.int32), z_e_head=z_e[:32].numpy(),
+               x_recon_head=x_rec[:32].numpy(), z_latent_sum=np.float64(z_latent.double().sum().item()),
+               z_latent_abs=np.float64(z_latent.double().abs().sum().item()))
+    for k, v in m.named_parameters():
+        out["grad/" + k] = v.grad.detach().numpy().copy()
+    np.savez_compressed(os.path.join(HERE, f"vqvae_{name}.npz"), **out)
+    print(name, "loss", loss.item(), "unique idx", len(np.unique(out["idx"])))
+
+
 MODEL_CASES = ("c1_init", "c1_spread", "small", "d787")
 QUANT_CASES = ("q_uniform64", "q_neartie", "q_k4096_d128", "q_d256_k128", "q_collapsed")
 
@@ -195,6 +239,12 @@ def run_quant_case(name):
 if __name__ == "__main__":
     torch.manual_seed(0)
     torch.set_num_threads(8)
+    if len(sys.argv) > 1 and sys.argv[1] == "vqvae":      # only the classic-VQVAE vectors
+        for c in VQVAE_CASES:
+            run_vqvae_case(c)
+        sys.exit(0)
+    for c in VQVAE_CASES:
+        run_vqvae_case(c)
     for c in MODEL_CASES:
         run_model_case(c)
     for c in QUANT_CASES:

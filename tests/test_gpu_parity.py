@@ -402,3 +402,42 @@ def test_fused_paths_ragged_and_unaligned_shapes(n, D, K):
         gr = orc.backward(p, x, fw)
         for k, t in m.named_parameters():
             assert orc.rel_err(t.grad.cpu().numpy(), gr[k]) < GTOL, k
+
+
+@pytest.mark.parametrize("mode", MODES)
+@pytest.mark.parametrize("case", ["vq_small", "vq_ref"])
+def test_classic_vqvae_vs_reference_golden(case, mode):
+    """Secondary variant: the classic VQVAE of vq_vae/backbone.py -- ReLU MLPs, squared distances,
+    straight-through estimator, loss = recon + embedding + 0.25 commitment -- against vectors produced by the REAL
+    reference module (tests/golden/vqvae_*.npz): indices, loss, latents and all 13 gradients."""
+    from lipvq_vae_b200 import VQVAE
+    from tests.golden.make_golden import vqvae_case_inputs
+    p, x = vqvae_case_inputs(case)
+    g = _load("vqvae_" + case)
+    K, D = p["embedding.weight"].shape
+    m = VQVAE(x.shape[1], D, num_embeddings=K).cuda()
+    assert tuple(m.state_dict().keys()) == orc.VQ_PARAM_NAMES
+    m.load_state_dict({k: torch.from_numpy(v.copy()) for k, v in p.items()}, strict=True)
+    m.search_mode = mode
+    xt = torch.from_numpy(x).cuda()
+    z_latent, loss = m(xt)
+    assert not z_latent.requires_grad and loss.dim() == 0 and loss.requires_grad
+    loss.backward()
+    torch.cuda.synchronize()
+    idx = m.last_indices.cpu().numpy()
+    fw = orc.vqvae_forward(p, x)
+    _, d1, d2 = orc.exact_top2(fw["z_e"], p["embedding.weight"])
+    must = orc.index_parity_mask(d1, d2)
+    assert np.array_equal(idx[must], g["idx"][must].astype(np.int64))
+    z_e = m.encoder(xt).cpu().numpy()
+    assert orc.rel_err(z_e[:32], g["z_e_head"]) < RTOL
+    if np.array_equal(idx, g["idx"]):
+        assert abs(loss.item() - g["loss"]) < RTOL * abs(g["loss"])
+        assert abs(z_latent.double().sum().item() - g["z_latent_sum"]) < RTOL * g["z_latent_abs"]
+        for k, t in m.named_parameters():
+            assert orc.rel_err(t.grad.cpu().numpy(), g["grad/" + k]) < GTOL, k
+    with torch.no_grad():
+        z2, loss2 = m(xt)
+    assert torch.equal(z2, z_latent) and abs(loss2.item() - loss.item()) < 1e-6 * abs(loss.item())
+    zq, qloss = m.quantize(torch.from_numpy(fw["z_e"]).cuda())
+    assert abs(qloss.item() - 1.25 * fw["mse_q"]) < RTOL * 1.25 * fw["mse_q"]

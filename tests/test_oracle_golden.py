@@ -114,3 +114,20 @@ def test_ema_update_properties():
     assert np.allclose(sums.sum(0), z.sum(0), rtol=1e-5)
     assert np.allclose(n1, 0.9 * n0 + 0.1 * counts)
     assert E1.shape == E.shape and np.isfinite(E1).all()
+
+
+@pytest.mark.parametrize("case", ["vq_small", "vq_ref"])
+def test_oracle_classic_vqvae_matches_reference(case):
+    """The oracle's restatement of the classic VQVAE (vq_vae/backbone.py:6-76, forward + autograd incl. the
+    straight-through route) against vectors produced by the real reference module."""
+    from tests.golden.make_golden import vqvae_case_inputs
+    p, x = vqvae_case_inputs(case)
+    g = dict(np.load(os.path.join(G, "vqvae_%s.npz" % case)))
+    fw = orc.vqvae_forward(p, x)
+    assert np.array_equal(fw["idx"], g["idx"])
+    assert abs(fw["loss"] - g["loss"]) < 1e-6 * abs(g["loss"])
+    assert orc.rel_err(fw["z_e"][:32], g["z_e_head"]) < 1e-6
+    assert orc.rel_err(fw["x_recon"][:32], g["x_recon_head"]) < 1e-6
+    gr = orc.vqvae_backward(p, x, fw)
+    for k in orc.VQ_PARAM_NAMES:
+        assert orc.rel_err(gr[k], g["grad/" + k]) < 2e-6, k
