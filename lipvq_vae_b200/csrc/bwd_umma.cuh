@@ -1,0 +1,331 @@
+// bwd_umma.cuh -- the N-row GEMMs of the tokenizer backward (autograd of v5:71-72, invoked icl.py:969) on the
+// 5th-gen tensor cores: tcgen05.mma kind::tf32, accumulators in TMEM, 3xTF32 split products
+//   A*B ~= A_lo*B_hi + A_hi*B_lo + A_hi*B_hi   (hi = tf32-rounded value, lo = exact fp32 remainder)
+// so the gradients keep fp32 parity (1e-5) with the reference's autograd.
+//
+//   wgrad_umma_kernel : part[cta][Nout][Kin+1] = dY[rows_cta, Nout]^T [X[rows_cta, Kin] | 1]
+//
+// The reduction axis of a weight gradient is the ROW axis, so both operands are "MN-major" for the tensor core:
+// a row-major [rows, cols] slab IS the canonical MN-major operand (rows of 32 fp32 = 128 B, swizzled in 32-byte
+// chunks, see desc_mn), no transposition anywhere -- TMA drops 16-row x 32-column boxes of dY and X straight
+// into operand position.  The tensor core reads only the upper 19 bits of an fp32 operand (measured: feeding raw
+// values and hi = rna(v) give the same 2e-6 error), so the raw image serves as the hi operand and only the lo
+// image (v - trunc_tf32(v)) is computed, by 8 converter warps, shared memory to shared memory.  Every CTA walks
+// its own contiguous row range, keeps the whole [Nout, Kin] partial in TMEM and writes it once; a fixed-order
+// reduction over the CTAs (splitk_reduce_kernel) makes the result deterministic.
+#pragma once
+#include "common.cuh"
+#include "ptx_sm100.cuh"
+#include <cstdlib>
+
+namespace lipvq {
+namespace bwd5 {
+
+constexpr int NLOAD = 256;          // 8 converter warps
+constexpr int NTHR = NLOAD + 64;    // + 1 MMA-issuing warp + 1 TMA producer warp
+constexpr int R = 16;               // rows per slab
+constexpr int KG = R / 8;           // one kind::tf32 MMA consumes 8 rows (K = 8)
+constexpr int NST_MAX = 12;         // slab ring depth: as many stages as fit (TMA runs that many slabs ahead)
+constexpr int CH = 16;              // slabs per accumulation chunk (256 rows), see below
+constexpr int MAX_NOUT = 256, MAX_KIN = 128;
+
+__device__ __forceinline__ void split_rna(float v, uint32_t &hi, uint32_t &lo) {
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(hi) : "f"(v));
+    lo = __float_as_uint(v - __uint_as_float(hi));
+}
+
+// MN-major fp32/tf32 operands have ONE legal shared-memory layout on sm_100: SWIZZLE_128B_BASE32B (layout type 1),
+// canonical form Swizzle<2,5,2> o ((T,8,m),(4,k)):((1,T,LBO),(.,SBO)), T = 4 fp32 -- an atom is 4 k-rows of 128
+// bytes (32 consecutive M/N elements), the 32-byte chunk c of row r sits at chunk (c ^ (r & 3)) -- what TMA's
+// CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B writes.  Here: the two 4-row atoms of one K = 8 MMA are 512 B apart (SBO),
+// consecutive 32-column blocks one 16-row TMA box = 2 KB apart (LBO); the 8-row k groups inside a box are walked
+// by the issuing thread through the start address.
+__device__ __forceinline__ uint64_t desc_mn_sw128(uint32_t saddr) {
+    return (uint64_t)((saddr >> 4) & 0x3FFF) | ((uint64_t)((KG * 1024) >> 4) << 16) | ((uint64_t)(512 >> 4) << 32) |
+           (1ull << 46) | (1ull << 61);
+}
+// kind::tf32, fp32 accumulate, A and B both MN-major (bits 15 / 16)
+__host__ __device__ constexpr uint32_t idesc_tf32_mn(int M, int N) {
+    return ptx::umma_idesc_tf32(M, N) | (1u << 15) | (1u << 16);
+}
+
+// The operand with at most 128 columns plays A (M = 128, zero padded), the other one B (N <= 256): for
+// Nout > 128 the product is computed transposed (A = X, B = dY) so one M tile always suffices.
+struct WgGeom {
+    int swap, colsP, colsQ, NI, nblkQ, imgP, imgQ, stage, nst, smem;
+};
+inline __host__ __device__ WgGeom wg_geom(int Nout, int Kin) {
+    WgGeom g;
+    g.swap = Nout > 128;
+    g.colsP = g.swap ? Kin : Nout;
+    g.colsQ = g.swap ? Nout : Kin;
+    g.NI = (g.colsQ + 15) / 16 * 16;
+    g.nblkQ = (g.NI + 31) / 32;
+    g.imgP = 4 * R * 128;
+    g.imgQ = g.nblkQ * R * 128;
+    g.stage = 2 * (g.imgP + g.imgQ);
+    g.nst = (227 * 1024 - 2048) / g.stage;
+    if (g.nst > NST_MAX) g.nst = NST_MAX;
+    g.smem = g.nst * g.stage + 1024 + 1024;
+    return g;
+}
+
+// byte offset of 16-byte chunk (row r of the slab, column c) inside an image: 32-column blocks of R rows x 128 B
+__device__ __forceinline__ int img_off(int r, int c) {
+    const int j = (c & 31) >> 2;
+    return ((c >> 5) * (R * 128)) + (r << 7) + (((j >> 1) ^ (r & 3)) << 5) + ((j & 1) << 4);
+}
+__device__ __forceinline__ void named_sync_loaders() { asm volatile("bar.sync 1, %0;" ::"n"(NLOAD) : "memory"); }
+
+// Roles: warp 9 (one lane) issues the TMA box loads of a slab into a ring stage, up to NST slabs ahead; warps 0-7
+// write the lo images of a landed stage and sum the bias gradient (column sums of dY) from the values they
+// touch; warp 8 (one lane) issues the MMAs of a converted stage and frees it through tcgen05.commit.  The tensor
+// core accumulates with truncation, a bias that grows with the number of accumulations (measured 7e-9 per row),
+// so a TMEM accumulator only collects a chunk of CH slabs (256 rows); at a chunk end the converter warps add it
+// (fp32, round-to-nearest) to a master accumulator in the other half of TMEM (tcgen05.ld / add / tcgen05.st).
+__global__ void __launch_bounds__(NTHR, 1)
+wgrad_umma_kernel(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__ CUtensorMap tm_q, int64_t rows,
+                  int Nout, int Kin, int64_t rows_per_cta, float *__restrict__ part, int groups) {
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t raw = ptx::smem_u32(smem_raw);
+    uint8_t *sm = smem_raw + (((raw + 1023u) & ~1023u) - raw);
+    const uint32_t s0 = ptx::smem_u32(sm);
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const WgGeom G = wg_geom(Nout, Kin);
+    const int NST = G.nst, STAGE = G.stage, P_IMG = G.imgP, Q_IMG = G.imgQ, NI = G.NI;
+    // stage layout: P_raw (= hi) | P_lo | Q_raw (= hi) | Q_lo
+    uint8_t *bars = sm + NST * STAGE;
+    const uint32_t bar_tma = ptx::smem_u32(bars), bar_full = bar_tma + 8 * NST_MAX, bar_free = bar_full + 8 * NST_MAX,
+                   bar_chunk = bar_free + 8 * NST_MAX, bar_flush = bar_chunk + 8;
+    volatile uint32_t *tmem_slot = reinterpret_cast<volatile uint32_t *>(bars + 8 * (3 * NST_MAX + 2));
+
+    // zero the ring once: blocks past the last real column block are never written again
+    for (int i = tid; i < NST * STAGE / 16; i += NTHR) reinterpret_cast<uint4 *>(sm)[i] = make_uint4(0, 0, 0, 0);
+    if (tid == 0) {
+        for (int i = 0; i < NST; ++i) {
+            ptx::mbar_init(bar_tma + 8 * i, 1);
+            ptx::mbar_init(bar_full + 8 * i, (NLOAD / 32) / groups);
+            ptx::mbar_init(bar_free + 8 * i, 1);
+        }
+        ptx::mbar_init(bar_chunk, 1);
+        ptx::mbar_init(bar_flush, NLOAD / 32);
+        ptx::fence_barrier_init();
+    }
+    if (warp == 0) ptx::tmem_alloc<512>(ptx::smem_u32((const void *)tmem_slot));
+    ptx::fence_proxy_async();
+    ptx::tc_fence_before();
+    __syncthreads();
+    ptx::tc_fence_after();
+    const uint32_t tmem = *tmem_slot;
+
+    const int64_t row_beg = (int64_t)blockIdx.x * rows_per_cta;
+    const int64_t row_end = row_beg + rows_per_cta < rows ? row_beg + rows_per_cta : rows;
+    const int n_slabs = row_beg < row_end ? (int)((row_end - row_beg + R - 1) / R) : 0;
+    const int ld = Kin + 1;
+    float *C = part + (size_t)blockIdx.x * Nout * ld;
+    const int boxes_p = (G.colsP + 31) >> 5, boxes_q = (G.colsQ + 31) >> 5;
+
+    if (warp == NLOAD / 32 + 1) {
+        // ---------------------------------------------------------------- TMA producer (one lane)
+        if (lane == 0) {
+            ptx::tma_prefetch_desc(&tm_p);
+            ptx::tma_prefetch_desc(&tm_q);
+        }
+        // lane b issues box b of a slab (P boxes first), lane 0 arms the stage barrier before anyone issues
+        for (int slab = 0; slab < n_slabs; ++slab) {
+            const int stage = slab % NST;
+            const uint32_t bar = bar_tma + 8 * stage, p_raw = s0 + stage * STAGE, q_raw = p_raw + 2 * P_IMG;
+            const int row = (int)(row_beg + (int64_t)slab * R);
+            if (lane == 0) {
+                if (slab >= NST) ptx::mbar_wait(bar_free + 8 * stage, ((slab / NST) - 1) & 1);
+                ptx::mbar_arrive_expect_tx(bar, (uint32_t)(boxes_p + boxes_q) * (R * 128));
+            }
+            __syncwarp();
+            if (lane < boxes_p) ptx::tma_load_2d(&tm_p, bar, p_raw + lane * (R * 128), lane * 32, row);
+            else if (lane < boxes_p + boxes_q)
+                ptx::tma_load_2d(&tm_q, bar, q_raw + (lane - boxes_p) * (R * 128), (lane - boxes_p) * 32, row);
+        }
+    } else if (warp == NLOAD / 32) {
+        // ---------------------------------------------------------------- MMA issuer (one lane)
+        if (lane == 0) {
+            const uint32_t idesc = idesc_tf32_mn(128, NI);
+            for (int slab = 0; slab < n_slabs; ++slab) {
+                const int stage = slab % NST, in_chunk = slab % CH;
+                if (in_chunk == 0 && slab > 0) ptx::mbar_wait(bar_flush, ((slab / CH) - 1) & 1);   // chunk acc was drained
+                ptx::mbar_wait(bar_full + 8 * stage, (slab / NST) & 1);
+                ptx::tc_fence_after();
+                const uint32_t a_hi = s0 + stage * STAGE, a_lo = a_hi + P_IMG, b_hi = a_hi + 2 * P_IMG, b_lo = b_hi + Q_IMG;
+#pragma unroll
+                for (int g = 0; g < KG; ++g) {
+                    const uint64_t bh = desc_mn_sw128(b_hi + g * 1024), bl = desc_mn_sw128(b_lo + g * 1024);
+                    const uint64_t ah = desc_mn_sw128(a_hi + g * 1024), al = desc_mn_sw128(a_lo + g * 1024);
+                    ptx::umma_tf32_ss(tmem, al, bh, idesc, (in_chunk | g) ? 1u : 0u);
+                    ptx::umma_tf32_ss(tmem, ah, bl, idesc, 1u);
+                    ptx::umma_tf32_ss(tmem, ah, bh, idesc, 1u);
+                }
+                ptx::umma_commit(bar_free + 8 * stage);
+                if (in_chunk == CH - 1 || slab == n_slabs - 1) ptx::umma_commit(bar_chunk);
+            }
+        }
+    } else {
+        // ---------------------------------------------------------------- converters / flushers
+        const int lq = warp & 3, half = warp >> 2;
+        const uint32_t t_lane = tmem + ((uint32_t)(lq * 32) << 16);
+        {   // master accumulator (columns 256..511) starts at zero
+            uint32_t z[16];
+#pragma unroll
+            for (int i = 0; i < 16; ++i) z[i] = 0u;
+            for (int cb = half; cb < 16; cb += 2) ptx::tmem_st_32x32b_x16(t_lane + 256 + cb * 16, z);
+            ptx::tmem_st_wait();
+        }
+        // A converter warp owns whole slabs (slab % 8 == warp, so 8 slabs are converted concurrently and one
+        // warp's proxy fence never stalls the others); a lane owns 16-byte column chunks lane, lane + 32 of every row.
+        const int p4 = G.colsP >> 2, q4 = G.colsQ >> 2;
+        float4 bsum[2];   // column sums of dY (the P operand, or Q when the roles are swapped)
+        bsum[0] = bsum[1] = make_float4(0.f, 0.f, 0.f, 0.f);
+        auto lo_of = [](float v) { return v - __uint_as_float(__float_as_uint(v) & 0xffffe000u); };
+        auto add4 = [](float4 &a, const float4 &v) { a.x += v.x; a.y += v.y; a.z += v.z; a.w += v.w; };
+        auto conv = [&](uint8_t *img, int lo_delta, int off, float4 &acc, bool sum) {
+            const float4 v = *reinterpret_cast<const float4 *>(img + off);
+            *reinterpret_cast<float4 *>(img + lo_delta + off) = make_float4(lo_of(v.x), lo_of(v.y), lo_of(v.z), lo_of(v.w));
+            if (sum) add4(acc, v);
+        };
+        // a parity wait is only meaningful one phase ahead: a warp's next slab must not be more than a ring away
+        // converter warps work in `groups` groups of W warps; a group owns whole slabs (slab % groups), a warp of the
+        // group every W-th row, a lane the 16-byte column chunks lane, lane + 32
+        const int W = (NLOAD / 32) / groups, gi = warp / W, wi = warp % W;
+        const int ncw = NST < groups ? NST : groups;
+        const int n_chunks = (n_slabs + CH - 1) / CH;
+        for (int chunk = 0; chunk < n_chunks; ++chunk) {
+            const int s_end = (chunk + 1) * CH < n_slabs ? (chunk + 1) * CH : n_slabs;
+            for (int slab = chunk * CH + gi; slab < s_end && gi < ncw; slab += ncw) {
+                const int stage = slab % NST;
+                ptx::mbar_wait(bar_tma + 8 * stage, (slab / NST) & 1);
+                uint8_t *sp = sm + stage * STAGE, *sq = sp + 2 * P_IMG;
+#pragma unroll 4
+                for (int r = wi; r < R; r += W) {
+                    if (lane < p4) conv(sp, P_IMG, img_off(r, lane << 2), bsum[0], !G.swap);
+                    if (lane < q4) conv(sq, Q_IMG, img_off(r, lane << 2), bsum[0], G.swap);
+                    if (lane + 32 < q4) conv(sq, Q_IMG, img_off(r, (lane + 32) << 2), bsum[1], G.swap);
+                }
+                ptx::fence_proxy_async();
+                __syncwarp();
+                if (lane == 0) ptx::mbar_arrive(bar_full + 8 * stage);
+            }
+            // chunk accumulator (columns 0..) += into the master (columns 256..), fp32 round-to-nearest
+            ptx::mbar_wait(bar_chunk, chunk & 1);
+            ptx::tc_fence_after();
+            for (int cb = half; cb < NI / 16; cb += 2) {
+                uint32_t a[16], m[16];
+                ptx::tmem_ld_32x32b_x16(t_lane + cb * 16, a);
+                ptx::tmem_ld_32x32b_x16(t_lane + 256 + cb * 16, m);
+                ptx::tmem_ld_wait();
+#pragma unroll
+                for (int i = 0; i < 16; ++i) m[i] = __float_as_uint(__uint_as_float(m[i]) + __uint_as_float(a[i]));
+                ptx::tmem_st_32x32b_x16(t_lane + 256 + cb * 16, m);
+            }
+            ptx::tmem_st_wait();
+            ptx::tc_fence_before();
+            __syncwarp();
+            if (lane == 0) ptx::mbar_arrive(bar_flush);
+        }
+        // every MMA has completed (the last flush waited for it) and every TMA load has landed: the ring is free
+        // -> bias-gradient scratch [8 warps][Nout], summed in warp order
+        named_sync_loaders();
+        float *sdb = reinterpret_cast<float *>(sm);
+        {
+            const int d4 = Nout >> 2;
+            if (lane < d4) *reinterpret_cast<float4 *>(sdb + warp * Nout + (lane << 2)) = bsum[0];
+            if (lane + 32 < d4) *reinterpret_cast<float4 *>(sdb + warp * Nout + ((lane + 32) << 2)) = bsum[1];
+        }
+        named_sync_loaders();
+        for (int c = tid; c < Nout; c += NLOAD) {
+            float t = 0.f;
+#pragma unroll
+            for (int w = 0; w < NLOAD / 32; ++w) t += sdb[w * Nout + c];
+            C[(size_t)c * ld + Kin] = t;
+        }
+        // master accumulator -> this CTA's partial (D[m][n]: m = P column, n = Q column)
+        ptx::tc_fence_after();
+        const int m = lq * 32 + lane;
+        for (int cb = half; cb < NI / 16; cb += 2) {
+            uint32_t v[16];
+            ptx::tmem_ld_32x32b_x16(t_lane + 256 + cb * 16, v);
+            ptx::tmem_ld_wait();
+            if (m < G.colsP) {
+#pragma unroll
+                for (int i = 0; i < 16; ++i) {
+                    const int n = cb * 16 + i;
+                    if (n < G.colsQ) {
+                        if (G.swap) C[(size_t)n * ld + m] = __uint_as_float(v[i]);
+                        else C[(size_t)m * ld + n] = __uint_as_float(v[i]);
+                    }
+                }
+            }
+        }
+    }
+    ptx::tc_fence_before();
+    __syncthreads();
+    if (warp == 0) ptx::tmem_dealloc<512>(tmem);
+}
+
+// ------------------------------------------------------------------ host side
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                  const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+inline EncodeTiledFn encode_tiled() {
+    static EncodeTiledFn fn = nullptr;
+    if (!fn) {
+        void *p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = (EncodeTiledFn)p;
+    }
+    return fn;
+}
+// fp32 [rows, cols] row-major, box = 32 columns x box_rows rows, 32-byte-atom 128-byte swizzle, zero fill past the edges
+inline int make_slab_tmap(CUtensorMap *m, const float *ptr, uint64_t rows, uint64_t cols, uint32_t box_rows) {
+    EncodeTiledFn fn = encode_tiled();
+    if (!fn) return LIPVQ_ECUDA;
+    cuuint64_t dims[2] = {cols, rows};
+    cuuint64_t strides[1] = {cols * sizeof(float)};
+    cuuint32_t box[2] = {32, box_rows};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float *>(ptr), dims, strides, box, estr,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    return r == CUDA_SUCCESS ? LIPVQ_OK : LIPVQ_ECUDA;
+}
+
+inline bool wgrad_umma_ok(int64_t rows, int Nout, int Kin) {
+    return Nout >= 4 && Nout <= MAX_NOUT && Kin >= 4 && Kin <= MAX_KIN && (Nout & 3) == 0 && (Kin & 3) == 0 &&
+           rows >= 4096 && rows < (1ll << 31) && wg_geom(Nout, Kin).nst >= 2;
+}
+inline int wgrad_umma_grid(int64_t rows, int64_t *rows_per_cta) {
+    int64_t slabs = (rows + R - 1) / R;
+    int64_t per = (slabs + kNumSMs - 1) / kNumSMs * R;
+    *rows_per_cta = per;
+    return (int)((rows + per - 1) / per);
+}
+// part: [grid][Nout][Kin+1]; returns the number of partials in *splits
+inline int wgrad_umma_launch(const float *dY, const float *X, int64_t rows, int Nout, int Kin, float *part,
+                             int *splits, cudaStream_t st) {
+    int64_t per;
+    const int grid = wgrad_umma_grid(rows, &per);
+    const WgGeom G = wg_geom(Nout, Kin);
+    const int smem = G.smem;
+    CUtensorMap tm_dy, tm_x;
+    LIPVQ_TRY(make_slab_tmap(&tm_dy, dY, (uint64_t)rows, (uint64_t)Nout, R));
+    LIPVQ_TRY(make_slab_tmap(&tm_x, X, (uint64_t)rows, (uint64_t)Kin, R));
+    LIPVQ_CUDA_OK(cudaFuncSetAttribute(wgrad_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    ProfScope prof("wgrad_umma_kernel", st);
+    static const int groups = [] { const char *e = getenv("LIPVQ_WG_GROUPS"); int g = e ? atoi(e) : 2; return (g == 1 || g == 2 || g == 4 || g == 8) ? g : 2; }();
+    wgrad_umma_kernel<<<grid, NTHR, smem, st>>>(G.swap ? tm_x : tm_dy, G.swap ? tm_dy : tm_x, rows, Nout, Kin, per, part, groups);
+    LIPVQ_LAUNCH_OK();
+    *splits = grid;
+    return LIPVQ_OK;
+}
+
+}  // namespace bwd5
+}  // namespace lipvq

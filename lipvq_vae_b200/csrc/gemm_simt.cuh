@@ -6,6 +6,7 @@
 #include <cstring>
 
 #include "common.cuh"
+#include "bwd_umma.cuh"
 
 namespace lipvq {
 
@@ -491,7 +492,9 @@ inline int splits_for_rows(int64_t rows, int Nout, int Kin) {
     return (int)s;
 }
 inline size_t splitk_ws_floats(int64_t rows, int Nout, int Kin) {
-    return (size_t)splits_for_rows(rows, Nout, Kin) * Nout * (Kin + 1);
+    size_t s = (size_t)splits_for_rows(rows, Nout, Kin);
+    if (bwd5::wgrad_umma_ok(rows, Nout, Kin) && s < (size_t)kNumSMs) s = kNumSMs;   // one partial per CTA
+    return s * Nout * (Kin + 1);
 }
 
 // ---------------------------------------------------------------- weight gradient on the tensor cores
@@ -608,6 +611,15 @@ inline int linear_bwd_weight(const float *dY, const float *X, float *dW, float *
                              int Nout, int Kin, float *part, cudaStream_t st, const float *out_scale_dev = nullptr) {
     const int splits = splits_for_rows(rows, Nout, Kin);
     static const bool simt = [] { const char *e = getenv("LIPVQ_GEMM"); return e && !strcmp(e, "simt"); }();
+    static const bool legacy = [] { const char *e = getenv("LIPVQ_GEMM"); return e && !strcmp(e, "mma_sync"); }();
+    if (!simt && !legacy && bwd5::wgrad_umma_ok(rows, Nout, Kin) && aligned16(dY) && aligned16(X)) {
+        int parts = 0;
+        LIPVQ_TRY(bwd5::wgrad_umma_launch(dY, X, rows, Nout, Kin, part, &parts, st));
+        const int total = Nout * (Kin + 1);
+        splitk_reduce_kernel<<<(total + 255) / 256, 256, 0, st>>>(part, parts, Nout, Kin, dW, db, out_scale_dev);
+        LIPVQ_LAUNCH_OK();
+        return LIPVQ_OK;
+    }
     if (!simt && (Nout & 3) == 0 && (Kin & 3) == 0 && aligned16(dY) && aligned16(X) &&
         (double)rows * Nout * Kin >= 1.0e7) {
         int64_t k_chunk = (rows + splits - 1) / splits;
