@@ -16,7 +16,6 @@
 #pragma once
 #include "common.cuh"
 #include "ptx_sm100.cuh"
-#include <cstdlib>
 
 namespace lipvq {
 namespace bwd5 {
@@ -26,7 +25,7 @@ constexpr int NTHR = NLOAD + 64;    // + 1 MMA-issuing warp + 1 TMA producer war
 constexpr int R = 16;               // rows per slab
 constexpr int KG = R / 8;           // one kind::tf32 MMA consumes 8 rows (K = 8)
 constexpr int NST_MAX = 12;         // slab ring depth: as many stages as fit (TMA runs that many slabs ahead)
-constexpr int CH = 16;              // slabs per accumulation chunk (256 rows), see below
+constexpr int CH_DEFAULT = 16;      // slabs per accumulation chunk (256 rows), see below
 constexpr int MAX_NOUT = 256, MAX_KIN = 128;
 
 __device__ __forceinline__ void split_rna(float v, uint32_t &hi, uint32_t &lo) {
@@ -43,6 +42,14 @@ __device__ __forceinline__ void split_rna(float v, uint32_t &hi, uint32_t &lo) {
 __device__ __forceinline__ uint64_t desc_mn_sw128(uint32_t saddr) {
     return (uint64_t)((saddr >> 4) & 0x3FFF) | ((uint64_t)((KG * 1024) >> 4) << 16) | ((uint64_t)(512 >> 4) << 32) |
            (1ull << 46) | (1ull << 61);
+}
+// descriptor = {low word: start >> 4 | LBO >> 4 << 16, high word: SBO >> 4 | version 1 << 14 | layout type << 29}; the
+// issuing thread only ever adds 16-byte offsets to the low word (shared memory is < 256 KB: the 14-bit field never
+// overflows), which keeps the per-MMA instruction count of that single thread small -- it is what bounds these kernels
+__device__ __forceinline__ uint64_t mk64(uint32_t lo, uint32_t hi) {
+    uint64_t d;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(d) : "r"(lo), "r"(hi));
+    return d;
 }
 // kind::tf32, fp32 accumulate, A and B both MN-major (bits 15 / 16)
 __host__ __device__ constexpr uint32_t idesc_tf32_mn(int M, int N) {
@@ -85,7 +92,7 @@ __device__ __forceinline__ void named_sync_loaders() { asm volatile("bar.sync 1,
 // (fp32, round-to-nearest) to a master accumulator in the other half of TMEM (tcgen05.ld / add / tcgen05.st).
 __global__ void __launch_bounds__(NTHR, 1)
 wgrad_umma_kernel(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__ CUtensorMap tm_q, int64_t rows,
-                  int Nout, int Kin, int64_t rows_per_cta, float *__restrict__ part, int groups) {
+                  int Nout, int Kin, int64_t rows_per_cta, float *__restrict__ part, int groups, int CH) {
     extern __shared__ uint8_t smem_raw[];
     const uint32_t raw = ptx::smem_u32(smem_raw);
     uint8_t *sm = smem_raw + (((raw + 1023u) & ~1023u) - raw);
@@ -124,6 +131,9 @@ wgrad_umma_kernel(const __grid_constant__ CUtensorMap tm_p, const __grid_constan
     const int ld = Kin + 1;
     float *C = part + (size_t)blockIdx.x * Nout * ld;
     const int boxes_p = (G.colsP + 31) >> 5, boxes_q = (G.colsQ + 31) >> 5;
+    // chunk accumulators: columns 0.. (hi*hi), 128.. (lo*hi), 384.. (hi*lo) when NI <= 128, else one at 0; master at 256
+    const bool chains3 = NI <= 128;
+    const uint32_t acc1 = chains3 ? 128u : 0u, acc2 = chains3 ? 384u : 0u;
 
     if (warp == NLOAD / 32 + 1) {
         // ---------------------------------------------------------------- TMA producer (one lane)
@@ -132,39 +142,56 @@ wgrad_umma_kernel(const __grid_constant__ CUtensorMap tm_p, const __grid_constan
             ptx::tma_prefetch_desc(&tm_q);
         }
         // lane b issues box b of a slab (P boxes first), lane 0 arms the stage barrier before anyone issues
+        int stage = 0;
+        uint32_t ph = 1;   // parity of the previous use of this stage
         for (int slab = 0; slab < n_slabs; ++slab) {
-            const int stage = slab % NST;
             const uint32_t bar = bar_tma + 8 * stage, p_raw = s0 + stage * STAGE, q_raw = p_raw + 2 * P_IMG;
-            const int row = (int)(row_beg + (int64_t)slab * R);
+            const int row = (int)row_beg + slab * R;
             if (lane == 0) {
-                if (slab >= NST) ptx::mbar_wait(bar_free + 8 * stage, ((slab / NST) - 1) & 1);
+                if (slab >= NST) ptx::mbar_wait(bar_free + 8 * stage, ph);
                 ptx::mbar_arrive_expect_tx(bar, (uint32_t)(boxes_p + boxes_q) * (R * 128));
             }
             __syncwarp();
             if (lane < boxes_p) ptx::tma_load_2d(&tm_p, bar, p_raw + lane * (R * 128), lane * 32, row);
             else if (lane < boxes_p + boxes_q)
                 ptx::tma_load_2d(&tm_q, bar, q_raw + (lane - boxes_p) * (R * 128), (lane - boxes_p) * 32, row);
+            if (++stage == NST) { stage = 0; ph ^= 1u; }
         }
     } else if (warp == NLOAD / 32) {
         // ---------------------------------------------------------------- MMA issuer (one lane)
         if (lane == 0) {
             const uint32_t idesc = idesc_tf32_mn(128, NI);
+            const uint32_t hi_w = (512u >> 4) | (1u << 14) | (1u << 29);
+            const uint32_t lo0 = (s0 >> 4) | ((uint32_t)((KG * 1024) >> 4) << 16);
+            const uint32_t o_al = (uint32_t)P_IMG >> 4, o_bh = (uint32_t)(2 * P_IMG) >> 4, o_bl = (uint32_t)(2 * P_IMG + Q_IMG) >> 4;
+            const uint32_t st_step = (uint32_t)STAGE >> 4;
+            int stage = 0, in_chunk = 0;
+            uint32_t ph = 0, fl_ph = 0, lo_w = lo0;
             for (int slab = 0; slab < n_slabs; ++slab) {
-                const int stage = slab % NST, in_chunk = slab % CH;
-                if (in_chunk == 0 && slab > 0) ptx::mbar_wait(bar_flush, ((slab / CH) - 1) & 1);   // chunk acc was drained
-                ptx::mbar_wait(bar_full + 8 * stage, (slab / NST) & 1);
+                if (in_chunk == 0 && slab > 0) {   // chunk accumulators were drained
+                    ptx::mbar_wait(bar_flush, fl_ph);
+                    fl_ph ^= 1u;
+                }
+                ptx::mbar_wait(bar_full + 8 * stage, ph);
                 ptx::tc_fence_after();
-                const uint32_t a_hi = s0 + stage * STAGE, a_lo = a_hi + P_IMG, b_hi = a_hi + 2 * P_IMG, b_lo = b_hi + Q_IMG;
 #pragma unroll
                 for (int g = 0; g < KG; ++g) {
-                    const uint64_t bh = desc_mn_sw128(b_hi + g * 1024), bl = desc_mn_sw128(b_lo + g * 1024);
-                    const uint64_t ah = desc_mn_sw128(a_hi + g * 1024), al = desc_mn_sw128(a_lo + g * 1024);
-                    ptx::umma_tf32_ss(tmem, al, bh, idesc, (in_chunk | g) ? 1u : 0u);
-                    ptx::umma_tf32_ss(tmem, ah, bl, idesc, 1u);
-                    ptx::umma_tf32_ss(tmem, ah, bh, idesc, 1u);
+                    const uint32_t w = lo_w + 64u * g;
+                    const uint64_t ah = mk64(w, hi_w), al = mk64(w + o_al, hi_w), bh = mk64(w + o_bh, hi_w),
+                                   bl = mk64(w + o_bl, hi_w);
+                    // the three split terms go to separate accumulators when they fit (NI <= 128): the small terms
+                    // then do not suffer the truncation of being added to the large running sum
+                    const uint32_t first = (in_chunk | g) ? 1u : 0u;
+                    ptx::umma_tf32_ss(tmem + acc1, al, bh, idesc, first);
+                    ptx::umma_tf32_ss(tmem + acc2, ah, bl, idesc, chains3 ? first : 1u);
+                    ptx::umma_tf32_ss(tmem, ah, bh, idesc, chains3 ? first : 1u);
                 }
                 ptx::umma_commit(bar_free + 8 * stage);
-                if (in_chunk == CH - 1 || slab == n_slabs - 1) ptx::umma_commit(bar_chunk);
+                const bool last = in_chunk == CH - 1 || slab == n_slabs - 1;
+                if (last) ptx::umma_commit(bar_chunk);
+                in_chunk = last ? 0 : in_chunk + 1;
+                lo_w += st_step;
+                if (++stage == NST) { stage = 0; ph ^= 1u; lo_w = lo0; }
             }
         }
     } else {
@@ -196,11 +223,17 @@ wgrad_umma_kernel(const __grid_constant__ CUtensorMap tm_p, const __grid_constan
         const int W = (NLOAD / 32) / groups, gi = warp / W, wi = warp % W;
         const int ncw = NST < groups ? NST : groups;
         const int n_chunks = (n_slabs + CH - 1) / CH;
+        int cv_slab = 0, cv_stage = 0;
+        uint32_t cv_ph = 0;
         for (int chunk = 0; chunk < n_chunks; ++chunk) {
             const int s_end = (chunk + 1) * CH < n_slabs ? (chunk + 1) * CH : n_slabs;
             for (int slab = chunk * CH + gi; slab < s_end && gi < ncw; slab += ncw) {
-                const int stage = slab % NST;
-                ptx::mbar_wait(bar_tma + 8 * stage, (slab / NST) & 1);
+                while (cv_slab < slab) {   // advance (stage, phase) to this slab without dividing
+                    ++cv_slab;
+                    if (++cv_stage == NST) { cv_stage = 0; cv_ph ^= 1u; }
+                }
+                const int stage = cv_stage;
+                ptx::mbar_wait(bar_tma + 8 * stage, cv_ph);
                 uint8_t *sp = sm + stage * STAGE, *sq = sp + 2 * P_IMG;
 #pragma unroll 4
                 for (int r = wi; r < R; r += W) {
@@ -220,6 +253,15 @@ wgrad_umma_kernel(const __grid_constant__ CUtensorMap tm_p, const __grid_constan
                 ptx::tmem_ld_32x32b_x16(t_lane + cb * 16, a);
                 ptx::tmem_ld_32x32b_x16(t_lane + 256 + cb * 16, m);
                 ptx::tmem_ld_wait();
+                if (chains3) {
+                    uint32_t a1[16], a2[16];
+                    ptx::tmem_ld_32x32b_x16(t_lane + acc1 + cb * 16, a1);
+                    ptx::tmem_ld_32x32b_x16(t_lane + acc2 + cb * 16, a2);
+                    ptx::tmem_ld_wait();
+#pragma unroll
+                    for (int i = 0; i < 16; ++i)
+                        a[i] = __float_as_uint((__uint_as_float(a1[i]) + __uint_as_float(a2[i])) + __uint_as_float(a[i]));
+                }
 #pragma unroll
                 for (int i = 0; i < 16; ++i) m[i] = __float_as_uint(__uint_as_float(m[i]) + __uint_as_float(a[i]));
                 ptx::tmem_st_32x32b_x16(t_lane + 256 + cb * 16, m);
@@ -300,7 +342,7 @@ inline int make_slab_tmap(CUtensorMap *m, const float *ptr, uint64_t rows, uint6
 
 inline bool wgrad_umma_ok(int64_t rows, int Nout, int Kin) {
     return Nout >= 4 && Nout <= MAX_NOUT && Kin >= 4 && Kin <= MAX_KIN && (Nout & 3) == 0 && (Kin & 3) == 0 &&
-           rows >= 4096 && rows < (1ll << 31) && wg_geom(Nout, Kin).nst >= 2;
+           rows >= 2048 && rows < (1ll << 31) && wg_geom(Nout, Kin).nst >= 2;
 }
 inline int wgrad_umma_grid(int64_t rows, int64_t *rows_per_cta) {
     int64_t slabs = (rows + R - 1) / R;
@@ -320,10 +362,228 @@ inline int wgrad_umma_launch(const float *dY, const float *X, int64_t rows, int 
     LIPVQ_TRY(make_slab_tmap(&tm_x, X, (uint64_t)rows, (uint64_t)Kin, R));
     LIPVQ_CUDA_OK(cudaFuncSetAttribute(wgrad_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     ProfScope prof("wgrad_umma_kernel", st);
-    static const int groups = [] { const char *e = getenv("LIPVQ_WG_GROUPS"); int g = e ? atoi(e) : 2; return (g == 1 || g == 2 || g == 4 || g == 8) ? g : 2; }();
-    wgrad_umma_kernel<<<grid, NTHR, smem, st>>>(G.swap ? tm_x : tm_dy, G.swap ? tm_dy : tm_x, rows, Nout, Kin, per, part, groups);
+    // 2 converter groups of 4 warps, 16 slabs (256 rows) per accumulation chunk: measured best / 1e-6 accurate
+    wgrad_umma_kernel<<<grid, NTHR, smem, st>>>(G.swap ? tm_x : tm_dy, G.swap ? tm_dy : tm_x, rows, Nout, Kin, per, part, 2,
+                                                CH_DEFAULT);
     LIPVQ_LAUNCH_OK();
     *splits = grid;
+    return LIPVQ_OK;
+}
+
+
+// =====================================================================================================================
+//   dgrad_umma_kernel : dX[M, Kout] = scale * (dY[M, Nn] W[Nn, Kout]) (.) act'(dpre[M, Kout])      (autograd of a Linear
+//   followed by GELU / ReLU, v5:54-59 and backbone.py:17-32)
+//
+// W in its natural row-major layout IS the MN-major B operand (rows = reduction axis): its tf32 hi / lo images stay
+// resident in shared memory for the whole launch.  The A operand lives in TMEM (tcgen05.mma with A in tensor memory,
+// lane = row): 8 loader warps read 64 B of their own row per 32-column block straight from global memory into
+// registers (two blocks ahead), split into hi / lo and tcgen05.st them into a 4-slot ring of TMEM columns -- dY never
+// touches shared memory.  One lane of warp 16 issues the 3 MMAs per K = 8 step into one of two accumulators; 8
+// epilogue warps read the finished accumulator, apply the activation derivative and store dX while the next tile's
+// MMAs run into the other accumulator.   TMEM columns: acc0 0 | acc1 128 | A ring 256 + 64 * slot (hi 32 | lo 32).
+namespace dg {
+constexpr int TM = 128;
+constexpr int NLD = 256, NEP = 256, NT = NLD + NEP + 32;
+constexpr int SLOTS = 4;
+__host__ __device__ constexpr int nn_pad(int Nn) { return (Nn + 7) / 8 * 8; }
+__host__ __device__ constexpr int w_img_bytes(int Nn, int Kout) { return (Kout / 32) * nn_pad(Nn) * 128; }
+__host__ __device__ constexpr int smem_bytes(int Nn, int Kout) { return 2 * w_img_bytes(Nn, Kout) + 256 + 1024; }
+}  // namespace dg
+
+template <int DACT>
+__global__ void __launch_bounds__(dg::NT, 1)
+dgrad_umma_kernel(const float *__restrict__ dY, const float *__restrict__ W, const float *__restrict__ dpre,
+                  float *__restrict__ dX, int64_t M, int Nn, int Kout, const float *__restrict__ scale_dev) {
+    using namespace dg;
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t raw = ptx::smem_u32(smem_raw);
+    uint8_t *sm = smem_raw + (((raw + 1023u) & ~1023u) - raw);
+    const uint32_t s0 = ptx::smem_u32(sm);
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int NnP = nn_pad(Nn), IMG = w_img_bytes(Nn, Kout), KB = (Nn + 31) >> 5;
+    uint8_t *bars = sm + 2 * IMG;
+    const uint32_t bar_afull = ptx::smem_u32(bars), bar_afree = bar_afull + 8 * SLOTS, bar_cfull = bar_afree + 8 * SLOTS,
+                   bar_cfree = bar_cfull + 16;
+    volatile uint32_t *tmem_slot = reinterpret_cast<volatile uint32_t *>(bars + 8 * (2 * SLOTS + 4));
+
+    // W -> hi | lo operand images: 32-column blocks of NnP rows x 128 B, 32-byte chunks swizzled by (row & 3)
+    {
+        const int k4 = Kout >> 2;
+        for (int i = tid; i < NnP * k4; i += NT) {
+            const int k = i / k4, c = (i - k * k4) << 2, j = (c & 31) >> 2;
+            const float4 v = k < Nn ? __ldg(reinterpret_cast<const float4 *>(W + (size_t)k * Kout + c))
+                                    : make_float4(0.f, 0.f, 0.f, 0.f);
+            uint32_t h[4], l[4];
+            split_rna(v.x, h[0], l[0]); split_rna(v.y, h[1], l[1]);
+            split_rna(v.z, h[2], l[2]); split_rna(v.w, h[3], l[3]);
+            const int off = (c >> 5) * (NnP * 128) + (k << 7) + (((j >> 1) ^ (k & 3)) << 5) + ((j & 1) << 4);
+            *reinterpret_cast<uint4 *>(sm + off) = make_uint4(h[0], h[1], h[2], h[3]);
+            *reinterpret_cast<uint4 *>(sm + IMG + off) = make_uint4(l[0], l[1], l[2], l[3]);
+        }
+    }
+    if (tid == 0) {
+        for (int i = 0; i < SLOTS; ++i) {
+            ptx::mbar_init(bar_afull + 8 * i, NLD / 32);
+            ptx::mbar_init(bar_afree + 8 * i, 1);
+        }
+        for (int i = 0; i < 2; ++i) {
+            ptx::mbar_init(bar_cfull + 8 * i, 1);
+            ptx::mbar_init(bar_cfree + 8 * i, NEP / 32);
+        }
+        ptx::fence_barrier_init();
+    }
+    if (warp == 0) ptx::tmem_alloc<512>(ptx::smem_u32((const void *)tmem_slot));
+    ptx::fence_proxy_async();
+    ptx::tc_fence_before();
+    __syncthreads();
+    ptx::tc_fence_after();
+    const uint32_t tmem = *tmem_slot;
+
+    const int64_t n_tiles = (M + TM - 1) / TM;
+    const int my_tiles = blockIdx.x < n_tiles ? (int)((n_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x) : 0;
+
+    if (warp == (NLD + NEP) / 32) {
+        // ---------------------------------------------------------------- MMA issuer (one lane)
+        if (lane == 0) {
+            const uint32_t idesc = ptx::umma_idesc_tf32(TM, Kout) | (1u << 16);   // B is MN-major
+            // B descriptor: 32-column blocks NnP*128 B apart (LBO), the two 4-row atoms of a K = 8 step 512 B apart (SBO)
+            const uint32_t hi_w = (512u >> 4) | (1u << 14) | (1u << 29);
+            const uint32_t lo_h = (s0 >> 4) | ((uint32_t)((NnP * 128) >> 4) << 16), lo_l = lo_h + ((uint32_t)IMG >> 4);
+            const uint32_t kb_step = 256u, s_step = 64u;   // 32 rows / 8 rows of 128 B, in 16-byte units
+            int slot = 0;
+            uint32_t a_ph = 0;
+            for (int t = 0; t < my_tiles; ++t) {
+                const int buf = t & 1;
+                if (t >= 2) {
+                    ptx::mbar_wait(bar_cfree + 8 * buf, ((t >> 1) - 1) & 1);
+                    ptx::tc_fence_after();
+                }
+                const uint32_t acc = tmem + buf * 128;
+                int k_left = (Nn + 7) >> 3;      // K = 8 steps left in this tile
+                uint32_t kw = 0;                 // (k0 * 128) >> 4
+                for (int kb = 0; kb < KB; ++kb) {
+                    ptx::mbar_wait(bar_afull + 8 * slot, a_ph);
+                    ptx::tc_fence_after();
+                    const int ks = k_left < 4 ? k_left : 4;
+                    const uint32_t a0 = tmem + 256 + slot * 64;
+#pragma unroll
+                    for (int s = 0; s < 4; ++s)
+                        if (s < ks) {
+                            const uint64_t bh = mk64(lo_h + kw + s_step * s, hi_w), bl = mk64(lo_l + kw + s_step * s, hi_w);
+                            ptx::umma_tf32_ts(acc, a0 + 32 + 8 * s, bh, idesc, (kb | s) ? 1u : 0u);
+                            ptx::umma_tf32_ts(acc, a0 + 8 * s, bl, idesc, 1u);
+                            ptx::umma_tf32_ts(acc, a0 + 8 * s, bh, idesc, 1u);
+                        }
+                    ptx::umma_commit(bar_afree + 8 * slot);
+                    k_left -= 4;
+                    kw += kb_step;
+                    if (++slot == SLOTS) { slot = 0; a_ph ^= 1u; }
+                }
+                ptx::umma_commit(bar_cfull + 8 * buf);
+            }
+        }
+    } else if (warp < NLD / 32) {
+        // ---------------------------------------------------------------- A loaders: global -> registers -> TMEM
+        const int r = tid & 127, h = tid >> 7;
+        const uint32_t t_lane = tmem + ((uint32_t)((warp & 3) * 32) << 16);
+        const int total = my_tiles * KB;
+        auto load = [&](int b, float4(&v)[4]) {
+            const int t = b / KB, kb = b - t * KB;
+            const int64_t row = ((int64_t)blockIdx.x + (int64_t)t * gridDim.x) * TM + r;
+            const int c0 = kb * 32 + h * 16;
+            const bool live = b < total && row < M;
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+                v[i] = (live && c0 + 4 * i < Nn) ? __ldg(reinterpret_cast<const float4 *>(dY + row * Nn + c0 + 4 * i))
+                                                 : make_float4(0.f, 0.f, 0.f, 0.f);
+        };
+        auto step = [&](int b, float4(&v)[4]) {
+            const int slot = b % SLOTS;
+            if (b >= SLOTS) {
+                ptx::mbar_wait(bar_afree + 8 * slot, ((b / SLOTS) - 1) & 1);
+                ptx::tc_fence_after();
+            }
+            uint32_t hi[16], lo[16];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                split_rna(v[i].x, hi[4 * i], lo[4 * i]); split_rna(v[i].y, hi[4 * i + 1], lo[4 * i + 1]);
+                split_rna(v[i].z, hi[4 * i + 2], lo[4 * i + 2]); split_rna(v[i].w, hi[4 * i + 3], lo[4 * i + 3]);
+            }
+            ptx::tmem_st_32x32b_x16(t_lane + 256 + slot * 64 + h * 16, hi);
+            ptx::tmem_st_32x32b_x16(t_lane + 256 + slot * 64 + 32 + h * 16, lo);
+            load(b + 2, v);
+            ptx::tmem_st_wait();
+            ptx::tc_fence_before();
+            __syncwarp();
+            if (lane == 0) ptx::mbar_arrive(bar_afull + 8 * slot);
+        };
+        float4 v0[4], v1[4];
+        load(0, v0);
+        load(1, v1);
+        for (int b = 0; b < total; b += 2) {
+            step(b, v0);
+            if (b + 1 < total) step(b + 1, v1);
+        }
+    } else {
+        // ---------------------------------------------------------------- epilogue: acc -> act' -> dX
+        const int e = tid - NLD, r = e & 127, h = e >> 7;
+        const uint32_t t_lane = tmem + ((uint32_t)((warp & 3) * 32) << 16);
+        const float out_scale = scale_dev ? __ldg(scale_dev) : 1.f;
+        for (int t = 0; t < my_tiles; ++t) {
+            const int buf = t & 1;
+            const int64_t row = ((int64_t)blockIdx.x + (int64_t)t * gridDim.x) * TM + r;
+            ptx::mbar_wait(bar_cfull + 8 * buf, (t >> 1) & 1);
+            ptx::tc_fence_after();
+            for (int cb = h; cb < Kout / 16; cb += 2) {
+                uint32_t a[16];
+                ptx::tmem_ld_32x32b_x16(t_lane + buf * 128 + cb * 16, a);
+                ptx::tmem_ld_wait();
+                if (row < M) {
+                    float *dst = dX + row * Kout + cb * 16;
+                    const float *pre = dpre + row * Kout + cb * 16;
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        float4 o = make_float4(out_scale * __uint_as_float(a[4 * i]), out_scale * __uint_as_float(a[4 * i + 1]),
+                                               out_scale * __uint_as_float(a[4 * i + 2]), out_scale * __uint_as_float(a[4 * i + 3]));
+                        if (DACT == ACT_GELU) {
+                            const float4 p = __ldg(reinterpret_cast<const float4 *>(pre) + i);
+                            o.x *= gelu_grad_fast_f(p.x); o.y *= gelu_grad_fast_f(p.y);
+                            o.z *= gelu_grad_fast_f(p.z); o.w *= gelu_grad_fast_f(p.w);
+                        }
+                        if (DACT == ACT_RELU) {
+                            const float4 p = __ldg(reinterpret_cast<const float4 *>(pre) + i);
+                            o.x = p.x > 0.f ? o.x : 0.f; o.y = p.y > 0.f ? o.y : 0.f;
+                            o.z = p.z > 0.f ? o.z : 0.f; o.w = p.w > 0.f ? o.w : 0.f;
+                        }
+                        reinterpret_cast<float4 *>(dst)[i] = o;
+                    }
+                }
+            }
+            ptx::tc_fence_before();
+            __syncwarp();
+            if (lane == 0) ptx::mbar_arrive(bar_cfree + 8 * buf);
+        }
+    }
+    ptx::tc_fence_before();
+    __syncthreads();
+    if (warp == 0) ptx::tmem_dealloc<512>(tmem);
+}
+
+inline bool dgrad_umma_ok(int64_t M, int Nn, int Kout) {
+    return (Kout == 64 || Kout == 128) && Nn >= 8 && (Nn & 3) == 0 && M >= 2048 &&
+           dg::smem_bytes(Nn, Kout) <= 227 * 1024;
+}
+template <int DACT>
+inline int dgrad_umma_launch(const float *dY, const float *W, const float *dpre, float *dX, int64_t M, int Nn, int Kout,
+                             const float *scale_dev, cudaStream_t st) {
+    const int smem = dg::smem_bytes(Nn, Kout);
+    LIPVQ_CUDA_OK(cudaFuncSetAttribute(dgrad_umma_kernel<DACT>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    const int64_t tiles = (M + dg::TM - 1) / dg::TM;
+    const int grid = (int)(tiles < kNumSMs ? tiles : kNumSMs);
+    ProfScope prof("dgrad_umma_kernel", st);
+    dgrad_umma_kernel<DACT><<<grid, dg::NT, smem, st>>>(dY, W, dpre, dX, M, Nn, Kout, scale_dev);
+    LIPVQ_LAUNCH_OK();
     return LIPVQ_OK;
 }
 

@@ -93,6 +93,23 @@ __device__ __forceinline__ float gelu_fast_f(float x) {
     const float r = ex2_approx(q);
     return x * (x >= 0.f ? 1.0f - r : r);
 }
+// d/dx [x Phi(x)] = Phi(x) + x phi(x) with the same tail fit for Phi and phi(x) = 2^(-x^2 log2(e)/2) / sqrt(2 pi) on
+// the ex2 unit: absolute error < 1e-6 on a function of range [-0.13, 1.13]; 16 instructions against ~50 for the
+// erff / expf form (the backward's GELU epilogue is instruction-bound)
+__device__ __forceinline__ float gelu_grad_fast_f(float x) {
+    const float u = fminf(fabsf(x), 6.0f);
+    float q = 5.184764121e-06f;
+    q = fmaf(q, u, -2.271982345e-05f);
+    q = fmaf(q, u, -5.336819246e-04f);
+    q = fmaf(q, u, 7.583174311e-03f);
+    q = fmaf(q, u, -5.285591416e-02f);
+    q = fmaf(q, u, -4.590896734e-01f);
+    q = fmaf(q, u, -1.151119478e+00f);
+    q = fmaf(q, u, -9.999997251e-01f);
+    const float r = ex2_approx(q);
+    const float pdf = 0.39894228040143268f * ex2_approx(-0.72134752044448170f * x * x);
+    return fmaf(x, pdf, x >= 0.f ? 1.0f - r : r);
+}
 // 1 / (1 + 2^(-a log2 e)) with the approximate ex2 / rcp units: relative error < 1e-6 (ex2.approx 2^-22, the
 // rounding of a*log2e, rcp.approx 1 ulp); saturates to 0 / 1 like the reference for large |a|
 __device__ __forceinline__ float sigmoid_fast_f(float a) {

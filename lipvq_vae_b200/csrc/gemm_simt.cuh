@@ -449,6 +449,10 @@ inline int linear_bwd_input(const float *dY, const float *W, const float *dpre, 
                             float aux_alpha, const float *aux_scale_dev, cudaStream_t st,
                             const float *out_scale_dev = nullptr) {
     static const bool simt = [] { const char *e = getenv("LIPVQ_GEMM"); return e && !strcmp(e, "simt"); }();
+    static const bool legacy = [] { const char *e = getenv("LIPVQ_GEMM"); return e && !strcmp(e, "mma_sync"); }();
+    if (!simt && !legacy && !aux1 && bwd5::dgrad_umma_ok(M, N, K) && aligned16(dY) && aligned16(W) && aligned16(dX) &&
+        (DACT == ACT_NONE || aligned16(dpre)))
+        return bwd5::dgrad_umma_launch<DACT>(dY, W, dpre, dX, M, N, K, out_scale_dev, st);
     if (!simt && !aux1 && (K == 64 || K == 128) && (N & 3) == 0 && aligned16(dY) && aligned16(W) && aligned16(dX) &&
         (DACT == ACT_NONE || aligned16(dpre)) && (double)M * N * K >= 1.0e7) {
         const size_t smem = ((size_t)((N + DG_BK - 1) / DG_BK) * DG_BK * (K + 8) + (size_t)DG_ST * DG_BM * DG_ALD) * 4;

@@ -441,3 +441,43 @@ def test_classic_vqvae_vs_reference_golden(case, mode):
     assert torch.equal(z2, z_latent) and abs(loss2.item() - loss.item()) < 1e-6 * abs(loss.item())
     zq, qloss = m.quantize(torch.from_numpy(fw["z_e"]).cuda())
     assert abs(qloss.item() - 1.25 * fw["mse_q"]) < RTOL * 1.25 * fw["mse_q"]
+
+
+@pytest.mark.parametrize("M,Nout,Kin,masked", [(2049, 208, 128, False), (100003, 208, 128, False), (4136, 128, 64, True),
+                                               (655360, 128, 64, False), (30000, 64, 12, False), (2560, 256, 128, True),
+                                               (5000, 12, 128, False), (2048, 36, 64, True)])
+def test_linear_backward_tensor_kernels_vs_float64(M, Nout, Kin, masked):
+    """The tcgen05 backward kernels (csrc/bwd_umma.cuh: TMA-fed MN-major weight gradient with chunked accumulation,
+    TMEM-operand input gradient) through lipvq_linear_bwd, against float64 matmuls of the same operands: autograd of
+    nn.Linear (v5:54-59, backbone.py:17-32).  Ragged row counts, a 6.5-block reduction width (208), the ReLU mask, the
+    transposed-role case (Nout > 128) and BASELINE config 3's row count."""
+    from lipvq_vae_b200 import _native as N
+    lib = N.lib()
+    dev = torch.device("cuda:0")
+    g = torch.Generator(device="cpu").manual_seed(M + 7 * Nout + Kin)
+    dY = (torch.randn(M, Nout, generator=g) * 1e-4).to(dev)       # gradient-sized values
+    X = torch.randn(M, Kin, generator=g).to(dev)
+    W = (torch.randn(Nout, Kin, generator=g) / Kin ** 0.5).to(dev)
+    mask = torch.relu(torch.randn(M, Kin, generator=g)).to(dev) if masked else None
+    dX = torch.full((M, Kin), float("nan"), device=dev)
+    dW = torch.full((Nout, Kin), float("nan"), device=dev)
+    db = torch.full((Nout,), float("nan"), device=dev)
+    ws = torch.empty(lib.lipvq_linear_bwd_ws_bytes(M, Nout, Kin), dtype=torch.uint8, device=dev)
+    st = torch.cuda.current_stream().cuda_stream
+    N.check(lib.lipvq_linear_bwd(dY.data_ptr(), X.data_ptr(), W.data_ptr(), mask.data_ptr() if masked else None,
+                                 dX.data_ptr(), dW.data_ptr(), db.data_ptr(), M, Nout, Kin, ws.data_ptr(), ws.numel(), st),
+            "lipvq_linear_bwd")
+    torch.cuda.synchronize()
+    rW, rb, rX = dY.double().t() @ X.double(), dY.double().sum(0), dY.double() @ W.double()
+    if masked:
+        rX = rX * (mask > 0)
+    for name, got, ref in (("dW", dW, rW), ("db", db, rb), ("dX", dX, rX)):
+        err = ((got.double() - ref).abs().max() / ref.abs().max()).item()
+        assert err < 5e-6, (name, err)
+    # same call twice -> bit-identical results (fixed-order reduction over the per-CTA partials)
+    dW2 = torch.empty_like(dW)
+    N.check(lib.lipvq_linear_bwd(dY.data_ptr(), X.data_ptr(), W.data_ptr(), mask.data_ptr() if masked else None,
+                                 dX.data_ptr(), dW2.data_ptr(), db.data_ptr(), M, Nout, Kin, ws.data_ptr(), ws.numel(), st),
+            "lipvq_linear_bwd")
+    torch.cuda.synchronize()
+    assert torch.equal(dW, dW2)

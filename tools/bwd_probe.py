@@ -18,11 +18,13 @@ for (Nout, Kin, scale) in [(208, 128, 1.0), (64, 12, 1.0)] if os.environ.get('PR
         W = (torch.randn(Nout, Kin, generator=g) / Kin ** 0.5).to(dev)
         dX = torch.empty(M, Kin, device=dev); dW = torch.empty(Nout, Kin, device=dev); db = torch.empty(Nout, device=dev)
         ws = torch.empty(lib.lipvq_linear_bwd_ws_bytes(M, Nout, Kin), dtype=torch.uint8, device=dev)
+        mask = torch.relu(torch.randn(M, Kin, generator=g)).to(dev) if (Nout + Kin + M) % 2 else None
         def run(_i=0):
-            N.check(lib.lipvq_linear_bwd(dY.data_ptr(), X.data_ptr(), W.data_ptr(), None, dX.data_ptr(), dW.data_ptr(),
+            N.check(lib.lipvq_linear_bwd(dY.data_ptr(), X.data_ptr(), W.data_ptr(), mask.data_ptr() if mask is not None else None, dX.data_ptr(), dW.data_ptr(),
                                          db.data_ptr(), M, Nout, Kin, ws.data_ptr(), ws.numel(), st), "linear_bwd")
         run(); torch.cuda.synchronize()
         rW = dY.double().t() @ X.double(); rb = dY.double().sum(0); rX = dY.double() @ W.double()
+        if mask is not None: rX = rX * (mask > 0)
         def err(a, r): return ((a.double() - r).abs().max() / r.abs().max()).item()
         eW, eb, eX = err(dW, rW), err(db, rb), err(dX, rX)
         good = eW < 4e-6 and eb < 2e-6 and eX < 5e-6
