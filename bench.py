@@ -289,6 +289,26 @@ def run_ours(args, rank, world, local_rank):
              "n_gpus": world, "ms_per_step": ms_train, "chunks_per_s": world * CHUNKS / (ms_train / 1e3),
              "steps": tr_steps, "own_kernel_launches_per_step": train_launches,
              "allreduce_bytes": int(trainer.dp._bucket.flat.numel() * 4), "timing": "CUDA events, max over ranks"}
+    if rank == 0:
+        # per-kernel split of the training step (library CUDA events around each launch, after the timed region);
+        # the two backward GEMM families report against their rooflines: weight gradients 2*N*sum(Nout*Kin) flop as
+        # 3 tf32 MMAs per product, input gradients likewise; both also move every saved activation once
+        rep = N.profile_kernels(train_step, 3)
+        train["kernels_us_per_step"] = {k: 1e3 * v[1] / 3 for k, v in rep.items()}
+        Hh, H1h, D, F = H_DIM, 64, D_LAT, F_DIM
+        hbm_peak_for_train = _peaks()[0]["hbm_gbs"]
+        wg_flop = 2.0 * rows * (D * Hh + Hh * H1h + H1h * F)
+        dg_flop = 2.0 * rows * (D * Hh + Hh * H1h)
+        wg_bytes = 4.0 * rows * (D + Hh + Hh + H1h + H1h + F)
+        dg_bytes = 4.0 * rows * (D + 2 * Hh + Hh + 2 * H1h)
+        for kname, flop, byts in (("wgrad_umma_kernel", wg_flop, wg_bytes), ("dgrad_umma_kernel", dg_flop, dg_bytes)):
+            us = train["kernels_us_per_step"].get(kname)
+            if us:
+                train.setdefault("backward_rooflines", []).append({
+                    "kernel": kname, "us_per_step": us, "bound": "hbm", "achieved": byts / (us * 1e-6) / 1e9,
+                    "peak": hbm_peak_for_train, "unit": "GB/s", "frac": byts / (us * 1e-6) / 1e9 / hbm_peak_for_train,
+                    "tensor_tflops_fp32_equivalent": flop / (us * 1e-6) / 1e12,
+                    "algorithmic": "reads of dY and the saved activations + writes of the activation gradients, fp32, once each"})
     del trainer, m_tr
     # EMA variant of the same step (north_star item 3; extension, not in the reference): the codebook follows the EMA
     # of its clusters -- per-code counts/sums by the scatter-add kernel, all-reduced in one more collective
