@@ -289,11 +289,14 @@ def run_ours(args, rank, world, local_rank):
              "n_gpus": world, "ms_per_step": ms_train, "chunks_per_s": world * CHUNKS / (ms_train / 1e3),
              "steps": tr_steps, "own_kernel_launches_per_step": train_launches,
              "allreduce_bytes": int(trainer.dp._bucket.flat.numel() * 4), "timing": "CUDA events, max over ranks"}
+    # per-kernel split of the training step (library CUDA events around each launch, after the timed region).  EVERY
+    # rank runs these three steps -- each contains the gradient all-reduce -- and only rank 0 keeps the report.
+    rep = N.profile_kernels(train_step, 3)
+    torch.cuda.synchronize()
+    barrier()
     if rank == 0:
-        # per-kernel split of the training step (library CUDA events around each launch, after the timed region);
         # the two backward GEMM families report against their rooflines: weight gradients 2*N*sum(Nout*Kin) flop as
         # 3 tf32 MMAs per product, input gradients likewise; both also move every saved activation once
-        rep = N.profile_kernels(train_step, 3)
         train["kernels_us_per_step"] = {k: 1e3 * v[1] / 3 for k, v in rep.items()}
         Hh, H1h, D, F = H_DIM, 64, D_LAT, F_DIM
         hbm_peak_for_train = _peaks()[0]["hbm_gbs"]
