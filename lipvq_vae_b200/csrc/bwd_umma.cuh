@@ -3,11 +3,12 @@
 //   A*B ~= A_lo*B_hi + A_hi*B_lo + A_hi*B_hi   (hi = tf32-rounded value, lo = exact fp32 remainder)
 // so the gradients keep fp32 parity (1e-5) with the reference's autograd.
 //
-//   wgrad_umma_kernel : part[cta][Nout][Kin+1] = dY[rows_cta, Nout]^T [X[rows_cta, Kin] | 1]
+//   wgrad_umma_kernel : part[cta][Nout][Kin+1] = [ dY[rows_cta, Nout]^T X[rows_cta, Kin] | column sums of dY ]
+//   dgrad_umma_kernel : dX = scale * (dY W) (.) act'(pre)                       (second half of this file)
 //
 // The reduction axis of a weight gradient is the ROW axis, so both operands are "MN-major" for the tensor core:
 // a row-major [rows, cols] slab IS the canonical MN-major operand (rows of 32 fp32 = 128 B, swizzled in 32-byte
-// chunks, see desc_mn), no transposition anywhere -- TMA drops 16-row x 32-column boxes of dY and X straight
+// chunks, see desc_mn_sw128), no transposition anywhere -- TMA drops 16-row x 32-column boxes of dY and X straight
 // into operand position.  The tensor core reads only the upper 19 bits of an fp32 operand (measured: feeding raw
 // values and hi = rna(v) give the same 2e-6 error), so the raw image serves as the hi operand and only the lo
 // image (v - trunc_tf32(v)) is computed, by 8 converter warps, shared memory to shared memory.  Every CTA walks
@@ -45,7 +46,7 @@ __device__ __forceinline__ uint64_t desc_mn_sw128(uint32_t saddr) {
 }
 // descriptor = {low word: start >> 4 | LBO >> 4 << 16, high word: SBO >> 4 | version 1 << 14 | layout type << 29}; the
 // issuing thread only ever adds 16-byte offsets to the low word (shared memory is < 256 KB: the 14-bit field never
-// overflows), which keeps the per-MMA instruction count of that single thread small -- it is what bounds these kernels
+// overflows), which keeps the per-MMA instruction count of that single thread small
 __device__ __forceinline__ uint64_t mk64(uint32_t lo, uint32_t hi) {
     uint64_t d;
     asm("mov.b64 %0, {%1, %2};" : "=l"(d) : "r"(lo), "r"(hi));
