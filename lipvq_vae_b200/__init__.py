@@ -10,7 +10,8 @@ from .tokenizer import LLFQVAE_V4, LFQQuantizer, LipschitzMLP, install_into_robo
 from .vqvae_classic import VQVAE
 from .stream import HostTokenizer, bind_host_thread_to_gpu_node
 from .dist import DataParallelTokenizer, FlatAdamW, TokenizerTrainer, shard_rows
+from .cache import PromptTokenCache
 
 __all__ = ["LLFQVAE_V4", "VQVAE", "LFQQuantizer", "LipschitzMLP", "install_into_robomimic", "HostTokenizer", "bind_host_thread_to_gpu_node", "DataParallelTokenizer", "FlatAdamW", "TokenizerTrainer",
-           "shard_rows", "LipVQNativeError",
+           "shard_rows", "PromptTokenCache", "LipVQNativeError",
            "SEARCH_EXACT", "SEARCH_TENSOR", "build_native", "native_lib", "LIB_PATH"]
