@@ -107,8 +107,12 @@ __global__ void __launch_bounds__(QE_THR) quantize_emit_kernel(
     __shared__ float red[8];
     const int tid = threadIdx.x;
     const unsigned dq = VEC4 ? (unsigned)D >> 2 : (unsigned)D;
-    const unsigned magic = (unsigned)((0x100000000ull + dq - 1) / dq);   // i / dq == umulhi(i, magic), i < 2^32/dq
+    // i / dq == umulhi(i, magic) for i < 2^32/dq; a divisor of 1 would need magic = 2^32 (truncates to 0), so it is
+    // special-cased at the two call sites (latent_dim 1 or 4, feature_dim 1)
+    const unsigned magic = (unsigned)((0x100000000ull + dq - 1) / dq);
     const unsigned fmagic = (unsigned)((0x100000000ull + (unsigned)F - 1) / (unsigned)F);
+    auto div_dq = [&](unsigned i) { return dq == 1u ? i : __umulhi(i, magic); };
+    auto div_f = [&](unsigned i) { return F == 1 ? i : __umulhi(i, fmagic); };
     float sq = 0.f, sr = 0.f;
     const int64_t n_tiles = (n_rows + QE_ROWS - 1) / QE_ROWS;
     for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
@@ -130,7 +134,7 @@ __global__ void __launch_bounds__(QE_THR) quantize_emit_kernel(
                 for (int u = 0; u < 4; ++u) {
                     const unsigned i = i0 + u * QE_THR;
                     if (i < total) {
-                        const unsigned r = __umulhi(i, magic), c = i - r * dq;
+                        const unsigned r = div_dq(i), c = i - r * dq;
                         e[u] = __ldg(reinterpret_cast<const float4 *>(E + (size_t)sidx[r] * D) + c);
                         z[u] = __ldcs(zt + i);
                     }
@@ -154,7 +158,7 @@ __global__ void __launch_bounds__(QE_THR) quantize_emit_kernel(
             }
         } else {
             for (unsigned i = tid; i < total; i += QE_THR) {
-                const unsigned r = __umulhi(i, magic), c = i - r * dq;
+                const unsigned r = div_dq(i), c = i - r * dq;
                 const float e = __ldg(E + (size_t)sidx[r] * D + c);
                 const float zz = __ldcs(z_e + r0 * D + i);
                 const float dd = e - zz;
@@ -166,7 +170,7 @@ __global__ void __launch_bounds__(QE_THR) quantize_emit_kernel(
         if (R) {
             const unsigned tf = (unsigned)rows * (unsigned)F;
             for (unsigned i = tid; i < tf; i += QE_THR) {
-                const unsigned r = __umulhi(i, fmagic), f = i - r * (unsigned)F;
+                const unsigned r = div_f(i), f = i - r * (unsigned)F;
                 const float v = __ldg(R + (size_t)sidx[r] * F + f);
                 if (x_recon) x_recon[r0 * F + i] = v;
                 if (x) { const float dd = v - __ldg(x + r0 * F + i); sr = fmaf(dd, dd, sr); }

@@ -725,11 +725,8 @@ inline int launch_tc(const CUtensorMap &ta, const CUtensorMap &tb, const Geometr
                      cudaStream_t st) {
     using L = SmemLayout<NKB, A_BUFS, STAGES>;
     auto kern = vq_tc_kernel<NKB, A_BUFS, STAGES>;
-    static bool attr_done = false;
-    if (!attr_done) {
-        LIPVQ_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::TOTAL));
-        attr_done = true;
-    }
+    // (the attribute is per device and the call is cheap: set it on every launch, as set_smem in mlp_tc.cuh does)
+    LIPVQ_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::TOTAL));
     const int grid = (int)(g.n_tiles < kNumSMs ? g.n_tiles : kNumSMs);
     ProfScope prof("vq_tc_kernel", st);
     kern<<<grid, NT, L::TOTAL, st>>>(ta, tb, g.n, (int)g.n_tiles, g.nct, g.NK16, w.zn, w.emax,

@@ -13,6 +13,12 @@ import torch.distributed as dist
 CHUNK_LEN = 10  # rows per action chunk (obs_nets.py:1298)
 
 
+def _bump_param_epoch(model):
+    """Parameters were rewritten through raw pointers / ``.data`` (no autograd ``_version`` bump): tell the caches
+    that key on parameter identity (``cache.PromptTokenCache``) that their entries are stale."""
+    model._param_epoch = getattr(model, "_param_epoch", 0) + 1
+
+
 def shard_rows(n_total: int, rank: int, world: int, align: int = CHUNK_LEN):
     """Contiguous, chunk-aligned [start, stop) row range of ``rank``; the ranges tile [0, n_total)."""
     if world < 1 or not (0 <= rank < world):
@@ -68,6 +74,7 @@ class DataParallelTokenizer:
         if broadcast_params and self.world > 1:
             for p in model.parameters():
                 dist.broadcast(p.data, src=0, group=process_group)
+            _bump_param_epoch(model)
 
     # ------------------------------------------------------------------ forward
     def global_rows(self, n_local: int, device) -> int:
@@ -81,8 +88,12 @@ class DataParallelTokenizer:
         """forward on this rank's rows; ``n_total`` (global rows) skips the count all-reduce."""
         if n_total is None:
             n_total = self.global_rows(x_local.shape[0], x_local.device)
-        self.model.n_total_rows = n_total
-        return self.model(x_local)
+        prev = self.model.n_total_rows
+        self.model.n_total_rows = n_total            # only for the duration of this call (later direct calls of the
+        try:                                         # model must see their own row count again)
+            return self.model(x_local)
+        finally:
+            self.model.n_total_rows = prev
 
     # ------------------------------------------------------------------ collectives
     def _params(self):
@@ -126,6 +137,7 @@ class FlatAdamW:
     and ``lipvq_adamw_step`` updates everything at once from a flat gradient (the all-reduce bucket)."""
 
     def __init__(self, model, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=1e-4):
+        self.model = model
         self.params = [p for p in model.parameters()]
         dev = self.params[0].device
         self.numel = sum(p.numel() for p in self.params)
@@ -152,38 +164,87 @@ class FlatAdamW:
         N.check(N.lib().lipvq_adamw_step(self.flat.data_ptr(), flat_grad.data_ptr(), self.exp_avg.data_ptr(),
                                          self.exp_avg_sq.data_ptr(), self.numel, self.steps, self.lr, self.betas[0],
                                          self.betas[1], self.eps, self.weight_decay, st), "lipvq_adamw_step")
+        _bump_param_epoch(self.model)            # written through raw pointers: no autograd version bump
 
 
 class TokenizerTrainer:
     """One data-parallel training step of the tokenizer (BASELINE config 3): forward + backward on this rank's
-    rows, ONE all-reduce of the flat gradient bucket, ONE fused AdamW launch.  Mirrors what
-    ``ICLTransformer_GMM`` does with ``self.vq_vae_model`` each iteration (icl.py:913-914, 968-970)."""
+    rows, the gradient all-reduce, ONE fused AdamW launch.  Mirrors what ``ICLTransformer_GMM`` does with
+    ``self.vq_vae_model`` each iteration (icl.py:913-914, 968-970).
 
-    def __init__(self, model, process_group=None, lr=1e-3, weight_decay=1e-4, ema_codebook=False, ema_gamma=0.99):
+    The step calls the C ABI directly (``tokenizer.train_forward`` / ``train_backward_*``), no autograd graph: the
+    backward kernels write the 14 gradients straight into views of the flat all-reduce bucket (``p.grad`` ARE those
+    views), so nothing is packed or unpacked around the collective, and the collective is split in two so that it
+    overlaps the backward:
+      1. decoder backward -> struct fields 7..13 (codebook, decoder.*, to_output.*: 80 % of the bucket, one contiguous
+         slice) + the loss scalar are all-reduced on the communication stream while
+      2. the encoder backward (the N-row GEMMs, ~60 % of the step) runs; its slice (fields 0..6) follows.
+    ``overlap=False`` issues ONE all-reduce after the whole backward (the round-1 behaviour) for A/B timing."""
+
+    def __init__(self, model, process_group=None, lr=1e-3, weight_decay=1e-4, ema_codebook=False, ema_gamma=0.99,
+                 overlap=True):
         self.dp = DataParallelTokenizer(model, process_group)
         self.opt = FlatAdamW(model, lr=lr, weight_decay=weight_decay)
         self.model = model
+        self.overlap = overlap
         # EMA mode (extension, SURVEY 8a row 11): the codebook follows the EMA of its clusters instead of AdamW --
         # its gradient is zeroed in the bucket and counts[K] + sums[K,D] are all-reduced in one more collective
         self.ema_codebook, self.ema_gamma = ema_codebook, ema_gamma
-        self._cb_index = [i for i, p in enumerate(self.opt.params) if p is model.quantizer.codebook][0]
+        params = self.opt.params
+        self._cb_index = [i for i, p in enumerate(params) if p is model.quantizer.codebook][0]
+        if [id(p) for p in params] != [id(p) for p in model._param_list()]:
+            raise RuntimeError("parameter order differs from the C ABI's struct order")
+        # gradient bucket: 14 views in struct order + 1 float for the loss; the decoder-side slice starts at the codebook
+        self.bucket = FlatBucket([p.shape for p in params], params[0].device, extra=1)
+        self.dp._bucket = self.bucket
+        self._split = sum(self.bucket.sizes[:self._cb_index])
+        self._gs = torch.ones(1, dtype=torch.float32, device=params[0].device)      # dL/dloss = 1
+
+    def _all_reduce(self, t, async_op):
+        if self.dp.world > 1:
+            return dist.all_reduce(t, group=self.dp.pg, async_op=async_op)
+        return None
 
     def step(self, x_local, n_total=None):
-        for p in self.opt.params:
-            p.grad = None                       # optimizer.zero_grad(set_to_none=True), icl.py:913
-        z_latent, loss = self.dp(x_local, n_total)
-        loss.backward()
+        from . import tokenizer as T
+        m, b = self.model, self.bucket
+        if not x_local.is_cuda:
+            raise T.LipVQNativeError("TokenizerTrainer.step needs a CUDA batch: there is no CPU path")
+        x = x_local.detach().contiguous()
+        n = x.shape[0]
+        if n_total is None:
+            n_total = self.dp.global_rows(n, x.device)
+        if n == 0:
+            raise ValueError("every rank needs at least one row (shard_rows keeps shards non-empty for N >= world)")
+        params = [p.detach() for p in self.opt.params]
+        z_q, stats, idx, vq_stats, x_recon, saved = T.train_forward(x, max(int(n_total), 1), int(m.search_mode),
+                                                                   m._dims(), params)
+        m.last_z_e, m.last_indices, m.last_reconstruction = saved["z_e"], idx, x_recon
+        m.last_loss_terms, m.last_search_stats = stats, vq_stats
         if self.ema_codebook:
-            counts, sums = self.model.codebook_statistics()
+            counts, sums = m.codebook_statistics()
             self.dp.allreduce_codebook_stats(counts, sums)
-        loss_global = self.dp.allreduce_grads(loss)
-        if self.ema_codebook:
-            cb = self.model.quantizer.codebook
-            keep = cb.data.clone()                              # AdamW must not move (or decay) the codebook
-            self.dp._bucket.views[self._cb_index].zero_()
-            self.opt.step(self.dp._bucket.flat)
-            cb.data.copy_(keep)
-            self.model.ema_update(counts, sums, gamma=self.ema_gamma)
+        b.extra.copy_(stats[0:1])
+        T.train_backward_decoder(saved, self._gs, b.views)
+        w1 = self._all_reduce(b.flat[self._split:], True) if self.overlap else None     # codebook .. to_output + loss
+        T.train_backward_encoder(saved, self._gs, b.views)
+        if self.overlap:
+            w0 = self._all_reduce(b.flat[:self._split], True)
+            for w in (w1, w0):
+                if w is not None:
+                    w.wait()                      # stream-level wait: the host does not block
         else:
-            self.opt.step(self.dp._bucket.flat)
-        return z_latent, loss_global
+            self._all_reduce(b.flat, False)
+        for p, v in zip(self.opt.params, b.views):
+            p.grad = v                            # the reduced (global-mean) gradients, no copy
+        if self.ema_codebook:
+            cb = m.quantizer.codebook
+            keep = cb.data.clone()                              # AdamW must not move (or decay) the codebook
+            b.views[self._cb_index].zero_()
+            self.opt.step(b.flat)
+            cb.data.copy_(keep)
+            m.ema_update(counts, sums, gamma=self.ema_gamma)
+        else:
+            self.opt.step(b.flat)
+        _bump_param_epoch(m)
+        return z_q, b.extra[0]

@@ -67,6 +67,76 @@ def _contig(ts):
     return [t if t.is_contiguous() else t.contiguous() for t in ts]
 
 
+def _empty_acts(dev, n, dims, with_gpre=True):
+    """Activation tensors kept between a training forward and its backward (lipvq_acts_t)."""
+    f32 = dict(dtype=torch.float32, device=dev)
+    F_, H1, H, D, K = dims.F, dims.H1, dims.H, dims.D, dims.K
+    t = dict(a1=torch.empty(n, H1, **f32), h1=torch.empty(n, H1, **f32),
+             a2=torch.empty(n, H, **f32), h2=torch.empty(n, H, **f32),
+             scale=torch.empty(D, **f32), Wn=torch.empty(D, H, **f32), z_e=torch.empty(n, D, **f32),
+             # decoder activations are kept per CODE (z_q takes K distinct values), not per row
+             c1=torch.empty(K, H1, **f32), d1=torch.empty(K, H1, **f32),
+             c2=torch.empty(K, H, **f32), d2=torch.empty(K, H, **f32), xr_code=torch.empty(K, F_, **f32))
+    if with_gpre:
+        t["g_pre"] = torch.empty(n, D, **f32)   # commitment gradient through the sigmoid, written by the emit pass
+    return t
+
+
+def train_forward(x, n_total, search_mode, dims, params):
+    """Training-mode forward of LLFQVAE_V4.forward (v5:70-84) through the C ABI, every activation the backward
+    needs kept.  Returns ``(z_q, stats float[4], idx, vq_stats, x_recon, saved)``; ``saved`` feeds
+    ``train_backward_decoder`` / ``train_backward_encoder``.  No autograd involved (``_TokenizerFn`` and
+    ``dist.TokenizerTrainer`` are the two callers)."""
+    lib = N.lib()
+    dev = x.device
+    n = x.shape[0]
+    f32 = dict(dtype=torch.float32, device=dev)
+    st = _stream_ptr(dev)
+    ws = _workspace(dev, dims, n)
+    P = _param_struct(N.Params, params)
+    stats = torch.empty(4, **f32)
+    idx = torch.empty(n, dtype=torch.int64, device=dev)
+    z_q = torch.empty(n, dims.D, **f32)
+    vq_stats = torch.empty(4, dtype=torch.int32, device=dev)
+    x_recon = torch.empty(n, dims.F, **f32)
+    acts = _empty_acts(dev, n, dims)
+    sse = torch.empty(2, dtype=torch.float64, device=dev)
+    A = _acts_struct(idx=idx, z_q=z_q, x_recon=x_recon, **acts)
+    wsz = ws.numel()
+    N.check(lib.lipvq_encode_search_fwd(C.byref(dims), C.byref(P), _p(x), n, C.byref(A), search_mode,
+                                        _p(vq_stats), _p(ws), wsz, st), "lipvq_encode_search_fwd")
+    N.check(lib.lipvq_quantize_decode_fwd(C.byref(dims), C.byref(P), _p(x), n, n_total, C.byref(A), _p(sse),
+                                          _p(stats), _p(ws), wsz, st), "lipvq_quantize_decode_fwd")
+    saved = dict(x=x, params=list(params), idx=idx, z_q=z_q, dims=dims, n_total=n_total, **acts)
+    return z_q, stats, idx, vq_stats, x_recon, saved
+
+
+def _bwd_args(saved, grads):
+    dims, x = saved["dims"], saved["x"]
+    dev = x.device
+    n = x.shape[0]
+    ws = _workspace(dev, dims, n)
+    P = _param_struct(N.Params, saved["params"])
+    G = _param_struct(N.Grads, grads)
+    A = _acts_struct(**{k: saved[k] for k in N._ACT_FIELDS if k in saved})
+    return dims, x, n, ws, P, G, A, _stream_ptr(dev)
+
+
+def train_backward_decoder(saved, gs, grads):
+    """Gradients of the decoder / to_output parameters and the COMPLETE codebook gradient (struct fields 7..13 of
+    ``grads``, a list of 14 tensors in state_dict order, overwritten).  ``gs``: device float[1] = dL/dloss."""
+    dims, x, n, ws, P, G, A, st = _bwd_args(saved, grads)
+    N.check(N.lib().lipvq_decoder_bwd(C.byref(dims), C.byref(P), _p(x), n, saved["n_total"], _p(gs), C.byref(A),
+                                      C.byref(G), _p(ws), ws.numel(), st), "lipvq_decoder_bwd")
+
+
+def train_backward_encoder(saved, gs, grads):
+    """Gradients of encoder.* and to_latent.* (struct fields 0..6 of ``grads``)."""
+    dims, x, n, ws, P, G, A, st = _bwd_args(saved, grads)
+    N.check(N.lib().lipvq_encoder_bwd(C.byref(dims), C.byref(P), _p(x), n, saved["n_total"], _p(gs), C.byref(A),
+                                      C.byref(G), _p(ws), ws.numel(), st), "lipvq_encoder_bwd")
+
+
 class _TokenizerFn(torch.autograd.Function):
     """forward + backward of LLFQVAE_V4.forward (v5:70-84) through the C ABI.
 
@@ -82,79 +152,47 @@ class _TokenizerFn(torch.autograd.Function):
         n = x.shape[0]
         params = _contig(params)
         f32 = dict(dtype=torch.float32, device=dev)
-        F_, H1, H, D, K = dims.F, dims.H1, dims.H, dims.D, dims.K
-        st = _stream_ptr(dev)
-        ws = _workspace(dev, dims, n)
-        P = _param_struct(N.Params, params)
         need_grad = any(ctx.needs_input_grad[4:])
-        stats = torch.empty(4, **f32)
-        idx = torch.empty(n, dtype=torch.int64, device=dev)
-        z_q = torch.empty(n, D, **f32)
-        vq_stats = torch.empty(4, dtype=torch.int32, device=dev)
         if n == 0:
-            stats.zero_(); vq_stats.zero_()
-            x_recon = torch.empty(0, F_, **f32)
+            stats = torch.zeros(4, **f32)
+            vq_stats = torch.zeros(4, dtype=torch.int32, device=dev)
+            idx = torch.empty(0, dtype=torch.int64, device=dev)
+            z_q = torch.empty(0, dims.D, **f32)
+            x_recon = torch.empty(0, dims.F, **f32)
             ctx.mark_non_differentiable(z_q, idx, vq_stats, x_recon)
-            ctx.empty = True
+            ctx.saved = None
             return z_q, stats, idx, vq_stats, x_recon, None
-        ctx.empty = False
-        x_recon = torch.empty(n, F_, **f32)
         if not need_grad:
+            st = _stream_ptr(dev)
+            ws = _workspace(dev, dims, n)
+            P = _param_struct(N.Params, params)
+            stats = torch.empty(4, **f32)
+            idx = torch.empty(n, dtype=torch.int64, device=dev)
+            z_q = torch.empty(n, dims.D, **f32)
+            vq_stats = torch.empty(4, dtype=torch.int32, device=dev)
+            x_recon = torch.empty(n, dims.F, **f32)
             N.check(lib.lipvq_forward_fused(C.byref(dims), C.byref(P), _p(x), n, n_total, search_mode, _p(z_q),
                                             _p(idx), _p(x_recon), _p(stats), _p(vq_stats), _p(ws), ws.numel(), st),
                     "lipvq_forward_fused")
             ctx.mark_non_differentiable(z_q, idx, vq_stats, x_recon)
+            ctx.saved = None
             return z_q, stats, idx, vq_stats, x_recon, None
-        a1 = torch.empty(n, H1, **f32); h1 = torch.empty(n, H1, **f32)
-        a2 = torch.empty(n, H, **f32); h2 = torch.empty(n, H, **f32)
-        scale = torch.empty(D, **f32); Wn = torch.empty(D, H, **f32)
-        z_e = torch.empty(n, D, **f32)
-        # decoder activations are kept per CODE (z_q takes K distinct values), not per row
-        c1 = torch.empty(K, H1, **f32); d1 = torch.empty(K, H1, **f32)
-        c2 = torch.empty(K, H, **f32); d2 = torch.empty(K, H, **f32)
-        xr_code = torch.empty(K, F_, **f32)
-        sse = torch.empty(2, dtype=torch.float64, device=dev)
-        g_pre = torch.empty(n, D, **f32)     # commitment gradient through the sigmoid, written by the emit pass
-        A = _acts_struct(a1=a1, h1=h1, a2=a2, h2=h2, scale=scale, Wn=Wn, z_e=z_e, idx=idx, z_q=z_q,
-                         c1=c1, d1=d1, c2=c2, d2=d2, xr_code=xr_code, x_recon=x_recon, g_pre=g_pre)
-        wsz = ws.numel()
-        N.check(lib.lipvq_encode_search_fwd(C.byref(dims), C.byref(P), _p(x), n, C.byref(A), search_mode,
-                                            _p(vq_stats), _p(ws), wsz, st), "lipvq_encode_search_fwd")
-        N.check(lib.lipvq_quantize_decode_fwd(C.byref(dims), C.byref(P), _p(x), n, n_total, C.byref(A), _p(sse),
-                                              _p(stats), _p(ws), wsz, st), "lipvq_quantize_decode_fwd")
-        ctx.save_for_backward(x, *params, a1, h1, a2, h2, scale, Wn, z_e, idx, z_q, c1, d1, c2, d2, xr_code, g_pre)
-        ctx.dims = dims
-        ctx.n_total = n_total
-        ctx.mark_non_differentiable(z_q, idx, vq_stats, x_recon, z_e)
-        return z_q, stats, idx, vq_stats, x_recon, z_e
+        z_q, stats, idx, vq_stats, x_recon, saved = train_forward(x, n_total, search_mode, dims, params)
+        ctx.saved = saved           # plain tensors created here: nothing autograd needs to version-check
+        ctx.mark_non_differentiable(z_q, idx, vq_stats, x_recon, saved["z_e"])
+        return z_q, stats, idx, vq_stats, x_recon, saved["z_e"]
 
     @staticmethod
     def backward(ctx, g_zlat, g_stats, g_idx, g_vq, g_xr, g_ze=None):
         none4 = (None, None, None, None)
-        if ctx.empty or g_stats is None:
+        if ctx.saved is None or g_stats is None:
             return none4 + (None,) * 14
-        lib = N.lib()
-        saved = ctx.saved_tensors
-        x, params = saved[0], saved[1:15]
-        a1, h1, a2, h2, scale, Wn, z_e, idx, z_q, c1, d1, c2, d2, xr_code, g_pre = saved[15:]
-        dims = ctx.dims
-        dev = x.device
-        n = x.shape[0]
-        D, K = dims.D, dims.K
-        st = _stream_ptr(dev)
-        ws = _workspace(dev, dims, n)
-        wsz = ws.numel()
+        saved = ctx.saved
         # dL/dloss lives on the device; the kernels read it there (no host sync)
         gs = g_stats[0:1].contiguous().float()
-        grads = [torch.empty_like(p) for p in params]
-        P = _param_struct(N.Params, params)
-        G = _param_struct(N.Grads, grads)
-        A = _acts_struct(a1=a1, h1=h1, a2=a2, h2=h2, scale=scale, Wn=Wn, z_e=z_e, idx=idx, z_q=z_q,
-                         c1=c1, d1=d1, c2=c2, d2=d2, xr_code=xr_code, g_pre=g_pre)
-        N.check(lib.lipvq_decoder_bwd(C.byref(dims), C.byref(P), _p(x), n, ctx.n_total, _p(gs), C.byref(A),
-                                      C.byref(G), _p(ws), wsz, st), "lipvq_decoder_bwd")
-        N.check(lib.lipvq_encoder_bwd(C.byref(dims), C.byref(P), _p(x), n, ctx.n_total, _p(gs), C.byref(A),
-                                      C.byref(G), _p(ws), wsz, st), "lipvq_encoder_bwd")
+        grads = [torch.empty_like(p) for p in saved["params"]]
+        train_backward_decoder(saved, gs, grads)
+        train_backward_encoder(saved, gs, grads)
         out = [g if ctx.needs_input_grad[4 + i] else None for i, g in enumerate(grads)]
         return none4 + tuple(out)
 
@@ -297,6 +335,9 @@ class LLFQVAE_V4(nn.Module):
         # keeps the reference's "14 parameters, no buffers" surface (algo.py:323-337 serialises state_dict only)
         self.ema_cluster_size = None
         self.ema_cluster_sum = None
+        # bumped by every parameter update that bypasses autograd's version counters (FlatAdamW.step, ema_update,
+        # TokenizerTrainer.step, the data-parallel broadcast): PromptTokenCache keys on it
+        self._param_epoch = 0
 
     # ------------------------------------------------------------------ EMA codebook update (extension)
     @torch.no_grad()
@@ -330,6 +371,7 @@ class LLFQVAE_V4(nn.Module):
         N.check(N.lib().lipvq_ema_update(_p(E), _p(self.ema_cluster_size), _p(self.ema_cluster_sum), _p(counts.contiguous()),
                                          _p(sums.contiguous()), self.num_codes, self.latent_dim, float(gamma), float(eps),
                                          _p(ws), ws.numel(), _stream_ptr(E.device)), "lipvq_ema_update")
+        self._param_epoch += 1
 
     # ------------------------------------------------------------------ helpers
     def _dims(self):

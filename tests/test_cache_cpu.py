@@ -76,3 +76,41 @@ def test_lru_capacity_and_passthrough_with_grad():
     with torch.no_grad():
         c(xs[0])
     assert m.calls == before + 3
+
+
+def test_wrapper_is_state_dict_transparent():
+    """wrapping must not change the checkpoint keys (strict load/save at robomimic/algo/algo.py:323-337)."""
+    m = _CountingTokenizer()
+    c = PromptTokenCache(m)
+    assert list(c.state_dict().keys()) == list(m.state_dict().keys()) == ["lin.weight", "lin.bias"]
+    assert [id(p) for p in c.parameters()] == [id(p) for p in m.parameters()]
+    # as a registered submodule of a parent, the keys carry the parent's prefix only
+    parent = torch.nn.Module()
+    parent.action_network = c
+    ref_parent = torch.nn.Module()
+    ref_parent.action_network = _CountingTokenizer()
+    assert list(parent.state_dict().keys()) == list(ref_parent.state_dict().keys())
+    parent.load_state_dict(ref_parent.state_dict(), strict=True)
+    assert torch.equal(m.lin.weight, ref_parent.action_network.lin.weight)
+    ref_parent.load_state_dict(parent.state_dict(), strict=True)
+    # attributes of the wrapped tokenizer stay reachable through the wrapper
+    assert c.calls == m.calls and c.model is m
+
+
+def test_raw_pointer_update_invalidates_through_param_epoch():
+    """FlatAdamW / ema_update / TokenizerTrainer write parameters through raw pointers or ``.data`` --
+    no autograd version bump -- and advance ``model._param_epoch`` instead; the cache must miss afterwards."""
+    from lipvq_vae_b200.dist import _bump_param_epoch
+    m = _CountingTokenizer()
+    c = PromptTokenCache(m)
+    x = torch.randn(10, 12)
+    with torch.no_grad():
+        z0, _ = c(x)
+        c(x)
+        assert m.calls == 1
+        m.lin.weight.data.add_(1.0)          # what a raw-pointer kernel write looks like to autograd: nothing
+        versions_only = tuple((p.data_ptr(), p._version) for p in m.parameters())
+        assert versions_only == c._param_state[1:]
+        _bump_param_epoch(m)                  # what FlatAdamW.step / ema_update / TokenizerTrainer.step do
+        z1, _ = c(x)
+    assert m.calls == 2 and not torch.equal(z0, z1)
