@@ -25,7 +25,7 @@
 extern "C" {
 #endif
 
-#define LIPVQ_ABI_VERSION 5
+#define LIPVQ_ABI_VERSION 6
 
 enum {
     LIPVQ_OK = 0,
@@ -201,11 +201,23 @@ int lipvq_encoder_bwd(const lipvq_dims_t *dims, const lipvq_params_t *p, const f
 
 /* Whole forward in one call (inference / no-grad; LLFQVAE_V4.forward v5:70-84):
  * x -> z_latent[N,D], idx[N], x_recon[N,F] (nullable), loss_out float[4] (nullable).
- * Intermediates live in ws. */
+ * Intermediates live in ws.
+ * aux_stream / ev_fork / ev_join (all three or none; cudaStream_t / cudaEvent_t owned by the CALLER): when given, the
+ * parameter-only per-code decoder table is enqueued on aux_stream between ev_fork (recorded on `stream`) and ev_join
+ * (waited on by `stream` before the emit pass), so it runs beside the encoder and search kernels.  The library creates
+ * no stream and no event of its own: the call is re-entrant across streams and can be captured into a CUDA graph. */
 int lipvq_forward_fused(const lipvq_dims_t *dims, const lipvq_params_t *p, const float *x,
                         int64_t n_rows, int64_t n_total, int32_t search_mode, float *z_latent,
                         int64_t *idx, float *x_recon, float *loss_out, int32_t *stats, void *ws,
-                        size_t ws_bytes, void *stream);
+                        size_t ws_bytes, void *stream, void *aux_stream, void *ev_fork, void *ev_join);
+
+/* The same forward as ONE kernel launch (+ one memset node) for the reference's real call sizes, N = B*T = 80 / 500
+ * rows (v5:89-93; obs_nets.py:1298): exact fp32 on the CUDA cores, direct-form distances sum (z-e)^2, first minimal
+ * index on ties, deterministic loss reduction.  lipvq_forward_fused routes here by itself for n_rows <= 2048;
+ * this entry point accepts up to 65 536 rows.  ws: 8 B per row + 12 B per 4 rows + 1 KB. */
+int lipvq_forward_small(const lipvq_dims_t *dims, const lipvq_params_t *p, const float *x,
+                        int64_t n_rows, int64_t n_total, float *z_latent, int64_t *idx, float *x_recon,
+                        float *loss_out, int32_t *stats, void *ws, size_t ws_bytes, void *stream);
 
 /* AdamW step over one flat fp32 tensor (torch.optim.AdamW semantics as configured at
  * robomimic/algo/icl.py:886-889): decoupled weight decay, bias-corrected moments.

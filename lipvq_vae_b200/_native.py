@@ -121,7 +121,8 @@ SIGNATURES = {
     "lipvq_decoder_bwd": (C.c_int, [_DP, _PP, _VP, _I64, _I64, _VP, _AP, _GP, _VP, _SZ, _VP]),
     "lipvq_scatter_add": (C.c_int, [_VP, _VP, _I64, _I32, _I32, _VP, _VP, _VP]),
     "lipvq_encoder_bwd": (C.c_int, [_DP, _PP, _VP, _I64, _I64, _VP, _AP, _GP, _VP, _SZ, _VP]),
-    "lipvq_forward_fused": (C.c_int, [_DP, _PP, _VP, _I64, _I64, _I32, _VP, _VP, _VP, _VP, _VP, _VP, _SZ, _VP]),
+    "lipvq_forward_fused": (C.c_int, [_DP, _PP, _VP, _I64, _I64, _I32, _VP, _VP, _VP, _VP, _VP, _VP, _SZ, _VP, _VP, _VP, _VP]),
+    "lipvq_forward_small": (C.c_int, [_DP, _PP, _VP, _I64, _I64, _VP, _VP, _VP, _VP, _VP, _VP, _SZ, _VP]),
     "lipvq_adamw_step": (C.c_int, [_VP, _VP, _VP, _VP, _I64, _I64, _F32, _F32, _F32, _F32, _F32, _VP]),
     "lipvq_ema_update": (C.c_int, [_VP, _VP, _VP, _VP, _VP, _I32, _I32, _F32, _F32, _VP, _SZ, _VP]),
     "lipvq_linear_bwd_ws_bytes": (_SZ, [_I64, _I32, _I32]),
@@ -149,7 +150,7 @@ def lib():
                     fn = getattr(h, name)
                     fn.restype = res
                     fn.argtypes = args
-                if h.lipvq_abi_version() != 5:
+                if h.lipvq_abi_version() != 6:
                     raise LipVQNativeError("ABI version mismatch")
                 _lib = h
     return _lib

@@ -3,7 +3,6 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
-#include <pthread.h>
 
 #include "common.cuh"
 #include "gemm_simt.cuh"
@@ -13,6 +12,7 @@
 #include "mlp_enc16.cuh"
 #include "vq_exact.cuh"
 #include "vq_tensor.cuh"
+#include "small_fwd.cuh"
 
 namespace lipvq {
 thread_local cudaError_t g_last_cuda_error = cudaSuccess;
@@ -57,34 +57,6 @@ static bool use_mlp_tc(const lipvq_dims_t *d) {
     return !simt && mlp::supported(d);
 }
 
-// One low-priority helper stream per device for parameter-only work that is off the critical path (the per-code
-// decoder table of the fused forward): forked from / joined to the caller's stream with events, so the caller's
-// stream order is preserved and the work fills the SMs the persistent kernels leave idle at their tails.
-// LIPVQ_SIDE_STREAM=0 keeps everything on the caller's stream.
-static cudaStream_t side_stream() {
-    static const bool off = [] { const char *e = getenv("LIPVQ_SIDE_STREAM"); return e && !strcmp(e, "0"); }();
-    if (off) return nullptr;
-    static cudaStream_t streams[64] = {};
-    static bool tried[64] = {};
-    int dev = -1;
-    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
-    if (!__atomic_load_n(&tried[dev], __ATOMIC_ACQUIRE)) {
-        static pthread_mutex_t mu = PTHREAD_MUTEX_INITIALIZER;
-        pthread_mutex_lock(&mu);
-        if (!tried[dev]) {
-            int lo = 0, hi = 0;
-            cudaStream_t s = nullptr;
-            if (cudaDeviceGetStreamPriorityRange(&lo, &hi) != cudaSuccess ||
-                cudaStreamCreateWithPriority(&s, cudaStreamNonBlocking, lo) != cudaSuccess)
-                s = nullptr;
-            streams[dev] = s;
-            __atomic_store_n(&tried[dev], true, __ATOMIC_RELEASE);
-        }
-        pthread_mutex_unlock(&mu);
-    }
-    return streams[dev];
-}
-
 static size_t max_splitk_floats(const lipvq_dims_t *d, int64_t n) {
     size_t m = 0;
     auto up = [&](int Nout, int Kin) { size_t v = splitk_ws_floats(n, Nout, Kin); if (v > m) m = v; };
@@ -115,6 +87,7 @@ static size_t workspace_bytes_impl(const lipvq_dims_t *d, int64_t n) {
     bytes += N * sizeof(int64_t) + 4096;
     bytes += align_up(2 * kQeBlocks * sizeof(float), 256) + 1024;
     bytes += mlp::enc_scratch_bytes(d->D) + 2048;
+    bytes += small::scratch_bytes(n > 0 ? n : 1);
     return align_up(bytes, 256);
 }
 }  // namespace lipvq
@@ -618,12 +591,16 @@ int lipvq_encoder_bwd(const lipvq_dims_t *d, const lipvq_params_t *p, const floa
 int lipvq_forward_fused(const lipvq_dims_t *d, const lipvq_params_t *p, const float *x, int64_t n,
                         int64_t n_total, int32_t search_mode, float *z_latent, int64_t *idx,
                         float *x_recon, float *loss_out, int32_t *stats, void *ws, size_t ws_bytes,
-                        void *stream) {
+                        void *stream, void *aux_stream, void *ev_fork, void *ev_join) {
     if (!dims_ok(d) || n < 0 || n_total < n) return LIPVQ_ESHAPE;
     if (n == 0) return LIPVQ_OK;
     if (!p || !aligned16(x) || !aligned16(z_latent)) return LIPVQ_EALIGN;
     if (ws_bytes < workspace_bytes_impl(d, n) || !aligned16(ws)) return LIPVQ_EWORKSPACE;
     cudaStream_t st = (cudaStream_t)stream;
+    // the reference's real call sizes (80 / 500 rows, v5:89-93): one exact-fp32 kernel instead of 12 launches
+    static const bool no_small = [] { const char *e = getenv("LIPVQ_SMALL"); return e && !strcmp(e, "0"); }();
+    if (!no_small && idx && small::supported(d, n))
+        return small::launch(d, p, x, n, n_total, z_latent, idx, x_recon, loss_out, stats, ws, st);
     Bump b(ws, ws_bytes);
     lipvq_acts_t a;
     const bool tc = use_mlp_tc(d);   // tensor path keeps h1/a*/c*/d* on chip: only h2 and z_e touch HBM
@@ -647,29 +624,35 @@ int lipvq_forward_fused(const lipvq_dims_t *d, const lipvq_params_t *p, const fl
     // the rest of the workspace serves the encoder image + the search (checked against their own needs there)
     void *es_ws = (void *)align_up((size_t)(b.base + b.off), 256);
     const size_t es_bytes = ws_bytes - (size_t)((char *)es_ws - (char *)ws);
-    // the per-code decoder table depends on the parameters only: it runs on the helper stream (forked here, joined
-    // before the emit pass) beside the encoder / search kernels instead of between them
-    cudaStream_t side = side_stream();
-    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+    // The per-code decoder table depends on the parameters only.  With a caller-supplied helper stream and two
+    // events it runs beside the encoder / search kernels (forked here, joined before the emit pass) instead of
+    // between them; the library itself owns no stream and no event (re-entrant, graph-capturable).
+    cudaStream_t side = (cudaStream_t)aux_stream;
+    cudaEvent_t e_fork = (cudaEvent_t)ev_fork, e_join = (cudaEvent_t)ev_join;
     bool forked = false;
-    if (side && cudaEventCreateWithFlags(&ev_fork, cudaEventDisableTiming) == cudaSuccess &&
-        cudaEventCreateWithFlags(&ev_join, cudaEventDisableTiming) == cudaSuccess) {
+    if (side && e_fork && e_join) {
         float *R = (float *)align_up((size_t)part + align_up(2 * kQeBlocks * sizeof(float), 256), 256);   // qd scratch tail
-        int rc = LIPVQ_OK;
-        if (cudaEventRecord(ev_fork, st) == cudaSuccess && cudaStreamWaitEvent(side, ev_fork, 0) == cudaSuccess) {
-            rc = decoder_code_table(d, p, nullptr, nullptr, nullptr, nullptr, R, side);
-            if (rc == LIPVQ_OK && cudaEventRecord(ev_join, side) == cudaSuccess) {
-                forked = true;
-                a.xr_code = R;
-            }
-        }
+        LIPVQ_CUDA_OK(cudaEventRecord(e_fork, st));
+        LIPVQ_CUDA_OK(cudaStreamWaitEvent(side, e_fork, 0));
+        LIPVQ_TRY(decoder_code_table(d, p, nullptr, nullptr, nullptr, nullptr, R, side));
+        LIPVQ_CUDA_OK(cudaEventRecord(e_join, side));
+        forked = true;
+        a.xr_code = R;
     }
     int rc = lipvq_encode_search_fwd(d, p, x, n, &a, search_mode, stats, es_ws, es_bytes, stream);
-    if (forked && cudaStreamWaitEvent(st, ev_join, 0) != cudaSuccess && rc == LIPVQ_OK) rc = LIPVQ_ECUDA;
-    if (ev_fork) cudaEventDestroy(ev_fork);
-    if (ev_join) cudaEventDestroy(ev_join);
+    if (forked && cudaStreamWaitEvent(st, e_join, 0) != cudaSuccess && rc == LIPVQ_OK) rc = LIPVQ_ECUDA;   // always re-join
     LIPVQ_TRY(rc);
     return quantize_decode_impl(d, p, x, n, n_total, &a, sse, loss_out, part, part_bytes, stream, forked);
+}
+
+int lipvq_forward_small(const lipvq_dims_t *d, const lipvq_params_t *p, const float *x, int64_t n, int64_t n_total,
+                        float *z_latent, int64_t *idx, float *x_recon, float *loss_out, int32_t *stats, void *ws,
+                        size_t ws_bytes, void *stream) {
+    if (!dims_ok(d) || n < 0 || n_total < n || n > (1 << 16) || small::smem_bytes(d) > 200 * 1024) return LIPVQ_ESHAPE;
+    if (n == 0) return LIPVQ_OK;
+    if (!p || !aligned16(x) || !aligned16(z_latent) || !idx) return LIPVQ_EALIGN;
+    if (ws_bytes < small::scratch_bytes(n) || !aligned16(ws)) return LIPVQ_EWORKSPACE;
+    return small::launch(d, p, x, n, n_total, z_latent, idx, x_recon, loss_out, stats, ws, (cudaStream_t)stream);
 }
 
 int lipvq_adamw_step(float *param, const float *grad, float *exp_avg, float *exp_avg_sq, int64_t n,

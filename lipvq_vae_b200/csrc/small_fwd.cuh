@@ -1,0 +1,333 @@
+// small_fwd.cuh -- the WHOLE no-grad forward (v5:70-84) as ONE kernel for the reference's real call sizes
+// (N = B*T = 80 rows in the image config, 500 in the low-dim one: v5:89-93).  At these sizes the
+// 12-launch tensor path is pure launch latency; here a (splits x row-groups) grid does everything in exact fp32 on
+// the CUDA cores:
+//   every CTA of row group g recomputes the encoder for its 4 rows (143 KB of weights from L2, ~36 k MACs per row),
+//   scans ITS slice of the codebook in direct form sum (z - e)^2 (the reference's arithmetic, v5:41-45) with
+//   lane = code over shared-memory staged tiles, and publishes (distance, code) per row with one 64-bit atomicMax;
+//   the LAST CTA of the group to arrive (ticket counter) gathers z_q = E[idx], runs the decoder on its 4 rows and
+//   writes the group's two loss partials; the last GROUP sums the partials in group order (deterministic).
+// One launch + one memset node; no tensor cores (K-dims of 12/64/128 on 4 rows would idle them), no workspace
+// beyond (8 B per row + 12 B per group).
+#pragma once
+#include "common.cuh"
+
+namespace lipvq {
+namespace small {
+
+constexpr int SR = 4;            // rows per row group (CTA)
+constexpr int ST = 256;          // threads per CTA
+constexpr int SDC = 64;          // latent columns per staged codebook chunk
+constexpr int SPITCH = SDC + 4;  // padded pitch (floats): lane stride 17 float4 -> conflict-free 128-bit reads
+constexpr int MAX_ROWS = 2048;   // above this the tensor path wins
+
+// one layer for the CTA's SR rows: warp per output neuron (NJ in flight), lanes stride the reduction axis
+template <int ACT>
+__device__ __forceinline__ void rows_layer(const float *__restrict__ W, const float *__restrict__ bias, int n_out,
+                                           int k_in, const float *s_in /* [SR][k_in] */, float *s_out /* [SR][n_out] */,
+                                           float *__restrict__ g_out /* nullable [SR][n_out] global */, int rows_valid) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarp = ST / 32;
+    constexpr int NJ = 4;
+    for (int j0 = warp * NJ; j0 < n_out; j0 += nwarp * NJ) {
+        float acc[NJ][SR];
+#pragma unroll
+        for (int q = 0; q < NJ; ++q)
+#pragma unroll
+            for (int r = 0; r < SR; ++r) acc[q][r] = 0.f;
+        for (int k = lane; k < k_in; k += 32) {
+            float w[NJ];
+#pragma unroll
+            for (int q = 0; q < NJ; ++q) w[q] = j0 + q < n_out ? __ldg(W + (size_t)(j0 + q) * k_in + k) : 0.f;
+#pragma unroll
+            for (int r = 0; r < SR; ++r) {
+                const float a = s_in[r * k_in + k];
+#pragma unroll
+                for (int q = 0; q < NJ; ++q) acc[q][r] = fmaf(w[q], a, acc[q][r]);
+            }
+        }
+#pragma unroll
+        for (int q = 0; q < NJ; ++q) {
+            const int j = j0 + q;
+            if (j >= n_out) break;          // warp-uniform
+#pragma unroll
+            for (int r = 0; r < SR; ++r) acc[q][r] = warp_sum(acc[q][r]);
+            if (lane < SR) {
+                float v = 0.f;
+#pragma unroll
+                for (int r = 0; r < SR; ++r) v = lane == r ? acc[q][r] : v;
+                v = apply_act<ACT>(v + __ldg(bias + j));
+                s_out[lane * n_out + j] = v;
+                if (g_out && lane < rows_valid) g_out[(size_t)lane * n_out + j] = v;
+            }
+        }
+    }
+}
+
+// z = sigmoid(h (W * scale)^T + b) with scale_j = min(1, softplus(ci_j) / sum_k |W_jk|) computed in the same pass
+// over the row of W (v5:6-12, 22-24); the product W_jk * scale_j is rounded before the FMA, as in the reference
+__device__ __forceinline__ void lipschitz_rows_layer(const float *__restrict__ W, const float *__restrict__ bias,
+                                                     const float *__restrict__ ci, int n_out, int k_in,
+                                                     const float *s_in, float *s_out, int out_pitch) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarp = ST / 32;
+    for (int j = warp; j < n_out; j += nwarp) {
+        const float *wr = W + (size_t)j * k_in;
+        float s = 0.f;
+        for (int k = lane; k < k_in; k += 32) s += fabsf(__ldg(wr + k));
+        s = warp_sum(s);
+        const float sc = fminf(1.0f, softplus_f(__ldg(ci + j)) / s);
+        float acc[SR];
+#pragma unroll
+        for (int r = 0; r < SR; ++r) acc[r] = 0.f;
+        for (int k = lane; k < k_in; k += 32) {
+            const float w = __ldg(wr + k) * sc;
+#pragma unroll
+            for (int r = 0; r < SR; ++r) acc[r] = fmaf(w, s_in[r * k_in + k], acc[r]);
+        }
+#pragma unroll
+        for (int r = 0; r < SR; ++r) acc[r] = warp_sum(acc[r]);
+        if (lane < SR) {
+            float v = 0.f;
+#pragma unroll
+            for (int r = 0; r < SR; ++r) v = lane == r ? acc[r] : v;
+            s_out[lane * out_pitch + j] = sigmoid_f(v + __ldg(bias + j));
+        }
+    }
+}
+
+struct Scratch {
+    unsigned long long *best;   // [n_rows] ~((d2 bits << 32) | code), zero-initialised (= no candidate yet)
+    int *group_done;            // [G] arrival counters
+    int *groups_done;           // [1]
+    float *part;                // [G][2] {sse_q, sse_r}
+};
+inline size_t scratch_bytes(int64_t n) {
+    const int64_t G = (n + SR - 1) / SR;
+    return align_up((size_t)n * 8, 256) + align_up((size_t)(G + 1) * 4, 256) + align_up((size_t)G * 8, 256) + 256;
+}
+// everything that must start at zero comes first and is contiguous: best | counters
+inline Scratch carve(void *ws, int64_t n, size_t *zero_bytes) {
+    const int64_t G = (n + SR - 1) / SR;
+    char *b = (char *)align_up((size_t)ws, 256);
+    Scratch s;
+    s.best = (unsigned long long *)b;
+    b += align_up((size_t)n * 8, 256);
+    s.group_done = (int *)b;
+    s.groups_done = s.group_done + G;
+    b += align_up((size_t)(G + 1) * 4, 256);
+    *zero_bytes = (size_t)(b - (char *)s.best);
+    s.part = (float *)b;
+    return s;
+}
+
+__global__ void __launch_bounds__(ST) small_forward_kernel(
+    lipvq_params_t p, const float *__restrict__ x, int n_rows, int F, int H1, int H, int D, int K, int splits,
+    Scratch sc, float *__restrict__ z_latent, int64_t *__restrict__ idx_out, float *__restrict__ x_recon,
+    float *__restrict__ loss_out, double inv_nf, double inv_nd) {
+    extern __shared__ float sm[];
+    // [SR][F] x | [SR][H1] | [SR][H] | [SR][ZP] z_e (zero-padded to whole chunks) | [8 warps][32][SPITCH] codebook
+    // tiles (re-used as z_q + decoder activations by the finishing CTA)
+    const int ZP = (D + SDC - 1) / SDC * SDC;
+    float *s_x = sm, *s_h1 = s_x + SR * F, *s_h2 = s_h1 + SR * H1, *s_z = s_h2 + SR * H;
+    float *s_tile = s_z + SR * ZP;
+    __shared__ float red[ST / 32];
+    __shared__ int s_ticket;
+    __shared__ int s_idx[SR];
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int g = blockIdx.y, split = blockIdx.x;
+    const int r0 = g * SR;
+    const int rows_valid = min(SR, n_rows - r0);
+
+    for (int i = tid; i < SR * F; i += ST) {
+        const int r = i / F;
+        s_x[i] = r < rows_valid ? x[(size_t)r0 * F + i] : 0.f;
+    }
+    for (int i = tid; i < SR * ZP; i += ST) s_z[i] = 0.f;
+    __syncthreads();
+    rows_layer<ACT_GELU>(p.enc0_w, p.enc0_b, H1, F, s_x, s_h1, nullptr, 0);
+    __syncthreads();
+    rows_layer<ACT_GELU>(p.enc2_w, p.enc2_b, H, H1, s_h1, s_h2, nullptr, 0);
+    __syncthreads();
+    lipschitz_rows_layer(p.lat_W, p.lat_b, p.lat_ci, D, H, s_h2, s_z, ZP);
+    __syncthreads();
+
+    // ---- this CTA's slice of the codebook: codes [k_lo, k_hi), 32-code tiles dealt to the warps round-robin
+    {
+        const int per = ((K + splits - 1) / splits + 31) / 32 * 32;
+        const int k_lo = split * per, k_hi = min(K, k_lo + per);
+        const bool vec = (D & 3) == 0;
+        float *tile = s_tile + warp * 32 * SPITCH;
+        float bd[SR];
+        int bk[SR];
+#pragma unroll
+        for (int r = 0; r < SR; ++r) { bd[r] = INFINITY; bk[r] = 0x7fffffff; }
+        for (int t0 = k_lo + warp * 32; t0 < k_hi; t0 += (ST / 32) * 32) {
+            float acc[SR];
+#pragma unroll
+            for (int r = 0; r < SR; ++r) acc[r] = 0.f;
+            for (int d0 = 0; d0 < D; d0 += SDC) {
+                const int dc = min(SDC, D - d0);
+                // stage 32 codes x SDC columns (zero past the row / the slice): coalesced global reads, padded pitch
+                __syncwarp();
+                if (vec) {
+                    for (int i = lane; i < 32 * (SDC / 4); i += 32) {
+                        const int c = i / (SDC / 4), q = i - c * (SDC / 4);
+                        const int code = t0 + c;
+                        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+                        if (code < k_hi && 4 * q < dc)
+                            v = __ldg(reinterpret_cast<const float4 *>(p.codebook + (size_t)code * D + d0) + q);
+                        *reinterpret_cast<float4 *>(tile + c * SPITCH + 4 * q) = v;
+                    }
+                } else {
+                    for (int i = lane; i < 32 * SDC; i += 32) {
+                        const int c = i / SDC, d = i - c * SDC;
+                        const int code = t0 + c;
+                        tile[c * SPITCH + d] = (code < k_hi && d < dc) ? __ldg(p.codebook + (size_t)code * D + d0 + d) : 0.f;
+                    }
+                }
+                __syncwarp();
+                const float4 *tl = reinterpret_cast<const float4 *>(tile + lane * SPITCH);
+                const int nq = (dc + 3) >> 2;
+#pragma unroll 4
+                for (int q = 0; q < nq; ++q) {
+                    const float4 e = tl[q];
+#pragma unroll
+                    for (int r = 0; r < SR; ++r) {
+                        const float4 z = *reinterpret_cast<const float4 *>(s_z + r * ZP + d0 + 4 * q);   // broadcast
+                        const float a = z.x - e.x, b = z.y - e.y, c2 = z.z - e.z, d3 = z.w - e.w;
+                        acc[r] = fmaf(a, a, acc[r]);
+                        acc[r] = fmaf(b, b, acc[r]);
+                        acc[r] = fmaf(c2, c2, acc[r]);
+                        acc[r] = fmaf(d3, d3, acc[r]);
+                    }
+                }
+            }
+            const int code = t0 + lane;
+            if (code < k_hi) {
+#pragma unroll
+                for (int r = 0; r < SR; ++r)
+                    if (acc[r] < bd[r]) { bd[r] = acc[r]; bk[r] = code; }     // codes ascend per lane: first minimum wins
+            }
+        }
+        // warp argmin per row (lowest code on ties), then one 64-bit atomic per (warp, row)
+#pragma unroll
+        for (int r = 0; r < SR; ++r) {
+            float d = bd[r];
+            int k = bk[r];
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                const float od = __shfl_xor_sync(0xffffffffu, d, o);
+                const int ok = __shfl_xor_sync(0xffffffffu, k, o);
+                if (od < d || (od == d && ok < k)) { d = od; k = ok; }
+            }
+            if (lane == 0 && r < rows_valid && k != 0x7fffffff) {
+                const unsigned long long key = ((unsigned long long)__float_as_uint(d) << 32) | (unsigned)k;
+                atomicMax(sc.best + r0 + r, ~key);
+            }
+        }
+    }
+    // ---- the last CTA of the row group finishes the rows
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) s_ticket = atomicAdd(sc.group_done + g, 1);
+    __syncthreads();
+    if (s_ticket != splits - 1) return;
+    __threadfence();
+    if (tid < SR) {
+        int k = 0;
+        if (tid < rows_valid) {
+            const unsigned long long key = ~(*reinterpret_cast<volatile unsigned long long *>(sc.best + r0 + tid));
+            k = (int)(key & 0xffffffffu);
+            if (k < 0 || k >= K) k = 0;
+            idx_out[r0 + tid] = (int64_t)k;
+        }
+        s_idx[tid] = k;
+    }
+    __syncthreads();
+    float *s_q = s_tile, *s_c1 = s_q + SR * D, *s_c2 = s_c1 + SR * H1, *s_o = s_c2 + SR * H;
+    float sq = 0.f;
+    for (int i = tid; i < SR * D; i += ST) {
+        const int r = i / D, d = i - r * D;
+        const float e = __ldg(p.codebook + (size_t)s_idx[r] * D + d);
+        s_q[i] = e;
+        if (r < rows_valid) {
+            z_latent[(size_t)(r0 + r) * D + d] = e;
+            const float df = e - s_z[r * ZP + d];
+            sq = fmaf(df, df, sq);
+        }
+    }
+    __syncthreads();
+    rows_layer<ACT_GELU>(p.dec0_w, p.dec0_b, H1, D, s_q, s_c1, nullptr, 0);
+    __syncthreads();
+    rows_layer<ACT_GELU>(p.dec2_w, p.dec2_b, H, H1, s_c1, s_c2, nullptr, 0);
+    __syncthreads();
+    rows_layer<ACT_NONE>(p.out_w, p.out_b, F, H, s_c2, s_o, x_recon ? x_recon + (size_t)r0 * F : nullptr, rows_valid);
+    __syncthreads();
+    float sr = 0.f;
+    for (int i = tid; i < rows_valid * F; i += ST) {
+        const float df = s_o[i] - s_x[i];
+        sr = fmaf(df, df, sr);
+    }
+    sq = block_sum<ST>(sq, red);
+    sr = block_sum<ST>(sr, red);
+    if (tid == 0) {
+        sc.part[2 * g] = sq;
+        sc.part[2 * g + 1] = sr;
+        __threadfence();
+        s_ticket = atomicAdd(sc.groups_done, 1);
+    }
+    __syncthreads();
+    if (s_ticket != (int)gridDim.y - 1 || loss_out == nullptr) return;
+    __threadfence();
+    if (warp == 0) {       // every group's partials, in group order (lane-strided, fixed shuffle tree): deterministic
+        double a = 0.0, b = 0.0;
+        const volatile float *pp = sc.part;
+        for (int i = lane; i < (int)gridDim.y; i += 32) { a += (double)pp[2 * i]; b += (double)pp[2 * i + 1]; }
+        a = warp_sum_d(a);
+        b = warp_sum_d(b);
+        if (lane == 0) {
+            const double recon = b * inv_nf, commit = a * inv_nd;
+            loss_out[0] = (float)(recon + 0.25 * commit + 0.25 * commit);
+            loss_out[1] = (float)recon;
+            loss_out[2] = (float)commit;
+            loss_out[3] = (float)commit;
+        }
+    }
+}
+
+inline size_t smem_bytes(const lipvq_dims_t *d) {
+    const size_t head = (size_t)SR * (d->F + d->H1 + d->H + (d->D + SDC - 1) / SDC * SDC);
+    const size_t tiles = (size_t)(ST / 32) * 32 * SPITCH;
+    const size_t tail = (size_t)SR * (d->D + d->H1 + d->H + d->F);
+    return (head + (tiles > tail ? tiles : tail)) * sizeof(float);
+}
+inline bool supported(const lipvq_dims_t *d, int64_t n) {
+    return n >= 1 && n <= MAX_ROWS && smem_bytes(d) <= 200 * 1024;
+}
+
+inline int launch(const lipvq_dims_t *d, const lipvq_params_t *p, const float *x, int64_t n, int64_t n_total,
+                  float *z_latent, int64_t *idx, float *x_recon, float *loss_out, int32_t *stats, void *ws,
+                  cudaStream_t st) {
+    size_t zero_bytes = 0;
+    const Scratch sc = carve(ws, n, &zero_bytes);
+    LIPVQ_CUDA_OK(cudaMemsetAsync(sc.best, 0, zero_bytes, st));
+    if (stats) LIPVQ_CUDA_OK(cudaMemsetAsync(stats, 0, 4 * sizeof(int32_t), st));
+    const int G = (int)((n + SR - 1) / SR);
+    // enough CTAs to cover the chip about twice, at least 32 codes per split
+    int splits = (2 * kNumSMs + G - 1) / G;
+    if (splits > 64) splits = 64;
+    if (splits < 1) splits = 1;
+    const int per = ((d->K + splits - 1) / splits + 31) / 32 * 32;     // codes per split, whole 32-code tiles
+    splits = (d->K + per - 1) / per;                                   // (no empty slices)
+    const size_t smem = smem_bytes(d);
+    LIPVQ_CUDA_OK(cudaFuncSetAttribute(small_forward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const double nt = (double)(n_total > 0 ? n_total : 1);
+    ProfScope prof("small_forward_kernel", st);
+    small_forward_kernel<<<dim3(splits, G), ST, smem, st>>>(*p, x, (int)n, d->F, d->H1, d->H, d->D, d->K, splits, sc,
+                                                            z_latent, idx, x_recon, loss_out, 1.0 / (nt * d->F),
+                                                            1.0 / (nt * d->D));
+    LIPVQ_LAUNCH_OK();
+    return LIPVQ_OK;
+}
+
+}  // namespace small
+}  // namespace lipvq

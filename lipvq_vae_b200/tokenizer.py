@@ -20,6 +20,22 @@ from . import _native as N
 from ._native import LipVQNativeError
 
 _WS = {}  # (device index, stream) -> uint8 workspace tensor
+_AUX = {}  # device index -> (helper stream, fork event, join event) lent to lipvq_forward_fused
+AUX_MIN_ROWS = 16384   # below this the fork/join costs more than the 18 us decoder table it hides
+
+
+def _aux(dev):
+    """Helper stream + two events owned by THIS module (the C library owns none): the parameter-only decoder table of
+    a large no-grad forward runs on the helper stream beside the encoder / search kernels."""
+    a = _AUX.get(dev.index)
+    if a is None:
+        lo, _hi = 0, 0
+        s = torch.cuda.Stream(device=dev, priority=0)
+        ef, ej = torch.cuda.Event(), torch.cuda.Event()
+        with torch.cuda.device(dev):
+            ef.record(s); ej.record(s)             # materialise the cudaEvent_t handles
+        a = _AUX[dev.index] = (s, ef, ej)
+    return a
 
 
 def _stream_ptr(dev):
@@ -171,9 +187,13 @@ class _TokenizerFn(torch.autograd.Function):
             z_q = torch.empty(n, dims.D, **f32)
             vq_stats = torch.empty(4, dtype=torch.int32, device=dev)
             x_recon = torch.empty(n, dims.F, **f32)
+            aux = (None, None, None)
+            if n >= AUX_MIN_ROWS and not torch.cuda.is_current_stream_capturing():
+                s_aux, ef, ej = _aux(dev)
+                aux = (C.c_void_p(s_aux.cuda_stream), C.c_void_p(ef.cuda_event), C.c_void_p(ej.cuda_event))
             N.check(lib.lipvq_forward_fused(C.byref(dims), C.byref(P), _p(x), n, n_total, search_mode, _p(z_q),
-                                            _p(idx), _p(x_recon), _p(stats), _p(vq_stats), _p(ws), ws.numel(), st),
-                    "lipvq_forward_fused")
+                                            _p(idx), _p(x_recon), _p(stats), _p(vq_stats), _p(ws), ws.numel(), st,
+                                            *aux), "lipvq_forward_fused")
             ctx.mark_non_differentiable(z_q, idx, vq_stats, x_recon)
             ctx.saved = None
             return z_q, stats, idx, vq_stats, x_recon, None

@@ -27,7 +27,7 @@ def test_header_symbols_exported(native):
     for name in declared:
         assert hasattr(h, name), name
     h.lipvq_abi_version.restype = ctypes.c_int
-    assert h.lipvq_abi_version() == 5
+    assert h.lipvq_abi_version() == 6
     h.lipvq_strerror.restype = ctypes.c_char_p
     assert h.lipvq_strerror(-4) == b"workspace too small"
 

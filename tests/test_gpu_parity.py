@@ -392,9 +392,12 @@ def test_fused_paths_ragged_and_unaligned_shapes(n, D, K):
     loss.backward()
     torch.cuda.synchronize()
     idx = m.last_indices.cpu().numpy()
-    assert np.array_equal(idx, idx0) and torch.equal(z_lat, z_lat0)
+    # the no-grad call of <= 2048 rows runs the single-kernel exact path (csrc/small_fwd.cuh), the autograd call the
+    # tensor path: their encoders round differently (1e-6), so they may only disagree inside the near-tie window
+    mt = torch.from_numpy(must).cuda()
+    assert np.array_equal(idx[must], idx0[must]) and torch.equal(z_lat[mt], z_lat0[mt])
     assert np.array_equal(idx[must], fw["idx"][must])
-    if np.array_equal(idx, fw["idx"]):
+    if np.array_equal(idx, fw["idx"]) and np.array_equal(idx0, fw["idx"]):
         assert abs(loss.item() - fw["loss"]) < RTOL * abs(fw["loss"])
         assert abs(loss0.item() - fw["loss"]) < RTOL * abs(fw["loss"])
         assert orc.rel_err(z_lat.cpu().numpy(), fw["z_latent"]) < 1e-6

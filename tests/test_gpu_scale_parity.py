@@ -119,7 +119,8 @@ def test_tiny_dims_forward_backward(F, D, K, n):
         torch.cuda.synchronize()
         idx = m.last_indices.cpu().numpy()
         assert np.array_equal(idx[must], fw["idx"][must])
-        assert np.array_equal(z_lat.cpu().numpy(), p["quantizer.codebook"][idx]) and torch.equal(z0, z_lat)
+        mt = torch.from_numpy(must).cuda()       # (the no-grad call runs the single-kernel exact path)
+        assert np.array_equal(z_lat.cpu().numpy(), p["quantizer.codebook"][idx]) and torch.equal(z0[mt], z_lat[mt])
         if np.array_equal(idx, fw["idx"]):
             assert abs(loss.item() - fw["loss"]) < RTOL * abs(fw["loss"]) and abs(loss0.item() - fw["loss"]) < RTOL * abs(fw["loss"])
             assert orc.rel_err(m.last_reconstruction.cpu().numpy(), fw["x_recon"]) < RTOL
@@ -226,3 +227,82 @@ def test_two_gpu_trainer_replicas_identical_and_match_one_gpu(tmp_path, overlap)
     # Adam's step is +-lr wherever |g| sits at its own rounding noise: bound by the total possible movement, and
     # require fp32-rounding agreement on 99 % of the elements
     assert d.max() <= steps * 1e-3 * 1.01 and np.quantile(d, 0.99) < 2e-6, (d.max(), np.quantile(d, 0.99))
+
+
+# ----------------------------------------------------------------------------- the single-kernel small-N forward
+def _small_forward(p, x, n_total=None):
+    """lipvq_forward_small through the raw C ABI."""
+    import ctypes as C
+    from lipvq_vae_b200 import _native as N
+    F = p["encoder.0.weight"].shape[1]
+    K, D = p["quantizer.codebook"].shape
+    H = p["encoder.2.weight"].shape[0]
+    dims = N.Dims(F, 64, H, D, K)
+    dev = "cuda:0"
+    ts = [torch.from_numpy(p[k].copy()).to(dev) for k in N.PARAM_KEYS]
+    P = N.Params(*[t.data_ptr() for t in ts])
+    n = x.shape[0]
+    xt = torch.from_numpy(x).to(dev)
+    z = torch.empty(n, D, device=dev)
+    idx = torch.empty(n, dtype=torch.int64, device=dev)
+    xr = torch.empty(n, F, device=dev)
+    loss = torch.empty(4, device=dev)
+    stats = torch.empty(4, dtype=torch.int32, device=dev)
+    ws = torch.empty(16 * n + 65536, dtype=torch.uint8, device=dev)
+    st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    N.check(N.lib().lipvq_forward_small(C.byref(dims), C.byref(P), xt.data_ptr(), n, n_total or n, z.data_ptr(),
+                                        idx.data_ptr(), xr.data_ptr(), loss.data_ptr(), stats.data_ptr(), ws.data_ptr(),
+                                        ws.numel(), st), "lipvq_forward_small")
+    torch.cuda.synchronize()
+    return z.cpu().numpy(), idx.cpu().numpy(), xr.cpu().numpy(), loss.cpu().numpy().astype(np.float64)
+
+
+@pytest.mark.parametrize("case", ["small", "d787", "c1_spread", "c1_init"])
+def test_small_forward_kernel_vs_reference_golden(case):
+    """csrc/small_fwd.cuh against the vectors of the REAL reference module (tests/golden/model_*.npz)."""
+    from tests.golden.make_golden import case_inputs
+    p, x = case_inputs(case)
+    g = dict(np.load(os.path.join(os.path.dirname(__file__), "golden", "model_%s.npz" % case)))
+    z, idx, xr, loss = _small_forward(p, x)
+    fw = orc.forward(p, x)
+    _, d1, d2 = orc.exact_top2(fw["z_e"], p["quantizer.codebook"])
+    must = orc.index_parity_mask(d1, d2)
+    ref_idx = g["idx"].astype(np.int64)
+    assert np.array_equal(idx[must], ref_idx[must])
+    assert np.array_equal(z, p["quantizer.codebook"][idx])
+    if np.array_equal(idx, ref_idx):
+        assert abs(loss[0] - g["loss"]) < RTOL * abs(g["loss"]), (loss, g["loss"])
+        assert orc.rel_err(xr[:32], g["x_recon_head"]) < RTOL
+        assert abs(xr.astype(np.float64).sum() - g["x_recon_sum"]) < RTOL * g["x_recon_abs"]
+        assert abs(loss[1] - fw["recon_loss"]) < RTOL * fw["recon_loss"] and abs(loss[2] - fw["commit_loss"]) < RTOL * fw["commit_loss"]
+    # run-to-run determinism of the whole output, loss reduction included
+    z2, idx2, xr2, loss2 = _small_forward(p, x)
+    assert np.array_equal(idx, idx2) and np.array_equal(xr, xr2) and np.array_equal(loss, loss2)
+
+
+@pytest.mark.parametrize("n,F,D,K", [(1, 12, 208, 1024), (80, 12, 208, 1024), (500, 12, 208, 1024), (3, 12, 50, 33),
+                                     (257, 5, 7, 100), (2048, 12, 36, 64), (130, 1, 4, 16), (64, 12, 1, 8)])
+def test_small_forward_kernel_shapes_vs_oracle(n, F, D, K):
+    rng = np.random.default_rng(n + F + D + K)
+    p = orc.init_params(F, D, K, 128, seed=n + D)
+    p["to_latent.W"] = (0.08 * p["to_latent.W"]).astype(np.float32)
+    p["to_latent.ci"][::3] = 5.0
+    zc = orc.encode(p, (2.0 * rng.random((K, F)) - 1.0).astype(np.float32))
+    p["quantizer.codebook"] = (zc + 1e-3 * rng.standard_normal(zc.shape)).astype(np.float32)
+    x = (2.0 * rng.random((n, F)) - 1.0).astype(np.float32)
+    fw = orc.forward(p, x)
+    _, d1, d2 = orc.exact_top2(fw["z_e"], p["quantizer.codebook"])
+    must = orc.index_parity_mask(d1, d2) if K > 1 else np.ones(n, bool)
+    n_total = 3 * n                                     # a data-parallel shard: the loss carries 1/n_total
+    z, idx, xr, loss = _small_forward(p, x, n_total)
+    assert np.array_equal(idx[must], fw["idx"][must])
+    assert np.array_equal(z, p["quantizer.codebook"][idx])
+    if np.array_equal(idx, fw["idx"]):
+        assert orc.rel_err(xr, fw["x_recon"]) < RTOL
+        ref = fw["loss"] * n / n_total
+        assert abs(loss[0] - ref) < RTOL * abs(ref), (loss[0], ref)
+    # and the module routes no-grad calls of this size here: same tokens as the raw call
+    m = _model(p)
+    with torch.no_grad():
+        z_m, loss_m = m(torch.from_numpy(x).cuda())
+    assert np.array_equal(m.last_indices.cpu().numpy(), idx) and np.array_equal(z_m.cpu().numpy(), z)
