@@ -132,12 +132,19 @@ def run_reference_arm(args, rank, world):
     val = sample_chunks / (ms / 1e3)
     sample = ("%d chunks (%d rows) per step, numpy port of the reference's broadcast-form forward "
               "(v5:37-48 literally), %d threads over row blocks" % (sample_chunks, rows, cores))
+    # what the reference's own entry point does: torch.set_num_threads(1) (robomimic/scripts/train.py:57)
+    t1 = min(cpu_reference_sample(rows, 1) for _ in range(2))
     _emit({
         "impl": "reference", "metric": "action chunks tokenized/sec (encode+quantize+decode)", "value": val,
         "unit": "chunks/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "sample": sample},
-        "cpu_baseline": {"value": val, "unit": "chunks/s", "cores": cores, "kind": "port", "sample": sample},
+        "config": {"workload": WORKLOAD + " -- CPU arm: numpy PORT of the reference forward timed on a %d-chunk SAMPLE "
+                               "of that batch and extrapolated per chunk (rows are independent); the reference itself "
+                               "is a Python/torch module that cannot travel to this box" % sample_chunks,
+                   "sample": sample},
+        "cpu_baseline": {"value": val, "unit": "chunks/s", "cores": cores, "kind": "port", "sample": sample,
+                         "one_thread_value": sample_chunks / t1,
+                         "one_thread_note": "1 thread, as robomimic/scripts/train.py:57 pins torch"},
         "e2e": {"value": val, "unit": "chunks/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     })
 
@@ -313,6 +320,24 @@ def run_ours(args, rank, world, local_rank):
                     "tensor_tflops_fp32_equivalent": flop / (us * 1e-6) / 1e12,
                     "algorithmic": "reads of dY and the saved activations + writes of the activation gradients, fp32, once each"})
     del trainer, m_tr
+    if world > 1:
+        # A/B of the collective: the round-1 schedule (ONE all-reduce after the whole backward) against the split,
+        # overlapped one above -- the difference is what the overlap hides
+        m_tr = copy.deepcopy(m).train()
+        trainer = TokenizerTrainer(m_tr, overlap=False)
+        for i in range(2):
+            train_step(i)
+        torch.cuda.synchronize()
+        barrier()
+        ms_serial = _time_events(train_step, tr_steps, torch)
+        barrier()
+        t = torch.tensor([ms_serial], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        train["ms_per_step_one_allreduce_after_backward"] = float(t.item())
+        del trainer, m_tr
+    train["collective"] = ("2 NCCL all-reduces per step: [codebook .. to_output grads + loss] issued after the decoder "
+                           "backward, under the encoder backward; [encoder + to_latent grads] after it; gradients are "
+                           "written by the kernels straight into the flat bucket (no pack/unpack copies)")
     # EMA variant of the same step (north_star item 3; extension, not in the reference): the codebook follows the EMA
     # of its clusters -- per-code counts/sums by the scatter-add kernel, all-reduced in one more collective
     m_tr = copy.deepcopy(m).train()
@@ -331,9 +356,18 @@ def run_ours(args, rank, world, local_rank):
                                      "extra": "scatter-add of z_e per code + all-reduce of counts[K], sums[K,D] + "
                                               "lipvq_ema_update (parity unpinned: no reference counterpart)"}
     del trainer, m_tr
+    torch.cuda.empty_cache()
+    skip = set(filter(None, args.skip.split(",")))
+    # ---- BASELINE configs 4 and 5 run on EVERY rank (weak scaling, max over ranks inside the legs)
+    c4 = None if "config4" in skip else _guard(config4_leg, torch, N, lib, dev, rank, world, peaks, args.steps)
+    torch.cuda.empty_cache()
+    c5 = None if "config5" in skip else _guard(config5_leg, torch, dev, rank, world, args.steps)
+    torch.cuda.empty_cache()
 
     if rank != 0:
         return
+    parity = None if "parity" in skip else parity_leg(torch, m, p, xs[0])      # raises SystemExit on a mismatch
+    latency = None if "latency" in skip else _guard(latency_leg, torch, N, dev, p)
     # ---- per-kernel durations INSIDE the step: the library brackets each of its launches with CUDA events on
     #      the launching stream (lipvq_profile_begin/end); same workload, same rotating inputs
     prof_iters = max(5, args.steps)
@@ -356,7 +390,7 @@ def run_ours(args, rank, world, local_rank):
               "2*K*D flop/row = %d (fp16 operands, fp32 accumulate; SURVEY 8d)" % FLOP_PER_ROW_SEARCH),
         # the encoder's binding roof at the optimum is HBM: its stores (z_e + the search operand) take 133 us at the
         # measured copy bandwidth, its 3-term fp16 split products 98 us at the measured tensor rate
-        _roof("enc_fused_kernel", "hbm", rows * (F_DIM * 4.0 + D_LAT * 4 + ZB_BYTES), peaks["hbm_gbs"], "GB/s",
+        _roof("enc16_fused_kernel", "hbm", rows * (F_DIM * 4.0 + D_LAT * 4 + ZB_BYTES), peaks["hbm_gbs"], "GB/s",
               "read x (F*4 B) + write z_e (D*4 B) + write the search's fp16 row operand (%d B) per row; its GEMMs are "
               "71168 fp32-equivalent flop/row run as 3 kind::f16 MMAs per product (tensor floor 98 us < HBM floor "
               "133 us), see `tensor_tflops_fp32_equivalent`" % ZB_BYTES),
@@ -376,7 +410,7 @@ def run_ours(args, rank, world, local_rank):
         r["peak_source"] = peak_src + (" bf16 sustained (kernel timed inside the step)" if r["bound"] == "tensor"
                                        else " HBM copy bandwidth")
     for r in rooflines:
-        if r["kernel"] == "enc_fused_kernel":
+        if r["kernel"] == "enc16_fused_kernel":
             r["tensor_tflops_fp32_equivalent"] = rows * 2.0 * (F_DIM * 64 + 64 * H_DIM + H_DIM * D_LAT) / (
                 r["us_per_launch"] * 1e-6) / 1e12
             r["peak_source"] = peak_src + " HBM copy bandwidth"
@@ -467,7 +501,8 @@ def run_ours(args, rank, world, local_rank):
                          % (NBUF, NBUF * rows * F_DIM * 4 / 1e6, rows * (2 * D_LAT * 4 + 512 + 8 + F_DIM * 4) / 1e9)},
         "e2e": {"value": e2e, "unit": "chunks/s", "ms_per_step": ms_e2e,
                 "h2d_bytes_per_step": rows * F_DIM * 4, "d2h_bytes_per_step": rows * 8 + 16,
-                "api": "HostTokenizer.submit(pinned host batch) / collect(): per step one H2D of the batch, "
+                "api": "z_latent stays on the device (its consumer, the policy embedding, is there: obs_nets.py:1336, 2582); "
+                       "HostTokenizer.submit(pinned host batch) / collect(): per step one H2D of the batch, "
                        "LLFQVAE_V4.forward, one D2H of token indices + loss terms; uploads/downloads of neighbouring "
                        "steps overlap the kernels (%d slots)" % DEPTH,
                 "host_numa_binding": ("rank bound to %d CPUs local to its GPU" % len(numa_cpus)) if numa_cpus else "none",
@@ -476,8 +511,247 @@ def run_ours(args, rank, world, local_rank):
         "gpu_launches": int(launches), "clocks": clk, "roofline": roofline, "rooflines": rooflines,
         "kernels_us_per_step": kern_us, "cpu_baseline": cpu_baseline,
         "config2_vq_alone": c2, "hbm_kernel": hbm, "train_step": train,
+        "parity": parity, "parity_checked_rows": parity["parity_checked_rows"] if parity else 0,
+        "latency_us": latency, "config4_sweep": c4, "config5_icrt": c5,
     }
     _emit(out)
+
+
+# ------------------------------------------------------------------------------------------ extra legs
+def _guard(fn, *a, **k):
+    """An extra leg must never cost the headline line: report its error instead."""
+    try:
+        return fn(*a, **k)
+    except Exception as e:           # noqa: BLE001
+        return {"error": "%s: %s" % (type(e).__name__, str(e)[:300])}
+
+
+def spread_params(seed=11):
+    """Weights with index diversity (random init collapses every row onto one code): a milder Lipschitz
+    layer with both ``min`` branches in use and a codebook sampled from the encoder's own outputs."""
+    import numpy as np
+    from oracle import lipvq_oracle as orc        # input generator + checker only
+    rng = np.random.default_rng(seed)
+    p = orc.init_params(F_DIM, D_LAT, K_CODES, H_DIM, seed=seed)
+    p["to_latent.W"] = (0.08 * p["to_latent.W"]).astype(np.float32)
+    p["to_latent.ci"][::3] = 5.0
+    z = orc.encode(p, (2.0 * rng.random((K_CODES, F_DIM)) - 1.0).astype(np.float32))
+    p["quantizer.codebook"] = (z + 1e-3 * rng.standard_normal(z.shape)).astype(np.float32)
+    return p
+
+
+def parity_leg(torch, m, p, x_dev, slice_rows=16384):
+    """Check outputs of the TIMED forward against the oracle before anything is printed: indices
+    of the first `slice_rows` rows of the timed batch bit-exact outside the 1e-5 gap window, z_latent the gathered
+    codeword, and -- on a forward of the slice alone -- reconstruction and the loss terms within 1e-5.  Run twice:
+    the timed (reference-init, collapsed) weights and spread weights."""
+    import numpy as np
+    from oracle import lipvq_oracle as orc
+    from lipvq_vae_b200 import LLFQVAE_V4
+    out = {"rule": "idx bit-exact where the float64 top-2 distance gap > 1e-5 relative; z_latent == E[idx]; "
+                   "x_recon, loss terms within 1e-5 (oracle.exact_top2 / oracle.decode on the same rows)"}
+    total = 0
+    for name, params in (("timed_weights", p), ("spread_weights", spread_params())):
+        mm = m
+        if name != "timed_weights":
+            mm = LLFQVAE_V4(F_DIM, D_LAT, num_codes=K_CODES, hidden_dim=H_DIM).to(x_dev.device)
+            mm.load_state_dict({k: torch.from_numpy(v.copy()) for k, v in params.items()})
+            mm.search_mode = m.search_mode
+        with torch.no_grad():
+            z_full, _ = mm(x_dev)                                   # the timed call, whole batch
+            idx_full = mm.last_indices[:slice_rows].cpu().numpy()
+            z_head = z_full[:slice_rows].cpu().numpy()
+            xs_dev = x_dev[:slice_rows].contiguous()
+            _, loss_s = mm(xs_dev)                                  # the slice alone (its own loss terms)
+            idx_s = mm.last_indices.cpu().numpy()
+            terms = mm.last_loss_terms.cpu().numpy().astype(np.float64)
+            xr = mm.last_reconstruction.cpu().numpy()
+        xs = xs_dev.cpu().numpy()
+        E = params["quantizer.codebook"]
+        z_e = orc.encode(params, xs)
+        ref_idx, d1, d2 = orc.exact_top2(z_e, E)
+        must = orc.index_parity_mask(d1, d2)
+        ok_idx = bool(np.array_equal(idx_full[must], ref_idx[must]) and np.array_equal(idx_s[must], ref_idx[must]))
+        ok_z = bool(np.array_equal(z_head, E[idx_full]))
+        xr_code = orc.decode(params, E)
+        recon = float(np.sum((xr_code[idx_s].astype(np.float64) - xs) ** 2)) / (slice_rows * F_DIM)
+        commit = float(np.sum((E[idx_s].astype(np.float64) - z_e) ** 2)) / (slice_rows * D_LAT)
+        ref_loss = recon + 0.5 * commit
+        err_loss = abs(float(loss_s) - ref_loss) / abs(ref_loss)
+        err_xr = float(orc.rel_err(xr, xr_code[idx_s]))
+        ok = ok_idx and ok_z and err_loss < 1e-5 and err_xr < 1e-5 and abs(terms[1] - recon) < 1e-5 * recon
+        out[name] = {"rows": slice_rows, "rows_outside_gap_window": int(must.sum()), "unique_codes": int(len(np.unique(ref_idx))),
+                     "idx_ok": ok_idx, "z_latent_ok": ok_z, "loss_rel_err": err_loss, "x_recon_rel_err": err_xr, "ok": bool(ok)}
+        if not ok:
+            raise SystemExit("bench.py: parity check FAILED on %s: %r" % (name, out[name]))
+        total += slice_rows
+    out["parity_checked_rows"] = total
+    return out
+
+
+def latency_leg(torch, N, dev, p):
+    """The reference's real call sizes (N = B*T = 80 rows image config, 500 rows low-dim config; v5:89-93): per-call
+    latency of the no-grad forward (rollouts, icl.py:836-843) and of forward+backward (training, icl.py:913-970)."""
+    import time as _t
+    from lipvq_vae_b200 import LLFQVAE_V4
+    m = LLFQVAE_V4(F_DIM, D_LAT, num_codes=K_CODES, hidden_dim=H_DIM).to(dev)
+    m.load_state_dict({k: torch.from_numpy(v.copy()) for k, v in p.items()})
+    res = {"note": "gpu_us = CUDA events around 200 back-to-back calls / 200 (includes launch gaps when the host is the "
+                   "limit); kernels_us = sum of this library's kernel durations per call (library CUDA events); "
+                   "host_us = wall clock per call with a synchronize at the end; graph_us = CUDA-graph replay of the "
+                   "same no-grad call"}
+    for n in (80, 500):
+        x = torch.randn(n, F_DIM, device=dev)
+
+        def fwd(i):
+            with torch.no_grad():
+                m(x)
+
+        def fwdbwd(i):
+            for q in m.parameters():
+                q.grad = None
+            _, loss = m(x)
+            loss.backward()
+        r = {}
+        for name, fn in (("forward", fwd), ("forward_backward", fwdbwd)):
+            for i in range(10):
+                fn(i)
+            iters = 200
+            gpu_ms = _time_events(fn, iters, torch)
+            torch.cuda.synchronize()
+            t0 = _t.perf_counter()
+            for i in range(iters):
+                fn(i)
+            torch.cuda.synchronize()
+            host_us = 1e6 * (_t.perf_counter() - t0) / iters
+            rep = N.profile_kernels(fn, 20)
+            r[name] = {"gpu_us": 1e3 * gpu_ms, "host_us": host_us,
+                       "kernels_us": 1e3 * sum(v[1] for v in rep.values()) / 20,
+                       "launches": sum(v[0] for v in rep.values()) / 20, "kernels": sorted(rep.keys())}
+        # CUDA-graph replay of the no-grad forward (static input / output buffers)
+        s = torch.cuda.Stream(device=dev)
+        s.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(s):
+            for i in range(3):
+                fwd(i)
+        torch.cuda.current_stream().wait_stream(s)
+        torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, stream=s):
+            with torch.no_grad():
+                z_static, loss_static = m(x)
+        for i in range(10):
+            g.replay()
+        r["forward"]["graph_us"] = 1e3 * _time_events(lambda i: g.replay(), 200, torch)
+        with torch.no_grad():
+            z_eager, loss_eager = m(x)
+        r["forward"]["graph_matches_eager"] = bool(torch.equal(z_static, z_eager) and torch.equal(loss_static, loss_eager))
+        res["n%d" % n] = r
+    return res
+
+
+def config4_leg(torch, N, lib, dev, rank, world, peaks, steps):
+    """BASELINE config 4: large-codebook sweep, per GPU N=2^20 rows, D in {128,256}, K in {4096,16384,65536}, fp16
+    tensor-core distances + fp32 rescoring of near-ties; every rank runs it on its own data (seed 0+rank), times are the
+    max over ranks; rank 0 checks a row slice against oracle.exact_top2."""
+    import ctypes as C
+    import numpy as np
+    import torch.distributed as dist
+    n = 1 << 20
+    sustained = peaks.get("bf16_tflops_sustained", peaks["bf16_tflops"])
+    cases = []
+    g = torch.Generator(device="cpu").manual_seed(rank)
+    st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    for D in (128, 256):
+        z = torch.rand(n, D, generator=g).to(dev)
+        for K in (4096, 16384, 65536):
+            E = torch.rand(K, D, generator=g).to(dev)
+            need = C.c_size_t(0)
+            N.check(lib.lipvq_workspace_bytes(C.byref(N.Dims(1, 1, 1, D, K)), n, C.byref(need)))
+            ws = torch.empty(need.value + 4096, dtype=torch.uint8, device=dev)
+            idx = torch.empty(n, dtype=torch.int64, device=dev)
+            stats = torch.zeros(4, dtype=torch.int32, device=dev)
+
+            def call(i):
+                N.check(lib.lipvq_vq_argmin(z.data_ptr(), E.data_ptr(), n, D, K, 1, idx.data_ptr(), None,
+                                            stats.data_ptr(), ws.data_ptr(), ws.numel(), st))
+            for i in range(2):
+                call(i)
+            ms = _time_events(call, max(3, steps // 6), torch)
+            rep = N.profile_kernels(call, 2)
+            if world > 1:
+                t = torch.tensor([ms], device=dev, dtype=torch.float64)
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+                ms = float(t.item())
+            tf = n * 2.0 * K * D / (ms / 1e3) / 1e12
+            c = {"D": D, "K": K, "rows_per_gpu": n, "call_ms": ms, "call_tflops": tf, "frac_of_sustained_bf16": tf / sustained,
+                 "aggregate_tflops": world * tf, "fallback_rows": int(stats[0].item()), "rescored_codes": int(stats[1].item()),
+                 "kernels_us": {k: 1e3 * v[1] / 2 for k, v in rep.items()}}
+            if "vq_tc_kernel" in rep:
+                c["vq_tc_kernel_tflops"] = n * 2.0 * K * D / (rep["vq_tc_kernel"][1] / 2 / 1e3) / 1e12
+            if rank == 0:
+                from oracle import lipvq_oracle as orc
+                rows = 16384 if K <= 16384 else 4096
+                ref, d1, d2 = orc.exact_top2(z[:rows].cpu().numpy(), E.cpu().numpy(), block_rows=512 if K > 16384 else 2048)
+                must = orc.index_parity_mask(d1, d2)
+                got = idx[:rows].cpu().numpy()
+                c["parity_rows"] = rows
+                c["parity_ok"] = bool(np.array_equal(got[must], ref[must]))
+                if not c["parity_ok"]:
+                    raise SystemExit("bench.py: config 4 parity FAILED at D=%d K=%d" % (D, K))
+            cases.append(c)
+            del E, ws, idx
+        del z
+    return {"workload": "large-codebook sweep, N=2^20 rows per GPU, fp16 tensor-core distances + fp32 near-tie rescore "
+                        "(lipvq_vq_argmin from fp32 z / E, operand conversion and resolve passes included)",
+            "n_gpus": world, "peak": sustained, "peak_source": "bf16 sustained, MEASURED_PEAKS.json", "cases": cases,
+            "timing": "CUDA events, max over ranks"}
+
+
+def config5_leg(torch, dev, rank, world, steps):
+    """BASELINE config 5: ICRT in-context transformer policy training with the LipVQ tokenizer inline (icl.py:891-974
+    replayed by lipvq_vae_b200.icrt.ICRTTrainer; the policy is stock torch, pinned to the reference network by
+    tests/test_icrt_integration_cpu.py), synthetic prompt/query sequences, data parallel (weak scaling)."""
+    from collections import OrderedDict
+    import torch.distributed as dist
+    from lipvq_vae_b200.icrt import ICRTPolicy, ICRTTrainer, synthetic_icrt_batch
+    obs_shapes = OrderedDict(robot0_eef_pos=[3], robot0_eef_quat=[4], robot0_gripper_qpos=[2], object=[199])   # D = 208
+    torch.manual_seed(0)
+    pol = ICRTPolicy(obs_shapes, embed_dim=512, num_layers=6, num_heads=8, context_length=10).to(dev).train()
+    if world > 1:
+        for q in pol.parameters():
+            dist.broadcast(q.data, src=0)
+    tr = ICRTTrainer(pol)
+    out = {"workload": "ICRT training iteration (tokenizer fwd+bwd+AdamW, then policy NLL fwd+bwd+AdamW), %.1f M-parameter "
+                       "policy (6 layers, d=512, 30 tokens), tokenizer D=208 K=1024, synthetic sequences; "
+                       "policy = stock torch eager fp32" % (sum(q.numel() for q in pol.parameters()) / 1e6),
+           "n_gpus": world, "cases": []}
+    for n_seq in (32, 512, 4096):          # B = n_seq/2 query sequences (+ as many prompts): 160 / 2560 / 20480 tokenizer rows
+        batch = synthetic_icrt_batch(obs_shapes, n_seq, device=dev, seed=100 + rank)
+        for i in range(2):
+            tr.step(batch)
+        k = max(3, steps // 4)
+        ms = _time_events(lambda i: tr.step(batch), k, torch)
+        # the tokenizer's share: the same rows through forward + backward + its AdamW alone
+        tok, opt = pol.vq_vae_model, tr.vq_optimizer
+        rows = batch["actions"][:n_seq // 2].reshape(-1, 12).contiguous()
+
+        def tok_only(i):
+            opt.zero_grad()
+            _, l = tok(rows)
+            l.backward()
+            opt.step()
+        for i in range(2):
+            tok_only(i)
+        ms_tok = _time_events(tok_only, k, torch)
+        if world > 1:
+            t = torch.tensor([ms, ms_tok], device=dev, dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms, ms_tok = t.tolist()
+        out["cases"].append({"sequences_per_gpu": n_seq, "tokenizer_rows_per_gpu": int(rows.shape[0]), "ms_per_iteration": ms,
+                             "iterations_per_s": 1e3 / ms, "sequences_per_s": world * n_seq / (ms / 1e3),
+                             "tokenizer_ms": ms_tok, "tokenizer_share": ms_tok / ms})
+    return out
 
 
 def main():
@@ -488,6 +762,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--search", default="tensor", choices=["tensor", "exact"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--skip", default="", help="comma list of extra legs to skip: parity,latency,config4,config5")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     # libraries (NCCL's version banner, ...) write to fd 1: keep stdout for the ONE JSON line

@@ -582,7 +582,7 @@ inline int encoder_fused16_launch(const lipvq_dims_t *d, const lipvq_params_t *p
         }
     }
     if (!force_tf32) {
-        ProfScope prof("enc_fused_kernel", st);
+        ProfScope prof("enc16_fused_kernel", st);
         auto launch = [&](auto kern) -> int {
             LIPVQ_TRY(set_smem(kern, Enc16Smem::TOTAL));
             kern<<<grid_for(n), ENC_THR, Enc16Smem::TOTAL, st>>>(x, p->enc0_w, p->enc0_b, p->enc2_w, p->enc2_b, Wn,
@@ -595,7 +595,7 @@ inline int encoder_fused16_launch(const lipvq_dims_t *d, const lipvq_params_t *p
         LIPVQ_LAUNCH_OK();
     }
     {   // tf32 kernel: runs only when the flag is set (returns at once otherwise)
-        ProfScope prof(force_tf32 ? "enc_fused_kernel" : "enc_tf32_fallback (gated)", st);
+        ProfScope prof(force_tf32 ? "enc_fused_kernel (tf32)" : "enc_fused_kernel (tf32 fallback, gated)", st);
         const int *gate = force_tf32 ? nullptr : flag;
         auto launch = [&](auto kern) -> int {
             LIPVQ_TRY(set_smem(kern, EncSmem::TOTAL));
