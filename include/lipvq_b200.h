@@ -157,7 +157,7 @@ int lipvq_decoder_fwd(const lipvq_dims_t *dims, const lipvq_params_t *p, const f
                       void *ws, size_t ws_bytes, void *stream);
 
 /* Gather + decoder + both loss sums (v5:47, 74-81).  The decoder runs once per CODE (xr_code = decoder(E),
- * [K,F]); one streaming pass over the rows then writes z_q[n] = E[idx[n]] to acts->z_q (this IS z_latent,
+ * [K,F]); one streaming pass over the rows then writes z_q[n] = E[idx[n]] to acts->z_q (nullable; this IS z_latent,
  * v5:74), x_recon[n] = xr_code[idx[n]] to acts->x_recon (nullable), and sse[0] = sum (x_recon-x)^2,
  * sse[1] = sum (z_q-z_e)^2 (device double[2], overwritten).  acts: idx, z_e are read; z_q is written;
  * c1,d1,c2,d2,xr_code ([K,.], code level) and g_pre ([N,D]) are written when non-null (kept for backward).
@@ -200,7 +200,8 @@ int lipvq_encoder_bwd(const lipvq_dims_t *dims, const lipvq_params_t *p, const f
                       size_t ws_bytes, void *stream);
 
 /* Whole forward in one call (inference / no-grad; LLFQVAE_V4.forward v5:70-84):
- * x -> z_latent[N,D], idx[N], x_recon[N,F] (nullable), loss_out float[4] (nullable).
+ * x -> z_latent[N,D] (nullable: tokens-only mode for a consumer that embeds per CODE, the [N,D] write -- 94 % of the
+ * forward's mandatory HBM traffic -- is then skipped), idx[N], x_recon[N,F] (nullable), loss_out float[4] (nullable).
  * Intermediates live in ws.
  * aux_stream / ev_fork / ev_join (all three or none; cudaStream_t / cudaEvent_t owned by the CALLER): when given, the
  * parameter-only per-code decoder table is enqueued on aux_stream between ev_fork (recorded on `stream`) and ev_join

@@ -1,6 +1,7 @@
 // common.cuh -- shared device helpers for the LipVQ-VAE tokenizer kernels (sm_100a only).
 #pragma once
 #include <cuda_runtime.h>
+#include <nvtx3/nvToolsExt.h>
 #include <stdint.h>
 
 #include "../../include/lipvq_b200.h"
@@ -46,6 +47,14 @@ struct ProfScope {
     ProfScope(const char *name, cudaStream_t s) : rec(g_prof_on ? prof_open(name, s) : -1), st(s) {}
     ~ProfScope() { if (rec >= 0) prof_close(rec, st); }
 };
+
+// NVTX range around every C-ABI entry point (tracing).  nvtx3 is header-only and resolves the
+// tool's injection library lazily: without a profiler attached a push/pop is one predictable branch.
+struct NvtxRange {
+    explicit NvtxRange(const char *name) { nvtxRangePushA(name); }
+    ~NvtxRange() { nvtxRangePop(); }
+};
+#define LIPVQ_NVTX(name) ::lipvq::NvtxRange _nvtx_range_(name)
 
 constexpr int kNumSMs = 148;  // B200: 2 dies x 74 SMs
 

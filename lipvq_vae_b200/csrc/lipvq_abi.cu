@@ -175,6 +175,7 @@ int lipvq_workspace_bytes(const lipvq_dims_t *dims, int64_t n_rows, size_t *out_
 
 int lipvq_encoder_fwd(const lipvq_dims_t *d, const lipvq_params_t *p, const float *x, int64_t n,
                       const lipvq_acts_t *a, void *ws, size_t ws_bytes, void *stream) {
+    LIPVQ_NVTX("lipvq_encoder_fwd");
     if (!dims_ok(d) || n < 0) return LIPVQ_ESHAPE;
     if (!p || !a) return LIPVQ_EALIGN;
     if (n == 0) return LIPVQ_OK;
@@ -207,6 +208,7 @@ int lipvq_encoder_fwd(const lipvq_dims_t *d, const lipvq_params_t *p, const floa
 
 int lipvq_linear_fwd(const float *X, const float *W, const float *b, float *Y, int64_t M, int32_t Nn,
                      int32_t K, int32_t act, void *stream) {
+    LIPVQ_NVTX("lipvq_linear_fwd");
     if (M < 0 || Nn < 1 || K < 1) return LIPVQ_ESHAPE;
     if (M == 0) return LIPVQ_OK;
     if (!aligned16(X) || !aligned16(W) || !aligned16(Y)) return LIPVQ_EALIGN;
@@ -225,6 +227,7 @@ size_t lipvq_linear_bwd_ws_bytes(int64_t M, int32_t Nn, int32_t K) {
 
 int lipvq_linear_bwd(const float *dY, const float *X, const float *W, const float *x_mask, float *dX, float *dW,
                      float *db, int64_t M, int32_t Nn, int32_t K, void *ws, size_t ws_bytes, void *stream) {
+    LIPVQ_NVTX("lipvq_linear_bwd");
     if (M < 0 || Nn < 1 || K < 1) return LIPVQ_ESHAPE;
     if (!aligned16(dY) || !aligned16(X) || !aligned16(W) || !dW) return LIPVQ_EALIGN;
     if (ws_bytes < lipvq_linear_bwd_ws_bytes(M, Nn, K) || !aligned16(ws)) return LIPVQ_EWORKSPACE;
@@ -245,6 +248,7 @@ int lipvq_linear_bwd(const float *dY, const float *X, const float *W, const floa
 
 int lipvq_scatter_add_diff(const float *src, const int64_t *idx, const float *table, float alpha,
                            const float *grad_scale, int64_t n, int32_t D, int32_t K, float *sums, void *stream) {
+    LIPVQ_NVTX("lipvq_scatter_add_diff");
     if (n < 0 || D < 1 || K < 1) return LIPVQ_ESHAPE;
     if (n == 0) return LIPVQ_OK;
     if (!aligned16(src) || !idx || !aligned16(table) || !aligned16(sums)) return LIPVQ_EALIGN;
@@ -301,6 +305,7 @@ int lipvq_vqvae_ste_grad(float *g_zq, const float *z_e, const float *z_q, int64_
 
 int lipvq_lipschitz_fwd(const float *h, const float *W, const float *b, const float *ci, float *scale,
                         float *Wn, float *z_e, int64_t n, int32_t D, int32_t H, void *stream) {
+    LIPVQ_NVTX("lipvq_lipschitz_fwd");
     if (n < 0 || D < 1 || H < 1) return LIPVQ_ESHAPE;
     if (!aligned16(W) || !ci || !aligned16(scale) || !aligned16(Wn)) return LIPVQ_EALIGN;
     cudaStream_t st = (cudaStream_t)stream;
@@ -314,6 +319,7 @@ int lipvq_lipschitz_fwd(const float *h, const float *W, const float *b, const fl
 int lipvq_vq_argmin(const float *z, const float *E, int64_t n, int32_t D, int32_t K, int32_t mode,
                     int64_t *idx, float *best_d2, int32_t *stats, void *ws, size_t ws_bytes,
                     void *stream) {
+    LIPVQ_NVTX("lipvq_vq_argmin");
     if (n < 0 || D < 1 || D > 8192 || K < 1 || K > (1 << 20)) return LIPVQ_ESHAPE;
     if (n == 0) return LIPVQ_OK;
     if (!aligned16(z) || !aligned16(E) || !idx) return LIPVQ_EALIGN;
@@ -329,6 +335,7 @@ int lipvq_vq_argmin(const float *z, const float *E, int64_t n, int32_t D, int32_
 int lipvq_encode_search_fwd(const lipvq_dims_t *d, const lipvq_params_t *p, const float *x, int64_t n,
                             const lipvq_acts_t *a, int32_t search_mode, int32_t *stats, void *ws, size_t ws_bytes,
                             void *stream) {
+    LIPVQ_NVTX("lipvq_encode_search_fwd");
     if (!dims_ok(d) || n < 0) return LIPVQ_ESHAPE;
     if (!p || !a) return LIPVQ_EALIGN;
     if (n == 0) return LIPVQ_OK;
@@ -360,6 +367,7 @@ int lipvq_encode_search_fwd(const lipvq_dims_t *d, const lipvq_params_t *p, cons
 
 int lipvq_gather_loss(const float *z_e, const float *E, const int64_t *idx, int64_t n, int32_t D,
                       int32_t K, float *z_q, double *sse_q, void *ws, size_t ws_bytes, void *stream) {
+    LIPVQ_NVTX("lipvq_gather_loss");
     if (n < 0 || D < 1 || K < 1) return LIPVQ_ESHAPE;
     if (!aligned16(z_e) || !aligned16(E) || !idx || !aligned16(z_q) || !sse_q) return LIPVQ_EALIGN;
     if (ws_bytes < 2 * kQeBlocks * sizeof(float) || !aligned16(ws)) return LIPVQ_EWORKSPACE;
@@ -381,6 +389,7 @@ int lipvq_gather_loss(const float *z_e, const float *E, const int64_t *idx, int6
 int lipvq_decoder_fwd(const lipvq_dims_t *d, const lipvq_params_t *p, const float *z_q, const float *x,
                       int64_t n, const lipvq_acts_t *a, double *sse_r, void *ws, size_t ws_bytes,
                       void *stream) {
+    LIPVQ_NVTX("lipvq_decoder_fwd");
     if (!dims_ok(d) || n < 0) return LIPVQ_ESHAPE;
     if (!p || !a) return LIPVQ_EALIGN;
     if (n == 0) return LIPVQ_OK;
@@ -431,6 +440,7 @@ static int quantize_decode_impl(const lipvq_dims_t *d, const lipvq_params_t *p, 
 int lipvq_quantize_decode_fwd(const lipvq_dims_t *d, const lipvq_params_t *p, const float *x, int64_t n,
                               int64_t n_total, const lipvq_acts_t *a, double *sse, float *loss_out, void *ws,
                               size_t ws_bytes, void *stream) {
+    LIPVQ_NVTX("lipvq_quantize_decode_fwd");
     return quantize_decode_impl(d, p, x, n, n_total, a, sse, loss_out, ws, ws_bytes, stream, false);
 }
 
@@ -447,7 +457,7 @@ static int quantize_decode_impl(const lipvq_dims_t *d, const lipvq_params_t *p, 
         return LIPVQ_OK;
     }
     auto opt16 = [](const void *q) { return q == nullptr || aligned16(q); };
-    if (!a->idx || !aligned16(a->z_e) || !aligned16(a->z_q) || !opt16(a->x_recon) || !opt16(x) || !opt16(a->c1) ||
+    if (!a->idx || !aligned16(a->z_e) || !opt16(a->z_q) || !opt16(a->x_recon) || !opt16(x) || !opt16(a->c1) ||
         !opt16(a->d1) || !opt16(a->c2) || !opt16(a->d2) || !opt16(a->xr_code))
         return LIPVQ_EALIGN;
     if (ws_bytes < qd_ws_bytes(d) || !aligned16(ws)) return LIPVQ_EWORKSPACE;
@@ -498,6 +508,7 @@ int lipvq_loss_finalize(const double *sse_r, const double *sse_q, int64_t n_tota
 int lipvq_decoder_bwd(const lipvq_dims_t *d, const lipvq_params_t *p, const float *x, int64_t n,
                       int64_t n_total, const float *grad_scale, const lipvq_acts_t *a, const lipvq_grads_t *g,
                       void *ws, size_t ws_bytes, void *stream) {
+    LIPVQ_NVTX("lipvq_decoder_bwd");
     if (!dims_ok(d) || n <= 0 || n_total < n) return LIPVQ_ESHAPE;
     if (!p || !a || !g || !aligned16(x) || !a->idx || !aligned16(a->z_e) || !aligned16(a->c1) || !aligned16(a->d1) ||
         !aligned16(a->c2) || !aligned16(a->d2) || !aligned16(a->xr_code) || !aligned16(g->codebook))
@@ -542,6 +553,7 @@ int lipvq_decoder_bwd(const lipvq_dims_t *d, const lipvq_params_t *p, const floa
 
 int lipvq_scatter_add(const float *src, const int64_t *idx, int64_t n, int32_t D, int32_t K, float *sums,
                       float *counts, void *stream) {
+    LIPVQ_NVTX("lipvq_scatter_add");
     if (n < 0 || D < 1 || K < 1) return LIPVQ_ESHAPE;
     if (n == 0) return LIPVQ_OK;
     if (!aligned16(src) || !idx || !aligned16(sums)) return LIPVQ_EALIGN;
@@ -555,6 +567,7 @@ int lipvq_scatter_add(const float *src, const int64_t *idx, int64_t n, int32_t D
 int lipvq_encoder_bwd(const lipvq_dims_t *d, const lipvq_params_t *p, const float *x, int64_t n,
                       int64_t n_total, const float *grad_scale, const lipvq_acts_t *a, const lipvq_grads_t *g,
                       void *ws, size_t ws_bytes, void *stream) {
+    LIPVQ_NVTX("lipvq_encoder_bwd");
     if (!dims_ok(d) || n <= 0 || n_total < n) return LIPVQ_ESHAPE;
     if (!p || !a || !g || !aligned16(x)) return LIPVQ_EALIGN;
     if (ws_bytes < workspace_bytes_impl(d, n) || !aligned16(ws)) return LIPVQ_EWORKSPACE;
@@ -592,9 +605,10 @@ int lipvq_forward_fused(const lipvq_dims_t *d, const lipvq_params_t *p, const fl
                         int64_t n_total, int32_t search_mode, float *z_latent, int64_t *idx,
                         float *x_recon, float *loss_out, int32_t *stats, void *ws, size_t ws_bytes,
                         void *stream, void *aux_stream, void *ev_fork, void *ev_join) {
+    LIPVQ_NVTX("lipvq_forward_fused");
     if (!dims_ok(d) || n < 0 || n_total < n) return LIPVQ_ESHAPE;
     if (n == 0) return LIPVQ_OK;
-    if (!p || !aligned16(x) || !aligned16(z_latent)) return LIPVQ_EALIGN;
+    if (!p || !aligned16(x) || (z_latent && !aligned16(z_latent))) return LIPVQ_EALIGN;
     if (ws_bytes < workspace_bytes_impl(d, n) || !aligned16(ws)) return LIPVQ_EWORKSPACE;
     cudaStream_t st = (cudaStream_t)stream;
     // the reference's real call sizes (80 / 500 rows, v5:89-93): one exact-fp32 kernel instead of 12 launches
@@ -648,9 +662,10 @@ int lipvq_forward_fused(const lipvq_dims_t *d, const lipvq_params_t *p, const fl
 int lipvq_forward_small(const lipvq_dims_t *d, const lipvq_params_t *p, const float *x, int64_t n, int64_t n_total,
                         float *z_latent, int64_t *idx, float *x_recon, float *loss_out, int32_t *stats, void *ws,
                         size_t ws_bytes, void *stream) {
+    LIPVQ_NVTX("lipvq_forward_small");
     if (!dims_ok(d) || n < 0 || n_total < n || n > (1 << 16) || small::smem_bytes(d) > 200 * 1024) return LIPVQ_ESHAPE;
     if (n == 0) return LIPVQ_OK;
-    if (!p || !aligned16(x) || !aligned16(z_latent) || !idx) return LIPVQ_EALIGN;
+    if (!p || !aligned16(x) || (z_latent && !aligned16(z_latent)) || !idx) return LIPVQ_EALIGN;
     if (ws_bytes < small::scratch_bytes(n) || !aligned16(ws)) return LIPVQ_EWORKSPACE;
     return small::launch(d, p, x, n, n_total, z_latent, idx, x_recon, loss_out, stats, ws, (cudaStream_t)stream);
 }
@@ -658,6 +673,7 @@ int lipvq_forward_small(const lipvq_dims_t *d, const lipvq_params_t *p, const fl
 int lipvq_adamw_step(float *param, const float *grad, float *exp_avg, float *exp_avg_sq, int64_t n,
                      int64_t step, float lr, float beta1, float beta2, float eps, float weight_decay,
                      void *stream) {
+    LIPVQ_NVTX("lipvq_adamw_step");
     if (n < 0 || step < 1) return LIPVQ_ESHAPE;
     if (n == 0) return LIPVQ_OK;
     if (!param || !grad || !exp_avg || !exp_avg_sq) return LIPVQ_EALIGN;
@@ -674,6 +690,7 @@ int lipvq_adamw_step(float *param, const float *grad, float *exp_avg, float *exp
 
 int lipvq_ema_update(float *E, float *n_ema, float *m_ema, const float *counts, const float *sums,
                      int32_t K, int32_t D, float gamma, float eps, void *ws, size_t ws_bytes, void *stream) {
+    LIPVQ_NVTX("lipvq_ema_update");
     if (K < 1 || D < 1) return LIPVQ_ESHAPE;
     if (!E || !n_ema || !m_ema || !counts || !sums) return LIPVQ_EALIGN;
     if (ws_bytes < 64 * sizeof(float) + 256 + sizeof(double) || !aligned16(ws)) return LIPVQ_EWORKSPACE;

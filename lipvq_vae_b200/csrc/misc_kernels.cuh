@@ -127,7 +127,7 @@ __global__ void __launch_bounds__(QE_THR) quantize_emit_kernel(
         const unsigned total = (unsigned)rows * dq;
         if (VEC4) {
             const float4 *zt = reinterpret_cast<const float4 *>(z_e + r0 * D);
-            float4 *qt = reinterpret_cast<float4 *>(z_q + r0 * D);
+            float4 *qt = z_q ? reinterpret_cast<float4 *>(z_q + r0 * D) : nullptr;
             for (unsigned i0 = tid; i0 < total; i0 += 4 * QE_THR) {
                 float4 e[4], z[4];
 #pragma unroll
@@ -143,7 +143,7 @@ __global__ void __launch_bounds__(QE_THR) quantize_emit_kernel(
                 for (int u = 0; u < 4; ++u) {
                     const unsigned i = i0 + u * QE_THR;
                     if (i < total) {
-                        __stcs(qt + i, e[u]);
+                        if (z_q) __stcs(qt + i, e[u]);
                         const float dx = e[u].x - z[u].x, dy = e[u].y - z[u].y, dz = e[u].z - z[u].z,
                                     dw = e[u].w - z[u].w;
                         sq += dx * dx + dy * dy + dz * dz + dw * dw;
@@ -162,7 +162,7 @@ __global__ void __launch_bounds__(QE_THR) quantize_emit_kernel(
                 const float e = __ldg(E + (size_t)sidx[r] * D + c);
                 const float zz = __ldcs(z_e + r0 * D + i);
                 const float dd = e - zz;
-                __stcs(z_q + r0 * D + i, e);
+                if (z_q) __stcs(z_q + r0 * D + i, e);
                 sq += dd * dd;
                 if (GPRE) __stcs(gpre + r0 * D + i, -a_q * dd * zz * (1.0f - zz));
             }

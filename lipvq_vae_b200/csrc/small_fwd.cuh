@@ -250,7 +250,7 @@ __global__ void __launch_bounds__(ST) small_forward_kernel(
         const float e = __ldg(p.codebook + (size_t)s_idx[r] * D + d);
         s_q[i] = e;
         if (r < rows_valid) {
-            z_latent[(size_t)(r0 + r) * D + d] = e;
+            if (z_latent) z_latent[(size_t)(r0 + r) * D + d] = e;
             const float df = e - s_z[r * ZP + d];
             sq = fmaf(df, df, sq);
         }

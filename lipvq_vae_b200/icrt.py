@@ -158,8 +158,13 @@ class ICRTPolicy(nn.Module):
 
     def __init__(self, obs_shapes, ac_dim=12, embed_dim=512, num_layers=6, num_heads=8, context_length=10,
                  causal=False, emb_dropout=0.1, attn_dropout=0.1, block_output_dropout=0.1,
-                 nn_parameter_for_timesteps=True, num_modes=5, min_std=0.01, tokenizer_cls=LLFQVAE_V4):
+                 nn_parameter_for_timesteps=True, num_modes=5, min_std=0.01, tokenizer_cls=LLFQVAE_V4,
+                 fuse_action_embedding=False):
         super().__init__()
+        # opt-in: embed the prompt tokens per CODE ([K, 512] table + gather, ``embed_latent``) instead of
+        # running embed_encoder over the [B*T, latent_dim] ``z_latent``; under no_grad the tokenizer then skips the
+        # ``z_latent`` write altogether (``forward_tokens``).  Same numbers up to fp32 summation order.
+        self.fuse_action_embedding = fuse_action_embedding
         self.ac_dim, self.num_modes, self.min_std = ac_dim, num_modes, min_std
         self.context_length, self.embed_dim = context_length, embed_dim
         self.nn_parameter_for_timesteps = nn_parameter_for_timesteps
@@ -182,8 +187,8 @@ class ICRTPolicy(nn.Module):
         self._vq_vae_loss = None
 
     # obs_nets.py:2524-2543
-    def input_embedding(self, x):
-        e = self.nets["embed_encoder"](x)
+    def input_embedding(self, x, pre_embedded=False):
+        e = x if pre_embedded else self.nets["embed_encoder"](x)
         if self.nn_parameter_for_timesteps:
             t = self.params["embed_timestep"]
         else:
@@ -193,10 +198,25 @@ class ICRTPolicy(nn.Module):
     def forward_train(self, obs_dict, context_obs, actions, goal_dict=None, low_noise_eval=False):
         B, T = actions.shape[:2]
         flat = lambda dct: {k: v.reshape(B * T, *v.shape[2:]) for k, v in dct.items()}     # icl_time_distributed
-        o, c, a = self.nets["encoder"](flat(obs_dict), flat(context_obs), actions.reshape(B * T, -1))
-        self._vq_vae_loss = self.nets["encoder"]._vq_vae_loss
-        o, c, a = (t.reshape(B, T, -1) for t in (o, c, a))
-        oe, ce, ae = self.input_embedding(o), self.input_embedding(c), self.input_embedding(a)
+        enc = self.nets["encoder"]
+        tok = enc.action_network
+        if self.fuse_action_embedding and hasattr(tok, "embed_latent"):
+            o, c = enc.nets["obs"](flat(obs_dict)), enc.nets["obs"](flat(context_obs))
+            rows = actions.reshape(B * T, -1)
+            if torch.is_grad_enabled():
+                _, loss = tok(rows)
+                idx = tok.last_indices
+            else:
+                idx, loss = tok.forward_tokens(rows)               # no [B*T, latent_dim] tensor at all
+            enc._vq_vae_loss = self._vq_vae_loss = loss
+            ae = self.input_embedding(tok.embed_latent(self.nets["embed_encoder"], idx).reshape(B, T, -1), pre_embedded=True)
+            o, c = o.reshape(B, T, -1), c.reshape(B, T, -1)
+        else:
+            o, c, a = enc(flat(obs_dict), flat(context_obs), actions.reshape(B * T, -1))
+            self._vq_vae_loss = enc._vq_vae_loss
+            o, c, a = (t.reshape(B, T, -1) for t in (o, c, a))
+            ae = self.input_embedding(a)
+        oe, ce = self.input_embedding(o), self.input_embedding(c)
         ctx = torch.stack([ce, ae], dim=2).view(B, 2 * T, -1)                                # obs_nets.py:2586-2591
         h = self.nets["transformer"](torch.cat([ctx, oe], dim=1))[:, -T:]                     # :2594-2603
         out = self.nets["decoder"](h.reshape(B * T, -1))

@@ -425,6 +425,49 @@ class LLFQVAE_V4(nn.Module):
         return z_latent, stats[0]
 
     @torch.no_grad()
+    def forward_tokens(self, x):
+        """Tokens-only no-grad forward: ``(indices int64[N], loss 0-dim)`` with the [N, latent_dim] ``z_latent`` write
+        skipped (94 % of the forward's mandatory HBM traffic).  For a consumer that embeds per CODE --
+        ``embed_latent`` -- instead of per row; ``last_reconstruction`` / ``last_loss_terms`` are set as by forward."""
+        _check_cuda(x, "x")
+        if x.dim() != 2 or x.shape[1] != self.feature_dim:
+            raise RuntimeError("expected x of shape [N, %d], got %s" % (self.feature_dim, tuple(x.shape)))
+        x = x.contiguous()
+        dev, n = x.device, x.shape[0]
+        dims = self._dims()
+        n_total = max(int(self.n_total_rows) if self.n_total_rows is not None else n, 1)
+        stats = torch.zeros(4, dtype=torch.float32, device=dev)
+        idx = torch.empty(n, dtype=torch.int64, device=dev)
+        vq_stats = torch.zeros(4, dtype=torch.int32, device=dev)
+        x_recon = torch.empty(n, self.feature_dim, dtype=torch.float32, device=dev)
+        if n:
+            params = _contig([p.detach() for p in self._param_list()])
+            P = _param_struct(N.Params, params)
+            ws = _workspace(dev, dims, n)
+            aux = (None, None, None)
+            if n >= AUX_MIN_ROWS and not torch.cuda.is_current_stream_capturing():
+                s_aux, ef, ej = _aux(dev)
+                aux = (C.c_void_p(s_aux.cuda_stream), C.c_void_p(ef.cuda_event), C.c_void_p(ej.cuda_event))
+            N.check(N.lib().lipvq_forward_fused(C.byref(dims), C.byref(P), _p(x), n, n_total, int(self.search_mode), None,
+                                                _p(idx), _p(x_recon), _p(stats), _p(vq_stats), _p(ws), ws.numel(),
+                                                _stream_ptr(dev), *aux), "lipvq_forward_fused")
+        self.last_z_e, self.last_indices, self.last_reconstruction = None, idx, x_recon
+        self.last_loss_terms, self.last_search_stats = stats, vq_stats
+        return idx, stats[0]
+
+    def embed_latent(self, embed: nn.Linear, indices=None):
+        """``embed(z_latent)`` for the policy's input embedding (``nets["embed_encoder"]``, a Linear(latent_dim -> 512):
+        robomimic/models/obs_nets.py:2537-2543, called :2582) WITHOUT the [N, latent_dim] tensor: ``z_latent`` takes
+        only K distinct values (v5:47, 74), so ``embed(z_latent)[n] = (E W^T + b)[idx[n]]`` -- a [K, 512] table (K rows
+        of GEMM instead of N) and a gather.  Differentiable w.r.t. ``embed``'s parameters (the codebook is detached,
+        exactly like ``z_latent``); stock torch ops on the caller's side of the boundary."""
+        indices = self.last_indices if indices is None else indices
+        if indices is None:
+            raise LipVQNativeError("embed_latent needs indices (call forward / forward_tokens first)")
+        table = torch.nn.functional.linear(self.quantizer.codebook.detach(), embed.weight, embed.bias)    # [K, 512]
+        return table.index_select(0, indices)
+
+    @torch.no_grad()
     def encode(self, x):
         """z_e = to_latent(encoder(x))  (v5:71-72)"""
         return self.to_latent(self.encoder(x))

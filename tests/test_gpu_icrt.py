@@ -117,3 +117,43 @@ def test_icrt_trainer_steps_and_cache_wiring():
         for _ in range(3):                      # a rollout re-tokenises the same prompt every environment step
             pol.forward_train(obs_dict=obs, context_obs=obs, actions=batch["actions"][:4].contiguous())
     assert cache.hits - h0 >= 1
+
+
+def test_fused_action_embedding_equals_plain_path():
+    """embed_encoder(z_latent) as a [K, 512] per-code table + gather (``embed_latent``), with the tokenizer
+    in tokens-only mode under no_grad (``forward_tokens``: no z_latent write) -- same GMM, same tokenizer loss, same
+    gradients on embed_encoder as the reference-shaped path."""
+    g, sd = _golden()
+    dev = "cuda:0"
+    obs = {k: torch.from_numpy(g["obs::" + k]).to(dev) for k in OBS_SHAPES}
+    ctx = {k: torch.from_numpy(g["ctx::" + k]).to(dev) for k in OBS_SHAPES}
+    pa, ta = torch.from_numpy(g["prompt_actions"]).to(dev), torch.from_numpy(g["train_actions"]).to(dev)
+    outs = {}
+    for fuse in (False, True):
+        pol = _policy(sd)
+        pol.fuse_action_embedding = fuse
+        d = pol.forward_train(obs_dict=obs, context_obs=ctx, actions=pa)
+        nll = -d.log_prob(ta).mean()
+        nll.backward()
+        with torch.no_grad():
+            d0 = pol.forward_train(obs_dict=obs, context_obs=ctx, actions=pa)
+            lp0 = d0.log_prob(ta)
+            vq0 = pol._vq_vae_loss.clone()
+        outs[fuse] = (d.component_distribution.base_dist.loc.detach(), d.mixture_distribution.logits.detach(),
+                      pol.nets["embed_encoder"].weight.grad.clone(), lp0, vq0, pol.vq_vae_model.last_indices.clone())
+    a, b = outs[False], outs[True]
+    assert torch.equal(a[5], b[5])
+    for i, name in enumerate(("means", "logits", "embed_encoder.weight.grad", "log_probs (no_grad)")):
+        scale = max(1.0, a[i].abs().max().item())
+        assert (a[i] - b[i]).abs().max().item() <= 2e-5 * scale, name
+    assert abs(a[4].item() - b[4].item()) <= 1e-6 * abs(a[4].item())
+    # tokens-only mode returns the same tokens and loss as the full forward
+    tok = _policy(sd).vq_vae_model
+    rows = pa.reshape(-1, 12).contiguous()
+    with torch.no_grad():
+        z, loss = tok(rows)
+        idx_full = tok.last_indices.clone()
+        idx, loss_t = tok.forward_tokens(rows)
+    assert torch.equal(idx, idx_full) and abs(loss.item() - loss_t.item()) <= 1e-6 * abs(loss.item())
+    emb = torch.nn.Linear(36, 64).to(dev)
+    assert (tok.embed_latent(emb, idx) - emb(z)).abs().max().item() < 1e-5
