@@ -190,6 +190,18 @@ int lipvq_decoder_bwd(const lipvq_dims_t *dims, const lipvq_params_t *p, const f
 int lipvq_scatter_add(const float *src, const int64_t *idx, int64_t n_rows, int32_t D, int32_t K,
                       float *sums, float *counts, void *stream);
 
+/* DETERMINISTIC per-code sums (same results bit for bit on every run and every rank): a counting sort of the rows
+ * by code and a fixed reduction tree instead of floating-point atomics.
+ *   sums[k,:] (+)= alpha * gs * sum_{idx[n]=k} (table ? table[k,:] - src[n,:] : src[n,:])     gs = *grad_scale or 1
+ *   counts[k]   = |{n: idx[n]=k}|   (nullable)
+ * accumulate != 0 adds to sums, otherwise sums is overwritten (codes without rows get 0).  K <= 8192.
+ * Serves the codebook gradient (autograd's index_put_ accumulate, v5:47) inside lipvq_decoder_bwd and the EMA
+ * cluster statistics; ws >= lipvq_segment_sum_ws_bytes(n, D, K). */
+size_t lipvq_segment_sum_ws_bytes(int64_t n_rows, int32_t D, int32_t K);
+int lipvq_segment_sum(const float *src, const int64_t *idx, const float *table, float alpha,
+                      const float *grad_scale, int64_t n_rows, int32_t D, int32_t K, int32_t accumulate,
+                      float *sums, float *counts, void *ws, size_t ws_bytes, void *stream);
+
 /* Backward of the encoder from the commitment term only (v5:80; there is no straight-through
  * path): g_ze = 0.5*(z_e - z_q)/(n_total*D) -> sigmoid' -> Lipschitz-norm backward
  * (through scale, sum|W|, softplus) -> MLP backward.  With acts->g_pre (written by the forward for the same

@@ -13,6 +13,7 @@
 #include "vq_exact.cuh"
 #include "vq_tensor.cuh"
 #include "small_fwd.cuh"
+#include "seg_reduce.cuh"
 
 namespace lipvq {
 thread_local cudaError_t g_last_cuda_error = cudaSuccess;
@@ -88,6 +89,7 @@ static size_t workspace_bytes_impl(const lipvq_dims_t *d, int64_t n) {
     bytes += align_up(2 * kQeBlocks * sizeof(float), 256) + 1024;
     bytes += mlp::enc_scratch_bytes(d->D) + 2048;
     bytes += small::scratch_bytes(n > 0 ? n : 1);
+    if (seg::supported(d->K, n > 0 ? n : 1)) bytes += seg::plan_bytes(n > 0 ? n : 1, d->K, d->D > d->F ? d->D : d->F);
     return align_up(bytes, 256);
 }
 }  // namespace lipvq
@@ -525,10 +527,24 @@ int lipvq_decoder_bwd(const lipvq_dims_t *d, const lipvq_params_t *p, const floa
     const float a_r = (float)(2.0 / ((double)n_total * d->F));
     const float a_q = (float)(0.5 / ((double)n_total * d->D));
     const unsigned blocks = (unsigned)((n + SC_ROWS - 1) / SC_ROWS);
+    // deterministic per-code sums (counting sort by code + fixed reduction tree, seg_reduce.cuh); LIPVQ_SCATTER=atomic
+    // restores the fp32-atomic kernel (A/B timing), which also serves K > 8192
+    static const bool force_atomic = [] { const char *e = getenv("LIPVQ_SCATTER"); return e && !strcmp(e, "atomic"); }();
+    const bool det = !force_atomic && seg::supported(K, n);
+    seg::Plan plan;
+    if (det) {
+        const int Dm = d->D > d->F ? d->D : d->F;
+        void *pw = b.take<char>(seg::plan_bytes(n, K, Dm));
+        if (!b.ok()) return LIPVQ_EWORKSPACE;
+        plan = seg::carve(pw, n, K, Dm);
+        LIPVQ_TRY(seg::build_plan(a->idx, plan, st));
+    }
     // every row with code k sees the same decoder, so the reconstruction gradient is summed per code first:
     // g_R[k] = sum_{idx[n]=k} 2 (x_recon[n] - x[n]) / (n_total F), and the decoder backward runs on K rows
-    LIPVQ_CUDA_OK(cudaMemsetAsync(g_R, 0, (size_t)K * d->F * sizeof(float), st));
-    {
+    if (det) {
+        LIPVQ_TRY(seg::reduce(x, a->xr_code, d->F, plan, a_r, grad_scale, false, g_R, nullptr, st));
+    } else {
+        LIPVQ_CUDA_OK(cudaMemsetAsync(g_R, 0, (size_t)K * d->F * sizeof(float), st));
         ProfScope prof("scatter_add_kernel", st);
         scatter_add_kernel<true><<<blocks, 256, 0, st>>>(x, a->idx, n, d->F, K, g_R, nullptr, a->xr_code, a_r, grad_scale);
         LIPVQ_LAUNCH_OK();
@@ -542,13 +558,36 @@ int lipvq_decoder_bwd(const lipvq_dims_t *d, const lipvq_params_t *p, const floa
     LIPVQ_TRY(linear_bwd_input<ACT_NONE>(g_c1, p->dec0_w, nullptr, g->codebook, K, d->H1, d->D, nullptr, nullptr, 0.f,
                                          nullptr, st));
     // ... plus the codebook loss: sum_{idx[n]=k} 0.5 (E[k] - z_e[n]) / (n_total D)   (v5:81)
-    {
+    if (det) {
+        LIPVQ_TRY(seg::reduce(a->z_e, p->codebook, d->D, plan, a_q, grad_scale, true, g->codebook, nullptr, st));
+    } else {
         ProfScope prof("scatter_add_kernel", st);
         scatter_add_kernel<true><<<blocks, 256, 0, st>>>(a->z_e, a->idx, n, d->D, K, g->codebook, nullptr, p->codebook,
                                                          a_q, grad_scale);
         LIPVQ_LAUNCH_OK();
     }
     return LIPVQ_OK;
+}
+
+// Deterministic per-code sums through the C ABI (EMA statistics, tests): see seg_reduce.cuh.
+size_t lipvq_segment_sum_ws_bytes(int64_t n, int32_t D, int32_t K) {
+    if (n < 1 || D < 1 || !seg::supported(K, n)) return 0;
+    return seg::plan_bytes(n, K, D) + 256;
+}
+
+int lipvq_segment_sum(const float *src, const int64_t *idx, const float *table, float alpha, const float *grad_scale,
+                      int64_t n, int32_t D, int32_t K, int32_t accumulate, float *sums, float *counts, void *ws,
+                      size_t ws_bytes, void *stream) {
+    LIPVQ_NVTX("lipvq_segment_sum");
+    if (n < 0 || D < 1 || K < 1) return LIPVQ_ESHAPE;
+    if (n == 0) return LIPVQ_OK;
+    if (!seg::supported(K, n)) return LIPVQ_ESHAPE;
+    if (!aligned16(src) || !idx || !aligned16(sums) || (table && !aligned16(table))) return LIPVQ_EALIGN;
+    if (ws_bytes < lipvq_segment_sum_ws_bytes(n, D, K) || !aligned16(ws)) return LIPVQ_EWORKSPACE;
+    cudaStream_t st = (cudaStream_t)stream;
+    const seg::Plan plan = seg::carve(ws, n, K, D);
+    LIPVQ_TRY(seg::build_plan(idx, plan, st));
+    return seg::reduce(src, table, D, plan, alpha, grad_scale, accumulate != 0, sums, counts, st);
 }
 
 int lipvq_scatter_add(const float *src, const int64_t *idx, int64_t n, int32_t D, int32_t K, float *sums,

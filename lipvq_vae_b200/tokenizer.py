@@ -372,10 +372,21 @@ class LLFQVAE_V4(nn.Module):
         z_e = z_e.contiguous()
         indices = indices.contiguous()
         K, D = self.num_codes, self.latent_dim
+        n = z_e.shape[0]
+        lib = N.lib()
+        need = lib.lipvq_segment_sum_ws_bytes(n, D, K) if n else 0
+        if need:
+            # deterministic: counting sort by code + fixed reduction tree (bit-identical on every run and every rank)
+            counts = torch.empty(K, dtype=torch.float32, device=z_e.device)
+            sums = torch.empty(K, D, dtype=torch.float32, device=z_e.device)
+            ws = torch.empty(need, dtype=torch.uint8, device=z_e.device)
+            N.check(lib.lipvq_segment_sum(_p(z_e), _p(indices), None, 1.0, None, n, D, K, 0, _p(sums), _p(counts), _p(ws),
+                                          ws.numel(), _stream_ptr(z_e.device)), "lipvq_segment_sum")
+            return counts, sums
         counts = torch.zeros(K, dtype=torch.float32, device=z_e.device)
         sums = torch.zeros(K, D, dtype=torch.float32, device=z_e.device)
-        N.check(N.lib().lipvq_scatter_add(_p(z_e), _p(indices), z_e.shape[0], D, K, _p(sums), _p(counts),
-                                          _stream_ptr(z_e.device)), "lipvq_scatter_add")
+        N.check(lib.lipvq_scatter_add(_p(z_e), _p(indices), n, D, K, _p(sums), _p(counts),
+                                      _stream_ptr(z_e.device)), "lipvq_scatter_add")
         return counts, sums
 
     @torch.no_grad()

@@ -306,3 +306,64 @@ def test_small_forward_kernel_shapes_vs_oracle(n, F, D, K):
     with torch.no_grad():
         z_m, loss_m = m(torch.from_numpy(x).cuda())
     assert np.array_equal(m.last_indices.cpu().numpy(), idx) and np.array_equal(z_m.cpu().numpy(), z)
+
+
+# ----------------------------------------------------------------------------- deterministic per-code sums
+@pytest.mark.parametrize("n,D,K,collapsed", [(100003, 208, 1024, True), (100003, 208, 1024, False), (5000, 50, 100, False),
+                                             (70000, 12, 1024, False), (1, 208, 1024, False), (300000, 64, 8192, False),
+                                             (655360, 208, 1024, True)])
+def test_segment_sum_deterministic_and_exact(n, D, K, collapsed):
+    """lipvq_segment_sum (csrc/seg_reduce.cuh): sums, differences against a table, counts and accumulation against
+    float64; bit-identical results over repeated runs (the property the atomic scatter did not have)."""
+    import ctypes as C
+    from lipvq_vae_b200 import _native as N
+    lib = N.lib()
+    rng = np.random.default_rng(n + D + K)
+    src = rng.random((n, D), dtype=np.float32)
+    idx = np.full(n, 7 % K, np.int64) if collapsed else rng.integers(0, K, n)
+    if not collapsed and n > 10:
+        idx[: n // 3] = idx[0]                      # one heavy code next to many light ones
+    T = rng.random((K, D), dtype=np.float32)
+    gs = torch.tensor([0.5], device="cuda")
+    ts, ti, tT = torch.from_numpy(src).cuda(), torch.from_numpy(idx).cuda(), torch.from_numpy(T).cuda()
+    ws = torch.empty(lib.lipvq_segment_sum_ws_bytes(n, D, K), dtype=torch.uint8, device="cuda")
+    st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+    def run(table, alpha, scale, accumulate, init):
+        sums = torch.full((K, D), init, device="cuda")
+        counts = torch.empty(K, device="cuda")
+        N.check(lib.lipvq_segment_sum(ts.data_ptr(), ti.data_ptr(), table.data_ptr() if table is not None else None, alpha,
+                                      scale.data_ptr() if scale is not None else None, n, D, K, int(accumulate),
+                                      sums.data_ptr(), counts.data_ptr(), ws.data_ptr(), ws.numel(), st))
+        torch.cuda.synchronize()
+        return sums.cpu().numpy(), counts.cpu().numpy()
+
+    ref = np.zeros((K, D), np.float64)
+    np.add.at(ref, idx, src.astype(np.float64))
+    cnt = np.bincount(idx, minlength=K).astype(np.float64)
+    s1, c1 = run(None, 1.0, None, False, 123.0)
+    assert np.array_equal(c1, cnt)
+    assert orc.rel_err(s1, ref) < 1e-6
+    for _ in range(3):
+        s2, _ = run(None, 1.0, None, False, -5.0)
+        assert np.array_equal(s1, s2), "not bit-identical run to run"
+    # difference mode + device-side scale + accumulation: sums = 2 + 0.25 * 0.5 * sum (T[k] - src[n])
+    s3, _ = run(tT, 0.25, gs, True, 2.0)
+    ref3 = 2.0 + 0.125 * (cnt[:, None] * T.astype(np.float64) - ref)
+    assert np.abs(s3 - ref3).max() <= 2e-6 * max(1.0, np.abs(ref3).max())
+
+
+def test_backward_is_bit_identical_run_to_run():
+    """all 14 gradients of two identical training forwards/backwards agree bit for bit (deterministic codebook
+    gradient + the fixed-order wgrad reductions)."""
+    p = spread_params(12, 208, 1024, seed=4)
+    x = torch.from_numpy((2.0 * np.random.default_rng(9).random((30000, 12)) - 1.0).astype(np.float32)).cuda()
+    grads = []
+    for _ in range(2):
+        m = _model(p)
+        _, loss = m(x)
+        loss.backward()
+        torch.cuda.synchronize()
+        grads.append({k: t.grad.clone() for k, t in m.named_parameters()})
+    for k in grads[0]:
+        assert torch.equal(grads[0][k], grads[1][k]), k
