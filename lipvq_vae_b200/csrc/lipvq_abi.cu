@@ -58,6 +58,8 @@ static bool use_mlp_tc(const lipvq_dims_t *d) {
     return !simt && mlp::supported(d);
 }
 
+constexpr int kFwdMaxChunks = 8;   // row chunks of the overlapped large-batch forward
+
 static size_t max_splitk_floats(const lipvq_dims_t *d, int64_t n) {
     size_t m = 0;
     auto up = [&](int Nout, int Kin) { size_t v = splitk_ws_floats(n, Nout, Kin); if (v > m) m = v; };
@@ -86,7 +88,7 @@ static size_t workspace_bytes_impl(const lipvq_dims_t *d, int64_t n) {
     size_t bytes = fl * sizeof(float) + 64 * 256;    // alignment slack for the bump allocator
     bytes += vq_tensor_ws_bytes(n, d->D, d->K);
     bytes += N * sizeof(int64_t) + 4096;
-    bytes += align_up(2 * kQeBlocks * sizeof(float), 256) + 1024;
+    bytes += kFwdMaxChunks * align_up(2 * kQeBlocks * sizeof(float), 256) + 1024;
     bytes += mlp::enc_scratch_bytes(d->D) + 2048;
     bytes += small::scratch_bytes(n > 0 ? n : 1);
     if (seg::supported(d->K, n > 0 ? n : 1)) bytes += seg::plan_bytes(n > 0 ? n : 1, d->K, d->D > d->F ? d->D : d->F);
@@ -415,7 +417,7 @@ int lipvq_decoder_fwd(const lipvq_dims_t *d, const lipvq_params_t *p, const floa
 
 // scratch of lipvq_quantize_decode_fwd: [sse partials | xr_code when not supplied]
 static size_t qd_ws_bytes(const lipvq_dims_t *d) {
-    return align_up(2 * kQeBlocks * sizeof(float), 256) +
+    return kFwdMaxChunks * align_up(2 * kQeBlocks * sizeof(float), 256) +
            code_level_floats(d) * sizeof(float) + 256;
 }
 
@@ -640,6 +642,103 @@ int lipvq_encoder_bwd(const lipvq_dims_t *d, const lipvq_params_t *p, const floa
     return LIPVQ_OK;
 }
 
+
+// ---- chunked forward (large no-grad batches): the three big kernels of the forward are bound by three different
+// resources -- encoder: instruction issue, search: tensor pipe / TMEM reads, emit: HBM -- but the first two are
+// persistent one-CTA-per-SM kernels that cannot share an SM with each other.  The emit pass can: its CTAs are small.
+// So the batch is cut into row chunks (whole waves of 128-row tiles), encoder + search of chunk c+1 run on the caller's
+// stream while the emit pass of chunk c runs on the caller-supplied helper stream.  LIPVQ_FWD_CHUNKS=<n> overrides
+// (1 = off).
+static int forward_chunks(const lipvq_dims_t *d, int64_t n, int32_t search_mode) {
+    static const int env = [] { const char *e = getenv("LIPVQ_FWD_CHUNKS"); return e ? atoi(e) : 0; }();
+    const bool fuse = use_mlp_tc(d) && search_mode == LIPVQ_SEARCH_TENSOR && vq_tensor_supported(d->D, d->K) &&
+                      n <= (int64_t)0x7fffffff - tc::BM;
+    if (!fuse) return 1;
+    const int64_t tiles = (n + tc::BM - 1) / tc::BM;
+    int c = env > 0 ? env : (tiles >= 16 * kNumSMs ? 4 : 1);
+    if (c > kFwdMaxChunks) c = kFwdMaxChunks;
+    while (c > 1 && tiles / c < 2 * kNumSMs) --c;
+    return c;
+}
+
+static int forward_chunked(const lipvq_dims_t *d, const lipvq_params_t *p, const float *x, int64_t n, int64_t n_total,
+                           const lipvq_acts_t *a, double *sse, float *loss_out, int32_t *stats, float *part, float *R,
+                           void *es_ws, size_t es_bytes, int chunks, cudaStream_t st, cudaStream_t side,
+                           cudaEvent_t e_fork, cudaEvent_t e_join) {
+    if (!aligned16(a->scale) || !aligned16(a->Wn) || !aligned16(a->z_e) || !a->idx) return LIPVQ_EALIGN;
+    // row ranges: whole waves of tiles per chunk
+    const int64_t tiles = (n + tc::BM - 1) / tc::BM;
+    int64_t waves = (tiles + kNumSMs - 1) / kNumSMs;
+    const int64_t wpc = (waves + chunks - 1) / chunks;
+    const int64_t rows_pc = wpc * kNumSMs * tc::BM;
+    chunks = (int)((n + rows_pc - 1) / rows_pc);
+    if (es_bytes < mlp::enc_scratch_bytes(d->D) + 2048 + vq_tensor_ws_bytes(rows_pc < n ? rows_pc : n, d->D, d->K))
+        return LIPVQ_EWORKSPACE;
+    uint8_t *img = (uint8_t *)align_up((size_t)es_ws, 1024);
+    void *vq_ws = (void *)align_up((size_t)(img + mlp::enc_scratch_bytes(d->D)), 1024);
+    // helper stream: the per-code decoder table first (parameters only)
+    LIPVQ_CUDA_OK(cudaEventRecord(e_fork, st));
+    LIPVQ_CUDA_OK(cudaStreamWaitEvent(side, e_fork, 0));
+    LIPVQ_TRY(decoder_code_table(d, p, nullptr, nullptr, nullptr, nullptr, R, side));
+    // codebook operand once (mu, Eb, norms and the counters sit at chunk-independent offsets of the search workspace)
+    {
+        const tc::Geometry g0 = tc::geometry(rows_pc < n ? rows_pc : n, d->D, d->K);
+        const tc::Workspace w0 = tc::carve(vq_ws, g0);
+        LIPVQ_TRY(vq_tensor_prep(p->codebook, g0, w0, st));
+    }
+    const size_t pstride = align_up(2 * kQeBlocks * sizeof(float), 256) / sizeof(float);
+    ChunkGrids cg;
+    cg.n = chunks;
+    const float a_q = (float)(0.5 / ((double)(n_total > 0 ? n_total : 1) * d->D));
+    (void)a_q;
+    int *counters = nullptr;
+    for (int c = 0; c < chunks; ++c) {
+        const int64_t r0 = (int64_t)c * rows_pc, nc = (n - r0 < rows_pc ? n - r0 : rows_pc);
+        const tc::Geometry g = tc::geometry(nc, d->D, d->K);
+        const tc::Workspace w = tc::carve(vq_ws, g);
+        counters = w.counters;
+        if (c > 0) {
+            vq_counters_next_chunk_kernel<<<1, 32, 0, st>>>(w.counters);
+            LIPVQ_LAUNCH_OK();
+        }
+        LIPVQ_TRY(mlp::encoder_fused16_launch(d, p, x + r0 * d->F, nc, nullptr, nullptr, nullptr, nullptr, a->scale, a->Wn,
+                                              a->z_e + r0 * d->D, img, w.mu, w.Zb, w.zn, g.DKz, w.counters, st));
+        LIPVQ_TRY(vq_tensor_search(a->z_e + r0 * d->D, p->codebook, g, w, a->idx + r0, nullptr, nullptr, st));
+        // emit of this chunk on the helper stream, behind its search
+        LIPVQ_CUDA_OK(cudaEventRecord(e_fork, st));
+        LIPVQ_CUDA_OK(cudaStreamWaitEvent(side, e_fork, 0));
+        const int64_t etiles = (nc + QE_ROWS - 1) / QE_ROWS;
+        const int grid = (int)(etiles < kQeBlocks ? etiles : kQeBlocks);
+        cg.grid[c] = grid;
+        float *pc = part + (size_t)c * pstride;
+        float *zq = a->z_q ? a->z_q + r0 * d->D : nullptr;
+        float *xr = a->x_recon ? a->x_recon + r0 * d->F : nullptr;
+        {
+            ProfScope prof("quantize_emit_kernel", side);
+            if ((d->D & 3) == 0)
+                quantize_emit_kernel<true><<<grid, QE_THR, 0, side>>>(a->z_e + r0 * d->D, p->codebook, R, a->idx + r0,
+                                                                      x + r0 * d->F, nc, d->D, d->F, d->K, zq, xr, pc);
+            else
+                quantize_emit_kernel<false><<<grid, QE_THR, 0, side>>>(a->z_e + r0 * d->D, p->codebook, R, a->idx + r0,
+                                                                       x + r0 * d->F, nc, d->D, d->F, d->K, zq, xr, pc);
+            LIPVQ_LAUNCH_OK();
+        }
+    }
+    LIPVQ_CUDA_OK(cudaEventRecord(e_join, side));
+    LIPVQ_CUDA_OK(cudaStreamWaitEvent(st, e_join, 0));
+    if (stats) {
+        vq_counters_next_chunk_kernel<<<1, 32, 0, st>>>(counters);
+        LIPVQ_LAUNCH_OK();
+        vq_counters_report_kernel<<<1, 32, 0, st>>>(counters, stats);
+        LIPVQ_LAUNCH_OK();
+    }
+    const double nt = (double)(n_total > 0 ? n_total : 1);
+    partials2_chunks_to_double_kernel<<<1, 256, 0, st>>>(part, cg, (int)pstride, sse, loss_out, 1.0 / (nt * d->F),
+                                                         1.0 / (nt * d->D));
+    LIPVQ_LAUNCH_OK();
+    return LIPVQ_OK;
+}
+
 int lipvq_forward_fused(const lipvq_dims_t *d, const lipvq_params_t *p, const float *x, int64_t n,
                         int64_t n_total, int32_t search_mode, float *z_latent, int64_t *idx,
                         float *x_recon, float *loss_out, int32_t *stats, void *ws, size_t ws_bytes,
@@ -684,7 +783,13 @@ int lipvq_forward_fused(const lipvq_dims_t *d, const lipvq_params_t *p, const fl
     cudaEvent_t e_fork = (cudaEvent_t)ev_fork, e_join = (cudaEvent_t)ev_join;
     bool forked = false;
     if (side && e_fork && e_join) {
-        float *R = (float *)align_up((size_t)part + align_up(2 * kQeBlocks * sizeof(float), 256), 256);   // qd scratch tail
+        float *R = (float *)align_up((size_t)part + kFwdMaxChunks * align_up(2 * kQeBlocks * sizeof(float), 256), 256);   // qd scratch tail
+        // large batches on the fused tensor path: row chunks, the HBM-bound emit pass of chunk c on the helper stream
+        // under the issue-bound encoder / tensor-bound search kernels of chunk c+1
+        const int chunks = forward_chunks(d, n, search_mode);
+        if (chunks > 1)
+            return forward_chunked(d, p, x, n, n_total, &a, sse, loss_out, stats, part, R, es_ws, es_bytes, chunks, st, side,
+                                   e_fork, e_join);
         LIPVQ_CUDA_OK(cudaEventRecord(e_fork, st));
         LIPVQ_CUDA_OK(cudaStreamWaitEvent(side, e_fork, 0));
         LIPVQ_TRY(decoder_code_table(d, p, nullptr, nullptr, nullptr, nullptr, R, side));

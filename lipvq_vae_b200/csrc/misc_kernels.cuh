@@ -206,6 +206,50 @@ __global__ void partials2_to_double_kernel(const float *__restrict__ part, int n
     }
 }
 
+// the same for a forward that ran its emit pass in up to 8 row chunks (each chunk's partials: [2][grid[c]] floats at
+// part + c * stride): chunk by chunk, fixed order inside a chunk, in double.
+struct ChunkGrids { int n; int grid[8]; };
+__global__ void partials2_chunks_to_double_kernel(const float *__restrict__ part, ChunkGrids cg, int stride,
+                                                  double *__restrict__ sse, float *__restrict__ loss_out, double inv_nf,
+                                                  double inv_nd) {
+    __shared__ double sm[2][8];
+    double q = 0.0, r = 0.0;
+    for (int c = 0; c < cg.n; ++c) {
+        const float *pc = part + (size_t)c * stride;
+        const int n = cg.grid[c];
+        double a = 0.0, b = 0.0;
+        for (int i = threadIdx.x; i < n; i += blockDim.x) { a += (double)pc[i]; b += (double)pc[n + i]; }
+        a = warp_sum_d(a); b = warp_sum_d(b);
+        __syncthreads();
+        if ((threadIdx.x & 31) == 0) { sm[0][threadIdx.x >> 5] = a; sm[1][threadIdx.x >> 5] = b; }
+        __syncthreads();
+        if (threadIdx.x == 0)
+            for (int w = 0; w < (int)(blockDim.x >> 5); ++w) { q += sm[0][w]; r += sm[1][w]; }
+    }
+    if (threadIdx.x == 0) {
+        sse[0] = r; sse[1] = q;
+        if (loss_out) {
+            const double recon = r * inv_nf, commit = q * inv_nd;
+            loss_out[0] = (float)(recon + 0.25 * commit + 0.25 * commit);
+            loss_out[1] = (float)recon;
+            loss_out[2] = (float)commit;
+            loss_out[3] = (float)commit;
+        }
+    }
+}
+
+// search counters between two row chunks of one forward: the list lengths [0] (exact scan) and [4] (rescore) restart,
+// their totals accumulate in [5] and [7]; [1] codes rescored, [2] rows resolved directly and [3] the range flag carry on
+__global__ void vq_counters_next_chunk_kernel(int *__restrict__ counters) {
+    if (threadIdx.x == 0) {
+        counters[5] += counters[0]; counters[7] += counters[4];
+        counters[0] = 0; counters[4] = 0;
+    }
+}
+__global__ void vq_counters_report_kernel(const int *__restrict__ counters, int *__restrict__ stats) {
+    if (threadIdx.x == 0) { stats[0] = counters[5]; stats[1] = counters[1]; stats[2] = counters[2]; stats[3] = counters[3]; }
+}
+
 // ---------------------------------------------------------------- per-code decoder table (k7)
 // xr_code = to_output(decoder(E)) for all K codes (v5:62-68, 75-76 on the K distinct values of z_q).  K rows are
 // too few for the tensor cores to pay off (a 128-row UMMA tile would keep 8 SMs busy for 40 us), so this runs on

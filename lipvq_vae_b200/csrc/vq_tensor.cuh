@@ -290,7 +290,8 @@ struct SmemLayout {
     static constexpr int B_BYTES = STAGES * B_ST_BYTES;
     static constexpr int BAR_OFF = A_BYTES + B_BYTES;
     static constexpr int NBARS = 2 * A_BUFS + 2 * STAGES + 4;
-    static constexpr int TOTAL = BAR_OFF + NBARS * 8 + 16 + 1024;   // + tmem ptr + alignment slack
+    static constexpr int RES_OFF = BAR_OFF + NBARS * 8 + 16;        // row exchange of the in-kernel resolve: 3 x 128 words
+    static constexpr int TOTAL = RES_OFF + 3 * BM * 4 + 1024;       // + alignment slack
 };
 
 constexpr float RESC_C1 = OP_U4 * 1.004f;       // 2*(2u+u^2), u = unit roundoff of the operand type
@@ -324,13 +325,25 @@ __device__ __forceinline__ float min8(const uint32_t *r) {
     return ptx::fmin3(a, b, fminf(__uint_as_float(r[6]), __uint_as_float(r[7])));
 }
 
+// order-preserving map float -> unsigned (atomicMin on the key == min on the float) and back
+__device__ __forceinline__ unsigned fkey(float f) {
+    const unsigned b = __float_as_uint(f);
+    return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+}
+__device__ __forceinline__ float fkey_inv(unsigned k) {
+    return __uint_as_float((k & 0x80000000u) ? (k & 0x7fffffffu) : ~k);
+}
+
 template <int NKB, int A_BUFS, int STAGES>
 __global__ void __launch_bounds__(NT, 1) vq_tc_kernel(const __grid_constant__ CUtensorMap tmapA,
                                                        const __grid_constant__ CUtensorMap tmapB,
                                                        int64_t n_rows, int n_tiles, int nct, int nk16,
                                                        const float *__restrict__ zn, const float *__restrict__ emax_p,
                                                        float abs_c, uint2 *__restrict__ cand,
-                                                       int *__restrict__ cand_meta) {
+                                                       int *__restrict__ cand_meta, int K,
+                                                       int64_t *__restrict__ idx_out, int want_d2,
+                                                       int *__restrict__ resc_list, int *__restrict__ exact_list,
+                                                       int *__restrict__ counters) {
     using L = SmemLayout<NKB, A_BUFS, STAGES>;
     extern __shared__ uint8_t smem_raw[];
     const uint32_t raw = ptx::smem_u32(smem_raw);
@@ -345,8 +358,13 @@ __global__ void __launch_bounds__(NT, 1) vq_tc_kernel(const __grid_constant__ CU
     auto t_full = [&](int i) { return sBar + 8u * (2 * A_BUFS + 2 * STAGES + i); };
     auto t_empty = [&](int i) { return sBar + 8u * (2 * A_BUFS + 2 * STAGES + 2 + i); };
     volatile uint32_t *tmem_ptr = reinterpret_cast<volatile uint32_t *>(gen + L::BAR_OFF + L::NBARS * 8);
+    // per-row exchange between the four column parts of a row (in-kernel resolve): ordered key of the row minimum,
+    // number of listed elements inside the final window, lowest such code
+    unsigned *s_min = reinterpret_cast<unsigned *>(gen + L::RES_OFF);
+    int *s_nin = reinterpret_cast<int *>(s_min + BM), *s_code = s_nin + BM;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (threadIdx.x < BM) { s_min[threadIdx.x] = 0xffffffffu; s_nin[threadIdx.x] = 0; s_code[threadIdx.x] = 0x7fffffff; }
 
     if (warp == 0 && lane == 0) {
         ptx::tma_prefetch_desc(&tmapA);
@@ -431,6 +449,7 @@ __global__ void __launch_bounds__(NT, 1) vq_tc_kernel(const __grid_constant__ CU
         constexpr int PW = BN / NPART;            // columns per part
         int acc = 0, accph = 0;
         const float emax = __ldg(emax_p);
+        const bool range_bad = __ldg(counters + 3) != 0;   // set by the operand passes, which finished before this launch
         for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
             const int r_in = quarter * 32 + lane;
             const int64_t row = (int64_t)tile * BM + r_in;
@@ -477,6 +496,45 @@ __global__ void __launch_bounds__(NT, 1) vq_tc_kernel(const __grid_constant__ CU
                 if (++acc == 2) { acc = 0; accph ^= 1; }
             }
             if (row_ok) cand_meta[((size_t)tile * NPART + part) * BM + r_in] = cnt;
+            // ---- resolve (was a separate kernel): the four parts of a row agree on the row minimum, count the listed
+            // elements inside the FINAL window tau(row) and decide: exactly one -> it IS the nearest code, idx is
+            // written here; several -> fp32 rescore list; list overflow / range flag -> exact scan list.
+            asm volatile("bar.sync 1, 512;" ::: "memory");      // the previous tile's decision (and reset) is done
+            if (row_ok) atomicMin(&s_min[r_in], fkey(gb));
+            asm volatile("bar.sync 1, 512;" ::: "memory");
+            if (row_ok) {
+                int nin = 0, code = 0x7fffffff;
+                if (cnt > LCAP) nin = 1 << 20;
+                else {
+                    const float T = fkey_inv(s_min[r_in]) + tau;
+                    for (int e = 0; e < cnt; ++e) {
+                        const uint2 x = out[e * BM];                       // (this thread's own stores)
+                        if (__uint_as_float(x.x) <= T) {
+                            const int c0 = (int)(x.y & 0xffffffu);
+                            uint32_t m = x.y >> 24;
+                            if (c0 + 8 > K) m &= (1u << max(K - c0, 0)) - 1u;     // padding codes of the last chunk
+                            nin += __popc(m);
+                            if (m) code = min(code, c0 + __ffs(m) - 1);
+                        }
+                    }
+                }
+                if (nin) atomicAdd(&s_nin[r_in], nin);
+                if (code != 0x7fffffff) atomicMin(&s_code[r_in], code);
+            }
+            asm volatile("bar.sync 1, 512;" ::: "memory");
+            if (part == 0) {
+                bool fast = false;
+                if (row_ok) {
+                    const int nin = s_nin[r_in];
+                    if (range_bad || nin >= (1 << 20) || nin == 0 || nin > 64)   // 0 cannot happen for finite inputs
+                        exact_list[atomicAdd(counters + 0, 1)] = (int)row;
+                    else if (nin == 1 && !want_d2) { idx_out[row] = (int64_t)s_code[r_in]; fast = true; }
+                    else resc_list[atomicAdd(counters + 4, 1)] = (int)row;
+                }
+                s_min[r_in] = 0xffffffffu; s_nin[r_in] = 0; s_code[r_in] = 0x7fffffff;
+                const unsigned nf = __popc(__ballot_sync(0xffffffffu, fast));
+                if (lane == 0 && nf) atomicAdd(counters + 2, (int)nf);
+            }
         }
     }
     ptx::tc_fence_before();
@@ -494,65 +552,6 @@ __global__ void __launch_bounds__(NT, 1) vq_tc_kernel(const __grid_constant__ CU
 //
 // counters: [0] rows sent to the exact scan, [1] codes rescored, [2] rows resolved without rescoring,
 //           [3] operand-range flag, [4] rows on the rescore list.
-
-// 3a. one THREAD per row (coalesced record reads): a row with exactly one listed element inside its final
-// window is decided -- that element IS the nearest code; everything else goes on a work list.
-__global__ void __launch_bounds__(256) vq_resolve_kernel(int64_t n_rows, int K, const uint2 *__restrict__ cand,
-                                                         const int *__restrict__ cand_meta,
-                                                         const float *__restrict__ zn,
-                                                         const float *__restrict__ emax_p, float abs_c,
-                                                         int64_t *__restrict__ idx_out, int want_d2,
-                                                         int *__restrict__ resc_list, int *__restrict__ exact_list,
-                                                         int *__restrict__ counters) {
-    const float emax = __ldg(emax_p);
-    const bool range_bad = counters[3] != 0;   // set by the operand passes, which finished before this launch
-    int n_fast = 0;
-    for (int64_t row = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; row < n_rows;
-         row += (int64_t)gridDim.x * blockDim.x) {
-        const int64_t tile = row >> 7;
-        const int r = (int)(row & 127);
-        int cn[NPART];
-        bool bad = range_bad;
-#pragma unroll
-        for (int p = 0; p < NPART; ++p) {
-            cn[p] = __ldg(cand_meta + (tile * NPART + p) * BM + r);
-            bad |= cn[p] > LCAP;
-        }
-        if (bad) {
-            exact_list[atomicAdd(counters + 0, 1)] = (int)row;
-            continue;
-        }
-        const uint2 *e0 = cand + tile * NPART * LCAP * BM + r;
-        float gb = BIG;
-#pragma unroll
-        for (int p = 0; p < NPART; ++p)
-            for (int e = 0; e < cn[p]; ++e) gb = fminf(gb, __uint_as_float(__ldg(e0 + (p * LCAP + e) * BM).x));
-        const float T = gb + tau_of(__ldg(zn + row), emax, abs_c);
-        int nin = 0, code = 0;
-#pragma unroll
-        for (int p = 0; p < NPART; ++p)
-            for (int e = 0; e < cn[p]; ++e) {
-                const uint2 x = __ldg(e0 + (p * LCAP + e) * BM);
-                if (__uint_as_float(x.x) <= T) {
-                    const int c0 = (int)(x.y & 0xffffffu);
-                    uint32_t m = x.y >> 24;
-                    if (c0 + 8 > K) m &= (1u << max(K - c0, 0)) - 1u;     // padding codes of the last chunk
-                    nin += __popc(m);
-                    if (m) code = c0 + __ffs(m) - 1;
-                }
-            }
-        if (nin == 1 && !want_d2) {
-            idx_out[row] = (int64_t)code;
-            ++n_fast;
-        } else if (nin == 0 || nin > 64) {      // 0 cannot happen for finite inputs; > 64 exceeds the warp list
-            exact_list[atomicAdd(counters + 0, 1)] = (int)row;
-        } else {
-            resc_list[atomicAdd(counters + 4, 1)] = (int)row;
-        }
-    }
-    n_fast = (int)warp_sum((float)n_fast);
-    if ((threadIdx.x & 31) == 0 && n_fast) atomicAdd(counters + 2, n_fast);
-}
 
 // 3b. one WARP per listed row: the listed elements inside the window (<= 64) are rescored NG at a time in fp32
 // direct form sum (z-e)^2 (the reference's arithmetic, v5:41-45); the first minimal index wins.
@@ -722,7 +721,7 @@ inline Workspace carve(void *ws, const Geometry &g) {
 
 template <int NKB, int A_BUFS, int STAGES>
 inline int launch_tc(const CUtensorMap &ta, const CUtensorMap &tb, const Geometry &g, const Workspace &w,
-                     cudaStream_t st) {
+                     int64_t *idx, bool want_d2, cudaStream_t st) {
     using L = SmemLayout<NKB, A_BUFS, STAGES>;
     auto kern = vq_tc_kernel<NKB, A_BUFS, STAGES>;
     // (the attribute is per device and the call is cheap: set it on every launch, as set_smem in mlp_tc.cuh does)
@@ -730,7 +729,8 @@ inline int launch_tc(const CUtensorMap &ta, const CUtensorMap &tb, const Geometr
     const int grid = (int)(g.n_tiles < kNumSMs ? g.n_tiles : kNumSMs);
     ProfScope prof("vq_tc_kernel", st);
     kern<<<grid, NT, L::TOTAL, st>>>(ta, tb, g.n, (int)g.n_tiles, g.nct, g.NK16, w.zn, w.emax,
-                                     OP_ABS * sqrtf((float)g.D), w.cand, w.cand_meta);
+                                     OP_ABS * sqrtf((float)g.D), w.cand, w.cand_meta, g.K, idx, want_d2 ? 1 : 0,
+                                     w.resc_list, w.list, w.counters);
     LIPVQ_LAUNCH_OK();
     return LIPVQ_OK;
 }
@@ -767,23 +767,15 @@ inline int vq_tensor_search(const float *z, const float *E, const tc::Geometry &
     LIPVQ_TRY(make_tmap(&tb, w.Eb, (uint64_t)g.Kp, (uint64_t)g.DKp, BN));
     int rc = LIPVQ_ESHAPE;
     switch (g.NKB) {
-        case 1: rc = launch_tc<1, 2, 6>(ta, tb, g, w, st); break;
-        case 2: rc = launch_tc<2, 2, 5>(ta, tb, g, w, st); break;
-        case 3: rc = launch_tc<3, 2, 4>(ta, tb, g, w, st); break;
-        case 4: rc = launch_tc<4, 2, 3>(ta, tb, g, w, st); break;
-        case 5: rc = launch_tc<5, 1, 4>(ta, tb, g, w, st); break;
+        case 1: rc = launch_tc<1, 2, 6>(ta, tb, g, w, idx, d2 != nullptr, st); break;
+        case 2: rc = launch_tc<2, 2, 5>(ta, tb, g, w, idx, d2 != nullptr, st); break;
+        case 3: rc = launch_tc<3, 2, 4>(ta, tb, g, w, idx, d2 != nullptr, st); break;
+        case 4: rc = launch_tc<4, 2, 3>(ta, tb, g, w, idx, d2 != nullptr, st); break;
+        case 5: rc = launch_tc<5, 1, 4>(ta, tb, g, w, idx, d2 != nullptr, st); break;
         default: break;
     }
     LIPVQ_TRY(rc);
     const float abs_c = OP_ABS * sqrtf((float)D);
-    {
-        int64_t blocks = (n + 255) / 256;
-        if (blocks > 8 * kNumSMs) blocks = 8 * kNumSMs;
-        ProfScope prof("vq_resolve_kernel", st);
-        vq_resolve_kernel<<<(unsigned)blocks, 256, 0, st>>>(n, K, w.cand, w.cand_meta, w.zn, w.emax, abs_c, idx,
-                                                            d2 != nullptr, w.resc_list, w.list, w.counters);
-        LIPVQ_LAUNCH_OK();
-    }
     {
         int64_t blocks = (n + 7) / 8;
         if (blocks > 8 * kNumSMs) blocks = 8 * kNumSMs;   // grid-stride over the device-side list length
