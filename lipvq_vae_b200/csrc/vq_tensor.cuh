@@ -32,6 +32,7 @@ constexpr int UK = 16;           // UMMA K for 16-bit inputs
 constexpr int A_KB_BYTES = BM * 128;
 constexpr int B_ST_BYTES = BN * 128;
 constexpr int NT = 640;          // warp0 TMA, warp1 MMA, warp2 TMEM alloc, warps 4..19 epilogue
+constexpr int NT_CONV = 768;     // + warps 20..23: fp32 rows -> fp16 operand tile in shared memory (standalone search)
 constexpr int NPART = 4;         // column parts of an accumulator (64 columns each), one epilogue warp per (quarter, part)
 constexpr int NCAND = 4;         // chunk minima kept per (row, column half, code tile)
 constexpr int LCAP = 16;         // candidate entries kept per (row, column half)
@@ -334,8 +335,11 @@ __device__ __forceinline__ float fkey_inv(unsigned k) {
     return __uint_as_float((k & 0x80000000u) ? (k & 0x7fffffffu) : ~k);
 }
 
-template <int NKB, int A_BUFS, int STAGES>
-__global__ void __launch_bounds__(NT, 1) vq_tc_kernel(const __grid_constant__ CUtensorMap tmapA,
+// CONV: the row operand is not read from a pre-converted fp16 image (tmapA) but built in shared memory by four
+// converter warps straight from the fp32 rows z (thread = row; [fp16(z - mu) | 1 1 1 | 0..] in the TMA/UMMA 128-byte
+// swizzle, zn = ||z - mu|| to global): the standalone search API needs no separate conversion pass over z.
+template <int NKB, int A_BUFS, int STAGES, bool CONV = false>
+__global__ void __launch_bounds__(CONV ? NT_CONV : NT, 1) vq_tc_kernel(const __grid_constant__ CUtensorMap tmapA,
                                                        const __grid_constant__ CUtensorMap tmapB,
                                                        int64_t n_rows, int n_tiles, int nct, int nk16,
                                                        const float *__restrict__ zn, const float *__restrict__ emax_p,
@@ -343,7 +347,10 @@ __global__ void __launch_bounds__(NT, 1) vq_tc_kernel(const __grid_constant__ CU
                                                        int *__restrict__ cand_meta, int K,
                                                        int64_t *__restrict__ idx_out, int want_d2,
                                                        int *__restrict__ resc_list, int *__restrict__ exact_list,
-                                                       int *__restrict__ counters) {
+                                                       int *__restrict__ counters,
+                                                       const float *__restrict__ zsrc = nullptr,
+                                                       const float *__restrict__ mu = nullptr, int D = 0,
+                                                       float *__restrict__ zn_out = nullptr) {
     using L = SmemLayout<NKB, A_BUFS, STAGES>;
     extern __shared__ uint8_t smem_raw[];
     const uint32_t raw = ptx::smem_u32(smem_raw);
@@ -369,7 +376,7 @@ __global__ void __launch_bounds__(NT, 1) vq_tc_kernel(const __grid_constant__ CU
     if (warp == 0 && lane == 0) {
         ptx::tma_prefetch_desc(&tmapA);
         ptx::tma_prefetch_desc(&tmapB);
-        for (int i = 0; i < A_BUFS; ++i) { ptx::mbar_init(a_full(i), 1); ptx::mbar_init(a_empty(i), 1); }
+        for (int i = 0; i < A_BUFS; ++i) { ptx::mbar_init(a_full(i), CONV ? 4 : 1); ptx::mbar_init(a_empty(i), 1); }
         for (int i = 0; i < STAGES; ++i) { ptx::mbar_init(b_full(i), 1); ptx::mbar_init(b_empty(i), 1); }
         for (int i = 0; i < 2; ++i) { ptx::mbar_init(t_full(i), 1); ptx::mbar_init(t_empty(i), 4 * NPART); }
         ptx::fence_barrier_init();
@@ -392,11 +399,13 @@ __global__ void __launch_bounds__(NT, 1) vq_tc_kernel(const __grid_constant__ CU
                     ptx::tma_load_2d(&tmapA, a_full(ab), sA + (ab * NKB + kb) * A_KB_BYTES, kb * KBLK, tile * BM);
                 if (++ab == A_BUFS) { ab = 0; aph ^= 1; }
             };
-            if (A_BUFS > 1 && (int)blockIdx.x < n_tiles) load_a(blockIdx.x);
+            if (!CONV && A_BUFS > 1 && (int)blockIdx.x < n_tiles) load_a(blockIdx.x);
             for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
                 // double-buffered rows: fetch the NEXT tile's rows before streaming this tile's codebook
-                if (A_BUFS > 1) { if (tile + (int)gridDim.x < n_tiles) load_a(tile + gridDim.x); }
-                else load_a(tile);
+                if (!CONV) {
+                    if (A_BUFS > 1) { if (tile + (int)gridDim.x < n_tiles) load_a(tile + gridDim.x); }
+                    else load_a(tile);
+                }
                 for (int c = 0; c < nct; ++c)
                     for (int kb = 0; kb < NKB; ++kb) {
                         ptx::mbar_wait(b_empty(st), sph ^ 1);
@@ -440,6 +449,79 @@ __global__ void __launch_bounds__(NT, 1) vq_tc_kernel(const __grid_constant__ CU
                 if (++ab == A_BUFS) { ab = 0; aph ^= 1; }
             }
         }
+    } else if (CONV && warp >= 20) {
+        // ===== converter: thread = row of the tile; 8 columns (32 B in, 16 B out) per step =====
+        const int r = (warp - 20) * 32 + lane;
+        const int cpr = nk16 * 2;                       // 8-column pieces per row (whole MMA K steps)
+        const bool vec = (D & 3) == 0;
+        const uint32_t sw = (uint32_t)(r & 7);
+        int ab = 0, aph = 0;
+        bool bad = false;
+        for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+            const int64_t row = (int64_t)tile * BM + r;
+            const bool ok = row < n_rows;
+            const float *zr = zsrc + row * D;
+            ptx::mbar_wait(a_empty(ab), aph ^ 1);
+            float ss = 0.f;
+            for (int c0 = 0; c0 < cpr; c0 += 4) {       // 4 pieces = 8 independent 16-byte loads in flight
+                float v[4][8];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    const int d0 = (c0 + u) * 8;
+#pragma unroll
+                    for (int q = 0; q < 2; ++q) {
+                        const int d = d0 + 4 * q;
+                        float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
+                        if (ok && c0 + u < cpr && d < D) {
+                            if (vec) t = __ldg(reinterpret_cast<const float4 *>(zr + d));
+                            else {
+                                t.x = __ldg(zr + d);
+                                if (d + 1 < D) t.y = __ldg(zr + d + 1);
+                                if (d + 2 < D) t.z = __ldg(zr + d + 2);
+                                if (d + 3 < D) t.w = __ldg(zr + d + 3);
+                            }
+                        }
+                        v[u][4 * q] = t.x; v[u][4 * q + 1] = t.y; v[u][4 * q + 2] = t.z; v[u][4 * q + 3] = t.w;
+                    }
+                }
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    const int c = c0 + u;
+                    if (c < cpr) {
+                        const int d0 = c * 8;
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) {
+                            const int d = d0 + i;
+                            if (ok && d < D) {
+                                v[u][i] -= __ldg(mu + d);
+                                ss = fmaf(v[u][i], v[u][i], ss);
+                                bad |= !(fabsf(v[u][i]) <= OP_MAX);     // (also catches NaN)
+                            } else {
+                                v[u][i] = (ok && d < D + 3) ? 1.0f : 0.f;
+                            }
+                        }
+                        uint32_t o[4];
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) {
+                            const op2_t pr = f2op2(v[u][2 * i], v[u][2 * i + 1]);
+                            o[i] = *reinterpret_cast<const uint32_t *>(&pr);
+                        }
+                        const uint32_t dst = sA + (uint32_t)((ab * NKB + (c >> 3)) * A_KB_BYTES) + (uint32_t)r * 128u +
+                                             ((((uint32_t)c & 7u) ^ sw) << 4);
+                        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(dst), "r"(o[0]), "r"(o[1]), "r"(o[2]),
+                                     "r"(o[3])
+                                     : "memory");
+                    }
+                }
+            }
+            if (ok) zn_out[row] = bad ? -1.0f : sqrtf(ss);    // negative: this row takes the exact scan
+            bad = false;
+            __threadfence();                 // zn is read by this CTA's epilogue warps (ld.cg) and by the rescore pass
+            ptx::fence_proxy_async();        // the tile is read by the tensor core through the async proxy
+            __syncwarp();
+            if (lane == 0) ptx::mbar_arrive(a_full(ab));
+            if (++ab == A_BUFS) { ab = 0; aph ^= 1; }
+        }
     } else if (warp >= 4) {
         // ===== epilogue: 16 warps; warp%4 = TMEM lane quarter, (warp-4)/4 = 64-column part =====
         // (TMEM reads run at 64 B/clk/SM: 2048 cycles per 128x256 accumulator, the floor of this kernel for
@@ -449,12 +531,17 @@ __global__ void __launch_bounds__(NT, 1) vq_tc_kernel(const __grid_constant__ CU
         constexpr int PW = BN / NPART;            // columns per part
         int acc = 0, accph = 0;
         const float emax = __ldg(emax_p);
-        const bool range_bad = __ldg(counters + 3) != 0;   // set by the operand passes, which finished before this launch
+        // set by the operand passes, which finished before this launch (CONV: a row whose own operand left the fp16
+        // range is flagged by its converter thread through a negative zn and goes to the exact scan by itself)
+        const bool range_bad = __ldg(counters + 3) != 0;
         for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
             const int r_in = quarter * 32 + lane;
             const int64_t row = (int64_t)tile * BM + r_in;
             const bool row_ok = row < n_rows;
-            const float znr = row_ok ? __ldg(zn + row) : 0.f;
+            // (CONV: zn of this tile was written by this CTA's converter warps before the tile's first MMA was issued)
+            float znr = row_ok ? (CONV ? __ldcg(zn + row) : __ldg(zn + row)) : 0.f;
+            const bool row_bad = CONV && !(znr >= 0.f);
+            if (row_bad) znr = 0.f;
             const float tau = tau_of(znr, emax, abs_c);
             uint2 *out = cand + ((size_t)tile * NPART + part) * LCAP * BM + r_in;
             float gb = BIG;
@@ -526,7 +613,7 @@ __global__ void __launch_bounds__(NT, 1) vq_tc_kernel(const __grid_constant__ CU
                 bool fast = false;
                 if (row_ok) {
                     const int nin = s_nin[r_in];
-                    if (range_bad || nin >= (1 << 20) || nin == 0 || nin > 64)   // 0 cannot happen for finite inputs
+                    if (range_bad || row_bad || nin >= (1 << 20) || nin == 0 || nin > 64)   // 0 cannot happen for finite inputs
                         exact_list[atomicAdd(counters + 0, 1)] = (int)row;
                     else if (nin == 1 && !want_d2) { idx_out[row] = (int64_t)s_code[r_in]; fast = true; }
                     else resc_list[atomicAdd(counters + 4, 1)] = (int)row;
@@ -719,18 +806,19 @@ inline Workspace carve(void *ws, const Geometry &g) {
     return w;
 }
 
-template <int NKB, int A_BUFS, int STAGES>
+template <int NKB, int A_BUFS, int STAGES, bool CONV = false>
 inline int launch_tc(const CUtensorMap &ta, const CUtensorMap &tb, const Geometry &g, const Workspace &w,
-                     int64_t *idx, bool want_d2, cudaStream_t st) {
+                     int64_t *idx, bool want_d2, cudaStream_t st, const float *zsrc = nullptr) {
     using L = SmemLayout<NKB, A_BUFS, STAGES>;
-    auto kern = vq_tc_kernel<NKB, A_BUFS, STAGES>;
+    auto kern = vq_tc_kernel<NKB, A_BUFS, STAGES, CONV>;
     // (the attribute is per device and the call is cheap: set it on every launch, as set_smem in mlp_tc.cuh does)
     LIPVQ_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::TOTAL));
     const int grid = (int)(g.n_tiles < kNumSMs ? g.n_tiles : kNumSMs);
     ProfScope prof("vq_tc_kernel", st);
-    kern<<<grid, NT, L::TOTAL, st>>>(ta, tb, g.n, (int)g.n_tiles, g.nct, g.NK16, w.zn, w.emax,
-                                     OP_ABS * sqrtf((float)g.D), w.cand, w.cand_meta, g.K, idx, want_d2 ? 1 : 0,
-                                     w.resc_list, w.list, w.counters);
+    kern<<<grid, CONV ? NT_CONV : NT, L::TOTAL, st>>>(ta, tb, g.n, (int)g.n_tiles, g.nct, g.NK16, w.zn, w.emax,
+                                                      OP_ABS * sqrtf((float)g.D), w.cand, w.cand_meta, g.K, idx,
+                                                      want_d2 ? 1 : 0, w.resc_list, w.list, w.counters, zsrc, w.mu, g.D,
+                                                      w.zn);
     LIPVQ_LAUNCH_OK();
     return LIPVQ_OK;
 }
@@ -757,16 +845,27 @@ inline int vq_tensor_prep(const float *E, const tc::Geometry &g, const tc::Works
 }
 
 // passes 2-3 (+ exact tier) on operands already in the workspace (Zb, zn written by pass 1 or by the encoder)
+// conv: the row operand is built inside the search kernel from the fp32 rows z (standalone API); otherwise it is
+// read from the fp16 image w.Zb / w.zn that the fused encoder (or vq_convert_z) wrote
 inline int vq_tensor_search(const float *z, const float *E, const tc::Geometry &g, const tc::Workspace &w,
-                            int64_t *idx, float *d2, int32_t *stats, cudaStream_t st) {
+                            int64_t *idx, float *d2, int32_t *stats, cudaStream_t st, bool conv = false) {
     using namespace tc;
     const int64_t n = g.n;
     const int D = g.D, K = g.K;
     CUtensorMap ta, tb;
-    LIPVQ_TRY(make_tmap(&ta, w.Zb, (uint64_t)g.Np, (uint64_t)g.DKz, BM));
     LIPVQ_TRY(make_tmap(&tb, w.Eb, (uint64_t)g.Kp, (uint64_t)g.DKp, BN));
+    if (conv) ta = tb;                    // (unused by the kernel in this mode)
+    else LIPVQ_TRY(make_tmap(&ta, w.Zb, (uint64_t)g.Np, (uint64_t)g.DKz, BM));
     int rc = LIPVQ_ESHAPE;
-    switch (g.NKB) {
+    if (conv) switch (g.NKB) {
+        case 1: rc = launch_tc<1, 2, 6, true>(ta, tb, g, w, idx, d2 != nullptr, st, z); break;
+        case 2: rc = launch_tc<2, 2, 5, true>(ta, tb, g, w, idx, d2 != nullptr, st, z); break;
+        case 3: rc = launch_tc<3, 2, 4, true>(ta, tb, g, w, idx, d2 != nullptr, st, z); break;
+        case 4: rc = launch_tc<4, 2, 3, true>(ta, tb, g, w, idx, d2 != nullptr, st, z); break;
+        case 5: rc = launch_tc<5, 1, 4, true>(ta, tb, g, w, idx, d2 != nullptr, st, z); break;
+        default: break;
+    }
+    else switch (g.NKB) {
         case 1: rc = launch_tc<1, 2, 6>(ta, tb, g, w, idx, d2 != nullptr, st); break;
         case 2: rc = launch_tc<2, 2, 5>(ta, tb, g, w, idx, d2 != nullptr, st); break;
         case 3: rc = launch_tc<3, 2, 4>(ta, tb, g, w, idx, d2 != nullptr, st); break;
@@ -801,6 +900,9 @@ inline int vq_tensor_launch(const float *z, const float *E, int64_t n, int D, in
     const Geometry g = geometry(n, D, K);
     const Workspace w = carve((void *)align_up((size_t)ws, 1024), g);
     LIPVQ_TRY(vq_tensor_prep(E, g, w, st));
+    // LIPVQ_VQ_CONVERT=pass restores the separate conversion pass over z (A/B timing)
+    static const bool sep = [] { const char *e = getenv("LIPVQ_VQ_CONVERT"); return e && !strcmp(e, "pass"); }();
+    if (!sep) return vq_tensor_search(z, E, g, w, idx, d2, stats, st, true);
     {
         const int cpr = g.DKz >> 3;
         const int rpb = cpr <= 32 ? 8 * (32 / cpr) : 256 / cpr;
