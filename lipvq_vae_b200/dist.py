@@ -182,11 +182,17 @@ class TokenizerTrainer:
     ``overlap=False`` issues ONE all-reduce after the whole backward (the round-1 behaviour) for A/B timing."""
 
     def __init__(self, model, process_group=None, lr=1e-3, weight_decay=1e-4, ema_codebook=False, ema_gamma=0.99,
-                 overlap=True):
+                 overlap=True, concurrent_backward=False):
         self.dp = DataParallelTokenizer(model, process_group)
         self.opt = FlatAdamW(model, lr=lr, weight_decay=weight_decay)
         self.model = model
         self.overlap = overlap
+        # The decoder-side backward (per-code GEMMs + the per-code segment sums) and the encoder-side backward (the
+        # N-row GEMMs) depend only on the forward and write disjoint gradient slices: with concurrent_backward they run
+        # on two streams (each with its own workspace), the small decoder-side kernels filling the SM and HBM slack the
+        # persistent encoder-side kernels leave.
+        self.concurrent_backward = concurrent_backward
+        self._side = None
         # EMA mode (extension, SURVEY 8a row 11): the codebook follows the EMA of its clusters instead of AdamW --
         # its gradient is zeroed in the bucket and counts[K] + sums[K,D] are all-reduced in one more collective
         self.ema_codebook, self.ema_gamma = ema_codebook, ema_gamma
@@ -225,9 +231,20 @@ class TokenizerTrainer:
             counts, sums = m.codebook_statistics()
             self.dp.allreduce_codebook_stats(counts, sums)
         b.extra.copy_(stats[0:1])
-        T.train_backward_decoder(saved, self._gs, b.views)
-        w1 = self._all_reduce(b.flat[self._split:], True) if self.overlap else None     # codebook .. to_output + loss
-        T.train_backward_encoder(saved, self._gs, b.views)
+        if self.concurrent_backward:
+            main = torch.cuda.current_stream(x.device)
+            if self._side is None:
+                self._side = torch.cuda.Stream(device=x.device)
+            self._side.wait_stream(main)
+            with torch.cuda.stream(self._side):
+                T.train_backward_decoder(saved, self._gs, b.views)
+                w1 = self._all_reduce(b.flat[self._split:], True) if self.overlap else None
+            T.train_backward_encoder(saved, self._gs, b.views)
+            main.wait_stream(self._side)
+        else:
+            T.train_backward_decoder(saved, self._gs, b.views)
+            w1 = self._all_reduce(b.flat[self._split:], True) if self.overlap else None     # codebook .. to_output + loss
+            T.train_backward_encoder(saved, self._gs, b.views)
         if self.overlap:
             w0 = self._all_reduce(b.flat[:self._split], True)
             for w in (w1, w0):
