@@ -383,6 +383,7 @@ def run_ours(args, rank, world, local_rank):
         return
     parity = None if "parity" in skip else parity_leg(torch, m, p, xs[0])      # raises SystemExit on a mismatch
     latency = None if "latency" in skip else _guard(latency_leg, torch, N, dev, p)
+    vqc = None if "vqvae" in skip else _guard(vqvae_classic_leg, torch, dev, rows, args.steps)
     # ---- per-kernel durations INSIDE the step: the library brackets each of its launches with CUDA events on
     #      the launching stream (lipvq_profile_begin/end); same workload, same rotating inputs
     prof_iters = max(5, args.steps)
@@ -527,7 +528,7 @@ def run_ours(args, rank, world, local_rank):
         "kernels_us_per_step": kern_us, "cpu_baseline": cpu_baseline,
         "config2_vq_alone": c2, "hbm_kernel": hbm, "train_step": train,
         "parity": parity, "parity_checked_rows": parity["parity_checked_rows"] if parity else 0,
-        "latency_us": latency, "config4_sweep": c4, "config5_icrt": c5,
+        "latency_us": latency, "config4_sweep": c4, "config5_icrt": c5, "vqvae_classic": vqc,
     }
     _emit(out)
 
@@ -663,6 +664,32 @@ def latency_leg(torch, N, dev, p):
         r["forward"]["graph_matches_eager"] = bool(torch.equal(z_static, z_eager) and torch.equal(loss_static, loss_eager))
         res["n%d" % n] = r
     return res
+
+
+def vqvae_classic_leg(torch, dev, rows, steps):
+    """the reference's classic VQVAE (vq_vae/backbone.py:6-76; ReLU MLPs, squared distances,
+    straight-through estimator), same batch as the headline, reference constructor defaults (K=128)."""
+    from lipvq_vae_b200 import VQVAE
+    torch.manual_seed(0)
+    m = VQVAE(F_DIM, D_LAT).to(dev)
+    x = torch.randn(rows, F_DIM, device=dev)
+
+    def fwd(i):
+        with torch.no_grad():
+            m(x)
+
+    def fwdbwd(i):
+        for q in m.parameters():
+            q.grad = None
+        _, loss = m(x)
+        loss.backward()
+    out = {"workload": "classic VQVAE (backbone.py:6-76), %d chunks, latent_dim=%d, num_embeddings=128" % (rows // CHUNK_LEN, D_LAT)}
+    for name, fn in (("forward", fwd), ("forward_backward", fwdbwd)):
+        for i in range(3):
+            fn(i)
+        ms = _time_events(fn, max(3, steps // 4), torch)
+        out[name] = {"ms": ms, "chunks_per_s": rows / CHUNK_LEN / (ms / 1e3)}
+    return out
 
 
 def config4_leg(torch, N, lib, dev, rank, world, peaks, steps):
