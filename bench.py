@@ -335,9 +335,9 @@ def run_ours(args, rank, world, local_rank):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         train["ms_per_step_one_allreduce_after_backward"] = float(t.item())
         del trainer, m_tr
-    # A/B: decoder-side and encoder-side backward on two streams
+    # A/B: decoder-side and encoder-side backward on ONE stream (the default runs them on two)
     m_tr = copy.deepcopy(m).train()
-    trainer = TokenizerTrainer(m_tr, concurrent_backward=True)
+    trainer = TokenizerTrainer(m_tr, concurrent_backward=False)
     for i in range(2):
         train_step(i)
     torch.cuda.synchronize()
@@ -348,7 +348,7 @@ def run_ours(args, rank, world, local_rank):
         t = torch.tensor([ms_cc], device=dev, dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms_cc = float(t.item())
-    train["ms_per_step_concurrent_backward"] = ms_cc
+    train["ms_per_step_serial_backward"] = ms_cc
     del trainer, m_tr
     train["collective"] = ("2 NCCL all-reduces per step: [codebook .. to_output grads + loss] issued after the decoder "
                            "backward, under the encoder backward; [encoder + to_latent grads] after it; gradients are "

@@ -646,16 +646,18 @@ int lipvq_encoder_bwd(const lipvq_dims_t *d, const lipvq_params_t *p, const floa
 // ---- chunked forward (large no-grad batches): the three big kernels of the forward are bound by three different
 // resources -- encoder: instruction issue, search: tensor pipe / TMEM reads, emit: HBM -- but the first two are
 // persistent one-CTA-per-SM kernels that cannot share an SM with each other.  The emit pass can: its CTAs are small.
-// So the batch is cut into row chunks (whole waves of 128-row tiles), encoder + search of chunk c+1 run on the caller's
-// stream while the emit pass of chunk c runs on the caller-supplied helper stream.  LIPVQ_FWD_CHUNKS=<n> overrides
-// (1 = off).
+// So the batch CAN be cut into row chunks (whole waves of 128-row tiles), encoder + search of chunk c+1 on the caller's
+// stream while the emit pass of chunk c runs on the caller-supplied helper stream (LIPVQ_FWD_CHUNKS=<n>).  MEASURED
+// NEGATIVE on B200 (profiles/r02_fwd_chunks.jsonl): the persistent kernels leave the emit CTAs no shared memory to be
+// resident beside them, the kernels only interleave at their tails and every chunk pays the encoder's weight-staging
+// prologue again -- so the default is ONE chunk and the path stays as an A/B knob.
 static int forward_chunks(const lipvq_dims_t *d, int64_t n, int32_t search_mode) {
     static const int env = [] { const char *e = getenv("LIPVQ_FWD_CHUNKS"); return e ? atoi(e) : 0; }();
     const bool fuse = use_mlp_tc(d) && search_mode == LIPVQ_SEARCH_TENSOR && vq_tensor_supported(d->D, d->K) &&
                       n <= (int64_t)0x7fffffff - tc::BM;
     if (!fuse) return 1;
     const int64_t tiles = (n + tc::BM - 1) / tc::BM;
-    int c = env > 0 ? env : (tiles >= 16 * kNumSMs ? 4 : 1);
+    int c = env > 0 ? env : 1;     // measured (profiles/r02_fwd_chunks.jsonl): 0.80 / 0.85 / 0.94 / 1.05 ms at 1 / 2 / 4 / 8 chunks -> off
     if (c > kFwdMaxChunks) c = kFwdMaxChunks;
     while (c > 1 && tiles / c < 2 * kNumSMs) --c;
     return c;

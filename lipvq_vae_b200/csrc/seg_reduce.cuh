@@ -207,7 +207,36 @@ __global__ void __launch_bounds__(256) seg0_kernel(const float *__restrict__ src
     const int beg = __ldg(seg_off + k) + j * CH, end = min(__ldg(seg_off + k + 1), beg + CH);
     const bool vec = (D & 3) == 0 && ((reinterpret_cast<uintptr_t>(src) | (DIFF ? reinterpret_cast<uintptr_t>(T) : 0)) & 15) == 0;
     float *out = part0 + (size_t)item * D;
-    if (vec) {
+    if (vec && (D >> 2) <= 16) {
+        // narrow rows (the F = 12 reconstruction gradient: 3 float4 per row): P lanes per row, 32 / P rows per step;
+        // every lane sums its own rows in order, the row groups are then combined by a fixed shuffle tree
+        const int D4 = D >> 2;
+        int P = 1;
+        while (P < D4) P <<= 1;
+        const int R = 32 / P, rsub = lane / P, c = lane - rsub * P;
+        float4 a = make_float4(0.f, 0.f, 0.f, 0.f), t = a;
+        if (DIFF && c < D4) t = __ldg(reinterpret_cast<const float4 *>(T + (size_t)k * D) + c);
+        for (int e = beg + rsub; e < end; e += 2 * R) {
+            float4 v0 = make_float4(0.f, 0.f, 0.f, 0.f), v1 = v0;
+            const bool h1 = e + R < end;
+            if (c < D4) {
+                v0 = __ldg(reinterpret_cast<const float4 *>(src + (size_t)__ldg(perm + e) * D) + c);
+                if (h1) v1 = __ldg(reinterpret_cast<const float4 *>(src + (size_t)__ldg(perm + e + R) * D) + c);
+            }
+            if (DIFF) {
+                a.x += t.x - v0.x; a.y += t.y - v0.y; a.z += t.z - v0.z; a.w += t.w - v0.w;
+                if (h1) { a.x += t.x - v1.x; a.y += t.y - v1.y; a.z += t.z - v1.z; a.w += t.w - v1.w; }
+            } else {
+                a.x += v0.x; a.y += v0.y; a.z += v0.z; a.w += v0.w;
+                if (h1) { a.x += v1.x; a.y += v1.y; a.z += v1.z; a.w += v1.w; }
+            }
+        }
+        for (int o = P; o < 32; o <<= 1) {
+            a.x += __shfl_xor_sync(0xffffffffu, a.x, o); a.y += __shfl_xor_sync(0xffffffffu, a.y, o);
+            a.z += __shfl_xor_sync(0xffffffffu, a.z, o); a.w += __shfl_xor_sync(0xffffffffu, a.w, o);
+        }
+        if (rsub == 0 && c < D4) reinterpret_cast<float4 *>(out)[c] = a;
+    } else if (vec) {
         const int D4 = D >> 2;
         for (int c0 = 0; c0 < D4; c0 += 64) {          // two float4 column groups per lane and pass
             const int ca = c0 + lane, cb = c0 + 32 + lane;
@@ -257,50 +286,48 @@ __global__ void __launch_bounds__(256) seg0_kernel(const float *__restrict__ src
     }
 }
 
-// level 1: item = (code k, chunk j of its level-0 items): sequential sum of <= CH partial rows
+// sequential fp32 sum of rows [beg, end) of a [., D] partial array for this lane's column, 8 loads in flight
+__device__ __forceinline__ float column_sum(const float *__restrict__ part, int D, int c, int beg, int end) {
+    float a = 0.f;
+    int e = beg;
+    for (; e + 8 <= end; e += 8) {
+        float v[8];
+#pragma unroll
+        for (int q = 0; q < 8; ++q) v[q] = part[(size_t)(e + q) * D + c];
+#pragma unroll
+        for (int q = 0; q < 8; ++q) a += v[q];
+    }
+    for (; e < end; ++e) a += part[(size_t)e * D + c];
+    return a;
+}
+
+// level 1: one warp per (item = code k, chunk j of its level-0 items; 32-column group): sum of <= CH partial rows
 __global__ void __launch_bounds__(256) seg1_kernel(const float *__restrict__ part0, int D, int K,
                                                    const int *__restrict__ item_off0, const int *__restrict__ item_off1,
                                                    float *__restrict__ part1) {
-    const int item = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    const int item = blockIdx.x * 8 + (threadIdx.x >> 5), c = blockIdx.y * 32 + (threadIdx.x & 31);
     if (item >= __ldg(item_off1 + K)) return;
     const int k = find_segment(item_off1, K, item);
     const int j = item - __ldg(item_off1 + k);
     const int beg = __ldg(item_off0 + k) + j * CH, end = min(__ldg(item_off0 + k + 1), beg + CH);
-    for (int c = lane; c < D; c += 32) {
-        float a = 0.f;
-        int e = beg;
-        for (; e + 4 <= end; e += 4) {
-            const float v0 = part0[(size_t)e * D + c], v1 = part0[(size_t)(e + 1) * D + c];
-            const float v2 = part0[(size_t)(e + 2) * D + c], v3 = part0[(size_t)(e + 3) * D + c];
-            a += v0; a += v1; a += v2; a += v3;
-        }
-        for (; e < end; ++e) a += part0[(size_t)e * D + c];
-        part1[(size_t)item * D + c] = a;
-    }
+    if (c < D) part1[(size_t)item * D + c] = column_sum(part0, D, c, beg, end);
 }
 
-// final: one warp per code: sums[k] (+)= scale * sum of its level-1 items (in order); counts[k] = count[k]
+// final: one warp per (code, 32-column group): sums[k] (+)= scale * sum of its level-1 items (in order); counts[k]
 __global__ void __launch_bounds__(256) seg_final_kernel(const float *__restrict__ part1, int D, int K,
                                                         const int *__restrict__ item_off1, const int *__restrict__ count,
                                                         float alpha, const float *__restrict__ gs, int accumulate,
                                                         float *__restrict__ sums, float *__restrict__ counts) {
-    const int k = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    const int k = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31, c = blockIdx.y * 32 + lane;
     if (k >= K) return;
     if (gs) alpha *= __ldg(gs);
     const int beg = __ldg(item_off1 + k), end = __ldg(item_off1 + k + 1);
-    for (int c = lane; c < D; c += 32) {
-        float a = 0.f;
-        int e = beg;
-        for (; e + 4 <= end; e += 4) {
-            const float v0 = part1[(size_t)e * D + c], v1 = part1[(size_t)(e + 1) * D + c];
-            const float v2 = part1[(size_t)(e + 2) * D + c], v3 = part1[(size_t)(e + 3) * D + c];
-            a += v0; a += v1; a += v2; a += v3;
-        }
-        for (; e < end; ++e) a += part1[(size_t)e * D + c];
+    if (c < D) {
+        const float a = column_sum(part1, D, c, beg, end);
         float *o = sums + (size_t)k * D + c;
         *o = accumulate ? *o + alpha * a : alpha * a;
     }
-    if (counts && lane == 0) counts[k] = (float)__ldg(count + k);
+    if (counts && lane == 0 && blockIdx.y == 0) counts[k] = (float)__ldg(count + k);
 }
 
 inline bool supported(int K, int64_t n) { return K >= 1 && K <= KMAX && n >= 1 && n < (int64_t)0x7fffffff - RB; }
@@ -330,9 +357,10 @@ inline int reduce(const float *src, const float *T, int D, const Plan &p, float 
     if (T) seg0_kernel<true><<<g0, 256, 0, st>>>(src, T, D, K, p.perm, p.seg_off, p.item_off0, p.part0);
     else seg0_kernel<false><<<g0, 256, 0, st>>>(src, nullptr, D, K, p.perm, p.seg_off, p.item_off0, p.part0);
     LIPVQ_LAUNCH_OK();
-    seg1_kernel<<<g1, 256, 0, st>>>(p.part0, D, K, p.item_off0, p.item_off1, p.part1);
+    const unsigned gy = (unsigned)((D + 31) / 32);
+    seg1_kernel<<<dim3(g1, gy), 256, 0, st>>>(p.part0, D, K, p.item_off0, p.item_off1, p.part1);
     LIPVQ_LAUNCH_OK();
-    seg_final_kernel<<<(K + 7) / 8, 256, 0, st>>>(p.part1, D, K, p.item_off1, p.count, alpha, gs, accumulate ? 1 : 0, sums,
+    seg_final_kernel<<<dim3((K + 7) / 8, gy), 256, 0, st>>>(p.part1, D, K, p.item_off1, p.count, alpha, gs, accumulate ? 1 : 0, sums,
                                                   counts);
     LIPVQ_LAUNCH_OK();
     return LIPVQ_OK;

@@ -313,17 +313,29 @@ __device__ __forceinline__ float tau_of(float znr, float emax, float abs_c) {
 // (a superset of the final window: the running minimum only decreases); code0 = first code of the chunk and
 // mask = which of its 8 elements were inside that window.  The common path costs the chunk minima only.
 __device__ __noinline__ void cand_compact(uint2 *out, int &cnt, float T) {
-    int k = 0;                  // full: drop entries that fell out of the (shrinking) window
-    for (int e = 0; e < LCAP; ++e) {
+    int k = 0;                  // nearly full: drop entries that fell out of the (shrinking) window
+    const int n = cnt < LCAP ? cnt : LCAP;
+    for (int e = 0; e < n; ++e) {
         const uint2 x = out[e * BM];
         if (__uint_as_float(x.x) <= T) out[(k++) * BM] = x;
     }
-    cnt = k < LCAP ? k : LCAP + 1;
+    cnt = k;
 }
 __device__ __forceinline__ float min8(const uint32_t *r) {
     const float a = ptx::fmin3(__uint_as_float(r[0]), __uint_as_float(r[1]), __uint_as_float(r[2]));
     const float b = ptx::fmin3(__uint_as_float(r[3]), __uint_as_float(r[4]), __uint_as_float(r[5]));
     return ptx::fmin3(a, b, fminf(__uint_as_float(r[6]), __uint_as_float(r[7])));
+}
+
+// predicated 8-byte global store (keeps the epilogue's record path free of divergent branches)
+__device__ __forceinline__ void st_global_v2_if(uint2 *p, uint32_t a, uint32_t b, bool pred) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "setp.ne.b32 p, %3, 0;\n"
+        "@p st.global.v2.b32 [%0], {%1, %2};\n"
+        "}\n" ::"l"(p), "r"(a), "r"(b), "r"((uint32_t)pred)
+        : "memory");
 }
 
 // order-preserving map float -> unsigned (atomicMin on the key == min on the float) and back
@@ -524,8 +536,13 @@ __global__ void __launch_bounds__(CONV ? NT_CONV : NT, 1) vq_tc_kernel(const __g
         }
     } else if (warp >= 4) {
         // ===== epilogue: 16 warps; warp%4 = TMEM lane quarter, (warp-4)/4 = 64-column part =====
-        // (TMEM reads run at 64 B/clk/SM: 2048 cycles per 128x256 accumulator, the floor of this kernel for
-        //  D < 256; enough warps are needed so that one warp's tcgen05.ld overlaps another's min network)
+        // Measured (tools/tmem_probe.cu, profiles/r02_tmem_probe.txt): 16 warps of tcgen05.ld.32x32b.x32 read TMEM at
+        // 530 B/clk/SM = 250 cycles per 128x256 fp32 accumulator, also under a concurrent MMA stream -- far below the
+        // MMA time of an accumulator (161 cycles per M=128 N=256 K=16 instruction with both operands in shared memory:
+        // 805 cycles at D=64, 2254 at D=208).  What the epilogue must not exceed is its INSTRUCTION budget, so the
+        // per-chunk work below is branch-free: with 32 rows per warp a divergent "record this chunk" body is taken by
+        // some lane almost every time (each row has its own running minimum), and used to cost ~3000 issue cycles
+        // per accumulator.
         const int quarter = warp & 3, part = (warp - 4) >> 2;
         const uint32_t lane_addr = ((uint32_t)(quarter * 32) << 16);
         constexpr int PW = BN / NPART;            // columns per part
@@ -546,6 +563,7 @@ __global__ void __launch_bounds__(CONV ? NT_CONV : NT, 1) vq_tc_kernel(const __g
             uint2 *out = cand + ((size_t)tile * NPART + part) * LCAP * BM + r_in;
             float gb = BIG;
             int cnt = 0;
+            bool ovf = false;
             for (int c = 0; c < nct; ++c) {
                 ptx::mbar_wait(t_full(acc), accph);
                 ptx::tc_fence_after();
@@ -566,22 +584,30 @@ __global__ void __launch_bounds__(CONV ? NT_CONV : NT, 1) vq_tc_kernel(const __g
                     for (int j = 0; j < 4; ++j) cm[j] = min8(r + 8 * j);
                     gb = fminf(gb, ptx::fmin3(cm[0], cm[1], fminf(cm[2], cm[3])));
                     const float T = gb + tau;
+                    const float Tm = T + fabsf(T) * 1.2e-7f + 1e-37f;     // > T: (v - Tm) is negative for every v <= T
+                    // room for this batch's (at most 4) records, so the per-chunk stores need no capacity test
+                    if (cnt > LCAP - 4) {                                  // rare
+                        cand_compact(out, cnt, T);
+                        if (cnt > LCAP - 4) { ovf = true; cnt = 0; }       // flat score landscape: the row takes the exact scan
+                    }
 #pragma unroll
                     for (int j = 0; j < 4; ++j) {
-                        if (cm[j] <= T && row_ok) {
-                            uint32_t m = 0;
+                        // window mask of the chunk, always and branch-free: sign bit of (v - Tm) shifted in, last element
+                        // first so that element e lands in bit e (2 instructions per element)
+                        uint32_t m = 0;
 #pragma unroll
-                            for (int e = 0; e < 8; ++e)
-                                if (__uint_as_float(r[8 * j + e]) <= T) m |= 1u << e;
-                            if (cnt >= LCAP) cand_compact(out, cnt, T);
-                            if (cnt < LCAP)
-                                out[(cnt++) * BM] =
-                                    make_uint2(__float_as_uint(cm[j]), (uint32_t)(code0 + b * 32 + 8 * j) | (m << 24));
-                        }
+                        for (int e = 7; e >= 0; --e)
+                            m = __funnelshift_l(__float_as_uint(__uint_as_float(r[8 * j + e]) - Tm), m, 1);
+                        // PREDICATED record: one entry per chunk whose minimum is inside the running window
+                        const bool put = (cm[j] <= T) && row_ok;
+                        st_global_v2_if(out + cnt * BM, __float_as_uint(cm[j]),
+                                        (uint32_t)(code0 + b * 32 + 8 * j) | (m << 24), put);
+                        cnt += put ? 1 : 0;
                     }
                 }
                 if (++acc == 2) { acc = 0; accph ^= 1; }
             }
+            if (ovf) cnt = LCAP + 1;
             if (row_ok) cand_meta[((size_t)tile * NPART + part) * BM + r_in] = cnt;
             // ---- resolve (was a separate kernel): the four parts of a row agree on the row minimum, count the listed
             // elements inside the FINAL window tau(row) and decide: exactly one -> it IS the nearest code, idx is

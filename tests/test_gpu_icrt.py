@@ -52,7 +52,8 @@ def test_icrt_iteration_matches_reference_network(mode):
     vq_opt.zero_grad()
     d = pol.forward_train(obs_dict=obs, context_obs=ctx, actions=pa)
     # --- the tokenizer inside the policy forward (obs_nets.py:1335-1337)
-    p_tok = {k[len(TOK):]: g["sd::" + k] for k in g if k.startswith("sd::" + TOK)}
+    pre = "sd::" + TOK
+    p_tok = {k[len(pre):]: g[k] for k in g if k.startswith(pre)}
     z_e = orc.encode(p_tok, g["prompt_actions"].reshape(-1, 12))
     _, d1, d2 = orc.exact_top2(z_e, p_tok["quantizer.codebook"])
     must = orc.index_parity_mask(d1, d2)
