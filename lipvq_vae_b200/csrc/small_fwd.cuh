@@ -34,7 +34,8 @@ __device__ __forceinline__ void rows_layer(const float *__restrict__ W, const fl
         for (int q = 0; q < NJ; ++q)
 #pragma unroll
             for (int r = 0; r < SR; ++r) acc[q][r] = 0.f;
-        for (int k = lane; k < k_in; k += 32) {
+#pragma unroll 4
+        for (int k = lane; k < k_in; k += 32) {      // (the kernel is latency bound: keep 16 weight loads in flight)
             float w[NJ];
 #pragma unroll
             for (int q = 0; q < NJ; ++q) w[q] = j0 + q < n_out ? __ldg(W + (size_t)(j0 + q) * k_in + k) : 0.f;
@@ -69,6 +70,58 @@ __device__ __forceinline__ void lipschitz_rows_layer(const float *__restrict__ W
                                                      const float *__restrict__ ci, int n_out, int k_in,
                                                      const float *s_in, float *s_out, int out_pitch) {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarp = ST / 32;
+    constexpr int NJ = 4, KR = 4;       // neurons in flight per warp; weight registers per lane and neuron (k_in <= 128)
+    if (k_in <= 32 * KR) {
+        // latency-bound at these sizes: all NJ x KR weights of the step are loaded at once (one L2 round trip),
+        // the row sums, the scale and the products come from registers
+        for (int j0 = warp * NJ; j0 < n_out; j0 += nwarp * NJ) {
+            float w[NJ][KR], s[NJ];
+#pragma unroll
+            for (int q = 0; q < NJ; ++q)
+#pragma unroll
+                for (int t = 0; t < KR; ++t) {
+                    const int k = lane + 32 * t;
+                    w[q][t] = (j0 + q < n_out && k < k_in) ? __ldg(W + (size_t)(j0 + q) * k_in + k) : 0.f;
+                }
+#pragma unroll
+            for (int q = 0; q < NJ; ++q) {
+                float a = 0.f;
+#pragma unroll
+                for (int t = 0; t < KR; ++t) a += fabsf(w[q][t]);      // lane-strided order == the two-pass loop below
+                s[q] = warp_sum(a);
+            }
+            float acc[NJ][SR];
+#pragma unroll
+            for (int q = 0; q < NJ; ++q) {
+                const float sc = j0 + q < n_out ? fminf(1.0f, softplus_f(__ldg(ci + j0 + q)) / s[q]) : 0.f;
+#pragma unroll
+                for (int r = 0; r < SR; ++r) acc[q][r] = 0.f;
+#pragma unroll
+                for (int t = 0; t < KR; ++t) {
+                    const int k = lane + 32 * t;
+                    if (k < k_in) {
+                        const float ws = w[q][t] * sc;
+#pragma unroll
+                        for (int r = 0; r < SR; ++r) acc[q][r] = fmaf(ws, s_in[r * k_in + k], acc[q][r]);
+                    }
+                }
+            }
+#pragma unroll
+            for (int q = 0; q < NJ; ++q) {
+                const int j = j0 + q;
+                if (j >= n_out) break;          // warp-uniform
+#pragma unroll
+                for (int r = 0; r < SR; ++r) acc[q][r] = warp_sum(acc[q][r]);
+                if (lane < SR) {
+                    float v = 0.f;
+#pragma unroll
+                    for (int r = 0; r < SR; ++r) v = lane == r ? acc[q][r] : v;
+                    s_out[lane * out_pitch + j] = sigmoid_f(v + __ldg(bias + j));
+                }
+            }
+        }
+        return;
+    }
     for (int j = warp; j < n_out; j += nwarp) {
         const float *wr = W + (size_t)j * k_in;
         float s = 0.f;
@@ -313,7 +366,9 @@ inline int launch(const lipvq_dims_t *d, const lipvq_params_t *p, const float *x
     if (stats) LIPVQ_CUDA_OK(cudaMemsetAsync(stats, 0, 4 * sizeof(int32_t), st));
     const int G = (int)((n + SR - 1) / SR);
     // enough CTAs to cover the chip about twice, at least 32 codes per split
-    int splits = (2 * kNumSMs + G - 1) / G;
+    // every warp of a CTA should own a 32-code tile (256 codes per CTA) unless that leaves most of the chip idle
+    int splits = (d->K + 255) / 256;
+    while ((int64_t)splits * G < kNumSMs && splits * 32 < d->K) splits *= 2;
     if (splits > 64) splits = 64;
     if (splits < 1) splits = 1;
     const int per = ((d->K + splits - 1) / splits + 31) / 32 * 32;     // codes per split, whole 32-code tiles

@@ -561,7 +561,8 @@ __global__ void __launch_bounds__(CONV ? NT_CONV : NT, 1) vq_tc_kernel(const __g
             if (row_bad) znr = 0.f;
             const float tau = tau_of(znr, emax, abs_c);
             uint2 *out = cand + ((size_t)tile * NPART + part) * LCAP * BM + r_in;
-            float gb = BIG;
+            float gb = BIG, m1 = BIG, m2 = BIG;
+            uint32_t info1 = 0;
             int cnt = 0;
             bool ovf = false;
             for (int c = 0; c < nct; ++c) {
@@ -600,9 +601,15 @@ __global__ void __launch_bounds__(CONV ? NT_CONV : NT, 1) vq_tc_kernel(const __g
                             m = __funnelshift_l(__float_as_uint(__uint_as_float(r[8 * j + e]) - Tm), m, 1);
                         // PREDICATED record: one entry per chunk whose minimum is inside the running window
                         const bool put = (cm[j] <= T) && row_ok;
-                        st_global_v2_if(out + cnt * BM, __float_as_uint(cm[j]),
-                                        (uint32_t)(code0 + b * 32 + 8 * j) | (m << 24), put);
+                        const uint32_t info = (uint32_t)(code0 + b * 32 + 8 * j) | (m << 24);
+                        st_global_v2_if(out + cnt * BM, __float_as_uint(cm[j]), info, put);
                         cnt += put ? 1 : 0;
+                        // the two smallest chunk minima of this (row, part) stay in registers: the tile-end decision
+                        // below needs nothing from memory
+                        const bool lt = cm[j] < m1;
+                        m2 = lt ? m1 : fminf(m2, cm[j]);
+                        info1 = lt ? info : info1;
+                        m1 = lt ? cm[j] : m1;
                     }
                 }
                 if (++acc == 2) { acc = 0; accph ^= 1; }
@@ -613,24 +620,21 @@ __global__ void __launch_bounds__(CONV ? NT_CONV : NT, 1) vq_tc_kernel(const __g
             // elements inside the FINAL window tau(row) and decide: exactly one -> it IS the nearest code, idx is
             // written here; several -> fp32 rescore list; list overflow / range flag -> exact scan list.
             asm volatile("bar.sync 1, 512;" ::: "memory");      // the previous tile's decision (and reset) is done
-            if (row_ok) atomicMin(&s_min[r_in], fkey(gb));
+            if (row_ok) atomicMin(&s_min[r_in], fkey(m1));
             asm volatile("bar.sync 1, 512;" ::: "memory");
             if (row_ok) {
-                int nin = 0, code = 0x7fffffff;
-                if (cnt > LCAP) nin = 1 << 20;
-                else {
-                    const float T = fkey_inv(s_min[r_in]) + tau;
-                    for (int e = 0; e < cnt; ++e) {
-                        const uint2 x = out[e * BM];                       // (this thread's own stores)
-                        if (__uint_as_float(x.x) <= T) {
-                            const int c0 = (int)(x.y & 0xffffffu);
-                            uint32_t m = x.y >> 24;
-                            if (c0 + 8 > K) m &= (1u << max(K - c0, 0)) - 1u;     // padding codes of the last chunk
-                            nin += __popc(m);
-                            if (m) code = min(code, c0 + __ffs(m) - 1);
-                        }
-                    }
+                // (the mask of the best chunk was taken against the window of ITS time, a superset of the final one: a
+                //  row can only be sent to the rescore list needlessly, never decided wrongly)
+                const float T = fkey_inv(s_min[r_in]) + tau;
+                int nin = ovf ? (1 << 20) : 0, code = 0x7fffffff;
+                if (m1 <= T) {
+                    const int c0 = (int)(info1 & 0xffffffu);
+                    uint32_t m = info1 >> 24;
+                    if (c0 + 8 > K) m &= (1u << max(K - c0, 0)) - 1u;     // padding codes of the last chunk
+                    nin += __popc(m);
+                    if (m) code = c0 + __ffs(m) - 1;
                 }
+                if (m2 <= T) nin += 1 << 10;                              // a second chunk of this part: rescore decides
                 if (nin) atomicAdd(&s_nin[r_in], nin);
                 if (code != 0x7fffffff) atomicMin(&s_code[r_in], code);
             }
@@ -639,7 +643,7 @@ __global__ void __launch_bounds__(CONV ? NT_CONV : NT, 1) vq_tc_kernel(const __g
                 bool fast = false;
                 if (row_ok) {
                     const int nin = s_nin[r_in];
-                    if (range_bad || row_bad || nin >= (1 << 20) || nin == 0 || nin > 64)   // 0 cannot happen for finite inputs
+                    if (range_bad || row_bad || nin >= (1 << 20) || nin == 0)   // 0 cannot happen for finite inputs
                         exact_list[atomicAdd(counters + 0, 1)] = (int)row;
                     else if (nin == 1 && !want_d2) { idx_out[row] = (int64_t)s_code[r_in]; fast = true; }
                     else resc_list[atomicAdd(counters + 4, 1)] = (int)row;
@@ -673,7 +677,7 @@ __global__ void __launch_bounds__(256) vq_rescore_kernel(
     const float *__restrict__ z, const float *__restrict__ E, int D, int K, const uint2 *__restrict__ cand,
     const int *__restrict__ cand_meta, const float *__restrict__ zn, const float *__restrict__ emax_p, float abs_c,
     int64_t *__restrict__ idx_out, float *__restrict__ d2_out, const int *__restrict__ resc_list,
-    int *__restrict__ counters) {
+    int *__restrict__ counters, int *__restrict__ exact_list) {
     constexpr int LPG = 32 / NG;       // lanes per code
     __shared__ int s_codes[8][64];
     __shared__ int s_cnt[8];
@@ -718,7 +722,12 @@ __global__ void __launch_bounds__(256) vq_rescore_kernel(
                 }
             }
         __syncwarp();
-        const int nc = min(s_cnt[wib], 64);      // resolve guarantees <= 64
+        if (s_cnt[wib] > 64) {                   // too many listed elements for the warp list: the exact scan takes the row
+            if (lane == 0) exact_list[atomicAdd(counters + 0, 1)] = (int)row;
+            __syncwarp();
+            continue;
+        }
+        const int nc = s_cnt[wib];
         float best = INFINITY;
         int bidx = 0x7fffffff;
         const float *zr = z + row * D;
@@ -907,10 +916,10 @@ inline int vq_tensor_search(const float *z, const float *E, const tc::Geometry &
         ProfScope prof("vq_rescore_kernel", st);
         if ((D & 3) == 0)
             vq_rescore_kernel<4, true><<<(unsigned)blocks, 256, 0, st>>>(z, E, D, K, w.cand, w.cand_meta, w.zn, w.emax,
-                                                                        abs_c, idx, d2, w.resc_list, w.counters);
+                                                                        abs_c, idx, d2, w.resc_list, w.counters, w.list);
         else
             vq_rescore_kernel<4, false><<<(unsigned)blocks, 256, 0, st>>>(z, E, D, K, w.cand, w.cand_meta, w.zn, w.emax,
-                                                                         abs_c, idx, d2, w.resc_list, w.counters);
+                                                                         abs_c, idx, d2, w.resc_list, w.counters, w.list);
         LIPVQ_LAUNCH_OK();
     }
     // tier 2: rows whose candidate list overflowed -> exact fp32 scan (count stays on the device)
