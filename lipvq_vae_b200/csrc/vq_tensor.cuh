@@ -555,11 +555,12 @@ __global__ void __launch_bounds__(CONV ? NT_CONV : NT, 1) vq_tc_kernel(const __g
             const int r_in = quarter * 32 + lane;
             const int64_t row = (int64_t)tile * BM + r_in;
             const bool row_ok = row < n_rows;
-            // (CONV: zn of this tile was written by this CTA's converter warps before the tile's first MMA was issued)
-            float znr = row_ok ? (CONV ? __ldcg(zn + row) : __ldg(zn + row)) : 0.f;
-            const bool row_bad = CONV && !(znr >= 0.f);
-            if (row_bad) znr = 0.f;
-            const float tau = tau_of(znr, emax, abs_c);
+            // CONV: zn of this tile is written by this CTA's converter warps before they release the tile to the MMA
+            // issuer, so it may only be read once the tile's FIRST accumulator has been signalled (below); reading it
+            // here would race with the converter (and pick up the previous call's value from the workspace)
+            float znr = (row_ok && !CONV) ? __ldg(zn + row) : 0.f;
+            bool row_bad = false;
+            float tau = tau_of(znr, emax, abs_c);
             uint2 *out = cand + ((size_t)tile * NPART + part) * LCAP * BM + r_in;
             float gb = BIG, m1 = BIG, m2 = BIG;
             uint32_t info1 = 0;
@@ -568,6 +569,12 @@ __global__ void __launch_bounds__(CONV ? NT_CONV : NT, 1) vq_tc_kernel(const __g
             for (int c = 0; c < nct; ++c) {
                 ptx::mbar_wait(t_full(acc), accph);
                 ptx::tc_fence_after();
+                if (CONV && c == 0) {
+                    znr = row_ok ? __ldcg(zn + row) : 0.f;
+                    row_bad = !(znr >= 0.f);
+                    if (row_bad) znr = 0.f;
+                    tau = tau_of(znr, emax, abs_c);
+                }
                 const uint32_t col0 = tmem_base + acc * BN + part * PW;
                 const int code0 = c * BN + part * PW;
 #pragma unroll

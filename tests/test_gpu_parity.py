@@ -231,8 +231,11 @@ def test_large_n_properties():
     with torch.no_grad():
         q.codebook.copy_(torch.rand(K, D, device="cuda"))
     out = {}
+    from lipvq_vae_b200 import tokenizer
     for mode in MODES:
         q.search_mode = mode
+        for ws in tokenizer._WS.values():       # scratch poisoned: nothing may depend on what a previous call left there
+            ws.fill_(0xFF)
         out[mode] = q(z)
     zq0, i0 = out[0]
     zq1, i1 = out[1]

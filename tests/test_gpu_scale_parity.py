@@ -28,6 +28,15 @@ def _model(p, mode=1, dev="cuda:0"):
     return m
 
 
+def _poison_workspaces():
+    """Fill every cached scratch workspace with 0xFF bytes (NaN floats, -1 ints): a kernel that reads scratch before it
+    wrote it -- or a value a previous call left there -- then fails loudly instead of passing by luck."""
+    from lipvq_vae_b200 import tokenizer
+    for ws in tokenizer._WS.values():
+        ws.fill_(0xFF)
+    torch.cuda.synchronize()
+
+
 def spread_params(F=12, D=208, K=1024, seed=11):
     """Weights with index diversity (random init collapses onto one code): a milder Lipschitz layer with
     both ``min`` branches in use and a codebook sampled from the encoder's own output distribution."""
@@ -47,6 +56,7 @@ def test_forward_at_bench_size_vs_oracle():
     p = spread_params(F, D, K)
     x = (2.0 * np.random.default_rng(5).random((n, F)) - 1.0).astype(np.float32)
     m = _model(p)
+    _poison_workspaces()
     with torch.no_grad():
         z_lat, loss = m(torch.from_numpy(x).cuda())
     torch.cuda.synchronize()
@@ -90,6 +100,7 @@ def test_config2_search_vs_oracle():
         must = orc.index_parity_mask(d1, d2)
         for mode in (1, 0):
             q.search_mode = mode
+            _poison_workspaces()
             z_q, idx = q(zt)
             idx = idx.cpu().numpy()
             assert np.array_equal(idx[must], ref_idx[must]), (name, mode, int((idx != ref_idx)[must].sum()))
