@@ -16,7 +16,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(HERE)
 CSRC = os.path.join(HERE, "csrc")
 LIB_DIR = os.path.join(HERE, "_lib")
-LIB_PATH = os.path.join(LIB_DIR, "liblipvq_b200.so")
+LIB_PATH = os.environ.get("LIPVQ_LIB") or os.path.join(LIB_DIR, "liblipvq_b200.so")   # LIPVQ_LIB: A/B builds
 HEADER = os.path.join(ROOT, "include", "lipvq_b200.h")
 
 SEARCH_EXACT = 0

@@ -32,7 +32,9 @@ constexpr int UK = 16;           // UMMA K for 16-bit inputs
 constexpr int A_KB_BYTES = BM * 128;
 constexpr int B_ST_BYTES = BN * 128;
 constexpr int NT = 640;          // warp0 TMA, warp1 MMA, warp2 TMEM alloc, warps 4..19 epilogue
-constexpr int NT_CONV = 768;     // + warps 20..23: fp32 rows -> fp16 operand tile in shared memory (standalone search)
+constexpr int NCW = 2;            // converter warps of the standalone search: warps 2 and 3 (extra warps would cut the
+                                  // register budget of the 16 epilogue warps below what they need)
+constexpr int NT_CONV = NT;
 constexpr int NPART = 4;         // column parts of an accumulator (64 columns each), one epilogue warp per (quarter, part)
 constexpr int NCAND = 4;         // chunk minima kept per (row, column half, code tile)
 constexpr int LCAP = 16;         // candidate entries kept per (row, column half)
@@ -388,7 +390,7 @@ __global__ void __launch_bounds__(CONV ? NT_CONV : NT, 1) vq_tc_kernel(const __g
     if (warp == 0 && lane == 0) {
         ptx::tma_prefetch_desc(&tmapA);
         ptx::tma_prefetch_desc(&tmapB);
-        for (int i = 0; i < A_BUFS; ++i) { ptx::mbar_init(a_full(i), CONV ? 4 : 1); ptx::mbar_init(a_empty(i), 1); }
+        for (int i = 0; i < A_BUFS; ++i) { ptx::mbar_init(a_full(i), CONV ? NCW : 1); ptx::mbar_init(a_empty(i), 1); }
         for (int i = 0; i < STAGES; ++i) { ptx::mbar_init(b_full(i), 1); ptx::mbar_init(b_empty(i), 1); }
         for (int i = 0; i < 2; ++i) { ptx::mbar_init(t_full(i), 1); ptx::mbar_init(t_empty(i), 4 * NPART); }
         ptx::fence_barrier_init();
@@ -461,73 +463,93 @@ __global__ void __launch_bounds__(CONV ? NT_CONV : NT, 1) vq_tc_kernel(const __g
                 if (++ab == A_BUFS) { ab = 0; aph ^= 1; }
             }
         }
-    } else if (CONV && warp >= 20) {
-        // ===== converter: thread = row of the tile; 8 columns (32 B in, 16 B out) per step =====
-        const int r = (warp - 20) * 32 + lane;
-        const int cpr = nk16 * 2;                       // 8-column pieces per row (whole MMA K steps)
+    } else if (CONV && (warp == 2 || warp == 3)) {
+        // ===== converter: a warp takes row quads of the tile, one row at a time with its lanes ACROSS the row (coalesced
+        // 512-byte requests; a lane-per-row layout cost 32 L1 wavefronts per request and made this role the limit of
+        // the kernel); lane <-> 4 consecutive columns -> two half2 = 8 bytes of the swizzled K-major tile =====
+        const int cw = warp - 2;
+        const int Q = nk16 * 4;                         // 4-column groups per row (whole MMA K steps)
         const bool vec = (D & 3) == 0;
-        const uint32_t sw = (uint32_t)(r & 7);
         int ab = 0, aph = 0;
-        bool bad = false;
-        for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-            const int64_t row = (int64_t)tile * BM + r;
-            const bool ok = row < n_rows;
-            const float *zr = zsrc + row * D;
-            ptx::mbar_wait(a_empty(ab), aph ^ 1);
-            float ss = 0.f;
-            for (int c0 = 0; c0 < cpr; c0 += 4) {       // 4 pieces = 8 independent 16-byte loads in flight
-                float v[4][8];
-#pragma unroll
-                for (int u = 0; u < 4; ++u) {
-                    const int d0 = (c0 + u) * 8;
-#pragma unroll
-                    for (int q = 0; q < 2; ++q) {
-                        const int d = d0 + 4 * q;
-                        float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
-                        if (ok && c0 + u < cpr && d < D) {
-                            if (vec) t = __ldg(reinterpret_cast<const float4 *>(zr + d));
-                            else {
-                                t.x = __ldg(zr + d);
-                                if (d + 1 < D) t.y = __ldg(zr + d + 1);
-                                if (d + 2 < D) t.z = __ldg(zr + d + 2);
-                                if (d + 3 < D) t.w = __ldg(zr + d + 3);
-                            }
-                        }
-                        v[u][4 * q] = t.x; v[u][4 * q + 1] = t.y; v[u][4 * q + 2] = t.z; v[u][4 * q + 3] = t.w;
-                    }
-                }
-#pragma unroll
-                for (int u = 0; u < 4; ++u) {
-                    const int c = c0 + u;
-                    if (c < cpr) {
-                        const int d0 = c * 8;
-#pragma unroll
-                        for (int i = 0; i < 8; ++i) {
-                            const int d = d0 + i;
-                            if (ok && d < D) {
-                                v[u][i] -= __ldg(mu + d);
-                                ss = fmaf(v[u][i], v[u][i], ss);
-                                bad |= !(fabsf(v[u][i]) <= OP_MAX);     // (also catches NaN)
-                            } else {
-                                v[u][i] = (ok && d < D + 3) ? 1.0f : 0.f;
-                            }
-                        }
-                        uint32_t o[4];
-#pragma unroll
-                        for (int i = 0; i < 4; ++i) {
-                            const op2_t pr = f2op2(v[u][2 * i], v[u][2 * i + 1]);
-                            o[i] = *reinterpret_cast<const uint32_t *>(&pr);
-                        }
-                        const uint32_t dst = sA + (uint32_t)((ab * NKB + (c >> 3)) * A_KB_BYTES) + (uint32_t)r * 128u +
-                                             ((((uint32_t)c & 7u) ^ sw) << 4);
-                        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(dst), "r"(o[0]), "r"(o[1]), "r"(o[2]),
-                                     "r"(o[3])
-                                     : "memory");
-                    }
+        float row_ss = 0.f;
+        bool row_bad_acc = false;
+        auto load_quad = [&](const float *zr, bool ok, int q) -> float4 {
+            float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
+            const int d = 4 * q;
+            if (ok && q < Q && d < D) {
+                if (vec) t = __ldg(reinterpret_cast<const float4 *>(zr + d));
+                else {
+                    t.x = __ldg(zr + d);
+                    if (d + 1 < D) t.y = __ldg(zr + d + 1);
+                    if (d + 2 < D) t.z = __ldg(zr + d + 2);
+                    if (d + 3 < D) t.w = __ldg(zr + d + 3);
                 }
             }
-            if (ok) zn_out[row] = bad ? -1.0f : sqrtf(ss);    // negative: this row takes the exact scan
-            bad = false;
+            return t;
+        };
+        for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+            ptx::mbar_wait(a_empty(ab), aph ^ 1);
+            const uint32_t tile_s = sA + (uint32_t)(ab * NKB * A_KB_BYTES);
+            for (int r0 = 8 * cw; r0 < BM; r0 += 8 * NCW) {        // 8 rows in flight; row groups dealt round-robin to the warps
+                for (int p = 0; p * 32 < Q; ++p) {
+                    const int q = p * 32 + lane;
+                    float4 t[8];
+#pragma unroll
+                    for (int u = 0; u < 8; ++u) {
+                        const int64_t row = (int64_t)tile * BM + r0 + u;
+                        t[u] = load_quad(zsrc + row * D, row < n_rows, q);
+                    }
+                    float4 m4 = make_float4(0.f, 0.f, 0.f, 0.f);
+                    const int d = 4 * q;
+                    if (q < Q && d < D) {
+                        if (vec) m4 = __ldg(reinterpret_cast<const float4 *>(mu + d));
+                        else {
+                            m4.x = __ldg(mu + d);
+                            if (d + 1 < D) m4.y = __ldg(mu + d + 1);
+                            if (d + 2 < D) m4.z = __ldg(mu + d + 2);
+                            if (d + 3 < D) m4.w = __ldg(mu + d + 3);
+                        }
+                    }
+#pragma unroll
+                    for (int u = 0; u < 8; ++u) {
+                        const int r = r0 + u;
+                        const bool ok = (int64_t)tile * BM + r < n_rows;
+                        float v[4] = {t[u].x - m4.x, t[u].y - m4.y, t[u].z - m4.z, t[u].w - m4.w};
+                        float ssq = 0.f;
+                        bool bad = false;
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) {
+                            const int dd = d + i;
+                            if (ok && dd < D) {
+                                ssq = fmaf(v[i], v[i], ssq);
+                                bad |= !(fabsf(v[i]) <= OP_MAX);     // (also catches NaN)
+                            } else {
+                                v[i] = (ok && dd < D + 3) ? 1.0f : 0.f;
+                            }
+                        }
+                        if (q < Q) {
+                            const op2_t p0 = f2op2(v[0], v[1]), p1 = f2op2(v[2], v[3]);
+                            const uint32_t dst = tile_s + (uint32_t)((q >> 4) * A_KB_BYTES) + (uint32_t)r * 128u +
+                                                 (((uint32_t)((q & 15) >> 1) ^ (uint32_t)(r & 7)) << 4) + (uint32_t)(q & 1) * 8u;
+                            asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(dst),
+                                         "r"(*reinterpret_cast<const uint32_t *>(&p0)),
+                                         "r"(*reinterpret_cast<const uint32_t *>(&p1))
+                                         : "memory");
+                        }
+                        // row norm: this pass's lanes, fixed shuffle tree; passes accumulate in order (deterministic)
+                        ssq = warp_sum(ssq);
+                        const bool any_bad = __any_sync(0xffffffffu, bad);
+                        if (lane == u) {          // lane u keeps row r0+u's running (ss, bad) across the passes
+                            row_ss = (p == 0 ? 0.f : row_ss) + ssq;
+                            row_bad_acc = (p == 0 ? false : row_bad_acc) || any_bad;
+                        }
+                    }
+                }
+                if (lane < 8) {
+                    const int64_t row = (int64_t)tile * BM + r0 + lane;
+                    if (row < n_rows) zn_out[row] = row_bad_acc ? -1.0f : sqrtf(row_ss);   // negative: exact scan for this row
+                }
+            }
             __threadfence();                 // zn is read by this CTA's epilogue warps (ld.cg) and by the rescore pass
             ptx::fence_proxy_async();        // the tile is read by the tensor core through the async proxy
             __syncwarp();
@@ -600,18 +622,33 @@ __global__ void __launch_bounds__(CONV ? NT_CONV : NT, 1) vq_tc_kernel(const __g
                     }
 #pragma unroll
                     for (int j = 0; j < 4; ++j) {
-                        // window mask of the chunk, always and branch-free: sign bit of (v - Tm) shifted in, last element
-                        // first so that element e lands in bit e (2 instructions per element)
+                        const bool put = (cm[j] <= T) && row_ok;
+                        uint32_t info = (uint32_t)(code0 + b * 32 + 8 * j);
+#ifdef LIPVQ_EPI_PRED
+                        // branch-free variant (A/B: measured SLOWER, 4.4 k vs 3.1-3.5 k cycles per accumulator -- the ALU
+                        // pipe, not divergence, is what the epilogue runs out of): mask always, predicated record
                         uint32_t m = 0;
 #pragma unroll
                         for (int e = 7; e >= 0; --e)
                             m = __funnelshift_l(__float_as_uint(__uint_as_float(r[8 * j + e]) - Tm), m, 1);
-                        // PREDICATED record: one entry per chunk whose minimum is inside the running window
-                        const bool put = (cm[j] <= T) && row_ok;
-                        const uint32_t info = (uint32_t)(code0 + b * 32 + 8 * j) | (m << 24);
+                        info |= m << 24;
                         st_global_v2_if(out + cnt * BM, __float_as_uint(cm[j]), info, put);
                         cnt += put ? 1 : 0;
-                        // the two smallest chunk minima of this (row, part) stay in registers: the tile-end decision
+#else
+                        // one record per chunk whose minimum is inside the running window: the window mask of its 8
+                        // elements (sign bit of v - Tm shifted in, last element first so that element e lands in bit e)
+                        if (put) {
+                            uint32_t m = 0;
+#pragma unroll
+                            for (int e = 7; e >= 0; --e)
+                                m = __funnelshift_l(__float_as_uint(__uint_as_float(r[8 * j + e]) - Tm), m, 1);
+                            info |= m << 24;
+                            out[cnt * BM] = make_uint2(__float_as_uint(cm[j]), info);
+                            ++cnt;
+                        }
+#endif
+                        // the two smallest chunk minima of this (row, part) stay in registers (a new part minimum is
+                        // always inside the running window, so its record -- and mask -- exists): the tile-end decision
                         // below needs nothing from memory
                         const bool lt = cm[j] < m1;
                         m2 = lt ? m1 : fminf(m2, cm[j]);
@@ -804,11 +841,14 @@ inline EncodeTiledFn encode_fn() {
     return fn;
 }
 // bf16 [rows, cols] row-major, box = {64 cols, box_rows}, 128-byte swizzle
-inline int make_tmap(CUtensorMap *m, const void *ptr, uint64_t rows, uint64_t cols, uint32_t box_rows) {
+// pitch_cols (default = cols): row pitch of the array in elements when only the first `cols` columns are exposed -- the
+// rest of a box is then out of bounds and zero-filled by the TMA unit instead of being fetched
+inline int make_tmap(CUtensorMap *m, const void *ptr, uint64_t rows, uint64_t cols, uint32_t box_rows,
+                     uint64_t pitch_cols = 0) {
     EncodeTiledFn fn = encode_fn();
     if (!fn) return LIPVQ_ECUDA;
     cuuint64_t dims[2] = {cols, rows};
-    cuuint64_t strides[1] = {cols * 2};
+    cuuint64_t strides[1] = {(pitch_cols ? pitch_cols : cols) * 2};
     cuuint32_t box[2] = {(cuuint32_t)KBLK, box_rows};
     cuuint32_t estr[2] = {1, 1};
 #ifdef LIPVQ_VQ_BF16
@@ -855,7 +895,9 @@ inline int launch_tc(const CUtensorMap &ta, const CUtensorMap &tb, const Geometr
     auto kern = vq_tc_kernel<NKB, A_BUFS, STAGES, CONV>;
     // (the attribute is per device and the call is cheap: set it on every launch, as set_smem in mlp_tc.cuh does)
     LIPVQ_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::TOTAL));
-    const int grid = (int)(g.n_tiles < kNumSMs ? g.n_tiles : kNumSMs);
+    int grid = (int)(g.n_tiles < kNumSMs ? g.n_tiles : kNumSMs);
+    static const int env_grid = [] { const char *e = getenv("LIPVQ_VQ_GRID"); return e ? atoi(e) : 0; }();   // A/B probe
+    if (env_grid > 0 && env_grid < grid) grid = env_grid;
     ProfScope prof("vq_tc_kernel", st);
     kern<<<grid, CONV ? NT_CONV : NT, L::TOTAL, st>>>(ta, tb, g.n, (int)g.n_tiles, g.nct, g.NK16, w.zn, w.emax,
                                                       OP_ABS * sqrtf((float)g.D), w.cand, w.cand_meta, g.K, idx,
@@ -895,7 +937,9 @@ inline int vq_tensor_search(const float *z, const float *E, const tc::Geometry &
     const int64_t n = g.n;
     const int D = g.D, K = g.K;
     CUtensorMap ta, tb;
-    LIPVQ_TRY(make_tmap(&tb, w.Eb, (uint64_t)g.Kp, (uint64_t)g.DKp, BN));
+    // only the DKz columns the MMA K steps read are exposed: the padding of the last 64-column block is zero-filled
+    // by the TMA unit, not streamed from L2 (the kernel is bound by the bytes each SM ingests per accumulator)
+    LIPVQ_TRY(make_tmap(&tb, w.Eb, (uint64_t)g.Kp, (uint64_t)g.DKz, BN, (uint64_t)g.DKp));
     if (conv) ta = tb;                    // (unused by the kernel in this mode)
     else LIPVQ_TRY(make_tmap(&ta, w.Zb, (uint64_t)g.Np, (uint64_t)g.DKz, BM));
     int rc = LIPVQ_ESHAPE;

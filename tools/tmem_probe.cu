@@ -176,6 +176,150 @@ static void run(const char *name, int ld_shape, int ld_warps, int ld_iters, int 
     CK(cudaFree(d));
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// (4) cta_group::2: a CTA pair issues M=256 MMAs from the leader CTA; each CTA holds its 128 rows of A and HALF of B
+//     (N/2 rows) in its own shared memory, so the per-SM shared-memory read per MMA drops from A 4 KB + B 8 KB to
+//     4 KB + 4 KB.  (5) the 1-CTA MMA stream while other warps write shared memory at the rate a TMA-fed B ring does.
+__device__ __forceinline__ uint32_t cluster_ctarank() { uint32_t r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return r; }
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\nbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(128, 1) probe2_kernel(int mma_n, int mma_count, Result *out) {
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t raw = ptx::smem_u32(smem_raw);
+    const uint32_t base = (raw + 1023u) & ~1023u;
+    uint8_t *gen = smem_raw + (base - raw);
+    const uint32_t sbar = base + 65536;
+    volatile uint32_t *tmem_slot = reinterpret_cast<volatile uint32_t *>(gen + 65536 + 16);
+    for (int i = threadIdx.x; i < 65536 / 4; i += blockDim.x) reinterpret_cast<uint32_t *>(gen)[i] = 0x3c003c00u;
+    ptx::fence_proxy_async();
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t rank = cluster_ctarank();
+    if (threadIdx.x == 0) { ptx::mbar_init(sbar, 1); ptx::fence_barrier_init(); }
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(ptx::smem_u32((const void *)tmem_slot)), "r"(512) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+    }
+    ptx::tc_fence_before();
+    cluster_sync_all();
+    ptx::tc_fence_after();
+    const uint32_t tmem0 = *tmem_slot;
+    long long t0 = 0, t1 = 0;
+    if (rank == 0 && warp == 1 && lane == 0) {
+        const uint32_t idesc = ptx::umma_idesc_f16(256, mma_n);
+        const uint64_t ad = ptx::umma_desc_sw128(base), bd = ptx::umma_desc_sw128(base + 16384);
+        t0 = clock64();
+        for (int i = 0; i < mma_count; ++i) {
+            const uint32_t d = tmem0 + (uint32_t)((i & 1) * 256);
+            asm volatile(
+                "{\n.reg .pred p;\nsetp.ne.b32 p, %4, 0;\n"
+                "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n}\n" ::"r"(d), "l"(ad + 2 * (i & 3)),
+                "l"(bd + 2 * (i & 3)), "r"(idesc), "r"(1u)
+                : "memory");
+        }
+        asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(sbar),
+                     "h"((uint16_t)3)
+                     : "memory");
+    }
+    if (warp == 1 && lane == 0) {
+        ptx::mbar_wait(sbar, 0);
+        t1 = clock64();
+        if (rank == 0) out[blockIdx.x >> 1].mma_cycles = t1 - t0;
+    }
+    ptx::tc_fence_before();
+    cluster_sync_all();
+    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem0), "r"(512) : "memory");
+}
+
+// 1-CTA SS MMA stream + `sts_warps` warps storing 16 B per lane to shared memory as fast as they can issue
+__global__ void __launch_bounds__(576, 1) probe3_kernel(int mma_n, int mma_count, int sts_warps, int sts_gap, Result *out) {
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t raw = ptx::smem_u32(smem_raw);
+    const uint32_t base = (raw + 1023u) & ~1023u;
+    uint8_t *gen = smem_raw + (base - raw);
+    const uint32_t sbar = base + 131072;
+    volatile uint32_t *tmem_slot = reinterpret_cast<volatile uint32_t *>(gen + 131072 + 16);
+    volatile int *stop = reinterpret_cast<volatile int *>(gen + 131072 + 32);
+    for (int i = threadIdx.x; i < 65536 / 4; i += blockDim.x) reinterpret_cast<uint32_t *>(gen)[i] = 0x3c003c00u;
+    ptx::fence_proxy_async();
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (threadIdx.x == 0) { ptx::mbar_init(sbar, 1); ptx::fence_barrier_init(); *stop = 0; }
+    if (warp == 0) ptx::tmem_alloc<512>(ptx::smem_u32((const void *)tmem_slot));
+    ptx::tc_fence_before();
+    __syncthreads();
+    ptx::tc_fence_after();
+    const uint32_t tmem0 = *tmem_slot;
+    long long bytes = 0;
+    if (warp == 1) {
+        if (lane == 0) {
+            const uint32_t idesc = ptx::umma_idesc_f16(128, mma_n);
+            const uint64_t ad = ptx::umma_desc_sw128(base), bd = ptx::umma_desc_sw128(base + 16384);
+            const long long t0 = clock64();
+            for (int i = 0; i < mma_count; ++i)
+                ptx::umma_bf16(tmem0 + (uint32_t)((i & 1) * 256), ad + 2 * (i & 3), bd + 2 * (i & 3), idesc, 1u);
+            ptx::umma_commit(sbar);
+            ptx::mbar_wait(sbar, 0);
+            out[blockIdx.x].mma_cycles = clock64() - t0;
+            *stop = 1;
+        }
+    } else if (warp >= 2 && warp < 2 + sts_warps) {
+        // the second 64 KB of the buffer plays the B ring being refilled
+        uint32_t dst = base + 65536 + (uint32_t)((warp - 2) * 4096 + lane * 16);
+        int it = 0;
+        const long long t0 = clock64();
+        while (!*stop) {
+            asm volatile("st.shared.v4.b32 [%0], {%1, %1, %1, %1};" ::"r"(dst + (uint32_t)((it & 7) * 512)), "r"(it) : "memory");
+            ++it;
+            bytes += 512;
+            for (int g = 0; g < sts_gap; ++g) asm volatile("nanosleep.u32 0;" :::);
+        }
+        if (lane == 0 && warp == 2) out[blockIdx.x].ld_cycles = (long long)((double)bytes * sts_warps / (double)(clock64() - t0) * 1000.0);
+    }
+    ptx::tc_fence_before();
+    __syncthreads();
+    if (warp == 0) ptx::tmem_dealloc<512>(tmem0);
+}
+
+static void run2(int mma_n, int mma_count) {
+    const int pairs = 74;
+    Result *d;
+    CK(cudaMalloc(&d, sizeof(Result) * pairs));
+    CK(cudaMemset(d, 0, sizeof(Result) * pairs));
+    const int smem = 65536 + 64 + 1024;
+    CK(cudaFuncSetAttribute(probe2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    for (int rep = 0; rep < 2; ++rep) {
+        probe2_kernel<<<2 * pairs, 128, smem>>>(mma_n, mma_count, d);
+        CK(cudaDeviceSynchronize());
+    }
+    Result h[74];
+    CK(cudaMemcpy(h, d, sizeof(Result) * pairs, cudaMemcpyDeviceToHost));
+    double mc = 0;
+    for (int i = 0; i < pairs; ++i) mc += h[i].mma_cycles;
+    mc /= pairs;
+    printf("mma SS cta_group::2 M=256 N=%-3d (74 CTA pairs)   mma: %9.0f cyc  %6.1f cyc/MMA (per 128-row half: nominal %d)\n", mma_n, mc,
+           mc / mma_count, mma_n / 2);
+    CK(cudaFree(d));
+}
+static void run3(int mma_n, int mma_count, int sts_warps, int gap) {
+    Result *d;
+    CK(cudaMalloc(&d, sizeof(Result) * 148));
+    CK(cudaMemset(d, 0, sizeof(Result) * 148));
+    const int smem = 131072 + 64 + 1024;
+    CK(cudaFuncSetAttribute(probe3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    for (int rep = 0; rep < 2; ++rep) {
+        probe3_kernel<<<148, (2 + sts_warps) * 32, smem>>>(mma_n, mma_count, sts_warps, gap, d);
+        CK(cudaDeviceSynchronize());
+    }
+    Result h[148];
+    CK(cudaMemcpy(h, d, sizeof(Result) * 148, cudaMemcpyDeviceToHost));
+    double mc = 0, bw = 0;
+    for (int i = 0; i < 148; ++i) { mc += h[i].mma_cycles; bw += h[i].ld_cycles / 1000.0; }
+    printf("mma SS N=%d + %2d warps of st.shared.v4 (gap %d)    mma: %6.1f cyc/MMA   shared-memory writes %6.1f B/clk/SM\n", mma_n, sts_warps, gap,
+           mc / 148 / mma_count, bw / 148);
+    CK(cudaFree(d));
+}
+
 int main() {
     int dev = 0;
     cudaDeviceProp p;
@@ -203,5 +347,14 @@ int main() {
     run("ld x32 16 warps + mma SS N=128", 2, 16, 64, 1, 128, 4096, G);
     run("ld x32  8 warps + mma SS N=256", 2, 8, 64, 1, 256, 2048, G);
     run("ld x32 16 warps + mma TS N=256", 2, 16, 64, 2, 256, 2048, G);
+    // (4) CTA pairs
+    run2(256, 512);
+    run2(128, 512);
+    // (5) shared-memory write traffic beside the 1-CTA MMA stream
+    run3(256, 2048, 0, 0);
+    run3(256, 2048, 1, 8);
+    run3(256, 2048, 2, 4);
+    run3(256, 2048, 4, 0);
+    run3(256, 2048, 8, 0);
     return 0;
 }
