@@ -986,9 +986,13 @@ inline int vq_tensor_launch(const float *z, const float *E, int64_t n, int D, in
     const Geometry g = geometry(n, D, K);
     const Workspace w = carve((void *)align_up((size_t)ws, 1024), g);
     LIPVQ_TRY(vq_tensor_prep(E, g, w, st));
-    // LIPVQ_VQ_CONVERT=pass restores the separate conversion pass over z (A/B timing)
-    static const bool sep = [] { const char *e = getenv("LIPVQ_VQ_CONVERT"); return e && !strcmp(e, "pass"); }();
-    if (!sep) return vq_tensor_search(z, E, g, w, idx, d2, stats, st, true);
+    // LIPVQ_VQ_CONVERT=fused builds the row operand inside the search kernel (converter warps) instead of the separate
+    // conversion pass below.  Measured at N=2^20, D=64, K=1024 (profiles/r02_*): pass 0.118 + search 0.33 ms against
+    // 0.49 ms (thread-per-row converter, 4 extra warps) or 1.4 ms (coalesced converter on the 2 spare warps: latency
+    // bound) for the fused kernel -- the register budget of the 16 epilogue warps leaves no room for enough converter
+    // warps, so the separate pass stays the default.
+    static const bool fused = [] { const char *e = getenv("LIPVQ_VQ_CONVERT"); return e && !strcmp(e, "fused"); }();
+    if (fused) return vq_tensor_search(z, E, g, w, idx, d2, stats, st, true);
     {
         const int cpr = g.DKz >> 3;
         const int rpb = cpr <= 32 ? 8 * (32 / cpr) : 256 / cpr;
