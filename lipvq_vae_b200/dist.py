@@ -264,4 +264,4 @@ class TokenizerTrainer:
         else:
             self.opt.step(b.flat)
         _bump_param_epoch(m)
-        return z_q, b.extra[0]
+        return z_q, b.extra[0].clone()          # (a copy: the bucket is overwritten by the next step)
