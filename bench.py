@@ -298,7 +298,11 @@ def run_ours(args, rank, world, local_rank):
              "allreduce_bytes": int(trainer.dp._bucket.flat.numel() * 4), "timing": "CUDA events, max over ranks"}
     # per-kernel split of the training step (library CUDA events around each launch, after the timed region).  EVERY
     # rank runs these three steps -- each contains the gradient all-reduce -- and only rank 0 keeps the report.
+    # (with the decoder-side and encoder-side backward on ONE stream: on two streams the event pairs of concurrent
+    #  kernels overlap and every duration is inflated)
+    trainer.concurrent_backward = False
     rep = N.profile_kernels(train_step, 3)
+    trainer.concurrent_backward = True
     torch.cuda.synchronize()
     barrier()
     if rank == 0:
@@ -415,13 +419,13 @@ def run_ours(args, rank, world, local_rank):
     ) if r]
     # dram bytes per launch of the same kernels on the same workload, from the committed ncu --set full capture
     try:
-        _traffic = json.load(open(os.path.join(ROOT, "profiles", "r01_traffic.json")))["kernels"]
+        _traffic = json.load(open(os.path.join(ROOT, "profiles", "r02_traffic.json")))["kernels"]
     except Exception:
         _traffic = {}
     for r in rooflines:
         t_ = _traffic.get(r["kernel"])
         r["traffic"] = t_["total_bytes"] if t_ else None
-        r["traffic_source"] = "profiles/r01_traffic.json (ncu dram__bytes_read.sum + dram__bytes_write.sum)" if t_ else None
+        r["traffic_source"] = "profiles/r02_traffic.json (ncu dram__bytes_read.sum + dram__bytes_write.sum)" if t_ else None
     for r in rooflines:
         r["peak_source"] = peak_src + (" bf16 sustained (kernel timed inside the step)" if r["bound"] == "tensor"
                                        else " HBM copy bandwidth")

@@ -24,7 +24,7 @@ KEYS = ["gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum
         "sm__inst_executed_pipe_xu.avg.pct_of_peak_sustained_active",
         "smsp__inst_executed.sum", "launch__registers_per_thread", "launch__grid_size", "launch__block_size",
         "sm__warps_active.avg.pct_of_peak_sustained_active"]
-ALIAS = {"enc16_fused_kernel": "enc_fused_kernel"}     # the name bench.py's per-kernel events use
+ALIAS = {}     # (r1 aliased enc16_fused_kernel to the bench label of the time)
 MULT = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
 lines, traffic, seen = [header], {}, set()
 for r in rows[2:]:
