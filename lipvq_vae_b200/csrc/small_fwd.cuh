@@ -21,6 +21,29 @@ constexpr int SDC = 64;          // latent columns per staged codebook chunk
 constexpr int SPITCH = SDC + 4;  // padded pitch (floats): lane stride 17 float4 -> conflict-free 128-bit reads
 constexpr int MAX_ROWS = 2048;   // above this the tensor path wins
 
+// weight / bias read: a plain generic load -- the pointers are global memory in the direct variant and shared memory in
+// the staged one
+__device__ __forceinline__ float ldw(const float *p) { return *p; }
+
+// 16-byte asynchronous global -> shared copies (LDGSTS): whole weight matrices and codebook tiles are put in flight at
+// once, the kernel being a chain of L2 round trips otherwise.  src_bytes = 0 zero-fills the destination.
+__device__ __forceinline__ void cp_async16(void *dst, const void *src, int src_bytes = 16) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"((uint32_t)__cvta_generic_to_shared(dst)), "l"(src),
+                 "r"(src_bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+// n floats, whole CTA; 16-byte path when both sides allow it
+__device__ __forceinline__ void stage_floats(float *dst, const float *__restrict__ src, int n) {
+    if ((n & 3) == 0 && ((reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(dst)) & 15) == 0) {
+        for (int i = threadIdx.x; i < (n >> 2); i += ST) cp_async16(dst + 4 * i, src + 4 * i);
+    } else {
+        for (int i = threadIdx.x; i < n; i += ST) dst[i] = __ldg(src + i);
+    }
+}
+
 // one layer for the CTA's SR rows: warp per output neuron (NJ in flight), lanes stride the reduction axis
 template <int ACT>
 __device__ __forceinline__ void rows_layer(const float *__restrict__ W, const float *__restrict__ bias, int n_out,
@@ -38,7 +61,7 @@ __device__ __forceinline__ void rows_layer(const float *__restrict__ W, const fl
         for (int k = lane; k < k_in; k += 32) {      // (the kernel is latency bound: keep 16 weight loads in flight)
             float w[NJ];
 #pragma unroll
-            for (int q = 0; q < NJ; ++q) w[q] = j0 + q < n_out ? __ldg(W + (size_t)(j0 + q) * k_in + k) : 0.f;
+            for (int q = 0; q < NJ; ++q) w[q] = j0 + q < n_out ? ldw(W + (size_t)(j0 + q) * k_in + k) : 0.f;
 #pragma unroll
             for (int r = 0; r < SR; ++r) {
                 const float a = s_in[r * k_in + k];
@@ -56,7 +79,7 @@ __device__ __forceinline__ void rows_layer(const float *__restrict__ W, const fl
                 float v = 0.f;
 #pragma unroll
                 for (int r = 0; r < SR; ++r) v = lane == r ? acc[q][r] : v;
-                v = apply_act<ACT>(v + __ldg(bias + j));
+                v = apply_act<ACT>(v + ldw(bias + j));
                 s_out[lane * n_out + j] = v;
                 if (g_out && lane < rows_valid) g_out[(size_t)lane * n_out + j] = v;
             }
@@ -81,7 +104,7 @@ __device__ __forceinline__ void lipschitz_rows_layer(const float *__restrict__ W
 #pragma unroll
                 for (int t = 0; t < KR; ++t) {
                     const int k = lane + 32 * t;
-                    w[q][t] = (j0 + q < n_out && k < k_in) ? __ldg(W + (size_t)(j0 + q) * k_in + k) : 0.f;
+                    w[q][t] = (j0 + q < n_out && k < k_in) ? ldw(W + (size_t)(j0 + q) * k_in + k) : 0.f;
                 }
 #pragma unroll
             for (int q = 0; q < NJ; ++q) {
@@ -93,7 +116,7 @@ __device__ __forceinline__ void lipschitz_rows_layer(const float *__restrict__ W
             float acc[NJ][SR];
 #pragma unroll
             for (int q = 0; q < NJ; ++q) {
-                const float sc = j0 + q < n_out ? fminf(1.0f, softplus_f(__ldg(ci + j0 + q)) / s[q]) : 0.f;
+                const float sc = j0 + q < n_out ? fminf(1.0f, softplus_f(ldw(ci + j0 + q)) / s[q]) : 0.f;
 #pragma unroll
                 for (int r = 0; r < SR; ++r) acc[q][r] = 0.f;
 #pragma unroll
@@ -116,7 +139,7 @@ __device__ __forceinline__ void lipschitz_rows_layer(const float *__restrict__ W
                     float v = 0.f;
 #pragma unroll
                     for (int r = 0; r < SR; ++r) v = lane == r ? acc[q][r] : v;
-                    s_out[lane * out_pitch + j] = sigmoid_f(v + __ldg(bias + j));
+                    s_out[lane * out_pitch + j] = sigmoid_f(v + ldw(bias + j));
                 }
             }
         }
@@ -125,14 +148,14 @@ __device__ __forceinline__ void lipschitz_rows_layer(const float *__restrict__ W
     for (int j = warp; j < n_out; j += nwarp) {
         const float *wr = W + (size_t)j * k_in;
         float s = 0.f;
-        for (int k = lane; k < k_in; k += 32) s += fabsf(__ldg(wr + k));
+        for (int k = lane; k < k_in; k += 32) s += fabsf(ldw(wr + k));
         s = warp_sum(s);
-        const float sc = fminf(1.0f, softplus_f(__ldg(ci + j)) / s);
+        const float sc = fminf(1.0f, softplus_f(ldw(ci + j)) / s);
         float acc[SR];
 #pragma unroll
         for (int r = 0; r < SR; ++r) acc[r] = 0.f;
         for (int k = lane; k < k_in; k += 32) {
-            const float w = __ldg(wr + k) * sc;
+            const float w = ldw(wr + k) * sc;
 #pragma unroll
             for (int r = 0; r < SR; ++r) acc[r] = fmaf(w, s_in[r * k_in + k], acc[r]);
         }
@@ -142,7 +165,7 @@ __device__ __forceinline__ void lipschitz_rows_layer(const float *__restrict__ W
             float v = 0.f;
 #pragma unroll
             for (int r = 0; r < SR; ++r) v = lane == r ? acc[r] : v;
-            s_out[lane * out_pitch + j] = sigmoid_f(v + __ldg(bias + j));
+            s_out[lane * out_pitch + j] = sigmoid_f(v + ldw(bias + j));
         }
     }
 }
@@ -172,6 +195,10 @@ inline Scratch carve(void *ws, int64_t n, size_t *zero_bytes) {
     return s;
 }
 
+// STAGED: the encoder (then, in the finishing CTA, the decoder) weights are copied into shared memory with one wave of
+// 16-byte asynchronous copies, and the codebook tiles are double buffered, so the kernel pays a handful of L2 round
+// trips instead of ~40 dependent ones; needs enc/dec weights <= ~150 KB (latent_dim <= ~256), else the direct variant.
+template <bool STAGED>
 __global__ void __launch_bounds__(ST) small_forward_kernel(
     lipvq_params_t p, const float *__restrict__ x, int n_rows, int F, int H1, int H, int D, int K, int splits,
     Scratch sc, float *__restrict__ z_latent, int64_t *__restrict__ idx_out, float *__restrict__ x_recon,
@@ -181,7 +208,7 @@ __global__ void __launch_bounds__(ST) small_forward_kernel(
     // tiles (re-used as z_q + decoder activations by the finishing CTA)
     const int ZP = (D + SDC - 1) / SDC * SDC;
     float *s_x = sm, *s_h1 = s_x + SR * F, *s_h2 = s_h1 + SR * H1, *s_z = s_h2 + SR * H;
-    float *s_tile = s_z + SR * ZP;
+    float *s_tile = s_z + SR * ZP;      // big region: STAGED: encoder weights, then 2 x tiles, then decoder weights
     __shared__ float red[ST / 32];
     __shared__ int s_ticket;
     __shared__ int s_idx[SR];
@@ -195,20 +222,44 @@ __global__ void __launch_bounds__(ST) small_forward_kernel(
         s_x[i] = r < rows_valid ? x[(size_t)r0 * F + i] : 0.f;
     }
     for (int i = tid; i < SR * ZP; i += ST) s_z[i] = 0.f;
+    const float *w0 = p.enc0_w, *b0 = p.enc0_b, *w1 = p.enc2_w, *b1 = p.enc2_b, *wl = p.lat_W, *bl = p.lat_b, *cl = p.lat_ci;
+    if (STAGED) {
+        float *q = s_tile;               // (every piece starts 16-byte aligned: sizes are rounded up to 4 floats)
+        auto put = [&](const float *src, int n) { float *d = q; stage_floats(d, src, n); q += (n + 3) & ~3; return (const float *)d; };
+        w0 = put(p.enc0_w, H1 * F); b0 = put(p.enc0_b, H1); w1 = put(p.enc2_w, H * H1); b1 = put(p.enc2_b, H);
+        wl = put(p.lat_W, D * H); bl = put(p.lat_b, D); cl = put(p.lat_ci, D);
+        cp_async_commit();
+        cp_async_wait<0>();
+    }
     __syncthreads();
-    rows_layer<ACT_GELU>(p.enc0_w, p.enc0_b, H1, F, s_x, s_h1, nullptr, 0);
+    rows_layer<ACT_GELU>(w0, b0, H1, F, s_x, s_h1, nullptr, 0);
     __syncthreads();
-    rows_layer<ACT_GELU>(p.enc2_w, p.enc2_b, H, H1, s_h1, s_h2, nullptr, 0);
+    rows_layer<ACT_GELU>(w1, b1, H, H1, s_h1, s_h2, nullptr, 0);
     __syncthreads();
-    lipschitz_rows_layer(p.lat_W, p.lat_b, p.lat_ci, D, H, s_h2, s_z, ZP);
-    __syncthreads();
+    lipschitz_rows_layer(wl, bl, cl, D, H, s_h2, s_z, ZP);
+    __syncthreads();          // (STAGED: the weight region is free from here on: the codebook tiles take it over)
 
     // ---- this CTA's slice of the codebook: codes [k_lo, k_hi), 32-code tiles dealt to the warps round-robin
     {
         const int per = ((K + splits - 1) / splits + 31) / 32 * 32;
         const int k_lo = split * per, k_hi = min(K, k_lo + per);
         const bool vec = (D & 3) == 0;
-        float *tile = s_tile + warp * 32 * SPITCH;
+        float *tile = s_tile + warp * (STAGED ? 2 : 1) * 32 * SPITCH;
+        // STAGED: chunk i+1 of this warp's (tile, column chunk) sequence is in flight while chunk i is used
+        const int nchunk = (D + SDC - 1) / SDC;
+        auto issue_chunk = [&](int t0, int d0, float *buf) {
+            const int dc = min(SDC, D - d0);
+            for (int i = lane; i < 32 * (SDC / 4); i += 32) {
+                const int c = i / (SDC / 4), q = i - c * (SDC / 4);
+                const int code = t0 + c;
+                const bool in = code < k_hi && 4 * q < dc;
+                cp_async16(buf + c * SPITCH + 4 * q, p.codebook + (in ? (size_t)code * D + d0 + 4 * q : 0), in ? 16 : 0);
+            }
+            cp_async_commit();
+        };
+        const bool pipelined = STAGED && vec;
+        if (pipelined && k_lo + warp * 32 < k_hi) issue_chunk(k_lo + warp * 32, 0, tile);
+        int seq = 0;
         float bd[SR];
         int bk[SR];
 #pragma unroll
@@ -220,8 +271,21 @@ __global__ void __launch_bounds__(ST) small_forward_kernel(
             for (int d0 = 0; d0 < D; d0 += SDC) {
                 const int dc = min(SDC, D - d0);
                 // stage 32 codes x SDC columns (zero past the row / the slice): coalesced global reads, padded pitch
+                float *cur = tile;
+                if (pipelined) {
+                    cur = tile + (seq & 1) * 32 * SPITCH;
+                    float *nxt = tile + ((seq + 1) & 1) * 32 * SPITCH;
+                    __syncwarp();                        // every lane is done reading the buffer about to be refilled
+                    const bool last_chunk = d0 + SDC >= D;
+                    const int nt0 = last_chunk ? t0 + (ST / 32) * 32 : t0, nd0 = last_chunk ? 0 : d0 + SDC;
+                    if (nt0 < k_hi) { issue_chunk(nt0, nd0, nxt); cp_async_wait<1>(); }
+                    else cp_async_wait<0>();
+                    ++seq;
+                    (void)nchunk;
+                } else
                 __syncwarp();
-                if (vec) {
+                if (pipelined) {
+                } else if (vec) {
                     for (int i = lane; i < 32 * (SDC / 4); i += 32) {
                         const int c = i / (SDC / 4), q = i - c * (SDC / 4);
                         const int code = t0 + c;
@@ -238,7 +302,7 @@ __global__ void __launch_bounds__(ST) small_forward_kernel(
                     }
                 }
                 __syncwarp();
-                const float4 *tl = reinterpret_cast<const float4 *>(tile + lane * SPITCH);
+                const float4 *tl = reinterpret_cast<const float4 *>(cur + lane * SPITCH);
                 const int nq = (dc + 3) >> 2;
 #pragma unroll 4
                 for (int q = 0; q < nq; ++q) {
@@ -297,6 +361,14 @@ __global__ void __launch_bounds__(ST) small_forward_kernel(
     }
     __syncthreads();
     float *s_q = s_tile, *s_c1 = s_q + SR * D, *s_c2 = s_c1 + SR * H1, *s_o = s_c2 + SR * H;
+    const float *v0 = p.dec0_w, *c0 = p.dec0_b, *v1 = p.dec2_w, *c1 = p.dec2_b, *vo = p.out_w, *co = p.out_b;
+    if (STAGED) {
+        float *q = s_o + ((SR * F + 3) & ~3);
+        auto put = [&](const float *src, int n) { float *d = q; stage_floats(d, src, n); q += (n + 3) & ~3; return (const float *)d; };
+        v0 = put(p.dec0_w, H1 * D); c0 = put(p.dec0_b, H1); v1 = put(p.dec2_w, H * H1); c1 = put(p.dec2_b, H);
+        vo = put(p.out_w, F * H); co = put(p.out_b, F);
+        cp_async_commit();               // (lands while the gather below runs)
+    }
     float sq = 0.f;
     for (int i = tid; i < SR * D; i += ST) {
         const int r = i / D, d = i - r * D;
@@ -308,12 +380,13 @@ __global__ void __launch_bounds__(ST) small_forward_kernel(
             sq = fmaf(df, df, sq);
         }
     }
+    if (STAGED) cp_async_wait<0>();
     __syncthreads();
-    rows_layer<ACT_GELU>(p.dec0_w, p.dec0_b, H1, D, s_q, s_c1, nullptr, 0);
+    rows_layer<ACT_GELU>(v0, c0, H1, D, s_q, s_c1, nullptr, 0);
     __syncthreads();
-    rows_layer<ACT_GELU>(p.dec2_w, p.dec2_b, H, H1, s_c1, s_c2, nullptr, 0);
+    rows_layer<ACT_GELU>(v1, c1, H, H1, s_c1, s_c2, nullptr, 0);
     __syncthreads();
-    rows_layer<ACT_NONE>(p.out_w, p.out_b, F, H, s_c2, s_o, x_recon ? x_recon + (size_t)r0 * F : nullptr, rows_valid);
+    rows_layer<ACT_NONE>(vo, co, F, H, s_c2, s_o, x_recon ? x_recon + (size_t)r0 * F : nullptr, rows_valid);
     __syncthreads();
     float sr = 0.f;
     for (int i = tid; i < rows_valid * F; i += ST) {
@@ -347,12 +420,20 @@ __global__ void __launch_bounds__(ST) small_forward_kernel(
     }
 }
 
-inline size_t smem_bytes(const lipvq_dims_t *d) {
+inline size_t r4(size_t n) { return (n + 3) & ~(size_t)3; }
+inline size_t smem_bytes(const lipvq_dims_t *d, bool staged = false) {
     const size_t head = (size_t)SR * (d->F + d->H1 + d->H + (d->D + SDC - 1) / SDC * SDC);
-    const size_t tiles = (size_t)(ST / 32) * 32 * SPITCH;
-    const size_t tail = (size_t)SR * (d->D + d->H1 + d->H + d->F);
-    return (head + (tiles > tail ? tiles : tail)) * sizeof(float);
+    size_t tiles = (size_t)(ST / 32) * 32 * SPITCH * (staged ? 2 : 1);
+    size_t tail = (size_t)SR * (d->D + d->H1 + d->H) + r4((size_t)SR * d->F);
+    if (staged) {
+        const size_t enc = r4((size_t)d->H1 * d->F) + r4(d->H1) + r4((size_t)d->H * d->H1) + r4(d->H) + r4((size_t)d->D * d->H) + 2 * r4(d->D);
+        const size_t dec = r4((size_t)d->H1 * d->D) + r4(d->H1) + r4((size_t)d->H * d->H1) + r4(d->H) + r4((size_t)d->F * d->H) + r4(d->F);
+        tail += dec;
+        if (enc > tiles) tiles = enc;
+    }
+    return (head + (tiles > tail ? tiles : tail)) * sizeof(float) + 64;
 }
+inline bool staged_ok(const lipvq_dims_t *d) { return smem_bytes(d, true) <= 200 * 1024; }
 inline bool supported(const lipvq_dims_t *d, int64_t n) {
     return n >= 1 && n <= MAX_ROWS && smem_bytes(d) <= 200 * 1024;
 }
@@ -366,18 +447,21 @@ inline int launch(const lipvq_dims_t *d, const lipvq_params_t *p, const float *x
     if (stats) LIPVQ_CUDA_OK(cudaMemsetAsync(stats, 0, 4 * sizeof(int32_t), st));
     const int G = (int)((n + SR - 1) / SR);
     // enough CTAs to cover the chip about twice, at least 32 codes per split
-    // every warp of a CTA should own a 32-code tile (256 codes per CTA) unless that leaves most of the chip idle
-    int splits = (d->K + 255) / 256;
-    while ((int64_t)splits * G < kNumSMs && splits * 32 < d->K) splits *= 2;
-    if (splits > 64) splits = 64;
+    // ONE wave of CTAs (the kernel is a chain of dependent L2 round trips: a second wave doubles its latency): as many
+    // codebook splits per row group as fit on the chip, whole 32-code tiles per split
+    int splits = kNumSMs / G;
     if (splits < 1) splits = 1;
-    const int per = ((d->K + splits - 1) / splits + 31) / 32 * 32;     // codes per split, whole 32-code tiles
+    if (splits > 64) splits = 64;
+    const int per = ((d->K + splits - 1) / splits + 31) / 32 * 32;     // codes per split
     splits = (d->K + per - 1) / per;                                   // (no empty slices)
-    const size_t smem = smem_bytes(d);
-    LIPVQ_CUDA_OK(cudaFuncSetAttribute(small_forward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    static const bool no_stage = [] { const char *e = getenv("LIPVQ_SMALL_STAGED"); return e && !strcmp(e, "0"); }();
+    const bool staged = !no_stage && staged_ok(d);
+    const size_t smem = smem_bytes(d, staged);
+    auto kern = staged ? small_forward_kernel<true> : small_forward_kernel<false>;
+    LIPVQ_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const double nt = (double)(n_total > 0 ? n_total : 1);
     ProfScope prof("small_forward_kernel", st);
-    small_forward_kernel<<<dim3(splits, G), ST, smem, st>>>(*p, x, (int)n, d->F, d->H1, d->H, d->D, d->K, splits, sc,
+    kern<<<dim3(splits, G), ST, smem, st>>>(*p, x, (int)n, d->F, d->H1, d->H, d->D, d->K, splits, sc,
                                                             z_latent, idx, x_recon, loss_out, 1.0 / (nt * d->F),
                                                             1.0 / (nt * d->D));
     LIPVQ_LAUNCH_OK();
