@@ -16,7 +16,8 @@ namespace lipvq {
 namespace small {
 
 constexpr int SR = 4;            // rows per row group (CTA)
-constexpr int ST = 256;          // threads per CTA
+constexpr int ST = 512;          // threads per CTA (16 warps: the layers are chains of shuffles and MUFU ops, latency bound)
+constexpr int TW = 8;            // warps that scan codebook tiles (each owns two 8.7 KB tile buffers)
 constexpr int SDC = 64;          // latent columns per staged codebook chunk
 constexpr int SPITCH = SDC + 4;  // padded pitch (floats): lane stride 17 float4 -> conflict-free 128-bit reads
 constexpr int MAX_ROWS = 2048;   // above this the tensor path wins
@@ -199,7 +200,7 @@ inline Scratch carve(void *ws, int64_t n, size_t *zero_bytes) {
 // 16-byte asynchronous copies, and the codebook tiles are double buffered, so the kernel pays a handful of L2 round
 // trips instead of ~40 dependent ones; needs enc/dec weights <= ~150 KB (latent_dim <= ~256), else the direct variant.
 template <bool STAGED>
-__global__ void __launch_bounds__(ST) small_forward_kernel(
+__global__ void __launch_bounds__(ST, 1) small_forward_kernel(
     lipvq_params_t p, const float *__restrict__ x, int n_rows, int F, int H1, int H, int D, int K, int splits,
     Scratch sc, float *__restrict__ z_latent, int64_t *__restrict__ idx_out, float *__restrict__ x_recon,
     float *__restrict__ loss_out, double inv_nf, double inv_nd) {
@@ -244,7 +245,7 @@ __global__ void __launch_bounds__(ST) small_forward_kernel(
         const int per = ((K + splits - 1) / splits + 31) / 32 * 32;
         const int k_lo = split * per, k_hi = min(K, k_lo + per);
         const bool vec = (D & 3) == 0;
-        float *tile = s_tile + warp * (STAGED ? 2 : 1) * 32 * SPITCH;
+        float *tile = s_tile + (warp < TW ? warp : 0) * (STAGED ? 2 : 1) * 32 * SPITCH;
         // STAGED: chunk i+1 of this warp's (tile, column chunk) sequence is in flight while chunk i is used
         const int nchunk = (D + SDC - 1) / SDC;
         auto issue_chunk = [&](int t0, int d0, float *buf) {
@@ -258,13 +259,13 @@ __global__ void __launch_bounds__(ST) small_forward_kernel(
             cp_async_commit();
         };
         const bool pipelined = STAGED && vec;
-        if (pipelined && k_lo + warp * 32 < k_hi) issue_chunk(k_lo + warp * 32, 0, tile);
+        if (pipelined && warp < TW && k_lo + warp * 32 < k_hi) issue_chunk(k_lo + warp * 32, 0, tile);
         int seq = 0;
         float bd[SR];
         int bk[SR];
 #pragma unroll
         for (int r = 0; r < SR; ++r) { bd[r] = INFINITY; bk[r] = 0x7fffffff; }
-        for (int t0 = k_lo + warp * 32; t0 < k_hi; t0 += (ST / 32) * 32) {
+        for (int t0 = k_lo + warp * 32; warp < TW && t0 < k_hi; t0 += TW * 32) {
             float acc[SR];
 #pragma unroll
             for (int r = 0; r < SR; ++r) acc[r] = 0.f;
@@ -277,7 +278,7 @@ __global__ void __launch_bounds__(ST) small_forward_kernel(
                     float *nxt = tile + ((seq + 1) & 1) * 32 * SPITCH;
                     __syncwarp();                        // every lane is done reading the buffer about to be refilled
                     const bool last_chunk = d0 + SDC >= D;
-                    const int nt0 = last_chunk ? t0 + (ST / 32) * 32 : t0, nd0 = last_chunk ? 0 : d0 + SDC;
+                    const int nt0 = last_chunk ? t0 + TW * 32 : t0, nd0 = last_chunk ? 0 : d0 + SDC;
                     if (nt0 < k_hi) { issue_chunk(nt0, nd0, nxt); cp_async_wait<1>(); }
                     else cp_async_wait<0>();
                     ++seq;
@@ -423,7 +424,7 @@ __global__ void __launch_bounds__(ST) small_forward_kernel(
 inline size_t r4(size_t n) { return (n + 3) & ~(size_t)3; }
 inline size_t smem_bytes(const lipvq_dims_t *d, bool staged = false) {
     const size_t head = (size_t)SR * (d->F + d->H1 + d->H + (d->D + SDC - 1) / SDC * SDC);
-    size_t tiles = (size_t)(ST / 32) * 32 * SPITCH * (staged ? 2 : 1);
+    size_t tiles = (size_t)TW * 32 * SPITCH * (staged ? 2 : 1);
     size_t tail = (size_t)SR * (d->D + d->H1 + d->H) + r4((size_t)SR * d->F);
     if (staged) {
         const size_t enc = r4((size_t)d->H1 * d->F) + r4(d->H1) + r4((size_t)d->H * d->H1) + r4(d->H) + r4((size_t)d->D * d->H) + 2 * r4(d->D);
