@@ -226,7 +226,7 @@ int lipvq_forward_fused(const lipvq_dims_t *dims, const lipvq_params_t *p, const
 
 /* The same forward as ONE kernel launch (+ one memset node) for the reference's real call sizes, N = B*T = 80 / 500
  * rows (v5:89-93; obs_nets.py:1298): exact fp32 on the CUDA cores, direct-form distances sum (z-e)^2, first minimal
- * index on ties, deterministic loss reduction.  lipvq_forward_fused routes here by itself for n_rows <= 2048;
+ * index on ties, deterministic loss reduction.  lipvq_forward_fused routes here by itself for n_rows <= 768 (the measured crossover);
  * this entry point accepts up to 65 536 rows.  ws: 8 B per row + 12 B per 4 rows + 1 KB. */
 int lipvq_forward_small(const lipvq_dims_t *dims, const lipvq_params_t *p, const float *x,
                         int64_t n_rows, int64_t n_total, float *z_latent, int64_t *idx, float *x_recon,

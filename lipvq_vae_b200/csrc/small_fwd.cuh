@@ -20,7 +20,8 @@ constexpr int ST = 512;          // threads per CTA (16 warps: the layers are ch
 constexpr int TW = 8;            // warps that scan codebook tiles (each owns two 8.7 KB tile buffers)
 constexpr int SDC = 64;          // latent columns per staged codebook chunk
 constexpr int SPITCH = SDC + 4;  // padded pitch (floats): lane stride 17 float4 -> conflict-free 128-bit reads
-constexpr int MAX_ROWS = 2048;   // above this the tensor path wins
+constexpr int MAX_ROWS = 768;    // measured crossover with the multi-launch tensor path (~110 us of launches): 47 us at 80
+                                 // rows, 66 us at 500, 121 us at 1024 for this kernel
 
 // weight / bias read: a plain generic load -- the pointers are global memory in the direct variant and shared memory in
 // the staged one
