@@ -395,7 +395,7 @@ def test_fused_paths_ragged_and_unaligned_shapes(n, D, K):
     loss.backward()
     torch.cuda.synchronize()
     idx = m.last_indices.cpu().numpy()
-    # the no-grad call of <= 2048 rows runs the single-kernel exact path (csrc/small_fwd.cuh), the autograd call the
+    # the no-grad call of <= 768 rows runs the single-kernel exact path (csrc/small_fwd.cuh), the autograd call the
     # tensor path: their encoders round differently (1e-6), so they may only disagree inside the near-tie window
     mt = torch.from_numpy(must).cuda()
     assert np.array_equal(idx[must], idx0[must]) and torch.equal(z_lat[mt], z_lat0[mt])
