@@ -21,7 +21,7 @@
 namespace lipvq {
 namespace bwd5 {
 
-constexpr int NLOAD = 256;          // 8 converter warps
+constexpr int NLOAD = 512;          // 16 converter warps
 constexpr int NTHR = NLOAD + 64;    // + 1 MMA-issuing warp + 1 TMA producer warp
 constexpr int R = 16;               // rows per slab
 constexpr int KG = R / 8;           // one kind::tf32 MMA consumes 8 rows (K = 8)
@@ -32,6 +32,23 @@ constexpr int MAX_NOUT = 256, MAX_KIN = 128;
 __device__ __forceinline__ void split_rna(float v, uint32_t &hi, uint32_t &lo) {
     asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(hi) : "f"(v));
     lo = __float_as_uint(v - __uint_as_float(hi));
+}
+
+// 256-bit global accesses (sm_100: LDG.E.ENL2.256 / STG.E.ENL2.256): a thread that walks its OWN row touches a
+// different 128-byte line than its neighbours, so the L1 spends one wavefront per thread and instruction whatever
+// the width -- 32 bytes per wavefront instead of 16 is what takes dgrad_umma_kernel off the L1 limit (ncu round 2:
+// l1tex 69-97 % of peak with 128-bit accesses).
+struct __align__(32) F8 { float v[8]; };
+__device__ __forceinline__ F8 ldg256(const float *p) {
+    F8 r;
+    asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=f"(r.v[0]), "=f"(r.v[1]), "=f"(r.v[2]), "=f"(r.v[3]), "=f"(r.v[4]), "=f"(r.v[5]), "=f"(r.v[6]), "=f"(r.v[7])
+                 : "l"(p));
+    return r;
+}
+__device__ __forceinline__ void stg256(float *p, const F8 &r) {
+    asm volatile("st.global.v8.f32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "f"(r.v[0]), "f"(r.v[1]), "f"(r.v[2]),
+                 "f"(r.v[3]), "f"(r.v[4]), "f"(r.v[5]), "f"(r.v[6]), "f"(r.v[7]) : "memory");
 }
 
 // MN-major fp32/tf32 operands have ONE legal shared-memory layout on sm_100: SWIZZLE_128B_BASE32B (layout type 1),
@@ -91,9 +108,12 @@ __device__ __forceinline__ void named_sync_loaders() { asm volatile("bar.sync 1,
 // core accumulates with truncation, a bias that grows with the number of accumulations (measured 7e-9 per row),
 // so a TMEM accumulator only collects a chunk of CH slabs (256 rows); at a chunk end the converter warps add it
 // (fp32, round-to-nearest) to a master accumulator in the other half of TMEM (tcgen05.ld / add / tcgen05.st).
-__global__ void __launch_bounds__(NTHR, 1)
+template <int W>   // converter warps per group (a multiple of 4); NLOAD / 32 / W groups convert that many slabs concurrently
+__global__ void __launch_bounds__(NTHR, 1)   // 18 warps = 5 on one scheduler: 96 registers per thread
 wgrad_umma_kernel(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__ CUtensorMap tm_q, int64_t rows,
-                  int Nout, int Kin, int64_t rows_per_cta, float *__restrict__ part, int groups, int CH) {
+                  int Nout, int Kin, int64_t rows_per_cta, float *__restrict__ part, int CH) {
+    constexpr int NW = NLOAD / 32, groups = NW / W;
+    static_assert(W % 4 == 0 && R % W == 0 && NW % W == 0, "a warp's rows must share (row & 3), the swizzle phase");
     extern __shared__ uint8_t smem_raw[];
     const uint32_t raw = ptx::smem_u32(smem_raw);
     uint8_t *sm = smem_raw + (((raw + 1023u) & ~1023u) - raw);
@@ -112,7 +132,7 @@ wgrad_umma_kernel(const __grid_constant__ CUtensorMap tm_p, const __grid_constan
     if (tid == 0) {
         for (int i = 0; i < NST; ++i) {
             ptx::mbar_init(bar_tma + 8 * i, 1);
-            ptx::mbar_init(bar_full + 8 * i, (NLOAD / 32) / groups);
+            ptx::mbar_init(bar_full + 8 * i, W);
             ptx::mbar_init(bar_free + 8 * i, 1);
         }
         ptx::mbar_init(bar_chunk, 1);
@@ -198,30 +218,35 @@ wgrad_umma_kernel(const __grid_constant__ CUtensorMap tm_p, const __grid_constan
     } else {
         // ---------------------------------------------------------------- converters / flushers
         const int lq = warp & 3, half = warp >> 2;
+        constexpr int NH = NW / 4;   // warps per TMEM lane quarter
         const uint32_t t_lane = tmem + ((uint32_t)(lq * 32) << 16);
         {   // master accumulator (columns 256..511) starts at zero
             uint32_t z[16];
 #pragma unroll
             for (int i = 0; i < 16; ++i) z[i] = 0u;
-            for (int cb = half; cb < 16; cb += 2) ptx::tmem_st_32x32b_x16(t_lane + 256 + cb * 16, z);
+            for (int cb = half; cb < 16; cb += NH) ptx::tmem_st_32x32b_x16(t_lane + 256 + cb * 16, z);
             ptx::tmem_st_wait();
         }
-        // A converter warp owns whole slabs (slab % 8 == warp, so 8 slabs are converted concurrently and one
-        // warp's proxy fence never stalls the others); a lane owns 16-byte column chunks lane, lane + 32 of every row.
+        // Converter warps work in `groups` groups of W warps.  A group owns whole slabs (slab % groups), a warp of the
+        // group the rows wi, wi + W, .. of the slab, a lane the 16-byte column chunks lane (P and Q) and lane + 32 (Q).
+        // W is a multiple of 4, so all rows of a warp share the swizzle phase (row & 3): a lane's byte offsets inside
+        // a stage are fixed for the whole launch and the per-slab code is loads, 2 ALU ops per value and stores.  All
+        // loads of a slab are issued before the first store (the compiler cannot reorder them itself: raw and lo
+        // images live in the same shared array), which is what hides the shared-memory latency with 4 warps per
+        // scheduler.
         const int p4 = G.colsP >> 2, q4 = G.colsQ >> 2;
+        const int gi = warp / W, wi = warp % W;
+        constexpr int RW = R / W;
+        const bool hasP = lane < p4, hasQ0 = lane < q4, hasQ1 = lane + 32 < q4;
+        const int offP = img_off(wi, lane << 2), offQ1 = img_off(wi, (lane + 32) << 2);   // offQ0 == offP
         float4 bsum[2];   // column sums of dY (the P operand, or Q when the roles are swapped)
         bsum[0] = bsum[1] = make_float4(0.f, 0.f, 0.f, 0.f);
-        auto lo_of = [](float v) { return v - __uint_as_float(__float_as_uint(v) & 0xffffe000u); };
-        auto add4 = [](float4 &a, const float4 &v) { a.x += v.x; a.y += v.y; a.z += v.z; a.w += v.w; };
-        auto conv = [&](uint8_t *img, int lo_delta, int off, float4 &acc, bool sum) {
-            const float4 v = *reinterpret_cast<const float4 *>(img + off);
-            *reinterpret_cast<float4 *>(img + lo_delta + off) = make_float4(lo_of(v.x), lo_of(v.y), lo_of(v.z), lo_of(v.w));
-            if (sum) add4(acc, v);
+        auto lo4 = [](const float4 &v) {
+            auto lo_of = [](float x) { return x - __uint_as_float(__float_as_uint(x) & 0xffffe000u); };
+            return make_float4(lo_of(v.x), lo_of(v.y), lo_of(v.z), lo_of(v.w));
         };
+        auto add4 = [](float4 &a, const float4 &v) { a.x += v.x; a.y += v.y; a.z += v.z; a.w += v.w; };
         // a parity wait is only meaningful one phase ahead: a warp's next slab must not be more than a ring away
-        // converter warps work in `groups` groups of W warps; a group owns whole slabs (slab % groups), a warp of the
-        // group every W-th row, a lane the 16-byte column chunks lane, lane + 32
-        const int W = (NLOAD / 32) / groups, gi = warp / W, wi = warp % W;
         const int ncw = NST < groups ? NST : groups;
         const int n_chunks = (n_slabs + CH - 1) / CH;
         int cv_slab = 0, cv_stage = 0;
@@ -236,11 +261,27 @@ wgrad_umma_kernel(const __grid_constant__ CUtensorMap tm_p, const __grid_constan
                 const int stage = cv_stage;
                 ptx::mbar_wait(bar_tma + 8 * stage, cv_ph);
                 uint8_t *sp = sm + stage * STAGE, *sq = sp + 2 * P_IMG;
-#pragma unroll 4
-                for (int r = wi; r < R; r += W) {
-                    if (lane < p4) conv(sp, P_IMG, img_off(r, lane << 2), bsum[0], !G.swap);
-                    if (lane < q4) conv(sq, Q_IMG, img_off(r, lane << 2), bsum[0], G.swap);
-                    if (lane + 32 < q4) conv(sq, Q_IMG, img_off(r, (lane + 32) << 2), bsum[1], G.swap);
+                float4 vp[RW], vq0[RW], vq1[RW];
+#pragma unroll
+                for (int k = 0; k < RW; ++k) {
+                    if (hasP) vp[k] = *reinterpret_cast<const float4 *>(sp + offP + k * (W * 128));
+                    if (hasQ0) vq0[k] = *reinterpret_cast<const float4 *>(sq + offP + k * (W * 128));
+                    if (hasQ1) vq1[k] = *reinterpret_cast<const float4 *>(sq + offQ1 + k * (W * 128));
+                }
+#pragma unroll
+                for (int k = 0; k < RW; ++k) {
+                    if (hasP) {
+                        *reinterpret_cast<float4 *>(sp + P_IMG + offP + k * (W * 128)) = lo4(vp[k]);
+                        if (!G.swap) add4(bsum[0], vp[k]);
+                    }
+                    if (hasQ0) {
+                        *reinterpret_cast<float4 *>(sq + Q_IMG + offP + k * (W * 128)) = lo4(vq0[k]);
+                        if (G.swap) add4(bsum[0], vq0[k]);
+                    }
+                    if (hasQ1) {
+                        *reinterpret_cast<float4 *>(sq + Q_IMG + offQ1 + k * (W * 128)) = lo4(vq1[k]);
+                        if (G.swap) add4(bsum[1], vq1[k]);
+                    }
                 }
                 ptx::fence_proxy_async();
                 __syncwarp();
@@ -249,7 +290,7 @@ wgrad_umma_kernel(const __grid_constant__ CUtensorMap tm_p, const __grid_constan
             // chunk accumulator (columns 0..) += into the master (columns 256..), fp32 round-to-nearest
             ptx::mbar_wait(bar_chunk, chunk & 1);
             ptx::tc_fence_after();
-            for (int cb = half; cb < NI / 16; cb += 2) {
+            for (int cb = half; cb < NI / 16; cb += NH) {
                 uint32_t a[16], m[16];
                 ptx::tmem_ld_32x32b_x16(t_lane + cb * 16, a);
                 ptx::tmem_ld_32x32b_x16(t_lane + 256 + cb * 16, m);
@@ -273,7 +314,7 @@ wgrad_umma_kernel(const __grid_constant__ CUtensorMap tm_p, const __grid_constan
             if (lane == 0) ptx::mbar_arrive(bar_flush);
         }
         // every MMA has completed (the last flush waited for it) and every TMA load has landed: the ring is free
-        // -> bias-gradient scratch [8 warps][Nout], summed in warp order
+        // -> bias-gradient scratch [NW warps][Nout], summed in warp order
         named_sync_loaders();
         float *sdb = reinterpret_cast<float *>(sm);
         {
@@ -291,7 +332,7 @@ wgrad_umma_kernel(const __grid_constant__ CUtensorMap tm_p, const __grid_constan
         // master accumulator -> this CTA's partial (D[m][n]: m = P column, n = Q column)
         ptx::tc_fence_after();
         const int m = lq * 32 + lane;
-        for (int cb = half; cb < NI / 16; cb += 2) {
+        for (int cb = half; cb < NI / 16; cb += NH) {
             uint32_t v[16];
             ptx::tmem_ld_32x32b_x16(t_lane + 256 + cb * 16, v);
             ptx::tmem_ld_wait();
@@ -361,11 +402,17 @@ inline int wgrad_umma_launch(const float *dY, const float *X, int64_t rows, int 
     CUtensorMap tm_dy, tm_x;
     LIPVQ_TRY(make_slab_tmap(&tm_dy, dY, (uint64_t)rows, (uint64_t)Nout, R));
     LIPVQ_TRY(make_slab_tmap(&tm_x, X, (uint64_t)rows, (uint64_t)Kin, R));
-    LIPVQ_CUDA_OK(cudaFuncSetAttribute(wgrad_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    static const int wpg = [] { const char *e = getenv("LIPVQ_WGRAD_WPG"); return e ? atoi(e) : 16; }();   // A/B probe
     ProfScope prof("wgrad_umma_kernel", st);
-    // 2 converter groups of 4 warps, 16 slabs (256 rows) per accumulation chunk: measured best / 1e-6 accurate
-    wgrad_umma_kernel<<<grid, NTHR, smem, st>>>(G.swap ? tm_x : tm_dy, G.swap ? tm_dy : tm_x, rows, Nout, Kin, per, part, 2,
-                                                CH_DEFAULT);
+    // all 16 converter warps on one slab (one row each), 16 slabs (256 rows) per accumulation chunk (1e-6 accurate)
+    auto go = [&](auto kern) -> int {
+        LIPVQ_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        kern<<<grid, NTHR, smem, st>>>(G.swap ? tm_x : tm_dy, G.swap ? tm_dy : tm_x, rows, Nout, Kin, per, part, CH_DEFAULT);
+        return LIPVQ_OK;
+    };
+    if (wpg == 8) LIPVQ_TRY(go(wgrad_umma_kernel<8>));
+    else if (wpg == 4) LIPVQ_TRY(go(wgrad_umma_kernel<4>));
+    else LIPVQ_TRY(go(wgrad_umma_kernel<16>));
     LIPVQ_LAUNCH_OK();
     *splits = grid;
     return LIPVQ_OK;
@@ -387,12 +434,13 @@ namespace dg {
 constexpr int TM = 128;
 constexpr int NLD = 256, NEP = 256, NT = NLD + NEP + 32;
 constexpr int SLOTS = 4;
+constexpr int LOOK = 3;             // A blocks a loader thread keeps in flight (registers)
 __host__ __device__ constexpr int nn_pad(int Nn) { return (Nn + 7) / 8 * 8; }
 __host__ __device__ constexpr int w_img_bytes(int Nn, int Kout) { return (Kout / 32) * nn_pad(Nn) * 128; }
 __host__ __device__ constexpr int smem_bytes(int Nn, int Kout) { return 2 * w_img_bytes(Nn, Kout) + 256 + 1024; }
 }  // namespace dg
 
-template <int DACT>
+template <int DACT, bool WIDE>
 __global__ void __launch_bounds__(dg::NT, 1)
 dgrad_umma_kernel(const float *__restrict__ dY, const float *__restrict__ W, const float *__restrict__ dpre,
                   float *__restrict__ dX, int64_t M, int Nn, int Kout, const float *__restrict__ scale_dev) {
@@ -489,17 +537,35 @@ dgrad_umma_kernel(const float *__restrict__ dY, const float *__restrict__ W, con
         const int r = tid & 127, h = tid >> 7;
         const uint32_t t_lane = tmem + ((uint32_t)((warp & 3) * 32) << 16);
         const int total = my_tiles * KB;
-        auto load = [&](int b, float4(&v)[4]) {
+        // WIDE (Nn % 8 == 0, 32-byte aligned rows): two 256-bit loads per row and block instead of four 128-bit ones
+        auto load = [&](int b, float(&v)[16]) {
             const int t = b / KB, kb = b - t * KB;
             const int64_t row = ((int64_t)blockIdx.x + (int64_t)t * gridDim.x) * TM + r;
             const int c0 = kb * 32 + h * 16;
             const bool live = b < total && row < M;
+            const float *src = dY + row * Nn + c0;
+            if (WIDE) {
 #pragma unroll
-            for (int i = 0; i < 4; ++i)
-                v[i] = (live && c0 + 4 * i < Nn) ? __ldg(reinterpret_cast<const float4 *>(dY + row * Nn + c0 + 4 * i))
-                                                 : make_float4(0.f, 0.f, 0.f, 0.f);
+                for (int i = 0; i < 2; ++i) {
+                    if (live && c0 + 8 * i < Nn) {
+                        const F8 q = ldg256(src + 8 * i);
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) v[8 * i + j] = q.v[j];
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) v[8 * i + j] = 0.f;
+                    }
+                }
+            } else {
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const float4 q = (live && c0 + 4 * i < Nn) ? __ldg(reinterpret_cast<const float4 *>(src) + i)
+                                                               : make_float4(0.f, 0.f, 0.f, 0.f);
+                    v[4 * i] = q.x; v[4 * i + 1] = q.y; v[4 * i + 2] = q.z; v[4 * i + 3] = q.w;
+                }
+            }
         };
-        auto step = [&](int b, float4(&v)[4]) {
+        auto step = [&](int b, float(&v)[16]) {
             const int slot = b % SLOTS;
             if (b >= SLOTS) {
                 ptx::mbar_wait(bar_afree + 8 * slot, ((b / SLOTS) - 1) & 1);
@@ -507,24 +573,23 @@ dgrad_umma_kernel(const float *__restrict__ dY, const float *__restrict__ W, con
             }
             uint32_t hi[16], lo[16];
 #pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                split_rna(v[i].x, hi[4 * i], lo[4 * i]); split_rna(v[i].y, hi[4 * i + 1], lo[4 * i + 1]);
-                split_rna(v[i].z, hi[4 * i + 2], lo[4 * i + 2]); split_rna(v[i].w, hi[4 * i + 3], lo[4 * i + 3]);
-            }
+            for (int i = 0; i < 16; ++i) split_rna(v[i], hi[i], lo[i]);
             ptx::tmem_st_32x32b_x16(t_lane + 256 + slot * 64 + h * 16, hi);
             ptx::tmem_st_32x32b_x16(t_lane + 256 + slot * 64 + 32 + h * 16, lo);
-            load(b + 2, v);
+            load(b + LOOK, v);
             ptx::tmem_st_wait();
             ptx::tc_fence_before();
             __syncwarp();
             if (lane == 0) ptx::mbar_arrive(bar_afull + 8 * slot);
         };
-        float4 v0[4], v1[4];
+        float v0[16], v1[16], v2[16];
         load(0, v0);
         load(1, v1);
-        for (int b = 0; b < total; b += 2) {
+        load(2, v2);
+        for (int b = 0; b < total; b += 3) {
             step(b, v0);
             if (b + 1 < total) step(b + 1, v1);
+            if (b + 2 < total) step(b + 2, v2);
         }
     } else {
         // ---------------------------------------------------------------- epilogue: acc -> act' -> dX
@@ -534,30 +599,57 @@ dgrad_umma_kernel(const float *__restrict__ dY, const float *__restrict__ W, con
         for (int t = 0; t < my_tiles; ++t) {
             const int buf = t & 1;
             const int64_t row = ((int64_t)blockIdx.x + (int64_t)t * gridDim.x) * TM + r;
+            // the saved pre-activations of this thread's row are requested BEFORE the accumulator is waited for
+            // (and the next column block's before the current one is used): their latency hides behind the MMAs
+            const bool live = row < M;
+            const float *pre = dpre + row * Kout;
+            float *dst = dX + row * Kout;
+            float pv[16] = {};
+            auto load_pre = [&](int cb) {
+                if (DACT == ACT_NONE || !live || cb >= Kout / 16) return;
+                if (WIDE) {
+#pragma unroll
+                    for (int i = 0; i < 2; ++i) {
+                        const F8 q = ldg256(pre + cb * 16 + 8 * i);
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) pv[8 * i + j] = q.v[j];
+                    }
+                } else {
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        const float4 q = __ldg(reinterpret_cast<const float4 *>(pre + cb * 16) + i);
+                        pv[4 * i] = q.x; pv[4 * i + 1] = q.y; pv[4 * i + 2] = q.z; pv[4 * i + 3] = q.w;
+                    }
+                }
+            };
+            load_pre(h);
             ptx::mbar_wait(bar_cfull + 8 * buf, (t >> 1) & 1);
             ptx::tc_fence_after();
             for (int cb = h; cb < Kout / 16; cb += 2) {
                 uint32_t a[16];
                 ptx::tmem_ld_32x32b_x16(t_lane + buf * 128 + cb * 16, a);
                 ptx::tmem_ld_wait();
-                if (row < M) {
-                    float *dst = dX + row * Kout + cb * 16;
-                    const float *pre = dpre + row * Kout + cb * 16;
+                float o[16];
 #pragma unroll
-                    for (int i = 0; i < 4; ++i) {
-                        float4 o = make_float4(out_scale * __uint_as_float(a[4 * i]), out_scale * __uint_as_float(a[4 * i + 1]),
-                                               out_scale * __uint_as_float(a[4 * i + 2]), out_scale * __uint_as_float(a[4 * i + 3]));
-                        if (DACT == ACT_GELU) {
-                            const float4 p = __ldg(reinterpret_cast<const float4 *>(pre) + i);
-                            o.x *= gelu_grad_fast_f(p.x); o.y *= gelu_grad_fast_f(p.y);
-                            o.z *= gelu_grad_fast_f(p.z); o.w *= gelu_grad_fast_f(p.w);
+                for (int i = 0; i < 16; ++i) {
+                    o[i] = out_scale * __uint_as_float(a[i]);
+                    if (DACT == ACT_GELU) o[i] *= gelu_grad_fast_f(pv[i]);
+                    if (DACT == ACT_RELU) o[i] = pv[i] > 0.f ? o[i] : 0.f;
+                }
+                load_pre(cb + 2);
+                if (live) {
+                    if (WIDE) {
+#pragma unroll
+                        for (int i = 0; i < 2; ++i) {
+                            F8 q;
+#pragma unroll
+                            for (int j = 0; j < 8; ++j) q.v[j] = o[8 * i + j];
+                            stg256(dst + cb * 16 + 8 * i, q);
                         }
-                        if (DACT == ACT_RELU) {
-                            const float4 p = __ldg(reinterpret_cast<const float4 *>(pre) + i);
-                            o.x = p.x > 0.f ? o.x : 0.f; o.y = p.y > 0.f ? o.y : 0.f;
-                            o.z = p.z > 0.f ? o.z : 0.f; o.w = p.w > 0.f ? o.w : 0.f;
-                        }
-                        reinterpret_cast<float4 *>(dst)[i] = o;
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < 4; ++i)
+                            reinterpret_cast<float4 *>(dst + cb * 16)[i] = make_float4(o[4 * i], o[4 * i + 1], o[4 * i + 2], o[4 * i + 3]);
                     }
                 }
             }
@@ -579,11 +671,20 @@ template <int DACT>
 inline int dgrad_umma_launch(const float *dY, const float *W, const float *dpre, float *dX, int64_t M, int Nn, int Kout,
                              const float *scale_dev, cudaStream_t st) {
     const int smem = dg::smem_bytes(Nn, Kout);
-    LIPVQ_CUDA_OK(cudaFuncSetAttribute(dgrad_umma_kernel<DACT>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     const int64_t tiles = (M + dg::TM - 1) / dg::TM;
     const int grid = (int)(tiles < kNumSMs ? tiles : kNumSMs);
+    static const bool narrow = [] { const char *e = getenv("LIPVQ_DGRAD"); return e && !strcmp(e, "narrow"); }();   // A/B
+    auto al32 = [](const void *p) { return (reinterpret_cast<uintptr_t>(p) & 31) == 0; };
+    const bool wide = (Nn & 7) == 0 && al32(dY) && al32(dX) && (DACT == ACT_NONE || al32(dpre)) &&
+                      !narrow;
     ProfScope prof("dgrad_umma_kernel", st);
-    dgrad_umma_kernel<DACT><<<grid, dg::NT, smem, st>>>(dY, W, dpre, dX, M, Nn, Kout, scale_dev);
+    if (wide) {
+        LIPVQ_CUDA_OK(cudaFuncSetAttribute(dgrad_umma_kernel<DACT, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        dgrad_umma_kernel<DACT, true><<<grid, dg::NT, smem, st>>>(dY, W, dpre, dX, M, Nn, Kout, scale_dev);
+    } else {
+        LIPVQ_CUDA_OK(cudaFuncSetAttribute(dgrad_umma_kernel<DACT, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        dgrad_umma_kernel<DACT, false><<<grid, dg::NT, smem, st>>>(dY, W, dpre, dX, M, Nn, Kout, scale_dev);
+    }
     LIPVQ_LAUNCH_OK();
     return LIPVQ_OK;
 }

@@ -610,12 +610,142 @@ __global__ void __launch_bounds__(GNT) wgrad_tc3_kernel(const float *__restrict_
     if (blockIdx.y == 0 && tid < GBM && m0 + tid < Nout) C[(size_t)(m0 + tid) * ld + Kin] = bsum;
 }
 
+// ---------------------------------------------------------------- weight gradient of a NARROW-input layer (Kin <= 16)
+// The first encoder layer has Kin = feature_dim = 12 (v5:54): its weight gradient is 2 * Nout * Kin = 1.5 kflop per row
+// against 304 bytes -- a streaming reduction, not a GEMM.  On the tensor-core kernel the per-slab machinery costs more
+// than the data (measured 137 us for 200 MB); here a thread owns 4 rows of dW (4 x Kin accumulators), a "row lane" of
+// Nout / 4 threads walks every RL-th row of the block's row range with plain fp32 FMAs (exact, no split products:
+// 48 FMAs for 4 vector loads), and the row lanes are summed in a fixed order: part[z][Nout][Kin+1], bias column
+// included.  KG = ceil(Kin / 4) float4 groups of X per row.
+// dY and X rows of a block are contiguous in memory: they stream through a WN_NS-deep ring of WN_SR-row stages filled
+// by 16-byte asynchronous copies (zero-filled past the block's last row), so the bytes in flight do not depend on
+// registers.
+constexpr int WN_NT = 256, WN_SR = 64, WN_NS = 4;
+template <int KG>
+__global__ void __launch_bounds__(WN_NT, 2) wgrad_narrow_kernel(const float *__restrict__ dY, const float *__restrict__ X,
+                                                                 int64_t rows, int Nout, int Kin, int64_t k_chunk,
+                                                                 float *__restrict__ part) {
+    extern __shared__ __align__(16) float wn_sm[];
+    const int tid = threadIdx.x;
+    const int per_lane = Nout >> 2, RL = WN_NT / per_lane;
+    const int lane_row = tid / per_lane, j0 = (tid - lane_row * per_lane) << 2;
+    const bool active = lane_row < RL;
+    const int64_t r_beg = (int64_t)blockIdx.x * k_chunk, r_end = r_beg + k_chunk < rows ? r_beg + k_chunk : rows;
+    const int n_rows = r_beg < r_end ? (int)(r_end - r_beg) : 0, n_st = (n_rows + WN_SR - 1) / WN_SR;
+    const int stage_floats = WN_SR * (Nout + Kin);
+    float acc[4][4 * KG], bs[4];
+#pragma unroll
+    for (int a = 0; a < 4; ++a) {
+        bs[a] = 0.f;
+#pragma unroll
+        for (int b = 0; b < 4 * KG; ++b) acc[a][b] = 0.f;
+    }
+    auto issue = [&](int st_i) {
+        if (st_i < n_st) {
+            float *sy = wn_sm + (size_t)(st_i % WN_NS) * stage_floats, *sx = sy + WN_SR * Nout;
+            const int live = n_rows - st_i * WN_SR < WN_SR ? n_rows - st_i * WN_SR : WN_SR;   // rows of this stage
+            const float *gy = dY + (r_beg + (int64_t)st_i * WN_SR) * Nout, *gx = X + (r_beg + (int64_t)st_i * WN_SR) * Kin;
+            const int ny = WN_SR * Nout / 4, ly = live * Nout / 4, nx = WN_SR * Kin / 4, lx = live * Kin / 4;
+            for (int i = tid; i < ny; i += WN_NT) cp_async16(sy + 4 * i, i < ly ? gy + 4 * i : dY, i < ly);
+            for (int i = tid; i < nx; i += WN_NT) cp_async16(sx + 4 * i, i < lx ? gx + 4 * i : X, i < lx);
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+    for (int s0 = 0; s0 < WN_NS - 1; ++s0) issue(s0);
+    for (int st_i = 0; st_i < n_st; ++st_i) {
+        issue(st_i + WN_NS - 1);   // refills the buffer consumed in the previous iteration (barrier below)
+        asm volatile("cp.async.wait_group %0;" ::"n"(WN_NS - 1) : "memory");
+        __syncthreads();
+        if (active) {
+            const float *sy = wn_sm + (size_t)(st_i % WN_NS) * stage_floats, *sx = sy + WN_SR * Nout;
+#pragma unroll 2
+            for (int rr = lane_row; rr < WN_SR; rr += RL) {
+                const float4 g = *reinterpret_cast<const float4 *>(sy + rr * Nout + j0);
+                const float gv[4] = {g.x, g.y, g.z, g.w};
+                float4 x[KG];
+#pragma unroll
+                for (int q = 0; q < KG; ++q) x[q] = *reinterpret_cast<const float4 *>(sx + rr * Kin + 4 * q);
+#pragma unroll
+                for (int a = 0; a < 4; ++a) {
+                    bs[a] += gv[a];
+#pragma unroll
+                    for (int q = 0; q < KG; ++q) {
+                        acc[a][4 * q] = fmaf(gv[a], x[q].x, acc[a][4 * q]);
+                        acc[a][4 * q + 1] = fmaf(gv[a], x[q].y, acc[a][4 * q + 1]);
+                        acc[a][4 * q + 2] = fmaf(gv[a], x[q].z, acc[a][4 * q + 2]);
+                        acc[a][4 * q + 3] = fmaf(gv[a], x[q].w, acc[a][4 * q + 3]);
+                    }
+                }
+            }
+        }
+        __syncthreads();
+    }
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    __syncthreads();
+    // row lanes -> one partial, summed in lane order (round-robin over the shared scratch in groups of WN_G lanes)
+    const int ld = Kin + 1, tile = Nout * ld;
+    float *C = part + (size_t)blockIdx.x * tile;
+    constexpr int WN_G = 4;   // row lanes staged per round: WN_G * tile floats of shared memory
+    for (int l0 = 0; l0 < RL; l0 += WN_G) {
+        if (active && lane_row >= l0 && lane_row < l0 + WN_G) {
+            float *dst = wn_sm + (size_t)(lane_row - l0) * tile;
+#pragma unroll
+            for (int a = 0; a < 4; ++a) {
+#pragma unroll
+                for (int b = 0; b < 4 * KG; ++b)
+                    if (b < Kin) dst[(j0 + a) * ld + b] = acc[a][b];
+                dst[(j0 + a) * ld + Kin] = bs[a];
+            }
+        }
+        __syncthreads();
+        const int nl = RL - l0 < WN_G ? RL - l0 : WN_G;
+        for (int i = tid; i < tile; i += WN_NT) {
+            float v = l0 ? C[i] : 0.f;
+            for (int l = 0; l < nl; ++l) v += wn_sm[(size_t)l * tile + i];
+            C[i] = v;
+        }
+        __syncthreads();
+    }
+}
+inline int wgrad_narrow_smem(int Nout, int Kin) {
+    const int ring = WN_NS * WN_SR * (Nout + Kin) * (int)sizeof(float), red = 4 * Nout * (Kin + 1) * (int)sizeof(float);
+    return ring > red ? ring : red;
+}
+inline bool wgrad_narrow_ok(int64_t rows, int Nout, int Kin) {
+    return Kin >= 4 && Kin <= 16 && (Kin & 3) == 0 && (Nout & 3) == 0 && Nout >= 4 && Nout <= 4 * WN_NT && rows >= 2048 &&
+           wgrad_narrow_smem(Nout, Kin) <= 100 * 1024;
+}
+
 // dW[Nout,Kin] = dY[rows,Nout]^T X[rows,Kin];  db[Nout] = column sums of dY.  part = scratch.
 inline int linear_bwd_weight(const float *dY, const float *X, float *dW, float *db, int64_t rows,
                              int Nout, int Kin, float *part, cudaStream_t st, const float *out_scale_dev = nullptr) {
     const int splits = splits_for_rows(rows, Nout, Kin);
     static const bool simt = [] { const char *e = getenv("LIPVQ_GEMM"); return e && !strcmp(e, "simt"); }();
     static const bool legacy = [] { const char *e = getenv("LIPVQ_GEMM"); return e && !strcmp(e, "mma_sync"); }();
+    static const bool no_narrow = [] { const char *e = getenv("LIPVQ_WGRAD_NARROW"); return e && !strcmp(e, "0"); }();
+    if (!simt && !legacy && !no_narrow && wgrad_narrow_ok(rows, Nout, Kin) && aligned16(dY) && aligned16(X)) {
+        const int64_t k_chunk = (rows + splits - 1) / splits;
+        const int smem = wgrad_narrow_smem(Nout, Kin);
+        {
+            ProfScope prof("wgrad_narrow_kernel", st);
+            auto go = [&](auto kern) -> int {
+                LIPVQ_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+                kern<<<splits, WN_NT, smem, st>>>(dY, X, rows, Nout, Kin, k_chunk, part);
+                return LIPVQ_OK;
+            };
+            switch (Kin >> 2) {
+            case 1: LIPVQ_TRY(go(wgrad_narrow_kernel<1>)); break;
+            case 2: LIPVQ_TRY(go(wgrad_narrow_kernel<2>)); break;
+            case 3: LIPVQ_TRY(go(wgrad_narrow_kernel<3>)); break;
+            default: LIPVQ_TRY(go(wgrad_narrow_kernel<4>)); break;
+            }
+            LIPVQ_LAUNCH_OK();
+        }
+        const int total = Nout * (Kin + 1);
+        splitk_reduce_kernel<<<(total + 255) / 256, 256, 0, st>>>(part, splits, Nout, Kin, dW, db, out_scale_dev);
+        LIPVQ_LAUNCH_OK();
+        return LIPVQ_OK;
+    }
     if (!simt && !legacy && bwd5::wgrad_umma_ok(rows, Nout, Kin) && aligned16(dY) && aligned16(X)) {
         int parts = 0;
         LIPVQ_TRY(bwd5::wgrad_umma_launch(dY, X, rows, Nout, Kin, part, &parts, st));
