@@ -46,6 +46,7 @@ __device__ __forceinline__ F8 ldg256(const float *p) {
                  : "l"(p));
     return r;
 }
+__device__ __forceinline__ void prefetch_l2(const void *p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 __device__ __forceinline__ void stg256(float *p, const F8 &r) {
     asm volatile("st.global.v8.f32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "f"(r.v[0]), "f"(r.v[1]), "f"(r.v[2]),
                  "f"(r.v[3]), "f"(r.v[4]), "f"(r.v[5]), "f"(r.v[6]), "f"(r.v[7]) : "memory");
@@ -443,7 +444,7 @@ __host__ __device__ constexpr int smem_bytes(int Nn, int Kout) { return 2 * w_im
 template <int DACT, bool WIDE>
 __global__ void __launch_bounds__(dg::NT, 1)
 dgrad_umma_kernel(const float *__restrict__ dY, const float *__restrict__ W, const float *__restrict__ dpre,
-                  float *__restrict__ dX, int64_t M, int Nn, int Kout, const float *__restrict__ scale_dev) {
+                  float *__restrict__ dX, int64_t M, int Nn, int Kout, const float *__restrict__ scale_dev, int PF) {
     using namespace dg;
     extern __shared__ uint8_t smem_raw[];
     const uint32_t raw = ptx::smem_u32(smem_raw);
@@ -577,6 +578,12 @@ dgrad_umma_kernel(const float *__restrict__ dY, const float *__restrict__ W, con
             ptx::tmem_st_32x32b_x16(t_lane + 256 + slot * 64 + h * 16, hi);
             ptx::tmem_st_32x32b_x16(t_lane + 256 + slot * 64 + 32 + h * 16, lo);
             load(b + LOOK, v);
+            if (h == 0) {   // the 128-byte line of this row PF blocks further ahead -> L2
+                const int bp = b + PF;
+                const int tp = bp / KB, kp = bp - tp * KB;
+                const int64_t prow = ((int64_t)blockIdx.x + (int64_t)tp * gridDim.x) * TM + r;
+                if (bp < total && prow < M && kp * 32 < Nn) prefetch_l2(dY + prow * Nn + kp * 32);
+            }
             ptx::tmem_st_wait();
             ptx::tc_fence_before();
             __syncwarp();
@@ -623,6 +630,11 @@ dgrad_umma_kernel(const float *__restrict__ dY, const float *__restrict__ W, con
                 }
             };
             load_pre(h);
+            if (DACT != ACT_NONE && t + 1 < my_tiles) {   // next tile's half row -> L2 (no registers held)
+                const int64_t nrow = row + (int64_t)gridDim.x * TM;
+                if (nrow < M)
+                    for (int c = h * (Kout >> 1); c < (h + 1) * (Kout >> 1); c += 32) prefetch_l2(dpre + nrow * Kout + c);
+            }
             ptx::mbar_wait(bar_cfull + 8 * buf, (t >> 1) & 1);
             ptx::tc_fence_after();
             for (int cb = h; cb < Kout / 16; cb += 2) {
@@ -673,6 +685,7 @@ inline int dgrad_umma_launch(const float *dY, const float *W, const float *dpre,
     const int smem = dg::smem_bytes(Nn, Kout);
     const int64_t tiles = (M + dg::TM - 1) / dg::TM;
     const int grid = (int)(tiles < kNumSMs ? tiles : kNumSMs);
+    static const int pf = [] { const char *e = getenv("LIPVQ_DGRAD_PF"); return e ? atoi(e) : 10; }();   // L2 prefetch distance (blocks)
     static const bool narrow = [] { const char *e = getenv("LIPVQ_DGRAD"); return e && !strcmp(e, "narrow"); }();   // A/B
     auto al32 = [](const void *p) { return (reinterpret_cast<uintptr_t>(p) & 31) == 0; };
     const bool wide = (Nn & 7) == 0 && al32(dY) && al32(dX) && (DACT == ACT_NONE || al32(dpre)) &&
@@ -680,10 +693,10 @@ inline int dgrad_umma_launch(const float *dY, const float *W, const float *dpre,
     ProfScope prof("dgrad_umma_kernel", st);
     if (wide) {
         LIPVQ_CUDA_OK(cudaFuncSetAttribute(dgrad_umma_kernel<DACT, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-        dgrad_umma_kernel<DACT, true><<<grid, dg::NT, smem, st>>>(dY, W, dpre, dX, M, Nn, Kout, scale_dev);
+        dgrad_umma_kernel<DACT, true><<<grid, dg::NT, smem, st>>>(dY, W, dpre, dX, M, Nn, Kout, scale_dev, pf);
     } else {
         LIPVQ_CUDA_OK(cudaFuncSetAttribute(dgrad_umma_kernel<DACT, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-        dgrad_umma_kernel<DACT, false><<<grid, dg::NT, smem, st>>>(dY, W, dpre, dX, M, Nn, Kout, scale_dev);
+        dgrad_umma_kernel<DACT, false><<<grid, dg::NT, smem, st>>>(dY, W, dpre, dX, M, Nn, Kout, scale_dev, pf);
     }
     LIPVQ_LAUNCH_OK();
     return LIPVQ_OK;

@@ -172,6 +172,100 @@ __device__ __forceinline__ void lipschitz_rows_layer(const float *__restrict__ W
     }
 }
 
+// ---- thread-per-neuron layers over PADDED shared-memory weight rows (the default when every dimension is a multiple
+// of 4).  The warp-per-neuron form above spends 5 shuffle + 5 add instructions per (neuron, row) reduction -- ncu
+// (round 2) put 45 % of the kernel's instructions in the 208 x 128 Lipschitz layer alone.  Here a thread owns one
+// neuron and a 1 / KS slice of the reduction axis: 128-bit reads of its weight row (row pitch = an ODD number of
+// 16-byte chunks: conflict-free across the lanes of a warp), 128-bit broadcast reads of the SR activation rows, 4 * SR
+// FMAs per weight chunk and NO shuffles; the KS slices meet in shared memory and are summed in slice order.
+__host__ __device__ inline int wpitch(int k_in) {
+    int p4 = (k_in + 3) >> 2;
+    if (!(p4 & 1)) ++p4;
+    return p4 << 2;
+}
+// [n_rows][k_in] row-major (k_in % 4 == 0) -> padded rows; 16-byte asynchronous copies when the source allows
+__device__ __forceinline__ void stage_rows(float *dst, const float *__restrict__ src, int n_rows, int k_in, int pitch) {
+    const int c4 = k_in >> 2;
+    if ((reinterpret_cast<uintptr_t>(src) & 15) == 0) {
+        for (int i = threadIdx.x; i < n_rows * c4; i += ST) {
+            const int j = i / c4, c = i - j * c4;
+            cp_async16(dst + j * pitch + 4 * c, src + (size_t)j * k_in + 4 * c);
+        }
+    } else {
+        for (int i = threadIdx.x; i < n_rows * k_in; i += ST) {
+            const int j = i / k_in, c = i - j * k_in;
+            dst[j * pitch + c] = __ldg(src + i);
+        }
+    }
+}
+constexpr int TPN_SCRATCH = SR * ST + 2 * ST;   // floats: slice partials [KS][SR][n_pad] | |W| partials [KS][n_pad] | scale
+// LIP: z = act(h (W * scale)^T + b), scale_j = min(1, softplus(ci_j) / sum_k |W_jk|), the product W_jk * scale_j rounded
+// before the FMA as in the reference (v5:6-12, 22-24).  Contains block barriers: call from all ST threads.
+template <int ACT, bool LIP>
+__device__ __forceinline__ void rows_layer_tpn(const float *sW, int P, const float *bias, const float *ci, int n_out,
+                                               int k_in, const float *s_in, int in_pitch, float *s_out, int out_pitch,
+                                               float *s_scr, float *__restrict__ g_out, int rows_valid) {
+    const int tid = threadIdx.x;
+    const int n_pad = (n_out + 31) & ~31;
+    int KS = ST / n_pad;
+    KS = KS < 1 ? 1 : (KS > 4 ? 4 : KS);
+    const int k4 = k_in >> 2, kc4 = (k4 + KS - 1) / KS;
+    float *s_part = s_scr, *s_abs = s_scr + SR * ST, *s_scale = s_abs + ST;
+    const int s = tid / n_pad, j = tid - s * n_pad;
+    const bool slot = s < KS, on = slot && j < n_out;
+    const int q_lo = s * kc4, q_hi = (q_lo + kc4 < k4) ? q_lo + kc4 : k4;
+    const float4 *wrow = reinterpret_cast<const float4 *>(sW + (size_t)(on ? j : 0) * P);
+    float sc = 1.f;
+    if (LIP) {
+        float a = 0.f;
+        if (on)
+            for (int q = q_lo; q < q_hi; ++q) {
+                const float4 w = wrow[q];
+                a += (fabsf(w.x) + fabsf(w.y)) + (fabsf(w.z) + fabsf(w.w));
+            }
+        if (slot) s_abs[s * n_pad + j] = a;
+        __syncthreads();
+        if (tid < n_out) {
+            float t = 0.f;
+            for (int s2 = 0; s2 < KS; ++s2) t += s_abs[s2 * n_pad + tid];
+            s_scale[tid] = fminf(1.0f, softplus_f(ldw(ci + tid)) / t);
+        }
+        __syncthreads();
+        if (on) sc = s_scale[j];
+    }
+    float acc[SR];
+#pragma unroll
+    for (int r = 0; r < SR; ++r) acc[r] = 0.f;
+    if (on) {
+#pragma unroll 2
+        for (int q = q_lo; q < q_hi; ++q) {
+            float4 w = wrow[q];
+            if (LIP) { w.x *= sc; w.y *= sc; w.z *= sc; w.w *= sc; }
+#pragma unroll
+            for (int r = 0; r < SR; ++r) {
+                const float4 a = *reinterpret_cast<const float4 *>(s_in + r * in_pitch + 4 * q);   // broadcast
+                acc[r] = fmaf(w.x, a.x, acc[r]);
+                acc[r] = fmaf(w.y, a.y, acc[r]);
+                acc[r] = fmaf(w.z, a.z, acc[r]);
+                acc[r] = fmaf(w.w, a.w, acc[r]);
+            }
+        }
+    }
+    if (slot) {
+#pragma unroll
+        for (int r = 0; r < SR; ++r) s_part[(s * SR + r) * n_pad + j] = acc[r];
+    }
+    __syncthreads();
+    for (int i = tid; i < SR * n_out; i += ST) {
+        const int r = i / n_out, j2 = i - r * n_out;
+        float v = 0.f;
+        for (int s2 = 0; s2 < KS; ++s2) v += s_part[(s2 * SR + r) * n_pad + j2];
+        v = apply_act<ACT>(v + ldw(bias + j2));
+        s_out[r * out_pitch + j2] = v;
+        if (g_out && r < rows_valid) g_out[(size_t)r * n_out + j2] = v;
+    }
+}
+
 struct Scratch {
     unsigned long long *best;   // [n_rows] ~((d2 bits << 32) | code), zero-initialised (= no candidate yet)
     int *group_done;            // [G] arrival counters
@@ -200,17 +294,19 @@ inline Scratch carve(void *ws, int64_t n, size_t *zero_bytes) {
 // STAGED: the encoder (then, in the finishing CTA, the decoder) weights are copied into shared memory with one wave of
 // 16-byte asynchronous copies, and the codebook tiles are double buffered, so the kernel pays a handful of L2 round
 // trips instead of ~40 dependent ones; needs enc/dec weights <= ~150 KB (latent_dim <= ~256), else the direct variant.
-template <bool STAGED>
+template <int MODE>   // 0: weights read in place; 1: staged, warp-per-neuron layers; 2: staged + padded, thread-per-neuron layers
 __global__ void __launch_bounds__(ST, 1) small_forward_kernel(
     lipvq_params_t p, const float *__restrict__ x, int n_rows, int F, int H1, int H, int D, int K, int splits,
     Scratch sc, float *__restrict__ z_latent, int64_t *__restrict__ idx_out, float *__restrict__ x_recon,
     float *__restrict__ loss_out, double inv_nf, double inv_nd) {
-    extern __shared__ float sm[];
+    constexpr bool STAGED = MODE != 0, TPN = MODE == 2;
+    extern __shared__ __align__(16) float sm[];
     // [SR][F] x | [SR][H1] | [SR][H] | [SR][ZP] z_e (zero-padded to whole chunks) | [8 warps][32][SPITCH] codebook
     // tiles (re-used as z_q + decoder activations by the finishing CTA)
     const int ZP = (D + SDC - 1) / SDC * SDC;
     float *s_x = sm, *s_h1 = s_x + SR * F, *s_h2 = s_h1 + SR * H1, *s_z = s_h2 + SR * H;
-    float *s_tile = s_z + SR * ZP;      // big region: STAGED: encoder weights, then 2 x tiles, then decoder weights
+    float *s_scr = s_z + SR * ZP;       // TPN: slice partials of the thread-per-neuron layers
+    float *s_tile = s_scr + (TPN ? TPN_SCRATCH : 0);   // big region: STAGED: encoder weights, then 2 x tiles, then decoder weights
     __shared__ float red[ST / 32];
     __shared__ int s_ticket;
     __shared__ int s_idx[SR];
@@ -228,17 +324,32 @@ __global__ void __launch_bounds__(ST, 1) small_forward_kernel(
     if (STAGED) {
         float *q = s_tile;               // (every piece starts 16-byte aligned: sizes are rounded up to 4 floats)
         auto put = [&](const float *src, int n) { float *d = q; stage_floats(d, src, n); q += (n + 3) & ~3; return (const float *)d; };
-        w0 = put(p.enc0_w, H1 * F); b0 = put(p.enc0_b, H1); w1 = put(p.enc2_w, H * H1); b1 = put(p.enc2_b, H);
-        wl = put(p.lat_W, D * H); bl = put(p.lat_b, D); cl = put(p.lat_ci, D);
+        auto put_rows = [&](const float *src, int n_out, int k_in) {
+            if (!TPN) return put(src, n_out * k_in);
+            float *d = q;
+            stage_rows(d, src, n_out, k_in, wpitch(k_in));
+            q += n_out * wpitch(k_in);
+            return (const float *)d;
+        };
+        w0 = put_rows(p.enc0_w, H1, F); b0 = put(p.enc0_b, H1); w1 = put_rows(p.enc2_w, H, H1); b1 = put(p.enc2_b, H);
+        wl = put_rows(p.lat_W, D, H); bl = put(p.lat_b, D); cl = put(p.lat_ci, D);
         cp_async_commit();
         cp_async_wait<0>();
     }
     __syncthreads();
-    rows_layer<ACT_GELU>(w0, b0, H1, F, s_x, s_h1, nullptr, 0);
-    __syncthreads();
-    rows_layer<ACT_GELU>(w1, b1, H, H1, s_h1, s_h2, nullptr, 0);
-    __syncthreads();
-    lipschitz_rows_layer(wl, bl, cl, D, H, s_h2, s_z, ZP);
+    if (TPN) {
+        rows_layer_tpn<ACT_GELU, false>(w0, wpitch(F), b0, nullptr, H1, F, s_x, F, s_h1, H1, s_scr, nullptr, 0);
+        __syncthreads();
+        rows_layer_tpn<ACT_GELU, false>(w1, wpitch(H1), b1, nullptr, H, H1, s_h1, H1, s_h2, H, s_scr, nullptr, 0);
+        __syncthreads();
+        rows_layer_tpn<ACT_SIGMOID, true>(wl, wpitch(H), bl, cl, D, H, s_h2, H, s_z, ZP, s_scr, nullptr, 0);
+    } else {
+        rows_layer<ACT_GELU>(w0, b0, H1, F, s_x, s_h1, nullptr, 0);
+        __syncthreads();
+        rows_layer<ACT_GELU>(w1, b1, H, H1, s_h1, s_h2, nullptr, 0);
+        __syncthreads();
+        lipschitz_rows_layer(wl, bl, cl, D, H, s_h2, s_z, ZP);
+    }
     __syncthreads();          // (STAGED: the weight region is free from here on: the codebook tiles take it over)
 
     // ---- this CTA's slice of the codebook: codes [k_lo, k_hi), 32-code tiles dealt to the warps round-robin
@@ -367,8 +478,15 @@ __global__ void __launch_bounds__(ST, 1) small_forward_kernel(
     if (STAGED) {
         float *q = s_o + ((SR * F + 3) & ~3);
         auto put = [&](const float *src, int n) { float *d = q; stage_floats(d, src, n); q += (n + 3) & ~3; return (const float *)d; };
-        v0 = put(p.dec0_w, H1 * D); c0 = put(p.dec0_b, H1); v1 = put(p.dec2_w, H * H1); c1 = put(p.dec2_b, H);
-        vo = put(p.out_w, F * H); co = put(p.out_b, F);
+        auto put_rows = [&](const float *src, int n_out, int k_in) {
+            if (!TPN) return put(src, n_out * k_in);
+            float *d = q;
+            stage_rows(d, src, n_out, k_in, wpitch(k_in));
+            q += n_out * wpitch(k_in);
+            return (const float *)d;
+        };
+        v0 = put_rows(p.dec0_w, H1, D); c0 = put(p.dec0_b, H1); v1 = put_rows(p.dec2_w, H, H1); c1 = put(p.dec2_b, H);
+        vo = put_rows(p.out_w, F, H); co = put(p.out_b, F);
         cp_async_commit();               // (lands while the gather below runs)
     }
     float sq = 0.f;
@@ -384,11 +502,20 @@ __global__ void __launch_bounds__(ST, 1) small_forward_kernel(
     }
     if (STAGED) cp_async_wait<0>();
     __syncthreads();
-    rows_layer<ACT_GELU>(v0, c0, H1, D, s_q, s_c1, nullptr, 0);
-    __syncthreads();
-    rows_layer<ACT_GELU>(v1, c1, H, H1, s_c1, s_c2, nullptr, 0);
-    __syncthreads();
-    rows_layer<ACT_NONE>(vo, co, F, H, s_c2, s_o, x_recon ? x_recon + (size_t)r0 * F : nullptr, rows_valid);
+    if (TPN) {
+        rows_layer_tpn<ACT_GELU, false>(v0, wpitch(D), c0, nullptr, H1, D, s_q, D, s_c1, H1, s_scr, nullptr, 0);
+        __syncthreads();
+        rows_layer_tpn<ACT_GELU, false>(v1, wpitch(H1), c1, nullptr, H, H1, s_c1, H1, s_c2, H, s_scr, nullptr, 0);
+        __syncthreads();
+        rows_layer_tpn<ACT_NONE, false>(vo, wpitch(H), co, nullptr, F, H, s_c2, H, s_o, F, s_scr,
+                                        x_recon ? x_recon + (size_t)r0 * F : nullptr, rows_valid);
+    } else {
+        rows_layer<ACT_GELU>(v0, c0, H1, D, s_q, s_c1, nullptr, 0);
+        __syncthreads();
+        rows_layer<ACT_GELU>(v1, c1, H, H1, s_c1, s_c2, nullptr, 0);
+        __syncthreads();
+        rows_layer<ACT_NONE>(vo, co, F, H, s_c2, s_o, x_recon ? x_recon + (size_t)r0 * F : nullptr, rows_valid);
+    }
     __syncthreads();
     float sr = 0.f;
     for (int i = tid; i < rows_valid * F; i += ST) {
@@ -423,19 +550,26 @@ __global__ void __launch_bounds__(ST, 1) small_forward_kernel(
 }
 
 inline size_t r4(size_t n) { return (n + 3) & ~(size_t)3; }
-inline size_t smem_bytes(const lipvq_dims_t *d, bool staged = false) {
-    const size_t head = (size_t)SR * (d->F + d->H1 + d->H + (d->D + SDC - 1) / SDC * SDC);
-    size_t tiles = (size_t)TW * 32 * SPITCH * (staged ? 2 : 1);
+inline size_t smem_bytes(const lipvq_dims_t *d, int mode = 0) {
+    size_t head = (size_t)SR * (d->F + d->H1 + d->H + (d->D + SDC - 1) / SDC * SDC);
+    if (mode == 2) head += TPN_SCRATCH;
+    size_t tiles = (size_t)TW * 32 * SPITCH * (mode ? 2 : 1);
     size_t tail = (size_t)SR * (d->D + d->H1 + d->H) + r4((size_t)SR * d->F);
-    if (staged) {
-        const size_t enc = r4((size_t)d->H1 * d->F) + r4(d->H1) + r4((size_t)d->H * d->H1) + r4(d->H) + r4((size_t)d->D * d->H) + 2 * r4(d->D);
-        const size_t dec = r4((size_t)d->H1 * d->D) + r4(d->H1) + r4((size_t)d->H * d->H1) + r4(d->H) + r4((size_t)d->F * d->H) + r4(d->F);
+    auto wsz = [&](int n_out, int k_in) { return mode == 2 ? (size_t)n_out * wpitch(k_in) : r4((size_t)n_out * k_in); };
+    if (mode) {
+        const size_t enc = wsz(d->H1, d->F) + r4(d->H1) + wsz(d->H, d->H1) + r4(d->H) + wsz(d->D, d->H) + 2 * r4(d->D);
+        const size_t dec = wsz(d->H1, d->D) + r4(d->H1) + wsz(d->H, d->H1) + r4(d->H) + wsz(d->F, d->H) + r4(d->F);
         tail += dec;
         if (enc > tiles) tiles = enc;
     }
     return (head + (tiles > tail ? tiles : tail)) * sizeof(float) + 64;
 }
-inline bool staged_ok(const lipvq_dims_t *d) { return smem_bytes(d, true) <= 200 * 1024; }
+inline bool staged_ok(const lipvq_dims_t *d) { return smem_bytes(d, 1) <= 200 * 1024; }
+// thread-per-neuron layers: 16-byte rows everywhere, every layer's neurons fit one pass of the CTA
+inline bool tpn_ok(const lipvq_dims_t *d) {
+    const int mx = d->D > d->H ? (d->D > d->H1 ? d->D : d->H1) : (d->H > d->H1 ? d->H : d->H1);
+    return ((d->F | d->H1 | d->H | d->D) & 3) == 0 && mx <= ST && d->F <= ST && smem_bytes(d, 2) <= 200 * 1024;
+}
 inline bool supported(const lipvq_dims_t *d, int64_t n) {
     return n >= 1 && n <= MAX_ROWS && smem_bytes(d) <= 200 * 1024;
 }
@@ -457,9 +591,10 @@ inline int launch(const lipvq_dims_t *d, const lipvq_params_t *p, const float *x
     const int per = ((d->K + splits - 1) / splits + 31) / 32 * 32;     // codes per split
     splits = (d->K + per - 1) / per;                                   // (no empty slices)
     static const bool no_stage = [] { const char *e = getenv("LIPVQ_SMALL_STAGED"); return e && !strcmp(e, "0"); }();
-    const bool staged = !no_stage && staged_ok(d);
-    const size_t smem = smem_bytes(d, staged);
-    auto kern = staged ? small_forward_kernel<true> : small_forward_kernel<false>;
+    static const bool no_tpn = [] { const char *e = getenv("LIPVQ_SMALL_LAYERS"); return e && !strcmp(e, "warp"); }();   // A/B
+    const int mode = no_stage ? 0 : (!no_tpn && tpn_ok(d)) ? 2 : staged_ok(d) ? 1 : 0;
+    const size_t smem = smem_bytes(d, mode);
+    auto kern = mode == 2 ? small_forward_kernel<2> : mode == 1 ? small_forward_kernel<1> : small_forward_kernel<0>;
     LIPVQ_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const double nt = (double)(n_total > 0 ? n_total : 1);
     ProfScope prof("small_forward_kernel", st);

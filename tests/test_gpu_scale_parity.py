@@ -385,3 +385,44 @@ def test_backward_is_bit_identical_run_to_run():
         grads.append({k: t.grad.clone() for k, t in m.named_parameters()})
     for k in grads[0]:
         assert torch.equal(grads[0][k], grads[1][k]), k
+
+
+@pytest.mark.parametrize("n", [80, 500, 5000])
+def test_nograd_fast_path_equals_general_path(n):
+    """The no-grad host fast path (no autograd.Function, cached parameter struct / workspace size) returns exactly what
+    the general path returns, follows in-place parameter updates, and notices re-allocated parameter storage."""
+    p = spread_params()
+    m = _model(p)
+    x = torch.from_numpy(np.random.default_rng(3).standard_normal((n, 12)).astype(np.float32)).cuda()
+
+    def general(xx):
+        z, loss = m(xx)                      # grad enabled: the autograd.Function path
+        return z.clone(), loss.detach().clone(), m.last_indices.clone(), m.last_reconstruction.clone()
+
+    def fast(xx):
+        with torch.no_grad():
+            z, loss = m(xx)
+        from lipvq_vae_b200 import tokenizer
+        assert tokenizer._FAST.get(m) is not None, "fast path not taken"
+        import copy
+        copy.deepcopy(m)                      # the caches live outside the instance: modules stay copyable
+        return z.clone(), loss.clone(), m.last_indices.clone(), m.last_reconstruction.clone()
+
+    for rnd in range(3):
+        zg, lg, ig, rg = general(x)
+        zf, lf, i_f, rf = fast(x)
+        assert torch.equal(ig, i_f) and torch.equal(zg, zf)
+        assert torch.allclose(rg, rf, rtol=1e-6, atol=1e-7)
+        assert abs(lg.item() - lf.item()) <= 1e-6 * abs(lg.item())
+        with torch.no_grad():
+            if rnd == 0:
+                m.quantizer.codebook.mul_(1.5)            # in place: same storage, new values
+            else:
+                w = m.encoder[0].weight
+                w.data = (w.data * 0.9).clone()           # new storage: the cached struct must be rebuilt
+    # and against the oracle once, after both kinds of update
+    sd = {k: v.detach().cpu().numpy() for k, v in m.state_dict().items()}
+    fw = orc.forward(sd, x.cpu().numpy())
+    zf, lf, i_f, rf = fast(x)
+    assert abs(lf.item() - fw["loss"]) <= RTOL * abs(fw["loss"])
+    assert (i_f.cpu().numpy() == fw["idx"]).mean() > 0.999
