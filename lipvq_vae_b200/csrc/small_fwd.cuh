@@ -310,6 +310,7 @@ __global__ void __launch_bounds__(ST, 1) small_forward_kernel(
     __shared__ float red[ST / 32];
     __shared__ int s_ticket;
     __shared__ int s_idx[SR];
+    __shared__ unsigned long long s_key[TW][SR];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int g = blockIdx.y, split = blockIdx.x;
     const int r0 = g * SR;
@@ -449,11 +450,20 @@ __global__ void __launch_bounds__(ST, 1) small_forward_kernel(
                 const int ok = __shfl_xor_sync(0xffffffffu, k, o);
                 if (od < d || (od == d && ok < k)) { d = od; k = ok; }
             }
-            if (lane == 0 && r < rows_valid && k != 0x7fffffff) {
+            // the tile warps meet in shared memory first: ONE global atomic per (CTA, row) -- the same-address atomics of
+            // a row group serialise in L2, and their acknowledgement is what the fence below waits for
+            if (lane == 0 && warp < TW) {
                 const unsigned long long key = ((unsigned long long)__float_as_uint(d) << 32) | (unsigned)k;
-                atomicMax(sc.best + r0 + r, ~key);
+                s_key[warp][r] = (k != 0x7fffffff) ? ~key : 0ull;
             }
         }
+    }
+    __syncthreads();
+    if (tid < rows_valid) {
+        unsigned long long m = 0ull;
+#pragma unroll
+        for (int w = 0; w < TW; ++w) m = s_key[w][tid] > m ? s_key[w][tid] : m;
+        if (m) atomicMax(sc.best + r0 + tid, m);
     }
     // ---- the last CTA of the row group finishes the rows
     __threadfence();
