@@ -330,7 +330,7 @@ def run_ours(args, rank, world, local_rank):
     del trainer, m_tr
     if world > 1:
         # A/B of the collective: the split schedule (first half of the bucket all-reduced UNDER the encoder backward)
-        # against the default above (ONE all-reduce after the whole backward) -- measured negative, see dist.py
+        # against the default above (ONE all-reduce after the whole backward) -- measured no better, see dist.py
         m_tr = copy.deepcopy(m).train()
         trainer = TokenizerTrainer(m_tr, overlap=True)
         for i in range(3):
@@ -361,8 +361,8 @@ def run_ours(args, rank, world, local_rank):
     train["collective"] = ("ONE NCCL all-reduce per step over the flat gradient bucket (14 tensors + the loss scalar), after "
                            "the backward; gradients are written by the kernels straight into the bucket (no pack/unpack "
                            "copies).  The split schedule that puts 80 % of the bucket under the encoder backward is the "
-                           "A/B leg ms_per_step_split_allreduce_under_backward: it loses, because an NCCL kernel on one "
-                           "SM pushes the persistent one-CTA-per-SM backward kernels into a second wave")
+                           "A/B leg ms_per_step_split_allreduce_under_backward: no gain (the collective is ~40 us alone "
+                           "and competes for SMs with the persistent one-CTA-per-SM backward kernels)")
     # EMA variant of the same step (north_star item 3; extension, not in the reference): the codebook follows the EMA
     # of its clusters -- per-code counts/sums by the scatter-add kernel, all-reduced in one more collective
     m_tr = copy.deepcopy(m).train()

@@ -181,10 +181,11 @@ class TokenizerTrainer:
       1. decoder backward -> struct fields 7..13 (codebook, decoder.*, to_output.*: 80 % of the bucket, one contiguous
          slice) + the loss scalar are all-reduced on the communication stream while
       2. the encoder backward (the N-row GEMMs, ~45 % of the step) runs; its slice (fields 0..6) follows.
-    Measured NEGATIVE and therefore not the default (8 x B200, 65 536 chunks per GPU: 3.61 ms per step against 2.20 ms
-    for the single all-reduce; 2 GPUs: 2.55 against 2.38): the encoder-side backward kernels are persistent, one CTA per
-    SM with a static row partition, so an NCCL kernel that holds even one SM while they run pushes their last CTA into
-    a second wave and doubles their time -- far more than the ~40 us the collective costs when it runs alone."""
+    Measured no better and therefore not the default (65 536 chunks per GPU, 5 warm-up steps: 2.21 ms per step against
+    2.17 ms for the single all-reduce on 8 x B200, 2.17 against 2.16 on 2): the collective costs ~40 us when it runs alone,
+    and the encoder-side backward kernels it would hide under are persistent, one CTA per SM with a static row partition,
+    so an NCCL kernel that holds an SM while they run delays their last CTA.  (A first measurement with 2 warm-up steps
+    showed 3.6 ms for the split schedule: NCCL's first calls on the communication stream were inside the timed steps.)"""
 
     def __init__(self, model, process_group=None, lr=1e-3, weight_decay=1e-4, ema_codebook=False, ema_gamma=0.99,
                  overlap=False, concurrent_backward=True):
