@@ -451,7 +451,10 @@ def test_classic_vqvae_vs_reference_golden(case, mode):
 
 @pytest.mark.parametrize("M,Nout,Kin,masked", [(2049, 208, 128, False), (100003, 208, 128, False), (4136, 128, 64, True),
                                                (655360, 128, 64, False), (30000, 64, 12, False), (2560, 256, 128, True),
-                                               (5000, 12, 128, False), (2048, 36, 64, True)])
+                                               (5000, 12, 128, False), (2048, 36, 64, True),
+                                               # narrow inputs: the streaming fp32 weight-gradient kernel, every KG template
+                                               (30000, 64, 4, False), (100003, 80, 8, True), (655360, 64, 12, False),
+                                               (2051, 12, 16, False), (4099, 36, 12, True), (3000, 256, 16, False)])
 def test_linear_backward_tensor_kernels_vs_float64(M, Nout, Kin, masked):
     """The tcgen05 backward kernels (csrc/bwd_umma.cuh: TMA-fed MN-major weight gradient with chunked accumulation,
     TMEM-operand input gradient) through lipvq_linear_bwd, against float64 matmuls of the same operands: autograd of
