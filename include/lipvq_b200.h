@@ -33,7 +33,8 @@ enum {
     LIPVQ_EALIGN = -2,     /* a pointer is null or not 16-byte aligned                      */
     LIPVQ_EARCH = -3,      /* the current device is not sm_100                              */
     LIPVQ_EWORKSPACE = -4, /* ws_bytes is smaller than lipvq_workspace_bytes(...)           */
-    LIPVQ_ECUDA = -5       /* a CUDA runtime/driver call failed (see lipvq_last_cuda_error) */
+    LIPVQ_ECUDA = -5,      /* a CUDA runtime/driver call failed (see lipvq_last_cuda_error) */
+    LIPVQ_ELIMIT = -6      /* a size exceeds the fixed limit of an allocation-free entry point */
 };
 
 /* search modes for lipvq_vq_argmin */
@@ -231,6 +232,23 @@ int lipvq_forward_fused(const lipvq_dims_t *dims, const lipvq_params_t *p, const
 int lipvq_forward_small(const lipvq_dims_t *dims, const lipvq_params_t *p, const float *x,
                         int64_t n_rows, int64_t n_total, float *z_latent, int64_t *idx, float *x_recon,
                         float *loss_out, int32_t *stats, void *ws, size_t ws_bytes, void *stream);
+
+/* Allocation-free variant of lipvq_forward_small.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot allocate device memory (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc).  Same kernel, same results; there is no ws argument: the kernel's scratch
+ * (8 B per row + 12 B per 4 rows) lives in a 64 KB file-scope `static __device__` array inside the library, which every
+ * GPU that loads the library holds until exit.  The call performs no cudaMalloc / cudaFree and no allocating library
+ * call; inputs and outputs are the caller's.
+ *   limit : n_rows <= LIPVQ_FORWARD_SMALL_STATIC_MAX_ROWS, otherwise LIPVQ_ELIMIT (nothing is launched);
+ *   sharing: all calls on one device use the SAME array -- the part that must start at zero is cleared on `stream`
+ *            before the kernel, so back-to-back calls on one stream are safe, but calls that overlap on the GPU
+ *            (different streams, or concurrent host threads) race and give wrong tokens;
+ *   set-up : the first call on each device resolves the array's device address (cudaGetSymbolAddress); make that
+ *            first call outside stream capture. */
+#define LIPVQ_FORWARD_SMALL_STATIC_MAX_ROWS 4096
+int lipvq_forward_small_static(const lipvq_dims_t *dims, const lipvq_params_t *p, const float *x,
+                               int64_t n_rows, int64_t n_total, float *z_latent, int64_t *idx, float *x_recon,
+                               float *loss_out, int32_t *stats, void *stream);
 
 /* AdamW step over one flat fp32 tensor (torch.optim.AdamW semantics as configured at
  * robomimic/algo/icl.py:886-889): decoupled weight decay, bias-corrected moments.

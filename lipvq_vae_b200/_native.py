@@ -125,6 +125,7 @@ SIGNATURES = {
     "lipvq_segment_sum_ws_bytes": (_SZ, [_I64, _I32, _I32]),
     "lipvq_segment_sum": (C.c_int, [_VP, _VP, _VP, _F32, _VP, _I64, _I32, _I32, _I32, _VP, _VP, _VP, _SZ, _VP]),
     "lipvq_forward_small": (C.c_int, [_DP, _PP, _VP, _I64, _I64, _VP, _VP, _VP, _VP, _VP, _VP, _SZ, _VP]),
+    "lipvq_forward_small_static": (C.c_int, [_DP, _PP, _VP, _I64, _I64, _VP, _VP, _VP, _VP, _VP, _VP]),
     "lipvq_adamw_step": (C.c_int, [_VP, _VP, _VP, _VP, _I64, _I64, _F32, _F32, _F32, _F32, _F32, _VP]),
     "lipvq_ema_update": (C.c_int, [_VP, _VP, _VP, _VP, _VP, _I32, _I32, _F32, _F32, _VP, _SZ, _VP]),
     "lipvq_linear_bwd_ws_bytes": (_SZ, [_I64, _I32, _I32]),

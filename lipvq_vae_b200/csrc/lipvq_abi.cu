@@ -4,6 +4,7 @@
 #include <cstdlib>
 #include <cstring>
 
+#include <atomic>
 #include "common.cuh"
 #include "gemm_simt.cuh"
 #include "misc_kernels.cuh"
@@ -110,6 +111,7 @@ const char *lipvq_strerror(int code) {
         case LIPVQ_EARCH: return "device is not sm_100 (B200)";
         case LIPVQ_EWORKSPACE: return "workspace too small";
         case LIPVQ_ECUDA: return "CUDA error";
+        case LIPVQ_ELIMIT: return "size exceeds the fixed limit of an allocation-free entry point (static device scratch)";
         default: return "unknown error";
     }
 }
@@ -814,6 +816,46 @@ int lipvq_forward_small(const lipvq_dims_t *d, const lipvq_params_t *p, const fl
     if (!p || !aligned16(x) || (z_latent && !aligned16(z_latent)) || !idx) return LIPVQ_EALIGN;
     if (ws_bytes < small::scratch_bytes(n) || !aligned16(ws)) return LIPVQ_EWORKSPACE;
     return small::launch(d, p, x, n, n_total, z_latent, idx, x_recon, loss_out, stats, ws, (cudaStream_t)stream);
+}
+
+// ---- allocation-free variant of lipvq_forward_small (no counterpart in the reference).
+// The scratch lives in a file-scope __device__ array: every GPU that loads the library holds these
+// 64 KB until exit, every call on a device shares them (calls that overlap on the GPU race), and the array keeps the
+// last call's contents -- small::launch clears the part that must start at zero (best[] + the ticket counters) with
+// a memset node on the caller's stream before the kernel.  In host code the array's NAME is only a host-side stand-in:
+// the device address comes from cudaGetSymbolAddress, once per device, with that device current.
+constexpr int kStaticSmallMaxRows = LIPVQ_FORWARD_SMALL_STATIC_MAX_ROWS;
+constexpr size_t kStaticSmallBytes = 64 * 1024;
+static __device__ __align__(256) unsigned char g_small_static_scratch[kStaticSmallBytes];
+static_assert(LIPVQ_FORWARD_SMALL_STATIC_MAX_ROWS == 4096, "header and scratch size go together");
+
+static int small_static_scratch_ptr(void **out) {
+    constexpr int kMaxDev = 64;
+    static std::atomic<void *> ptrs[kMaxDev];
+    int dev = -1;
+    LIPVQ_CUDA_OK(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= kMaxDev) return LIPVQ_ESHAPE;
+    void *ptr = ptrs[dev].load(std::memory_order_acquire);
+    if (!ptr) {
+        LIPVQ_CUDA_OK(cudaGetSymbolAddress(&ptr, g_small_static_scratch));   // this device's copy of the array
+        if (!ptr) return LIPVQ_ECUDA;
+        ptrs[dev].store(ptr, std::memory_order_release);
+    }
+    *out = ptr;
+    return LIPVQ_OK;
+}
+
+int lipvq_forward_small_static(const lipvq_dims_t *d, const lipvq_params_t *p, const float *x, int64_t n, int64_t n_total,
+                               float *z_latent, int64_t *idx, float *x_recon, float *loss_out, int32_t *stats,
+                               void *stream) {
+    LIPVQ_NVTX("lipvq_forward_small_static");
+    if (!dims_ok(d) || n < 0 || n_total < n || small::smem_bytes(d) > 200 * 1024) return LIPVQ_ESHAPE;
+    if (n > kStaticSmallMaxRows || small::scratch_bytes(n) > kStaticSmallBytes) return LIPVQ_ELIMIT;
+    if (n == 0) return LIPVQ_OK;
+    if (!p || !aligned16(x) || (z_latent && !aligned16(z_latent)) || !idx) return LIPVQ_EALIGN;
+    void *scratch = nullptr;
+    LIPVQ_TRY(small_static_scratch_ptr(&scratch));
+    return small::launch(d, p, x, n, n_total, z_latent, idx, x_recon, loss_out, stats, scratch, (cudaStream_t)stream);
 }
 
 int lipvq_adamw_step(float *param, const float *grad, float *exp_avg, float *exp_avg_sq, int64_t n,
