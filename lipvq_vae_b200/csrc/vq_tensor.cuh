@@ -165,49 +165,62 @@ __global__ void __launch_bounds__(256) vq_convert_z_warp_kernel(const float *__r
     const bool active = rl < rpw, vec = (D & 3) == 0;
     const int d0 = ch * 8;
     bool bad = false;
-    for (int64_t r0 = (int64_t)blockIdx.x * rpb; r0 < Np; r0 += (int64_t)gridDim.x * rpb) {
-        const int64_t r = r0 + warp * rpw + rl;
-        float ss = 0.f;
-        if (active && r < Np) {
-            float v[8];
+    // two row sets per iteration, all loads of both issued before the first use (the pass is a pure stream: what
+    // limits it is the bytes a thread keeps in flight)
+    constexpr int U = 2;
+    const int64_t stride = (int64_t)gridDim.x * rpb;
+    for (int64_t r0 = (int64_t)blockIdx.x * rpb; r0 < Np; r0 += U * stride) {
+        float4 t[U][2];
+        int64_t rr[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            rr[u] = r0 + u * stride + warp * rpw + rl;
 #pragma unroll
             for (int q = 0; q < 2; ++q) {
                 const int d = d0 + 4 * q;
-                float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
-                if (r < n && d < D) {
-                    const float *p = z + r * D + d;
-                    if (vec) t = __ldg(reinterpret_cast<const float4 *>(p));
+                t[u][q] = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (active && rr[u] < n && d < D) {
+                    const float *p = z + rr[u] * D + d;
+                    if (vec) t[u][q] = __ldg(reinterpret_cast<const float4 *>(p));
                     else {
-                        t.x = __ldg(p);
-                        if (d + 1 < D) t.y = __ldg(p + 1);
-                        if (d + 2 < D) t.z = __ldg(p + 2);
-                        if (d + 3 < D) t.w = __ldg(p + 3);
+                        t[u][q].x = __ldg(p);
+                        if (d + 1 < D) t[u][q].y = __ldg(p + 1);
+                        if (d + 2 < D) t[u][q].z = __ldg(p + 2);
+                        if (d + 3 < D) t[u][q].w = __ldg(p + 3);
                     }
                 }
-                v[4 * q] = t.x; v[4 * q + 1] = t.y; v[4 * q + 2] = t.z; v[4 * q + 3] = t.w;
             }
+        }
 #pragma unroll
-            for (int i = 0; i < 8; ++i) {
-                const int d = d0 + i;
-                if (r < n && d < D) {
-                    v[i] -= s_mu[d];
-                    ss = fmaf(v[i], v[i], ss);
-                    bad |= !(fabsf(v[i]) <= OP_MAX);
-                } else {
-                    v[i] = (r < n && d < D + 3) ? 1.0f : 0.f;
+        for (int u = 0; u < U; ++u) {
+            const int64_t r = rr[u];
+            if (r0 + u * stride >= Np) break;                 // warp-uniform
+            float ss = 0.f;
+            if (active && r < Np) {
+                float v[8] = {t[u][0].x, t[u][0].y, t[u][0].z, t[u][0].w, t[u][1].x, t[u][1].y, t[u][1].z, t[u][1].w};
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    const int d = d0 + i;
+                    if (r < n && d < D) {
+                        v[i] -= s_mu[d];
+                        ss = fmaf(v[i], v[i], ss);
+                        bad |= !(fabsf(v[i]) <= OP_MAX);
+                    } else {
+                        v[i] = (r < n && d < D + 3) ? 1.0f : 0.f;
+                    }
                 }
-            }
-            __align__(16) op2_t o[4];
+                __align__(16) op2_t o[4];
 #pragma unroll
-            for (int i = 0; i < 4; ++i) o[i] = f2op2(v[2 * i], v[2 * i + 1]);
-            *reinterpret_cast<uint4 *>(Zb + r * DKz + d0) = *reinterpret_cast<const uint4 *>(o);
+                for (int i = 0; i < 4; ++i) o[i] = f2op2(v[2 * i], v[2 * i + 1]);
+                *reinterpret_cast<uint4 *>(Zb + r * DKz + d0) = *reinterpret_cast<const uint4 *>(o);
+            }
+            float tsum = ss;                                 // chunk 0 + chunk 1 + ... (fixed order)
+            for (int i = 1; i < cpr; ++i) {
+                const float o = __shfl_down_sync(0xffffffffu, ss, i);
+                if (ch + i < cpr) tsum += o;
+            }
+            if (active && ch == 0 && r < n) zn[r] = sqrtf(tsum);
         }
-        float t = ss;                                    // chunk 0 + chunk 1 + ... (fixed order)
-        for (int i = 1; i < cpr; ++i) {
-            const float o = __shfl_down_sync(0xffffffffu, ss, i);
-            if (ch + i < cpr) t += o;
-        }
-        if (active && ch == 0 && r < n) zn[r] = sqrtf(t);
     }
     if (__any_sync(0xffffffffu, bad) && lane == 0) atomicOr(counters + 3, 1);   // operand out of range -> exact search
 }
@@ -729,24 +742,45 @@ __global__ void __launch_bounds__(256) vq_rescore_kernel(
     const float emax = __ldg(emax_p);
     const int n_list = counters[4];
     int n_resc = 0;
-    for (int li = blockIdx.x * 8 + wib; li < n_list; li += gridDim.x * 8) {
-        const int64_t row = resc_list[li];
-        const int64_t tile = row >> 7;
-        const int r = (int)(row & 127);
-        // lanes 0..15 / 16..31 read the entries of parts (0,1) then (2,3)
-        uint2 ent[2];
-        bool has_e[2];
+    // The per-row chain is list entry -> entry counts -> entries -> z / E rows: four dependent round trips for a few
+    // hundred flops.  The first three of the NEXT listed row are issued before the current row's distances are
+    // computed (registers), so a warp pays ~two round trips per row instead of four.
+    const int li_step = gridDim.x * 8;
+    auto fetch_meta = [&](int li, int64_t &row, int (&cnt)[2]) {
+        row = li < n_list ? (int64_t)resc_list[li] : -1;
+        cnt[0] = cnt[1] = 0;
+        if (row >= 0) {
+            const int64_t tile = row >> 7;
+            const int r = (int)(row & 127);
+#pragma unroll
+            for (int h = 0; h < 2; ++h) cnt[h] = __ldg(cand_meta + (tile * NPART + 2 * h + (lane >> 4)) * BM + r);
+        }
+    };
+    auto fetch_ent = [&](int64_t row, const int (&cnt)[2], uint2 (&ent)[2]) {
+        ent[0] = ent[1] = make_uint2(0u, 0u);
+        if (row >= 0) {
+            const int64_t tile = row >> 7;
+            const int r = (int)(row & 127), e = lane & 15;
+#pragma unroll
+            for (int h = 0; h < 2; ++h)
+                if (e < cnt[h]) ent[h] = __ldg(cand + ((tile * NPART + 2 * h + (lane >> 4)) * LCAP + e) * BM + r);
+        }
+    };
+    int64_t row_n;
+    int cnt_n[2];
+    uint2 ent_n[2];
+    fetch_meta(blockIdx.x * 8 + wib, row_n, cnt_n);
+    fetch_ent(row_n, cnt_n, ent_n);
+    for (int li = blockIdx.x * 8 + wib; li < n_list; li += li_step) {
+        const int64_t row = row_n;
+        // lanes 0..15 / 16..31 hold the entries of parts (0,1) then (2,3)
+        uint2 ent[2] = {ent_n[0], ent_n[1]};
+        bool has_e[2] = {(lane & 15) < cnt_n[0], (lane & 15) < cnt_n[1]};
+        fetch_meta(li + li_step, row_n, cnt_n);          // next row: in flight during this row's work
         float gb = BIG;
 #pragma unroll
-        for (int h = 0; h < 2; ++h) {
-            const int p = 2 * h + (lane >> 4), e = lane & 15;
-            has_e[h] = e < __ldg(cand_meta + (tile * NPART + p) * BM + r);
-            ent[h] = make_uint2(0u, 0u);
-            if (has_e[h]) {
-                ent[h] = __ldg(cand + ((tile * NPART + p) * LCAP + e) * BM + r);
-                gb = fminf(gb, __uint_as_float(ent[h].x));
-            }
-        }
+        for (int h = 0; h < 2; ++h)
+            if (has_e[h]) gb = fminf(gb, __uint_as_float(ent[h].x));
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) gb = fminf(gb, __shfl_xor_sync(0xffffffffu, gb, o));
         const float T = gb + tau_of(__ldg(zn + row), emax, abs_c);
@@ -769,9 +803,11 @@ __global__ void __launch_bounds__(256) vq_rescore_kernel(
         if (s_cnt[wib] > 64) {                   // too many listed elements for the warp list: the exact scan takes the row
             if (lane == 0) exact_list[atomicAdd(counters + 0, 1)] = (int)row;
             __syncwarp();
+            fetch_ent(row_n, cnt_n, ent_n);
             continue;
         }
         const int nc = s_cnt[wib];
+        fetch_ent(row_n, cnt_n, ent_n);
         float best = INFINITY;
         int bidx = 0x7fffffff;
         const float *zr = z + row * D;
