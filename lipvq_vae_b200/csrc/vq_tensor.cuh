@@ -450,7 +450,23 @@ __global__ void __launch_bounds__(CONV ? NT_CONV : NT, 1) vq_tc_kernel(const __g
 #else
             constexpr uint32_t idesc = ptx::umma_idesc_f16(BM, BN);
 #endif
+            // The issuing thread is a serial resource: measured (tools/mma_rate_probe.cu) an MMA costs max(50, N/2) cycles
+            // when its operands are ready in uniform registers, but 160-235 when descriptor arithmetic, a counted loop
+            // and register->uniform moves sit between two of them -- with 14 MMAs per accumulator at D=208 that, not
+            // the tensor pipe (128 cycles per instruction), set the pace of this kernel.  So: descriptors are a constant
+            // high word and a running low word (16-byte units; the 14-bit start field cannot overflow below 256 KB of
+            // shared memory), the four K=16 slices of a K block are written out, and nothing else is computed here.
+            const uint32_t desc_hi = (uint32_t)(1024 >> 4) | (1u << 14) | (2u << 29);      // SBO | version 1 | SWIZZLE_128B
+            auto mk = [&](uint32_t lo) {
+                uint64_t d;
+                asm("mov.b64 %0, {%1, %2};" : "=l"(d) : "r"(lo), "r"(desc_hi));
+                return d;
+            };
+            const uint32_t a_lo0 = ((sA >> 4) & 0x3FFFu) | (1u << 16), b_lo0 = ((sB >> 4) & 0x3FFFu) | (1u << 16);
+            constexpr uint32_t A_KB16 = A_KB_BYTES >> 4, B_ST16 = B_ST_BYTES >> 4, A_BUF16 = (uint32_t)NKB * A_KB16;
+            const int nk_last = nk16 - (NKB - 1) * (KBLK / UK);       // K=16 slices of the last K block (1..4)
             int st = 0, sph = 0, ab = 0, aph = 0, acc = 0, accph = 0;
+            uint32_t b_lo = b_lo0, a_buf_lo = a_lo0;
             for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
                 ptx::mbar_wait(a_full(ab), aph);
                 ptx::tc_fence_after();
@@ -458,22 +474,31 @@ __global__ void __launch_bounds__(CONV ? NT_CONV : NT, 1) vq_tc_kernel(const __g
                     ptx::mbar_wait(t_empty(acc), accph ^ 1);
                     ptx::tc_fence_after();
                     const uint32_t d_tmem = tmem_base + acc * BN;
+                    uint32_t a_lo = a_buf_lo;
+#pragma unroll
                     for (int kb = 0; kb < NKB; ++kb) {
                         ptx::mbar_wait(b_full(st), sph);
                         ptx::tc_fence_after();
-                        const uint64_t ad = ptx::umma_desc_sw128(sA + (ab * NKB + kb) * A_KB_BYTES);
-                        const uint64_t bd = ptx::umma_desc_sw128(sB + st * B_ST_BYTES);
-                        const int nk = min(KBLK / UK, nk16 - kb * (KBLK / UK));
-                        for (int k = 0; k < nk; ++k)   // +32 B per K=16 slice inside the swizzle row
-                            ptx::umma_bf16(d_tmem, ad + 2 * k, bd + 2 * k, idesc, (kb | k) ? 1u : 0u);
+                        if (kb < NKB - 1 || nk_last == 4) {
+                            ptx::umma_bf16(d_tmem, mk(a_lo), mk(b_lo), idesc, kb ? 1u : 0u);
+                            ptx::umma_bf16(d_tmem, mk(a_lo + 2), mk(b_lo + 2), idesc, 1u);
+                            ptx::umma_bf16(d_tmem, mk(a_lo + 4), mk(b_lo + 4), idesc, 1u);
+                            ptx::umma_bf16(d_tmem, mk(a_lo + 6), mk(b_lo + 6), idesc, 1u);
+                        } else {
+                            for (int k = 0; k < nk_last; ++k)   // +32 B per K=16 slice inside the swizzle row
+                                ptx::umma_bf16(d_tmem, mk(a_lo + 2 * k), mk(b_lo + 2 * k), idesc, (kb | k) ? 1u : 0u);
+                        }
                         ptx::umma_commit(b_empty(st));
-                        if (++st == STAGES) { st = 0; sph ^= 1; }
+                        a_lo += A_KB16;
+                        b_lo += B_ST16;
+                        if (++st == STAGES) { st = 0; sph ^= 1; b_lo = b_lo0; }
                     }
                     ptx::umma_commit(t_full(acc));
                     if (++acc == 2) { acc = 0; accph ^= 1; }
                 }
                 ptx::umma_commit(a_empty(ab));
-                if (++ab == A_BUFS) { ab = 0; aph ^= 1; }
+                a_buf_lo += A_BUF16;
+                if (++ab == A_BUFS) { ab = 0; aph ^= 1; a_buf_lo = a_lo0; }
             }
         }
     } else if (CONV && (warp == 2 || warp == 3)) {
@@ -633,6 +658,36 @@ __global__ void __launch_bounds__(CONV ? NT_CONV : NT, 1) vq_tc_kernel(const __g
                         cand_compact(out, cnt, T);
                         if (cnt > LCAP - 4) { ovf = true; cnt = 0; }       // flat score landscape: the row takes the exact scan
                     }
+#ifndef LIPVQ_EPI_CHUNKWISE
+                    // Records are rare per ROW (a handful of new running minima per part) but not per WARP: with 32 rows in
+                    // a warp some lane has one in ~98 % of the chunks, so code under `if (put)` per chunk runs for every
+                    // chunk -- and the 8-element window mask (16 instructions) was 60 % of this epilogue.  Here the four
+                    // chunk tests of a batch are collected first and the record body runs ONCE per batch, every lane on
+                    // ITS chunk (values picked with selects); a second trip only for a lane with two chunks of one batch
+                    // inside the window.  The two smallest chunk minima are tracked in the same body: a chunk that is a
+                    // new minimum or lies inside the final window is always a record.
+                    uint32_t pm = (cm[0] <= T ? 1u : 0u) | (cm[1] <= T ? 2u : 0u) | (cm[2] <= T ? 4u : 0u) | (cm[3] <= T ? 8u : 0u);
+                    pm = row_ok ? pm : 0u;
+                    while (pm) {
+                        const int j = __ffs(pm) - 1;
+                        pm &= pm - 1;
+                        const bool j0 = j == 0, j1 = j == 1, j2 = j == 2;
+                        const float cmj = j0 ? cm[0] : j1 ? cm[1] : j2 ? cm[2] : cm[3];
+                        uint32_t m = 0;
+#pragma unroll
+                        for (int e = 7; e >= 0; --e) {
+                            const uint32_t bits = j0 ? r[e] : j1 ? r[8 + e] : j2 ? r[16 + e] : r[24 + e];
+                            m = __funnelshift_l(__float_as_uint(__uint_as_float(bits) - Tm), m, 1);
+                        }
+                        const uint32_t info = (uint32_t)(code0 + b * 32 + 8 * j) | (m << 24);
+                        out[cnt * BM] = make_uint2(__float_as_uint(cmj), info);
+                        ++cnt;
+                        const bool lt = cmj < m1;
+                        m2 = lt ? m1 : fminf(m2, cmj);
+                        info1 = lt ? info : info1;
+                        m1 = lt ? cmj : m1;
+                    }
+#else
 #pragma unroll
                     for (int j = 0; j < 4; ++j) {
                         const bool put = (cm[j] <= T) && row_ok;
@@ -668,6 +723,7 @@ __global__ void __launch_bounds__(CONV ? NT_CONV : NT, 1) vq_tc_kernel(const __g
                         info1 = lt ? info : info1;
                         m1 = lt ? cm[j] : m1;
                     }
+#endif
                 }
                 if (++acc == 2) { acc = 0; accph ^= 1; }
             }
@@ -991,7 +1047,11 @@ inline int vq_tensor_search(const float *z, const float *E, const tc::Geometry &
         case 1: rc = launch_tc<1, 2, 6>(ta, tb, g, w, idx, d2 != nullptr, st); break;
         case 2: rc = launch_tc<2, 2, 5>(ta, tb, g, w, idx, d2 != nullptr, st); break;
         case 3: rc = launch_tc<3, 2, 4>(ta, tb, g, w, idx, d2 != nullptr, st); break;
-        case 4: rc = launch_tc<4, 2, 3>(ta, tb, g, w, idx, d2 != nullptr, st); break;
+        case 4: {
+            static const bool a1 = [] { const char *e = getenv("LIPVQ_VQ_RING"); return e && !strcmp(e, "a1b5"); }();   // A/B probe
+            rc = a1 ? launch_tc<4, 1, 5>(ta, tb, g, w, idx, d2 != nullptr, st) : launch_tc<4, 2, 3>(ta, tb, g, w, idx, d2 != nullptr, st);
+            break;
+        }
         case 5: rc = launch_tc<5, 1, 4>(ta, tb, g, w, idx, d2 != nullptr, st); break;
         default: break;
     }
