@@ -300,12 +300,16 @@ __global__ void __launch_bounds__(256) vq_convert_z_kernel(const float *__restri
 // ------------------------------------------------------------------ pass 2: tcgen05 GEMM + fused chunk-min
 // Shared memory (dynamic, 1024-B aligned): A[A_BUFS][NKB] 16 KB K-blocks | B[STAGES] 32 KB | barriers.
 // All operand tiles are K-major with the 128-byte TMA/UMMA swizzle.
-template <int NKB, int A_BUFS, int STAGES>
+template <int NKB, int A_BUFS, int STAGES, bool PAIR = false>
 struct SmemLayout {
+    // PAIR (two CTAs, cta_group::2): a CTA holds HALF of every codebook stage, so the same ring bytes make 2 * STAGES
+    // stages; extra barriers a_peer[A_BUFS], b_peer[BST] are used by the leader only
+    static constexpr int BST = PAIR ? 2 * STAGES : STAGES;
+    static constexpr int B_STAGE = PAIR ? B_ST_BYTES / 2 : B_ST_BYTES;
     static constexpr int A_BYTES = A_BUFS * NKB * A_KB_BYTES;
     static constexpr int B_BYTES = STAGES * B_ST_BYTES;
     static constexpr int BAR_OFF = A_BYTES + B_BYTES;
-    static constexpr int NBARS = 2 * A_BUFS + 2 * STAGES + 4;
+    static constexpr int NBARS = 2 * A_BUFS + 2 * BST + 4 + (PAIR ? A_BUFS + BST : 0);
     static constexpr int RES_OFF = BAR_OFF + NBARS * 8 + 16;        // row exchange of the in-kernel resolve: 3 x 128 words
     static constexpr int TOTAL = RES_OFF + 3 * BM * 4 + 1024;       // + alignment slack
 };
@@ -365,7 +369,66 @@ __device__ __forceinline__ float fkey_inv(unsigned k) {
 // CONV: the row operand is not read from a pre-converted fp16 image (tmapA) but built in shared memory by four
 // converter warps straight from the fp32 rows z (thread = row; [fp16(z - mu) | 1 1 1 | 0..] in the TMA/UMMA 128-byte
 // swizzle, zn = ||z - mu|| to global): the standalone search API needs no separate conversion pass over z.
-template <int NKB, int A_BUFS, int STAGES, bool CONV = false>
+// PAIR (opt-in, LIPVQ_VQ_PAIR=1): two CTAs of a cluster work as one cta_group::2 unit on TWO row tiles at a time
+// (M = 256): each CTA holds its own 128 rows (A tile, TMEM accumulators, epilogue, decision) and HALF of every codebook
+// stage; the leader CTA issues the MMAs for both, and both CTAs' TMA loads are counted on the leader's barriers.
+// Built to test whether the codebook bytes an SM ingests bound the kernel at D = 208; they do not.  Measured with the
+// epilogue's arithmetic switched off (tools/vq_shape_probe.py, N = 2^20, K = 1024): the MMA side alone takes
+// ~570 + 185 cycles per MMA and accumulator in the one-CTA kernel (D = 253: 3 535 cycles for 16 MMAs) and the same in the
+// pair (3 452) -- 185 cycles per 128 x 256 x 16 MMA is what this B200 sustains on streamed operands (69 % of the nominal
+// 128; cuBLAS's measured burst peak is the same 69 % of nominal), whatever the ring depth, the issue loop or the B
+// bytes per SM.  Parity-tested (tests/test_gpu_scale_parity.py::test_pair_search_matches_oracle); not the default
+// because it is no faster (269 vs 263 us in the forward).
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\nbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// arrive on the barrier at the same shared-memory offset in CTA `rank` of the cluster
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t bar, uint32_t rank) {
+    asm volatile(
+        "{\n.reg .b32 ra;\n"
+        "mapa.shared::cluster.u32 ra, %0, %1;\n"
+        "mbarrier.arrive.release.cluster.shared::cluster.b64 _, [ra];\n}\n" ::"r"(bar), "r"(rank)
+        : "memory");
+}
+__device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity) {   // acquire at cluster scope
+    asm volatile(
+        "{\n.reg .pred p;\n"
+        "WAITC_LOOP:\n"
+        "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra WAITC_DONE;\n"
+        "bra WAITC_LOOP;\n"
+        "WAITC_DONE:\n}\n" ::"r"(bar), "r"(parity)
+        : "memory");
+}
+// TMA load whose completion is counted on the LEADER CTA's barrier (cta_group::2: the barrier may live in the peer CTA;
+// clearing bit 24 of a shared::cluster address selects the even CTA of the pair), so the leader's MMA thread waits on
+// ONE barrier for both halves and no relay thread sits in the operand path
+__device__ __forceinline__ void tma_load_2d_pair(const CUtensorMap *m, uint32_t bar, uint32_t dst, int c0, int c1) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+        ::"r"(dst), "l"(reinterpret_cast<uint64_t>(m)), "r"(bar & 0xFEFFFFFFu), "r"(c0), "r"(c1)
+        : "memory");
+}
+__device__ __forceinline__ void umma_f16_pair(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
+    asm volatile(
+        "{\n.reg .pred p;\nsetp.ne.b32 p, %4, 0;\n"
+        "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n}\n" ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc),
+        "r"(acc)
+        : "memory");
+}
+// completion of all MMAs issued so far -> arrive on the barrier at this offset in BOTH CTAs of the pair
+__device__ __forceinline__ void umma_commit_pair(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(bar),
+                 "h"((uint16_t)3)
+                 : "memory");
+}
+
+template <int NKB, int A_BUFS, int STAGES, bool CONV = false, bool PAIR = false>
 __global__ void __launch_bounds__(CONV ? NT_CONV : NT, 1) vq_tc_kernel(const __grid_constant__ CUtensorMap tmapA,
                                                        const __grid_constant__ CUtensorMap tmapB,
                                                        int64_t n_rows, int n_tiles, int nct, int nk16,
@@ -378,19 +441,24 @@ __global__ void __launch_bounds__(CONV ? NT_CONV : NT, 1) vq_tc_kernel(const __g
                                                        const float *__restrict__ zsrc = nullptr,
                                                        const float *__restrict__ mu = nullptr, int D = 0,
                                                        float *__restrict__ zn_out = nullptr) {
-    using L = SmemLayout<NKB, A_BUFS, STAGES>;
+    static_assert(!(CONV && PAIR), "the pair kernel reads the pre-converted row operand");
+    using L = SmemLayout<NKB, A_BUFS, STAGES, PAIR>;
+    constexpr int BST = L::BST, B_STAGE = L::B_STAGE;
     extern __shared__ uint8_t smem_raw[];
     const uint32_t raw = ptx::smem_u32(smem_raw);
-    const uint32_t base = (raw + 1023u) & ~1023u;
+    const uint32_t base = (raw + 1023u) & ~1023u;      // (the same offset in both CTAs of a pair: same kernel, same layout)
     uint8_t *gen = smem_raw + (base - raw);
     const uint32_t sA = base, sB = base + L::A_BYTES, sBar = base + L::BAR_OFF;
+    const uint32_t rank = PAIR ? cluster_ctarank() : 0u;
     // barrier slots
     auto a_full = [&](int i) { return sBar + 8u * i; };
     auto a_empty = [&](int i) { return sBar + 8u * (A_BUFS + i); };
     auto b_full = [&](int i) { return sBar + 8u * (2 * A_BUFS + i); };
-    auto b_empty = [&](int i) { return sBar + 8u * (2 * A_BUFS + STAGES + i); };
-    auto t_full = [&](int i) { return sBar + 8u * (2 * A_BUFS + 2 * STAGES + i); };
-    auto t_empty = [&](int i) { return sBar + 8u * (2 * A_BUFS + 2 * STAGES + 2 + i); };
+    auto b_empty = [&](int i) { return sBar + 8u * (2 * A_BUFS + BST + i); };
+    auto t_full = [&](int i) { return sBar + 8u * (2 * A_BUFS + 2 * BST + i); };
+    auto t_empty = [&](int i) { return sBar + 8u * (2 * A_BUFS + 2 * BST + 2 + i); };
+    auto a_peer = [&](int i) { return sBar + 8u * (2 * A_BUFS + 2 * BST + 4 + i); };            // PAIR, leader: peer's A tile landed
+    auto b_peer = [&](int i) { return sBar + 8u * (3 * A_BUFS + 2 * BST + 4 + i); };            // PAIR, leader: peer's B half landed
     volatile uint32_t *tmem_ptr = reinterpret_cast<volatile uint32_t *>(gen + L::BAR_OFF + L::NBARS * 8);
     // per-row exchange between the four column parts of a row (in-kernel resolve): ordered key of the row minimum,
     // number of listed elements inside the final window, lowest such code
@@ -404,51 +472,80 @@ __global__ void __launch_bounds__(CONV ? NT_CONV : NT, 1) vq_tc_kernel(const __g
         ptx::tma_prefetch_desc(&tmapA);
         ptx::tma_prefetch_desc(&tmapB);
         for (int i = 0; i < A_BUFS; ++i) { ptx::mbar_init(a_full(i), CONV ? NCW : 1); ptx::mbar_init(a_empty(i), 1); }
-        for (int i = 0; i < STAGES; ++i) { ptx::mbar_init(b_full(i), 1); ptx::mbar_init(b_empty(i), 1); }
-        for (int i = 0; i < 2; ++i) { ptx::mbar_init(t_full(i), 1); ptx::mbar_init(t_empty(i), 4 * NPART); }
+        for (int i = 0; i < BST; ++i) { ptx::mbar_init(b_full(i), 1); ptx::mbar_init(b_empty(i), 1); }
+        // PAIR: the leader's t_empty collects the epilogue warps of BOTH CTAs (the MMAs write both CTAs' TMEM)
+        for (int i = 0; i < 2; ++i) { ptx::mbar_init(t_full(i), 1); ptx::mbar_init(t_empty(i), (PAIR ? 2 : 1) * 4 * NPART); }
+        if (PAIR) {
+            for (int i = 0; i < A_BUFS; ++i) ptx::mbar_init(a_peer(i), 1);
+            for (int i = 0; i < BST; ++i) ptx::mbar_init(b_peer(i), 1);
+        }
         ptx::fence_barrier_init();
     }
-    if (warp == 2) ptx::tmem_alloc<512>(ptx::smem_u32((const void *)tmem_ptr));
+    if (warp == 2) {
+        if (PAIR) {
+            asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(ptx::smem_u32((const void *)tmem_ptr)), "r"(512) : "memory");
+            asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+        } else {
+            ptx::tmem_alloc<512>(ptx::smem_u32((const void *)tmem_ptr));
+        }
+    }
     ptx::tc_fence_before();
-    __syncthreads();
+    if (PAIR) cluster_sync_all(); else __syncthreads();
     ptx::tc_fence_after();
     const uint32_t tmem_base = *tmem_ptr;
+    // PAIR: the pair walks tile pairs (2 tp, 2 tp + 1); a CTA's own tile may lie past the end in the last pair (its rows
+    // then fail row_ok; the row operand of the last real tile is loaded in its place)
+    const int n_units = PAIR ? (n_tiles + 1) / 2 : n_tiles;
+    const int unit0 = PAIR ? (int)(blockIdx.x >> 1) : (int)blockIdx.x, unit_step = PAIR ? (int)(gridDim.x >> 1) : (int)gridDim.x;
+    auto tile_of = [&](int u) { return PAIR ? 2 * u + (int)rank : u; };
 
     if (warp == 0) {
         // ===== TMA producer =====
         if (lane == 0) {
             int st = 0, sph = 0, ab = 0, aph = 0;
-            auto load_a = [&](int tile) {
+            auto load_a = [&](int u) {
+                int tile = tile_of(u);
+                if (tile >= n_tiles) tile = n_tiles - 1;      // PAIR, odd tile count: any valid rows (results are not used)
                 ptx::mbar_wait(a_empty(ab), aph ^ 1);
-                ptx::mbar_arrive_expect_tx(a_full(ab), NKB * A_KB_BYTES);
+                // PAIR: both CTAs' bytes are counted on the leader's barrier; only the leader arms it
+                if (!PAIR || rank == 0) ptx::mbar_arrive_expect_tx(a_full(ab), (PAIR ? 2 : 1) * NKB * A_KB_BYTES);
 #pragma unroll
-                for (int kb = 0; kb < NKB; ++kb)
-                    ptx::tma_load_2d(&tmapA, a_full(ab), sA + (ab * NKB + kb) * A_KB_BYTES, kb * KBLK, tile * BM);
+                for (int kb = 0; kb < NKB; ++kb) {
+                    if (PAIR) tma_load_2d_pair(&tmapA, a_full(ab), sA + (ab * NKB + kb) * A_KB_BYTES, kb * KBLK, tile * BM);
+                    else ptx::tma_load_2d(&tmapA, a_full(ab), sA + (ab * NKB + kb) * A_KB_BYTES, kb * KBLK, tile * BM);
+                }
                 if (++ab == A_BUFS) { ab = 0; aph ^= 1; }
             };
-            if (!CONV && A_BUFS > 1 && (int)blockIdx.x < n_tiles) load_a(blockIdx.x);
-            for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+            if (!CONV && A_BUFS > 1 && unit0 < n_units) load_a(unit0);
+            for (int u = unit0; u < n_units; u += unit_step) {
                 // double-buffered rows: fetch the NEXT tile's rows before streaming this tile's codebook
                 if (!CONV) {
-                    if (A_BUFS > 1) { if (tile + (int)gridDim.x < n_tiles) load_a(tile + gridDim.x); }
-                    else load_a(tile);
+                    if (A_BUFS > 1) { if (u + unit_step < n_units) load_a(u + unit_step); }
+                    else load_a(u);
                 }
                 for (int c = 0; c < nct; ++c)
                     for (int kb = 0; kb < NKB; ++kb) {
                         ptx::mbar_wait(b_empty(st), sph ^ 1);
-                        ptx::mbar_arrive_expect_tx(b_full(st), B_ST_BYTES);
-                        ptx::tma_load_2d(&tmapB, b_full(st), sB + st * B_ST_BYTES, kb * KBLK, c * BN);
-                        if (++st == STAGES) { st = 0; sph ^= 1; }
+                        if (PAIR) {   // this CTA's half of the 256 codes (tmapB then has 128-row boxes)
+                            if (rank == 0) ptx::mbar_arrive_expect_tx(b_full(st), 2 * B_STAGE);
+                            tma_load_2d_pair(&tmapB, b_full(st), sB + st * B_STAGE, kb * KBLK, c * BN + (int)rank * (BN / 2));
+                        } else {
+                            ptx::mbar_arrive_expect_tx(b_full(st), B_STAGE);
+                            ptx::tma_load_2d(&tmapB, b_full(st), sB + st * B_STAGE, kb * KBLK, c * BN);
+                        }
+                        if (++st == BST) { st = 0; sph ^= 1; }
                     }
             }
         }
+    } else if (PAIR && warp == 1 && rank != 0) {
+        // ===== PAIR, second CTA: the leader issues the MMAs for both =====
     } else if (warp == 1) {
         // ===== MMA issuer (one thread) =====
         if (lane == 0) {
             #ifdef LIPVQ_VQ_BF16
-            constexpr uint32_t idesc = ptx::umma_idesc_bf16(BM, BN);
+            constexpr uint32_t idesc = ptx::umma_idesc_bf16(PAIR ? 2 * BM : BM, BN);
 #else
-            constexpr uint32_t idesc = ptx::umma_idesc_f16(BM, BN);
+            constexpr uint32_t idesc = ptx::umma_idesc_f16(PAIR ? 2 * BM : BM, BN);
 #endif
             // The issuing thread is a serial resource: measured (tools/mma_rate_probe.cu) an MMA costs max(50, N/2) cycles
             // when its operands are ready in uniform registers, but 160-235 when descriptor arithmetic, a counted loop
@@ -463,40 +560,51 @@ __global__ void __launch_bounds__(CONV ? NT_CONV : NT, 1) vq_tc_kernel(const __g
                 return d;
             };
             const uint32_t a_lo0 = ((sA >> 4) & 0x3FFFu) | (1u << 16), b_lo0 = ((sB >> 4) & 0x3FFFu) | (1u << 16);
-            constexpr uint32_t A_KB16 = A_KB_BYTES >> 4, B_ST16 = B_ST_BYTES >> 4, A_BUF16 = (uint32_t)NKB * A_KB16;
+            constexpr uint32_t A_KB16 = A_KB_BYTES >> 4, B_ST16 = (uint32_t)B_STAGE >> 4, A_BUF16 = (uint32_t)NKB * A_KB16;
+            auto mma = [&](uint32_t d, uint64_t ad, uint64_t bd, uint32_t acc_flag) {
+                if (PAIR) umma_f16_pair(d, ad, bd, idesc, acc_flag);
+                else ptx::umma_bf16(d, ad, bd, idesc, acc_flag);
+            };
+            auto commit = [&](uint32_t bar) {
+                if (PAIR) umma_commit_pair(bar);
+                else ptx::umma_commit(bar);
+            };
             const int nk_last = nk16 - (NKB - 1) * (KBLK / UK);       // K=16 slices of the last K block (1..4)
             int st = 0, sph = 0, ab = 0, aph = 0, acc = 0, accph = 0;
             uint32_t b_lo = b_lo0, a_buf_lo = a_lo0;
-            for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-                ptx::mbar_wait(a_full(ab), aph);
+            for (int u = unit0; u < n_units; u += unit_step) {
+                if (PAIR) mbar_wait_cluster(a_full(ab), aph);
+                else ptx::mbar_wait(a_full(ab), aph);
                 ptx::tc_fence_after();
                 for (int c = 0; c < nct; ++c) {
-                    ptx::mbar_wait(t_empty(acc), accph ^ 1);
+                    if (PAIR) mbar_wait_cluster(t_empty(acc), accph ^ 1);
+                    else ptx::mbar_wait(t_empty(acc), accph ^ 1);
                     ptx::tc_fence_after();
                     const uint32_t d_tmem = tmem_base + acc * BN;
                     uint32_t a_lo = a_buf_lo;
 #pragma unroll
                     for (int kb = 0; kb < NKB; ++kb) {
-                        ptx::mbar_wait(b_full(st), sph);
+                        if (PAIR) mbar_wait_cluster(b_full(st), sph);
+                        else ptx::mbar_wait(b_full(st), sph);
                         ptx::tc_fence_after();
                         if (kb < NKB - 1 || nk_last == 4) {
-                            ptx::umma_bf16(d_tmem, mk(a_lo), mk(b_lo), idesc, kb ? 1u : 0u);
-                            ptx::umma_bf16(d_tmem, mk(a_lo + 2), mk(b_lo + 2), idesc, 1u);
-                            ptx::umma_bf16(d_tmem, mk(a_lo + 4), mk(b_lo + 4), idesc, 1u);
-                            ptx::umma_bf16(d_tmem, mk(a_lo + 6), mk(b_lo + 6), idesc, 1u);
+                            mma(d_tmem, mk(a_lo), mk(b_lo), kb ? 1u : 0u);
+                            mma(d_tmem, mk(a_lo + 2), mk(b_lo + 2), 1u);
+                            mma(d_tmem, mk(a_lo + 4), mk(b_lo + 4), 1u);
+                            mma(d_tmem, mk(a_lo + 6), mk(b_lo + 6), 1u);
                         } else {
                             for (int k = 0; k < nk_last; ++k)   // +32 B per K=16 slice inside the swizzle row
-                                ptx::umma_bf16(d_tmem, mk(a_lo + 2 * k), mk(b_lo + 2 * k), idesc, (kb | k) ? 1u : 0u);
+                                mma(d_tmem, mk(a_lo + 2 * k), mk(b_lo + 2 * k), (kb | k) ? 1u : 0u);
                         }
-                        ptx::umma_commit(b_empty(st));
+                        commit(b_empty(st));
                         a_lo += A_KB16;
                         b_lo += B_ST16;
-                        if (++st == STAGES) { st = 0; sph ^= 1; b_lo = b_lo0; }
+                        if (++st == BST) { st = 0; sph ^= 1; b_lo = b_lo0; }
                     }
-                    ptx::umma_commit(t_full(acc));
+                    commit(t_full(acc));
                     if (++acc == 2) { acc = 0; accph ^= 1; }
                 }
-                ptx::umma_commit(a_empty(ab));
+                commit(a_empty(ab));
                 a_buf_lo += A_BUF16;
                 if (++ab == A_BUFS) { ab = 0; aph ^= 1; a_buf_lo = a_lo0; }
             }
@@ -611,7 +719,8 @@ __global__ void __launch_bounds__(CONV ? NT_CONV : NT, 1) vq_tc_kernel(const __g
         // set by the operand passes, which finished before this launch (CONV: a row whose own operand left the fp16
         // range is flagged by its converter thread through a negative zn and goes to the exact scan by itself)
         const bool range_bad = __ldg(counters + 3) != 0;
-        for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        for (int u = unit0; u < n_units; u += unit_step) {
+            const int tile = tile_of(u);      // (PAIR: may be n_tiles in the last pair -- every row then fails row_ok)
             const int r_in = quarter * 32 + lane;
             const int64_t row = (int64_t)tile * BM + r_in;
             const bool row_ok = row < n_rows;
@@ -645,7 +754,10 @@ __global__ void __launch_bounds__(CONV ? NT_CONV : NT, 1) vq_tc_kernel(const __g
                     if (b == PW / 32 - 1) {   // accumulator part fully in registers: hand the TMEM stage back
                         ptx::tc_fence_before();
                         __syncwarp();
-                        if (lane == 0) ptx::mbar_arrive(t_empty(acc));
+                        if (lane == 0) {
+                            if (PAIR && rank != 0) mbar_arrive_cluster(t_empty(acc), 0u);   // the leader issues the MMAs for both
+                            else ptx::mbar_arrive(t_empty(acc));
+                        }
                     }
                     float cm[4];
 #pragma unroll
@@ -768,8 +880,11 @@ __global__ void __launch_bounds__(CONV ? NT_CONV : NT, 1) vq_tc_kernel(const __g
         }
     }
     ptx::tc_fence_before();
-    __syncthreads();
-    if (warp == 2) ptx::tmem_dealloc<512>(tmem_base);
+    if (PAIR) cluster_sync_all(); else __syncthreads();      // (PAIR: the peer's barriers and shared memory stay alive until both are done)
+    if (warp == 2) {
+        if (PAIR) asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512) : "memory");
+        else ptx::tmem_dealloc<512>(tmem_base);
+    }
 }
 
 
@@ -980,6 +1095,38 @@ inline Workspace carve(void *ws, const Geometry &g) {
     return w;
 }
 
+// PAIR launch: clusters of two CTAs, an even grid; tb must have 128-row boxes
+template <int NKB, int A_BUFS, int STAGES>
+inline int launch_tc_pair(const CUtensorMap &ta, const CUtensorMap &tb_half, const Geometry &g, const Workspace &w,
+                          int64_t *idx, bool want_d2, cudaStream_t st) {
+    using L = SmemLayout<NKB, A_BUFS, STAGES, true>;
+    auto kern = vq_tc_kernel<NKB, A_BUFS, STAGES, false, true>;
+    LIPVQ_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::TOTAL));
+    const int64_t pairs = (g.n_tiles + 1) / 2;
+    int grid = 2 * (int)(pairs < kNumSMs / 2 ? pairs : kNumSMs / 2);
+    static const int env_grid = [] { const char *e = getenv("LIPVQ_VQ_GRID"); return e ? atoi(e) : 0; }();   // A/B probe
+    if (env_grid > 1 && env_grid < grid) grid = env_grid & ~1;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)grid);
+    cfg.blockDim = dim3(NT);
+    cfg.dynamicSmemBytes = L::TOTAL;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    ProfScope prof("vq_tc_kernel", st);
+    LIPVQ_CUDA_OK(cudaLaunchKernelEx(&cfg, kern, ta, tb_half, (int64_t)g.n, (int)g.n_tiles, g.nct, g.NK16, (const float *)w.zn,
+                                     (const float *)w.emax, OP_ABS * sqrtf((float)g.D), w.cand, w.cand_meta, g.K, idx,
+                                     want_d2 ? 1 : 0, w.resc_list, w.list, w.counters, (const float *)nullptr,
+                                     (const float *)w.mu, g.D, w.zn));
+    LIPVQ_LAUNCH_OK();
+    return LIPVQ_OK;
+}
+
 template <int NKB, int A_BUFS, int STAGES, bool CONV = false>
 inline int launch_tc(const CUtensorMap &ta, const CUtensorMap &tb, const Geometry &g, const Workspace &w,
                      int64_t *idx, bool want_d2, cudaStream_t st, const float *zsrc = nullptr) {
@@ -1043,7 +1190,21 @@ inline int vq_tensor_search(const float *z, const float *E, const tc::Geometry &
         case 5: rc = launch_tc<5, 1, 4, true>(ta, tb, g, w, idx, d2 != nullptr, st, z); break;
         default: break;
     }
-    else switch (g.NKB) {
+    static const int pair_env = [] { const char *e = getenv("LIPVQ_VQ_PAIR"); return e ? atoi(e) : -1; }();   // A/B probe: 0 off, 1 always
+    const bool pair = !conv && g.n_tiles >= 2 && pair_env == 1;   // opt-in: measured no faster, see vq_tc_kernel
+    if (pair) {
+        CUtensorMap tbh;
+        LIPVQ_TRY(make_tmap(&tbh, w.Eb, (uint64_t)g.Kp, (uint64_t)g.DKz, BN / 2, (uint64_t)g.DKp));
+        switch (g.NKB) {
+            case 1: rc = launch_tc_pair<1, 2, 6>(ta, tbh, g, w, idx, d2 != nullptr, st); break;
+            case 2: rc = launch_tc_pair<2, 2, 5>(ta, tbh, g, w, idx, d2 != nullptr, st); break;
+            case 3: rc = launch_tc_pair<3, 2, 4>(ta, tbh, g, w, idx, d2 != nullptr, st); break;
+            case 4: rc = launch_tc_pair<4, 2, 3>(ta, tbh, g, w, idx, d2 != nullptr, st); break;
+            case 5: rc = launch_tc_pair<5, 1, 4>(ta, tbh, g, w, idx, d2 != nullptr, st); break;
+            default: break;
+        }
+    } else if (conv) {
+    } else switch (g.NKB) {
         case 1: rc = launch_tc<1, 2, 6>(ta, tb, g, w, idx, d2 != nullptr, st); break;
         case 2: rc = launch_tc<2, 2, 5>(ta, tb, g, w, idx, d2 != nullptr, st); break;
         case 3: rc = launch_tc<3, 2, 4>(ta, tb, g, w, idx, d2 != nullptr, st); break;

@@ -426,3 +426,35 @@ def test_nograd_fast_path_equals_general_path(n):
     zf, lf, i_f, rf = fast(x)
     assert abs(lf.item() - fw["loss"]) <= RTOL * abs(fw["loss"])
     assert (i_f.cpu().numpy() == fw["idx"]).mean() > 0.999
+
+
+def test_pair_search_matches_oracle():
+    """The opt-in CTA-pair search kernel (cta_group::2, LIPVQ_VQ_PAIR=1; read once per process, hence the subprocess):
+    bit-exact indices outside the 1e-5 gap window against the float64 oracle, odd and even tile counts."""
+    import subprocess, sys, textwrap
+    code = textwrap.dedent("""
+        import ctypes as C, numpy as np, torch
+        from lipvq_vae_b200 import _native as N
+        from oracle import lipvq_oracle as orc
+        lib = N.lib(); dev = torch.device("cuda", 0)
+        for n, D, K in ((128 * 5 + 17, 208, 1024), (4096, 64, 300), (128 * 2, 253, 512)):
+            g = np.random.default_rng(n + D)
+            z = g.random((n, D), dtype=np.float32); E = g.random((K, D), dtype=np.float32)
+            zt, Et = torch.from_numpy(z).to(dev), torch.from_numpy(E).to(dev)
+            idx = torch.full((n,), -1, dtype=torch.int64, device=dev)
+            need = C.c_size_t(0)
+            N.check(lib.lipvq_workspace_bytes(C.byref(N.Dims(1, 1, 1, D, K)), n, C.byref(need)))
+            ws = torch.full((need.value + 4096,), 0xFF, dtype=torch.uint8, device=dev)
+            st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+            N.check(lib.lipvq_vq_argmin(zt.data_ptr(), Et.data_ptr(), n, D, K, 1, idx.data_ptr(), None, None, ws.data_ptr(), ws.numel(), st))
+            torch.cuda.synchronize()
+            i1, d1, d2 = orc.exact_top2(z, E)
+            must = (d2 - d1) > 1e-5 * np.maximum(d1, 1e-30)
+            got = idx.cpu().numpy()
+            assert must.mean() > 0.9 and np.array_equal(got[must], i1[must]), (n, D, K)
+        print("PAIR_OK")
+    """)
+    env = dict(os.environ, LIPVQ_VQ_PAIR="1")
+    r = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=300,
+                       cwd=os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    assert r.returncode == 0 and "PAIR_OK" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
