@@ -9,7 +9,7 @@ from lipvq_vae_b200 import _native as N
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 1 << 20
 K = int(sys.argv[2]) if len(sys.argv) > 2 else 1024
 lib = N.lib(); dev = torch.device("cuda", 0)
-for D in (61, 125, 189, 208, 253, 300):
+for D in [int(v) for v in os.environ.get('PROBE_D', '61,125,189,208,253,300').split(',')]:
     torch.manual_seed(0)
     z = torch.rand(n, D, device=dev); E = torch.rand(K, D, device=dev)
     idx = torch.empty(n, dtype=torch.int64, device=dev)
