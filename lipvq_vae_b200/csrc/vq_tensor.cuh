@@ -156,18 +156,24 @@ __global__ void __launch_bounds__(256) vq_convert_z_warp_kernel(const float *__r
                                                                 int64_t n, int64_t Np, int D, int DKz,
                                                                 op_t *__restrict__ Zb, float *__restrict__ zn,
                                                                 int *__restrict__ counters) {
-    __shared__ float s_mu[5 * KBLK];
-    for (int i = threadIdx.x; i < DKz; i += 256) s_mu[i] = i < D ? mu[i] : 0.f;
-    __syncthreads();
     const int cpr = DKz >> 3, rpw = 32 / cpr, rpb = 8 * rpw;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int rl = lane / cpr, ch = lane - rl * cpr;
     const bool active = rl < rpw, vec = (D & 3) == 0;
     const int d0 = ch * 8;
+    // ncu (round 2): this pass was ISSUE bound (72 % issue-active, 273 instructions per 3 rows), not memory bound.  So: a
+    // thread's 8 means live in registers (its columns never change), chunks that lie wholly inside the row take a
+    // 3-instruction-per-value path (the "1 1 1 | 0" tail only exists in the last chunks), rows past n are written as
+    // zeros on their own, and the row norm is a log-depth segmented tree instead of a cpr-step scan.
+    float mu_r[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) mu_r[i] = (active && d0 + i < D) ? __ldg(mu + d0 + i) : 0.f;
+    const bool full = active && d0 + 8 <= D && vec;      // whole chunk inside the row, 16-byte loads allowed
+    int top = 1;
+    while (top < cpr) top <<= 1;                         // first tree step: top / 2
+    float amax = 0.f;
     bool bad = false;
-    // two row sets per iteration, all loads of both issued before the first use (the pass is a pure stream: what
-    // limits it is the bytes a thread keeps in flight)
-    constexpr int U = 2;
+    constexpr int U = 2;                                 // row sets per iteration: all loads issued before the first use
     const int64_t stride = (int64_t)gridDim.x * rpb;
     for (int64_t r0 = (int64_t)blockIdx.x * rpb; r0 < Np; r0 += U * stride) {
         float4 t[U][2];
@@ -198,15 +204,27 @@ __global__ void __launch_bounds__(256) vq_convert_z_warp_kernel(const float *__r
             float ss = 0.f;
             if (active && r < Np) {
                 float v[8] = {t[u][0].x, t[u][0].y, t[u][0].z, t[u][0].w, t[u][1].x, t[u][1].y, t[u][1].z, t[u][1].w};
+                if (r >= n) {
 #pragma unroll
-                for (int i = 0; i < 8; ++i) {
-                    const int d = d0 + i;
-                    if (r < n && d < D) {
-                        v[i] -= s_mu[d];
+                    for (int i = 0; i < 8; ++i) v[i] = 0.f;   // padding rows of the last tile: all-zero operand
+                } else if (full) {
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        v[i] -= mu_r[i];
                         ss = fmaf(v[i], v[i], ss);
-                        bad |= !(fabsf(v[i]) <= OP_MAX);
-                    } else {
-                        v[i] = (r < n && d < D + 3) ? 1.0f : 0.f;
+                        amax = fmaxf(amax, fabsf(v[i]));
+                    }
+                } else {
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        const int d = d0 + i;
+                        if (d < D) {
+                            v[i] -= mu_r[i];
+                            ss = fmaf(v[i], v[i], ss);
+                            amax = fmaxf(amax, fabsf(v[i]));
+                        } else {
+                            v[i] = d < D + 3 ? 1.0f : 0.f;
+                        }
                     }
                 }
                 __align__(16) op2_t o[4];
@@ -214,14 +232,88 @@ __global__ void __launch_bounds__(256) vq_convert_z_warp_kernel(const float *__r
                 for (int i = 0; i < 4; ++i) o[i] = f2op2(v[2 * i], v[2 * i + 1]);
                 *reinterpret_cast<uint4 *>(Zb + r * DKz + d0) = *reinterpret_cast<const uint4 *>(o);
             }
-            float tsum = ss;                                 // chunk 0 + chunk 1 + ... (fixed order)
-            for (int i = 1; i < cpr; ++i) {
-                const float o = __shfl_down_sync(0xffffffffu, ss, i);
-                if (ch + i < cpr) tsum += o;
+            bad |= !(ss <= 3.0e38f);                          // NaN / inf in the row (fmaxf above drops NaNs)
+            // row norm: segmented tree over the row's cpr lanes (lanes ch < o add lane ch + o; fixed order)
+            float tsum = ss;
+            for (int o = top >> 1; o > 0; o >>= 1) {
+                const float other = __shfl_down_sync(0xffffffffu, tsum, o);
+                if (ch < o && ch + o < cpr) tsum += other;
             }
             if (active && ch == 0 && r < n) zn[r] = sqrtf(tsum);
         }
     }
+    bad |= !(amax <= OP_MAX);
+    if (__any_sync(0xffffffffu, bad) && lane == 0) atomicOr(counters + 3, 1);   // operand out of range -> exact search
+}
+
+// Rows wider than 32 chunks (D + 3 > 256): one warp per row, a lane takes chunks lane and lane + 32, the row norm is a
+// full-warp shuffle tree.  (The block-wide kernel below, which this replaces for 33 <= cpr <= 64, synchronised the block
+// once per 7 rows and ran at 2.4 TB/s.)
+__global__ void __launch_bounds__(256) vq_convert_z_wide_kernel(const float *__restrict__ z, const float *__restrict__ mu,
+                                                                int64_t n, int64_t Np, int D, int DKz,
+                                                                op_t *__restrict__ Zb, float *__restrict__ zn,
+                                                                int *__restrict__ counters) {
+    const int cpr = DKz >> 3;                    // 33 .. 64
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const bool vec = (D & 3) == 0;
+    float mu_r[2][8];
+#pragma unroll
+    for (int c = 0; c < 2; ++c)
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const int d = (lane + 32 * c) * 8 + i;
+            mu_r[c][i] = d < D ? __ldg(mu + d) : 0.f;
+        }
+    float amax = 0.f;
+    bool bad = false;
+    const int64_t stride = (int64_t)gridDim.x * 8;
+    for (int64_t r = (int64_t)blockIdx.x * 8 + warp; r < Np; r += stride) {
+        float4 t[2][2];
+#pragma unroll
+        for (int c = 0; c < 2; ++c)
+#pragma unroll
+            for (int q = 0; q < 2; ++q) {
+                const int d = (lane + 32 * c) * 8 + 4 * q;
+                t[c][q] = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (r < n && d < D) {
+                    const float *p = z + r * D + d;
+                    if (vec) t[c][q] = __ldg(reinterpret_cast<const float4 *>(p));
+                    else {
+                        t[c][q].x = __ldg(p);
+                        if (d + 1 < D) t[c][q].y = __ldg(p + 1);
+                        if (d + 2 < D) t[c][q].z = __ldg(p + 2);
+                        if (d + 3 < D) t[c][q].w = __ldg(p + 3);
+                    }
+                }
+            }
+        float ss = 0.f;
+#pragma unroll
+        for (int c = 0; c < 2; ++c) {
+            const int ch = lane + 32 * c, d0 = ch * 8;
+            if (ch >= cpr) continue;
+            float v[8] = {t[c][0].x, t[c][0].y, t[c][0].z, t[c][0].w, t[c][1].x, t[c][1].y, t[c][1].z, t[c][1].w};
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const int d = d0 + i;
+                if (r >= n) v[i] = 0.f;
+                else if (d < D) {
+                    v[i] -= mu_r[c][i];
+                    ss = fmaf(v[i], v[i], ss);
+                    amax = fmaxf(amax, fabsf(v[i]));
+                } else {
+                    v[i] = d < D + 3 ? 1.0f : 0.f;
+                }
+            }
+            __align__(16) op2_t o[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) o[i] = f2op2(v[2 * i], v[2 * i + 1]);
+            *reinterpret_cast<uint4 *>(Zb + r * DKz + d0) = *reinterpret_cast<const uint4 *>(o);
+        }
+        bad |= !(ss <= 3.0e38f);
+        ss = warp_sum(ss);
+        if (lane == 0 && r < n) zn[r] = sqrtf(ss);
+    }
+    bad |= !(amax <= OP_MAX);
     if (__any_sync(0xffffffffu, bad) && lane == 0) atomicOr(counters + 3, 1);   // operand out of range -> exact search
 }
 
@@ -1258,6 +1350,8 @@ inline int vq_tensor_launch(const float *z, const float *E, int64_t n, int D, in
         ProfScope prof("vq_convert_z_kernel", st);
         if (cpr <= 32)
             vq_convert_z_warp_kernel<<<(unsigned)blocks, 256, 0, st>>>(z, w.mu, n, g.Np, D, g.DKz, w.Zb, w.zn, w.counters);
+        else if (cpr <= 64)
+            vq_convert_z_wide_kernel<<<(unsigned)(8 * kNumSMs), 256, 0, st>>>(z, w.mu, n, g.Np, D, g.DKz, w.Zb, w.zn, w.counters);
         else
             vq_convert_z_kernel<<<(unsigned)blocks, 256, 0, st>>>(z, w.mu, n, g.Np, D, g.DKz, w.Zb, w.zn, w.counters);
         LIPVQ_LAUNCH_OK();

@@ -125,7 +125,7 @@ def test_quantizer_vs_reference_golden(case, mode):
 
 @pytest.mark.parametrize("mode", MODES)
 @pytest.mark.parametrize("n,D,K", [(1, 64, 128), (77, 36, 100), (1000, 100, 1000), (4097, 208, 1024),
-                                   (513, 787, 128), (300, 256, 4096), (200, 16, 3), (64, 8, 1)])
+                                   (513, 787, 128), (300, 256, 4096), (1029, 301, 700), (200, 16, 3), (64, 8, 1)])
 def test_search_vs_oracle_shapes(n, D, K, mode):
     """ragged sizes: rows not a multiple of the tile, D not a multiple of 4/16/64, tiny K."""
     from lipvq_vae_b200 import LFQQuantizer
