@@ -610,12 +610,14 @@ __global__ void __launch_bounds__(CONV ? NT_CONV : NT, 1) vq_tc_kernel(const __g
             };
             if (!CONV && A_BUFS > 1 && unit0 < n_units) load_a(unit0);
             for (int u = unit0; u < n_units; u += unit_step) {
-                // double-buffered rows: fetch the NEXT tile's rows before streaming this tile's codebook
-                if (!CONV) {
-                    if (A_BUFS > 1) { if (u + unit_step < n_units) load_a(u + unit_step); }
-                    else load_a(u);
-                }
-                for (int c = 0; c < nct; ++c)
+                if (!CONV && A_BUFS == 1) load_a(u);
+                for (int c = 0; c < nct; ++c) {
+                    // double-buffered rows: the NEXT tile's rows are fetched after this tile's first accumulator has its
+                    // codebook stages in flight.  Fetching them first (as this loop did) parks the producer on a_empty
+                    // -- the previous tile's last MMAs -- with an EMPTY codebook ring, and every tile then starts with a
+                    // TMA round trip nobody overlaps: the ~570 cycles per accumulator that tools/vq_shape_probe.py shows on
+                    // top of the MMAs themselves.
+                    if (!CONV && A_BUFS > 1 && c == (nct > 1 ? 1 : 0) && u + unit_step < n_units) load_a(u + unit_step);
                     for (int kb = 0; kb < NKB; ++kb) {
                         ptx::mbar_wait(b_empty(st), sph ^ 1);
                         if (PAIR) {   // this CTA's half of the 256 codes (tmapB then has 128-row boxes)
@@ -627,6 +629,7 @@ __global__ void __launch_bounds__(CONV ? NT_CONV : NT, 1) vq_tc_kernel(const __g
                         }
                         if (++st == BST) { st = 0; sph ^= 1; }
                     }
+                }
             }
         }
     } else if (PAIR && warp == 1 && rank != 0) {
