@@ -469,7 +469,7 @@ __device__ __forceinline__ float fkey_inv(unsigned k) {
 // ~570 + 185 cycles per MMA and accumulator in the one-CTA kernel (D = 253: 3 535 cycles for 16 MMAs) and the same in the
 // pair (3 452) -- 185 cycles per 128 x 256 x 16 MMA is what this B200 sustains on streamed operands (69 % of the nominal
 // 128; cuBLAS's measured burst peak is the same 69 % of nominal), whatever the ring depth, the issue loop or the B
-// bytes per SM.  Parity-tested (tests/test_gpu_scale_parity.py::test_pair_search_matches_oracle); not the default
+// bytes per SM.  Parity-tested (tests/test_gpu_scale_parity.py, the pair-search test); not the default
 // because it is no faster (269 vs 263 us in the forward).
 __device__ __forceinline__ uint32_t cluster_ctarank() {
     uint32_t r;
