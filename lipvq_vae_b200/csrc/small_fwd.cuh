@@ -333,21 +333,24 @@ __global__ void __launch_bounds__(ST, 1) small_forward_kernel(
             return (const float *)d;
         };
         w0 = put_rows(p.enc0_w, H1, F); b0 = put(p.enc0_b, H1); w1 = put_rows(p.enc2_w, H, H1); b1 = put(p.enc2_b, H);
+        cp_async_commit();               // group 1: the two MLP layers (37 KB) ...
         wl = put_rows(p.lat_W, D, H); bl = put(p.lat_b, D); cl = put(p.lat_ci, D);
-        cp_async_commit();
-        cp_async_wait<0>();
+        cp_async_commit();               // ... group 2: the Lipschitz layer (108 KB) keeps landing while they run
+        cp_async_wait<1>();
     }
     __syncthreads();
     if (TPN) {
         rows_layer_tpn<ACT_GELU, false>(w0, wpitch(F), b0, nullptr, H1, F, s_x, F, s_h1, H1, s_scr, nullptr, 0);
         __syncthreads();
         rows_layer_tpn<ACT_GELU, false>(w1, wpitch(H1), b1, nullptr, H, H1, s_h1, H1, s_h2, H, s_scr, nullptr, 0);
+        if (STAGED) cp_async_wait<0>();
         __syncthreads();
         rows_layer_tpn<ACT_SIGMOID, true>(wl, wpitch(H), bl, cl, D, H, s_h2, H, s_z, ZP, s_scr, nullptr, 0);
     } else {
         rows_layer<ACT_GELU>(w0, b0, H1, F, s_x, s_h1, nullptr, 0);
         __syncthreads();
         rows_layer<ACT_GELU>(w1, b1, H, H1, s_h1, s_h2, nullptr, 0);
+        if (STAGED) cp_async_wait<0>();
         __syncthreads();
         lipschitz_rows_layer(wl, bl, cl, D, H, s_h2, s_z, ZP);
     }
@@ -495,9 +498,11 @@ __global__ void __launch_bounds__(ST, 1) small_forward_kernel(
             q += n_out * wpitch(k_in);
             return (const float *)d;
         };
-        v0 = put_rows(p.dec0_w, H1, D); c0 = put(p.dec0_b, H1); v1 = put_rows(p.dec2_w, H, H1); c1 = put(p.dec2_b, H);
+        v0 = put_rows(p.dec0_w, H1, D); c0 = put(p.dec0_b, H1);
+        cp_async_commit();               // group 1 lands while the gather below runs ...
+        v1 = put_rows(p.dec2_w, H, H1); c1 = put(p.dec2_b, H);
         vo = put_rows(p.out_w, F, H); co = put(p.out_b, F);
-        cp_async_commit();               // (lands while the gather below runs)
+        cp_async_commit();               // ... group 2 while the first decoder layer does
     }
     float sq = 0.f;
     for (int i = tid; i < SR * D; i += ST) {
@@ -510,10 +515,11 @@ __global__ void __launch_bounds__(ST, 1) small_forward_kernel(
             sq = fmaf(df, df, sq);
         }
     }
-    if (STAGED) cp_async_wait<0>();
+    if (STAGED) cp_async_wait<1>();
     __syncthreads();
     if (TPN) {
         rows_layer_tpn<ACT_GELU, false>(v0, wpitch(D), c0, nullptr, H1, D, s_q, D, s_c1, H1, s_scr, nullptr, 0);
+        if (STAGED) cp_async_wait<0>();
         __syncthreads();
         rows_layer_tpn<ACT_GELU, false>(v1, wpitch(H1), c1, nullptr, H, H1, s_c1, H1, s_c2, H, s_scr, nullptr, 0);
         __syncthreads();
@@ -521,6 +527,7 @@ __global__ void __launch_bounds__(ST, 1) small_forward_kernel(
                                         x_recon ? x_recon + (size_t)r0 * F : nullptr, rows_valid);
     } else {
         rows_layer<ACT_GELU>(v0, c0, H1, D, s_q, s_c1, nullptr, 0);
+        if (STAGED) cp_async_wait<0>();
         __syncthreads();
         rows_layer<ACT_GELU>(v1, c1, H, H1, s_c1, s_c2, nullptr, 0);
         __syncthreads();
