@@ -30,6 +30,7 @@ def test_header_symbols_exported(native):
     assert h.lipvq_abi_version() == 6
     h.lipvq_strerror.restype = ctypes.c_char_p
     assert h.lipvq_strerror(-4) == b"workspace too small"
+    assert b"limit" in h.lipvq_strerror(-6)          # LIPVQ_ELIMIT: the allocation-free entry point's size cap
 
 
 def test_workspace_query_and_arg_checks(native):
